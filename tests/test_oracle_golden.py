@@ -1,0 +1,79 @@
+"""CPU: the oracle restatement against the golden vectors produced by the unmodified reference
+(oracle/make_golden.py).  This is what pins the oracle on machines without /root/reference."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import checkers as C
+from oracle import onf as O
+from oracle import sampling as S
+from oracle.planner import RecordedSource
+
+import _util as U
+
+
+def test_checker_labels_bit_exact():
+    fx = U.load("checkers.npz")
+    poses, sb, car = fx["poses"], fx["obstacles_sbend"], fx["obstacles_car"]
+    b = (0, 3, 0, 3)
+    assert np.array_equal(C.circle_labels(poses, sb, 0.3, b), fx["circle_sbend"])
+    assert np.array_equal(C.circle_labels(poses, car, 0.3, b), fx["circle_directed_car"])
+    assert np.array_equal(C.circle_labels(poses, car, 0.25, None), fx["circle_car_nobounds"])
+    assert np.array_equal(C.rectangle_labels(poses, car, (-0.3, 0.2, -0.3, 0.2), b), fx["rect_car"])
+    assert np.array_equal(C.rectangle_labels(poses, sb, (-0.2, 0.2, -0.2, 0.2), b), fx["rect_sbend"])
+    assert np.array_equal(C.boundary_labels(poses[:, :2], b), fx["boundary_only"])
+    ox, oy, cell = fx["grid_meta"]
+    assert np.array_equal(C.grid_labels(fx["grid_poses"], fx["grid"], ox, oy, cell), fx["grid_labels"])
+
+
+@pytest.mark.parametrize("name", ["holonomic", "car", "image"])
+def test_onf_forward_backward(name):
+    fx = U.load("onf.npz")
+    cfg = U.ONF_CFGS[name]
+    w = torch.tensor(fx[f"{name}/w"])
+    x, y = torch.tensor(fx[f"{name}/x"]), torch.tensor(fx[f"{name}/y"])
+    z, cache = O.onf_forward(w, cfg, x)
+    assert U.relerr(z, fx[f"{name}/z"]) < 1e-5
+    _, gz = O.bce_with_logits_grad(z, y)
+    gz = gz + 0.01 * torch.sigmoid(z)
+    gw, gx = O.onf_backward(w, cfg, cache, gz)
+    assert U.relerr(gw, fx[f"{name}/gw"]) < 1e-5
+    assert U.relerr(gx, fx[f"{name}/gx"]) < 1e-5
+
+
+def test_legacy_choice_indices_bit_exact():
+    fx = U.load("choice.npz")
+    for case in sorted({k.split("/")[0] for k in fx.files}):
+        reader = S.UniformReader(fx[f"{case}/u"])
+        idx = S.legacy_choice(fx[f"{case}/p"], 100, case.endswith("_1"), reader)
+        assert np.array_equal(idx, fx[f"{case}/idx"]), case
+        assert reader.used == len(fx[f"{case}/u"])
+
+
+@pytest.mark.parametrize("name", ["car", "corridor", "holonomic"])
+def test_lockstep_against_reference_states(name):
+    fx = U.load(f"lockstep_{name}.npz")
+    for k in fx["meta/steps"]:
+        op = U.oracle_planner(name, fx, f"step{k}/before")
+        var = U.variates_from(fx, f"step{k}/var")
+        op.step(RecordedSource(var))
+        after = U.state_from(fx, f"step{k}/after")
+        assert np.array_equal(op.last["train_labels"], fx[f"step{k}/labels"])
+        assert np.array_equal(op.last["train_positions"], fx[f"step{k}/checked"])
+        if "choice_idx" in var:
+            assert np.array_equal(op.last["choice_idx"], var["choice_idx"])
+        for key in ["w", "m", "v", "traj", "traj_m", "traj_v", "lam", "mu", "buf_pos", "buf_age"]:
+            assert U.relerr(op.state[key], after[key]) < 2e-6, (k, key)
+        for key in ["onf_step", "traj_step", "step_count"]:
+            assert op.state[key] == after[key]
+
+
+@pytest.mark.parametrize("name", ["car", "corridor", "holonomic"])
+def test_short_free_run_matches_reference_path(name):
+    """10 steps from the reference's initial state with the reference's variates (the loop is chaotic beyond
+    that); tolerance = north_star's path tolerance 1e-2 m / 1e-2 rad with margin."""
+    fx = U.load(f"lockstep_{name}.npz")
+    op = U.oracle_planner(name, fx, "free/state0")
+    for k in range(10):
+        op.step(RecordedSource(U.variates_from(fx, f"free/var{k}")))
+        assert np.abs(op.get_path() - fx[f"free/path{k}"]).max() < 1e-3, k
