@@ -1,0 +1,193 @@
+/*
+ * nfopp.h - C ABI of libnfopp.so: the B200-native (sm_100a) NFOPP optimisation inner loop.
+ *
+ * The reference (MisterMap/pytorch-motion-planner) is pure Python/PyTorch and has no FFI for this path;
+ * each entry point below therefore cites the reference *Python* interface it replaces
+ * (paths relative to the reference root, neural_field_optimal_planner/...).  The host side that
+ * mirrors the reference's classes lives in pytorch-motion-planner_b200/nfopp_b200 and binds this
+ * header through ctypes (INTEGRATION.md shows the stub a reference maintainer would add).
+ *
+ * Conventions
+ *  - every function returns 0 on success or a negative nfopp_status; nfopp_last_error() gives the text
+ *    (thread-local).  No exceptions, no torch types: plain pointers and sizes only.
+ *  - every pointer named *_dev is a DEVICE pointer on the current CUDA device; the library never
+ *    allocates device memory - the caller (PyTorch, for device memory and streams) owns all buffers.
+ *  - `stream` is a cudaStream_t passed as void*; all work is asynchronous with respect to it.
+ *  - "problems" (P) are independent planning problems, each with its own ONF weights, trajectory,
+ *    environment and RNG stream; arrays are problem-major and contiguous.
+ */
+#ifndef NFOPP_H
+#define NFOPP_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NFOPP_ABI_VERSION 1
+#define NFOPP_MAX_LAYERS 8
+
+typedef enum {
+    NFOPP_OK = 0,
+    NFOPP_ERR_INVALID = -1,     /* bad argument / unsupported configuration */
+    NFOPP_ERR_CUDA = -2,        /* a CUDA runtime call failed */
+    NFOPP_ERR_WORKSPACE = -3,   /* workspace too small or misaligned */
+    NFOPP_ERR_NAME = -4         /* unknown buffer name */
+} nfopp_status;
+
+/* ---- occupancy neural field (onf_model.py:8-31, angle_encoder.py:7-13) ---------------------------- */
+typedef struct {
+    float mean, sigma;          /* onf_model.py:27-28,38 */
+    int32_t use_cos;            /* onf_model.py:14,40-43: 200 Fourier features (sin|cos) instead of 100 (sin) */
+    int32_t angle;              /* onf_model.py:11-13: 20 heading features, input is (x,y,theta) */
+    int32_t hidden;             /* width of the hidden layers (100 in the reference); multiple of 4 */
+    int32_t layers;             /* number of hidden Linear+ReLU layers (2 in the reference), <= NFOPP_MAX_LAYERS */
+    int32_t bias;               /* onf_model.py:29: encoding_layer bias present */
+} nfopp_onf_config;
+
+/* Packed float32 parameter blob of one ONF (every segment starts on a multiple of 4 floats):
+ *   enc_w [F_pos,2] | enc_b [F_pos] | ang_b [A] | ang_f [A] | W_0 [H,F_in] | b_0 [H] | W_l [H,H] | b_l [H] ...
+ *   | w_out [H+F_in] | b_out [1]              (row-major, same element order as torch's nn.Linear.weight) */
+typedef struct {
+    int32_t f_pos, n_angle, f_in, in_dim;
+    int32_t off_enc_w, off_enc_b, off_ang_b, off_ang_f;
+    int32_t off_w[NFOPP_MAX_LAYERS], off_b[NFOPP_MAX_LAYERS];
+    int32_t off_w_out, off_b_out;
+    int32_t n_params;           /* blob length in floats (multiple of 4) */
+} nfopp_onf_layout;
+
+int nfopp_abi_version(void);
+const char *nfopp_last_error(void);
+int nfopp_onf_get_layout(const nfopp_onf_config *cfg, nfopp_onf_layout *out);
+
+/* ---- K1: ground-truth collision labelling (float64, bit-exact w.r.t. numpy) ----------------------- */
+/* poses_dev: [P, n, pose_dim] float64 (pose_dim 2 or 3); labels_dev: [P, n] uint8 (0/1).
+ * obstacles_dev: [P_env, m_max, 2] float64 with obstacle_count_dev [P_env] int32 (NULL => all m_max);
+ * P_env is 1 (shared by all problems) or P.  bounds: (x0,x1,y0,y1) or NULL for "no boundaries". */
+
+/* collision_checker/collision_checker.py:9-19 (base class: boundary only) */
+int nfopp_label_boundary(const double *poses_dev, int P, int n, int pose_dim, const double *bounds,
+                         uint8_t *labels_dev, void *stream);
+/* collision_checker/circle_collision_checker.py:11-14; circle_directed_collision_checker.py:5-6 */
+int nfopp_label_circle(const double *poses_dev, int P, int n, int pose_dim, const double *obstacles_dev,
+                       const int32_t *obstacle_count_dev, int P_env, int m_max, double radius,
+                       const double *bounds, uint8_t *labels_dev, void *stream);
+/* collision_checker/rectangle_collision_checker.py:11-26 + utils/position2.py:91-94; box=(x0,x1,y0,y1) */
+int nfopp_label_rectangle(const double *poses_dev, int P, int n, const double *obstacles_dev,
+                          const int32_t *obstacle_count_dev, int P_env, int m_max, const double *box,
+                          const double *bounds, uint8_t *labels_dev, void *stream);
+/* notebooks/onf_planner_image_map.ipynb:65-80 (MapCollisionChecker); grid_dev: [P_env, rows, cols] uint8 */
+int nfopp_label_grid(const double *poses_dev, int P, int n, int pose_dim, const uint8_t *grid_dev, int P_env,
+                     int rows, int cols, double origin_x, double origin_y, double cell, const double *bounds,
+                     uint8_t *labels_dev, void *stream);
+
+/* ---- K2: ONF forward / backward with per-problem weights (onf_model.py:33-50) ---------------------- */
+/* weights_dev [P, n_params]; x_dev [P, n, in_dim] float32; count_dev [P] int32 = valid points per problem
+ * (NULL => n); z_dev [P, n] logits.  `impl`: 0 = auto, 1 = FMA (CUDA-core fp32), 2 = tensor (tcgen05). */
+int nfopp_onf_forward(const nfopp_onf_config *cfg, const float *weights_dev, const float *x_dev,
+                      const int32_t *count_dev, int P, int n, float *z_dev, int impl, void *stream);
+
+/* gbar_mode selects dL/dz:
+ *   0 external : gz_dev [P,n] given (what autograd hands ONF.backward)
+ *   1 bce      : (sigmoid(z) - y)/count, y = aux_dev [P,n]           nerf_opt_planner.py:25,85-89
+ *   2 path     : w_c*sigmoid(z)                                      nerf_opt_planner.py:159,166-169
+ *   3 path_mu  : w_c*softplus_beta'(z) + aux*(1-tanh(z)^2), aux=mu~  constrained_nerf_opt_planner.py:82-89
+ * Outputs (each may be NULL): z_dev [P,n]; gx_dev [P,n,in_dim]; gpart_dev [P, tiles, n_params] per-tile
+ * partial weight gradients (tiles = nfopp_onf_tiles(cfg, n)), reduced in fixed order by nfopp_onf_adam /
+ * nfopp_onf_reduce_grad.  x_dev rows have in_dim columns. */
+int nfopp_onf_tiles(const nfopp_onf_config *cfg, int n);   /* point tiles per problem for n points */
+int nfopp_onf_backward(const nfopp_onf_config *cfg, const float *weights_dev, const float *x_dev,
+                       const int32_t *count_dev, int P, int n, int gbar_mode, const float *gz_dev,
+                       const float *aux_dev, float collision_weight, float beta, float *z_dev, float *gx_dev,
+                       float *gpart_dev, int impl, void *stream);
+/* sums the per-tile partials [P, tiles, n_params] into grad_dev [P, n_params] (fixed order) */
+int nfopp_onf_reduce_grad(const nfopp_onf_config *cfg, const float *gpart_dev, const int32_t *count_dev, int P,
+                          int n, float *grad_dev, void *stream);
+/* torch.optim.Adam single-tensor update (planner_factory.py:54,56,68,70) over [P, n_params]; `step` is the
+ * 1-based index of this update; gpart_dev is what nfopp_onf_backward wrote for the same cfg and n. */
+int nfopp_onf_adam(const nfopp_onf_config *cfg, float *weights_dev, float *m_dev, float *v_dev,
+                   const float *gpart_dev, const int32_t *count_dev, int P, int n, int step, double lr,
+                   double beta1, double beta2, double eps, void *stream);
+
+/* numpy legacy RandomState.choice(n, size, replace, p) on given uniforms (nerf_opt_planner.py:131).
+ * p_dev [P, n] float64 (normalised), u_dev [P, n_u] float64; idx_dev [P, size] int32; used_dev [P] int32 =
+ * uniforms consumed (negative => stream exhausted). */
+int nfopp_choice(const double *p_dev, int P, int n, int size, int replace, const double *u_dev, int n_u,
+                 int32_t *idx_dev, int32_t *used_dev, void *stream);
+
+/* ---- the planner engine: P independent NFOPP problems stepped together -------------------------- */
+typedef struct {
+    nfopp_onf_config onf;
+    int32_t problems;                   /* P */
+    int32_t constrained;                /* 0: NERFOptPlanner (x,y)   1: ConstrainedNERFOptPlanner (x,y,theta) */
+    int32_t trajectory_length;          /* T (planner_factory.py:15,55,69) */
+    /* optimisers (planner_factory.py:54-56,68-70) */
+    double onf_lr, onf_beta1, onf_beta2, traj_lr, traj_beta1, traj_beta2, adam_eps;
+    /* NERFOptPlanner.__init__ (nerf_opt_planner.py:11-14) */
+    double trajectory_random_offset, course_random_offset;
+    float collision_weight;
+    int32_t init_collision_points, reparametrize_trajectory_freq, optimize_collision_model_freq,
+        random_field_points, collision_point_count;
+    /* ConstrainedNERFOptPlanner.__init__ (constrained_nerf_opt_planner.py:13-18) */
+    double angle_offset;
+    float angle_weight, constraint_deltas_weight, multipliers_lr, boundary_weight, collision_multipliers_lr,
+        collision_beta, direction_delta_weight;
+    /* collision checker (collision_checker/*.py): 0 boundary only, 1 circle, 2 rectangle, 3 grid */
+    int32_t checker_kind;
+    int32_t env_shared;                 /* 1: one obstacle set / grid for all problems, 0: one per problem */
+    int32_t max_obstacles;              /* m_max (circle / rectangle) */
+    int32_t grid_rows, grid_cols;       /* grid checker */
+    double grid_origin_x, grid_origin_y, grid_cell;
+    double robot_radius;                /* circle */
+    double box[4];                      /* rectangle */
+    int32_t has_bounds;
+    double bounds[4];                   /* checker boundaries (x0,x1,y0,y1) */
+    double border[4];                   /* sampling / boundary-loss border = init(..., boundaries) */
+    /* randomness: 0 = on-device Philox4x32-10 (throughput), 1 = variates injected by the host (parity) */
+    int32_t rng_mode;
+    uint64_t seed;
+    int32_t max_choice_uniforms;        /* per problem per step, injected mode */
+    int32_t onf_impl;                   /* 0 auto, 1 FMA, 2 tensor */
+} nfopp_planner_config;
+
+typedef struct nfopp_engine nfopp_engine;
+
+/* Bytes of device workspace the engine needs (256-byte aligned).  The caller allocates it (torch.empty). */
+int nfopp_engine_workspace_bytes(const nfopp_planner_config *cfg, size_t *bytes);
+/* Replaces the constructors NERFOptPlanner.__init__ / ConstrainedNERFOptPlanner.__init__
+ * (nerf_opt_planner.py:11-43, constrained_nerf_opt_planner.py:13-40) for P problems at once. */
+int nfopp_engine_create(const nfopp_planner_config *cfg, void *workspace_dev, size_t workspace_bytes,
+                        nfopp_engine **out);
+int nfopp_engine_destroy(nfopp_engine *e);
+/* Named state / IO buffers inside the workspace (device pointer, byte size, dtype tag 'f','d','i','b' and up
+ * to 3 dims).  The host wraps them as tensors: this is export_state()/import_state() and the place where
+ * environments, start/goal, initial weights and (parity mode) variates are written.  Names: see DESIGN.md. */
+int nfopp_engine_buffer(nfopp_engine *e, const char *name, void **ptr_dev, size_t *bytes, char *dtype,
+                        int32_t dims[3]);
+int nfopp_engine_buffer_count(nfopp_engine *e);
+const char *nfopp_engine_buffer_name(nfopp_engine *e, int index);
+/* Host-side counters (the reference keeps them as Python ints / optimizer state):
+ * which: 0 = step_count (nerf_opt_planner.py:35), 1 = ONF Adam step, 2 = trajectory Adam step,
+ *        3 = has_previous_trajectory (nerf_opt_planner.py:37,79-82) */
+int nfopp_engine_get_counter(nfopp_engine *e, int which, int64_t *value);
+int nfopp_engine_set_counter(nfopp_engine *e, int which, int64_t value);
+/* NERFOptPlanner._init_collision_model (nerf_opt_planner.py:197-200): `iterations` ONF training steps on
+ * init_collision_points uniform field points each. */
+int nfopp_engine_warmup(nfopp_engine *e, int iterations, void *stream);
+/* NERFOptPlanner.step (nerf_opt_planner.py:60-71) / the constrained overrides, `n_steps` times for all P
+ * problems.  use_graph != 0 replays a captured CUDA graph of one step (Philox mode only). */
+int nfopp_engine_step(nfopp_engine *e, int n_steps, int use_graph, void *stream);
+/* NERFOptPlanner.get_path / full_trajectory (nerf_opt_planner.py:73-74,178-179): [P, T+2, D] float32 */
+int nfopp_engine_get_paths(nfopp_engine *e, float *paths_dev, void *stream);
+/* NERFOptPlanner.reparametrize_trajectory (nerf_opt_planner.py:224-244; constrained:132-171) on the stored
+ * trajectories and multipliers of all problems, outside a step (update_goal_point / update_start_point). */
+int nfopp_engine_reparametrize(nfopp_engine *e, void *stream);
+/* number of kernel launches issued by this engine so far (bench.py's gpu_launches) */
+int nfopp_engine_launch_count(nfopp_engine *e, int64_t *launches);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NFOPP_H */

@@ -1,0 +1,555 @@
+// engine.cu - the C ABI of libnfopp.so (include/nfopp.h): stateless ONF / Adam entry points and the planner
+// engine that sequences one NFOPP step as a handful of launches (optionally replayed as a CUDA graph).
+#include <math.h>
+#include <stdarg.h>
+
+#include <string>
+#include <vector>
+
+#include "onf.cuh"
+
+namespace nfopp {
+
+static thread_local char g_error[512] = "";
+void set_error(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_error, sizeof(g_error), fmt, ap);
+    va_end(ap);
+}
+
+static int align4(int n) { return (n + 3) / 4 * 4; }
+
+int make_onf_dims(const nfopp_onf_config *c, OnfDims *out) {
+    NFOPP_REQUIRE(c && out, "onf config missing");
+    NFOPP_REQUIRE(c->hidden >= 4 && c->hidden % 4 == 0, "onf: hidden=%d must be a positive multiple of 4", c->hidden);
+    NFOPP_REQUIRE(c->layers >= 1 && c->layers <= NFOPP_MAX_LAYERS, "onf: layers=%d out of range", c->layers);
+    NFOPP_REQUIRE(c->sigma != 0.f, "onf: sigma must be non-zero");
+    OnfDims d{};
+    nfopp_onf_layout &L = d.lay;
+    L.f_pos = c->use_cos ? 200 : 100;          // onf_model.py:14
+    L.n_angle = c->angle ? 20 : 0;             // angle_encoder.py:7,20-22
+    L.f_in = L.f_pos + L.n_angle;
+    L.in_dim = c->angle ? 3 : 2;
+    int off = 0;
+    L.off_enc_w = off; off = align4(off + L.f_pos * 2);
+    L.off_enc_b = off; off = align4(off + L.f_pos);
+    L.off_ang_b = off; off = align4(off + L.n_angle);
+    L.off_ang_f = off; off = align4(off + L.n_angle);
+    for (int l = 0; l < c->layers; ++l) {
+        int k = l == 0 ? L.f_in : c->hidden;
+        L.off_w[l] = off; off = align4(off + c->hidden * k);
+        L.off_b[l] = off; off = align4(off + c->hidden);
+    }
+    L.off_w_out = off; off = align4(off + c->hidden + L.f_in);
+    L.off_b_out = off; off = align4(off + 1);
+    L.n_params = off;
+    d.mean = c->mean; d.sigma = c->sigma; d.use_cos = c->use_cos; d.angle = c->angle;
+    d.H = c->hidden; d.L = c->layers; d.bias = c->bias;
+    *out = d;
+    return NFOPP_OK;
+}
+
+// from sample.cu / traj.cu
+int launch_sample_pre(const EngineDev &e, cudaStream_t s);
+int launch_warm_sample(const EngineDev &e, int iteration, cudaStream_t s);
+int launch_resample_label(const EngineDev &e, int resample, cudaStream_t s);
+int resample_prepare(const EngineDev &e);
+int traj_prepare(const EngineDev &e);
+int launch_traj_pre(const EngineDev &e, cudaStream_t s);
+int launch_traj_post(const EngineDev &e, cudaStream_t s);
+int launch_tick(const EngineDev &e, bool warm, cudaStream_t s);
+int launch_paths(const EngineDev &e, float *out, cudaStream_t s);
+int launch_reparam(const EngineDev &e, cudaStream_t s);
+
+static int tiles_for(const OnfDims &d, int n) {
+    int tp = onf_fma_tile_points(d);
+    return tp ? (n + tp - 1) / tp : 0;
+}
+
+}  // namespace nfopp
+
+using namespace nfopp;
+
+extern "C" int nfopp_abi_version(void) { return NFOPP_ABI_VERSION; }
+extern "C" const char *nfopp_last_error(void) { return g_error; }
+
+extern "C" int nfopp_onf_get_layout(const nfopp_onf_config *cfg, nfopp_onf_layout *out) {
+    OnfDims d;
+    int rc = make_onf_dims(cfg, &d);
+    if (rc) return rc;
+    NFOPP_REQUIRE(out, "layout out pointer missing");
+    *out = d.lay;
+    return NFOPP_OK;
+}
+
+extern "C" int nfopp_onf_tiles(const nfopp_onf_config *cfg, int n) {
+    OnfDims d;
+    if (make_onf_dims(cfg, &d)) return NFOPP_ERR_INVALID;
+    int tp = onf_fma_tile_points(d);
+    if (!tp) { set_error("onf: hidden=%d layers=%d too large for the FMA path", d.H, d.L); return NFOPP_ERR_INVALID; }
+    return (n + tp - 1) / tp;
+}
+
+extern "C" int nfopp_onf_forward(const nfopp_onf_config *cfg, const float *weights, const float *x,
+                                 const int32_t *count, int P, int n, float *z, int impl, void *stream) {
+    OnfDims d;
+    int rc = make_onf_dims(cfg, &d);
+    if (rc) return rc;
+    NFOPP_REQUIRE(weights && x && z && P > 0 && n >= 0, "onf_forward: bad arguments");
+    NFOPP_REQUIRE(impl == 0 || impl == 1, "onf_forward: impl=%d not available in this build", impl);
+    OnfArgs a{};
+    a.d = d; a.weights = weights; a.x = x; a.count = count; a.n = n; a.want_bwd = 0; a.z_out = z;
+    if ((rc = onf_fma_prepare(d))) return rc;
+    return onf_fma_launch(a, P, (cudaStream_t)stream);
+}
+
+extern "C" int nfopp_onf_backward(const nfopp_onf_config *cfg, const float *weights, const float *x,
+                                  const int32_t *count, int P, int n, int gbar_mode, const float *gz,
+                                  const float *aux, float collision_weight, float beta, float *z, float *gx,
+                                  float *gpart, int impl, void *stream) {
+    OnfDims d;
+    int rc = make_onf_dims(cfg, &d);
+    if (rc) return rc;
+    NFOPP_REQUIRE(weights && x && P > 0 && n >= 0, "onf_backward: bad arguments");
+    NFOPP_REQUIRE(gbar_mode >= 0 && gbar_mode <= 3, "onf_backward: gbar_mode=%d", gbar_mode);
+    NFOPP_REQUIRE(gbar_mode != 0 || gz, "onf_backward: external mode needs gz");
+    NFOPP_REQUIRE((gbar_mode != 1 && gbar_mode != 3) || aux, "onf_backward: mode %d needs aux", gbar_mode);
+    NFOPP_REQUIRE(impl == 0 || impl == 1, "onf_backward: impl=%d not available in this build", impl);
+    OnfArgs a{};
+    a.d = d; a.weights = weights; a.x = x; a.count = count; a.n = n; a.want_bwd = 1; a.gbar_mode = gbar_mode;
+    a.gz = gz; a.aux = aux; a.wc = collision_weight; a.beta = beta; a.z_out = z; a.gx_out = gx; a.gpart = gpart;
+    if ((rc = onf_fma_prepare(d))) return rc;
+    return onf_fma_launch(a, P, (cudaStream_t)stream);
+}
+
+extern "C" int nfopp_onf_reduce_grad(const nfopp_onf_config *cfg, const float *gpart, const int32_t *count, int P,
+                                     int n, float *grad, void *stream) {
+    OnfDims d;
+    int rc = make_onf_dims(cfg, &d);
+    if (rc) return rc;
+    NFOPP_REQUIRE(gpart && grad && P > 0 && n > 0, "onf_reduce_grad: bad arguments");
+    AdamArgs a{};
+    a.gpart = gpart; a.count = count; a.n = n; a.tp = onf_fma_tile_points(d); a.tiles = tiles_for(d, n);
+    a.n_params = d.lay.n_params; a.grad_out = grad;
+    return onf_adam_launch(a, P, (cudaStream_t)stream);
+}
+
+static void adam_scalars(double lr, double b1, double b2, double eps, int64_t step, AdamArgs *a) {
+    a->w1 = (float)(1.0 - b1);
+    a->beta2 = (float)b2;
+    a->w2 = (float)(1.0 - b2);
+    a->step_size = (float)(lr / (1.0 - pow(b1, (double)step)));
+    a->bc2_sqrt = (float)sqrt(1.0 - pow(b2, (double)step));
+    a->eps = (float)eps;
+}
+
+extern "C" int nfopp_onf_adam(const nfopp_onf_config *cfg, float *w, float *m, float *v, const float *gpart,
+                              const int32_t *count, int P, int n, int step, double lr, double beta1, double beta2,
+                              double eps, void *stream) {
+    OnfDims d;
+    int rc = make_onf_dims(cfg, &d);
+    if (rc) return rc;
+    NFOPP_REQUIRE(w && m && v && gpart && P > 0 && n > 0 && step >= 1, "onf_adam: bad arguments");
+    AdamArgs a{};
+    a.w = w; a.m = m; a.v = v; a.gpart = gpart; a.count = count; a.n = n; a.tp = onf_fma_tile_points(d);
+    a.tiles = tiles_for(d, n); a.n_params = d.lay.n_params;
+    adam_scalars(lr, beta1, beta2, eps, step, &a);
+    return onf_adam_launch(a, P, (cudaStream_t)stream);
+}
+
+// =====================================================================================================
+// planner engine
+// =====================================================================================================
+struct BufferInfo {
+    std::string name;
+    void **slot;
+    size_t bytes;
+    char dtype;
+    int32_t dims[3];
+    size_t offset;
+};
+
+struct nfopp_engine {
+    nfopp_planner_config cfg;
+    OnfDims onf;
+    EngineDev dev;
+    std::vector<BufferInfo> buffers;
+    unsigned char *workspace;
+    size_t workspace_bytes;
+    int tile_points, tiles;
+    StepParams host_sp;
+    bool sp_dirty;
+    int64_t launches;
+    int launches_per_step;
+    cudaGraph_t graph;
+    cudaGraphExec_t graph_exec;
+    int warm_iterations_done;
+};
+
+static void host_step_params(nfopp_engine *e) {
+    StepParams &sp = e->host_sp;
+    const nfopp_planner_config &c = e->cfg;
+    sp.do_train = (sp.step_count % c.optimize_collision_model_freq) == 0;
+    sp.do_reparam = (sp.step_count % c.reparametrize_trajectory_freq) == 0;
+    const double ko = sp.onf_step + 1, kt = sp.traj_step + 1;
+    sp.onf_step_size = (float)((double)c.onf_lr / (1.0 - pow((double)c.onf_beta1, ko)));
+    sp.onf_bc2_sqrt = (float)sqrt(1.0 - pow((double)c.onf_beta2, ko));
+    sp.traj_step_size = (float)((double)c.traj_lr / (1.0 - pow((double)c.traj_beta1, kt)));
+    sp.traj_bc2_sqrt = (float)sqrt(1.0 - pow((double)c.traj_beta2, kt));
+}
+
+template <typename T>
+static void add_buffer(nfopp_engine *e, const char *name, T **slot, char dtype, size_t d0, size_t d1 = 0, size_t d2 = 0) {
+    BufferInfo b;
+    b.name = name;
+    b.slot = reinterpret_cast<void **>(slot);
+    size_t count = d0 * (d1 ? d1 : 1) * (d2 ? d2 : 1);
+    b.bytes = count * sizeof(T);
+    b.dtype = dtype;
+    b.dims[0] = (int32_t)d0; b.dims[1] = (int32_t)d1; b.dims[2] = (int32_t)d2;
+    b.offset = 0;
+    e->buffers.push_back(b);
+}
+
+static int validate(const nfopp_planner_config *c, OnfDims *onf) {
+    NFOPP_REQUIRE(c, "planner config missing");
+    int rc = make_onf_dims(&c->onf, onf);
+    if (rc) return rc;
+    NFOPP_REQUIRE(c->problems >= 1, "problems=%d", c->problems);
+    NFOPP_REQUIRE(c->trajectory_length >= 2 && c->trajectory_length <= 4096, "trajectory_length=%d", c->trajectory_length);
+    NFOPP_REQUIRE(c->constrained || !c->onf.angle, "holonomic planner cannot feed an angle-encoding ONF");
+    NFOPP_REQUIRE(c->collision_point_count >= 1 && c->random_field_points >= 0 && c->init_collision_points >= 0,
+                  "sample counts out of range");
+    NFOPP_REQUIRE(c->reparametrize_trajectory_freq >= 1 && c->optimize_collision_model_freq >= 1, "freq must be >= 1");
+    NFOPP_REQUIRE(c->checker_kind >= 0 && c->checker_kind <= 3, "checker_kind=%d", c->checker_kind);
+    NFOPP_REQUIRE(c->checker_kind != 2 || c->constrained, "rectangle checker needs poses with heading");
+    NFOPP_REQUIRE(c->checker_kind != 3 || (c->grid_rows > 1 && c->grid_cols > 1 && c->grid_cell > 0), "grid shape missing");
+    NFOPP_REQUIRE(c->rng_mode == 0 || c->rng_mode == 1, "rng_mode=%d", c->rng_mode);
+    NFOPP_REQUIRE(c->onf_impl == 0 || c->onf_impl == 1, "onf_impl=%d not available in this build", c->onf_impl);
+    NFOPP_REQUIRE(onf_fma_tile_points(*onf) != 0, "ONF hidden=%d layers=%d too large for the FMA path", onf->H, onf->L);
+    return NFOPP_OK;
+}
+
+static int build_layout(nfopp_engine *e) {
+    const nfopp_planner_config &c = e->cfg;
+    EngineDev &d = e->dev;
+    const size_t P = c.problems, T = c.trajectory_length, D = c.constrained ? 3 : 2;
+    const size_t C = c.collision_point_count, NF = c.random_field_points, NW = c.init_collision_points;
+    const size_t NC = C + T - 1;
+    size_t NTR = (T - 1) + C + NF;
+    if (NW > NTR) NTR = NW;
+    const size_t NP = e->onf.lay.n_params;
+    e->tile_points = onf_fma_tile_points(e->onf);
+    e->tiles = (int)((NTR + e->tile_points - 1) / e->tile_points);
+    const bool inj = c.rng_mode == 1;
+    const size_t MU = inj ? (c.max_choice_uniforms > 0 ? c.max_choice_uniforms : 16 * C) : 0;
+    d.P = (int)P; d.T = (int)T; d.D = (int)D; d.C = (int)C; d.NF = (int)NF; d.NC = (int)NC; d.NTR = (int)NTR; d.NW = (int)NW;
+    d.max_choice_u = (int)MU;
+    const size_t PE = c.env_shared ? 1 : P;
+
+    add_buffer(e, "step_params", &d.sp, 'i', sizeof(StepParams) / 4);
+    add_buffer(e, "onf_w", &d.onf_w, 'f', P, NP);
+    add_buffer(e, "onf_m", &d.onf_m, 'f', P, NP);
+    add_buffer(e, "onf_v", &d.onf_v, 'f', P, NP);
+    add_buffer(e, "onf_gpart", &d.onf_gpart, 'f', P, e->tiles, NP);
+    add_buffer(e, "traj", &d.traj, 'f', P, T, D);
+    add_buffer(e, "traj_m", &d.traj_m, 'f', P, T, D);
+    add_buffer(e, "traj_v", &d.traj_v, 'f', P, T, D);
+    add_buffer(e, "prev_traj", &d.prev_traj, 'f', P, T, D);
+    add_buffer(e, "lam", &d.lam, 'f', P, T + 1);
+    add_buffer(e, "mu", &d.mu, 'f', P, T);
+    add_buffer(e, "start", &d.start, 'f', P, D);
+    add_buffer(e, "goal", &d.goal, 'f', P, D);
+    add_buffer(e, "buf_pos", &d.buf_pos, 'd', P, C, D);
+    add_buffer(e, "buf_age", &d.buf_age, 'd', P, C);
+    add_buffer(e, "buf_n", &d.buf_n, 'i', P);
+    add_buffer(e, "cand_pos", &d.cand_pos, 'd', P, NC, D);
+    add_buffer(e, "cand_age", &d.cand_age, 'd', P, NC);
+    add_buffer(e, "cand_x", &d.cand_x, 'f', P, NC, D);
+    add_buffer(e, "cand_z", &d.cand_z, 'f', P, NC);
+    add_buffer(e, "cand_n", &d.cand_n, 'i', P);
+    add_buffer(e, "train_pos", &d.train_pos, 'd', P, NTR, D);
+    add_buffer(e, "train_x", &d.train_x, 'f', P, NTR, D);
+    add_buffer(e, "train_y", &d.train_y, 'f', P, NTR);
+    add_buffer(e, "train_z", &d.train_z, 'f', P, NTR);
+    add_buffer(e, "train_n", &d.train_n, 'i', P);
+    add_buffer(e, "path_q", &d.path_q, 'f', P, T - 1, D);
+    add_buffer(e, "path_mu", &d.path_mu, 'f', P, T - 1);
+    add_buffer(e, "path_z", &d.path_z, 'f', P, T - 1);
+    add_buffer(e, "path_gq", &d.path_gq, 'f', P, T - 1, D);
+    add_buffer(e, "path_t", &d.path_t, 'f', P, T - 1);
+    add_buffer(e, "path_n", &d.path_n, 'i', P);
+    add_buffer(e, "choice_idx", &d.choice_idx, 'i', P, C);
+    add_buffer(e, "choice_used", &d.choice_used, 'i', P);
+    add_buffer(e, "status", &d.status, 'i', P);
+    add_buffer(e, "inv_hessian_t", &d.inv_hessian_t, 'f', T, T);
+    add_buffer(e, "lin_s", &d.lin_s, 'f', T);
+    if (c.checker_kind == 1 || c.checker_kind == 2) {
+        add_buffer(e, "obstacles", &d.obstacles, 'd', PE, c.max_obstacles > 0 ? c.max_obstacles : 1, 2);
+        add_buffer(e, "obstacle_n", &d.obstacle_n, 'i', PE);
+    }
+    if (c.checker_kind == 3) add_buffer(e, "grid", &d.grid, 'b', PE, c.grid_rows, c.grid_cols);
+    if (inj) {
+        add_buffer(e, "var_t_sample", &d.var_t_sample, 'd', P, T - 1);
+        add_buffer(e, "var_coarse_xy", &d.var_coarse_xy, 'd', P, T - 1, 2);
+        add_buffer(e, "var_coarse_th", &d.var_coarse_th, 'd', P, T - 1);
+        add_buffer(e, "var_fine_xy", &d.var_fine_xy, 'd', P, T - 1, 2);
+        add_buffer(e, "var_fine_th", &d.var_fine_th, 'd', P, T - 1);
+        add_buffer(e, "var_choice_u", &d.var_choice_u, 'd', P, MU);
+        add_buffer(e, "var_field_xy", &d.var_field_xy, 'd', P, NF > 0 ? NF : 1, 2);
+        add_buffer(e, "var_field_th", &d.var_field_th, 'd', P, NF > 0 ? NF : 1);
+        add_buffer(e, "var_warm_xy", &d.var_warm_xy, 'd', P, NW > 0 ? NW : 1, 2);
+        add_buffer(e, "var_warm_th", &d.var_warm_th, 'd', P, NW > 0 ? NW : 1);
+        add_buffer(e, "var_t_path", &d.var_t_path, 'f', P, T - 1);
+    }
+    size_t off = 0;
+    for (auto &b : e->buffers) {
+        b.offset = off;
+        off += (b.bytes + 255) / 256 * 256;
+    }
+    e->workspace_bytes = off;
+    return NFOPP_OK;
+}
+
+static void fill_dev_config(nfopp_engine *e) {
+    const nfopp_planner_config &c = e->cfg;
+    EngineDev &d = e->dev;
+    d.constrained = c.constrained; d.rng_mode = c.rng_mode; d.seed = c.seed;
+    d.fine_offset = c.trajectory_random_offset; d.coarse_offset = c.course_random_offset; d.angle_offset = c.angle_offset;
+    for (int i = 0; i < 4; ++i) { d.border[i] = c.border[i]; d.border_f[i] = (float)c.border[i]; }
+    d.collision_weight = c.collision_weight; d.angle_weight = c.angle_weight;
+    d.constraint_weight = c.constraint_deltas_weight; d.multipliers_lr = c.multipliers_lr;
+    d.boundary_weight = c.boundary_weight; d.mu_lr = c.collision_multipliers_lr; d.beta = c.collision_beta;
+    d.direction_weight = c.direction_delta_weight;
+    d.traj_w1 = (float)(1.0 - (double)c.traj_beta1); d.traj_beta2 = (float)c.traj_beta2;
+    d.traj_w2 = (float)(1.0 - (double)c.traj_beta2); d.traj_eps = (float)c.adam_eps;
+    d.onf_lr_d = c.onf_lr; d.onf_b1_d = c.onf_beta1; d.onf_b2_d = c.onf_beta2;
+    d.traj_lr_d = c.traj_lr; d.traj_b1_d = c.traj_beta1; d.traj_b2_d = c.traj_beta2;
+    d.reparam_freq = c.reparametrize_trajectory_freq; d.train_freq = c.optimize_collision_model_freq;
+    CheckerParams &k = d.checker;
+    k.kind = c.checker_kind; k.has_bounds = c.has_bounds;
+    for (int i = 0; i < 4; ++i) { k.bounds[i] = c.bounds[i]; k.box[i] = c.box[i]; }
+    k.radius = c.robot_radius; k.rows = c.grid_rows; k.cols = c.grid_cols;
+    k.ox = c.grid_origin_x; k.oy = c.grid_origin_y; k.cell = c.grid_cell;
+    d.env_shared = c.env_shared; d.m_max = c.max_obstacles > 0 ? c.max_obstacles : 1;
+}
+
+extern "C" int nfopp_engine_workspace_bytes(const nfopp_planner_config *cfg, size_t *bytes) {
+    nfopp_engine tmp{};
+    int rc = validate(cfg, &tmp.onf);
+    if (rc) return rc;
+    NFOPP_REQUIRE(bytes, "bytes pointer missing");
+    tmp.cfg = *cfg;
+    rc = build_layout(&tmp);
+    if (rc) return rc;
+    *bytes = tmp.workspace_bytes;
+    return NFOPP_OK;
+}
+
+static int upload_step_params(nfopp_engine *e, cudaStream_t s) {
+    host_step_params(e);
+    NFOPP_CHECK_CUDA(cudaMemcpyAsync(e->dev.sp, &e->host_sp, sizeof(StepParams), cudaMemcpyHostToDevice, s));
+    NFOPP_CHECK_CUDA(cudaStreamSynchronize(s));
+    e->sp_dirty = false;
+    return NFOPP_OK;
+}
+
+extern "C" int nfopp_engine_create(const nfopp_planner_config *cfg, void *workspace, size_t workspace_bytes,
+                                   nfopp_engine **out) {
+    NFOPP_REQUIRE(out, "engine out pointer missing");
+    nfopp_engine *e = new nfopp_engine{};
+    int rc = validate(cfg, &e->onf);
+    if (rc) { delete e; return rc; }
+    e->cfg = *cfg;
+    build_layout(e);
+    if (!workspace || workspace_bytes < e->workspace_bytes || (reinterpret_cast<uintptr_t>(workspace) & 255)) {
+        set_error("workspace: need %zu bytes, 256-byte aligned (got %zu at %p)", e->workspace_bytes, workspace_bytes, workspace);
+        delete e;
+        return NFOPP_ERR_WORKSPACE;
+    }
+    e->workspace = static_cast<unsigned char *>(workspace);
+    for (auto &b : e->buffers) *b.slot = e->workspace + b.offset;
+    fill_dev_config(e);
+    cudaError_t ce = cudaMemset(e->workspace, 0, e->workspace_bytes);
+    if (ce != cudaSuccess) {
+        set_error("cudaMemset(workspace) failed: %s", cudaGetErrorString(ce));
+        delete e;
+        return NFOPP_ERR_CUDA;
+    }
+    if ((rc = onf_fma_prepare(e->onf)) || (rc = resample_prepare(e->dev)) || (rc = traj_prepare(e->dev))) {
+        delete e;
+        return rc;
+    }
+    e->host_sp = StepParams{};
+    e->sp_dirty = true;
+    e->launches_per_step = 9;
+    *out = e;
+    return NFOPP_OK;
+}
+
+extern "C" int nfopp_engine_destroy(nfopp_engine *e) {
+    if (!e) return NFOPP_OK;
+    if (e->graph_exec) cudaGraphExecDestroy(e->graph_exec);
+    if (e->graph) cudaGraphDestroy(e->graph);
+    delete e;
+    return NFOPP_OK;
+}
+
+extern "C" int nfopp_engine_buffer_count(nfopp_engine *e) { return e ? (int)e->buffers.size() : 0; }
+extern "C" const char *nfopp_engine_buffer_name(nfopp_engine *e, int index) {
+    if (!e || index < 0 || index >= (int)e->buffers.size()) return nullptr;
+    return e->buffers[index].name.c_str();
+}
+
+extern "C" int nfopp_engine_buffer(nfopp_engine *e, const char *name, void **ptr, size_t *bytes, char *dtype,
+                                   int32_t dims[3]) {
+    NFOPP_REQUIRE(e && name, "engine_buffer: bad arguments");
+    for (auto &b : e->buffers) {
+        if (b.name == name) {
+            if (ptr) *ptr = *b.slot;
+            if (bytes) *bytes = b.bytes;
+            if (dtype) *dtype = b.dtype;
+            if (dims) for (int i = 0; i < 3; ++i) dims[i] = b.dims[i];
+            return NFOPP_OK;
+        }
+    }
+    set_error("unknown engine buffer '%s'", name);
+    return NFOPP_ERR_NAME;
+}
+
+extern "C" int nfopp_engine_get_counter(nfopp_engine *e, int which, int64_t *value) {
+    NFOPP_REQUIRE(e && value && which >= 0 && which <= 3, "get_counter: bad arguments");
+    const StepParams &sp = e->host_sp;
+    *value = which == 0 ? sp.step_count : which == 1 ? sp.onf_step : which == 2 ? sp.traj_step : sp.has_prev;
+    return NFOPP_OK;
+}
+
+extern "C" int nfopp_engine_set_counter(nfopp_engine *e, int which, int64_t value) {
+    NFOPP_REQUIRE(e && which >= 0 && which <= 3 && value >= 0, "set_counter: bad arguments");
+    StepParams &sp = e->host_sp;
+    if (which == 0) sp.step_count = (int32_t)value;
+    else if (which == 1) sp.onf_step = (int32_t)value;
+    else if (which == 2) sp.traj_step = (int32_t)value;
+    else sp.has_prev = value != 0;
+    e->sp_dirty = true;
+    return NFOPP_OK;
+}
+
+// one ONF training update on train_x/train_y/train_n (nerf_opt_planner.py:83-90)
+static int enqueue_train(nfopp_engine *e, bool warm, cudaStream_t s) {
+    const EngineDev &d = e->dev;
+    OnfArgs a{};
+    a.d = e->onf; a.weights = d.onf_w; a.x = d.train_x; a.count = d.train_n; a.n = d.NTR; a.x_stride = d.D;
+    a.want_bwd = 1; a.gbar_mode = 1; a.aux = d.train_y; a.z_out = d.train_z; a.gpart = d.onf_gpart;
+    a.sp = warm ? nullptr : d.sp;
+    int rc = onf_fma_launch(a, d.P, s);
+    if (rc) return rc;
+    AdamArgs ad{};
+    ad.w = d.onf_w; ad.m = d.onf_m; ad.v = d.onf_v; ad.gpart = d.onf_gpart; ad.count = d.train_n; ad.n = d.NTR;
+    ad.tp = e->tile_points; ad.tiles = e->tiles; ad.n_params = e->onf.lay.n_params;
+    ad.w1 = (float)(1.0 - (double)e->cfg.onf_beta1); ad.beta2 = (float)e->cfg.onf_beta2;
+    ad.w2 = (float)(1.0 - (double)e->cfg.onf_beta2); ad.eps = (float)e->cfg.adam_eps;
+    ad.sp = d.sp;
+    ad.warm = warm;
+    return onf_adam_launch(ad, d.P, s);
+}
+
+static int enqueue_step(nfopp_engine *e, cudaStream_t s) {
+    const EngineDev &d = e->dev;
+    int rc;
+    // (1) near-path + uniform samples, candidates            nerf_opt_planner.py:101-120
+    if ((rc = launch_sample_pre(d, s))) return rc;
+    // (2) ONF forward on the candidates (resampling weights)  :123-125   [skipped on device when !do_train]
+    {
+        OnfArgs a{};
+        a.d = e->onf; a.weights = d.onf_w; a.x = d.cand_x; a.count = d.cand_n; a.n = d.NC; a.x_stride = d.D;
+        a.z_out = d.cand_z; a.sp = d.sp;
+        if ((rc = onf_fma_launch(a, d.P, s))) return rc;
+    }
+    // (3) weighted resampling of the replay buffer + ground-truth labels  :126-133, :86
+    if ((rc = launch_resample_label(d, 1, s))) return rc;
+    // (4,5) BCE training step of the ONF: fwd+bwd per tile, then reduce + Adam   :83-90
+    if ((rc = enqueue_train(e, false, s))) return rc;
+    // (6) collision sample points on the path                 :113-117 / constrained:78-83
+    if ((rc = launch_traj_pre(d, s))) return rc;
+    // (7) ONF forward + input gradient at the path points     :166-169 / constrained:85-89
+    {
+        OnfArgs a{};
+        a.d = e->onf; a.weights = d.onf_w; a.x = d.path_q; a.count = d.path_n; a.n = d.T - 1; a.x_stride = d.D;
+        a.want_bwd = 1;
+        a.gbar_mode = d.constrained ? 3 : 2; a.aux = d.path_mu; a.wc = d.collision_weight;
+        a.beta = d.constrained ? d.beta : 1.f; a.z_out = d.path_z; a.gx_out = d.path_gq;
+        if ((rc = onf_fma_launch(a, d.P, s))) return rc;
+    }
+    // (8) trajectory gradient, preconditioner, Adam, multipliers, re-parametrisation  :143-155,224-244
+    if ((rc = launch_traj_post(d, s))) return rc;
+    // (9) counters
+    return launch_tick(d, false, s);
+}
+
+extern "C" int nfopp_engine_warmup(nfopp_engine *e, int iterations, void *stream) {
+    NFOPP_REQUIRE(e && iterations >= 0, "warmup: bad arguments");
+    cudaStream_t s = (cudaStream_t)stream;
+    int rc;
+    if (e->sp_dirty && (rc = upload_step_params(e, s))) return rc;
+    for (int it = 0; it < iterations; ++it) {
+        if ((rc = launch_warm_sample(e->dev, 1000000 + e->warm_iterations_done, s))) return rc;
+        if ((rc = launch_resample_label(e->dev, 0, s))) return rc;
+        if ((rc = enqueue_train(e, true, s))) return rc;
+        if ((rc = launch_tick(e->dev, true, s))) return rc;
+        e->host_sp.onf_step += 1;
+        e->warm_iterations_done += 1;
+        e->launches += 5;
+    }
+    host_step_params(e);
+    return NFOPP_OK;
+}
+
+extern "C" int nfopp_engine_step(nfopp_engine *e, int n_steps, int use_graph, void *stream) {
+    NFOPP_REQUIRE(e && n_steps >= 0, "step: bad arguments");
+    cudaStream_t s = (cudaStream_t)stream;
+    int rc;
+    if (e->sp_dirty && (rc = upload_step_params(e, s))) return rc;
+    if (use_graph && !e->graph_exec) {
+        NFOPP_REQUIRE(s != nullptr, "step: CUDA-graph capture needs a non-default stream");
+        NFOPP_CHECK_CUDA(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+        rc = enqueue_step(e, s);
+        cudaError_t ce = cudaStreamEndCapture(s, &e->graph);
+        if (rc) return rc;
+        NFOPP_CHECK_CUDA(ce);
+        NFOPP_CHECK_CUDA(cudaGraphInstantiate(&e->graph_exec, e->graph, 0));
+    }
+    for (int it = 0; it < n_steps; ++it) {
+        if (use_graph) {
+            NFOPP_CHECK_CUDA(cudaGraphLaunch(e->graph_exec, s));
+        } else if ((rc = enqueue_step(e, s))) {
+            return rc;
+        }
+        StepParams &sp = e->host_sp;
+        if (sp.do_train) { sp.onf_step += 1; sp.has_prev = 1; }
+        sp.traj_step += 1;
+        sp.step_count += 1;
+        host_step_params(e);
+        e->launches += e->launches_per_step;
+    }
+    return NFOPP_OK;
+}
+
+extern "C" int nfopp_engine_get_paths(nfopp_engine *e, float *paths, void *stream) {
+    NFOPP_REQUIRE(e && paths, "get_paths: bad arguments");
+    e->launches += 1;
+    return launch_paths(e->dev, paths, (cudaStream_t)stream);
+}
+
+extern "C" int nfopp_engine_reparametrize(nfopp_engine *e, void *stream) {
+    NFOPP_REQUIRE(e, "reparametrize: bad arguments");
+    e->launches += 1;
+    return launch_reparam(e->dev, (cudaStream_t)stream);
+}
+
+extern "C" int nfopp_engine_launch_count(nfopp_engine *e, int64_t *launches) {
+    NFOPP_REQUIRE(e && launches, "launch_count: bad arguments");
+    *launches = e->launches;
+    return NFOPP_OK;
+}

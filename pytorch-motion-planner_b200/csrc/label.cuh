@@ -1,0 +1,74 @@
+// label.cuh - ground-truth collision labels for one pose, float64, in numpy's operation order with FMA
+// contraction made impossible by explicit round-to-nearest intrinsics.
+#pragma once
+#include "common.cuh"
+
+namespace nfopp {
+
+struct CheckerParams {
+    int kind;          // 0 boundary only, 1 circle, 2 rectangle, 3 grid
+    int has_bounds;
+    double bounds[4];  // x0,x1,y0,y1
+    double radius;
+    double box[4];
+    int rows, cols;
+    double ox, oy, cell;
+};
+
+// collision_checker/collision_checker.py:12-19 (strict inequalities)
+__device__ __forceinline__ bool label_boundary(const CheckerParams &c, double x, double y) {
+    if (!c.has_bounds) return false;
+    return (x > c.bounds[1]) | (x < c.bounds[0]) | (y > c.bounds[3]) | (y < c.bounds[2]);
+}
+
+// circle_collision_checker.py:11-14: any_m sqrt(dx*dx + dy*dy) < r
+__device__ __forceinline__ bool label_circle(const double *__restrict__ obs, int m, double r, double x, double y) {
+    bool hit = false;
+    for (int i = 0; i < m; ++i) {
+        double dx = __dsub_rn(x, obs[2 * i]), dy = __dsub_rn(y, obs[2 * i + 1]);
+        double d = __dsqrt_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
+        hit |= d < r;
+    }
+    return hit;
+}
+
+// rectangle_collision_checker.py:11-26 with position2.py:91-94 (inv)
+__device__ __forceinline__ bool label_rectangle(const double *__restrict__ obs, int m, const double *box, double x,
+                                                double y, double th) {
+    double c = cos(th), s = sin(th);
+    double ix = __dsub_rn(__dmul_rn(-x, c), __dmul_rn(y, s));
+    double iy = __dsub_rn(__dmul_rn(x, s), __dmul_rn(y, c));
+    double ci = cos(-th), si = sin(-th);
+    bool hit = false;
+    for (int i = 0; i < m; ++i) {
+        double ox = obs[2 * i], oy = obs[2 * i + 1];
+        double x1 = __dadd_rn(__dsub_rn(__dmul_rn(ox, ci), __dmul_rn(oy, si)), ix);
+        double y1 = __dadd_rn(__dadd_rn(__dmul_rn(ox, si), __dmul_rn(oy, ci)), iy);
+        hit |= (x1 > box[0]) & (x1 < box[1]) & (y1 > box[2]) & (y1 < box[3]);
+    }
+    return hit;
+}
+
+// notebooks/onf_planner_image_map.ipynb:65-80: half-cell offset, C truncation, last row/col rejected
+__device__ __forceinline__ bool label_grid(const uint8_t *__restrict__ grid, const CheckerParams &c, double x,
+                                           double y) {
+    double half = __ddiv_rn(c.cell, 2.0);
+    double fx = __ddiv_rn(__dsub_rn(__dsub_rn(x, c.ox), half), c.cell);
+    double fy = __ddiv_rn(__dsub_rn(__dsub_rn(y, c.oy), half), c.cell);
+    int ix = __double2int_rz(fx), iy = __double2int_rz(fy);   // saturating; out-of-range => invalid either way
+    bool valid = (ix >= 0) & (iy >= 0) & (iy < c.rows - 1) & (ix < c.cols - 1) & (fx == fx) & (fy == fy);
+    if (!valid) return true;
+    return grid[(size_t)iy * c.cols + ix] > 0;
+}
+
+// one pose against one environment; obs may point to shared memory
+__device__ __forceinline__ bool label_pose(const CheckerParams &c, const double *__restrict__ obs, int m,
+                                           const uint8_t *__restrict__ grid, double x, double y, double th) {
+    bool hit = false;
+    if (c.kind == 1) hit = label_circle(obs, m, c.radius, x, y);
+    else if (c.kind == 2) hit = label_rectangle(obs, m, c.box, x, y, th);
+    else if (c.kind == 3) hit = label_grid(grid, c, x, y);
+    return hit | label_boundary(c, x, y);
+}
+
+}  // namespace nfopp

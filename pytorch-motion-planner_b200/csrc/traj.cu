@@ -1,0 +1,376 @@
+// traj.cu - K3: the trajectory half of a planner step, one CTA per problem, everything in shared memory.
+//   traj_pre : random collision sample points on the current path (+ interpolated collision multipliers)
+//   traj_post: analytic gradient of every loss term (CHOMP distance stencil, non-holonomic Lagrangian +
+//              quadratic term, forward-only direction term, boundary term, collision term through the ONF
+//              input gradients), inverse-Hessian preconditioning, Adam, multiplier ascent, and (every
+//              reparametrize_trajectory_freq steps) arc-length re-parametrisation.
+//   tick     : advances the device-side step counters.
+// The reference does all of this with ~1900 autograd ops per step; formulas follow
+// SURVEY.md appendix A.2-A.4 and cite the reference lines they restate.
+#include "engine.cuh"
+
+namespace nfopp {
+
+constexpr int TRAJ_THREADS = 128;
+
+// nerf_opt_planner.py:113-117,158 (holonomic) / constrained_nerf_opt_planner.py:78-83
+__global__ void __launch_bounds__(TRAJ_THREADS) traj_pre_kernel(const EngineDev e) {
+    const StepParams sp = *e.sp;
+    const int p = blockIdx.x, T = e.T, D = e.D, n = T - 1;
+    const float *X = e.traj + (size_t)p * T * D;
+    for (int i = threadIdx.x; i < n; i += TRAJ_THREADS) {
+        float t;
+        if (e.rng_mode == 1) {
+            t = e.var_t_path[(size_t)p * n + i];
+        } else {
+            uint4 r = Philox(e.seed)(i, RNG_T_PATH, sp.step_count, p);
+            t = e.constrained ? (float)(r.x >> 8) * (1.0f / 16777216.0f)      // torch.rand float32: 24 bits
+                              : (float)u53(r.x, r.y);                           // np.random.rand -> float32
+        }
+        e.path_t[(size_t)p * n + i] = t;
+        float *q = e.path_q + ((size_t)p * n + i) * D;
+        if (e.constrained) {
+            for (int d = 0; d < D; ++d) {
+                float delta = __fsub_rn(X[i * D + d], X[(i + 1) * D + d]);
+                if (d == 2) delta = wrap_angle_f(delta);
+                q[d] = __fadd_rn(X[(i + 1) * D + d], __fmul_rn(t, delta));
+            }
+            const float *mu = e.mu + (size_t)p * T;
+            e.path_mu[(size_t)p * n + i] = __fadd_rn(__fmul_rn(mu[i + 1], __fsub_rn(1.f, t)), __fmul_rn(mu[i], t));
+        } else {
+            const float omt = __fsub_rn(1.f, t);
+            for (int d = 0; d < D; ++d)
+                q[d] = __fadd_rn(__fmul_rn(X[(i + 1) * D + d], omt), __fmul_rn(X[i * D + d], t));
+        }
+    }
+    if (threadIdx.x == 0) e.path_n[p] = n;
+}
+
+__device__ __forceinline__ float relu_f(float v) { return v > 0.f ? v : 0.f; }
+
+struct TrajSmem {
+    float *full;     // [(T+2)*D]
+    float *hi, *lo;  // per segment: gradient contribution to node j+1 / node j, [(T+1)*D] each
+    float *g;        // raw gradient per trajectory point [T*D]
+    float *gm;       // g_mu [T]
+    float *cseg;     // non-holonomic residual per segment [T+1]
+    float *wd;       // wrapped dtheta per segment / segment length / cdf [T+2]
+    float *aux;      // [T+2]
+    float *red;      // [4]
+};
+
+__device__ TrajSmem carve_traj(float *base, int T, int D) {
+    TrajSmem s;
+    float *p = base;
+    s.full = p; p += (T + 2) * D;
+    s.hi = p; p += (T + 1) * D;
+    s.lo = p; p += (T + 1) * D;
+    s.g = p; p += T * D;
+    s.gm = p; p += T;
+    s.cseg = p; p += T + 1;
+    s.wd = p; p += T + 2;
+    s.aux = p; p += T + 2;
+    s.red = p;
+    return s;
+}
+
+static size_t traj_smem_bytes(int T, int D) {
+    return (size_t)((T + 2) * D + 2 * (T + 1) * D + T * D + T + (T + 1) + 2 * (T + 2) + 4) * sizeof(float);
+}
+
+// Writes the updated path / multipliers held in shared memory (s.full, s.gm = mu, s.cseg = lambda) back to
+// global memory, optionally through arc-length re-parametrisation.
+__device__ void store_path(const EngineDev &e, TrajSmem &s, int p, bool do_reparam) {
+    const int tid = threadIdx.x, T = e.T, D = e.D;
+    float *X = e.traj + (size_t)p * T * D;
+    float *lam = e.lam + (size_t)p * (T + 1), *mu = e.mu + (size_t)p * T;
+    if (do_reparam) {
+        // ---- nerf_opt_planner.py:224-248 / constrained:132-171 -------------------------------------
+        for (int j = tid; j <= T; j += TRAJ_THREADS) {
+            float acc = 0.f;
+            const int dn = e.constrained ? 2 : D;              // constrained:45-47 uses x,y only
+            for (int d = 0; d < dn; ++d) {
+                float df = s.full[(j + 1) * D + d] - s.full[j * D + d];
+                acc += df * df;
+            }
+            s.wd[j + 1] = sqrtf(acc);
+        }
+        __syncthreads();
+        if (tid == 0) {
+            float tot = 0.f;
+            for (int j = 1; j <= T + 1; ++j) tot += s.wd[j];
+            float acc = 0.f;
+            s.wd[0] = 0.f;
+            for (int j = 1; j <= T + 1; ++j) { acc += s.wd[j] / tot; s.wd[j] = acc; }   // cdf
+        }
+        __syncthreads();
+        const float *cdf = s.wd;
+        // node-centred constraint multipliers (constrained:161-164): [l0, (l_j+l_{j+1})/2 ..., l_T]
+        if (e.constrained) {
+            for (int j = tid; j <= T + 1; j += TRAJ_THREADS)
+                s.aux[j] = j == 0 ? s.cseg[0] : (j == T + 1 ? s.cseg[T] : (s.cseg[j - 1] + s.cseg[j]) * 0.5f);
+        }
+        __syncthreads();
+        for (int k = tid; k < T; k += TRAJ_THREADS) {
+            const float u = __ldg(e.lin_s + k);
+            int lo_i = 0, hi_i = T + 2;                        // torch.searchsorted (left): first cdf[idx] >= u
+            while (lo_i < hi_i) {
+                int mid = (lo_i + hi_i) >> 1;
+                if (cdf[mid] < u) lo_i = mid + 1; else hi_i = mid;
+            }
+            const int above = min(lo_i, T + 1), below = max(lo_i - 1, 0);
+            float den = cdf[above] - cdf[below];
+            if (den < 1e-5f) den = 1e-5f;
+            const float tau = (u - cdf[below]) / den;
+            const float *A = s.full + below * D, *B = s.full + above * D;
+            float *o = s.hi + k * D;                            // s.hi reused as the new trajectory
+            o[0] = __fadd_rn(__fmul_rn(1.f - tau, A[0]), __fmul_rn(tau, B[0]));
+            o[1] = __fadd_rn(__fmul_rn(1.f - tau, A[1]), __fmul_rn(tau, B[1]));
+            if (e.constrained) {
+                o[2] = __fadd_rn(A[2], __fmul_rn(tau, wrap_angle_f(B[2] - A[2])));
+                const float mb = below == 0 || below == T + 1 ? 0.f : s.gm[below - 1];   // zero-padded mu
+                const float ma = above == 0 || above == T + 1 ? 0.f : s.gm[above - 1];
+                s.lo[k] = __fadd_rn(__fmul_rn(1.f - tau, mb), __fmul_rn(tau, ma));       // new mu
+                s.lo[T + k] = __fadd_rn(__fmul_rn(1.f - tau, s.aux[below]), __fmul_rn(tau, s.aux[above]));
+            }
+        }
+        __syncthreads();
+        for (int i = tid; i < T * D; i += TRAJ_THREADS) X[i] = s.hi[i];
+        if (e.constrained) {
+            for (int k = tid; k < T; k += TRAJ_THREADS) mu[k] = s.lo[k];
+            const float *cn = s.lo + T;                        // constrained:168-171 back to segments
+            for (int j = tid; j <= T; j += TRAJ_THREADS)
+                lam[j] = j == 0 ? cn[0] : (j == T ? cn[T - 1] : (cn[j - 1] + cn[j]) * 0.5f);
+        }
+    } else {
+        for (int i = tid; i < T * D; i += TRAJ_THREADS) X[i] = s.full[D + i];
+        if (e.constrained) {
+            for (int k = tid; k < T; k += TRAJ_THREADS) mu[k] = s.gm[k];
+            for (int j = tid; j <= T; j += TRAJ_THREADS) lam[j] = s.cseg[j];
+        }
+    }
+}
+
+
+__global__ void __launch_bounds__(TRAJ_THREADS) traj_post_kernel(const EngineDev e) {
+    extern __shared__ __align__(16) float smem_f[];
+    const StepParams sp = *e.sp;
+    const int p = blockIdx.x, tid = threadIdx.x, T = e.T, D = e.D, n = T - 1;
+    TrajSmem s = carve_traj(smem_f, T, D);
+    float *X = e.traj + (size_t)p * T * D;
+    const float *gq = e.path_gq + (size_t)p * n * D;
+    const float *pz = e.path_z + (size_t)p * n;
+    const float *pt = e.path_t + (size_t)p * n;
+    float *lam = e.lam + (size_t)p * (T + 1), *mu = e.mu + (size_t)p * T;
+
+    // full trajectory = start | trajectory | goal  (nerf_opt_planner.py:73-74)
+    for (int i = tid; i < (T + 2) * D; i += TRAJ_THREADS) {
+        int node = i / D, d = i - node * D;
+        s.full[i] = node == 0 ? e.start[(size_t)p * D + d]
+                              : (node == T + 1 ? e.goal[(size_t)p * D + d] : X[(node - 1) * D + d]);
+    }
+    __syncthreads();
+    float ang_sum = 0.f;
+    if (e.constrained) {
+        // constrained:123-125: s = sum(wrap(dtheta)).detach() - theta_goal + theta_start
+        for (int j = tid; j <= T; j += TRAJ_THREADS)
+            s.wd[j] = wrap_angle_f(__fsub_rn(s.full[(j + 1) * 3 + 2], s.full[j * 3 + 2]));
+        __syncthreads();
+        if (tid == 0) {
+            float acc = 0.f;
+            for (int j = 0; j <= T; ++j) acc += s.wd[j];
+            s.red[0] = acc - s.full[(T + 1) * 3 + 2] + s.full[2];
+        }
+        __syncthreads();
+        ang_sum = s.red[0];
+    }
+    // ---- per-segment terms -------------------------------------------------------------------------
+    for (int j = tid; j <= T; j += TRAJ_THREADS) {
+        const float *a = s.full + j * D, *b = s.full + (j + 1) * D;
+        const float dx = b[0] - a[0], dy = b[1] - a[1];
+        float hx = 2.f * dx, hy = 2.f * dy, lx = -hx, ly = -hy, hth = 0.f, lth = 0.f;   // distance term
+        if (e.constrained) {
+            const float aw = e.angle_weight;
+            float dth = b[2] - a[2];
+            if (j == T) dth += ang_sum;                      // constrained:126
+            dth *= aw;                                       // :127
+            hth = 2.f * aw * dth;
+            lth = -hth;
+            // non-holonomic residual (:102-109) with multiplier + quadratic weight (:94-96)
+            const float abar = a[2] + wrap_angle_f(b[2] - a[2]) * 0.5f;
+            float sn, cs;
+            sincosf(abar, &sn, &cs);
+            const float c = dx * sn - dy * cs;
+            s.cseg[j] = c;
+            const float kap = lam[j] + 2.f * e.constraint_weight * c;
+            hx += kap * sn; lx -= kap * sn;
+            hy -= kap * cs; ly += kap * cs;
+            const float dcda = kap * (dx * cs + dy * sn) * 0.5f;
+            hth += dcda; lth += dcda;
+            if (e.direction_weight != 0.f) {                 // :111-118,93,98 (wrap(a_j - a_{j+1}))
+                const float abar2 = a[2] + wrap_angle_f(a[2] - b[2]) * 0.5f;
+                float sn2, cs2;
+                sincosf(abar2, &sn2, &cs2);
+                const float dd = -(cs2 * dx + sn2 * dy);
+                const float rho = 2.f * e.direction_weight * relu_f(dd);
+                hx -= rho * cs2; lx += rho * cs2;
+                hy -= rho * sn2; ly += rho * sn2;
+                const float ddda = rho * (sn2 * dx - cs2 * dy);
+                lth += 1.5f * ddda;
+                hth -= 0.5f * ddda;
+            }
+            s.hi[j * 3 + 2] = hth; s.lo[j * 3 + 2] = lth;
+        }
+        s.hi[j * D] = hx; s.hi[j * D + 1] = hy;
+        s.lo[j * D] = lx; s.lo[j * D + 1] = ly;
+    }
+    __syncthreads();
+    // ---- per-point gradient ------------------------------------------------------------------------
+    for (int i = tid; i < T; i += TRAJ_THREADS) {
+        float g[3];
+        for (int d = 0; d < D; ++d) g[d] = s.hi[i * D + d] + s.lo[(i + 1) * D + d];
+        if (e.constrained) {                                  // boundary term nerf_opt_planner.py:171-176
+            const float x = s.full[(i + 1) * D], y = s.full[(i + 1) * D + 1];
+            g[0] += e.boundary_weight * 2.f * (relu_f(x - e.border_f[1]) - relu_f(-x + e.border_f[0]));
+            g[1] += e.boundary_weight * 2.f * (relu_f(y - e.border_f[3]) - relu_f(-y + e.border_f[2]));
+        }
+        float gmu = 0.f;
+        if (i < n) {                                          // q_i depends on X[i] with weight t_i
+            const float t = pt[i];
+            for (int d = 0; d < D; ++d) g[d] += t * gq[i * D + d];
+            gmu += t * tanhf(pz[i]);
+        }
+        if (i >= 1) {                                         // and on X[i] via q_{i-1} with weight 1-t
+            const float omt = 1.f - pt[i - 1];
+            for (int d = 0; d < D; ++d) g[d] += omt * gq[(i - 1) * D + d];
+            gmu += omt * tanhf(pz[i - 1]);
+        }
+        for (int d = 0; d < D; ++d) s.g[i * D + d] = g[d];
+        s.gm[i] = gmu;
+    }
+    __syncthreads();
+    // ---- grad <- inv_hessian @ grad (nerf_opt_planner.py:151), Adam (:154) --------------------------
+    for (int i = tid; i < T; i += TRAJ_THREADS) {
+        float acc[3] = {0.f, 0.f, 0.f};
+        for (int j = 0; j < T; ++j) {
+            const float h = __ldg(e.inv_hessian_t + (size_t)j * T + i);      // = inv_hessian[i][j], coalesced
+            for (int d = 0; d < D; ++d) acc[d] = fmaf(h, s.g[j * D + d], acc[d]);
+        }
+        for (int d = 0; d < D; ++d) {
+            const size_t o = (size_t)p * T * D + i * D + d;
+            float m = e.traj_m[o], v = e.traj_v[o], w = X[i * D + d];
+            const float gr = acc[d];
+            m = fmaf(e.traj_w1, gr - m, m);
+            v = fmaf(e.traj_w2 * gr, gr, v * e.traj_beta2);
+            const float denom = sqrtf(v) / sp.traj_bc2_sqrt + e.traj_eps;
+            w = fmaf(-sp.traj_step_size, m / denom, w);
+            e.traj_m[o] = m; e.traj_v[o] = v;
+            s.full[(i + 1) * D + d] = w;
+            if (!(w == w) || fabsf(w) > 3.0e38f) atomicOr(&e.status[p], STATUS_NONFINITE);
+        }
+        if (e.constrained) {                                   // constrained:68-73
+            float m2 = mu[i] + e.mu_lr * s.gm[i];
+            s.gm[i] = m2 > 0.f ? m2 : 0.f;
+        }
+    }
+    if (e.constrained)                                         // constrained:66 (ascent on the residual)
+        for (int j = tid; j <= T; j += TRAJ_THREADS) s.cseg[j] = lam[j] + e.multipliers_lr * s.cseg[j];
+    __syncthreads();
+    // now: s.full = updated path, s.gm = updated mu, s.cseg = updated lambda
+    store_path(e, s, p, sp.do_reparam != 0);
+}
+
+// update_goal_point / update_start_point (nerf_opt_planner.py:202-218, constrained:178-194) and tests:
+// re-parametrise the stored trajectory (and multipliers) of every problem without an optimisation step.
+__global__ void __launch_bounds__(TRAJ_THREADS) reparam_kernel(const EngineDev e) {
+    extern __shared__ __align__(16) float smem_f[];
+    const int p = blockIdx.x, tid = threadIdx.x, T = e.T, D = e.D;
+    TrajSmem s = carve_traj(smem_f, T, D);
+    const float *X = e.traj + (size_t)p * T * D;
+    for (int i = tid; i < (T + 2) * D; i += TRAJ_THREADS) {
+        int node = i / D, d = i - node * D;
+        s.full[i] = node == 0 ? e.start[(size_t)p * D + d]
+                              : (node == T + 1 ? e.goal[(size_t)p * D + d] : X[(node - 1) * D + d]);
+    }
+    for (int k = tid; k < T; k += TRAJ_THREADS) s.gm[k] = e.mu[(size_t)p * T + k];
+    for (int j = tid; j <= T; j += TRAJ_THREADS) s.cseg[j] = e.lam[(size_t)p * (T + 1) + j];
+    __syncthreads();
+    store_path(e, s, p, true);
+}
+
+// last kernel of a step: advance counters, precompute next step's flags and Adam bias corrections
+__global__ void tick_kernel(const EngineDev e, int trained_this_step_unknown) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    StepParams sp = *e.sp;
+    if (sp.do_train) { sp.onf_step += 1; sp.has_prev = 1; }
+    sp.traj_step += 1;
+    sp.step_count += 1;
+    sp.do_train = (sp.step_count % e.train_freq) == 0;
+    sp.do_reparam = (sp.step_count % e.reparam_freq) == 0;
+    const double ko = sp.onf_step + 1, kt = sp.traj_step + 1;
+    sp.onf_step_size = (float)(e.onf_lr_d / (1.0 - pow(e.onf_b1_d, ko)));
+    sp.onf_bc2_sqrt = (float)sqrt(1.0 - pow(e.onf_b2_d, ko));
+    sp.traj_step_size = (float)(e.traj_lr_d / (1.0 - pow(e.traj_b1_d, kt)));
+    sp.traj_bc2_sqrt = (float)sqrt(1.0 - pow(e.traj_b2_d, kt));
+    *e.sp = sp;
+}
+
+// warm-up iterations only advance the ONF optimiser
+__global__ void tick_warm_kernel(const EngineDev e) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    StepParams sp = *e.sp;
+    sp.onf_step += 1;
+    const double ko = sp.onf_step + 1;
+    sp.onf_step_size = (float)(e.onf_lr_d / (1.0 - pow(e.onf_b1_d, ko)));
+    sp.onf_bc2_sqrt = (float)sqrt(1.0 - pow(e.onf_b2_d, ko));
+    *e.sp = sp;
+}
+
+__global__ void paths_kernel(const EngineDev e, float *__restrict__ out) {
+    const int p = blockIdx.x, T = e.T, D = e.D;
+    for (int i = threadIdx.x; i < (T + 2) * D; i += blockDim.x) {
+        int node = i / D, d = i - node * D;
+        out[(size_t)p * (T + 2) * D + i] = node == 0 ? e.start[(size_t)p * D + d]
+                                           : (node == T + 1 ? e.goal[(size_t)p * D + d]
+                                                            : e.traj[((size_t)p * T + node - 1) * D + d]);
+    }
+}
+
+int launch_traj_pre(const EngineDev &e, cudaStream_t s) {
+    traj_pre_kernel<<<e.P, TRAJ_THREADS, 0, s>>>(e);
+    NFOPP_CHECK_CUDA(cudaGetLastError());
+    return NFOPP_OK;
+}
+int traj_prepare(const EngineDev &e) {
+    size_t smem = traj_smem_bytes(e.T, e.D);
+    NFOPP_REQUIRE(smem <= 227 * 1024, "trajectory_length=%d exceeds shared memory", e.T);
+    if (smem > 48 * 1024)
+    {
+        NFOPP_CHECK_CUDA(cudaFuncSetAttribute(traj_post_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        NFOPP_CHECK_CUDA(cudaFuncSetAttribute(reparam_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    }
+    return NFOPP_OK;
+}
+int launch_traj_post(const EngineDev &e, cudaStream_t s) {
+    traj_post_kernel<<<e.P, TRAJ_THREADS, traj_smem_bytes(e.T, e.D), s>>>(e);
+    NFOPP_CHECK_CUDA(cudaGetLastError());
+    return NFOPP_OK;
+}
+int launch_reparam(const EngineDev &e, cudaStream_t s) {
+    reparam_kernel<<<e.P, TRAJ_THREADS, traj_smem_bytes(e.T, e.D), s>>>(e);
+    NFOPP_CHECK_CUDA(cudaGetLastError());
+    return NFOPP_OK;
+}
+int launch_tick(const EngineDev &e, bool warm, cudaStream_t s) {
+    if (warm) tick_warm_kernel<<<1, 32, 0, s>>>(e);
+    else tick_kernel<<<1, 32, 0, s>>>(e, 0);
+    NFOPP_CHECK_CUDA(cudaGetLastError());
+    return NFOPP_OK;
+}
+int launch_paths(const EngineDev &e, float *out, cudaStream_t s) {
+    paths_kernel<<<e.P, 128, 0, s>>>(e, out);
+    NFOPP_CHECK_CUDA(cudaGetLastError());
+    return NFOPP_OK;
+}
+
+}  // namespace nfopp

@@ -1,0 +1,127 @@
+"""BatchedPlanner - P independent NFOPP problems on one GPU (what the reference can only do as P separate
+Python processes).  Same verbs as ContinuousPlanner: init / step / get_path, with [P, ...] arrays.
+
+Multi-GPU: problems are sharded contiguously over ranks with no collective inside the loop; `gather_paths`
+is the one exchange (torch.distributed all_gather of the final [P_local, T+2, D] paths)."""
+import math
+from dataclasses import replace
+
+import numpy as np
+import torch
+
+from .engine import EngineConfig, OnfSpec, PlannerEngine, onf_segments
+
+
+def init_onf_weights(spec: OnfSpec, problems: int, use_normal_init: bool, seed: int, device) -> torch.Tensor:
+    """[P, n_params] initial ONF weights with torch's nn.Linear default distribution
+    (U(-1/sqrt(fan_in), 1/sqrt(fan_in)) for weights and biases), N(0,1) Fourier matrix when use_normal_init,
+    phases U(-pi, pi), frequencies 1..10 twice - what ONF.__init__ (onf_model.py:8-31) draws, vectorised over
+    problems.  Distribution-equivalent to constructing P modules, not stream-identical."""
+    segs, n_params = onf_segments(spec)
+    gen = torch.Generator(device=device)
+    gen.manual_seed(int(seed))
+    w = torch.zeros(problems, n_params, dtype=torch.float32, device=device)
+
+    def uniform(name, bound):
+        off, shape = segs[name]
+        n = int(np.prod(shape))
+        if n:
+            w[:, off:off + n] = (torch.rand(problems, n, generator=gen, device=device) * 2 - 1) * bound
+
+    f_in = segs["W0"][1][1]
+    for l in range(spec.layers):
+        fan = f_in if l == 0 else spec.hidden
+        uniform(f"W{l}", 1 / math.sqrt(fan))
+        uniform(f"b{l}", 1 / math.sqrt(fan))
+    uniform("w_out", 1 / math.sqrt(spec.hidden + f_in))
+    uniform("b_out", 1 / math.sqrt(spec.hidden + f_in))
+    uniform("enc_w", 1 / math.sqrt(2))
+    if spec.bias:
+        uniform("enc_b", 1 / math.sqrt(2))
+    if use_normal_init:
+        off, shape = segs["enc_w"]
+        n = int(np.prod(shape))
+        w[:, off:off + n] = torch.randn(problems, n, generator=gen, device=device)
+    if spec.angle:
+        uniform("ang_b", math.pi)
+        off, _ = segs["ang_f"]
+        f = torch.linspace(1, 10, 10, device=device)
+        w[:, off:off + 20] = torch.cat([f, f])
+    return w
+
+
+def shard_range(total: int, rank: int, world: int):
+    """Contiguous, balanced partition of problem ids [0,total) over ranks."""
+    base, extra = divmod(total, world)
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
+class BatchedPlanner:
+    def __init__(self, config: EngineConfig, device="cuda", use_normal_init=True):
+        self.config = config
+        self.engine = PlannerEngine(config, device=device)
+        self.device = self.engine.device
+        self._use_normal_init = use_normal_init
+
+    def init(self, start_points, goal_points, obstacles=None, obstacle_counts=None, grids=None, onf_weights=None):
+        """start/goal: [P, D]; obstacles [P|1, M, 2] or grids [P|1, rows, cols]; onf_weights [P, n_params] or
+        None (fresh initialisation seeded by config.seed)."""
+        eng = self.engine
+        eng.set_endpoints(start_points, goal_points)
+        if obstacles is not None:
+            eng.set_obstacles(obstacles, obstacle_counts)
+        if grids is not None:
+            eng.set_grid(grids)
+        if onf_weights is None:
+            onf_weights = init_onf_weights(self.config.onf, self.config.problems, self._use_normal_init,
+                                           self.config.seed + 7919, self.device)
+        eng["onf_w"].copy_(torch.as_tensor(onf_weights).to(self.device))
+        eng.init_trajectories()
+        eng.warmup(self.config.init_collision_iteration)
+        eng.set_counter("step_count", 0)
+
+    def step(self, n_steps=1, graph=True):
+        self.engine.step(n_steps, graph=graph and self.config.rng_mode == "philox")
+
+    def get_path(self) -> np.ndarray:
+        return self.engine.paths().cpu().numpy()
+
+    def paths(self) -> torch.Tensor:
+        return self.engine.paths()
+
+    def status(self) -> np.ndarray:
+        return self.engine["status"].cpu().numpy()
+
+    def gather_paths(self) -> torch.Tensor:
+        """All ranks' final paths on every rank (the only collective of the whole job).  Ranks may own
+        different numbers of problems; shards are padded to the largest for the all_gather."""
+        import torch.distributed as dist
+        local = self.engine.paths()
+        if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+            return local
+        world = dist.get_world_size()
+        counts = [torch.zeros(1, dtype=torch.int64, device=local.device) for _ in range(world)]
+        dist.all_gather(counts, torch.tensor([local.shape[0]], dtype=torch.int64, device=local.device))
+        biggest = int(max(int(c) for c in counts))
+        padded = torch.zeros(biggest, *local.shape[1:], dtype=local.dtype, device=local.device)
+        padded[:local.shape[0]] = local
+        parts = [torch.empty_like(padded) for _ in range(world)]
+        dist.all_gather(parts, padded)
+        return torch.cat([p[:int(c)] for p, c in zip(parts, counts)], 0)
+
+
+def corridor_config(problems: int, seed=0, **overrides) -> EngineConfig:
+    """BASELINE config 2: scripts/run_planner.py hyper-parameters (:14-55), forward-only
+    (direction_delta_weight=100, scripts/run_bench_mr.py:60), disc robot r=0.3 in jittered S-bend corridors."""
+    cfg = EngineConfig(
+        problems=problems, constrained=True, trajectory_length=100,
+        onf=OnfSpec(mean=0.0, sigma=1.0, use_cos=True, angle=True, hidden=100, layers=2),
+        onf_lr=5e-2, onf_betas=(0.9, 0.9), traj_lr=1e-2, traj_betas=(0.9, 0.9),
+        trajectory_random_offset=0.02, collision_weight=1.0, velocity_hessian_weight=0.5, random_field_points=10,
+        init_collision_iteration=0, constraint_deltas_weight=20.0, multipliers_lr=0.1, init_collision_points=100,
+        reparametrize_trajectory_freq=10, optimize_collision_model_freq=1, angle_weight=0.5, angle_offset=0.3,
+        boundary_weight=1.0, collision_multipliers_lr=1e-3, direction_delta_weight=100.0,
+        checker="circle", env_shared=False, max_obstacles=20, robot_radius=0.3, checker_bounds=(0.0, 3.0, 0.0, 3.0),
+        border=(-0.1, 3.1, -0.1, 3.1), rng_mode="philox", seed=seed)
+    return replace(cfg, **overrides)

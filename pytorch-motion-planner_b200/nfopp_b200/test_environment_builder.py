@@ -1,0 +1,86 @@
+"""The reference's fixed toy worlds (test_environment_builder.py:8-54) plus seeded batch generators for the
+BASELINE configs (jittered corridor walls, random-obstacle grids)."""
+import numpy as np
+
+from .test_environment import TestEnvironment
+
+_BOUNDS = (-0.1, 3.1, -0.1, 3.1)
+
+
+def _segment(p, q, count):
+    """`count` points from p to q inclusive."""
+    s = np.linspace(0.0, 1.0, count)[:, None]
+    return np.asarray(p, dtype=np.float64)[None] * (1 - s) + np.asarray(q, dtype=np.float64)[None] * s
+
+
+class TestEnvironmentBuilder(object):
+    __test__ = False
+
+    @staticmethod
+    def _obstacle_points():
+        # two vertical walls of 10 points: x=1.15, y in [0,2] and x=1.85, y in [1,3]  (:16-22)
+        y = np.linspace(0, 2, 10)
+        left = np.column_stack([np.full(10, 1.15), y])
+        right = np.column_stack([np.full(10, 1.85), y + 1])
+        return np.vstack([left, right])
+
+    @staticmethod
+    def _point_line(start, end, point_count):
+        return np.column_stack([np.linspace(start[0], end[0], point_count), np.linspace(start[1], end[1], point_count)])
+
+    @staticmethod
+    def _car_obstacle_points():
+        # parking nook: 4 walls of 10 points (:38-54)
+        top, left = 2.3, 1.6
+        walls = [((0, top), (left, top)), ((left, top), (left, 3)), ((2.5, top), (2.5, 3)), ((2.5, top), (3, top))]
+        return np.vstack([TestEnvironmentBuilder._point_line(a, b, 10) for a, b in walls])
+
+    @staticmethod
+    def make_test_environment():
+        return TestEnvironment(np.array([0.5, 0.5], dtype=np.float32), np.array([2.5, 2.5], dtype=np.float32), _BOUNDS,
+                               TestEnvironmentBuilder._obstacle_points())
+
+    @staticmethod
+    def make_test_environment_with_angles():
+        return TestEnvironment(np.array([0.5, 0.5, 0], dtype=np.float32), np.array([2.5, 1.5, 0], dtype=np.float32),
+                               _BOUNDS, TestEnvironmentBuilder._obstacle_points())
+
+    def make_car_environment(self):
+        return TestEnvironment(np.array([0.5, 1.5, 0], dtype=np.float32), np.array([2, 2.7, 0], dtype=np.float32),
+                               _BOUNDS, TestEnvironmentBuilder._car_obstacle_points())
+
+    # ---- batch generators (not in the reference: it has no batching) ----------
+    @staticmethod
+    def make_corridor_batch(problems, seed=0, points_per_wall=10):
+        """Jittered S-bend corridors: wall x ~ U(0.9,1.4)/(1.6,2.1), gap offsets ~ U(-0.3,0.3); problem i uses
+        RandomState(seed + i).  Returns (starts [P,3], goals [P,3], bounds, obstacles [P, 2*ppw, 2])."""
+        starts = np.tile(np.array([0.5, 0.5, 0], dtype=np.float32), (problems, 1))
+        goals = np.tile(np.array([2.5, 1.5, 0], dtype=np.float32), (problems, 1))
+        obstacles = np.empty((problems, 2 * points_per_wall, 2))
+        for i in range(problems):
+            rs = np.random.RandomState(seed + i)
+            x_left, x_right = rs.uniform(0.9, 1.4), rs.uniform(1.6, 2.1)
+            off_l, off_r = rs.uniform(-0.3, 0.3, 2)
+            obstacles[i, :points_per_wall] = _segment((x_left, 0 + off_l), (x_left, 2 + off_l), points_per_wall)
+            obstacles[i, points_per_wall:] = _segment((x_right, 1 + off_r), (x_right, 3 + off_r), points_per_wall)
+            goals[i, 1] = np.float32(1.5 + rs.uniform(-0.5, 0.5))
+        return starts, goals, _BOUNDS, obstacles
+
+    @staticmethod
+    def make_random_grid_batch(problems, rows=100, cols=100, obstacle_ratio=0.03, cell=0.03, seed=0):
+        """Random-obstacle occupancy grids (forest-style, obstacle_ratio 0.03); problem i uses
+        RandomState(seed + i).  A free disc is cleared around start and goal.
+        Returns (starts [P,3], goals [P,3], bounds, grids [P,rows,cols] uint8, origin, cell)."""
+        grids = np.zeros((problems, rows, cols), dtype=np.uint8)
+        w, h = cols * cell, rows * cell
+        starts = np.tile(np.array([0.15 * w, 0.15 * h, 0], dtype=np.float32), (problems, 1))
+        goals = np.tile(np.array([0.85 * w, 0.85 * h, 0], dtype=np.float32), (problems, 1))
+        yy, xx = np.mgrid[0:rows, 0:cols]
+        cx, cy = (xx + 0.5) * cell, (yy + 0.5) * cell
+        for i in range(problems):
+            rs = np.random.RandomState(seed + i)
+            g = rs.rand(rows, cols) < obstacle_ratio
+            for pt in (starts[i], goals[i]):
+                g &= (cx - pt[0]) ** 2 + (cy - pt[1]) ** 2 > (4 * cell) ** 2
+            grids[i] = g
+        return starts, goals, (0.0, w, 0.0, h), grids, (0.0, 0.0), cell

@@ -1,0 +1,111 @@
+"""GPU: the reference-facing Python API (what the reference's own tests assert, test/test_nerf_opt_planner.py
+:28-50 and test/test_constrained_nerf_opt_planner.py:30-50, plus path quality of the batched planner)."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+RUN_PLANNER = dict(
+    device="cuda", trajectory_length=100,
+    collision_model=dict(mean=0, sigma=1, use_cos=True, bias=True, use_normal_init=True, angle_encoding=True,
+                         name="ONF"),
+    trajectory_initializer=dict(name="TrajectoryInitializer", resolution=0.05),
+    collision_optimizer=dict(lr=5e-2, betas=(0.9, 0.9)), trajectory_optimizer=dict(lr=1e-2, betas=(0.9, 0.9)),
+    planner=dict(name="ConstrainedNERFOptPlanner", trajectory_random_offset=0.02, collision_weight=1,
+                 velocity_hessian_weight=0.5, random_field_points=10, init_collision_iteration=0,
+                 constraint_deltas_weight=20, multipliers_lr=0.1, init_collision_points=100,
+                 reparametrize_trajectory_freq=10, optimize_collision_model_freq=1, angle_weight=0.5,
+                 angle_offset=0.3, boundary_weight=1, collision_multipliers_lr=1e-3))
+
+
+def _attr(d):
+    from nfopp_b200.utils.attribute_dict import AttributeDict
+    return AttributeDict({k: _attr(v) if isinstance(v, dict) else v for k, v in d.items()})
+
+
+def test_holonomic_planner_api():
+    from nfopp_b200.collision_checker import CircleCollisionChecker
+    from nfopp_b200.planner_factory import PlannerFactory
+    from nfopp_b200.test_environment_builder import TestEnvironmentBuilder
+    np.random.seed(400); torch.manual_seed(100)
+    env = TestEnvironmentBuilder.make_test_environment()
+    checker = CircleCollisionChecker(0.3, (0, 3, 0, 3))
+    checker.update_obstacle_points(env.obstacle_points)
+    planner = PlannerFactory.make_onf_planner(checker)
+    planner.init(env.start_point, env.goal_point, env.bounds)
+    path = planner.get_path()
+    assert path.shape == (102, 2) and path.dtype == np.float32
+    assert np.allclose(path[0], env.start_point) and np.allclose(path[-1], env.goal_point)
+    for _ in range(100):
+        planner.step()
+    path = planner.get_path()
+    assert path.shape == (102, 2) and np.isfinite(path).all()
+    assert np.allclose(path[0], env.start_point) and np.allclose(path[-1], env.goal_point)
+    assert planner._step_count == 100
+    assert planner.checked_positions.shape == (209, 2) and planner.truth_collision.shape == (209,)
+    assert planner._collision_positions.shape == (100, 2)
+    assert planner._collision_model is not None and planner._device.type == "cuda"
+
+
+def test_constrained_planner_api_and_quality():
+    from nfopp_b200.collision_checker import RectangleCollisionChecker
+    from nfopp_b200.planner_factory import PlannerFactory
+    from nfopp_b200.test_environment_builder import TestEnvironmentBuilder
+    from nfopp_b200.utils.position2 import Position2
+    np.random.seed(400); torch.manual_seed(100)
+    env = TestEnvironmentBuilder().make_car_environment()
+    checker = RectangleCollisionChecker((-0.3, 0.2, -0.3, 0.2), (0, 3, 0, 3))
+    checker.update_obstacle_points(env.obstacle_points)
+    planner = PlannerFactory.make_constrained_onf_planner(checker, _attr(RUN_PLANNER))
+    planner.init(env.start_point, env.goal_point, env.bounds)
+    assert planner.get_path().shape == (102, 3)
+    planner.step()
+    w0 = planner._collision_model.mlp[0].weight.detach().clone()
+    for _ in range(299):
+        planner.step()
+    path = planner.get_path()
+    assert path.shape == (102, 3) and np.isfinite(path).all()
+    assert np.allclose(path[0], env.start_point) and np.allclose(path[-1], env.goal_point)
+    # module parameters are live views of the engine's weights
+    assert not torch.equal(w0, planner._collision_model.mlp[0].weight.detach())
+    # reference path quality after 300 steps (collision-free, non-holonomic residual ~0.03)
+    assert not checker.check_collision(Position2.from_vec(path.astype(np.float64))).any()
+    dx, dy = np.diff(path[:, 0]), np.diff(path[:, 1])
+    abar = path[:-1, 2] + ((np.diff(path[:, 2]) + np.pi) % (2 * np.pi) - np.pi) / 2
+    assert np.abs(dx * np.sin(abar) - dy * np.cos(abar)).max() < 0.1
+    assert isinstance(planner.checked_positions, Position2)
+    # warm re-planning API
+    planner.update_goal_point(np.array([2.0, 2.6, 0.0], dtype=np.float32))
+    planner.update_start_point(np.array([0.6, 1.5, 0.0], dtype=np.float32))
+    assert planner._step_count == 0
+    planner.step()
+    assert np.isfinite(planner.get_path()).all()
+
+
+def test_unknown_class_in_config_raises_keyerror():
+    from nfopp_b200.collision_checker import CircleCollisionChecker
+    from nfopp_b200.planner_factory import PlannerFactory
+    bad = _attr(RUN_PLANNER)
+    bad["collision_model"]["name"] = "NoSuchField"
+    with pytest.raises(KeyError):
+        PlannerFactory.make_constrained_onf_planner(CircleCollisionChecker(0.3), bad)
+
+
+def test_batched_corridors_reach_reference_quality():
+    """64 jittered corridor problems, 300 steps in Philox mode through a CUDA graph: paths finite, endpoints
+    pinned, and most problems collision-free (the reference solves its own S-bend in 300 steps)."""
+    from nfopp_b200.batched import BatchedPlanner, corridor_config
+    from nfopp_b200.test_environment_builder import TestEnvironmentBuilder
+    from oracle import checkers as OC
+    P = 64
+    starts, goals, bounds, obstacles = TestEnvironmentBuilder.make_corridor_batch(P, seed=0)
+    planner = BatchedPlanner(corridor_config(P, seed=3))
+    planner.init(starts, goals, obstacles=obstacles)
+    planner.step(300)
+    paths = planner.get_path()
+    assert paths.shape == (P, 102, 3) and np.isfinite(paths).all()
+    assert np.allclose(paths[:, 0], starts) and np.allclose(paths[:, -1], goals)
+    assert (planner.status() == 0).all()
+    free = [not OC.circle_labels(paths[p].astype(np.float64), obstacles[p], 0.3, (0, 3, 0, 3)).any() for p in range(P)]
+    assert np.mean(free) > 0.8, f"only {np.mean(free):.2f} of the corridor problems are collision-free"

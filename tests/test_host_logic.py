@@ -1,0 +1,185 @@
+"""CPU: host-side logic, C-ABI surface and multi-rank sharding (no GPU compute calls)."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+
+import _util as U
+from oracle import onf as O
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_loads_and_exports_every_declared_symbol():
+    from nfopp_b200 import _lib as L
+    header = open(os.path.join(ROOT, "include", "nfopp.h")).read()
+    declared = set(re.findall(r"\b(nfopp_[a-z_]+)\s*\(", header))
+    assert declared, "no declarations parsed"
+    handle = L.lib()
+    for name in declared:
+        assert hasattr(handle, name), f"{name} declared in include/nfopp.h but not exported"
+    assert declared == set(L.SIGNATURES), declared ^ set(L.SIGNATURES)
+    assert handle.nfopp_abi_version() == 1
+
+
+@pytest.mark.parametrize("name", list(U.ONF_CFGS))
+def test_blob_layout_matches_oracle(name):
+    from nfopp_b200.engine import OnfSpec, onf_segments
+    cfg = U.ONF_CFGS[name]
+    segs, total = onf_segments(OnfSpec(cfg.mean, cfg.sigma, cfg.use_cos, cfg.angle, cfg.hidden, cfg.layers))
+    lay, ototal = O.onf_layout(cfg)
+    assert total == ototal
+    assert {k: (o, tuple(s)) for k, (o, s) in segs.items()} == {k: (o, tuple(s)) for k, (o, s) in lay.items()}
+
+
+def test_invalid_configs_are_rejected_with_valueerror():
+    from nfopp_b200 import _lib as L
+    from nfopp_b200.engine import EngineConfig, OnfSpec
+    n = C.c_size_t()
+    for bad in (EngineConfig(onf=OnfSpec(hidden=30)), EngineConfig(trajectory_length=1),
+                EngineConfig(constrained=False, onf=OnfSpec(angle=True)),
+                EngineConfig(constrained=False, checker="rectangle")):
+        c = bad.to_c()
+        with pytest.raises(ValueError):
+            L.check(L.lib().nfopp_engine_workspace_bytes(C.byref(c), C.byref(n)))
+    ok = EngineConfig(problems=1024, onf=OnfSpec(use_cos=True, angle=True)).to_c()
+    L.check(L.lib().nfopp_engine_workspace_bytes(C.byref(ok), C.byref(n)))
+    assert 1024 * 33164 * 4 * 3 < n.value < 4 * 2 ** 30
+
+
+def test_no_cuda_means_loud_failure_not_fallback():
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from nfopp_b200 import _lib as L
+    from nfopp_b200.engine import EngineConfig, PlannerEngine
+    from nfopp_b200.onf_model import ONF
+    with pytest.raises(L.NfoppError):
+        PlannerEngine(EngineConfig())
+    with pytest.raises(L.NfoppError):
+        ONF(0, 1)(torch.zeros(4, 2))
+
+
+def test_onf_module_matches_reference_constructor_stream():
+    """Same torch seed => same initial weights as the reference's ONF (construction order is preserved);
+    checked against the golden weights the reference module produced (oracle/make_golden.py seeds 10,11,12)."""
+    from nfopp_b200.onf_model import ONF
+    fx = U.load("onf.npz")
+    cases = {"holonomic": (10, dict(mean=1.5, sigma=1)),
+             "car": (11, dict(mean=0, sigma=1, use_cos=True, use_normal_init=True, angle_encoding=True)),
+             "image": (12, dict(mean=0, sigma=7, use_cos=True, use_normal_init=True))}
+    for name, (seed, kw) in cases.items():
+        torch.manual_seed(seed)
+        model = ONF(**kw)
+        assert np.array_equal(model.packed_parameters().numpy(), fx[f"{name}/w"]), name
+        sd = model.state_dict()
+        model2 = ONF(**kw)
+        model2.load_state_dict(sd)
+        assert torch.equal(model2.packed_parameters(), model.packed_parameters())
+
+
+def test_batched_linspace_equals_torch_linspace():
+    from nfopp_b200.engine import batched_linspace
+    rs = np.random.RandomState(0)
+    a, b = torch.tensor(rs.uniform(-5, 5, 64).astype(np.float32)), torch.tensor(rs.uniform(-5, 5, 64).astype(np.float32))
+    got = batched_linspace(a, b, 102)
+    for i in range(64):
+        assert torch.equal(got[i], torch.linspace(a[i], b[i], 102)), i
+
+
+def test_environment_builder_matches_reference_geometry():
+    from nfopp_b200.test_environment_builder import TestEnvironmentBuilder as B
+    fx = U.load("checkers.npz")
+    assert np.array_equal(B._obstacle_points(), fx["obstacles_sbend"])
+    assert np.array_equal(B._car_obstacle_points(), fx["obstacles_car"])
+    env = B().make_car_environment()
+    assert env.start_point.dtype == np.float32 and tuple(env.bounds) == (-0.1, 3.1, -0.1, 3.1)
+    s, g, bounds, obs = B.make_corridor_batch(5, seed=1)
+    s2, g2, _, obs2 = B.make_corridor_batch(5, seed=1)
+    assert np.array_equal(obs, obs2) and obs.shape == (5, 20, 2) and not np.array_equal(obs[0], obs[1])
+
+
+def test_universal_factory_semantics():
+    from nfopp_b200.utils.attribute_dict import AttributeDict
+    from nfopp_b200.utils.universal_factory import UniversalFactory
+
+    class Thing:
+        def __init__(self, a, b=2):
+            self.a, self.b = a, b
+    f = UniversalFactory([Thing])
+    t = f.make_from_parameters(AttributeDict(name="Thing", a=1, ignored=5), b=7)
+    assert (t.a, t.b) == (1, 7)
+    with pytest.raises(KeyError, match="Unknown class"):
+        f.make_from_parameters(dict(name="Other"))
+    assert f.make_from_parameters(3) == 3
+
+
+def test_numpy_pairwise_sum_restatement():
+    """The CUDA resampler restates numpy's pairwise summation (sample.cu np_pairwise_sum); this is the same
+    algorithm in Python, checked against np.sum for the sizes the planner uses."""
+    def pw(a):
+        n = len(a)
+        if n < 8:
+            r = 0.0
+            for v in a:
+                r += v
+            return r
+        if n <= 128:
+            r = list(a[:8])
+            i = 8
+            while i < n - n % 8:
+                for j in range(8):
+                    r[j] += a[i + j]
+                i += 8
+            res = ((r[0] + r[1]) + (r[2] + r[3])) + ((r[4] + r[5]) + (r[6] + r[7]))
+            for v in a[i:]:
+                res += v
+            return res
+        n2 = n // 2
+        n2 -= n2 % 8
+        return pw(a[:n2]) + pw(a[n2:])
+    rs = np.random.RandomState(1)
+    for n in (5, 99, 100, 128, 129, 198, 199, 300, 1000):
+        a = rs.gamma(0.3, size=n)
+        assert pw(a) == np.sum(a), n
+
+
+def test_shard_range_partitions_all_problems():
+    from nfopp_b200.batched import shard_range
+    for total in (1, 7, 1024, 16384, 16385):
+        for world in (1, 2, 3, 8):
+            spans = [shard_range(total, r, world) for r in range(world)]
+            assert spans[0][0] == 0 and spans[-1][1] == total
+            assert all(spans[i][1] == spans[i + 1][0] for i in range(world - 1))
+            sizes = [b - a for a, b in spans]
+            assert max(sizes) - min(sizes) <= 1
+
+
+def _gather_worker(rank, world, port, out):
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from nfopp_b200.batched import BatchedPlanner, shard_range
+    lo, hi = shard_range(5, rank, world)
+
+    class FakeEngine:
+        def paths(self):
+            return torch.arange(lo, hi, dtype=torch.float32)[:, None, None].expand(hi - lo, 4, 3).contiguous()
+    bp = BatchedPlanner.__new__(BatchedPlanner)
+    bp.engine = FakeEngine()
+    got = bp.gather_paths()
+    torch.save(got, f"{out}.{rank}")
+    dist.destroy_process_group()
+
+
+def test_gather_paths_world_size_2_gloo(tmp_path):
+    """The one collective of the job (final path gather), uneven shards, over gloo on CPU."""
+    import torch.multiprocessing as mp
+    out = str(tmp_path / "g")
+    mp.spawn(_gather_worker, args=(2, 29533, out), nprocs=2, join=True)
+    for r in range(2):
+        got = torch.load(f"{out}.{r}")
+        assert got.shape == (5, 4, 3)
+        assert torch.equal(got[:, 0, 0], torch.arange(5, dtype=torch.float32))
