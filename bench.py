@@ -1,0 +1,297 @@
+#!/usr/bin/env python
+"""bench.py - NFOPP optimisation inner loop on B200: planner problem-steps/s.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--problems P]
+
+Workload (BASELINE.json configs[1]): non-holonomic forward-only ConstrainedNERFOptPlanner problems in jittered
+S-bend corridors (scripts/run_planner.py hyper-parameters, direction_delta_weight=100), 1024 problems per GPU,
+each with its own ONF weights, trajectory, obstacle set and RNG stream.  A "step" is one planner.step() of all
+problems.  N>1 (torchrun): problems are sharded, 1024 per GPU (weak scaling), no collective in the loop.
+
+JSON line: `value` = problem-steps/s with all state resident in HBM (CUDA-graph replay); `e2e` = the same metric
+through the host-facing API with HOST buffers: every step copies that step's environments (obstacle sets, start,
+goal) from pinned host memory and reads the paths back; `roofline` = the dominant kernel (ONF train fwd+bwd)
+timed live with CUDA events; `cpu_baseline` = the CPU oracle (restatement of the reference) on the host cores.
+"""
+import argparse
+import ctypes as C
+import json
+import multiprocessing as mp
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "pytorch-motion-planner_b200"), os.path.join(ROOT, "tests")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+METRIC = "planner problem-steps/s"
+UNIT = "problem-steps/s"
+PROBLEMS_PER_GPU = 1024
+
+
+def workload_config(problems):
+    return {"workload": "configs[1]: corridor, non-holonomic forward-only ConstrainedNERFOptPlanner",
+            "problems_per_gpu": problems, "trajectory_length": 100, "onf": "F_in=220 (200 Fourier + 20 angle), 2x100 hidden",
+            "samples_per_step": 209, "checker": "disc r=0.3 vs 20 obstacle points per problem",
+            "rng": "on-device Philox4x32-10", "launch": "CUDA graph of 9 kernels per step",
+            "l2": "per-step working set (ONF w/m/v + gradient partials, ~1.3 GB at 1024 problems) exceeds the 126 MB L2"}
+
+
+# ----------------------------------------------------------------------------------------- CPU baseline
+def _oracle_worker(args):
+    """Runs the CPU oracle (reference restatement) on one corridor problem for `budget` seconds."""
+    seed, budget = args
+    import numpy as np
+    import torch
+    torch.set_num_threads(1)
+    from oracle import checkers as OC
+    from oracle import onf as O
+    from oracle.planner import LiveSource, OraclePlanner, PlannerConfig
+    from nfopp_b200.test_environment_builder import TestEnvironmentBuilder
+    starts, goals, bounds, obstacles = TestEnvironmentBuilder.make_corridor_batch(1, seed=seed)
+    ocfg = O.OnfConfig(mean=0.0, sigma=1.0, use_cos=True, angle=True)
+    cfg = PlannerConfig(constrained=True, onf=ocfg, onf_lr=5e-2, onf_betas=(0.9, 0.9), traj_lr=1e-2,
+                        traj_betas=(0.9, 0.9), init_collision_iteration=0, angle_offset=0.3,
+                        direction_delta_weight=100.0)
+    blob = O.init_blob(ocfg, True, torch.Generator().manual_seed(seed))
+    op = OraclePlanner(cfg, blob, lambda p: OC.circle_labels(p, obstacles[0], 0.3, (0, 3, 0, 3)))
+    src = LiveSource(np.random.RandomState(seed), torch.Generator().manual_seed(seed))
+    op.init(starts[0], goals[0], bounds, src)
+    for _ in range(20):
+        op.step(src)
+    n, t0 = 0, time.perf_counter()
+    while time.perf_counter() - t0 < budget:
+        op.step(src)
+        n += 1
+    return n, time.perf_counter() - t0
+
+
+def cpu_baseline(cores, budget):
+    """problem-steps/s of the oracle with `cores` independent single-thread processes (the only way the
+    reference batches)."""
+    ctx = mp.get_context("spawn")
+    with ctx.Pool(cores) as pool:
+        res = pool.map(_oracle_worker, [(i, budget) for i in range(cores)])
+    value = sum(n / t for n, t in res)
+    return {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"{cores} independent corridor problems x {budget:.0f} s of oracle planner.step() each "
+                      f"({sum(n for n, _ in res)} steps), 1 torch thread per process"}
+
+
+# ----------------------------------------------------------------------------------------- clocks
+class ClockSampler:
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self._stop = index, [], threading.Event()
+        self._thread = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.FIELDS}",
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                self.rows.append([c.strip() for c in out.strip().split(",")])
+            except Exception:
+                pass
+            self._stop.wait(0.2)
+
+    def __enter__(self):
+        self._thread.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        self._thread.join(timeout=6)
+
+    def summary(self):
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+                for name, v in zip(names, r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            except Exception:
+                continue
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------------------- ours
+def run_ours(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from nfopp_b200.batched import BatchedPlanner, corridor_config, shard_range
+    from nfopp_b200.engine import onf_segments
+    from nfopp_b200.test_environment_builder import TestEnvironmentBuilder
+
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    P = args.problems
+    lo, hi = shard_range(P * world, rank, world)            # this rank's problem ids (weak scaling)
+    starts, goals, bounds, obstacles = TestEnvironmentBuilder.make_corridor_batch(hi - lo, seed=lo)
+    cfg = corridor_config(hi - lo, seed=1234 + lo)
+    planner = BatchedPlanner(cfg, device=f"cuda:{local}")
+    planner.init(starts, goals, obstacles=obstacles)
+    eng = planner.engine
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn(steps)
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms)
+
+    # ---- device-resident throughput: CUDA-graph replay --------------------------------------------
+    planner.step(args.warmup)
+    launches0 = eng.launches
+    with ClockSampler(local) as clocks:
+        ms = timed(lambda k: planner.step(k), args.steps)
+    launches = eng.launches - launches0
+    value = P * world * args.steps / (ms * 1e-3)
+
+    # ---- end-to-end through the host-facing API with HOST buffers ------------------------------------
+    h_obs = torch.as_tensor(obstacles).pin_memory()
+    h_start, h_goal = torch.as_tensor(starts).pin_memory(), torch.as_tensor(goals).pin_memory()
+    h_paths = torch.empty(hi - lo, 102, 3, dtype=torch.float32).pin_memory()
+    d_paths = torch.empty(hi - lo, 102, 3, dtype=torch.float32, device="cuda")
+    h2d = h_obs.numel() * 8 + (h_start.numel() + h_goal.numel()) * 4
+    d2h = h_paths.numel() * 4
+
+    def e2e_steps(k):
+        for _ in range(k):
+            eng["obstacles"].copy_(h_obs, non_blocking=True)      # update_obstacle_points for every problem
+            eng["start"].copy_(h_start, non_blocking=True)
+            eng["goal"].copy_(h_goal, non_blocking=True)
+            planner.step(1)
+            eng.paths(out=d_paths)
+            h_paths.copy_(d_paths, non_blocking=True)             # get_path()
+        torch.cuda.current_stream().synchronize()
+    e2e_steps(max(3, args.warmup // 2))
+    e2e_k = max(3, args.steps // 2)
+    ms_e2e = timed(e2e_steps, e2e_k)
+    e2e_value = P * world * e2e_k / (ms_e2e * 1e-3)
+
+    # ---- live per-kernel timing (CUDA events on the launching stream) -> roofline of the dominant kernel ----
+    prof = {}
+    reps = 5
+    for _ in range(reps):
+        for k, v in eng.profile_step().items():
+            prof[k] = prof.get(k, 0.0) + v / reps
+    barrier()
+    finite = bool(torch.isfinite(eng.paths()).all())
+    all_paths = planner.gather_paths()                           # the one collective of the job (NCCL)
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak_tf = peaks.get("bf16_tflops_sustained", 1400.0)
+    segs, n_params = onf_segments(cfg.onf)
+    f_pos, f_in, H, L = 200, 220, cfg.onf.hidden, cfg.onf.layers
+    mac = 2 * f_pos + f_in * H + (L - 1) * H * H + (H + f_in)            # MAC / point / pass
+    dom = max(prof, key=prof.get)
+    train_ms = prof["onf_train_fwd_bwd"]
+    flops_launch = 3 * 2 * mac * 209 * (hi - lo)                           # fwd + dgrad + wgrad over 209 points
+    achieved = flops_launch / (train_ms * 1e-3) / 1e12
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "roofline_traffic.json"))).get("onf_train_fwd_bwd")
+    except Exception:
+        pass
+    step_bytes = (24 * n_params + 15_000) * (hi - lo)                     # bytes / problem-step
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "config": workload_config(P),
+        "clocks": clocks.summary(),
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "steps": e2e_k, "ms_per_step": ms_e2e / e2e_k},
+        "gpu_launches": int(launches),
+        "roofline": {"kernel": "onf_tile_kernel (ONF train fwd+bwd, FMA path)", "bound": "tensor",
+                     "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved / peak_tf,
+                     "traffic": traffic, "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained (of measured)"
+                     if peaks else "fallback",
+                     "ms_per_launch": train_ms, "dominant_kernel": dom,
+                     "whole_step_hbm": {"algorithmic_bytes": step_bytes,
+                                        "achieved_gbs": step_bytes / (ms / args.steps * 1e-3) / 1e9,
+                                        "peak_gbs": peaks.get("hbm_gbs", 6650.0)}},
+        "kernel_ms": prof,
+        "paths_finite": finite, "paths_gathered": list(all_paths.shape),
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        cores = max(1, min(os.cpu_count() or 1, 32))
+        line["cpu_baseline"] = cpu_baseline(cores, args.cpu_seconds)
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# ----------------------------------------------------------------------------------------- reference arm
+def run_reference(args):
+    """The reference's own CPU implementation of the path: /root/reference cannot travel to the GPU box, so
+    this times the oracle port (pinned in lock-step against the live reference, tests/golden) on all host
+    cores, same config and metric; each step = a bounded sample (one planner.step() per process)."""
+    rank = int(os.environ.get("RANK", 0))
+    if rank != 0:
+        return
+    cores = max(1, os.cpu_count() or 1)
+    budget = max(2.0, min(30.0, args.cpu_seconds))
+    base = cpu_baseline(cores, budget)
+    line = {"impl": "reference", "metric": METRIC, "value": base["value"], "unit": UNIT,
+            "n_gpus": int(os.environ.get("WORLD_SIZE", args.gpus)), "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * cores / base["value"], "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args.problems),
+            "cpu_baseline": base,
+            "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--problems", type=int, default=PROBLEMS_PER_GPU, help="problems per GPU")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

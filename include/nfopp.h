@@ -179,6 +179,10 @@ int nfopp_engine_warmup(nfopp_engine *e, int iterations, void *stream);
 /* NERFOptPlanner.step (nerf_opt_planner.py:60-71) / the constrained overrides, `n_steps` times for all P
  * problems.  use_graph != 0 replays a captured CUDA graph of one step (Philox mode only). */
 int nfopp_engine_step(nfopp_engine *e, int n_steps, int use_graph, void *stream);
+/* One step() launched kernel by kernel with CUDA events in between (no graph): ms_out[0..9) = device time of the
+ * nine kernels of a step, in launch order; nfopp_engine_kernel_name(i) names them.  bench.py's live roofline. */
+int nfopp_engine_profile_step(nfopp_engine *e, float *ms_out, int n_out, void *stream);
+const char *nfopp_engine_kernel_name(int index);
 /* NERFOptPlanner.get_path / full_trajectory (nerf_opt_planner.py:73-74,178-179): [P, T+2, D] float32 */
 int nfopp_engine_get_paths(nfopp_engine *e, float *paths_dev, void *stream);
 /* NERFOptPlanner.reparametrize_trajectory (nerf_opt_planner.py:224-244; constrained:132-171) on the stored

@@ -248,7 +248,8 @@ static int build_layout(nfopp_engine *e) {
     d.max_choice_u = (int)MU;
     const size_t PE = c.env_shared ? 1 : P;
 
-    add_buffer(e, "step_params", &d.sp, 'i', sizeof(StepParams) / 4);
+    add_buffer(e, "step_params", &d.sp, 'i', 1);
+    e->buffers.back().dims[0] = (int32_t)(sizeof(StepParams) / 4);
     add_buffer(e, "onf_w", &d.onf_w, 'f', P, NP);
     add_buffer(e, "onf_m", &d.onf_m, 'f', P, NP);
     add_buffer(e, "onf_v", &d.onf_v, 'f', P, NP);
@@ -437,7 +438,7 @@ extern "C" int nfopp_engine_set_counter(nfopp_engine *e, int which, int64_t valu
 }
 
 // one ONF training update on train_x/train_y/train_n (nerf_opt_planner.py:83-90)
-static int enqueue_train(nfopp_engine *e, bool warm, cudaStream_t s) {
+static int enqueue_train(nfopp_engine *e, bool warm, cudaStream_t s, cudaEvent_t *ev = nullptr) {
     const EngineDev &d = e->dev;
     OnfArgs a{};
     a.d = e->onf; a.weights = d.onf_w; a.x = d.train_x; a.count = d.train_n; a.n = d.NTR; a.x_stride = d.D;
@@ -445,6 +446,7 @@ static int enqueue_train(nfopp_engine *e, bool warm, cudaStream_t s) {
     a.sp = warm ? nullptr : d.sp;
     int rc = onf_fma_launch(a, d.P, s);
     if (rc) return rc;
+    if (ev) NFOPP_CHECK_CUDA(cudaEventRecord(ev[0], s));
     AdamArgs ad{};
     ad.w = d.onf_w; ad.m = d.onf_m; ad.v = d.onf_v; ad.gpart = d.onf_gpart; ad.count = d.train_n; ad.n = d.NTR;
     ad.tp = e->tile_points; ad.tiles = e->tiles; ad.n_params = e->onf.lay.n_params;
@@ -452,14 +454,25 @@ static int enqueue_train(nfopp_engine *e, bool warm, cudaStream_t s) {
     ad.w2 = (float)(1.0 - (double)e->cfg.onf_beta2); ad.eps = (float)e->cfg.adam_eps;
     ad.sp = d.sp;
     ad.warm = warm;
-    return onf_adam_launch(ad, d.P, s);
+    rc = onf_adam_launch(ad, d.P, s);
+    if (rc) return rc;
+    if (ev) NFOPP_CHECK_CUDA(cudaEventRecord(ev[1], s));
+    return NFOPP_OK;
 }
 
-static int enqueue_step(nfopp_engine *e, cudaStream_t s) {
+static const char *const kStepKernelNames[9] = {"sample_pre", "onf_forward_candidates", "resample_label",
+                                                "onf_train_fwd_bwd", "onf_reduce_adam", "traj_pre",
+                                                "onf_path_fwd_dgrad", "traj_post", "tick"};
+
+static int enqueue_step(nfopp_engine *e, cudaStream_t s, cudaEvent_t *ev = nullptr) {
     const EngineDev &d = e->dev;
     int rc;
+    int evi = 0;
+#define NFOPP_MARK() do { if (ev) NFOPP_CHECK_CUDA(cudaEventRecord(ev[evi++], s)); } while (0)
+    NFOPP_MARK();
     // (1) near-path + uniform samples, candidates            nerf_opt_planner.py:101-120
     if ((rc = launch_sample_pre(d, s))) return rc;
+    NFOPP_MARK();
     // (2) ONF forward on the candidates (resampling weights)  :123-125   [skipped on device when !do_train]
     {
         OnfArgs a{};
@@ -467,12 +480,16 @@ static int enqueue_step(nfopp_engine *e, cudaStream_t s) {
         a.z_out = d.cand_z; a.sp = d.sp;
         if ((rc = onf_fma_launch(a, d.P, s))) return rc;
     }
+    NFOPP_MARK();
     // (3) weighted resampling of the replay buffer + ground-truth labels  :126-133, :86
     if ((rc = launch_resample_label(d, 1, s))) return rc;
+    NFOPP_MARK();
     // (4,5) BCE training step of the ONF: fwd+bwd per tile, then reduce + Adam   :83-90
-    if ((rc = enqueue_train(e, false, s))) return rc;
+    if ((rc = enqueue_train(e, false, s, ev ? &ev[evi] : nullptr))) return rc;
+    if (ev) evi += 2;
     // (6) collision sample points on the path                 :113-117 / constrained:78-83
     if ((rc = launch_traj_pre(d, s))) return rc;
+    NFOPP_MARK();
     // (7) ONF forward + input gradient at the path points     :166-169 / constrained:85-89
     {
         OnfArgs a{};
@@ -482,10 +499,15 @@ static int enqueue_step(nfopp_engine *e, cudaStream_t s) {
         a.beta = d.constrained ? d.beta : 1.f; a.z_out = d.path_z; a.gx_out = d.path_gq;
         if ((rc = onf_fma_launch(a, d.P, s))) return rc;
     }
+    NFOPP_MARK();
     // (8) trajectory gradient, preconditioner, Adam, multipliers, re-parametrisation  :143-155,224-244
     if ((rc = launch_traj_post(d, s))) return rc;
+    NFOPP_MARK();
     // (9) counters
-    return launch_tick(d, false, s);
+    if ((rc = launch_tick(d, false, s))) return rc;
+    NFOPP_MARK();
+#undef NFOPP_MARK
+    return NFOPP_OK;
 }
 
 extern "C" int nfopp_engine_warmup(nfopp_engine *e, int iterations, void *stream) {
@@ -534,6 +556,35 @@ extern "C" int nfopp_engine_step(nfopp_engine *e, int n_steps, int use_graph, vo
         e->launches += e->launches_per_step;
     }
     return NFOPP_OK;
+}
+
+extern "C" int nfopp_engine_profile_step(nfopp_engine *e, float *ms_out, int n_out, void *stream) {
+    NFOPP_REQUIRE(e && ms_out && n_out >= 9, "profile_step: need room for 9 kernel times");
+    cudaStream_t s = (cudaStream_t)stream;
+    int rc;
+    if (e->sp_dirty && (rc = upload_step_params(e, s))) return rc;
+    cudaEvent_t ev[10];
+    for (auto &x : ev) NFOPP_CHECK_CUDA(cudaEventCreate(&x));
+    rc = enqueue_step(e, s, ev);
+    if (!rc) {
+        cudaError_t ce = cudaStreamSynchronize(s);
+        if (ce != cudaSuccess) { set_error("profile_step: %s", cudaGetErrorString(ce)); rc = NFOPP_ERR_CUDA; }
+    }
+    if (!rc)
+        for (int i = 0; i < 9; ++i) cudaEventElapsedTime(&ms_out[i], ev[i], ev[i + 1]);
+    for (auto &x : ev) cudaEventDestroy(x);
+    if (rc) return rc;
+    StepParams &sp = e->host_sp;
+    if (sp.do_train) { sp.onf_step += 1; sp.has_prev = 1; }
+    sp.traj_step += 1;
+    sp.step_count += 1;
+    host_step_params(e);
+    e->launches += e->launches_per_step;
+    return NFOPP_OK;
+}
+
+extern "C" const char *nfopp_engine_kernel_name(int index) {
+    return index >= 0 && index < 9 ? kStepKernelNames[index] : nullptr;
 }
 
 extern "C" int nfopp_engine_get_paths(nfopp_engine *e, float *paths, void *stream) {

@@ -69,6 +69,8 @@ SIGNATURES = {
     "nfopp_engine_set_counter": (_I, [_P, _I, C.c_int64]),
     "nfopp_engine_warmup": (_I, [_P, _I, _P]),
     "nfopp_engine_step": (_I, [_P, _I, _I, _P]),
+    "nfopp_engine_profile_step": (_I, [_P, C.POINTER(C.c_float), _I, _P]),
+    "nfopp_engine_kernel_name": (C.c_char_p, [_I]),
     "nfopp_engine_get_paths": (_I, [_P, _P, _P]),
     "nfopp_engine_reparametrize": (_I, [_P, _P]),
     "nfopp_engine_launch_count": (_I, [_P, C.POINTER(C.c_int64)]),

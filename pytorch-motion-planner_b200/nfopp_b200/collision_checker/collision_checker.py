@@ -16,7 +16,7 @@ def _poses_of(test_positions):
     if hasattr(test_positions, "translation"):
         xy = np.asarray(test_positions.translation, dtype=np.float64).reshape(-1, 2)
         th = np.asarray(test_positions.rotation, dtype=np.float64).reshape(-1, 1)
-        return np.concatenate([xy, th], axis=1)
+        return np.ascontiguousarray(np.concatenate([xy, th], axis=1))
     return np.ascontiguousarray(np.asarray(test_positions, dtype=np.float64))
 
 

@@ -272,6 +272,13 @@ class PlannerEngine:
             else:
                 L.check(self._lib.nfopp_engine_step(self._h, int(n_steps), 0, L.stream_ptr()))
 
+    def profile_step(self) -> dict:
+        """One un-graphed step with CUDA events between its kernels -> {kernel name: milliseconds}."""
+        ms = (C.c_float * 9)()
+        with torch.cuda.device(self.device):
+            L.check(self._lib.nfopp_engine_profile_step(self._h, ms, 9, L.stream_ptr()))
+        return {self._lib.nfopp_engine_kernel_name(i).decode(): float(ms[i]) for i in range(9)}
+
     def paths(self, out=None) -> torch.Tensor:
         cfg = self.config
         if out is None:

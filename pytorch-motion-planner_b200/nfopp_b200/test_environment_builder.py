@@ -52,18 +52,21 @@ class TestEnvironmentBuilder(object):
     # ---- batch generators (not in the reference: it has no batching) ----------
     @staticmethod
     def make_corridor_batch(problems, seed=0, points_per_wall=10):
-        """Jittered S-bend corridors: wall x ~ U(0.9,1.4)/(1.6,2.1), gap offsets ~ U(-0.3,0.3); problem i uses
-        RandomState(seed + i).  Returns (starts [P,3], goals [P,3], bounds, obstacles [P, 2*ppw, 2])."""
+        """Jittered S-bend corridors around the reference's two-wall world (:16-22): left wall x ~ U(0.95,1.25),
+        channel width ~ U(0.7,0.9) (the reference's is 0.7; a disc of radius 0.3 needs > 0.6), wall ends shifted
+        by U(-0.2,0.2), goal height by U(-0.3,0.3); problem i uses RandomState(seed + i).
+        Returns (starts [P,3], goals [P,3], bounds, obstacles [P, 2*ppw, 2])."""
         starts = np.tile(np.array([0.5, 0.5, 0], dtype=np.float32), (problems, 1))
         goals = np.tile(np.array([2.5, 1.5, 0], dtype=np.float32), (problems, 1))
         obstacles = np.empty((problems, 2 * points_per_wall, 2))
         for i in range(problems):
             rs = np.random.RandomState(seed + i)
-            x_left, x_right = rs.uniform(0.9, 1.4), rs.uniform(1.6, 2.1)
-            off_l, off_r = rs.uniform(-0.3, 0.3, 2)
+            x_left = rs.uniform(0.95, 1.25)
+            x_right = x_left + rs.uniform(0.7, 0.9)
+            off_l, off_r = rs.uniform(-0.2, 0.2, 2)
             obstacles[i, :points_per_wall] = _segment((x_left, 0 + off_l), (x_left, 2 + off_l), points_per_wall)
             obstacles[i, points_per_wall:] = _segment((x_right, 1 + off_r), (x_right, 3 + off_r), points_per_wall)
-            goals[i, 1] = np.float32(1.5 + rs.uniform(-0.5, 0.5))
+            goals[i, 1] = np.float32(1.5 + rs.uniform(-0.3, 0.3))
         return starts, goals, _BOUNDS, obstacles
 
     @staticmethod
