@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define NFOPP_ABI_VERSION 1
+#define NFOPP_ABI_VERSION 2
 #define NFOPP_MAX_LAYERS 8
 
 typedef enum {
@@ -85,30 +85,37 @@ int nfopp_label_grid(const double *poses_dev, int P, int n, int pose_dim, const 
 
 /* ---- K2: ONF forward / backward with per-problem weights (onf_model.py:33-50) ---------------------- */
 /* weights_dev [P, n_params]; x_dev [P, n, in_dim] float32; count_dev [P] int32 = valid points per problem
- * (NULL => n); z_dev [P, n] logits.  `impl`: 0 = auto, 1 = FMA (CUDA-core fp32), 2 = tensor (tcgen05). */
+ * (NULL => n); z_dev [P, n] logits.
+ * `impl`: 0 = auto (tensor when the network shape allows it), 1 = FMA (CUDA-core fp32), 2 = tensor (tcgen05:
+ * bf16 hi/lo split operands, fp32 accumulation in TMEM; 2 hidden layers, hidden <= 111, f_in <= 224).
+ * `scratch_dev`: device scratch of nfopp_onf_scratch_bytes(cfg, P, impl) bytes (the tensor path keeps a bf16
+ * operand copy of the hidden-layer weights there; 0 bytes / NULL for the FMA path). */
+int nfopp_onf_scratch_bytes(const nfopp_onf_config *cfg, int P, int impl, size_t *bytes);
 int nfopp_onf_forward(const nfopp_onf_config *cfg, const float *weights_dev, const float *x_dev,
-                      const int32_t *count_dev, int P, int n, float *z_dev, int impl, void *stream);
+                      const int32_t *count_dev, int P, int n, float *z_dev, int impl, void *scratch_dev,
+                      void *stream);
 
 /* gbar_mode selects dL/dz:
  *   0 external : gz_dev [P,n] given (what autograd hands ONF.backward)
  *   1 bce      : (sigmoid(z) - y)/count, y = aux_dev [P,n]           nerf_opt_planner.py:25,85-89
  *   2 path     : w_c*sigmoid(z)                                      nerf_opt_planner.py:159,166-169
  *   3 path_mu  : w_c*softplus_beta'(z) + aux*(1-tanh(z)^2), aux=mu~  constrained_nerf_opt_planner.py:82-89
- * Outputs (each may be NULL): z_dev [P,n]; gx_dev [P,n,in_dim]; gpart_dev [P, tiles, n_params] per-tile
- * partial weight gradients (tiles = nfopp_onf_tiles(cfg, n)), reduced in fixed order by nfopp_onf_adam /
- * nfopp_onf_reduce_grad.  x_dev rows have in_dim columns. */
-int nfopp_onf_tiles(const nfopp_onf_config *cfg, int n);   /* point tiles per problem for n points */
+ * Outputs (each may be NULL): z_dev [P,n]; gx_dev [P,n,in_dim]; gpart_dev [P, slots, n_params] weight
+ * gradients, slots = nfopp_onf_tiles(cfg, n, impl): per-point-tile partials for the FMA path, ONE reduced
+ * gradient for the tensor path (it accumulates over the problem's points in TMEM); reduced in fixed order by
+ * nfopp_onf_adam / nfopp_onf_reduce_grad called with the same cfg, n and impl.  x_dev rows have in_dim columns. */
+int nfopp_onf_tiles(const nfopp_onf_config *cfg, int n, int impl);   /* gradient slots per problem for n points */
 int nfopp_onf_backward(const nfopp_onf_config *cfg, const float *weights_dev, const float *x_dev,
                        const int32_t *count_dev, int P, int n, int gbar_mode, const float *gz_dev,
                        const float *aux_dev, float collision_weight, float beta, float *z_dev, float *gx_dev,
-                       float *gpart_dev, int impl, void *stream);
-/* sums the per-tile partials [P, tiles, n_params] into grad_dev [P, n_params] (fixed order) */
+                       float *gpart_dev, int impl, void *scratch_dev, void *stream);
+/* sums the gradient slots [P, slots, n_params] into grad_dev [P, n_params] (fixed order) */
 int nfopp_onf_reduce_grad(const nfopp_onf_config *cfg, const float *gpart_dev, const int32_t *count_dev, int P,
-                          int n, float *grad_dev, void *stream);
+                          int n, int impl, float *grad_dev, void *stream);
 /* torch.optim.Adam single-tensor update (planner_factory.py:54,56,68,70) over [P, n_params]; `step` is the
- * 1-based index of this update; gpart_dev is what nfopp_onf_backward wrote for the same cfg and n. */
+ * 1-based index of this update; gpart_dev is what nfopp_onf_backward wrote for the same cfg, n and impl. */
 int nfopp_onf_adam(const nfopp_onf_config *cfg, float *weights_dev, float *m_dev, float *v_dev,
-                   const float *gpart_dev, const int32_t *count_dev, int P, int n, int step, double lr,
+                   const float *gpart_dev, const int32_t *count_dev, int P, int n, int impl, int step, double lr,
                    double beta1, double beta2, double eps, void *stream);
 
 /* numpy legacy RandomState.choice(n, size, replace, p) on given uniforms (nerf_opt_planner.py:131).
@@ -149,7 +156,7 @@ typedef struct {
     int32_t rng_mode;
     uint64_t seed;
     int32_t max_choice_uniforms;        /* per problem per step, injected mode */
-    int32_t onf_impl;                   /* 0 auto, 1 FMA, 2 tensor */
+    int32_t onf_impl;                   /* 0 auto (tensor when the shape allows), 1 FMA, 2 tensor */
 } nfopp_planner_config;
 
 typedef struct nfopp_engine nfopp_engine;
@@ -168,6 +175,11 @@ int nfopp_engine_buffer(nfopp_engine *e, const char *name, void **ptr_dev, size_
                         int32_t dims[3]);
 int nfopp_engine_buffer_count(nfopp_engine *e);
 const char *nfopp_engine_buffer_name(nfopp_engine *e, int index);
+/* The tensor path works on a bf16 operand copy of the hidden-layer weights that its training kernel keeps
+ * current.  nfopp_engine_buffer(e, "onf_w", ...) marks the copy stale (the caller may write the weights);
+ * call this after writing through a pointer obtained earlier (e.g. an nn.Module view of the buffer).  The copy
+ * is rebuilt at the start of the next warmup / step / profile_step. */
+int nfopp_engine_invalidate_weights(nfopp_engine *e);
 /* Host-side counters (the reference keeps them as Python ints / optimizer state):
  * which: 0 = step_count (nerf_opt_planner.py:35), 1 = ONF Adam step, 2 = trajectory Adam step,
  *        3 = has_previous_trajectory (nerf_opt_planner.py:37,79-82) */

@@ -62,7 +62,20 @@ int launch_tick(const EngineDev &e, bool warm, cudaStream_t s);
 int launch_paths(const EngineDev &e, float *out, cudaStream_t s);
 int launch_reparam(const EngineDev &e, cudaStream_t s);
 
-static int tiles_for(const OnfDims &d, int n) {
+// impl 0 = auto: the tensor path whenever the network shape fits it
+static int resolve_impl(const OnfDims &d, int impl, int *out) {
+    NFOPP_REQUIRE(impl >= 0 && impl <= 2, "impl=%d (0 auto, 1 FMA, 2 tensor)", impl);
+    if (impl == 0) impl = onf_tc_supported(d) ? 2 : 1;
+    NFOPP_REQUIRE(impl != 2 || onf_tc_supported(d),
+                  "onf(tensor): needs 2 hidden layers, hidden <= 111, f_in <= 224 (hidden=%d layers=%d)", d.H, d.L);
+    NFOPP_REQUIRE(impl != 1 || onf_fma_tile_points(d) != 0, "onf(fma): hidden=%d layers=%d does not fit shared memory", d.H, d.L);
+    *out = impl;
+    return NFOPP_OK;
+}
+
+// gradient slots per problem
+static int tiles_for(const OnfDims &d, int n, int impl) {
+    if (impl == 2) return 1;
     int tp = onf_fma_tile_points(d);
     return tp ? (n + tp - 1) / tp : 0;
 }
@@ -83,31 +96,57 @@ extern "C" int nfopp_onf_get_layout(const nfopp_onf_config *cfg, nfopp_onf_layou
     return NFOPP_OK;
 }
 
-extern "C" int nfopp_onf_tiles(const nfopp_onf_config *cfg, int n) {
+extern "C" int nfopp_onf_tiles(const nfopp_onf_config *cfg, int n, int impl) {
     OnfDims d;
     if (make_onf_dims(cfg, &d)) return NFOPP_ERR_INVALID;
-    int tp = onf_fma_tile_points(d);
-    if (!tp) { set_error("onf: hidden=%d layers=%d too large for the FMA path", d.H, d.L); return NFOPP_ERR_INVALID; }
-    return (n + tp - 1) / tp;
+    if (resolve_impl(d, impl, &impl)) return NFOPP_ERR_INVALID;
+    return tiles_for(d, n, impl);
+}
+
+extern "C" int nfopp_onf_scratch_bytes(const nfopp_onf_config *cfg, int P, int impl, size_t *bytes) {
+    OnfDims d;
+    int rc = make_onf_dims(cfg, &d);
+    if (rc) return rc;
+    NFOPP_REQUIRE(bytes && P >= 0, "onf_scratch_bytes: bad arguments");
+    if ((rc = resolve_impl(d, impl, &impl))) return rc;
+    *bytes = impl == 2 ? (size_t)P * onf_tc_packed_bytes(d) : 0;
+    return NFOPP_OK;
+}
+
+// one ONF launch through the chosen implementation (stateless API: the tensor path packs its operand copy first)
+static int onf_api_launch(const OnfDims &d, OnfArgs &a, int P, int impl, void *scratch, float *grad_out, cudaStream_t s) {
+    int rc;
+    if (impl == 1) {
+        if ((rc = onf_fma_prepare(d))) return rc;
+        a.gpart = grad_out;
+        return onf_fma_launch(a, P, s);
+    }
+    NFOPP_REQUIRE(scratch, "onf(tensor): scratch_dev missing (nfopp_onf_scratch_bytes)");
+    if ((rc = onf_tc_prepare(d))) return rc;
+    if ((rc = onf_tc_pack(d, a.weights, static_cast<unsigned char *>(scratch), P, s))) return rc;
+    OnfTcExtra x{};
+    x.packed = static_cast<const unsigned char *>(scratch);
+    x.grad_out = grad_out;
+    if (grad_out) NFOPP_CHECK_CUDA(cudaMemsetAsync(grad_out, 0, (size_t)P * d.lay.n_params * sizeof(float), s));
+    return onf_tc_launch(a, x, P, s);
 }
 
 extern "C" int nfopp_onf_forward(const nfopp_onf_config *cfg, const float *weights, const float *x,
-                                 const int32_t *count, int P, int n, float *z, int impl, void *stream) {
+                                 const int32_t *count, int P, int n, float *z, int impl, void *scratch, void *stream) {
     OnfDims d;
     int rc = make_onf_dims(cfg, &d);
     if (rc) return rc;
     NFOPP_REQUIRE(weights && x && z && P > 0 && n >= 0, "onf_forward: bad arguments");
-    NFOPP_REQUIRE(impl == 0 || impl == 1, "onf_forward: impl=%d not available in this build", impl);
+    if ((rc = resolve_impl(d, impl, &impl))) return rc;
     OnfArgs a{};
     a.d = d; a.weights = weights; a.x = x; a.count = count; a.n = n; a.want_bwd = 0; a.z_out = z;
-    if ((rc = onf_fma_prepare(d))) return rc;
-    return onf_fma_launch(a, P, (cudaStream_t)stream);
+    return onf_api_launch(d, a, P, impl, scratch, nullptr, (cudaStream_t)stream);
 }
 
 extern "C" int nfopp_onf_backward(const nfopp_onf_config *cfg, const float *weights, const float *x,
                                   const int32_t *count, int P, int n, int gbar_mode, const float *gz,
                                   const float *aux, float collision_weight, float beta, float *z, float *gx,
-                                  float *gpart, int impl, void *stream) {
+                                  float *gpart, int impl, void *scratch, void *stream) {
     OnfDims d;
     int rc = make_onf_dims(cfg, &d);
     if (rc) return rc;
@@ -115,22 +154,24 @@ extern "C" int nfopp_onf_backward(const nfopp_onf_config *cfg, const float *weig
     NFOPP_REQUIRE(gbar_mode >= 0 && gbar_mode <= 3, "onf_backward: gbar_mode=%d", gbar_mode);
     NFOPP_REQUIRE(gbar_mode != 0 || gz, "onf_backward: external mode needs gz");
     NFOPP_REQUIRE((gbar_mode != 1 && gbar_mode != 3) || aux, "onf_backward: mode %d needs aux", gbar_mode);
-    NFOPP_REQUIRE(impl == 0 || impl == 1, "onf_backward: impl=%d not available in this build", impl);
+    NFOPP_REQUIRE(gx || gpart, "onf_backward: neither gx nor gpart requested");
+    if ((rc = resolve_impl(d, impl, &impl))) return rc;
     OnfArgs a{};
     a.d = d; a.weights = weights; a.x = x; a.count = count; a.n = n; a.want_bwd = 1; a.gbar_mode = gbar_mode;
-    a.gz = gz; a.aux = aux; a.wc = collision_weight; a.beta = beta; a.z_out = z; a.gx_out = gx; a.gpart = gpart;
-    if ((rc = onf_fma_prepare(d))) return rc;
-    return onf_fma_launch(a, P, (cudaStream_t)stream);
+    a.gz = gz; a.aux = aux; a.wc = collision_weight; a.beta = beta; a.z_out = z; a.gx_out = gx;
+    return onf_api_launch(d, a, P, impl, scratch, gpart, (cudaStream_t)stream);
 }
 
 extern "C" int nfopp_onf_reduce_grad(const nfopp_onf_config *cfg, const float *gpart, const int32_t *count, int P,
-                                     int n, float *grad, void *stream) {
+                                     int n, int impl, float *grad, void *stream) {
     OnfDims d;
     int rc = make_onf_dims(cfg, &d);
     if (rc) return rc;
     NFOPP_REQUIRE(gpart && grad && P > 0 && n > 0, "onf_reduce_grad: bad arguments");
+    if ((rc = resolve_impl(d, impl, &impl))) return rc;
     AdamArgs a{};
-    a.gpart = gpart; a.count = count; a.n = n; a.tp = onf_fma_tile_points(d); a.tiles = tiles_for(d, n);
+    a.gpart = gpart; a.count = count; a.n = n; a.tp = impl == 2 ? (1 << 30) : onf_fma_tile_points(d);
+    a.tiles = tiles_for(d, n, impl);
     a.n_params = d.lay.n_params; a.grad_out = grad;
     return onf_adam_launch(a, P, (cudaStream_t)stream);
 }
@@ -145,15 +186,17 @@ static void adam_scalars(double lr, double b1, double b2, double eps, int64_t st
 }
 
 extern "C" int nfopp_onf_adam(const nfopp_onf_config *cfg, float *w, float *m, float *v, const float *gpart,
-                              const int32_t *count, int P, int n, int step, double lr, double beta1, double beta2,
-                              double eps, void *stream) {
+                              const int32_t *count, int P, int n, int impl, int step, double lr, double beta1,
+                              double beta2, double eps, void *stream) {
     OnfDims d;
     int rc = make_onf_dims(cfg, &d);
     if (rc) return rc;
     NFOPP_REQUIRE(w && m && v && gpart && P > 0 && n > 0 && step >= 1, "onf_adam: bad arguments");
+    if ((rc = resolve_impl(d, impl, &impl))) return rc;
     AdamArgs a{};
-    a.w = w; a.m = m; a.v = v; a.gpart = gpart; a.count = count; a.n = n; a.tp = onf_fma_tile_points(d);
-    a.tiles = tiles_for(d, n); a.n_params = d.lay.n_params;
+    a.w = w; a.m = m; a.v = v; a.gpart = gpart; a.count = count; a.n = n;
+    a.tp = impl == 2 ? (1 << 30) : onf_fma_tile_points(d);
+    a.tiles = tiles_for(d, n, impl); a.n_params = d.lay.n_params;
     adam_scalars(lr, beta1, beta2, eps, step, &a);
     return onf_adam_launch(a, P, (cudaStream_t)stream);
 }
@@ -177,6 +220,8 @@ struct nfopp_engine {
     std::vector<BufferInfo> buffers;
     unsigned char *workspace;
     size_t workspace_bytes;
+    int impl;                 // 1 FMA, 2 tensor (resolved)
+    bool pack_dirty;          // tensor path: onf_wp must be rebuilt from onf_w before the next launch
     int tile_points, tiles;
     StepParams host_sp;
     bool sp_dirty;
@@ -212,7 +257,7 @@ static void add_buffer(nfopp_engine *e, const char *name, T **slot, char dtype, 
     e->buffers.push_back(b);
 }
 
-static int validate(const nfopp_planner_config *c, OnfDims *onf) {
+static int validate(const nfopp_planner_config *c, OnfDims *onf, int *impl) {
     NFOPP_REQUIRE(c, "planner config missing");
     int rc = make_onf_dims(&c->onf, onf);
     if (rc) return rc;
@@ -226,9 +271,7 @@ static int validate(const nfopp_planner_config *c, OnfDims *onf) {
     NFOPP_REQUIRE(c->checker_kind != 2 || c->constrained, "rectangle checker needs poses with heading");
     NFOPP_REQUIRE(c->checker_kind != 3 || (c->grid_rows > 1 && c->grid_cols > 1 && c->grid_cell > 0), "grid shape missing");
     NFOPP_REQUIRE(c->rng_mode == 0 || c->rng_mode == 1, "rng_mode=%d", c->rng_mode);
-    NFOPP_REQUIRE(c->onf_impl == 0 || c->onf_impl == 1, "onf_impl=%d not available in this build", c->onf_impl);
-    NFOPP_REQUIRE(onf_fma_tile_points(*onf) != 0, "ONF hidden=%d layers=%d too large for the FMA path", onf->H, onf->L);
-    return NFOPP_OK;
+    return resolve_impl(*onf, c->onf_impl, impl);
 }
 
 static int build_layout(nfopp_engine *e) {
@@ -240,8 +283,8 @@ static int build_layout(nfopp_engine *e) {
     size_t NTR = (T - 1) + C + NF;
     if (NW > NTR) NTR = NW;
     const size_t NP = e->onf.lay.n_params;
-    e->tile_points = onf_fma_tile_points(e->onf);
-    e->tiles = (int)((NTR + e->tile_points - 1) / e->tile_points);
+    e->tile_points = e->impl == 2 ? 64 : onf_fma_tile_points(e->onf);
+    e->tiles = e->impl == 2 ? 1 : (int)((NTR + e->tile_points - 1) / e->tile_points);
     const bool inj = c.rng_mode == 1;
     const size_t MU = inj ? (c.max_choice_uniforms > 0 ? c.max_choice_uniforms : 16 * C) : 0;
     d.P = (int)P; d.T = (int)T; d.D = (int)D; d.C = (int)C; d.NF = (int)NF; d.NC = (int)NC; d.NTR = (int)NTR; d.NW = (int)NW;
@@ -253,7 +296,13 @@ static int build_layout(nfopp_engine *e) {
     add_buffer(e, "onf_w", &d.onf_w, 'f', P, NP);
     add_buffer(e, "onf_m", &d.onf_m, 'f', P, NP);
     add_buffer(e, "onf_v", &d.onf_v, 'f', P, NP);
-    add_buffer(e, "onf_gpart", &d.onf_gpart, 'f', P, e->tiles, NP);
+    if (e->impl == 2) {
+        // the tensor path accumulates weight gradients in TMEM and applies Adam in the same kernel: no partials
+        add_buffer(e, "onf_gpart", &d.onf_gpart, 'f', 1, 1, 4);
+        add_buffer(e, "onf_wp", &d.onf_wp, 'b', P, onf_tc_packed_bytes(e->onf));
+    } else {
+        add_buffer(e, "onf_gpart", &d.onf_gpart, 'f', P, e->tiles, NP);
+    }
     add_buffer(e, "traj", &d.traj, 'f', P, T, D);
     add_buffer(e, "traj_m", &d.traj_m, 'f', P, T, D);
     add_buffer(e, "traj_v", &d.traj_v, 'f', P, T, D);
@@ -338,7 +387,7 @@ static void fill_dev_config(nfopp_engine *e) {
 
 extern "C" int nfopp_engine_workspace_bytes(const nfopp_planner_config *cfg, size_t *bytes) {
     nfopp_engine tmp{};
-    int rc = validate(cfg, &tmp.onf);
+    int rc = validate(cfg, &tmp.onf, &tmp.impl);
     if (rc) return rc;
     NFOPP_REQUIRE(bytes, "bytes pointer missing");
     tmp.cfg = *cfg;
@@ -360,7 +409,7 @@ extern "C" int nfopp_engine_create(const nfopp_planner_config *cfg, void *worksp
                                    nfopp_engine **out) {
     NFOPP_REQUIRE(out, "engine out pointer missing");
     nfopp_engine *e = new nfopp_engine{};
-    int rc = validate(cfg, &e->onf);
+    int rc = validate(cfg, &e->onf, &e->impl);
     if (rc) { delete e; return rc; }
     e->cfg = *cfg;
     build_layout(e);
@@ -378,13 +427,15 @@ extern "C" int nfopp_engine_create(const nfopp_planner_config *cfg, void *worksp
         delete e;
         return NFOPP_ERR_CUDA;
     }
-    if ((rc = onf_fma_prepare(e->onf)) || (rc = resample_prepare(e->dev)) || (rc = traj_prepare(e->dev))) {
+    if ((rc = e->impl == 2 ? onf_tc_prepare(e->onf) : onf_fma_prepare(e->onf)) || (rc = resample_prepare(e->dev)) ||
+        (rc = traj_prepare(e->dev))) {
         delete e;
         return rc;
     }
     e->host_sp = StepParams{};
     e->sp_dirty = true;
-    e->launches_per_step = 9;
+    e->pack_dirty = true;
+    e->launches_per_step = e->impl == 2 ? 8 : 9;
     *out = e;
     return NFOPP_OK;
 }
@@ -408,6 +459,7 @@ extern "C" int nfopp_engine_buffer(nfopp_engine *e, const char *name, void **ptr
     NFOPP_REQUIRE(e && name, "engine_buffer: bad arguments");
     for (auto &b : e->buffers) {
         if (b.name == name) {
+            if (b.name == "onf_w") e->pack_dirty = true;      // the caller may write the weights
             if (ptr) *ptr = *b.slot;
             if (bytes) *bytes = b.bytes;
             if (dtype) *dtype = b.dtype;
@@ -417,6 +469,12 @@ extern "C" int nfopp_engine_buffer(nfopp_engine *e, const char *name, void **ptr
     }
     set_error("unknown engine buffer '%s'", name);
     return NFOPP_ERR_NAME;
+}
+
+extern "C" int nfopp_engine_invalidate_weights(nfopp_engine *e) {
+    NFOPP_REQUIRE(e, "invalidate_weights: bad arguments");
+    e->pack_dirty = true;
+    return NFOPP_OK;
 }
 
 extern "C" int nfopp_engine_get_counter(nfopp_engine *e, int which, int64_t *value) {
@@ -437,21 +495,55 @@ extern "C" int nfopp_engine_set_counter(nfopp_engine *e, int which, int64_t valu
     return NFOPP_OK;
 }
 
+// tensor path: (re)build the bf16 operand copy of the weights if the host may have written them
+static int ensure_packed(nfopp_engine *e, cudaStream_t s) {
+    if (e->impl != 2 || !e->pack_dirty) return NFOPP_OK;
+    int rc = onf_tc_pack(e->onf, e->dev.onf_w, e->dev.onf_wp, e->dev.P, s);
+    if (rc) return rc;
+    e->pack_dirty = false;
+    e->launches += 1;
+    return NFOPP_OK;
+}
+
+// forward / input-gradient ONF launch of the engine through the chosen implementation
+static int engine_onf(nfopp_engine *e, OnfArgs &a, cudaStream_t s) {
+    if (e->impl != 2) return onf_fma_launch(a, e->dev.P, s);
+    OnfTcExtra x{};
+    x.packed = e->dev.onf_wp;
+    return onf_tc_launch(a, x, e->dev.P, s);
+}
+
 // one ONF training update on train_x/train_y/train_n (nerf_opt_planner.py:83-90)
 static int enqueue_train(nfopp_engine *e, bool warm, cudaStream_t s, cudaEvent_t *ev = nullptr) {
     const EngineDev &d = e->dev;
     OnfArgs a{};
     a.d = e->onf; a.weights = d.onf_w; a.x = d.train_x; a.count = d.train_n; a.n = d.NTR; a.x_stride = d.D;
-    a.want_bwd = 1; a.gbar_mode = 1; a.aux = d.train_y; a.z_out = d.train_z; a.gpart = d.onf_gpart;
+    a.want_bwd = 1; a.gbar_mode = 1; a.aux = d.train_y; a.z_out = d.train_z;
+    const float w1 = (float)(1.0 - (double)e->cfg.onf_beta1), beta2 = (float)e->cfg.onf_beta2,
+                w2 = (float)(1.0 - (double)e->cfg.onf_beta2), eps = (float)e->cfg.adam_eps;
+    int rc;
+    if (e->impl == 2) {
+        // fwd + bwd + weight gradients in TMEM + Adam + operand-copy refresh: ONE kernel, no gradient in HBM
+        a.sp = d.sp;
+        OnfTcExtra x{};
+        x.packed = d.onf_wp; x.adam_w = d.onf_w; x.adam_m = d.onf_m; x.adam_v = d.onf_v; x.packed_out = d.onf_wp;
+        x.w1 = w1; x.beta2 = beta2; x.w2 = w2; x.eps = eps; x.warm = warm;
+        if ((rc = onf_tc_launch(a, x, d.P, s))) return rc;
+        if (ev) {
+            NFOPP_CHECK_CUDA(cudaEventRecord(ev[0], s));
+            NFOPP_CHECK_CUDA(cudaEventRecord(ev[1], s));
+        }
+        return NFOPP_OK;
+    }
+    a.gpart = d.onf_gpart;
     a.sp = warm ? nullptr : d.sp;
-    int rc = onf_fma_launch(a, d.P, s);
+    rc = onf_fma_launch(a, d.P, s);
     if (rc) return rc;
     if (ev) NFOPP_CHECK_CUDA(cudaEventRecord(ev[0], s));
     AdamArgs ad{};
     ad.w = d.onf_w; ad.m = d.onf_m; ad.v = d.onf_v; ad.gpart = d.onf_gpart; ad.count = d.train_n; ad.n = d.NTR;
     ad.tp = e->tile_points; ad.tiles = e->tiles; ad.n_params = e->onf.lay.n_params;
-    ad.w1 = (float)(1.0 - (double)e->cfg.onf_beta1); ad.beta2 = (float)e->cfg.onf_beta2;
-    ad.w2 = (float)(1.0 - (double)e->cfg.onf_beta2); ad.eps = (float)e->cfg.adam_eps;
+    ad.w1 = w1; ad.beta2 = beta2; ad.w2 = w2; ad.eps = eps;
     ad.sp = d.sp;
     ad.warm = warm;
     rc = onf_adam_launch(ad, d.P, s);
@@ -478,7 +570,7 @@ static int enqueue_step(nfopp_engine *e, cudaStream_t s, cudaEvent_t *ev = nullp
         OnfArgs a{};
         a.d = e->onf; a.weights = d.onf_w; a.x = d.cand_x; a.count = d.cand_n; a.n = d.NC; a.x_stride = d.D;
         a.z_out = d.cand_z; a.sp = d.sp;
-        if ((rc = onf_fma_launch(a, d.P, s))) return rc;
+        if ((rc = engine_onf(e, a, s))) return rc;
     }
     NFOPP_MARK();
     // (3) weighted resampling of the replay buffer + ground-truth labels  :126-133, :86
@@ -497,7 +589,7 @@ static int enqueue_step(nfopp_engine *e, cudaStream_t s, cudaEvent_t *ev = nullp
         a.want_bwd = 1;
         a.gbar_mode = d.constrained ? 3 : 2; a.aux = d.path_mu; a.wc = d.collision_weight;
         a.beta = d.constrained ? d.beta : 1.f; a.z_out = d.path_z; a.gx_out = d.path_gq;
-        if ((rc = onf_fma_launch(a, d.P, s))) return rc;
+        if ((rc = engine_onf(e, a, s))) return rc;
     }
     NFOPP_MARK();
     // (8) trajectory gradient, preconditioner, Adam, multipliers, re-parametrisation  :143-155,224-244
@@ -515,6 +607,7 @@ extern "C" int nfopp_engine_warmup(nfopp_engine *e, int iterations, void *stream
     cudaStream_t s = (cudaStream_t)stream;
     int rc;
     if (e->sp_dirty && (rc = upload_step_params(e, s))) return rc;
+    if ((rc = ensure_packed(e, s))) return rc;
     for (int it = 0; it < iterations; ++it) {
         if ((rc = launch_warm_sample(e->dev, 1000000 + e->warm_iterations_done, s))) return rc;
         if ((rc = launch_resample_label(e->dev, 0, s))) return rc;
@@ -522,7 +615,7 @@ extern "C" int nfopp_engine_warmup(nfopp_engine *e, int iterations, void *stream
         if ((rc = launch_tick(e->dev, true, s))) return rc;
         e->host_sp.onf_step += 1;
         e->warm_iterations_done += 1;
-        e->launches += 5;
+        e->launches += e->impl == 2 ? 4 : 5;
     }
     host_step_params(e);
     return NFOPP_OK;
@@ -533,6 +626,7 @@ extern "C" int nfopp_engine_step(nfopp_engine *e, int n_steps, int use_graph, vo
     cudaStream_t s = (cudaStream_t)stream;
     int rc;
     if (e->sp_dirty && (rc = upload_step_params(e, s))) return rc;
+    if ((rc = ensure_packed(e, s))) return rc;
     if (use_graph && !e->graph_exec) {
         NFOPP_REQUIRE(s != nullptr, "step: CUDA-graph capture needs a non-default stream");
         NFOPP_CHECK_CUDA(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
@@ -563,6 +657,7 @@ extern "C" int nfopp_engine_profile_step(nfopp_engine *e, float *ms_out, int n_o
     cudaStream_t s = (cudaStream_t)stream;
     int rc;
     if (e->sp_dirty && (rc = upload_step_params(e, s))) return rc;
+    if ((rc = ensure_packed(e, s))) return rc;
     cudaEvent_t ev[10];
     for (auto &x : ev) NFOPP_CHECK_CUDA(cudaEventCreate(&x));
     rc = enqueue_step(e, s, ev);

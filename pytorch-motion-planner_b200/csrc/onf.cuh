@@ -34,6 +34,22 @@ struct AdamArgs {
     float *grad_out;          // reduce-only mode when non-null
 };
 
+// extra arguments of the tensor-core path (onf_tc.cu)
+struct OnfTcExtra {
+    const unsigned char *packed;   // [P, onf_tc_packed_bytes] bf16 hi/lo operand copy of the hidden-layer weights
+    float *grad_out;               // [P, n_params] reduced gradient, or null
+    float *adam_w, *adam_m, *adam_v;   // fused Adam on [P, n_params] (engine), or null
+    unsigned char *packed_out;     // operand copy rewritten by the fused Adam
+    float w1, beta2, w2, eps;      // 1-beta1, beta2, 1-beta2, eps; step size / bias correction come from StepParams
+    int warm;                      // warm-up iteration: ignore StepParams::do_train
+};
+
+bool onf_tc_supported(const OnfDims &d);            // 2 hidden layers, hidden <= 111, f_in <= 224
+size_t onf_tc_packed_bytes(const OnfDims &d);       // per problem
+int onf_tc_prepare(const OnfDims &d);
+int onf_tc_pack(const OnfDims &d, const float *weights, unsigned char *packed, int P, cudaStream_t stream);
+int onf_tc_launch(const OnfArgs &a, const OnfTcExtra &x, int P, cudaStream_t stream);
+
 int onf_fma_tile_points(const OnfDims &d);          // 32, 16 or 0 (does not fit)
 int onf_fma_prepare(const OnfDims &d);               // one-time kernel attributes (outside graph capture)
 int onf_fma_launch(OnfArgs a, int P, cudaStream_t stream);

@@ -1,0 +1,833 @@
+// onf_tc.cu - K2, tensor-core path: the fused ONF kernel on tcgen05 (sm_100a).
+//
+// One CTA = one planning problem (its own weights); the problem's points are walked in tiles of <= 64.  Every
+// dense contraction of the forward pass (onf_model.py:33-50), of the input-gradient pass and of the
+// weight-gradient pass (what autograd does for nerf_opt_planner.py:85-90 / constrained...:85-100) is a
+// tcgen05.mma with the HIDDEN index on the UMMA M axis (128 TMEM lanes) and the POINT index on the N axis:
+//
+//   fwd1   D1[j,n]  = sum_k W1p[j,k] E[n,k]      A = W1p  (K-major)   B = E    (K-major)    K = K1
+//   fwd2   D2[i,n]  = sum_j W2p[i,j] H1[j,n]     A = W2p  (K-major)   B = H1   (MN-major)   K = KH
+//   wgrad2 dW2[i,j]+= sum_n gH2[i,n] H1[j,n]     A = gH2  (K-major)   B = H1   (K-major)    K = points
+//   dgrad2 gD1[j,n] = sum_i W2p[i,j] gH2[i,n]    A = W2p  (MN-major)  B = gH2  (MN-major)   K = KH
+//   dgrad1 gE[k,n]  = sum_j W1p[j,k] gH1[j,n]    A = W1p  (MN-major)  B = gH1  (MN-major)   K = KH  (2 M blocks)
+//   wgrad1 dW1[j,k]+= sum_n gH1[j,n] E[n,k]      A = gH1  (K-major)   B = E^T  (K-major)    K = points
+//
+// Precision: every fp32 operand is split into bf16 hi + bf16 lo and each product is three kind::f16 MMAs
+// (hi*hi + lo*hi + hi*lo) accumulated in fp32 in TMEM: ~3e-6 relative (umma_probe.cu), far inside the 1e-3
+// bar; single-pass bf16 (4e-3) or tf32 (5e-4 per operand) would not be.
+//
+// Row H of the layer-1 operand W1p holds the skip-connection weights w_out[H:], so the skip term of the logit
+// (onf_model.py:48-49) falls out of fwd1 as D1[H,n], its input gradient out of dgrad1 (gH1 row H := dL/dz) and
+// its weight gradient out of wgrad1 (row H of dW1) - no extra pass.  Biases, ReLU, the logit reduction, dL/dz,
+// the Fourier/angle encoding and its backward run on the CUDA cores between the MMAs, one TMEM lane (hidden
+// unit or feature) per thread, so every bias / per-unit reduction is thread-local.
+//
+// The weight-gradient accumulators (dW1: K1 columns, dW2: KH columns, fp32) stay in TMEM across all point tiles
+// of the problem; the epilogue streams them out once - either as a plain gradient or straight through Adam
+// (torch.optim.Adam, planner_factory.py:68), which also rewrites the bf16 hi/lo operand copy of the weights.
+// Nothing like the FMA path's per-tile gradient partials ever reaches HBM.
+#include "onf.cuh"
+#include "tc05.cuh"
+
+namespace nfopp {
+using namespace tc05;
+
+constexpr int TC_THREADS = 256;
+constexpr int TC_TP = 64;                        // points per tile = max UMMA N used for point-indexed outputs
+constexpr int TC_REGION = 32768;                 // E ring / gH2 / E^T scratch (two 16 KB halves: hi, lo)
+constexpr uint32_t TM_DW1 = 0, TM_DW2 = 224, TM_WORK = 336;   // TMEM column map (512 columns allocated)
+
+struct TcDims {
+    int F, A, FIN, H, K1, KH, MB;                // MB = M blocks of dgrad1 = feature groups of 128
+    int S_colW;                                  // column-octet stride of the packed weights = KH * 16 bytes
+    int w1_half, w2_half, h1_half;               // bytes of one hi (or lo) buffer
+    int off_w1, off_w2, off_h1, off_r, off_misc; // shared-memory byte offsets
+    int smem_bytes;
+    int packed_bytes;                            // per problem, global
+};
+
+__host__ __device__ inline int ru16(int x) { return (x + 15) / 16 * 16; }
+
+__host__ __device__ inline bool tc_make_dims(const OnfDims &d, TcDims *out) {
+    TcDims t{};
+    t.F = d.lay.f_pos; t.A = d.lay.n_angle; t.FIN = d.lay.f_in; t.H = d.H;
+    t.K1 = ru16(t.FIN); t.KH = ru16(t.H + 1); t.MB = (t.K1 + 127) / 128;
+    t.S_colW = t.KH * 16;
+    t.w1_half = (t.K1 / 8) * t.S_colW;
+    t.w2_half = (t.KH / 8) * t.S_colW;
+    t.h1_half = (t.KH / 8) * 1024;
+    t.off_w1 = 0;
+    t.off_w2 = 2 * t.w1_half;
+    t.off_h1 = t.off_w2 + 2 * t.w2_half;
+    t.off_r = t.off_h1 + 2 * t.h1_half;
+    t.off_misc = t.off_r + TC_REGION;
+    int misc_floats = 3 * t.F + 2 * t.A + 3 * t.H + 4 /*b3 + pad*/ + 5 * TC_TP + 4 * TC_TP + 4 * TC_TP * 3;
+    t.smem_bytes = t.off_misc + misc_floats * 4 + 64;
+    t.packed_bytes = 2 * t.w1_half + 2 * t.w2_half;
+    *out = t;
+    return d.L == 2 && t.KH <= 112 && t.K1 <= 224 && t.H >= 8 && t.smem_bytes <= 227 * 1024;
+}
+
+struct OnfTcArgs {
+    OnfDims d;
+    TcDims t;
+    const float *weights;          // [P, n_params] fp32 blob (encoder, biases, w_out[:H], b_out are read from here)
+    const unsigned char *packed;   // [P, packed_bytes] bf16 hi/lo operand copy of W1p / W2p
+    const float *x;
+    const int32_t *count;
+    const StepParams *sp;
+    int n, x_stride;
+    int want_bwd;                  // 0: logits only
+    int gbar_mode;
+    const float *gz, *aux;
+    float wc, beta;
+    float *z_out, *gx_out;
+    float *grad_out;               // [P, n_params] plain gradient (API), or null
+    // fused Adam (engine): updates w/m/v and the packed copy in place
+    float *adam_w, *adam_m, *adam_v;
+    unsigned char *packed_out;
+    float w1, beta2, w2, eps;
+    int warm;
+};
+
+struct TcPackArgs {
+    OnfDims d;
+    TcDims t;
+    const float *weights;
+    unsigned char *packed;
+};
+
+// ---- fp32 blob -> packed bf16 hi/lo operands (API entry points and engine start; the training kernel keeps
+// the copy current afterwards) -----------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) onf_tc_pack_kernel(const TcPackArgs a) {
+    const int p = blockIdx.y;
+    const TcDims &t = a.t;
+    const nfopp_onf_layout &L = a.d.lay;
+    const float *W = a.weights + (size_t)p * L.n_params;
+    unsigned char *out = a.packed + (size_t)p * t.packed_bytes;
+    const int rows = t.KH;
+    const int n1 = (t.K1 / 8) * rows, n2 = (t.KH / 8) * rows;
+    for (int item = blockIdx.x * blockDim.x + threadIdx.x; item < n1 + n2; item += gridDim.x * blockDim.x) {
+        const bool second = item >= n1;
+        const int it = second ? item - n1 : item;
+        const int oct = it / rows, r = it - oct * rows;
+        float v[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            const int c = oct * 8 + e;
+            float val = 0.f;
+            if (!second) {
+                if (c < t.FIN) {
+                    if (r < t.H) val = W[L.off_w[0] + r * t.FIN + c];
+                    else if (r == t.H) val = W[L.off_w_out + t.H + c];
+                }
+            } else if (r < t.H && c < t.H) {
+                val = W[L.off_w[1] + r * t.H + c];
+            }
+            v[e] = val;
+        }
+        uint4 hi, lo;
+        split8(v, hi, lo);
+        unsigned char *base = out + (second ? 2 * t.w1_half : 0);
+        const int half = second ? t.w2_half : t.w1_half;
+        const int off = oct * t.S_colW + (r / 8) * 128 + (r % 8) * 16;
+        *reinterpret_cast<uint4 *>(base + off) = hi;
+        *reinterpret_cast<uint4 *>(base + half + off) = lo;
+    }
+}
+
+// ---- device helpers ------------------------------------------------------------------------------------
+__device__ __forceinline__ void fast_sincos(float x, float *s, float *c) {
+    // Cody-Waite reduction to [-pi, pi] then MUFU: abs error ~5e-7 (outputs are in [-1,1])
+    const float k = rintf(x * 0.15915494309189535f);
+    float r = fmaf(k, -6.2831854820251465f, x);
+    r = fmaf(k, 1.7484555e-7f, r);
+    *s = __sinf(r);
+    *c = __cosf(r);
+}
+
+// column sums over the 32 lanes of a warp: lane L returns sum_lanes v[L]   (31 shuffles)
+__device__ __forceinline__ float colsum32(float (&v)[32], int lane) {
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) {
+        const bool up = (lane & o) != 0;
+#pragma unroll
+        for (int c = 0; c < o; ++c) {
+            const float keep = up ? v[c + o] : v[c];
+            const float send = up ? v[c] : v[c + o];
+            v[c] = keep + __shfl_xor_sync(0xffffffffu, send, o);
+        }
+    }
+    return v[0];
+}
+
+struct TcSmem {
+    unsigned char *w1h, *w1l, *w2h, *w2l, *h1h, *h1l, *rh, *rl;
+    float *enc_w, *enc_b, *ang_b, *ang_f, *b1, *b2, *w3h, *b3;
+    float *u0, *u1, *th, *skip, *gbar, *zp, *gx;
+    uint64_t *bars;
+    uint32_t *tmem_slot;
+    __device__ TcSmem(unsigned char *base, const TcDims &t) {
+        w1h = base + t.off_w1; w1l = w1h + t.w1_half;
+        w2h = base + t.off_w2; w2l = w2h + t.w2_half;
+        h1h = base + t.off_h1; h1l = h1h + t.h1_half;
+        rh = base + t.off_r; rl = rh + TC_REGION / 2;
+        float *f = reinterpret_cast<float *>(base + t.off_misc);
+        enc_w = f; f += 2 * t.F;
+        enc_b = f; f += t.F;
+        ang_b = f; f += t.A;
+        ang_f = f; f += t.A;
+        b1 = f; f += t.H;
+        b2 = f; f += t.H;
+        w3h = f; f += t.H;
+        b3 = f; f += 4;
+        u0 = f; f += TC_TP;
+        u1 = f; f += TC_TP;
+        th = f; f += TC_TP;
+        skip = f; f += TC_TP;
+        gbar = f; f += TC_TP;
+        zp = f; f += 4 * TC_TP;
+        gx = f; f += 4 * TC_TP * 3;
+        bars = reinterpret_cast<uint64_t *>(f);
+        tmem_slot = reinterpret_cast<uint32_t *>(bars + 4);
+    }
+};
+
+// one encoded feature and its derivative w.r.t. the sin/cos argument (onf_model.py:39-46, angle_encoder.py:15-18)
+__device__ __forceinline__ void encode_feature(const TcSmem &s, const TcDims &t, int use_cos, int f, float u0, float u1,
+                                               float th, float *e, float *de) {
+    float arg;
+    bool cosine;
+    if (f < t.F) {
+        arg = fmaf(u1, s.enc_w[2 * f + 1], fmaf(u0, s.enc_w[2 * f], s.enc_b[f]));
+        cosine = use_cos && f >= 100;
+    } else if (f < t.FIN) {
+        const int k = f - t.F;
+        arg = (th + s.ang_b[k]) * s.ang_f[k];
+        cosine = k >= t.A / 2;
+    } else {
+        *e = 0.f; *de = 0.f;
+        return;
+    }
+    float sn, cs;
+    fast_sincos(arg, &sn, &cs);
+    *e = cosine ? cs : sn;
+    *de = cosine ? -sn : cs;
+}
+
+// store 16 consecutive columns (col0 .. col0+15) of row `row` into a [row/8][col/8][row%8][col%8] operand buffer
+__device__ __forceinline__ void store_row16(unsigned char *hi_buf, unsigned char *lo_buf, int row, int col0,
+                                            const float *v, int S_row) {
+    uint4 h0, l0, h1, l1;
+    split8(v, h0, l0);
+    split8(v + 8, h1, l1);
+    const int off = (row >> 3) * S_row + (col0 >> 3) * 128 + (row & 7) * 16;
+    *reinterpret_cast<uint4 *>(hi_buf + off) = h0;
+    *reinterpret_cast<uint4 *>(hi_buf + off + 128) = h1;
+    *reinterpret_cast<uint4 *>(lo_buf + off) = l0;
+    *reinterpret_cast<uint4 *>(lo_buf + off + 128) = l1;
+}
+
+// three-pass split product: D (+)= Ahi*Bhi + Alo*Bhi + Ahi*Blo
+__device__ __forceinline__ void mma3(uint32_t tmem_d, uint64_t ah, uint64_t al, uint64_t bh, uint64_t bl, uint32_t idesc,
+                                     bool accumulate) {
+    mma_bf16(tmem_d, ah, bh, idesc, accumulate ? 1u : 0u);
+    mma_bf16(tmem_d, al, bh, idesc, 1u);
+    mma_bf16(tmem_d, ah, bl, idesc, 1u);
+}
+
+__global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const OnfDims &d = a.d;
+    const TcDims &t = a.t;
+    const nfopp_onf_layout &L = d.lay;
+    const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int q = warp & 3, hcol = warp >> 2;          // TMEM lane quarter, column half of the tile
+    const int row = q * 32 + lane;                     // TMEM lane = hidden unit / feature-in-block of this thread
+    if (a.sp && !a.warm && !a.sp->do_train) return;    // engine: not a field-training step
+    const int cnt = a.count ? a.count[p] : a.n;
+    if (cnt <= 0) return;
+    const bool want_bwd = a.want_bwd != 0;
+    const bool want_wgrad = want_bwd && (a.grad_out != nullptr || a.adam_w != nullptr);
+    const bool want_gx = want_bwd && a.gx_out != nullptr;
+    const int F = t.F, FIN = t.FIN, H = t.H, K1 = t.K1, KH = t.KH;
+
+    TcSmem s(smem_raw, t);
+    const float *W = a.weights + (size_t)p * L.n_params;
+    uint64_t *bar_w = s.bars, *bar_mma = s.bars + 1, *bar_aux = s.bars + 2;
+
+    // ---- one-time setup: barriers, TMEM, packed weights by bulk copy, small fp32 parameters ----
+    if (tid == 0) {
+        mbar_init(bar_w, 1);
+        mbar_init(bar_mma, 1);
+        mbar_init(bar_aux, 1);
+        fence_mbar_init();
+    }
+    if (warp == 1) tmem_alloc(s.tmem_slot, 512);
+    __syncthreads();
+    if (tid == 0) {
+        const unsigned char *src = a.packed + (size_t)p * t.packed_bytes;
+        mbar_expect_tx(bar_w, (uint32_t)t.packed_bytes);
+        bulk_g2s(s.w1h, src, 2 * t.w1_half, bar_w);
+        bulk_g2s(s.w2h, src + 2 * t.w1_half, 2 * t.w2_half, bar_w);
+    }
+    for (int i = tid; i < 2 * F; i += TC_THREADS) s.enc_w[i] = W[L.off_enc_w + i];
+    for (int i = tid; i < F; i += TC_THREADS) s.enc_b[i] = W[L.off_enc_b + i];
+    for (int i = tid; i < t.A; i += TC_THREADS) {
+        s.ang_b[i] = W[L.off_ang_b + i];
+        s.ang_f[i] = W[L.off_ang_f + i];
+    }
+    for (int i = tid; i < H; i += TC_THREADS) {
+        s.b1[i] = W[L.off_b[0] + i];
+        s.b2[i] = W[L.off_b[1] + i];
+        s.w3h[i] = W[L.off_w_out + i];
+    }
+    if (tid == 0) s.b3[0] = W[L.off_b_out];
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem = *s.tmem_slot;
+    const uint32_t tm_lane = tmem + ((uint32_t)(q * 32) << 16);
+    if (tid == 0) mbar_wait(bar_w, 0);     // the MMA-issuing thread observes the bulk copies
+
+    uint32_t ph_mma = 0, ph_aux = 0;
+    bool pending_aux = false;
+    // thread-local gradient accumulators (this thread's hidden unit `row`, features row and 128+row, point tid)
+    float acc_db1 = 0.f, acc_db2 = 0.f, acc_dw3 = 0.f, acc_db3 = 0.f;
+    float acc_fa[2] = {0.f, 0.f}, acc_fb[2] = {0.f, 0.f}, acc_fc[2] = {0.f, 0.f};
+    const float my_b1 = row < H ? s.b1[row] : 0.f, my_b2 = row < H ? s.b2[row] : 0.f, my_w3 = row < H ? s.w3h[row] : 0.f;
+
+    const int tiles = (cnt + TC_TP - 1) / TC_TP;
+    for (int tile = 0; tile < tiles; ++tile) {
+        const int n0 = tile * TC_TP;
+        const int nv = min(TC_TP, cnt - n0);
+        const int Nt = ru16(nv);
+        const int c_lo = hcol * 32, c_hi = min(c_lo + 32, Nt);       // this warp's columns of the tile
+        // ---- P0: inputs (onf_model.py:37-38) ----
+        if (tid < TC_TP) {
+            float x0 = 0.f, x1 = 0.f, x2 = 0.f;
+            if (tid < nv) {
+                const float *xp = a.x + ((size_t)p * a.n + n0 + tid) * a.x_stride;
+                x0 = xp[0]; x1 = xp[1];
+                if (L.in_dim == 3) x2 = xp[2];
+            }
+            s.u0[tid] = (x0 - d.mean) / d.sigma;
+            s.u1[tid] = (x1 - d.mean) / d.sigma;
+            s.th[tid] = x2;
+        }
+        __syncthreads();
+        // ---- P1: encoding (CUDA cores) feeding fwd1 in groups of 128 features ----
+        {
+            const int n = tid & 63, oc = tid >> 6;
+            const float u0 = s.u0[n], u1 = s.u1[n], th = s.th[n];
+            for (int g = 0; g < t.MB; ++g) {
+                uint4 ehi[4], elo[4];
+#pragma unroll
+                for (int it = 0; it < 4; ++it) {
+                    const int f0 = 128 * g + 8 * (oc + 4 * it);
+                    float e[8];
+                    if (f0 < K1 && n < Nt) {
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            float de;
+                            encode_feature(s, t, d.use_cos, f0 + i, u0, u1, th, &e[i], &de);
+                        }
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) e[i] = 0.f;
+                    }
+                    split8(e, ehi[it], elo[it]);
+                }
+                if (g > 0 || pending_aux) {          // the scratch region is still being read by earlier MMAs
+                    mbar_wait(bar_aux, ph_aux);
+                    ph_aux ^= 1;
+                    pending_aux = false;
+                }
+#pragma unroll
+                for (int it = 0; it < 4; ++it) {
+                    const int fo = oc + 4 * it;
+                    if (128 * g + 8 * fo < K1 && n < Nt) {
+                        *reinterpret_cast<uint4 *>(s.rh + fo * 1024 + n * 16) = ehi[it];
+                        *reinterpret_cast<uint4 *>(s.rl + fo * 1024 + n * 16) = elo[it];
+                    }
+                }
+                fence_proxy_async();
+                fence_before_sync();
+                __syncthreads();
+                if (tid == 0) {
+                    fence_after_sync();
+                    const uint32_t idesc = instr_desc_bf16(128, Nt, 0, 0);
+                    const int ks_n = min(8, (K1 - 128 * g) / 16);
+                    for (int ks = 0; ks < ks_n; ++ks) {
+                        const uint32_t aoff = (uint32_t)(16 * g + 2 * ks) * t.S_colW, boff = (uint32_t)(2 * ks) * 1024;
+                        mma3(tmem + TM_WORK, desc_kmajor(smem_u32(s.w1h) + aoff, 128, t.S_colW),
+                             desc_kmajor(smem_u32(s.w1l) + aoff, 128, t.S_colW), desc_kmajor(smem_u32(s.rh) + boff, 128, 1024),
+                             desc_kmajor(smem_u32(s.rl) + boff, 128, 1024), idesc, g > 0 || ks > 0);
+                    }
+                    if (g + 1 < t.MB) mma_commit(bar_aux);
+                    else mma_commit(bar_mma);
+                }
+            }
+        }
+        // ---- P2: epilogue 1: bias + ReLU -> H1 operand; row H = skip term of the logit ----
+        mbar_wait(bar_mma, ph_mma);
+        ph_mma ^= 1;
+        fence_after_sync();
+        for (int c0 = c_lo; c0 < c_hi; c0 += 16) {
+            float v[16];
+            tmem_ld16(tm_lane + TM_WORK + c0, v);
+            if (row < H) {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i] + my_b1, 0.f);
+            } else {
+                if (row == H) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) s.skip[c0 + i] = v[i];
+                }
+#pragma unroll
+                for (int i = 0; i < 16; ++i) v[i] = 0.f;
+            }
+            if (row < KH) store_row16(s.h1h, s.h1l, row, c0, v, 1024);
+        }
+        fence_proxy_async();
+        fence_before_sync();
+        __syncthreads();
+        // ---- P3: fwd2 ----
+        if (tid == 0) {
+            fence_after_sync();
+            const uint32_t idesc = instr_desc_bf16(128, Nt, 0, 1);
+            for (int ks = 0; ks < KH / 16; ++ks) {
+                const uint32_t aoff = (uint32_t)(2 * ks) * t.S_colW, boff = (uint32_t)(2 * ks) * 1024;
+                mma3(tmem + TM_WORK + 64, desc_kmajor(smem_u32(s.w2h) + aoff, 128, t.S_colW),
+                     desc_kmajor(smem_u32(s.w2l) + aoff, 128, t.S_colW), desc_mnmajor(smem_u32(s.h1h) + boff, 1024, 128),
+                     desc_mnmajor(smem_u32(s.h1l) + boff, 1024, 128), idesc, ks > 0);
+            }
+            mma_commit(bar_mma);
+        }
+        // ---- P4: epilogue 2: logit, dL/dz, gH2 operand ----
+        mbar_wait(bar_mma, ph_mma);
+        ph_mma ^= 1;
+        fence_after_sync();
+        float r2[32];
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+            const int c0 = c_lo + 16 * half;
+            if (c0 < c_hi) {
+                tmem_ld16(tm_lane + TM_WORK + 64 + c0, &r2[16 * half]);
+#pragma unroll
+                for (int i = 0; i < 16; ++i) r2[16 * half + i] = row < H ? fmaxf(r2[16 * half + i] + my_b2, 0.f) : 0.f;
+            } else {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) r2[16 * half + i] = 0.f;
+            }
+        }
+        {
+            float pz[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) pz[i] = my_w3 * r2[i];
+            const float zs = colsum32(pz, lane);
+            s.zp[q * TC_TP + c_lo + lane] = zs;
+        }
+        __syncthreads();
+        if (tid < TC_TP) {
+            const int n = tid;
+            const float z = s.zp[n] + s.zp[TC_TP + n] + s.zp[2 * TC_TP + n] + s.zp[3 * TC_TP + n] + s.skip[n] + s.b3[0];
+            const bool valid = n < nv;
+            const size_t gi = (size_t)p * a.n + n0 + n;
+            if (valid && a.z_out) a.z_out[gi] = z;
+            float g = 0.f;
+            if (valid && want_bwd) {                        // dL/dz
+                if (a.gbar_mode == 0) g = a.gz[gi];
+                else if (a.gbar_mode == 1) g = (sigmoid_f(z) - a.aux[gi]) / (float)cnt;
+                else {
+                    const float zb = z * a.beta;
+                    const float ez = expf(zb);
+                    g = a.wc * (zb > 20.f ? 1.f : ez / (ez + 1.f));
+                    if (a.gbar_mode == 3) {
+                        const float th = tanhf(z);
+                        g += a.aux[gi] * (1.f - th * th);
+                    }
+                }
+            }
+            s.gbar[n] = g;
+            acc_db3 += g;
+        }
+        if (!want_bwd) {
+            __syncthreads();      // s.zp / s.skip are rewritten by the next tile
+            continue;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+            const int c0 = c_lo + 16 * half;
+            if (c0 < c_hi) {
+                float v[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    const float gb = s.gbar[c0 + i];
+                    const float rr = r2[16 * half + i];
+                    acc_dw3 = fmaf(gb, rr, acc_dw3);
+                    const float g = rr > 0.f ? gb * my_w3 : 0.f;
+                    acc_db2 += g;
+                    v[i] = g;
+                }
+                if (row < KH) store_row16(s.rh, s.rl, row, c0, v, 1024);
+            }
+        }
+        fence_proxy_async();
+        fence_before_sync();
+        __syncthreads();
+        // ---- P5: wgrad2 (persistent accumulator) + dgrad2 ----
+        if (tid == 0) {
+            fence_after_sync();
+            if (want_wgrad) {
+                const uint32_t idesc = instr_desc_bf16(128, KH, 0, 0);
+                for (int ks = 0; ks < Nt / 16; ++ks) {
+                    const uint32_t off = (uint32_t)(2 * ks) * 128;
+                    mma3(tmem + TM_DW2, desc_kmajor(smem_u32(s.rh) + off, 1024, 128), desc_kmajor(smem_u32(s.rl) + off, 1024, 128),
+                         desc_kmajor(smem_u32(s.h1h) + off, 1024, 128), desc_kmajor(smem_u32(s.h1l) + off, 1024, 128), idesc,
+                         tile > 0 || ks > 0);
+                }
+            }
+            const uint32_t idesc = instr_desc_bf16(128, Nt, 1, 1);
+            for (int ks = 0; ks < KH / 16; ++ks) {
+                const uint32_t aoff = (uint32_t)(2 * ks) * 128, boff = (uint32_t)(2 * ks) * 1024;
+                mma3(tmem + TM_WORK, desc_mnmajor(smem_u32(s.w2h) + aoff, 128, t.S_colW),
+                     desc_mnmajor(smem_u32(s.w2l) + aoff, 128, t.S_colW), desc_mnmajor(smem_u32(s.rh) + boff, 1024, 128),
+                     desc_mnmajor(smem_u32(s.rl) + boff, 1024, 128), idesc, ks > 0);
+            }
+            mma_commit(bar_mma);
+        }
+        // ---- P6: epilogue 3: ReLU mask of layer 1 -> gH1 operand (in place over H1); row H := dL/dz ----
+        mbar_wait(bar_mma, ph_mma);
+        ph_mma ^= 1;
+        fence_after_sync();
+        for (int c0 = c_lo; c0 < c_hi; c0 += 16) {
+            float v[16];
+            tmem_ld16(tm_lane + TM_WORK + c0, v);
+            if (row < H) {
+                const int off = (row >> 3) * 1024 + (c0 >> 3) * 128 + (row & 7) * 16;
+                const uint4 m0 = *reinterpret_cast<const uint4 *>(s.h1h + off);
+                const uint4 m1 = *reinterpret_cast<const uint4 *>(s.h1h + off + 128);
+                const uint32_t mw[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    const uint32_t bits = (mw[i >> 1] >> ((i & 1) * 16)) & 0x7FFFu;
+                    v[i] = bits != 0 ? v[i] : 0.f;
+                    acc_db1 += v[i];
+                }
+            } else if (row == H) {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) v[i] = s.gbar[c0 + i];
+            } else {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) v[i] = 0.f;
+            }
+            if (row < KH) store_row16(s.h1h, s.h1l, row, c0, v, 1024);
+        }
+        fence_proxy_async();
+        fence_before_sync();
+        __syncthreads();
+        // ---- P7: dgrad1: gE[k,n] for both feature blocks ----
+        if (tid == 0) {
+            fence_after_sync();
+            const uint32_t idesc = instr_desc_bf16(128, Nt, 1, 1);
+            for (int mb = 0; mb < t.MB; ++mb)
+                for (int ks = 0; ks < KH / 16; ++ks) {
+                    const uint32_t aoff = (uint32_t)(16 * mb) * t.S_colW + (uint32_t)(2 * ks) * 128, boff = (uint32_t)(2 * ks) * 1024;
+                    mma3(tmem + TM_WORK + 64 * mb, desc_mnmajor(smem_u32(s.w1h) + aoff, 128, t.S_colW),
+                         desc_mnmajor(smem_u32(s.w1l) + aoff, 128, t.S_colW), desc_mnmajor(smem_u32(s.h1h) + boff, 1024, 128),
+                         desc_mnmajor(smem_u32(s.h1l) + boff, 1024, 128), idesc, ks > 0);
+                }
+            mma_commit(bar_mma);
+        }
+        // ---- P8/P9: epilogue 4: encoding backward (+ input gradient), E^T operand, wgrad1 per feature block ----
+        mbar_wait(bar_mma, ph_mma);
+        ph_mma ^= 1;
+        fence_after_sync();
+#pragma unroll
+        for (int mb = 0; mb < 2; ++mb) {
+            if (mb >= t.MB) break;
+            const int f = 128 * mb + row;
+            const int pf = min(128, K1 - 128 * mb);              // features of this block that are MMA rows
+            float ew0 = 0.f, ew1 = 0.f, eaf = 0.f;
+            if (f < F) { ew0 = s.enc_w[2 * f]; ew1 = s.enc_w[2 * f + 1]; }
+            else if (f < FIN) eaf = s.ang_f[f - F];
+            float gq[32];
+            uint4 ehi[4], elo[4];
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+                const int c0 = c_lo + 16 * half;
+                float ev[16];
+                if (c0 < c_hi) {
+                    float v[16];
+                    tmem_ld16(tm_lane + TM_WORK + 64 * mb + c0, v);
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        const int n = c0 + i;
+                        float e, de;
+                        encode_feature(s, t, d.use_cos, f, s.u0[n], s.u1[n], s.th[n], &e, &de);
+                        const float gp = f < FIN ? v[i] * de : 0.f;      // rows >= f_in of the M block hold garbage
+                        ev[i] = e;
+                        gq[16 * half + i] = gp;
+                        if (f < F) {
+                            acc_fa[mb] = fmaf(gp, s.u0[n], acc_fa[mb]);
+                            acc_fb[mb] = fmaf(gp, s.u1[n], acc_fb[mb]);
+                            acc_fc[mb] += gp;
+                        } else if (f < FIN) {
+                            acc_fa[mb] = fmaf(gp, eaf, acc_fa[mb]);                          // d ang_b
+                            acc_fb[mb] = fmaf(gp, s.th[n] + s.ang_b[f - F], acc_fb[mb]);     // d ang_f (trained)
+                        }
+                    }
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) { ev[i] = 0.f; gq[16 * half + i] = 0.f; }
+                }
+                split8(ev, ehi[2 * half], elo[2 * half]);
+                split8(ev + 8, ehi[2 * half + 1], elo[2 * half + 1]);
+            }
+            if (want_gx) {
+                // gx[n] = (sum_f gp[f,n] * We[f,c]) / sigma ; g_theta[n] = sum_k gp[k,n] * f_k   (reduce over lanes)
+                float c0v[32], c1v[32], c2v[32];
+#pragma unroll
+                for (int i = 0; i < 32; ++i) { c0v[i] = gq[i] * ew0; c1v[i] = gq[i] * ew1; c2v[i] = gq[i] * eaf; }
+                const float s0 = colsum32(c0v, lane), s1 = colsum32(c1v, lane), s2 = colsum32(c2v, lane);
+                float *dst = s.gx + ((size_t)q * TC_TP + c_lo + lane) * 3;
+                if (mb == 0) { dst[0] = s0; dst[1] = s1; dst[2] = s2; }
+                else { dst[0] += s0; dst[1] += s1; dst[2] += s2; }
+            }
+            if (want_wgrad) {
+                if (mb > 0) {                       // wgrad1 of the previous block still reads the scratch region
+                    mbar_wait(bar_aux, ph_aux);
+                    ph_aux ^= 1;
+                }
+                if (row < pf) {
+#pragma unroll
+                    for (int o = 0; o < 4; ++o) {
+                        const int c0 = c_lo + 8 * o;
+                        if (c0 < c_hi) {
+                            const int off = (c0 >> 3) * 2048 + (row >> 3) * 128 + (row & 7) * 16;
+                            *reinterpret_cast<uint4 *>(s.rh + off) = ehi[o];
+                            *reinterpret_cast<uint4 *>(s.rl + off) = elo[o];
+                        }
+                    }
+                }
+                fence_proxy_async();
+                fence_before_sync();
+                __syncthreads();
+                if (tid == 0) {
+                    fence_after_sync();
+                    const uint32_t idesc = instr_desc_bf16(128, pf, 0, 0);
+                    for (int ks = 0; ks < Nt / 16; ++ks) {
+                        const uint32_t aoff = (uint32_t)(2 * ks) * 128, boff = (uint32_t)(2 * ks) * 2048;
+                        mma3(tmem + TM_DW1 + 128 * mb, desc_kmajor(smem_u32(s.h1h) + aoff, 1024, 128),
+                             desc_kmajor(smem_u32(s.h1l) + aoff, 1024, 128), desc_kmajor(smem_u32(s.rh) + boff, 128, 2048),
+                             desc_kmajor(smem_u32(s.rl) + boff, 128, 2048), idesc, tile > 0 || ks > 0);
+                    }
+                    mma_commit(bar_aux);
+                }
+                if (mb + 1 >= t.MB) pending_aux = true;
+            }
+        }
+        if (want_gx) {
+            __syncthreads();
+            if (tid < nv) {
+                const int n = tid;
+                float g0 = 0.f, g1 = 0.f, g2 = 0.f;
+#pragma unroll
+                for (int qq = 0; qq < 4; ++qq) {
+                    const float *src = s.gx + ((size_t)qq * TC_TP + n) * 3;
+                    g0 += src[0]; g1 += src[1]; g2 += src[2];
+                }
+                float *out = a.gx_out + ((size_t)p * a.n + n0 + n) * a.x_stride;
+                out[0] = g0 / d.sigma;
+                out[1] = g1 / d.sigma;
+                if (L.in_dim == 3) out[2] = g2;
+                for (int c = L.in_dim; c < a.x_stride; ++c) out[c] = 0.f;   // pose columns the ONF does not read
+            }
+        }
+        fence_before_sync();
+        __syncthreads();           // TMEM work columns and s.* scratch are reused by the next tile
+    }
+
+    // ---- weight gradients: drain the TMEM accumulators once per problem ----
+    if (want_wgrad) {
+        if (pending_aux) {
+            mbar_wait(bar_aux, ph_aux);
+            ph_aux ^= 1;
+        }
+        fence_after_sync();
+        const size_t po = (size_t)p * L.n_params;
+        const bool adam = a.adam_w != nullptr;
+        float step_size = 0.f, bc2_sqrt = 1.f;
+        if (adam) { step_size = a.sp->onf_step_size; bc2_sqrt = a.sp->onf_bc2_sqrt; }
+        // one parameter: plain gradient store, or torch.optim.Adam (_single_tensor_adam) returning the new weight
+        auto emit = [&](int idx, float g) -> float {
+            if (!adam) { a.grad_out[po + idx] = g; return 0.f; }
+            float w = a.adam_w[po + idx], m = a.adam_m[po + idx], v = a.adam_v[po + idx];
+            m = fmaf(a.w1, g - m, m);
+            v = fmaf(a.w2 * g, g, v * a.beta2);
+            const float denom = sqrtf(v) / bc2_sqrt + a.eps;
+            w = fmaf(-step_size, m / denom, w);
+            a.adam_w[po + idx] = w; a.adam_m[po + idx] = m; a.adam_v[po + idx] = v;
+            return w;
+        };
+        // 16 consecutive parameters of one row (float4 traffic), returns new weights in g[] (Adam mode)
+        auto emit16 = [&](int idx0, int valid, float *g) {
+#pragma unroll
+            for (int c4 = 0; c4 < 4; ++c4) {
+                if (4 * c4 >= valid) { g[4 * c4] = g[4 * c4 + 1] = g[4 * c4 + 2] = g[4 * c4 + 3] = 0.f; continue; }
+                const size_t o = po + idx0 + 4 * c4;
+                if (!adam) {
+                    *reinterpret_cast<float4 *>(a.grad_out + o) = make_float4(g[4 * c4], g[4 * c4 + 1], g[4 * c4 + 2], g[4 * c4 + 3]);
+                    continue;
+                }
+                const float4 w4 = *reinterpret_cast<const float4 *>(a.adam_w + o), m4 = *reinterpret_cast<const float4 *>(a.adam_m + o),
+                             v4 = *reinterpret_cast<const float4 *>(a.adam_v + o);
+                float wv[4] = {w4.x, w4.y, w4.z, w4.w}, mv[4] = {m4.x, m4.y, m4.z, m4.w}, vv[4] = {v4.x, v4.y, v4.z, v4.w};
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const float gg = g[4 * c4 + c];
+                    mv[c] = fmaf(a.w1, gg - mv[c], mv[c]);
+                    vv[c] = fmaf(a.w2 * gg, gg, vv[c] * a.beta2);
+                    const float denom = sqrtf(vv[c]) / bc2_sqrt + a.eps;
+                    wv[c] = fmaf(-step_size, mv[c] / denom, wv[c]);
+                    g[4 * c4 + c] = wv[c];
+                }
+                *reinterpret_cast<float4 *>(a.adam_w + o) = make_float4(wv[0], wv[1], wv[2], wv[3]);
+                *reinterpret_cast<float4 *>(a.adam_m + o) = make_float4(mv[0], mv[1], mv[2], mv[3]);
+                *reinterpret_cast<float4 *>(a.adam_v + o) = make_float4(vv[0], vv[1], vv[2], vv[3]);
+            }
+        };
+        unsigned char *pk = adam ? a.packed_out + (size_t)p * t.packed_bytes : nullptr;
+        // dW1: rows j < H -> mlp.0.weight[j,:], row H -> mlp2.0.weight[0, H:]
+        for (int ch = hcol; ch < K1 / 16; ch += 2) {
+            float g[16];
+            tmem_ld16(tm_lane + TM_DW1 + 16 * ch, g);
+            if (row <= H) {
+                const int base = row < H ? L.off_w[0] + row * FIN : L.off_w_out + H;
+                emit16(base + 16 * ch, FIN - 16 * ch, g);
+                if (adam) {
+                    uint4 h0, l0, h1, l1;
+                    split8(g, h0, l0);
+                    split8(g + 8, h1, l1);
+                    const int off = (2 * ch) * t.S_colW + (row >> 3) * 128 + (row & 7) * 16;
+                    *reinterpret_cast<uint4 *>(pk + off) = h0;
+                    *reinterpret_cast<uint4 *>(pk + off + t.S_colW) = h1;
+                    *reinterpret_cast<uint4 *>(pk + t.w1_half + off) = l0;
+                    *reinterpret_cast<uint4 *>(pk + t.w1_half + off + t.S_colW) = l1;
+                }
+            }
+        }
+        // dW2: rows i < H -> mlp.2.weight[i,:]
+        for (int ch = hcol; ch < KH / 16; ch += 2) {
+            float g[16];
+            tmem_ld16(tm_lane + TM_DW2 + 16 * ch, g);
+            if (row < H) {
+                emit16(L.off_w[1] + row * H + 16 * ch, H - 16 * ch, g);
+                if (adam) {
+                    uint4 h0, l0, h1, l1;
+                    split8(g, h0, l0);
+                    split8(g + 8, h1, l1);
+                    unsigned char *pk2 = pk + 2 * t.w1_half;
+                    const int off = (2 * ch) * t.S_colW + (row >> 3) * 128 + (row & 7) * 16;
+                    *reinterpret_cast<uint4 *>(pk2 + off) = h0;
+                    *reinterpret_cast<uint4 *>(pk2 + off + t.S_colW) = h1;
+                    *reinterpret_cast<uint4 *>(pk2 + t.w2_half + off) = l0;
+                    *reinterpret_cast<uint4 *>(pk2 + t.w2_half + off + t.S_colW) = l1;
+                }
+            }
+        }
+        // per-unit / per-feature vectors: combine the two column halves through shared memory (scratch region)
+        __syncthreads();
+        float *red = reinterpret_cast<float *>(s.rh);          // [9][2][128] + [64]
+        {
+            float *r0 = red + hcol * 128 + row;
+            r0[0 * 256] = acc_db1; r0[1 * 256] = acc_db2; r0[2 * 256] = acc_dw3;
+            r0[3 * 256] = acc_fa[0]; r0[4 * 256] = acc_fb[0]; r0[5 * 256] = acc_fc[0];
+            r0[6 * 256] = acc_fa[1]; r0[7 * 256] = acc_fb[1]; r0[8 * 256] = acc_fc[1];
+            if (tid < TC_TP) red[9 * 256 + tid] = acc_db3;
+        }
+        __syncthreads();
+        if (tid < 128) {
+            auto tot = [&](int qn) { return red[qn * 256 + tid] + red[qn * 256 + 128 + tid]; };
+            if (tid < H) {
+                emit(L.off_b[0] + tid, tot(0));
+                emit(L.off_b[1] + tid, tot(1));
+                emit(L.off_w_out + tid, tot(2));
+            }
+            for (int mb = 0; mb < t.MB; ++mb) {
+                const int f = 128 * mb + tid;
+                const float ga = tot(3 + 3 * mb), gb = tot(4 + 3 * mb), gc = tot(5 + 3 * mb);
+                if (f < F) {
+                    emit(L.off_enc_w + 2 * f, ga);
+                    emit(L.off_enc_w + 2 * f + 1, gb);
+                    emit(L.off_enc_b + f, d.bias ? gc : 0.f);
+                } else if (f < FIN) {
+                    emit(L.off_ang_b + f - F, ga);
+                    emit(L.off_ang_f + f - F, gb);
+                }
+            }
+            if (tid == 0) {
+                float g3 = 0.f;
+                for (int i = 0; i < TC_TP; ++i) g3 += red[9 * 256 + i];
+                emit(L.off_b_out, g3);
+            }
+        }
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem, 512);
+}
+
+// ---- host side ---------------------------------------------------------------------------------------------
+bool onf_tc_supported(const OnfDims &d) {
+    TcDims t;
+    return tc_make_dims(d, &t);
+}
+
+size_t onf_tc_packed_bytes(const OnfDims &d) {
+    TcDims t;
+    return tc_make_dims(d, &t) ? (size_t)t.packed_bytes : 0;
+}
+
+int onf_tc_prepare(const OnfDims &d) {
+    TcDims t;
+    NFOPP_REQUIRE(tc_make_dims(d, &t), "onf(tensor): needs 2 hidden layers, hidden <= 111, f_in <= 224 (hidden=%d layers=%d)", d.H,
+                  d.L);
+    NFOPP_CHECK_CUDA(cudaFuncSetAttribute(onf_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, t.smem_bytes));
+    return NFOPP_OK;
+}
+
+int onf_tc_pack(const OnfDims &d, const float *weights, unsigned char *packed, int P, cudaStream_t stream) {
+    TcPackArgs a{};
+    a.d = d;
+    NFOPP_REQUIRE(tc_make_dims(d, &a.t), "onf(tensor): unsupported network shape");
+    a.weights = weights; a.packed = packed;
+    if (P == 0) return NFOPP_OK;
+    const int items = (a.t.K1 / 8 + a.t.KH / 8) * a.t.KH;
+    dim3 grid((items + 255) / 256, P);
+    onf_tc_pack_kernel<<<grid, 256, 0, stream>>>(a);
+    NFOPP_CHECK_CUDA(cudaGetLastError());
+    return NFOPP_OK;
+}
+
+int onf_tc_launch(const OnfArgs &o, const OnfTcExtra &x, int P, cudaStream_t stream) {
+    OnfTcArgs a{};
+    a.d = o.d;
+    NFOPP_REQUIRE(tc_make_dims(o.d, &a.t), "onf(tensor): unsupported network shape");
+    a.weights = o.weights; a.packed = x.packed; a.x = o.x; a.count = o.count; a.sp = o.sp;
+    a.n = o.n; a.x_stride = o.x_stride ? o.x_stride : o.d.lay.in_dim;
+    a.want_bwd = o.want_bwd; a.gbar_mode = o.gbar_mode; a.gz = o.gz; a.aux = o.aux; a.wc = o.wc; a.beta = o.beta;
+    a.z_out = o.z_out; a.gx_out = o.gx_out; a.grad_out = x.grad_out;
+    a.adam_w = x.adam_w; a.adam_m = x.adam_m; a.adam_v = x.adam_v; a.packed_out = x.packed_out;
+    a.w1 = x.w1; a.beta2 = x.beta2; a.w2 = x.w2; a.eps = x.eps; a.warm = x.warm;
+    NFOPP_REQUIRE(a.packed, "onf(tensor): packed operand copy missing");
+    NFOPP_REQUIRE(!a.adam_w || (a.sp && a.packed_out), "onf(tensor): fused Adam needs step parameters and the packed copy");
+    if (a.n == 0 || P == 0) return NFOPP_OK;
+    onf_tc_kernel<<<P, TC_THREADS, a.t.smem_bytes, stream>>>(a);
+    NFOPP_CHECK_CUDA(cudaGetLastError());
+    return NFOPP_OK;
+}
+
+}  // namespace nfopp

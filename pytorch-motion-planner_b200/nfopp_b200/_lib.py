@@ -50,12 +50,13 @@ SIGNATURES = {
     "nfopp_label_circle": (_I, [_P, _I, _I, _I, _P, _P, _I, _I, C.c_double, _P, _P, _P]),
     "nfopp_label_rectangle": (_I, [_P, _I, _I, _P, _P, _I, _I, _P, _P, _P, _P]),
     "nfopp_label_grid": (_I, [_P, _I, _I, _I, _P, _I, _I, _I, C.c_double, C.c_double, C.c_double, _P, _P, _P]),
-    "nfopp_onf_forward": (_I, [C.POINTER(OnfConfig), _P, _P, _P, _I, _I, _P, _I, _P]),
-    "nfopp_onf_tiles": (_I, [C.POINTER(OnfConfig), _I]),
+    "nfopp_onf_scratch_bytes": (_I, [C.POINTER(OnfConfig), _I, _I, C.POINTER(C.c_size_t)]),
+    "nfopp_onf_forward": (_I, [C.POINTER(OnfConfig), _P, _P, _P, _I, _I, _P, _I, _P, _P]),
+    "nfopp_onf_tiles": (_I, [C.POINTER(OnfConfig), _I, _I]),
     "nfopp_onf_backward": (_I, [C.POINTER(OnfConfig), _P, _P, _P, _I, _I, _I, _P, _P, C.c_float, C.c_float, _P, _P,
-                                _P, _I, _P]),
-    "nfopp_onf_reduce_grad": (_I, [C.POINTER(OnfConfig), _P, _P, _I, _I, _P, _P]),
-    "nfopp_onf_adam": (_I, [C.POINTER(OnfConfig), _P, _P, _P, _P, _P, _I, _I, _I, C.c_double, C.c_double,
+                                _P, _I, _P, _P]),
+    "nfopp_onf_reduce_grad": (_I, [C.POINTER(OnfConfig), _P, _P, _I, _I, _I, _P, _P]),
+    "nfopp_onf_adam": (_I, [C.POINTER(OnfConfig), _P, _P, _P, _P, _P, _I, _I, _I, _I, C.c_double, C.c_double,
                             C.c_double, C.c_double, _P]),
     "nfopp_choice": (_I, [_P, _I, _I, _I, _I, _P, _I, _P, _P, _P]),
     "nfopp_engine_workspace_bytes": (_I, [C.POINTER(PlannerConfig), C.POINTER(C.c_size_t)]),
@@ -65,6 +66,7 @@ SIGNATURES = {
                                  C.POINTER(C.c_int32 * 3)]),
     "nfopp_engine_buffer_count": (_I, [_P]),
     "nfopp_engine_buffer_name": (C.c_char_p, [_P, _I]),
+    "nfopp_engine_invalidate_weights": (_I, [_P]),
     "nfopp_engine_get_counter": (_I, [_P, _I, C.POINTER(C.c_int64)]),
     "nfopp_engine_set_counter": (_I, [_P, _I, C.c_int64]),
     "nfopp_engine_warmup": (_I, [_P, _I, _P]),
@@ -94,7 +96,7 @@ def lib():
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(handle, name)
             fn.restype, fn.argtypes = res, args
-        if handle.nfopp_abi_version() != 1:
+        if handle.nfopp_abi_version() != 2:
             raise NfoppError("libnfopp.so ABI version mismatch")
         _lib = handle
     return _lib
@@ -110,6 +112,14 @@ def check(rc):
     if rc == -4:
         raise KeyError(msg)
     raise NfoppError(f"libnfopp error {rc}: {msg}")
+
+
+def onf_scratch(cfg, problems, impl, device):
+    """Device scratch an ONF forward/backward call of `impl` needs (tensor path: bf16 operand copy of the weights)."""
+    import torch
+    nbytes = C.c_size_t()
+    check(lib().nfopp_onf_scratch_bytes(C.byref(cfg), problems, impl, C.byref(nbytes)))
+    return torch.empty(max(int(nbytes.value), 16), dtype=torch.uint8, device=device)
 
 
 def ptr(t):

@@ -101,6 +101,7 @@ class EngineConfig:
     rng_mode: str = "philox"            # "philox" (on-device) | "inject" (host supplies every variate)
     seed: int = 0
     max_choice_uniforms: int = 0
+    onf_impl: str = "auto"              # ONF kernels: "auto" (tcgen05 when the shape allows) | "fma" | "tensor"
 
     @property
     def dim(self):
@@ -133,7 +134,8 @@ class EngineConfig:
         c.bounds = (C.c_double * 4)(*(self.checker_bounds or (0, 0, 0, 0)))
         c.border = (C.c_double * 4)(*self.border)
         c.rng_mode = {"philox": 0, "inject": 1}[self.rng_mode]
-        c.seed, c.max_choice_uniforms, c.onf_impl = self.seed, self.max_choice_uniforms, 0
+        c.seed, c.max_choice_uniforms = self.seed, self.max_choice_uniforms
+        c.onf_impl = {"auto": 0, "fma": 1, "tensor": 2}[self.onf_impl]
         return c
 
 
@@ -198,7 +200,15 @@ class PlannerEngine:
         return self.workspace[off:off + nb.value].view(dtype).view(*shape)
 
     def __getitem__(self, name) -> torch.Tensor:
+        if name == "onf_w":
+            # the caller may write the weights through this view: the tensor path rebuilds its bf16 operand copy
+            # at the next step.  Writers that keep a view (ONF modules adopted by a planner) call
+            # invalidate_weights() themselves.
+            self.invalidate_weights()
         return self.buffers[name]
+
+    def invalidate_weights(self):
+        L.check(self._lib.nfopp_engine_invalidate_weights(self._h))
 
     def set_constants(self):
         cfg = self.config

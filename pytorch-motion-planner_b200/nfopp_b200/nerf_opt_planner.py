@@ -116,6 +116,9 @@ class NERFOptPlanner(ContinuousPlanner):
             raise RuntimeError("call init(start_point, goal_point, boundaries) before step()")
         timer.tick("step")
         self._sync_environment()
+        # the caller holds the ONF module whose parameters are views of the engine's weights (planner._collision_model,
+        # scripts/run_planner.py:72-73) and may have written them: have the tensor path refresh its operand copy
+        self._engine.invalidate_weights()
         self._engine.step(1, graph=self._use_graph and self._rng_mode == "philox")
         timer.tock("step")
 

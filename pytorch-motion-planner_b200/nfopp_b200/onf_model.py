@@ -25,8 +25,9 @@ class _OnfFunction(torch.autograd.Function):
         xin = x[:, :module.in_dim].detach().to(torch.float32).contiguous()
         z = torch.empty(n, dtype=torch.float32, device=flat.device)
         with torch.cuda.device(flat.device):
-            L.check(L.lib().nfopp_onf_forward(C.byref(cfg), L.ptr(flat), L.ptr(xin), None, 1, n, L.ptr(z), 0,
-                                              L.stream_ptr()))
+            scratch = L.onf_scratch(cfg, 1, module.impl, flat.device)
+            L.check(L.lib().nfopp_onf_forward(C.byref(cfg), L.ptr(flat), L.ptr(xin), None, 1, n, L.ptr(z),
+                                              module.impl, L.ptr(scratch), L.stream_ptr()))
         ctx.module, ctx.xin, ctx.x_cols = module, xin, x.shape[1]
         return z
 
@@ -37,7 +38,8 @@ class _OnfFunction(torch.autograd.Function):
         cfg = spec.to_c()
         n = xin.shape[0]
         lib = L.lib()
-        tiles = lib.nfopp_onf_tiles(C.byref(cfg), n)
+        impl = module.impl
+        tiles = lib.nfopp_onf_tiles(C.byref(cfg), n, impl)
         gz = gz.detach().to(torch.float32).contiguous()
         gpart = torch.zeros(tiles * flat.numel(), dtype=torch.float32, device=flat.device)
         gflat = torch.empty_like(flat)
@@ -45,9 +47,10 @@ class _OnfFunction(torch.autograd.Function):
         gxin = torch.empty(n, module.in_dim, dtype=torch.float32, device=flat.device)
         with torch.cuda.device(flat.device):
             s = L.stream_ptr()
+            scratch = L.onf_scratch(cfg, 1, impl, flat.device)
             L.check(lib.nfopp_onf_backward(C.byref(cfg), L.ptr(flat), L.ptr(xin), None, 1, n, 0, L.ptr(gz), None,
-                                           0.0, 1.0, None, L.ptr(gxin), L.ptr(gpart), 0, s))
-            L.check(lib.nfopp_onf_reduce_grad(C.byref(cfg), L.ptr(gpart), None, 1, n, L.ptr(gflat), s))
+                                           0.0, 1.0, None, L.ptr(gxin), L.ptr(gpart), impl, L.ptr(scratch), s))
+            L.check(lib.nfopp_onf_reduce_grad(C.byref(cfg), L.ptr(gpart), None, 1, n, impl, L.ptr(gflat), s))
         gx[:, :module.in_dim] = gxin
         grads = []
         for name, _ in module._param_segments():
@@ -81,6 +84,7 @@ class ONF(nn.Module):
         self.spec = OnfSpec(mean=float(mean), sigma=float(sigma), use_cos=bool(use_cos), angle=bool(angle_encoding),
                             hidden=int(hidden), layers=int(layers), bias=bool(bias))
         self.in_dim = 3 if angle_encoding else 2
+        self.impl = 0               # kernel implementation: 0 auto (tcgen05 when the shape allows), 1 FMA, 2 tensor
         self._segments, self._n_params = onf_segments(self.spec)
         self._flat = None
         self._repack()

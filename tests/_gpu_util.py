@@ -12,6 +12,7 @@ def onf_spec(ocfg) -> OnfSpec:
 
 
 def engine_config(name, fx, rng_mode="inject", problems=1, **over) -> EngineConfig:
+    """over: any EngineConfig field, e.g. onf_impl="fma" | "tensor"."""
     pc = U.PLANNER_CFGS[name]
     obs = fx["meta/obstacles"]
     kw = dict(
