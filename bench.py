@@ -33,12 +33,18 @@ UNIT = "problem-steps/s"
 PROBLEMS_PER_GPU = 1024
 
 
-def workload_config(problems):
+def workload_config(problems, onf_impl="auto"):
+    tensor = onf_impl != "fma"
     return {"workload": "configs[1]: corridor, non-holonomic forward-only ConstrainedNERFOptPlanner",
             "problems_per_gpu": problems, "trajectory_length": 100, "onf": "F_in=220 (200 Fourier + 20 angle), 2x100 hidden",
             "samples_per_step": 209, "checker": "disc r=0.3 vs 20 obstacle points per problem",
-            "rng": "on-device Philox4x32-10", "launch": "CUDA graph of 9 kernels per step",
-            "l2": "per-step working set (ONF w/m/v + gradient partials, ~1.3 GB at 1024 problems) exceeds the 126 MB L2"}
+            "rng": "on-device Philox4x32-10",
+            "onf_impl": "tensor (tcgen05, bf16 hi/lo split operands, fp32 TMEM accumulators, fused Adam)" if tensor
+            else "fma (CUDA-core fp32)",
+            "launch": f"CUDA graph of {8 if tensor else 9} kernels per step",
+            "l2": "per-step working set (ONF w/m/v fp32 + bf16 operand copy, ~0.55 GB at 1024 problems) exceeds the 126 MB L2"
+            if tensor else
+            "per-step working set (ONF w/m/v + gradient partials, ~1.3 GB at 1024 problems) exceeds the 126 MB L2"}
 
 
 # ----------------------------------------------------------------------------------------- CPU baseline
@@ -145,6 +151,7 @@ def run_ours(args):
     lo, hi = shard_range(P * world, rank, world)            # this rank's problem ids (weak scaling)
     starts, goals, bounds, obstacles = TestEnvironmentBuilder.make_corridor_batch(hi - lo, seed=lo)
     cfg = corridor_config(hi - lo, seed=1234 + lo)
+    cfg.onf_impl = args.onf_impl
     planner = BatchedPlanner(cfg, device=f"cuda:{local}")
     planner.init(starts, goals, obstacles=obstacles)
     eng = planner.engine
@@ -223,21 +230,26 @@ def run_ours(args):
     train_ms = prof["onf_train_fwd_bwd"]
     flops_launch = 3 * 2 * mac * 209 * (hi - lo)                           # fwd + dgrad + wgrad over 209 points
     achieved = flops_launch / (train_ms * 1e-3) / 1e12
+    tensor = "onf_wp" in eng.buffers
     traffic = None
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "roofline_traffic.json"))).get("onf_train_fwd_bwd")
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "roofline_traffic.json"))).get(
+            "onf_train_fwd_bwd_tensor" if tensor else "onf_train_fwd_bwd")
     except Exception:
         pass
     step_bytes = (24 * n_params + 15_000) * (hi - lo)                     # bytes / problem-step
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic", "config": workload_config(P),
+        "dtype": "f32 (tensor path: bf16 hi/lo split products, fp32 accumulate)" if tensor else "f32",
+        "data": "synthetic", "config": workload_config(P, "tensor" if tensor else "fma"),
         "clocks": clocks.summary(),
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "steps": e2e_k, "ms_per_step": ms_e2e / e2e_k},
         "gpu_launches": int(launches),
-        "roofline": {"kernel": "onf_tile_kernel (ONF train fwd+bwd, FMA path)", "bound": "tensor",
+        "roofline": {"kernel": "onf_tc_kernel (ONF train fwd+bwd+Adam, tcgen05 path; algorithmic flops, the split "
+                               "products issue 3x as many MMAs)" if tensor else
+                     "onf_tile_kernel (ONF train fwd+bwd, FMA path)", "bound": "tensor",
                      "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved / peak_tf,
                      "traffic": traffic, "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained (of measured)"
                      if peaks else "fallback",
@@ -285,6 +297,8 @@ def main():
     ap.add_argument("--problems", type=int, default=PROBLEMS_PER_GPU, help="problems per GPU")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--onf-impl", default="auto", choices=["auto", "fma", "tensor"],
+                    help="ONF kernels: tcgen05 tensor path (default for the reference network shape) or CUDA-core FMA")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl == "reference":

@@ -32,7 +32,7 @@
 namespace nfopp {
 using namespace tc05;
 
-constexpr int TC_THREADS = 256;
+constexpr int TC_THREADS = 512;
 constexpr int TC_TP = 64;                        // points per tile = max UMMA N used for point-indexed outputs
 constexpr int TC_REGION = 32768;                 // E ring / gH2 / E^T scratch (two 16 KB halves: hi, lo)
 constexpr uint32_t TM_DW1 = 0, TM_DW2 = 224, TM_WORK = 336;   // TMEM column map (512 columns allocated)
@@ -65,7 +65,9 @@ __host__ __device__ inline bool tc_make_dims(const OnfDims &d, TcDims *out) {
     t.smem_bytes = t.off_misc + misc_floats * 4 + 64;
     t.packed_bytes = 2 * t.w1_half + 2 * t.w2_half;
     *out = t;
-    return d.L == 2 && t.KH <= 112 && t.K1 <= 224 && t.H >= 8 && t.smem_bytes <= 227 * 1024;
+    // the epilogue stages the whole gradient blob (+ 20 KB of per-unit partial sums) over the dead operand buffers
+    const int stage_bytes = ((d.lay.n_params + 31) / 32 * 32 + 10 * 512) * 4;
+    return d.L == 2 && t.KH <= 112 && t.K1 <= 224 && t.H >= 8 && t.smem_bytes <= 227 * 1024 && stage_bytes <= t.off_misc;
 }
 
 struct OnfTcArgs {
@@ -146,19 +148,20 @@ __device__ __forceinline__ void fast_sincos(float x, float *s, float *c) {
     *c = __cosf(r);
 }
 
-// column sums over the 32 lanes of a warp: lane L returns sum_lanes v[L]   (31 shuffles)
-__device__ __forceinline__ float colsum32(float (&v)[32], int lane) {
+// column sums over the 32 lanes of a warp for 16 columns: every lane returns sum_lanes v[lane >> 1]  (16 shuffles)
+__device__ __forceinline__ float colsum16(float (&v)[16], int lane) {
 #pragma unroll
-    for (int o = 16; o >= 1; o >>= 1) {
+    for (int o = 16; o >= 2; o >>= 1) {
         const bool up = (lane & o) != 0;
+        const int h = o >> 1;
 #pragma unroll
-        for (int c = 0; c < o; ++c) {
-            const float keep = up ? v[c + o] : v[c];
-            const float send = up ? v[c] : v[c + o];
+        for (int c = 0; c < h; ++c) {
+            const float keep = up ? v[c + h] : v[c];
+            const float send = up ? v[c] : v[c + h];
             v[c] = keep + __shfl_xor_sync(0xffffffffu, send, o);
         }
     }
-    return v[0];
+    return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 1);
 }
 
 struct TcSmem {
@@ -236,14 +239,16 @@ __device__ __forceinline__ void mma3(uint32_t tmem_d, uint64_t ah, uint64_t al, 
     mma_bf16(tmem_d, ah, bl, idesc, 1u);
 }
 
+// Thread layout: 16 warps.  warp = 4*cq + q: q = TMEM lane quarter (rows 32q..32q+31), cq = column quarter of the
+// point tile (columns 16cq..16cq+15).  A thread therefore owns one hidden unit / feature (`row`) and 16 points.
 __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const OnfDims &d = a.d;
     const TcDims &t = a.t;
     const nfopp_onf_layout &L = d.lay;
     const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int q = warp & 3, hcol = warp >> 2;          // TMEM lane quarter, column half of the tile
-    const int row = q * 32 + lane;                     // TMEM lane = hidden unit / feature-in-block of this thread
+    const int q = warp & 3, cq = warp >> 2;
+    const int row = q * 32 + lane;
     if (a.sp && !a.warm && !a.sp->do_train) return;    // engine: not a field-training step
     const int cnt = a.count ? a.count[p] : a.n;
     if (cnt <= 0) return;
@@ -256,7 +261,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
     const float *W = a.weights + (size_t)p * L.n_params;
     uint64_t *bar_w = s.bars, *bar_mma = s.bars + 1, *bar_aux = s.bars + 2;
 
-    // ---- one-time setup: barriers, TMEM, packed weights by bulk copy, small fp32 parameters ----
+    // ---- one-time setup: barriers, TMEM, packed weights by bulk copy (TMA), small fp32 parameters ----
     if (tid == 0) {
         mbar_init(bar_w, 1);
         mbar_init(bar_mma, 1);
@@ -292,9 +297,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
 
     uint32_t ph_mma = 0, ph_aux = 0;
     bool pending_aux = false;
-    // thread-local gradient accumulators (this thread's hidden unit `row`, features row and 128+row, point tid)
+    // thread-local gradient accumulators (hidden unit `row`; features row and 128+row; point tid)
     float acc_db1 = 0.f, acc_db2 = 0.f, acc_dw3 = 0.f, acc_db3 = 0.f;
-    float acc_fa[2] = {0.f, 0.f}, acc_fb[2] = {0.f, 0.f}, acc_fc[2] = {0.f, 0.f};
+    float fa0 = 0.f, fb0 = 0.f, fc0 = 0.f, fa1 = 0.f, fb1 = 0.f, fc1 = 0.f;
     const float my_b1 = row < H ? s.b1[row] : 0.f, my_b2 = row < H ? s.b2[row] : 0.f, my_w3 = row < H ? s.w3h[row] : 0.f;
 
     const int tiles = (cnt + TC_TP - 1) / TC_TP;
@@ -302,7 +307,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
         const int n0 = tile * TC_TP;
         const int nv = min(TC_TP, cnt - n0);
         const int Nt = ru16(nv);
-        const int c_lo = hcol * 32, c_hi = min(c_lo + 32, Nt);       // this warp's columns of the tile
+        const int c0 = 16 * cq;                        // this warp's 16 columns of the tile
+        const bool cols_on = c0 < Nt;
         // ---- P0: inputs (onf_model.py:37-38) ----
         if (tid < TC_TP) {
             float x0 = 0.f, x1 = 0.f, x2 = 0.f;
@@ -318,13 +324,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
         __syncthreads();
         // ---- P1: encoding (CUDA cores) feeding fwd1 in groups of 128 features ----
         {
-            const int n = tid & 63, oc = tid >> 6;
+            const int n = tid & 63, oc = tid >> 6;       // point, feature octet (0..7) within a 64-feature half group
             const float u0 = s.u0[n], u1 = s.u1[n], th = s.th[n];
+#pragma unroll 1
             for (int g = 0; g < t.MB; ++g) {
-                uint4 ehi[4], elo[4];
+                uint4 ehi[2], elo[2];
 #pragma unroll
-                for (int it = 0; it < 4; ++it) {
-                    const int f0 = 128 * g + 8 * (oc + 4 * it);
+                for (int it = 0; it < 2; ++it) {
+                    const int f0 = 128 * g + 8 * (oc + 8 * it);
                     float e[8];
                     if (f0 < K1 && n < Nt) {
 #pragma unroll
@@ -344,8 +351,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
                     pending_aux = false;
                 }
 #pragma unroll
-                for (int it = 0; it < 4; ++it) {
-                    const int fo = oc + 4 * it;
+                for (int it = 0; it < 2; ++it) {
+                    const int fo = oc + 8 * it;
                     if (128 * g + 8 * fo < K1 && n < Nt) {
                         *reinterpret_cast<uint4 *>(s.rh + fo * 1024 + n * 16) = ehi[it];
                         *reinterpret_cast<uint4 *>(s.rl + fo * 1024 + n * 16) = elo[it];
@@ -373,7 +380,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
         mbar_wait(bar_mma, ph_mma);
         ph_mma ^= 1;
         fence_after_sync();
-        for (int c0 = c_lo; c0 < c_hi; c0 += 16) {
+        if (cols_on) {
             float v[16];
             tmem_ld16(tm_lane + TM_WORK + c0, v);
             if (row < H) {
@@ -408,25 +415,21 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
         mbar_wait(bar_mma, ph_mma);
         ph_mma ^= 1;
         fence_after_sync();
-        float r2[32];
+        float r2[16];
+        if (cols_on) {
+            tmem_ld16(tm_lane + TM_WORK + 64 + c0, r2);
 #pragma unroll
-        for (int half = 0; half < 2; ++half) {
-            const int c0 = c_lo + 16 * half;
-            if (c0 < c_hi) {
-                tmem_ld16(tm_lane + TM_WORK + 64 + c0, &r2[16 * half]);
+            for (int i = 0; i < 16; ++i) r2[i] = row < H ? fmaxf(r2[i] + my_b2, 0.f) : 0.f;
+        } else {
 #pragma unroll
-                for (int i = 0; i < 16; ++i) r2[16 * half + i] = row < H ? fmaxf(r2[16 * half + i] + my_b2, 0.f) : 0.f;
-            } else {
-#pragma unroll
-                for (int i = 0; i < 16; ++i) r2[16 * half + i] = 0.f;
-            }
+            for (int i = 0; i < 16; ++i) r2[i] = 0.f;
         }
         {
-            float pz[32];
+            float pz[16];
 #pragma unroll
-            for (int i = 0; i < 32; ++i) pz[i] = my_w3 * r2[i];
-            const float zs = colsum32(pz, lane);
-            s.zp[q * TC_TP + c_lo + lane] = zs;
+            for (int i = 0; i < 16; ++i) pz[i] = my_w3 * r2[i];
+            const float zs = colsum16(pz, lane);
+            if ((lane & 1) == 0) s.zp[q * TC_TP + c0 + (lane >> 1)] = zs;
         }
         __syncthreads();
         if (tid < TC_TP) {
@@ -452,27 +455,19 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
             s.gbar[n] = g;
             acc_db3 += g;
         }
-        if (!want_bwd) {
-            __syncthreads();      // s.zp / s.skip are rewritten by the next tile
-            continue;
-        }
         __syncthreads();
+        if (!want_bwd) continue;
+        if (cols_on) {
+            float v[16];
 #pragma unroll
-        for (int half = 0; half < 2; ++half) {
-            const int c0 = c_lo + 16 * half;
-            if (c0 < c_hi) {
-                float v[16];
-#pragma unroll
-                for (int i = 0; i < 16; ++i) {
-                    const float gb = s.gbar[c0 + i];
-                    const float rr = r2[16 * half + i];
-                    acc_dw3 = fmaf(gb, rr, acc_dw3);
-                    const float g = rr > 0.f ? gb * my_w3 : 0.f;
-                    acc_db2 += g;
-                    v[i] = g;
-                }
-                if (row < KH) store_row16(s.rh, s.rl, row, c0, v, 1024);
+            for (int i = 0; i < 16; ++i) {
+                const float gb = s.gbar[c0 + i];
+                acc_dw3 = fmaf(gb, r2[i], acc_dw3);
+                const float g = r2[i] > 0.f ? gb * my_w3 : 0.f;
+                acc_db2 += g;
+                v[i] = g;
             }
+            if (row < KH) store_row16(s.rh, s.rl, row, c0, v, 1024);
         }
         fence_proxy_async();
         fence_before_sync();
@@ -502,7 +497,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
         mbar_wait(bar_mma, ph_mma);
         ph_mma ^= 1;
         fence_after_sync();
-        for (int c0 = c_lo; c0 < c_hi; c0 += 16) {
+        if (cols_on) {
             float v[16];
             tmem_ld16(tm_lane + TM_WORK + c0, v);
             if (row < H) {
@@ -545,21 +540,19 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
         mbar_wait(bar_mma, ph_mma);
         ph_mma ^= 1;
         fence_after_sync();
-#pragma unroll
-        for (int mb = 0; mb < 2; ++mb) {
-            if (mb >= t.MB) break;
+#pragma unroll 1
+        for (int mb = 0; mb < t.MB; ++mb) {
             const int f = 128 * mb + row;
             const int pf = min(128, K1 - 128 * mb);              // features of this block that are MMA rows
             float ew0 = 0.f, ew1 = 0.f, eaf = 0.f;
             if (f < F) { ew0 = s.enc_w[2 * f]; ew1 = s.enc_w[2 * f + 1]; }
             else if (f < FIN) eaf = s.ang_f[f - F];
-            float gq[32];
-            uint4 ehi[4], elo[4];
-#pragma unroll
-            for (int half = 0; half < 2; ++half) {
-                const int c0 = c_lo + 16 * half;
+            float ta = 0.f, tb = 0.f, tc = 0.f;
+            float gq[16];
+            uint4 ehi[2], elo[2];
+            {
                 float ev[16];
-                if (c0 < c_hi) {
+                if (cols_on) {
                     float v[16];
                     tmem_ld16(tm_lane + TM_WORK + 64 * mb + c0, v);
 #pragma unroll
@@ -569,47 +562,49 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
                         encode_feature(s, t, d.use_cos, f, s.u0[n], s.u1[n], s.th[n], &e, &de);
                         const float gp = f < FIN ? v[i] * de : 0.f;      // rows >= f_in of the M block hold garbage
                         ev[i] = e;
-                        gq[16 * half + i] = gp;
+                        gq[i] = gp;
                         if (f < F) {
-                            acc_fa[mb] = fmaf(gp, s.u0[n], acc_fa[mb]);
-                            acc_fb[mb] = fmaf(gp, s.u1[n], acc_fb[mb]);
-                            acc_fc[mb] += gp;
+                            ta = fmaf(gp, s.u0[n], ta);
+                            tb = fmaf(gp, s.u1[n], tb);
+                            tc += gp;
                         } else if (f < FIN) {
-                            acc_fa[mb] = fmaf(gp, eaf, acc_fa[mb]);                          // d ang_b
-                            acc_fb[mb] = fmaf(gp, s.th[n] + s.ang_b[f - F], acc_fb[mb]);     // d ang_f (trained)
+                            ta = fmaf(gp, eaf, ta);                            // d ang_b
+                            tb = fmaf(gp, s.th[n] + s.ang_b[f - F], tb);       // d ang_f (trained)
                         }
                     }
                 } else {
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) { ev[i] = 0.f; gq[16 * half + i] = 0.f; }
+                    for (int i = 0; i < 16; ++i) { ev[i] = 0.f; gq[i] = 0.f; }
                 }
-                split8(ev, ehi[2 * half], elo[2 * half]);
-                split8(ev + 8, ehi[2 * half + 1], elo[2 * half + 1]);
+                split8(ev, ehi[0], elo[0]);
+                split8(ev + 8, ehi[1], elo[1]);
             }
+            if (mb == 0) { fa0 += ta; fb0 += tb; fc0 += tc; }
+            else { fa1 += ta; fb1 += tb; fc1 += tc; }
             if (want_gx) {
                 // gx[n] = (sum_f gp[f,n] * We[f,c]) / sigma ; g_theta[n] = sum_k gp[k,n] * f_k   (reduce over lanes)
-                float c0v[32], c1v[32], c2v[32];
+                float cv[16];
+                float *dst = s.gx + ((size_t)q * TC_TP + c0 + (lane >> 1)) * 3;
 #pragma unroll
-                for (int i = 0; i < 32; ++i) { c0v[i] = gq[i] * ew0; c1v[i] = gq[i] * ew1; c2v[i] = gq[i] * eaf; }
-                const float s0 = colsum32(c0v, lane), s1 = colsum32(c1v, lane), s2 = colsum32(c2v, lane);
-                float *dst = s.gx + ((size_t)q * TC_TP + c_lo + lane) * 3;
-                if (mb == 0) { dst[0] = s0; dst[1] = s1; dst[2] = s2; }
-                else { dst[0] += s0; dst[1] += s1; dst[2] += s2; }
+                for (int c = 0; c < 3; ++c) {
+                    const float wgt = c == 0 ? ew0 : c == 1 ? ew1 : eaf;
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) cv[i] = gq[i] * wgt;
+                    const float sum = colsum16(cv, lane);
+                    if ((lane & 1) == 0) dst[c] = mb == 0 ? sum : dst[c] + sum;
+                }
             }
             if (want_wgrad) {
                 if (mb > 0) {                       // wgrad1 of the previous block still reads the scratch region
                     mbar_wait(bar_aux, ph_aux);
                     ph_aux ^= 1;
                 }
-                if (row < pf) {
+                if (row < pf && cols_on) {
 #pragma unroll
-                    for (int o = 0; o < 4; ++o) {
-                        const int c0 = c_lo + 8 * o;
-                        if (c0 < c_hi) {
-                            const int off = (c0 >> 3) * 2048 + (row >> 3) * 128 + (row & 7) * 16;
-                            *reinterpret_cast<uint4 *>(s.rh + off) = ehi[o];
-                            *reinterpret_cast<uint4 *>(s.rl + off) = elo[o];
-                        }
+                    for (int o = 0; o < 2; ++o) {
+                        const int off = ((c0 >> 3) + o) * 2048 + (row >> 3) * 128 + (row & 7) * 16;
+                        *reinterpret_cast<uint4 *>(s.rh + off) = ehi[o];
+                        *reinterpret_cast<uint4 *>(s.rl + off) = elo[o];
                     }
                 }
                 fence_proxy_async();
@@ -650,128 +645,148 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
         __syncthreads();           // TMEM work columns and s.* scratch are reused by the next tile
     }
 
-    // ---- weight gradients: drain the TMEM accumulators once per problem ----
+    // ---- weight gradients: TMEM accumulators -> shared memory in blob order -> coalesced Adam / gradient store ----
     if (want_wgrad) {
         if (pending_aux) {
             mbar_wait(bar_aux, ph_aux);
             ph_aux ^= 1;
         }
         fence_after_sync();
-        const size_t po = (size_t)p * L.n_params;
-        const bool adam = a.adam_w != nullptr;
-        float step_size = 0.f, bc2_sqrt = 1.f;
-        if (adam) { step_size = a.sp->onf_step_size; bc2_sqrt = a.sp->onf_bc2_sqrt; }
-        // one parameter: plain gradient store, or torch.optim.Adam (_single_tensor_adam) returning the new weight
-        auto emit = [&](int idx, float g) -> float {
-            if (!adam) { a.grad_out[po + idx] = g; return 0.f; }
-            float w = a.adam_w[po + idx], m = a.adam_m[po + idx], v = a.adam_v[po + idx];
-            m = fmaf(a.w1, g - m, m);
-            v = fmaf(a.w2 * g, g, v * a.beta2);
-            const float denom = sqrtf(v) / bc2_sqrt + a.eps;
-            w = fmaf(-step_size, m / denom, w);
-            a.adam_w[po + idx] = w; a.adam_m[po + idx] = m; a.adam_v[po + idx] = v;
-            return w;
-        };
-        // 16 consecutive parameters of one row (float4 traffic), returns new weights in g[] (Adam mode)
-        auto emit16 = [&](int idx0, int valid, float *g) {
-#pragma unroll
-            for (int c4 = 0; c4 < 4; ++c4) {
-                if (4 * c4 >= valid) { g[4 * c4] = g[4 * c4 + 1] = g[4 * c4 + 2] = g[4 * c4 + 3] = 0.f; continue; }
-                const size_t o = po + idx0 + 4 * c4;
-                if (!adam) {
-                    *reinterpret_cast<float4 *>(a.grad_out + o) = make_float4(g[4 * c4], g[4 * c4 + 1], g[4 * c4 + 2], g[4 * c4 + 3]);
-                    continue;
-                }
-                const float4 w4 = *reinterpret_cast<const float4 *>(a.adam_w + o), m4 = *reinterpret_cast<const float4 *>(a.adam_m + o),
-                             v4 = *reinterpret_cast<const float4 *>(a.adam_v + o);
-                float wv[4] = {w4.x, w4.y, w4.z, w4.w}, mv[4] = {m4.x, m4.y, m4.z, m4.w}, vv[4] = {v4.x, v4.y, v4.z, v4.w};
-#pragma unroll
-                for (int c = 0; c < 4; ++c) {
-                    const float gg = g[4 * c4 + c];
-                    mv[c] = fmaf(a.w1, gg - mv[c], mv[c]);
-                    vv[c] = fmaf(a.w2 * gg, gg, vv[c] * a.beta2);
-                    const float denom = sqrtf(vv[c]) / bc2_sqrt + a.eps;
-                    wv[c] = fmaf(-step_size, mv[c] / denom, wv[c]);
-                    g[4 * c4 + c] = wv[c];
-                }
-                *reinterpret_cast<float4 *>(a.adam_w + o) = make_float4(wv[0], wv[1], wv[2], wv[3]);
-                *reinterpret_cast<float4 *>(a.adam_m + o) = make_float4(mv[0], mv[1], mv[2], mv[3]);
-                *reinterpret_cast<float4 *>(a.adam_v + o) = make_float4(vv[0], vv[1], vv[2], vv[3]);
-            }
-        };
-        unsigned char *pk = adam ? a.packed_out + (size_t)p * t.packed_bytes : nullptr;
-        // dW1: rows j < H -> mlp.0.weight[j,:], row H -> mlp2.0.weight[0, H:]
-        for (int ch = hcol; ch < K1 / 16; ch += 2) {
+        // every MMA has completed: the operand buffers are dead, shared memory [0, n_params) floats now holds the
+        // gradient of the whole parameter blob (same element order as the fp32 weights)
+        float *G = reinterpret_cast<float *>(smem_raw);
+        float *red = G + ((L.n_params + 31) & ~31);                    // [10][4][128] partial per-unit sums
+        const int np4 = L.n_params / 4;
+        for (int i = tid; i < np4; i += TC_THREADS) reinterpret_cast<float4 *>(G)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        {
+            float *r0 = red + cq * 128 + row;
+            r0[0 * 512] = acc_db1; r0[1 * 512] = acc_db2; r0[2 * 512] = acc_dw3;
+            r0[3 * 512] = fa0; r0[4 * 512] = fb0; r0[5 * 512] = fc0;
+            r0[6 * 512] = fa1; r0[7 * 512] = fb1; r0[8 * 512] = fc1;
+            if (tid < TC_TP) red[9 * 512 + tid] = acc_db3;
+        }
+        __syncthreads();
+        // dW1: rows j < H -> mlp.0.weight[j,:], row H -> mlp2.0.weight[0, H:];  dW2: rows i < H -> mlp.2.weight[i,:]
+        for (int ch = cq; ch < K1 / 16; ch += 4) {
             float g[16];
             tmem_ld16(tm_lane + TM_DW1 + 16 * ch, g);
             if (row <= H) {
-                const int base = row < H ? L.off_w[0] + row * FIN : L.off_w_out + H;
-                emit16(base + 16 * ch, FIN - 16 * ch, g);
-                if (adam) {
-                    uint4 h0, l0, h1, l1;
-                    split8(g, h0, l0);
-                    split8(g + 8, h1, l1);
-                    const int off = (2 * ch) * t.S_colW + (row >> 3) * 128 + (row & 7) * 16;
-                    *reinterpret_cast<uint4 *>(pk + off) = h0;
-                    *reinterpret_cast<uint4 *>(pk + off + t.S_colW) = h1;
-                    *reinterpret_cast<uint4 *>(pk + t.w1_half + off) = l0;
-                    *reinterpret_cast<uint4 *>(pk + t.w1_half + off + t.S_colW) = l1;
-                }
+                float *dst = G + (row < H ? L.off_w[0] + row * FIN : L.off_w_out + H) + 16 * ch;
+#pragma unroll
+                for (int c4 = 0; c4 < 4; ++c4)
+                    if (16 * ch + 4 * c4 < FIN)
+                        *reinterpret_cast<float4 *>(dst + 4 * c4) = make_float4(g[4 * c4], g[4 * c4 + 1], g[4 * c4 + 2], g[4 * c4 + 3]);
             }
         }
-        // dW2: rows i < H -> mlp.2.weight[i,:]
-        for (int ch = hcol; ch < KH / 16; ch += 2) {
+        for (int ch = cq; ch < KH / 16; ch += 4) {
             float g[16];
             tmem_ld16(tm_lane + TM_DW2 + 16 * ch, g);
             if (row < H) {
-                emit16(L.off_w[1] + row * H + 16 * ch, H - 16 * ch, g);
-                if (adam) {
-                    uint4 h0, l0, h1, l1;
-                    split8(g, h0, l0);
-                    split8(g + 8, h1, l1);
-                    unsigned char *pk2 = pk + 2 * t.w1_half;
-                    const int off = (2 * ch) * t.S_colW + (row >> 3) * 128 + (row & 7) * 16;
-                    *reinterpret_cast<uint4 *>(pk2 + off) = h0;
-                    *reinterpret_cast<uint4 *>(pk2 + off + t.S_colW) = h1;
-                    *reinterpret_cast<uint4 *>(pk2 + t.w2_half + off) = l0;
-                    *reinterpret_cast<uint4 *>(pk2 + t.w2_half + off + t.S_colW) = l1;
-                }
+                float *dst = G + L.off_w[1] + row * H + 16 * ch;
+#pragma unroll
+                for (int c4 = 0; c4 < 4; ++c4)
+                    if (16 * ch + 4 * c4 < H)
+                        *reinterpret_cast<float4 *>(dst + 4 * c4) = make_float4(g[4 * c4], g[4 * c4 + 1], g[4 * c4 + 2], g[4 * c4 + 3]);
             }
         }
-        // per-unit / per-feature vectors: combine the two column halves through shared memory (scratch region)
-        __syncthreads();
-        float *red = reinterpret_cast<float *>(s.rh);          // [9][2][128] + [64]
-        {
-            float *r0 = red + hcol * 128 + row;
-            r0[0 * 256] = acc_db1; r0[1 * 256] = acc_db2; r0[2 * 256] = acc_dw3;
-            r0[3 * 256] = acc_fa[0]; r0[4 * 256] = acc_fb[0]; r0[5 * 256] = acc_fc[0];
-            r0[6 * 256] = acc_fa[1]; r0[7 * 256] = acc_fb[1]; r0[8 * 256] = acc_fc[1];
-            if (tid < TC_TP) red[9 * 256 + tid] = acc_db3;
-        }
-        __syncthreads();
         if (tid < 128) {
-            auto tot = [&](int qn) { return red[qn * 256 + tid] + red[qn * 256 + 128 + tid]; };
+            auto tot = [&](int qn) {
+                const float *r = red + qn * 512 + tid;
+                return (r[0] + r[128]) + (r[256] + r[384]);
+            };
             if (tid < H) {
-                emit(L.off_b[0] + tid, tot(0));
-                emit(L.off_b[1] + tid, tot(1));
-                emit(L.off_w_out + tid, tot(2));
+                G[L.off_b[0] + tid] = tot(0);
+                G[L.off_b[1] + tid] = tot(1);
+                G[L.off_w_out + tid] = tot(2);
             }
             for (int mb = 0; mb < t.MB; ++mb) {
                 const int f = 128 * mb + tid;
                 const float ga = tot(3 + 3 * mb), gb = tot(4 + 3 * mb), gc = tot(5 + 3 * mb);
                 if (f < F) {
-                    emit(L.off_enc_w + 2 * f, ga);
-                    emit(L.off_enc_w + 2 * f + 1, gb);
-                    emit(L.off_enc_b + f, d.bias ? gc : 0.f);
+                    G[L.off_enc_w + 2 * f] = ga;
+                    G[L.off_enc_w + 2 * f + 1] = gb;
+                    G[L.off_enc_b + f] = d.bias ? gc : 0.f;
                 } else if (f < FIN) {
-                    emit(L.off_ang_b + f - F, ga);
-                    emit(L.off_ang_f + f - F, gb);
+                    G[L.off_ang_b + f - F] = ga;
+                    G[L.off_ang_f + f - F] = gb;
                 }
             }
             if (tid == 0) {
                 float g3 = 0.f;
-                for (int i = 0; i < TC_TP; ++i) g3 += red[9 * 256 + i];
-                emit(L.off_b_out, g3);
+                for (int i = 0; i < TC_TP; ++i) g3 += red[9 * 512 + i];
+                G[L.off_b_out] = g3;
+            }
+        }
+        __syncthreads();
+        const size_t po = (size_t)p * L.n_params;
+        if (a.adam_w == nullptr) {
+            float4 *dst = reinterpret_cast<float4 *>(a.grad_out + po);
+            for (int i = tid; i < np4; i += TC_THREADS) dst[i] = reinterpret_cast<const float4 *>(G)[i];
+        } else {
+            // torch.optim.Adam (_single_tensor_adam) over the whole blob, fully coalesced; the new weights replace the
+            // gradient in shared memory and are re-split into the bf16 operand copy below
+            const float step_size = a.sp->onf_step_size, inv_bc2 = 1.f / a.sp->onf_bc2_sqrt;
+            float4 *w4 = reinterpret_cast<float4 *>(a.adam_w + po), *m4 = reinterpret_cast<float4 *>(a.adam_m + po),
+                   *v4 = reinterpret_cast<float4 *>(a.adam_v + po);
+            constexpr int U = 4;
+            for (int i0 = tid; i0 < np4; i0 += U * TC_THREADS) {
+                float4 wv[U], mv[U], vv[U];
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    const int i = i0 + u * TC_THREADS;
+                    if (i < np4) { wv[u] = w4[i]; mv[u] = m4[i]; vv[u] = v4[i]; }
+                }
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    const int i = i0 + u * TC_THREADS;
+                    if (i >= np4) continue;
+                    const float4 g4 = reinterpret_cast<const float4 *>(G)[i];
+                    float gg[4] = {g4.x, g4.y, g4.z, g4.w}, ww[4] = {wv[u].x, wv[u].y, wv[u].z, wv[u].w},
+                          mm[4] = {mv[u].x, mv[u].y, mv[u].z, mv[u].w}, v2[4] = {vv[u].x, vv[u].y, vv[u].z, vv[u].w};
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        mm[c] = fmaf(a.w1, gg[c] - mm[c], mm[c]);
+                        v2[c] = fmaf(a.w2 * gg[c], gg[c], v2[c] * a.beta2);
+                        const float denom = fmaf(sqrtf(v2[c]), inv_bc2, a.eps);
+                        ww[c] = fmaf(-step_size, __fdividef(mm[c], denom), ww[c]);
+                    }
+                    w4[i] = make_float4(ww[0], ww[1], ww[2], ww[3]);
+                    m4[i] = make_float4(mm[0], mm[1], mm[2], mm[3]);
+                    v4[i] = make_float4(v2[0], v2[1], v2[2], v2[3]);
+                    reinterpret_cast<float4 *>(G)[i] = make_float4(ww[0], ww[1], ww[2], ww[3]);
+                }
+            }
+            __syncthreads();
+            // refresh the packed operand copy: item = (matrix, column octet, row) -> 16 B of hi + 16 B of lo
+            unsigned char *pk = a.packed_out + (size_t)p * t.packed_bytes;
+            const int rows = KH, n1 = (K1 / 8) * rows, n2 = (KH / 8) * rows;
+            for (int item = tid; item < n1 + n2; item += TC_THREADS) {
+                const bool second = item >= n1;
+                const int it = second ? item - n1 : item;
+                const int oct = it / rows, r = it - oct * rows;
+                const int kdim = second ? H : FIN;
+                float v[8];
+                const float *src = nullptr;
+                if (!second) {
+                    if (r < H) src = G + L.off_w[0] + r * FIN;
+                    else if (r == H) src = G + L.off_w_out + H;
+                } else if (r < H) {
+                    src = G + L.off_w[1] + r * H;
+                }
+#pragma unroll
+                for (int h4 = 0; h4 < 2; ++h4) {
+                    const int c = oct * 8 + 4 * h4;
+                    float4 x4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (src && c < kdim) x4 = *reinterpret_cast<const float4 *>(src + c);
+                    v[4 * h4] = x4.x; v[4 * h4 + 1] = x4.y; v[4 * h4 + 2] = x4.z; v[4 * h4 + 3] = x4.w;
+                }
+                uint4 hi, lo;
+                split8(v, hi, lo);
+                unsigned char *base = pk + (second ? 2 * t.w1_half : 0);
+                const int half = second ? t.w2_half : t.w1_half;
+                const int off = oct * t.S_colW + (r >> 3) * 128 + (r & 7) * 16;
+                *reinterpret_cast<uint4 *>(base + off) = hi;
+                *reinterpret_cast<uint4 *>(base + half + off) = lo;
             }
         }
     }
@@ -779,6 +794,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
     __syncthreads();
     if (warp == 1) tmem_dealloc(tmem, 512);
 }
+
 
 // ---- host side ---------------------------------------------------------------------------------------------
 bool onf_tc_supported(const OnfDims &d) {
