@@ -61,7 +61,7 @@ __host__ __device__ inline bool tc_make_dims(const OnfDims &d, TcDims *out) {
     t.off_h1 = t.off_w2 + 2 * t.w2_half;
     t.off_r = t.off_h1 + 2 * t.h1_half;
     t.off_misc = t.off_r + TC_REGION;
-    int misc_floats = 3 * t.F + 2 * t.A + 3 * t.H + 4 /*b3 + pad*/ + 5 * TC_TP + 4 * TC_TP + 4 * TC_TP * 3;
+    int misc_floats = 3 * t.K1 + (t.A + 3) / 4 * 4 + 3 * t.H + 4 /*b3 + pad*/ + 5 * TC_TP + 4 * TC_TP + 4 * TC_TP * 3;
     t.smem_bytes = t.off_misc + misc_floats * 4 + 64;
     t.packed_bytes = 2 * t.w1_half + 2 * t.w2_half;
     *out = t;
@@ -139,15 +139,6 @@ __global__ void __launch_bounds__(256) onf_tc_pack_kernel(const TcPackArgs a) {
 }
 
 // ---- device helpers ------------------------------------------------------------------------------------
-__device__ __forceinline__ void fast_sincos(float x, float *s, float *c) {
-    // Cody-Waite reduction to [-pi, pi] then MUFU: abs error ~5e-7 (outputs are in [-1,1])
-    const float k = rintf(x * 0.15915494309189535f);
-    float r = fmaf(k, -6.2831854820251465f, x);
-    r = fmaf(k, 1.7484555e-7f, r);
-    *s = __sinf(r);
-    *c = __cosf(r);
-}
-
 // column sums over the 32 lanes of a warp for 16 columns: every lane returns sum_lanes v[lane >> 1]  (16 shuffles)
 __device__ __forceinline__ float colsum16(float (&v)[16], int lane) {
 #pragma unroll
@@ -166,7 +157,9 @@ __device__ __forceinline__ float colsum16(float (&v)[16], int lane) {
 
 struct TcSmem {
     unsigned char *w1h, *w1l, *w2h, *w2l, *h1h, *h1l, *rh, *rl;
-    float *enc_w, *enc_b, *ang_b, *ang_f, *b1, *b2, *w3h, *b3;
+    // per input feature f < K1: arg = x1 * pb + u0 * pa + pc  (x1 = u1 for Fourier features, theta for heading features;
+    // pc carries the bias and +pi/2 for cosine features, so every feature is sin(arg) with derivative cos(arg))
+    float *pa, *pb, *pc, *ang_b, *b1, *b2, *w3h, *b3;
     float *u0, *u1, *th, *skip, *gbar, *zp, *gx;
     uint64_t *bars;
     uint32_t *tmem_slot;
@@ -176,10 +169,10 @@ struct TcSmem {
         h1h = base + t.off_h1; h1l = h1h + t.h1_half;
         rh = base + t.off_r; rl = rh + TC_REGION / 2;
         float *f = reinterpret_cast<float *>(base + t.off_misc);
-        enc_w = f; f += 2 * t.F;
-        enc_b = f; f += t.F;
-        ang_b = f; f += t.A;
-        ang_f = f; f += t.A;
+        pa = f; f += t.K1;
+        pb = f; f += t.K1;
+        pc = f; f += t.K1;
+        ang_b = f; f += (t.A + 3) / 4 * 4;
         b1 = f; f += t.H;
         b2 = f; f += t.H;
         w3h = f; f += t.H;
@@ -196,26 +189,15 @@ struct TcSmem {
     }
 };
 
-// one encoded feature and its derivative w.r.t. the sin/cos argument (onf_model.py:39-46, angle_encoder.py:15-18)
-__device__ __forceinline__ void encode_feature(const TcSmem &s, const TcDims &t, int use_cos, int f, float u0, float u1,
-                                               float th, float *e, float *de) {
-    float arg;
-    bool cosine;
-    if (f < t.F) {
-        arg = fmaf(u1, s.enc_w[2 * f + 1], fmaf(u0, s.enc_w[2 * f], s.enc_b[f]));
-        cosine = use_cos && f >= 100;
-    } else if (f < t.FIN) {
-        const int k = f - t.F;
-        arg = (th + s.ang_b[k]) * s.ang_f[k];
-        cosine = k >= t.A / 2;
-    } else {
-        *e = 0.f; *de = 0.f;
-        return;
-    }
-    float sn, cs;
-    fast_sincos(arg, &sn, &cs);
-    *e = cosine ? cs : sn;
-    *de = cosine ? -sn : cs;
+// sin and cos of the feature argument (onf_model.py:39-46, angle_encoder.py:15-18 with the phase folded into pc)
+__device__ __forceinline__ float feature_arg(float pa, float pb, float pc, float u0, float x1) {
+    return fmaf(x1, pb, fmaf(u0, pa, pc));
+}
+__device__ __forceinline__ float reduce_2pi(float x) {
+    // Cody-Waite reduction to [-pi, pi]; the MUFU sin/cos that follow have abs error ~5e-7 there
+    const float k = rintf(x * 0.15915494309189535f);
+    float r = fmaf(k, -6.2831854820251465f, x);
+    return fmaf(k, 1.7484555e-7f, r);
 }
 
 // store 16 consecutive columns (col0 .. col0+15) of row `row` into a [row/8][col/8][row%8][col%8] operand buffer
@@ -233,10 +215,10 @@ __device__ __forceinline__ void store_row16(unsigned char *hi_buf, unsigned char
 
 // three-pass split product: D (+)= Ahi*Bhi + Alo*Bhi + Ahi*Blo
 __device__ __forceinline__ void mma3(uint32_t tmem_d, uint64_t ah, uint64_t al, uint64_t bh, uint64_t bl, uint32_t idesc,
-                                     bool accumulate) {
-    mma_bf16(tmem_d, ah, bh, idesc, accumulate ? 1u : 0u);
-    mma_bf16(tmem_d, al, bh, idesc, 1u);
-    mma_bf16(tmem_d, ah, bl, idesc, 1u);
+                                     bool accumulate, uint32_t issue) {
+    mma_bf16(tmem_d, ah, bh, idesc, accumulate ? 1u : 0u, issue);
+    mma_bf16(tmem_d, al, bh, idesc, 1u, issue);
+    mma_bf16(tmem_d, ah, bl, idesc, 1u, issue);
 }
 
 // Thread layout: 16 warps.  warp = 4*cq + q: q = TMEM lane quarter (rows 32q..32q+31), cq = column quarter of the
@@ -276,11 +258,20 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
         bulk_g2s(s.w1h, src, 2 * t.w1_half, bar_w);
         bulk_g2s(s.w2h, src + 2 * t.w1_half, 2 * t.w2_half, bar_w);
     }
-    for (int i = tid; i < 2 * F; i += TC_THREADS) s.enc_w[i] = W[L.off_enc_w + i];
-    for (int i = tid; i < F; i += TC_THREADS) s.enc_b[i] = W[L.off_enc_b + i];
-    for (int i = tid; i < t.A; i += TC_THREADS) {
-        s.ang_b[i] = W[L.off_ang_b + i];
-        s.ang_f[i] = W[L.off_ang_f + i];
+    for (int f = tid; f < K1; f += TC_THREADS) {
+        float pa = 0.f, pb = 0.f, pc = 0.f;
+        if (f < F) {
+            pa = W[L.off_enc_w + 2 * f];
+            pb = W[L.off_enc_w + 2 * f + 1];
+            pc = W[L.off_enc_b + f] + ((d.use_cos && f >= 100) ? 1.57079632679489662f : 0.f);
+        } else if (f < FIN) {
+            const int k = f - F;
+            const float b = W[L.off_ang_b + k], fr = W[L.off_ang_f + k];
+            s.ang_b[k] = b;
+            pb = fr;
+            pc = fmaf(b, fr, k >= t.A / 2 ? 1.57079632679489662f : 0.f);
+        }
+        s.pa[f] = pa; s.pb[f] = pb; s.pc[f] = pc;
     }
     for (int i = tid; i < H; i += TC_THREADS) {
         s.b1[i] = W[L.off_b[0] + i];
@@ -293,7 +284,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
     fence_after_sync();
     const uint32_t tmem = *s.tmem_slot;
     const uint32_t tm_lane = tmem + ((uint32_t)(q * 32) << 16);
-    if (tid == 0) mbar_wait(bar_w, 0);     // the MMA-issuing thread observes the bulk copies
+    if (warp == 0) mbar_wait(bar_w, 0);    // the MMA-issuing warp observes the bulk copies
 
     uint32_t ph_mma = 0, ph_aux = 0;
     bool pending_aux = false;
@@ -334,11 +325,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
                     const int f0 = 128 * g + 8 * (oc + 8 * it);
                     float e[8];
                     if (f0 < K1 && n < Nt) {
+                        float pa[8], pb[8], pc[8];
+                        *reinterpret_cast<float4 *>(pa) = *reinterpret_cast<const float4 *>(s.pa + f0);
+                        *reinterpret_cast<float4 *>(pa + 4) = *reinterpret_cast<const float4 *>(s.pa + f0 + 4);
+                        *reinterpret_cast<float4 *>(pb) = *reinterpret_cast<const float4 *>(s.pb + f0);
+                        *reinterpret_cast<float4 *>(pb + 4) = *reinterpret_cast<const float4 *>(s.pb + f0 + 4);
+                        *reinterpret_cast<float4 *>(pc) = *reinterpret_cast<const float4 *>(s.pc + f0);
+                        *reinterpret_cast<float4 *>(pc + 4) = *reinterpret_cast<const float4 *>(s.pc + f0 + 4);
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            float de;
-                            encode_feature(s, t, d.use_cos, f0 + i, u0, u1, th, &e[i], &de);
-                        }
+                        for (int i = 0; i < 8; ++i)
+                            e[i] = __sinf(reduce_2pi(feature_arg(pa[i], pb[i], pc[i], u0, f0 + i < F ? u1 : th)));
                     } else {
 #pragma unroll
                         for (int i = 0; i < 8; ++i) e[i] = 0.f;
@@ -361,18 +357,19 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
                 fence_proxy_async();
                 fence_before_sync();
                 __syncthreads();
-                if (tid == 0) {
+                if (warp == 0) {                 // warp-uniform: descriptor arithmetic stays on the uniform datapath
                     fence_after_sync();
+                    const uint32_t lead = elect_one();
                     const uint32_t idesc = instr_desc_bf16(128, Nt, 0, 0);
                     const int ks_n = min(8, (K1 - 128 * g) / 16);
                     for (int ks = 0; ks < ks_n; ++ks) {
                         const uint32_t aoff = (uint32_t)(16 * g + 2 * ks) * t.S_colW, boff = (uint32_t)(2 * ks) * 1024;
                         mma3(tmem + TM_WORK, desc_kmajor(smem_u32(s.w1h) + aoff, 128, t.S_colW),
                              desc_kmajor(smem_u32(s.w1l) + aoff, 128, t.S_colW), desc_kmajor(smem_u32(s.rh) + boff, 128, 1024),
-                             desc_kmajor(smem_u32(s.rl) + boff, 128, 1024), idesc, g > 0 || ks > 0);
+                             desc_kmajor(smem_u32(s.rl) + boff, 128, 1024), idesc, g > 0 || ks > 0, lead);
                     }
-                    if (g + 1 < t.MB) mma_commit(bar_aux);
-                    else mma_commit(bar_mma);
+                    if (g + 1 < t.MB) mma_commit(bar_aux, lead);
+                    else mma_commit(bar_mma, lead);
                 }
             }
         }
@@ -400,16 +397,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
         fence_before_sync();
         __syncthreads();
         // ---- P3: fwd2 ----
-        if (tid == 0) {
+        if (warp == 0) {                 // warp-uniform: descriptor arithmetic stays on the uniform datapath
             fence_after_sync();
+            const uint32_t lead = elect_one();
             const uint32_t idesc = instr_desc_bf16(128, Nt, 0, 1);
             for (int ks = 0; ks < KH / 16; ++ks) {
                 const uint32_t aoff = (uint32_t)(2 * ks) * t.S_colW, boff = (uint32_t)(2 * ks) * 1024;
                 mma3(tmem + TM_WORK + 64, desc_kmajor(smem_u32(s.w2h) + aoff, 128, t.S_colW),
                      desc_kmajor(smem_u32(s.w2l) + aoff, 128, t.S_colW), desc_mnmajor(smem_u32(s.h1h) + boff, 1024, 128),
-                     desc_mnmajor(smem_u32(s.h1l) + boff, 1024, 128), idesc, ks > 0);
+                     desc_mnmajor(smem_u32(s.h1l) + boff, 1024, 128), idesc, ks > 0, lead);
             }
-            mma_commit(bar_mma);
+            mma_commit(bar_mma, lead);
         }
         // ---- P4: epilogue 2: logit, dL/dz, gH2 operand ----
         mbar_wait(bar_mma, ph_mma);
@@ -473,15 +471,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
         fence_before_sync();
         __syncthreads();
         // ---- P5: wgrad2 (persistent accumulator) + dgrad2 ----
-        if (tid == 0) {
+        if (warp == 0) {                 // warp-uniform: descriptor arithmetic stays on the uniform datapath
             fence_after_sync();
+            const uint32_t lead = elect_one();
             if (want_wgrad) {
                 const uint32_t idesc = instr_desc_bf16(128, KH, 0, 0);
                 for (int ks = 0; ks < Nt / 16; ++ks) {
                     const uint32_t off = (uint32_t)(2 * ks) * 128;
                     mma3(tmem + TM_DW2, desc_kmajor(smem_u32(s.rh) + off, 1024, 128), desc_kmajor(smem_u32(s.rl) + off, 1024, 128),
                          desc_kmajor(smem_u32(s.h1h) + off, 1024, 128), desc_kmajor(smem_u32(s.h1l) + off, 1024, 128), idesc,
-                         tile > 0 || ks > 0);
+                         tile > 0 || ks > 0, lead);
                 }
             }
             const uint32_t idesc = instr_desc_bf16(128, Nt, 1, 1);
@@ -489,9 +488,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
                 const uint32_t aoff = (uint32_t)(2 * ks) * 128, boff = (uint32_t)(2 * ks) * 1024;
                 mma3(tmem + TM_WORK, desc_mnmajor(smem_u32(s.w2h) + aoff, 128, t.S_colW),
                      desc_mnmajor(smem_u32(s.w2l) + aoff, 128, t.S_colW), desc_mnmajor(smem_u32(s.rh) + boff, 1024, 128),
-                     desc_mnmajor(smem_u32(s.rl) + boff, 1024, 128), idesc, ks > 0);
+                     desc_mnmajor(smem_u32(s.rl) + boff, 1024, 128), idesc, ks > 0, lead);
             }
-            mma_commit(bar_mma);
+            mma_commit(bar_mma, lead);
         }
         // ---- P6: epilogue 3: ReLU mask of layer 1 -> gH1 operand (in place over H1); row H := dL/dz ----
         mbar_wait(bar_mma, ph_mma);
@@ -524,17 +523,18 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
         fence_before_sync();
         __syncthreads();
         // ---- P7: dgrad1: gE[k,n] for both feature blocks ----
-        if (tid == 0) {
+        if (warp == 0) {                 // warp-uniform: descriptor arithmetic stays on the uniform datapath
             fence_after_sync();
+            const uint32_t lead = elect_one();
             const uint32_t idesc = instr_desc_bf16(128, Nt, 1, 1);
             for (int mb = 0; mb < t.MB; ++mb)
                 for (int ks = 0; ks < KH / 16; ++ks) {
                     const uint32_t aoff = (uint32_t)(16 * mb) * t.S_colW + (uint32_t)(2 * ks) * 128, boff = (uint32_t)(2 * ks) * 1024;
                     mma3(tmem + TM_WORK + 64 * mb, desc_mnmajor(smem_u32(s.w1h) + aoff, 128, t.S_colW),
                          desc_mnmajor(smem_u32(s.w1l) + aoff, 128, t.S_colW), desc_mnmajor(smem_u32(s.h1h) + boff, 1024, 128),
-                         desc_mnmajor(smem_u32(s.h1l) + boff, 1024, 128), idesc, ks > 0);
+                         desc_mnmajor(smem_u32(s.h1l) + boff, 1024, 128), idesc, ks > 0, lead);
                 }
-            mma_commit(bar_mma);
+            mma_commit(bar_mma, lead);
         }
         // ---- P8/P9: epilogue 4: encoding backward (+ input gradient), E^T operand, wgrad1 per feature block ----
         mbar_wait(bar_mma, ph_mma);
@@ -544,33 +544,33 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
         for (int mb = 0; mb < t.MB; ++mb) {
             const int f = 128 * mb + row;
             const int pf = min(128, K1 - 128 * mb);              // features of this block that are MMA rows
-            float ew0 = 0.f, ew1 = 0.f, eaf = 0.f;
-            if (f < F) { ew0 = s.enc_w[2 * f]; ew1 = s.enc_w[2 * f + 1]; }
-            else if (f < FIN) eaf = s.ang_f[f - F];
-            float ta = 0.f, tb = 0.f, tc = 0.f;
+            const bool f_on = row < pf;                          // rows beyond hold garbage
+            const bool fourier = f < F;
+            const float ppa = f_on ? s.pa[f] : 0.f, ppb = f_on ? s.pb[f] : 0.f, ppc = f_on ? s.pc[f] : 0.f;
+            const float ew0 = fourier ? ppa : 0.f, ew1 = fourier ? ppb : 0.f, eaf = (!fourier && f < FIN) ? ppb : 0.f;
+            float ta = 0.f, tb = 0.f, tc = 0.f;                  // sum gp*u0, sum gp*x1, sum gp
             float gq[16];
             uint4 ehi[2], elo[2];
             {
                 float ev[16];
                 if (cols_on) {
-                    float v[16];
+                    float v[16], xu[16], x1[16];
                     tmem_ld16(tm_lane + TM_WORK + 64 * mb + c0, v);
+                    const float *x1src = fourier ? s.u1 : s.th;
+#pragma unroll
+                    for (int i4 = 0; i4 < 4; ++i4) {
+                        *reinterpret_cast<float4 *>(xu + 4 * i4) = *reinterpret_cast<const float4 *>(s.u0 + c0 + 4 * i4);
+                        *reinterpret_cast<float4 *>(x1 + 4 * i4) = *reinterpret_cast<const float4 *>(x1src + c0 + 4 * i4);
+                    }
 #pragma unroll
                     for (int i = 0; i < 16; ++i) {
-                        const int n = c0 + i;
-                        float e, de;
-                        encode_feature(s, t, d.use_cos, f, s.u0[n], s.u1[n], s.th[n], &e, &de);
-                        const float gp = f < FIN ? v[i] * de : 0.f;      // rows >= f_in of the M block hold garbage
-                        ev[i] = e;
+                        const float r = reduce_2pi(feature_arg(ppa, ppb, ppc, xu[i], x1[i]));
+                        const float gp = f_on ? v[i] * __cosf(r) : 0.f;
+                        ev[i] = __sinf(r);
                         gq[i] = gp;
-                        if (f < F) {
-                            ta = fmaf(gp, s.u0[n], ta);
-                            tb = fmaf(gp, s.u1[n], tb);
-                            tc += gp;
-                        } else if (f < FIN) {
-                            ta = fmaf(gp, eaf, ta);                            // d ang_b
-                            tb = fmaf(gp, s.th[n] + s.ang_b[f - F], tb);       // d ang_f (trained)
-                        }
+                        ta = fmaf(gp, xu[i], ta);
+                        tb = fmaf(gp, x1[i], tb);
+                        tc += gp;
                     }
                 } else {
 #pragma unroll
@@ -578,6 +578,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
                 }
                 split8(ev, ehi[0], elo[0]);
                 split8(ev + 8, ehi[1], elo[1]);
+            }
+            if (!fourier) {                                      // heading features: d ang_b = f_k * sum gp,
+                const float b = f < FIN ? s.ang_b[f - F] : 0.f;  // d ang_f = sum gp * (theta + b_k)  (trained)
+                tb = fmaf(b, tc, tb);
+                ta = eaf * tc;
             }
             if (mb == 0) { fa0 += ta; fb0 += tb; fc0 += tc; }
             else { fa1 += ta; fb1 += tb; fc1 += tc; }
@@ -610,16 +615,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
                 fence_proxy_async();
                 fence_before_sync();
                 __syncthreads();
-                if (tid == 0) {
+                if (warp == 0) {                 // warp-uniform: descriptor arithmetic stays on the uniform datapath
                     fence_after_sync();
+                    const uint32_t lead = elect_one();
                     const uint32_t idesc = instr_desc_bf16(128, pf, 0, 0);
                     for (int ks = 0; ks < Nt / 16; ++ks) {
                         const uint32_t aoff = (uint32_t)(2 * ks) * 128, boff = (uint32_t)(2 * ks) * 2048;
                         mma3(tmem + TM_DW1 + 128 * mb, desc_kmajor(smem_u32(s.h1h) + aoff, 1024, 128),
                              desc_kmajor(smem_u32(s.h1l) + aoff, 1024, 128), desc_kmajor(smem_u32(s.rh) + boff, 128, 2048),
-                             desc_kmajor(smem_u32(s.rl) + boff, 128, 2048), idesc, tile > 0 || ks > 0);
+                             desc_kmajor(smem_u32(s.rl) + boff, 128, 2048), idesc, tile > 0 || ks > 0, lead);
                     }
-                    mma_commit(bar_aux);
+                    mma_commit(bar_aux, lead);
                 }
                 if (mb + 1 >= t.MB) pending_aux = true;
             }
@@ -747,7 +753,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
                     for (int c = 0; c < 4; ++c) {
                         mm[c] = fmaf(a.w1, gg[c] - mm[c], mm[c]);
                         v2[c] = fmaf(a.w2 * gg[c], gg[c], v2[c] * a.beta2);
-                        const float denom = fmaf(sqrtf(v2[c]), inv_bc2, a.eps);
+                        float sq;
+                        asm("sqrt.approx.f32 %0, %1;" : "=f"(sq) : "f"(v2[c]));
+                        const float denom = fmaf(sq, inv_bc2, a.eps);
                         ww[c] = fmaf(-step_size, __fdividef(mm[c], denom), ww[c]);
                     }
                     w4[i] = make_float4(ww[0], ww[1], ww[2], ww[3]);

@@ -130,22 +130,41 @@ __host__ __device__ __forceinline__ uint32_t instr_desc_bf16(int M, int N, int a
     d |= (uint32_t)(M >> 4) << 24;
     return d;
 }
-// D[tmem] (+)= A[smem] * B[smem]; issued by ONE thread
-__device__ __forceinline__ void mma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
-                                         uint32_t accumulate) {
+// one lane of a converged warp (warp-uniform control flow around it keeps descriptor arithmetic on the uniform path)
+__device__ __forceinline__ uint32_t elect_one() {
+    uint32_t pred;
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
+        "elect.sync _|p, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(pred));
+    return pred;
+}
+// D[tmem] (+)= A[smem] * B[smem]; executed by the lanes with issue != 0 (exactly one lane must issue)
+__device__ __forceinline__ void mma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                         uint32_t accumulate, uint32_t issue = 1) {
+    asm volatile(
+        "{\n\t.reg .pred p, q;\n\t"
         "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        "setp.ne.b32 q, %5, 0;\n\t"
+        "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
         :
-        : "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(issue)
         : "memory");
 }
 // all tcgen05.mma issued so far by this thread -> one arrival on `bar` when they have completed
-__device__ __forceinline__ void mma_commit(uint64_t *bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
-                 : "memory");
+__device__ __forceinline__ void mma_commit(uint64_t *bar, uint32_t issue = 1) {
+    asm volatile(
+        "{\n\t.reg .pred q;\n\t"
+        "setp.ne.b32 q, %1, 0;\n\t"
+        "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}"
+        :
+        : "r"(smem_u32(bar)), "r"(issue)
+        : "memory");
 }
+// 1-D descriptor arithmetic: a descriptor whose start address is moved by `bytes` (no carry out of the 14-bit field
+// as long as the result stays inside the 227 KB shared-memory window)
+__device__ __forceinline__ uint64_t desc_advance(uint64_t desc, uint32_t bytes) { return desc + (uint64_t)(bytes >> 4); }
 
 // ---- fp32 -> (bf16 hi, bf16 lo) split: x ~= hi + lo with ~2^-17 relative error ------------------------
 __device__ __forceinline__ void split_bf16(float x, __nv_bfloat16 &hi, __nv_bfloat16 &lo) {
