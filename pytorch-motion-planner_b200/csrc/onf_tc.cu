@@ -1,6 +1,7 @@
 // onf_tc.cu - K2, tensor-core path: the fused ONF kernel on tcgen05 (sm_100a).
 //
-// One CTA = one planning problem (its own weights); the problem's points are walked in tiles of <= 64.  Every
+// One CTA = one planning problem (its own weights); the problem's points are walked in tiles of <= 32 by two groups
+// of 8 warps (alternating tiles) while a 17th warp issues every MMA, so one group's epilogue overlaps the other's MMAs.  Every
 // dense contraction of the forward pass (onf_model.py:33-50), of the input-gradient pass and of the
 // weight-gradient pass (what autograd does for nerf_opt_planner.py:85-90 / constrained...:85-100) is a
 // tcgen05.mma with the HIDDEN index on the UMMA M axis (128 TMEM lanes) and the POINT index on the N axis:
@@ -32,21 +33,25 @@
 namespace nfopp {
 using namespace tc05;
 
-constexpr int TC_THREADS = 512;
-constexpr int TC_TP = 64;                        // points per tile = max UMMA N used for point-indexed outputs
-constexpr int TC_REGION = 32768;                 // E ring / gH2 / E^T scratch (two 16 KB halves: hi, lo)
-constexpr uint32_t TM_DW1 = 0, TM_DW2 = 224, TM_WORK = 336;   // TMEM column map (512 columns allocated)
+constexpr int TC_WORKERS = 512;                  // 2 groups x 8 epilogue warps
+constexpr int TC_THREADS = TC_WORKERS + 32;      // + 1 MMA-issue warp
+constexpr int TC_GT = 256;                       // threads per group
+constexpr int TC_TP = 32;                        // points per tile (one group works on one tile at a time)
+constexpr int TC_RHALF = 8192;                   // scratch region half (hi or lo): E ring / gH2 / E^T for 32 points
+constexpr uint32_t TM_DW1 = 0, TM_DW2 = 224, TM_WORK = 336;   // TMEM columns; group g works in [336 + 64 g, +64)
 
 struct TcDims {
     int F, A, FIN, H, K1, KH, MB;                // MB = M blocks of dgrad1 = feature groups of 128
     int S_colW;                                  // column-octet stride of the packed weights = KH * 16 bytes
     int w1_half, w2_half, h1_half;               // bytes of one hi (or lo) buffer
-    int off_w1, off_w2, off_h1, off_r, off_misc; // shared-memory byte offsets
+    int off_w1, off_w2, off_grp, grp_bytes, off_misc;   // shared-memory byte offsets
     int smem_bytes;
     int packed_bytes;                            // per problem, global
 };
 
 __host__ __device__ inline int ru16(int x) { return (x + 15) / 16 * 16; }
+
+constexpr int TC_GRP_FLOATS = 5 * TC_TP + 4 * TC_TP + 4 * TC_TP * 3;     // u0,u1,th,skip,gbar | zp | gx
 
 __host__ __device__ inline bool tc_make_dims(const OnfDims &d, TcDims *out) {
     TcDims t{};
@@ -55,14 +60,14 @@ __host__ __device__ inline bool tc_make_dims(const OnfDims &d, TcDims *out) {
     t.S_colW = t.KH * 16;
     t.w1_half = (t.K1 / 8) * t.S_colW;
     t.w2_half = (t.KH / 8) * t.S_colW;
-    t.h1_half = (t.KH / 8) * 1024;
+    t.h1_half = (t.KH / 8) * (TC_TP / 8) * 128;
     t.off_w1 = 0;
     t.off_w2 = 2 * t.w1_half;
-    t.off_h1 = t.off_w2 + 2 * t.w2_half;
-    t.off_r = t.off_h1 + 2 * t.h1_half;
-    t.off_misc = t.off_r + TC_REGION;
-    int misc_floats = 3 * t.K1 + (t.A + 3) / 4 * 4 + 3 * t.H + 4 /*b3 + pad*/ + 5 * TC_TP + 4 * TC_TP + 4 * TC_TP * 3;
-    t.smem_bytes = t.off_misc + misc_floats * 4 + 64;
+    t.off_grp = t.off_w2 + 2 * t.w2_half;
+    t.grp_bytes = 2 * t.h1_half + 2 * TC_RHALF;
+    t.off_misc = t.off_grp + 2 * t.grp_bytes;
+    int misc_floats = 3 * t.K1 + (t.A + 3) / 4 * 4 + 3 * t.H + 4 /*b3 + pad*/ + 2 * TC_GRP_FLOATS;
+    t.smem_bytes = t.off_misc + misc_floats * 4 + 128;
     t.packed_bytes = 2 * t.w1_half + 2 * t.w2_half;
     *out = t;
     // the epilogue stages the whole gradient blob (+ 20 KB of per-unit partial sums) over the dead operand buffers
@@ -155,40 +160,6 @@ __device__ __forceinline__ float colsum16(float (&v)[16], int lane) {
     return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 1);
 }
 
-struct TcSmem {
-    unsigned char *w1h, *w1l, *w2h, *w2l, *h1h, *h1l, *rh, *rl;
-    // per input feature f < K1: arg = x1 * pb + u0 * pa + pc  (x1 = u1 for Fourier features, theta for heading features;
-    // pc carries the bias and +pi/2 for cosine features, so every feature is sin(arg) with derivative cos(arg))
-    float *pa, *pb, *pc, *ang_b, *b1, *b2, *w3h, *b3;
-    float *u0, *u1, *th, *skip, *gbar, *zp, *gx;
-    uint64_t *bars;
-    uint32_t *tmem_slot;
-    __device__ TcSmem(unsigned char *base, const TcDims &t) {
-        w1h = base + t.off_w1; w1l = w1h + t.w1_half;
-        w2h = base + t.off_w2; w2l = w2h + t.w2_half;
-        h1h = base + t.off_h1; h1l = h1h + t.h1_half;
-        rh = base + t.off_r; rl = rh + TC_REGION / 2;
-        float *f = reinterpret_cast<float *>(base + t.off_misc);
-        pa = f; f += t.K1;
-        pb = f; f += t.K1;
-        pc = f; f += t.K1;
-        ang_b = f; f += (t.A + 3) / 4 * 4;
-        b1 = f; f += t.H;
-        b2 = f; f += t.H;
-        w3h = f; f += t.H;
-        b3 = f; f += 4;
-        u0 = f; f += TC_TP;
-        u1 = f; f += TC_TP;
-        th = f; f += TC_TP;
-        skip = f; f += TC_TP;
-        gbar = f; f += TC_TP;
-        zp = f; f += 4 * TC_TP;
-        gx = f; f += 4 * TC_TP * 3;
-        bars = reinterpret_cast<uint64_t *>(f);
-        tmem_slot = reinterpret_cast<uint32_t *>(bars + 4);
-    }
-};
-
 // sin and cos of the feature argument (onf_model.py:39-46, angle_encoder.py:15-18 with the phase folded into pc)
 __device__ __forceinline__ float feature_arg(float pa, float pb, float pc, float u0, float x1) {
     return fmaf(x1, pb, fmaf(u0, pa, pc));
@@ -199,6 +170,51 @@ __device__ __forceinline__ float reduce_2pi(float x) {
     float r = fmaf(k, -6.2831854820251465f, x);
     return fmaf(k, 1.7484555e-7f, r);
 }
+
+// shared-memory views: weights and per-feature parameters are shared by the CTA, everything else is per group
+struct TcShared {
+    unsigned char *w1h, *w1l, *w2h, *w2l;
+    // per input feature f < K1: arg = x1 * pb + u0 * pa + pc  (x1 = u1 for Fourier features, theta for heading features;
+    // pc carries the bias and +pi/2 for cosine features, so every feature is sin(arg) with derivative cos(arg))
+    float *pa, *pb, *pc, *ang_b, *b1, *b2, *w3h, *b3;
+    float *grp_f;                 // 2 x TC_GRP_FLOATS
+    uint64_t *bars;               // [0] weights, then per group: ready, done, aux
+    uint32_t *tmem_slot;
+    __device__ TcShared(unsigned char *base, const TcDims &t) {
+        w1h = base + t.off_w1; w1l = w1h + t.w1_half;
+        w2h = base + t.off_w2; w2l = w2h + t.w2_half;
+        float *f = reinterpret_cast<float *>(base + t.off_misc);
+        pa = f; f += t.K1;
+        pb = f; f += t.K1;
+        pc = f; f += t.K1;
+        ang_b = f; f += (t.A + 3) / 4 * 4;
+        b1 = f; f += t.H;
+        b2 = f; f += t.H;
+        w3h = f; f += t.H;
+        b3 = f; f += 4;
+        grp_f = f; f += 2 * TC_GRP_FLOATS;
+        bars = reinterpret_cast<uint64_t *>(f);
+        tmem_slot = reinterpret_cast<uint32_t *>(bars + 8);
+    }
+};
+struct TcGroup {
+    unsigned char *h1h, *h1l, *rh, *rl;      // H1 / gH1 operand, scratch region (E ring / gH2 / E^T)
+    float *u0, *u1, *th, *skip, *gbar, *zp, *gx;
+    uint64_t *ready, *done, *aux;
+    __device__ TcGroup(unsigned char *base, const TcDims &t, const TcShared &s, int g) {
+        h1h = base + t.off_grp + g * t.grp_bytes; h1l = h1h + t.h1_half;
+        rh = h1l + t.h1_half; rl = rh + TC_RHALF;
+        float *f = s.grp_f + g * TC_GRP_FLOATS;
+        u0 = f; f += TC_TP;
+        u1 = f; f += TC_TP;
+        th = f; f += TC_TP;
+        skip = f; f += TC_TP;
+        gbar = f; f += TC_TP;
+        zp = f; f += 4 * TC_TP;
+        gx = f;
+        ready = s.bars + 1 + 3 * g; done = ready + 1; aux = ready + 2;
+    }
+};
 
 // store 16 consecutive columns (col0 .. col0+15) of row `row` into a [row/8][col/8][row%8][col%8] operand buffer
 __device__ __forceinline__ void store_row16(unsigned char *hi_buf, unsigned char *lo_buf, int row, int col0,
@@ -221,16 +237,124 @@ __device__ __forceinline__ void mma3(uint32_t tmem_d, uint64_t ah, uint64_t al, 
     mma_bf16(tmem_d, ah, bl, idesc, 1u, issue);
 }
 
-// Thread layout: 16 warps.  warp = 4*cq + q: q = TMEM lane quarter (rows 32q..32q+31), cq = column quarter of the
-// point tile (columns 16cq..16cq+15).  A thread therefore owns one hidden unit / feature (`row`) and 16 points.
+__device__ __forceinline__ void group_sync(int g) { asm volatile("bar.sync %0, %1;" ::"r"(1 + g), "r"(TC_GT) : "memory"); }
+// a worker thread has finished writing MMA operands (generic proxy) / reading TMEM: publish to the MMA warp
+__device__ __forceinline__ void signal_ready(uint64_t *bar) {
+    fence_proxy_async();
+    fence_before_sync();
+    mbar_arrive(bar);
+}
+__device__ __forceinline__ void wait_done(uint64_t *bar, uint32_t &phase) {
+    mbar_wait(bar, phase);
+    phase ^= 1;
+    fence_after_sync();
+}
+
+// S_row of the point-indexed operand buffers (H1, gH1, gH2): 4 point octets x 128 B
+constexpr uint32_t S_PT = (TC_TP / 8) * 128;
+
+// ---- the MMA-issue warp: serves both groups, one tile phase at a time, in whatever order they become ready ----
+__device__ __forceinline__ void tc_issue_warp(const OnfTcArgs &a, const TcShared &s, unsigned char *smem_raw, uint32_t tmem,
+                                              int cnt, bool want_bwd, bool want_wgrad) {
+    const TcDims &t = a.t;
+    const int K1 = t.K1, KH = t.KH, MB = t.MB;
+    const int n_tiles = (cnt + TC_TP - 1) / TC_TP;
+    const int n_phases = !want_bwd ? MB + 1 : (want_wgrad ? 2 * MB + 3 : MB + 3);
+    const uint32_t lead = elect_one();
+    const uint32_t w1h = smem_u32(s.w1h), w1l = smem_u32(s.w1l), w2h = smem_u32(s.w2h), w2l = smem_u32(s.w2l);
+    mbar_wait(s.bars, 0);                                     // packed weights have landed (bulk copies)
+    int tile[2] = {0, 1}, phase[2] = {0, 0};
+    uint32_t par[2] = {0, 0};
+    bool dw2_started = false, dw1_started[2] = {false, false};
+    const long long t_start = clock64();
+    while (tile[0] < n_tiles || tile[1] < n_tiles) {
+#pragma unroll
+        for (int g = 0; g < 2; ++g) {
+            if (tile[g] >= n_tiles) continue;
+            TcGroup G(smem_raw, t, s, g);
+            if (!mbar_try_wait(G.ready, par[g])) continue;
+            par[g] ^= 1;
+            fence_after_sync();
+            const int Nt = ru16(min(TC_TP, cnt - tile[g] * TC_TP));
+            const uint32_t tw = tmem + TM_WORK + 64 * g;
+            const uint32_t h1h = smem_u32(G.h1h), h1l = smem_u32(G.h1l), rh = smem_u32(G.rh), rl = smem_u32(G.rl);
+            const int ph = phase[g];
+            if (ph < MB) {
+                // fwd1, feature group ph: D1[j,n] (+)= W1p[j,k] E[n,k]
+                const uint32_t idesc = instr_desc_bf16(128, Nt, 0, 0);
+                const int ks_n = min(8, (K1 - 128 * ph) / 16);
+                for (int ks = 0; ks < ks_n; ++ks) {
+                    const uint32_t aoff = (uint32_t)(16 * ph + 2 * ks) * t.S_colW, boff = (uint32_t)(2 * ks) * S_PT;
+                    mma3(tw, desc_kmajor(w1h + aoff, 128, t.S_colW), desc_kmajor(w1l + aoff, 128, t.S_colW),
+                         desc_kmajor(rh + boff, 128, S_PT), desc_kmajor(rl + boff, 128, S_PT), idesc, ph > 0 || ks > 0, lead);
+                }
+                mma_commit(ph + 1 < MB ? G.aux : G.done, lead);
+            } else if (ph == MB) {
+                // fwd2: D2[i,n] = W2p[i,j] H1[j,n]
+                const uint32_t idesc = instr_desc_bf16(128, Nt, 0, 1);
+                for (int ks = 0; ks < KH / 16; ++ks) {
+                    const uint32_t aoff = (uint32_t)(2 * ks) * t.S_colW, boff = (uint32_t)(2 * ks) * S_PT;
+                    mma3(tw + 32, desc_kmajor(w2h + aoff, 128, t.S_colW), desc_kmajor(w2l + aoff, 128, t.S_colW),
+                         desc_mnmajor(h1h + boff, S_PT, 128), desc_mnmajor(h1l + boff, S_PT, 128), idesc, ks > 0, lead);
+                }
+                mma_commit(G.done, lead);
+            } else if (ph == MB + 1) {
+                // wgrad2 (persistent accumulator) + dgrad2
+                if (want_wgrad) {
+                    const uint32_t idesc = instr_desc_bf16(128, KH, 0, 0);
+                    for (int ks = 0; ks < Nt / 16; ++ks) {
+                        const uint32_t off = (uint32_t)(2 * ks) * 128;
+                        mma3(tmem + TM_DW2, desc_kmajor(rh + off, S_PT, 128), desc_kmajor(rl + off, S_PT, 128),
+                             desc_kmajor(h1h + off, S_PT, 128), desc_kmajor(h1l + off, S_PT, 128), idesc, dw2_started || ks > 0, lead);
+                    }
+                    dw2_started = true;
+                }
+                const uint32_t idesc = instr_desc_bf16(128, Nt, 1, 1);
+                for (int ks = 0; ks < KH / 16; ++ks) {
+                    const uint32_t aoff = (uint32_t)(2 * ks) * 128, boff = (uint32_t)(2 * ks) * S_PT;
+                    mma3(tw, desc_mnmajor(w2h + aoff, 128, t.S_colW), desc_mnmajor(w2l + aoff, 128, t.S_colW),
+                         desc_mnmajor(rh + boff, S_PT, 128), desc_mnmajor(rl + boff, S_PT, 128), idesc, ks > 0, lead);
+                }
+                mma_commit(G.done, lead);
+            } else if (ph == MB + 2) {
+                // dgrad1: gE[k,n] for all feature blocks
+                const uint32_t idesc = instr_desc_bf16(128, Nt, 1, 1);
+                for (int mb = 0; mb < MB; ++mb)
+                    for (int ks = 0; ks < KH / 16; ++ks) {
+                        const uint32_t aoff = (uint32_t)(16 * mb) * t.S_colW + (uint32_t)(2 * ks) * 128, boff = (uint32_t)(2 * ks) * S_PT;
+                        mma3(tw + 32 * mb, desc_mnmajor(w1h + aoff, 128, t.S_colW), desc_mnmajor(w1l + aoff, 128, t.S_colW),
+                             desc_mnmajor(h1h + boff, S_PT, 128), desc_mnmajor(h1l + boff, S_PT, 128), idesc, ks > 0, lead);
+                    }
+                mma_commit(G.done, lead);
+            } else {
+                // wgrad1, feature block mb: dW1[j, 128 mb + f] += gH1[j,n] E[n,f]
+                const int mb = ph - (MB + 3);
+                const int pf = min(128, K1 - 128 * mb);
+                const uint32_t idesc = instr_desc_bf16(128, pf, 0, 0);
+                for (int ks = 0; ks < Nt / 16; ++ks) {
+                    const uint32_t aoff = (uint32_t)(2 * ks) * 128, boff = (uint32_t)(2 * ks) * 2048;
+                    mma3(tmem + TM_DW1 + 128 * mb, desc_kmajor(h1h + aoff, S_PT, 128), desc_kmajor(h1l + aoff, S_PT, 128),
+                         desc_kmajor(rh + boff, 128, 2048), desc_kmajor(rl + boff, 128, 2048), idesc, dw1_started[mb] || ks > 0, lead);
+                }
+                dw1_started[mb] = true;
+                mma_commit(G.aux, lead);
+            }
+            if (++phase[g] == n_phases) { phase[g] = 0; tile[g] += 2; }
+        }
+        if (clock64() - t_start > 20000000000LL) __trap();    // protocol bug: fail loudly instead of hanging
+    }
+}
+
+// Thread layout: 17 warps.  Warps 0..15 are workers in two groups of 8 (group g = warp / 8 walks the tiles g, g+2, ...
+// of 32 points each); inside a group warp lw = 4*cq + q: q = TMEM lane quarter (rows 32q..32q+31), cq = column half
+// of the tile (columns 16cq..16cq+15), so a thread owns one hidden unit / feature (`row`) and 16 points.  Warp 16
+// issues every tcgen05.mma: while one group runs an epilogue on the CUDA cores the other group's MMAs execute.
 __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const OnfDims &d = a.d;
     const TcDims &t = a.t;
     const nfopp_onf_layout &L = d.lay;
     const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int q = warp & 3, cq = warp >> 2;
-    const int row = q * 32 + lane;
     if (a.sp && !a.warm && !a.sp->do_train) return;    // engine: not a field-training step
     const int cnt = a.count ? a.count[p] : a.n;
     if (cnt <= 0) return;
@@ -238,25 +362,28 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
     const bool want_wgrad = want_bwd && (a.grad_out != nullptr || a.adam_w != nullptr);
     const bool want_gx = want_bwd && a.gx_out != nullptr;
     const int F = t.F, FIN = t.FIN, H = t.H, K1 = t.K1, KH = t.KH;
+    const bool is_issuer = warp == TC_WORKERS / 32;
 
-    TcSmem s(smem_raw, t);
+    TcShared s(smem_raw, t);
     const float *W = a.weights + (size_t)p * L.n_params;
-    uint64_t *bar_w = s.bars, *bar_mma = s.bars + 1, *bar_aux = s.bars + 2;
 
-    // ---- one-time setup: barriers, TMEM, packed weights by bulk copy (TMA), small fp32 parameters ----
+    // ---- one-time setup: barriers, TMEM, packed weights by bulk copy (TMA), per-feature / per-unit fp32 parameters ----
     if (tid == 0) {
-        mbar_init(bar_w, 1);
-        mbar_init(bar_mma, 1);
-        mbar_init(bar_aux, 1);
+        mbar_init(s.bars, 1);
+        for (int g = 0; g < 2; ++g) {
+            mbar_init(s.bars + 1 + 3 * g, TC_GT);      // ready: every worker of the group arrives
+            mbar_init(s.bars + 2 + 3 * g, 1);          // done: one tcgen05.commit
+            mbar_init(s.bars + 3 + 3 * g, 1);          // aux: one tcgen05.commit
+        }
         fence_mbar_init();
     }
-    if (warp == 1) tmem_alloc(s.tmem_slot, 512);
+    if (is_issuer) tmem_alloc(s.tmem_slot, 512);
     __syncthreads();
-    if (tid == 0) {
+    if (is_issuer && lane == 0) {
         const unsigned char *src = a.packed + (size_t)p * t.packed_bytes;
-        mbar_expect_tx(bar_w, (uint32_t)t.packed_bytes);
-        bulk_g2s(s.w1h, src, 2 * t.w1_half, bar_w);
-        bulk_g2s(s.w2h, src + 2 * t.w1_half, 2 * t.w2_half, bar_w);
+        mbar_expect_tx(s.bars, (uint32_t)t.packed_bytes);
+        bulk_g2s(s.w1h, src, 2 * t.w1_half, s.bars);
+        bulk_g2s(s.w2h, src + 2 * t.w1_half, 2 * t.w2_half, s.bars);
     }
     for (int f = tid; f < K1; f += TC_THREADS) {
         float pa = 0.f, pb = 0.f, pc = 0.f;
@@ -283,397 +410,315 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
     __syncthreads();
     fence_after_sync();
     const uint32_t tmem = *s.tmem_slot;
-    const uint32_t tm_lane = tmem + ((uint32_t)(q * 32) << 16);
-    if (warp == 0) mbar_wait(bar_w, 0);    // the MMA-issuing warp observes the bulk copies
 
-    uint32_t ph_mma = 0, ph_aux = 0;
-    bool pending_aux = false;
-    // thread-local gradient accumulators (hidden unit `row`; features row and 128+row; point tid)
+    // worker identity (the issuer warp computes harmless values)
+    const int g = (warp >> 3) & 1, gt = tid & (TC_GT - 1), lw = warp & 7;
+    const int q = lw & 3, cq = lw >> 2;
+    const int row = q * 32 + lane;
+    const uint32_t tm_lane = tmem + ((uint32_t)(q * 32) << 16);
+    // thread-local gradient accumulators (hidden unit `row`; features row and 128+row; point gt)
     float acc_db1 = 0.f, acc_db2 = 0.f, acc_dw3 = 0.f, acc_db3 = 0.f;
     float fa0 = 0.f, fb0 = 0.f, fc0 = 0.f, fa1 = 0.f, fb1 = 0.f, fc1 = 0.f;
-    const float my_b1 = row < H ? s.b1[row] : 0.f, my_b2 = row < H ? s.b2[row] : 0.f, my_w3 = row < H ? s.w3h[row] : 0.f;
 
-    const int tiles = (cnt + TC_TP - 1) / TC_TP;
-    for (int tile = 0; tile < tiles; ++tile) {
-        const int n0 = tile * TC_TP;
-        const int nv = min(TC_TP, cnt - n0);
-        const int Nt = ru16(nv);
-        const int c0 = 16 * cq;                        // this warp's 16 columns of the tile
-        const bool cols_on = c0 < Nt;
-        // ---- P0: inputs (onf_model.py:37-38) ----
-        if (tid < TC_TP) {
-            float x0 = 0.f, x1 = 0.f, x2 = 0.f;
-            if (tid < nv) {
-                const float *xp = a.x + ((size_t)p * a.n + n0 + tid) * a.x_stride;
-                x0 = xp[0]; x1 = xp[1];
-                if (L.in_dim == 3) x2 = xp[2];
+    if (is_issuer) {
+        tc_issue_warp(a, s, smem_raw, tmem, cnt, want_bwd, want_wgrad);
+    } else {
+        TcGroup G(smem_raw, t, s, g);
+        const uint32_t tw = tm_lane + TM_WORK + 64 * g;
+        uint32_t ph_done = 0, ph_aux = 0;
+        bool pending_aux = false;
+        const float my_b1 = row < H ? s.b1[row] : 0.f, my_b2 = row < H ? s.b2[row] : 0.f, my_w3 = row < H ? s.w3h[row] : 0.f;
+        const int n_tiles = (cnt + TC_TP - 1) / TC_TP;
+        const int c0 = 16 * cq;                            // this warp's 16 columns of the tile
+        for (int tile = g; tile < n_tiles; tile += 2) {
+            const int n0 = tile * TC_TP;
+            const int nv = min(TC_TP, cnt - n0);
+            const int Nt = ru16(nv);
+            const bool cols_on = c0 < Nt;
+            // ---- P0: inputs (onf_model.py:37-38) ----
+            if (gt < TC_TP) {
+                float x0 = 0.f, x1 = 0.f, x2 = 0.f;
+                if (gt < nv) {
+                    const float *xp = a.x + ((size_t)p * a.n + n0 + gt) * a.x_stride;
+                    x0 = xp[0]; x1 = xp[1];
+                    if (L.in_dim == 3) x2 = xp[2];
+                }
+                G.u0[gt] = (x0 - d.mean) / d.sigma;
+                G.u1[gt] = (x1 - d.mean) / d.sigma;
+                G.th[gt] = x2;
             }
-            s.u0[tid] = (x0 - d.mean) / d.sigma;
-            s.u1[tid] = (x1 - d.mean) / d.sigma;
-            s.th[tid] = x2;
-        }
-        __syncthreads();
-        // ---- P1: encoding (CUDA cores) feeding fwd1 in groups of 128 features ----
-        {
-            const int n = tid & 63, oc = tid >> 6;       // point, feature octet (0..7) within a 64-feature half group
-            const float u0 = s.u0[n], u1 = s.u1[n], th = s.th[n];
+            group_sync(g);
+            // ---- P1: encoding (CUDA cores) feeding fwd1 in groups of 128 features ----
+            {
+                const int n = gt & 31, oc = gt >> 5;         // point, feature octet (0..7) within a 64-feature half group
+                const float u0 = G.u0[n], u1 = G.u1[n], th = G.th[n];
 #pragma unroll 1
-            for (int g = 0; g < t.MB; ++g) {
-                uint4 ehi[2], elo[2];
+                for (int fg = 0; fg < t.MB; ++fg) {
+                    uint4 ehi[2], elo[2];
 #pragma unroll
-                for (int it = 0; it < 2; ++it) {
-                    const int f0 = 128 * g + 8 * (oc + 8 * it);
-                    float e[8];
-                    if (f0 < K1 && n < Nt) {
-                        float pa[8], pb[8], pc[8];
-                        *reinterpret_cast<float4 *>(pa) = *reinterpret_cast<const float4 *>(s.pa + f0);
-                        *reinterpret_cast<float4 *>(pa + 4) = *reinterpret_cast<const float4 *>(s.pa + f0 + 4);
-                        *reinterpret_cast<float4 *>(pb) = *reinterpret_cast<const float4 *>(s.pb + f0);
-                        *reinterpret_cast<float4 *>(pb + 4) = *reinterpret_cast<const float4 *>(s.pb + f0 + 4);
-                        *reinterpret_cast<float4 *>(pc) = *reinterpret_cast<const float4 *>(s.pc + f0);
-                        *reinterpret_cast<float4 *>(pc + 4) = *reinterpret_cast<const float4 *>(s.pc + f0 + 4);
+                    for (int it = 0; it < 2; ++it) {
+                        const int f0 = 128 * fg + 8 * (oc + 8 * it);
+                        float e[8];
+                        if (f0 < K1 && n < Nt) {
+                            float pa[8], pb[8], pc[8];
+                            *reinterpret_cast<float4 *>(pa) = *reinterpret_cast<const float4 *>(s.pa + f0);
+                            *reinterpret_cast<float4 *>(pa + 4) = *reinterpret_cast<const float4 *>(s.pa + f0 + 4);
+                            *reinterpret_cast<float4 *>(pb) = *reinterpret_cast<const float4 *>(s.pb + f0);
+                            *reinterpret_cast<float4 *>(pb + 4) = *reinterpret_cast<const float4 *>(s.pb + f0 + 4);
+                            *reinterpret_cast<float4 *>(pc) = *reinterpret_cast<const float4 *>(s.pc + f0);
+                            *reinterpret_cast<float4 *>(pc + 4) = *reinterpret_cast<const float4 *>(s.pc + f0 + 4);
 #pragma unroll
-                        for (int i = 0; i < 8; ++i)
-                            e[i] = __sinf(reduce_2pi(feature_arg(pa[i], pb[i], pc[i], u0, f0 + i < F ? u1 : th)));
-                    } else {
+                            for (int i = 0; i < 8; ++i)
+                                e[i] = __sinf(reduce_2pi(feature_arg(pa[i], pb[i], pc[i], u0, f0 + i < F ? u1 : th)));
+                        } else {
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) e[i] = 0.f;
+                            for (int i = 0; i < 8; ++i) e[i] = 0.f;
+                        }
+                        split8(e, ehi[it], elo[it]);
                     }
-                    split8(e, ehi[it], elo[it]);
-                }
-                if (g > 0 || pending_aux) {          // the scratch region is still being read by earlier MMAs
-                    mbar_wait(bar_aux, ph_aux);
-                    ph_aux ^= 1;
-                    pending_aux = false;
-                }
+                    if (fg > 0 || pending_aux) {          // the scratch region is still being read by earlier MMAs
+                        mbar_wait(G.aux, ph_aux);
+                        ph_aux ^= 1;
+                        pending_aux = false;
+                    }
 #pragma unroll
-                for (int it = 0; it < 2; ++it) {
-                    const int fo = oc + 8 * it;
-                    if (128 * g + 8 * fo < K1 && n < Nt) {
-                        *reinterpret_cast<uint4 *>(s.rh + fo * 1024 + n * 16) = ehi[it];
-                        *reinterpret_cast<uint4 *>(s.rl + fo * 1024 + n * 16) = elo[it];
+                    for (int it = 0; it < 2; ++it) {
+                        const int fo = oc + 8 * it;
+                        if (128 * fg + 8 * fo < K1 && n < Nt) {
+                            *reinterpret_cast<uint4 *>(G.rh + fo * S_PT + n * 16) = ehi[it];
+                            *reinterpret_cast<uint4 *>(G.rl + fo * S_PT + n * 16) = elo[it];
+                        }
                     }
-                }
-                fence_proxy_async();
-                fence_before_sync();
-                __syncthreads();
-                if (warp == 0) {                 // warp-uniform: descriptor arithmetic stays on the uniform datapath
-                    fence_after_sync();
-                    const uint32_t lead = elect_one();
-                    const uint32_t idesc = instr_desc_bf16(128, Nt, 0, 0);
-                    const int ks_n = min(8, (K1 - 128 * g) / 16);
-                    for (int ks = 0; ks < ks_n; ++ks) {
-                        const uint32_t aoff = (uint32_t)(16 * g + 2 * ks) * t.S_colW, boff = (uint32_t)(2 * ks) * 1024;
-                        mma3(tmem + TM_WORK, desc_kmajor(smem_u32(s.w1h) + aoff, 128, t.S_colW),
-                             desc_kmajor(smem_u32(s.w1l) + aoff, 128, t.S_colW), desc_kmajor(smem_u32(s.rh) + boff, 128, 1024),
-                             desc_kmajor(smem_u32(s.rl) + boff, 128, 1024), idesc, g > 0 || ks > 0, lead);
-                    }
-                    if (g + 1 < t.MB) mma_commit(bar_aux, lead);
-                    else mma_commit(bar_mma, lead);
+                    signal_ready(G.ready);                // -> fwd1(fg)
                 }
             }
-        }
-        // ---- P2: epilogue 1: bias + ReLU -> H1 operand; row H = skip term of the logit ----
-        mbar_wait(bar_mma, ph_mma);
-        ph_mma ^= 1;
-        fence_after_sync();
-        if (cols_on) {
-            float v[16];
-            tmem_ld16(tm_lane + TM_WORK + c0, v);
-            if (row < H) {
+            // ---- P2: epilogue 1: bias + ReLU -> H1 operand; row H = skip term of the logit ----
+            wait_done(G.done, ph_done);
+            if (cols_on) {
+                float v[16];
+                tmem_ld16(tw + c0, v);
+                if (row < H) {
 #pragma unroll
-                for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i] + my_b1, 0.f);
+                    for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i] + my_b1, 0.f);
+                } else {
+                    if (row == H) {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) G.skip[c0 + i] = v[i];
+                    }
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) v[i] = 0.f;
+                }
+                if (row < KH) store_row16(G.h1h, G.h1l, row, c0, v, S_PT);
+            }
+            signal_ready(G.ready);                        // -> fwd2
+            // ---- P4: epilogue 2: logit, dL/dz, gH2 operand ----
+            wait_done(G.done, ph_done);
+            float r2[16];
+            if (cols_on) {
+                tmem_ld16(tw + 32 + c0, r2);
+#pragma unroll
+                for (int i = 0; i < 16; ++i) r2[i] = row < H ? fmaxf(r2[i] + my_b2, 0.f) : 0.f;
             } else {
-                if (row == H) {
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) s.skip[c0 + i] = v[i];
-                }
-#pragma unroll
-                for (int i = 0; i < 16; ++i) v[i] = 0.f;
+                for (int i = 0; i < 16; ++i) r2[i] = 0.f;
             }
-            if (row < KH) store_row16(s.h1h, s.h1l, row, c0, v, 1024);
-        }
-        fence_proxy_async();
-        fence_before_sync();
-        __syncthreads();
-        // ---- P3: fwd2 ----
-        if (warp == 0) {                 // warp-uniform: descriptor arithmetic stays on the uniform datapath
-            fence_after_sync();
-            const uint32_t lead = elect_one();
-            const uint32_t idesc = instr_desc_bf16(128, Nt, 0, 1);
-            for (int ks = 0; ks < KH / 16; ++ks) {
-                const uint32_t aoff = (uint32_t)(2 * ks) * t.S_colW, boff = (uint32_t)(2 * ks) * 1024;
-                mma3(tmem + TM_WORK + 64, desc_kmajor(smem_u32(s.w2h) + aoff, 128, t.S_colW),
-                     desc_kmajor(smem_u32(s.w2l) + aoff, 128, t.S_colW), desc_mnmajor(smem_u32(s.h1h) + boff, 1024, 128),
-                     desc_mnmajor(smem_u32(s.h1l) + boff, 1024, 128), idesc, ks > 0, lead);
+            {
+                float pz[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) pz[i] = my_w3 * r2[i];
+                const float zs = colsum16(pz, lane);
+                if ((lane & 1) == 0) G.zp[q * TC_TP + c0 + (lane >> 1)] = zs;
             }
-            mma_commit(bar_mma, lead);
-        }
-        // ---- P4: epilogue 2: logit, dL/dz, gH2 operand ----
-        mbar_wait(bar_mma, ph_mma);
-        ph_mma ^= 1;
-        fence_after_sync();
-        float r2[16];
-        if (cols_on) {
-            tmem_ld16(tm_lane + TM_WORK + 64 + c0, r2);
-#pragma unroll
-            for (int i = 0; i < 16; ++i) r2[i] = row < H ? fmaxf(r2[i] + my_b2, 0.f) : 0.f;
-        } else {
-#pragma unroll
-            for (int i = 0; i < 16; ++i) r2[i] = 0.f;
-        }
-        {
-            float pz[16];
-#pragma unroll
-            for (int i = 0; i < 16; ++i) pz[i] = my_w3 * r2[i];
-            const float zs = colsum16(pz, lane);
-            if ((lane & 1) == 0) s.zp[q * TC_TP + c0 + (lane >> 1)] = zs;
-        }
-        __syncthreads();
-        if (tid < TC_TP) {
-            const int n = tid;
-            const float z = s.zp[n] + s.zp[TC_TP + n] + s.zp[2 * TC_TP + n] + s.zp[3 * TC_TP + n] + s.skip[n] + s.b3[0];
-            const bool valid = n < nv;
-            const size_t gi = (size_t)p * a.n + n0 + n;
-            if (valid && a.z_out) a.z_out[gi] = z;
-            float g = 0.f;
-            if (valid && want_bwd) {                        // dL/dz
-                if (a.gbar_mode == 0) g = a.gz[gi];
-                else if (a.gbar_mode == 1) g = (sigmoid_f(z) - a.aux[gi]) / (float)cnt;
-                else {
-                    const float zb = z * a.beta;
-                    const float ez = expf(zb);
-                    g = a.wc * (zb > 20.f ? 1.f : ez / (ez + 1.f));
-                    if (a.gbar_mode == 3) {
-                        const float th = tanhf(z);
-                        g += a.aux[gi] * (1.f - th * th);
+            group_sync(g);
+            if (gt < TC_TP) {
+                const int n = gt;
+                const float z = G.zp[n] + G.zp[TC_TP + n] + G.zp[2 * TC_TP + n] + G.zp[3 * TC_TP + n] + G.skip[n] + s.b3[0];
+                const bool valid = n < nv;
+                const size_t gi = (size_t)p * a.n + n0 + n;
+                if (valid && a.z_out) a.z_out[gi] = z;
+                float gb = 0.f;
+                if (valid && want_bwd) {                        // dL/dz
+                    if (a.gbar_mode == 0) gb = a.gz[gi];
+                    else if (a.gbar_mode == 1) gb = (sigmoid_f(z) - a.aux[gi]) / (float)cnt;
+                    else {
+                        const float zb = z * a.beta;
+                        const float ez = expf(zb);
+                        gb = a.wc * (zb > 20.f ? 1.f : ez / (ez + 1.f));
+                        if (a.gbar_mode == 3) {
+                            const float th = tanhf(z);
+                            gb += a.aux[gi] * (1.f - th * th);
+                        }
                     }
                 }
+                G.gbar[n] = gb;
+                acc_db3 += gb;
             }
-            s.gbar[n] = g;
-            acc_db3 += g;
-        }
-        __syncthreads();
-        if (!want_bwd) continue;
-        if (cols_on) {
-            float v[16];
-#pragma unroll
-            for (int i = 0; i < 16; ++i) {
-                const float gb = s.gbar[c0 + i];
-                acc_dw3 = fmaf(gb, r2[i], acc_dw3);
-                const float g = r2[i] > 0.f ? gb * my_w3 : 0.f;
-                acc_db2 += g;
-                v[i] = g;
-            }
-            if (row < KH) store_row16(s.rh, s.rl, row, c0, v, 1024);
-        }
-        fence_proxy_async();
-        fence_before_sync();
-        __syncthreads();
-        // ---- P5: wgrad2 (persistent accumulator) + dgrad2 ----
-        if (warp == 0) {                 // warp-uniform: descriptor arithmetic stays on the uniform datapath
-            fence_after_sync();
-            const uint32_t lead = elect_one();
-            if (want_wgrad) {
-                const uint32_t idesc = instr_desc_bf16(128, KH, 0, 0);
-                for (int ks = 0; ks < Nt / 16; ++ks) {
-                    const uint32_t off = (uint32_t)(2 * ks) * 128;
-                    mma3(tmem + TM_DW2, desc_kmajor(smem_u32(s.rh) + off, 1024, 128), desc_kmajor(smem_u32(s.rl) + off, 1024, 128),
-                         desc_kmajor(smem_u32(s.h1h) + off, 1024, 128), desc_kmajor(smem_u32(s.h1l) + off, 1024, 128), idesc,
-                         tile > 0 || ks > 0, lead);
-                }
-            }
-            const uint32_t idesc = instr_desc_bf16(128, Nt, 1, 1);
-            for (int ks = 0; ks < KH / 16; ++ks) {
-                const uint32_t aoff = (uint32_t)(2 * ks) * 128, boff = (uint32_t)(2 * ks) * 1024;
-                mma3(tmem + TM_WORK, desc_mnmajor(smem_u32(s.w2h) + aoff, 128, t.S_colW),
-                     desc_mnmajor(smem_u32(s.w2l) + aoff, 128, t.S_colW), desc_mnmajor(smem_u32(s.rh) + boff, 1024, 128),
-                     desc_mnmajor(smem_u32(s.rl) + boff, 1024, 128), idesc, ks > 0, lead);
-            }
-            mma_commit(bar_mma, lead);
-        }
-        // ---- P6: epilogue 3: ReLU mask of layer 1 -> gH1 operand (in place over H1); row H := dL/dz ----
-        mbar_wait(bar_mma, ph_mma);
-        ph_mma ^= 1;
-        fence_after_sync();
-        if (cols_on) {
-            float v[16];
-            tmem_ld16(tm_lane + TM_WORK + c0, v);
-            if (row < H) {
-                const int off = (row >> 3) * 1024 + (c0 >> 3) * 128 + (row & 7) * 16;
-                const uint4 m0 = *reinterpret_cast<const uint4 *>(s.h1h + off);
-                const uint4 m1 = *reinterpret_cast<const uint4 *>(s.h1h + off + 128);
-                const uint32_t mw[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+            group_sync(g);
+            if (!want_bwd) continue;
+            if (cols_on) {
+                float v[16];
 #pragma unroll
                 for (int i = 0; i < 16; ++i) {
-                    const uint32_t bits = (mw[i >> 1] >> ((i & 1) * 16)) & 0x7FFFu;
-                    v[i] = bits != 0 ? v[i] : 0.f;
-                    acc_db1 += v[i];
+                    const float gb = G.gbar[c0 + i];
+                    acc_dw3 = fmaf(gb, r2[i], acc_dw3);
+                    const float gg = r2[i] > 0.f ? gb * my_w3 : 0.f;
+                    acc_db2 += gg;
+                    v[i] = gg;
                 }
-            } else if (row == H) {
-#pragma unroll
-                for (int i = 0; i < 16; ++i) v[i] = s.gbar[c0 + i];
-            } else {
-#pragma unroll
-                for (int i = 0; i < 16; ++i) v[i] = 0.f;
+                if (row < KH) store_row16(G.rh, G.rl, row, c0, v, S_PT);
             }
-            if (row < KH) store_row16(s.h1h, s.h1l, row, c0, v, 1024);
-        }
-        fence_proxy_async();
-        fence_before_sync();
-        __syncthreads();
-        // ---- P7: dgrad1: gE[k,n] for both feature blocks ----
-        if (warp == 0) {                 // warp-uniform: descriptor arithmetic stays on the uniform datapath
-            fence_after_sync();
-            const uint32_t lead = elect_one();
-            const uint32_t idesc = instr_desc_bf16(128, Nt, 1, 1);
-            for (int mb = 0; mb < t.MB; ++mb)
-                for (int ks = 0; ks < KH / 16; ++ks) {
-                    const uint32_t aoff = (uint32_t)(16 * mb) * t.S_colW + (uint32_t)(2 * ks) * 128, boff = (uint32_t)(2 * ks) * 1024;
-                    mma3(tmem + TM_WORK + 64 * mb, desc_mnmajor(smem_u32(s.w1h) + aoff, 128, t.S_colW),
-                         desc_mnmajor(smem_u32(s.w1l) + aoff, 128, t.S_colW), desc_mnmajor(smem_u32(s.h1h) + boff, 1024, 128),
-                         desc_mnmajor(smem_u32(s.h1l) + boff, 1024, 128), idesc, ks > 0, lead);
-                }
-            mma_commit(bar_mma, lead);
-        }
-        // ---- P8/P9: epilogue 4: encoding backward (+ input gradient), E^T operand, wgrad1 per feature block ----
-        mbar_wait(bar_mma, ph_mma);
-        ph_mma ^= 1;
-        fence_after_sync();
-#pragma unroll 1
-        for (int mb = 0; mb < t.MB; ++mb) {
-            const int f = 128 * mb + row;
-            const int pf = min(128, K1 - 128 * mb);              // features of this block that are MMA rows
-            const bool f_on = row < pf;                          // rows beyond hold garbage
-            const bool fourier = f < F;
-            const float ppa = f_on ? s.pa[f] : 0.f, ppb = f_on ? s.pb[f] : 0.f, ppc = f_on ? s.pc[f] : 0.f;
-            const float ew0 = fourier ? ppa : 0.f, ew1 = fourier ? ppb : 0.f, eaf = (!fourier && f < FIN) ? ppb : 0.f;
-            float ta = 0.f, tb = 0.f, tc = 0.f;                  // sum gp*u0, sum gp*x1, sum gp
-            float gq[16];
-            uint4 ehi[2], elo[2];
-            {
-                float ev[16];
-                if (cols_on) {
-                    float v[16], xu[16], x1[16];
-                    tmem_ld16(tm_lane + TM_WORK + 64 * mb + c0, v);
-                    const float *x1src = fourier ? s.u1 : s.th;
-#pragma unroll
-                    for (int i4 = 0; i4 < 4; ++i4) {
-                        *reinterpret_cast<float4 *>(xu + 4 * i4) = *reinterpret_cast<const float4 *>(s.u0 + c0 + 4 * i4);
-                        *reinterpret_cast<float4 *>(x1 + 4 * i4) = *reinterpret_cast<const float4 *>(x1src + c0 + 4 * i4);
-                    }
+            signal_ready(G.ready);                        // -> wgrad2 + dgrad2
+            // ---- P6: epilogue 3: ReLU mask of layer 1 -> gH1 operand (in place over H1); row H := dL/dz ----
+            wait_done(G.done, ph_done);
+            if (cols_on) {
+                float v[16];
+                tmem_ld16(tw + c0, v);
+                if (row < H) {
+                    const int off = (row >> 3) * S_PT + (c0 >> 3) * 128 + (row & 7) * 16;
+                    const uint4 m0 = *reinterpret_cast<const uint4 *>(G.h1h + off);
+                    const uint4 m1 = *reinterpret_cast<const uint4 *>(G.h1h + off + 128);
+                    const uint32_t mw[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
 #pragma unroll
                     for (int i = 0; i < 16; ++i) {
-                        const float r = reduce_2pi(feature_arg(ppa, ppb, ppc, xu[i], x1[i]));
-                        const float gp = f_on ? v[i] * __cosf(r) : 0.f;
-                        ev[i] = __sinf(r);
-                        gq[i] = gp;
-                        ta = fmaf(gp, xu[i], ta);
-                        tb = fmaf(gp, x1[i], tb);
-                        tc += gp;
+                        const uint32_t bits = (mw[i >> 1] >> ((i & 1) * 16)) & 0x7FFFu;
+                        v[i] = bits != 0 ? v[i] : 0.f;
+                        acc_db1 += v[i];
                     }
+                } else if (row == H) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) v[i] = G.gbar[c0 + i];
                 } else {
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) { ev[i] = 0.f; gq[i] = 0.f; }
+                    for (int i = 0; i < 16; ++i) v[i] = 0.f;
                 }
-                split8(ev, ehi[0], elo[0]);
-                split8(ev + 8, ehi[1], elo[1]);
+                if (row < KH) store_row16(G.h1h, G.h1l, row, c0, v, S_PT);
             }
-            if (!fourier) {                                      // heading features: d ang_b = f_k * sum gp,
-                const float b = f < FIN ? s.ang_b[f - F] : 0.f;  // d ang_f = sum gp * (theta + b_k)  (trained)
-                tb = fmaf(b, tc, tb);
-                ta = eaf * tc;
+            signal_ready(G.ready);                        // -> dgrad1
+            // ---- P8/P9: epilogue 4: encoding backward (+ input gradient), E^T operand, wgrad1 per feature block ----
+            wait_done(G.done, ph_done);
+#pragma unroll 1
+            for (int mb = 0; mb < t.MB; ++mb) {
+                const int f = 128 * mb + row;
+                const int pf = min(128, K1 - 128 * mb);              // features of this block that are MMA rows
+                const bool f_on = row < pf;                          // rows beyond hold garbage
+                const bool fourier = f < F;
+                const float ppa = f_on ? s.pa[f] : 0.f, ppb = f_on ? s.pb[f] : 0.f, ppc = f_on ? s.pc[f] : 0.f;
+                const float ew0 = fourier ? ppa : 0.f, ew1 = fourier ? ppb : 0.f, eaf = (!fourier && f < FIN) ? ppb : 0.f;
+                float ta = 0.f, tb = 0.f, tc = 0.f;                  // sum gp*u0, sum gp*x1, sum gp
+                float gq[16];
+                uint4 ehi[2], elo[2];
+                {
+                    float ev[16];
+                    if (cols_on) {
+                        float v[16], xu[16], x1[16];
+                        tmem_ld16(tw + 32 * mb + c0, v);
+                        const float *x1src = fourier ? G.u1 : G.th;
+#pragma unroll
+                        for (int i4 = 0; i4 < 4; ++i4) {
+                            *reinterpret_cast<float4 *>(xu + 4 * i4) = *reinterpret_cast<const float4 *>(G.u0 + c0 + 4 * i4);
+                            *reinterpret_cast<float4 *>(x1 + 4 * i4) = *reinterpret_cast<const float4 *>(x1src + c0 + 4 * i4);
+                        }
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) {
+                            const float r = reduce_2pi(feature_arg(ppa, ppb, ppc, xu[i], x1[i]));
+                            const float gp = f_on ? v[i] * __cosf(r) : 0.f;
+                            ev[i] = __sinf(r);
+                            gq[i] = gp;
+                            ta = fmaf(gp, xu[i], ta);
+                            tb = fmaf(gp, x1[i], tb);
+                            tc += gp;
+                        }
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) { ev[i] = 0.f; gq[i] = 0.f; }
+                    }
+                    split8(ev, ehi[0], elo[0]);
+                    split8(ev + 8, ehi[1], elo[1]);
+                }
+                if (!fourier) {                                      // heading features: d ang_b = f_k * sum gp,
+                    const float b = f < FIN ? s.ang_b[f - F] : 0.f;  // d ang_f = sum gp * (theta + b_k)  (trained)
+                    tb = fmaf(b, tc, tb);
+                    ta = eaf * tc;
+                }
+                if (mb == 0) { fa0 += ta; fb0 += tb; fc0 += tc; }
+                else { fa1 += ta; fb1 += tb; fc1 += tc; }
+                if (want_gx) {
+                    // gx[n] = (sum_f gp[f,n] * We[f,c]) / sigma ; g_theta[n] = sum_k gp[k,n] * f_k   (reduce over lanes)
+                    float cv[16];
+                    float *dst = G.gx + ((size_t)q * TC_TP + c0 + (lane >> 1)) * 3;
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) {
+                        const float wgt = c == 0 ? ew0 : c == 1 ? ew1 : eaf;
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) cv[i] = gq[i] * wgt;
+                        const float sum = colsum16(cv, lane);
+                        if ((lane & 1) == 0) dst[c] = mb == 0 ? sum : dst[c] + sum;
+                    }
+                }
+                if (want_wgrad) {
+                    if (mb > 0) {                       // wgrad1 of the previous block still reads the scratch region
+                        mbar_wait(G.aux, ph_aux);
+                        ph_aux ^= 1;
+                    }
+                    if (f_on && cols_on) {
+#pragma unroll
+                        for (int o = 0; o < 2; ++o) {
+                            const int off = ((c0 >> 3) + o) * 2048 + (row >> 3) * 128 + (row & 7) * 16;
+                            *reinterpret_cast<uint4 *>(G.rh + off) = ehi[o];
+                            *reinterpret_cast<uint4 *>(G.rl + off) = elo[o];
+                        }
+                    }
+                    signal_ready(G.ready);                // -> wgrad1(mb)
+                    if (mb + 1 >= t.MB) pending_aux = true;
+                }
             }
-            if (mb == 0) { fa0 += ta; fb0 += tb; fc0 += tc; }
-            else { fa1 += ta; fb1 += tb; fc1 += tc; }
             if (want_gx) {
-                // gx[n] = (sum_f gp[f,n] * We[f,c]) / sigma ; g_theta[n] = sum_k gp[k,n] * f_k   (reduce over lanes)
-                float cv[16];
-                float *dst = s.gx + ((size_t)q * TC_TP + c0 + (lane >> 1)) * 3;
+                group_sync(g);
+                if (gt < nv) {
+                    const int n = gt;
+                    float g0 = 0.f, g1 = 0.f, g2 = 0.f;
 #pragma unroll
-                for (int c = 0; c < 3; ++c) {
-                    const float wgt = c == 0 ? ew0 : c == 1 ? ew1 : eaf;
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) cv[i] = gq[i] * wgt;
-                    const float sum = colsum16(cv, lane);
-                    if ((lane & 1) == 0) dst[c] = mb == 0 ? sum : dst[c] + sum;
-                }
-            }
-            if (want_wgrad) {
-                if (mb > 0) {                       // wgrad1 of the previous block still reads the scratch region
-                    mbar_wait(bar_aux, ph_aux);
-                    ph_aux ^= 1;
-                }
-                if (row < pf && cols_on) {
-#pragma unroll
-                    for (int o = 0; o < 2; ++o) {
-                        const int off = ((c0 >> 3) + o) * 2048 + (row >> 3) * 128 + (row & 7) * 16;
-                        *reinterpret_cast<uint4 *>(s.rh + off) = ehi[o];
-                        *reinterpret_cast<uint4 *>(s.rl + off) = elo[o];
+                    for (int qq = 0; qq < 4; ++qq) {
+                        const float *src = G.gx + ((size_t)qq * TC_TP + n) * 3;
+                        g0 += src[0]; g1 += src[1]; g2 += src[2];
                     }
+                    float *out = a.gx_out + ((size_t)p * a.n + n0 + n) * a.x_stride;
+                    out[0] = g0 / d.sigma;
+                    out[1] = g1 / d.sigma;
+                    if (L.in_dim == 3) out[2] = g2;
+                    for (int c = L.in_dim; c < a.x_stride; ++c) out[c] = 0.f;   // pose columns the ONF does not read
                 }
-                fence_proxy_async();
-                fence_before_sync();
-                __syncthreads();
-                if (warp == 0) {                 // warp-uniform: descriptor arithmetic stays on the uniform datapath
-                    fence_after_sync();
-                    const uint32_t lead = elect_one();
-                    const uint32_t idesc = instr_desc_bf16(128, pf, 0, 0);
-                    for (int ks = 0; ks < Nt / 16; ++ks) {
-                        const uint32_t aoff = (uint32_t)(2 * ks) * 128, boff = (uint32_t)(2 * ks) * 2048;
-                        mma3(tmem + TM_DW1 + 128 * mb, desc_kmajor(smem_u32(s.h1h) + aoff, 1024, 128),
-                             desc_kmajor(smem_u32(s.h1l) + aoff, 1024, 128), desc_kmajor(smem_u32(s.rh) + boff, 128, 2048),
-                             desc_kmajor(smem_u32(s.rl) + boff, 128, 2048), idesc, tile > 0 || ks > 0, lead);
-                    }
-                    mma_commit(bar_aux, lead);
-                }
-                if (mb + 1 >= t.MB) pending_aux = true;
             }
+            group_sync(g);             // G.u0/u1/th, zp, gx are rewritten by the group's next tile
         }
-        if (want_gx) {
-            __syncthreads();
-            if (tid < nv) {
-                const int n = tid;
-                float g0 = 0.f, g1 = 0.f, g2 = 0.f;
-#pragma unroll
-                for (int qq = 0; qq < 4; ++qq) {
-                    const float *src = s.gx + ((size_t)qq * TC_TP + n) * 3;
-                    g0 += src[0]; g1 += src[1]; g2 += src[2];
-                }
-                float *out = a.gx_out + ((size_t)p * a.n + n0 + n) * a.x_stride;
-                out[0] = g0 / d.sigma;
-                out[1] = g1 / d.sigma;
-                if (L.in_dim == 3) out[2] = g2;
-                for (int c = L.in_dim; c < a.x_stride; ++c) out[c] = 0.f;   // pose columns the ONF does not read
-            }
+        if (pending_aux) {             // the last wgrad1 of this group
+            mbar_wait(G.aux, ph_aux);
+            ph_aux ^= 1;
         }
-        fence_before_sync();
-        __syncthreads();           // TMEM work columns and s.* scratch are reused by the next tile
     }
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
 
     // ---- weight gradients: TMEM accumulators -> shared memory in blob order -> coalesced Adam / gradient store ----
     if (want_wgrad) {
-        if (pending_aux) {
-            mbar_wait(bar_aux, ph_aux);
-            ph_aux ^= 1;
-        }
-        fence_after_sync();
         // every MMA has completed: the operand buffers are dead, shared memory [0, n_params) floats now holds the
         // gradient of the whole parameter blob (same element order as the fp32 weights)
         float *G = reinterpret_cast<float *>(smem_raw);
         float *red = G + ((L.n_params + 31) & ~31);                    // [10][4][128] partial per-unit sums
         const int np4 = L.n_params / 4;
         for (int i = tid; i < np4; i += TC_THREADS) reinterpret_cast<float4 *>(G)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        {
-            float *r0 = red + cq * 128 + row;
+        const int cq4 = warp >> 2;                                    // drain: 16 worker warps = 4 lane quarters x 4 column slots
+        if (!is_issuer) {
+            float *r0 = red + cq4 * 128 + row;
             r0[0 * 512] = acc_db1; r0[1 * 512] = acc_db2; r0[2 * 512] = acc_dw3;
             r0[3 * 512] = fa0; r0[4 * 512] = fb0; r0[5 * 512] = fc0;
             r0[6 * 512] = fa1; r0[7 * 512] = fb1; r0[8 * 512] = fc1;
-            if (tid < TC_TP) red[9 * 512 + tid] = acc_db3;
+            if (gt < TC_TP) red[9 * 512 + g * TC_TP + gt] = acc_db3;
         }
         __syncthreads();
         // dW1: rows j < H -> mlp.0.weight[j,:], row H -> mlp2.0.weight[0, H:];  dW2: rows i < H -> mlp.2.weight[i,:]
-        for (int ch = cq; ch < K1 / 16; ch += 4) {
+        for (int ch = cq4; ch < (is_issuer ? 0 : K1 / 16); ch += 4) {
             float g[16];
             tmem_ld16(tm_lane + TM_DW1 + 16 * ch, g);
             if (row <= H) {
@@ -684,7 +729,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
                         *reinterpret_cast<float4 *>(dst + 4 * c4) = make_float4(g[4 * c4], g[4 * c4 + 1], g[4 * c4 + 2], g[4 * c4 + 3]);
             }
         }
-        for (int ch = cq; ch < KH / 16; ch += 4) {
+        for (int ch = cq4; ch < (is_issuer ? 0 : KH / 16); ch += 4) {
             float g[16];
             tmem_ld16(tm_lane + TM_DW2 + 16 * ch, g);
             if (row < H) {
@@ -719,7 +764,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
             }
             if (tid == 0) {
                 float g3 = 0.f;
-                for (int i = 0; i < TC_TP; ++i) g3 += red[9 * 512 + i];
+                for (int i = 0; i < 2 * TC_TP; ++i) g3 += red[9 * 512 + i];
                 G[L.off_b_out] = g3;
             }
         }
@@ -800,9 +845,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
     }
     fence_before_sync();
     __syncthreads();
-    if (warp == 1) tmem_dealloc(tmem, 512);
+    if (is_issuer) tmem_dealloc(tmem, 512);
 }
-
 
 // ---- host side ---------------------------------------------------------------------------------------------
 bool onf_tc_supported(const OnfDims &d) {
