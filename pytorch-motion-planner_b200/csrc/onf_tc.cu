@@ -237,12 +237,24 @@ __device__ __forceinline__ void mma3(uint32_t tmem_d, uint64_t ah, uint64_t al, 
     mma_bf16(tmem_d, ah, bl, idesc, 1u, issue);
 }
 
+// K loop of one GEMM: `ksteps` x (three-pass split product), descriptors advanced by constant strides
+__device__ __forceinline__ void mma_kloop(uint32_t tmem_d, uint64_t ah, uint64_t al, uint64_t bh, uint64_t bl, uint32_t a_step,
+                                          uint32_t b_step, int ksteps, uint32_t idesc, bool accumulate, uint32_t issue) {
+    const uint64_t da = a_step >> 4, db = b_step >> 4;
+#pragma unroll 1
+    for (int ks = 0; ks < ksteps; ++ks) {
+        mma3(tmem_d, ah, al, bh, bl, idesc, accumulate || ks > 0, issue);
+        ah += da; al += da; bh += db; bl += db;
+    }
+}
+
 __device__ __forceinline__ void group_sync(int g) { asm volatile("bar.sync %0, %1;" ::"r"(1 + g), "r"(TC_GT) : "memory"); }
 // a worker thread has finished writing MMA operands (generic proxy) / reading TMEM: publish to the MMA warp
 __device__ __forceinline__ void signal_ready(uint64_t *bar) {
     fence_proxy_async();
     fence_before_sync();
-    mbar_arrive(bar);
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0) mbar_arrive(bar);     // one arrival per warp (8 per group), not 256 smem atomics
 }
 __device__ __forceinline__ void wait_done(uint64_t *bar, uint32_t &phase) {
     mbar_wait(bar, phase);
@@ -281,61 +293,42 @@ __device__ __forceinline__ void tc_issue_warp(const OnfTcArgs &a, const TcShared
             const int ph = phase[g];
             if (ph < MB) {
                 // fwd1, feature group ph: D1[j,n] (+)= W1p[j,k] E[n,k]
-                const uint32_t idesc = instr_desc_bf16(128, Nt, 0, 0);
-                const int ks_n = min(8, (K1 - 128 * ph) / 16);
-                for (int ks = 0; ks < ks_n; ++ks) {
-                    const uint32_t aoff = (uint32_t)(16 * ph + 2 * ks) * t.S_colW, boff = (uint32_t)(2 * ks) * S_PT;
-                    mma3(tw, desc_kmajor(w1h + aoff, 128, t.S_colW), desc_kmajor(w1l + aoff, 128, t.S_colW),
-                         desc_kmajor(rh + boff, 128, S_PT), desc_kmajor(rl + boff, 128, S_PT), idesc, ph > 0 || ks > 0, lead);
-                }
+                const uint32_t aoff = (uint32_t)(16 * ph) * t.S_colW;
+                mma_kloop(tw, desc_kmajor(w1h + aoff, 128, t.S_colW), desc_kmajor(w1l + aoff, 128, t.S_colW),
+                          desc_kmajor(rh, 128, S_PT), desc_kmajor(rl, 128, S_PT), 2 * t.S_colW, 2 * S_PT,
+                          min(8, (K1 - 128 * ph) / 16), instr_desc_bf16(128, Nt, 0, 0), ph > 0, lead);
                 mma_commit(ph + 1 < MB ? G.aux : G.done, lead);
             } else if (ph == MB) {
                 // fwd2: D2[i,n] = W2p[i,j] H1[j,n]
-                const uint32_t idesc = instr_desc_bf16(128, Nt, 0, 1);
-                for (int ks = 0; ks < KH / 16; ++ks) {
-                    const uint32_t aoff = (uint32_t)(2 * ks) * t.S_colW, boff = (uint32_t)(2 * ks) * S_PT;
-                    mma3(tw + 32, desc_kmajor(w2h + aoff, 128, t.S_colW), desc_kmajor(w2l + aoff, 128, t.S_colW),
-                         desc_mnmajor(h1h + boff, S_PT, 128), desc_mnmajor(h1l + boff, S_PT, 128), idesc, ks > 0, lead);
-                }
+                mma_kloop(tw + 32, desc_kmajor(w2h, 128, t.S_colW), desc_kmajor(w2l, 128, t.S_colW),
+                          desc_mnmajor(h1h, S_PT, 128), desc_mnmajor(h1l, S_PT, 128), 2 * t.S_colW, 2 * S_PT, KH / 16,
+                          instr_desc_bf16(128, Nt, 0, 1), false, lead);
                 mma_commit(G.done, lead);
             } else if (ph == MB + 1) {
-                // wgrad2 (persistent accumulator) + dgrad2
+                // wgrad2 (persistent accumulator): dW2[i,j] += gH2[i,n] H1[j,n];  dgrad2: gD1[j,n] = W2p[i,j] gH2[i,n]
                 if (want_wgrad) {
-                    const uint32_t idesc = instr_desc_bf16(128, KH, 0, 0);
-                    for (int ks = 0; ks < Nt / 16; ++ks) {
-                        const uint32_t off = (uint32_t)(2 * ks) * 128;
-                        mma3(tmem + TM_DW2, desc_kmajor(rh + off, S_PT, 128), desc_kmajor(rl + off, S_PT, 128),
-                             desc_kmajor(h1h + off, S_PT, 128), desc_kmajor(h1l + off, S_PT, 128), idesc, dw2_started || ks > 0, lead);
-                    }
+                    mma_kloop(tmem + TM_DW2, desc_kmajor(rh, S_PT, 128), desc_kmajor(rl, S_PT, 128), desc_kmajor(h1h, S_PT, 128),
+                              desc_kmajor(h1l, S_PT, 128), 256, 256, Nt / 16, instr_desc_bf16(128, KH, 0, 0), dw2_started, lead);
                     dw2_started = true;
                 }
-                const uint32_t idesc = instr_desc_bf16(128, Nt, 1, 1);
-                for (int ks = 0; ks < KH / 16; ++ks) {
-                    const uint32_t aoff = (uint32_t)(2 * ks) * 128, boff = (uint32_t)(2 * ks) * S_PT;
-                    mma3(tw, desc_mnmajor(w2h + aoff, 128, t.S_colW), desc_mnmajor(w2l + aoff, 128, t.S_colW),
-                         desc_mnmajor(rh + boff, S_PT, 128), desc_mnmajor(rl + boff, S_PT, 128), idesc, ks > 0, lead);
-                }
+                mma_kloop(tw, desc_mnmajor(w2h, 128, t.S_colW), desc_mnmajor(w2l, 128, t.S_colW), desc_mnmajor(rh, S_PT, 128),
+                          desc_mnmajor(rl, S_PT, 128), 256, 2 * S_PT, KH / 16, instr_desc_bf16(128, Nt, 1, 1), false, lead);
                 mma_commit(G.done, lead);
             } else if (ph == MB + 2) {
-                // dgrad1: gE[k,n] for all feature blocks
-                const uint32_t idesc = instr_desc_bf16(128, Nt, 1, 1);
-                for (int mb = 0; mb < MB; ++mb)
-                    for (int ks = 0; ks < KH / 16; ++ks) {
-                        const uint32_t aoff = (uint32_t)(16 * mb) * t.S_colW + (uint32_t)(2 * ks) * 128, boff = (uint32_t)(2 * ks) * S_PT;
-                        mma3(tw + 32 * mb, desc_mnmajor(w1h + aoff, 128, t.S_colW), desc_mnmajor(w1l + aoff, 128, t.S_colW),
-                             desc_mnmajor(h1h + boff, S_PT, 128), desc_mnmajor(h1l + boff, S_PT, 128), idesc, ks > 0, lead);
-                    }
+                // dgrad1: gE[k,n] = W1p[j,k] gH1[j,n] for all feature blocks
+                for (int mb = 0; mb < MB; ++mb) {
+                    const uint32_t aoff = (uint32_t)(16 * mb) * t.S_colW;
+                    mma_kloop(tw + 32 * mb, desc_mnmajor(w1h + aoff, 128, t.S_colW), desc_mnmajor(w1l + aoff, 128, t.S_colW),
+                              desc_mnmajor(h1h, S_PT, 128), desc_mnmajor(h1l, S_PT, 128), 256, 2 * S_PT, KH / 16,
+                              instr_desc_bf16(128, Nt, 1, 1), false, lead);
+                }
                 mma_commit(G.done, lead);
             } else {
                 // wgrad1, feature block mb: dW1[j, 128 mb + f] += gH1[j,n] E[n,f]
                 const int mb = ph - (MB + 3);
-                const int pf = min(128, K1 - 128 * mb);
-                const uint32_t idesc = instr_desc_bf16(128, pf, 0, 0);
-                for (int ks = 0; ks < Nt / 16; ++ks) {
-                    const uint32_t aoff = (uint32_t)(2 * ks) * 128, boff = (uint32_t)(2 * ks) * 2048;
-                    mma3(tmem + TM_DW1 + 128 * mb, desc_kmajor(h1h + aoff, S_PT, 128), desc_kmajor(h1l + aoff, S_PT, 128),
-                         desc_kmajor(rh + boff, 128, 2048), desc_kmajor(rl + boff, 128, 2048), idesc, dw1_started[mb] || ks > 0, lead);
-                }
+                mma_kloop(tmem + TM_DW1 + 128 * mb, desc_kmajor(h1h, S_PT, 128), desc_kmajor(h1l, S_PT, 128),
+                          desc_kmajor(rh, 128, 2048), desc_kmajor(rl, 128, 2048), 256, 4096, Nt / 16,
+                          instr_desc_bf16(128, min(128, K1 - 128 * mb), 0, 0), dw1_started[mb], lead);
                 dw1_started[mb] = true;
                 mma_commit(G.aux, lead);
             }
@@ -371,7 +364,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
     if (tid == 0) {
         mbar_init(s.bars, 1);
         for (int g = 0; g < 2; ++g) {
-            mbar_init(s.bars + 1 + 3 * g, TC_GT);      // ready: every worker of the group arrives
+            mbar_init(s.bars + 1 + 3 * g, TC_GT / 32); // ready: one arrival per worker warp of the group
             mbar_init(s.bars + 2 + 3 * g, 1);          // done: one tcgen05.commit
             mbar_init(s.bars + 3 + 3 * g, 1);          // aux: one tcgen05.commit
         }
