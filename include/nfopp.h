@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define NFOPP_ABI_VERSION 2
+#define NFOPP_ABI_VERSION 3
 #define NFOPP_MAX_LAYERS 8
 
 typedef enum {
@@ -86,11 +86,17 @@ int nfopp_label_grid(const double *poses_dev, int P, int n, int pose_dim, const 
 /* ---- K2: ONF forward / backward with per-problem weights (onf_model.py:33-50) ---------------------- */
 /* weights_dev [P, n_params]; x_dev [P, n, in_dim] float32; count_dev [P] int32 = valid points per problem
  * (NULL => n); z_dev [P, n] logits.
- * `impl`: 0 = auto (tensor when the network shape allows it), 1 = FMA (CUDA-core fp32), 2 = tensor (tcgen05:
- * bf16 hi/lo split operands, fp32 accumulation in TMEM; 2 hidden layers, hidden <= 111, f_in <= 224).
- * `scratch_dev`: device scratch of nfopp_onf_scratch_bytes(cfg, P, impl) bytes (the tensor path keeps a bf16
- * operand copy of the hidden-layer weights there; 0 bytes / NULL for the FMA path). */
+ * `impl`: 0 = auto, 1 = FMA (CUDA-core fp32), 2 = tensor (tcgen05, ONE fused kernel per call: bf16 hi/lo split
+ * operands, fp32 accumulation in TMEM, weights resident in shared memory; 2 hidden layers, hidden <= 111,
+ * f_in <= 224 = the reference's network), 3 = tensor-wide (tcgen05 grouped GEMM per layer with streamed weights,
+ * the same split-bf16 arithmetic: any hidden <= 1024 (multiple of 4), up to NFOPP_MAX_LAYERS layers, any point
+ * count - BASELINE configs 4 and 5).  auto = 2 when the shape fits it, else 3.
+ * `scratch_dev`: device scratch of nfopp_onf_scratch_bytes_n(cfg, P, n, impl, want_bwd) bytes: the tensor paths
+ * keep a bf16 operand copy of the hidden-layer weights there, the wide path also its activation / gradient
+ * operand tiles (~(2*f_in + 2*layers*hidden) * 4 bytes per point); 0 bytes / NULL for the FMA path.
+ * nfopp_onf_scratch_bytes is the n-independent form (impl 1 and 2 only). */
 int nfopp_onf_scratch_bytes(const nfopp_onf_config *cfg, int P, int impl, size_t *bytes);
+int nfopp_onf_scratch_bytes_n(const nfopp_onf_config *cfg, int P, int n, int impl, int want_bwd, size_t *bytes);
 int nfopp_onf_forward(const nfopp_onf_config *cfg, const float *weights_dev, const float *x_dev,
                       const int32_t *count_dev, int P, int n, float *z_dev, int impl, void *scratch_dev,
                       void *stream);
@@ -156,7 +162,7 @@ typedef struct {
     int32_t rng_mode;
     uint64_t seed;
     int32_t max_choice_uniforms;        /* per problem per step, injected mode */
-    int32_t onf_impl;                   /* 0 auto (tensor when the shape allows), 1 FMA, 2 tensor */
+    int32_t onf_impl;                   /* 0 auto, 1 FMA, 2 tensor (fused, reference shape), 3 tensor-wide */
 } nfopp_planner_config;
 
 typedef struct nfopp_engine nfopp_engine;

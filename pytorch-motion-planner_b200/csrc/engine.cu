@@ -64,8 +64,9 @@ int launch_reparam(const EngineDev &e, cudaStream_t s);
 
 // impl 0 = auto: the tensor path whenever the network shape fits it
 static int resolve_impl(const OnfDims &d, int impl, int *out) {
-    NFOPP_REQUIRE(impl >= 0 && impl <= 2, "impl=%d (0 auto, 1 FMA, 2 tensor)", impl);
-    if (impl == 0) impl = onf_tc_supported(d) ? 2 : 1;
+    NFOPP_REQUIRE(impl >= 0 && impl <= 3, "impl=%d (0 auto, 1 FMA, 2 tensor, 3 tensor-wide)", impl);
+    if (impl == 0) impl = onf_tc_supported(d) ? 2 : (onf_wide_supported(d) ? 3 : 1);
+    NFOPP_REQUIRE(impl != 3 || onf_wide_supported(d), "onf(wide): hidden=%d layers=%d unsupported", d.H, d.L);
     NFOPP_REQUIRE(impl != 2 || onf_tc_supported(d),
                   "onf(tensor): needs 2 hidden layers, hidden <= 111, f_in <= 224 (hidden=%d layers=%d)", d.H, d.L);
     NFOPP_REQUIRE(impl != 1 || onf_fma_tile_points(d) != 0, "onf(fma): hidden=%d layers=%d does not fit shared memory", d.H, d.L);
@@ -75,7 +76,7 @@ static int resolve_impl(const OnfDims &d, int impl, int *out) {
 
 // gradient slots per problem
 static int tiles_for(const OnfDims &d, int n, int impl) {
-    if (impl == 2) return 1;
+    if (impl >= 2) return 1;
     int tp = onf_fma_tile_points(d);
     return tp ? (n + tp - 1) / tp : 0;
 }
@@ -109,7 +110,19 @@ extern "C" int nfopp_onf_scratch_bytes(const nfopp_onf_config *cfg, int P, int i
     if (rc) return rc;
     NFOPP_REQUIRE(bytes && P >= 0, "onf_scratch_bytes: bad arguments");
     if ((rc = resolve_impl(d, impl, &impl))) return rc;
+    NFOPP_REQUIRE(impl != 3, "onf(wide): the scratch size depends on the point count - use nfopp_onf_scratch_bytes_n");
     *bytes = impl == 2 ? (size_t)P * onf_tc_packed_bytes(d) : 0;
+    return NFOPP_OK;
+}
+
+extern "C" int nfopp_onf_scratch_bytes_n(const nfopp_onf_config *cfg, int P, int n, int impl, int want_bwd, size_t *bytes) {
+    OnfDims d;
+    int rc = make_onf_dims(cfg, &d);
+    if (rc) return rc;
+    NFOPP_REQUIRE(bytes && P >= 0 && n >= 0, "onf_scratch_bytes_n: bad arguments");
+    if ((rc = resolve_impl(d, impl, &impl))) return rc;
+    if (impl == 3) *bytes = (size_t)P * onf_wide_packed_bytes(d) + onf_wide_workspace_bytes(d, P, n, want_bwd != 0);
+    else *bytes = impl == 2 ? (size_t)P * onf_tc_packed_bytes(d) : 0;
     return NFOPP_OK;
 }
 
@@ -122,6 +135,16 @@ static int onf_api_launch(const OnfDims &d, OnfArgs &a, int P, int impl, void *s
         return onf_fma_launch(a, P, s);
     }
     NFOPP_REQUIRE(scratch, "onf(tensor): scratch_dev missing (nfopp_onf_scratch_bytes)");
+    if (impl == 3) {
+        if ((rc = onf_wide_prepare(d))) return rc;
+        unsigned char *packed = static_cast<unsigned char *>(scratch);
+        if ((rc = onf_wide_pack(d, a.weights, packed, P, s))) return rc;
+        OnfWideExtra x{};
+        x.packed = packed;
+        x.workspace = packed + (size_t)P * onf_wide_packed_bytes(d);
+        x.grad_out = grad_out;
+        return onf_wide_launch(a, x, P, s);
+    }
     if ((rc = onf_tc_prepare(d))) return rc;
     if ((rc = onf_tc_pack(d, a.weights, static_cast<unsigned char *>(scratch), P, s))) return rc;
     OnfTcExtra x{};
@@ -170,7 +193,7 @@ extern "C" int nfopp_onf_reduce_grad(const nfopp_onf_config *cfg, const float *g
     NFOPP_REQUIRE(gpart && grad && P > 0 && n > 0, "onf_reduce_grad: bad arguments");
     if ((rc = resolve_impl(d, impl, &impl))) return rc;
     AdamArgs a{};
-    a.gpart = gpart; a.count = count; a.n = n; a.tp = impl == 2 ? (1 << 30) : onf_fma_tile_points(d);
+    a.gpart = gpart; a.count = count; a.n = n; a.tp = impl >= 2 ? (1 << 30) : onf_fma_tile_points(d);
     a.tiles = tiles_for(d, n, impl);
     a.n_params = d.lay.n_params; a.grad_out = grad;
     return onf_adam_launch(a, P, (cudaStream_t)stream);
@@ -195,7 +218,7 @@ extern "C" int nfopp_onf_adam(const nfopp_onf_config *cfg, float *w, float *m, f
     if ((rc = resolve_impl(d, impl, &impl))) return rc;
     AdamArgs a{};
     a.w = w; a.m = m; a.v = v; a.gpart = gpart; a.count = count; a.n = n;
-    a.tp = impl == 2 ? (1 << 30) : onf_fma_tile_points(d);
+    a.tp = impl >= 2 ? (1 << 30) : onf_fma_tile_points(d);
     a.tiles = tiles_for(d, n, impl); a.n_params = d.lay.n_params;
     adam_scalars(lr, beta1, beta2, eps, step, &a);
     return onf_adam_launch(a, P, (cudaStream_t)stream);
@@ -271,7 +294,10 @@ static int validate(const nfopp_planner_config *c, OnfDims *onf, int *impl) {
     NFOPP_REQUIRE(c->checker_kind != 2 || c->constrained, "rectangle checker needs poses with heading");
     NFOPP_REQUIRE(c->checker_kind != 3 || (c->grid_rows > 1 && c->grid_cols > 1 && c->grid_cell > 0), "grid shape missing");
     NFOPP_REQUIRE(c->rng_mode == 0 || c->rng_mode == 1, "rng_mode=%d", c->rng_mode);
-    return resolve_impl(*onf, c->onf_impl, impl);
+    if ((rc = resolve_impl(*onf, c->onf_impl, impl))) return rc;
+    NFOPP_REQUIRE(*impl != 3 || c->optimize_collision_model_freq == 1,
+                  "onf(wide) in the planner engine needs optimize_collision_model_freq == 1");
+    return NFOPP_OK;
 }
 
 static int build_layout(nfopp_engine *e) {
@@ -283,8 +309,8 @@ static int build_layout(nfopp_engine *e) {
     size_t NTR = (T - 1) + C + NF;
     if (NW > NTR) NTR = NW;
     const size_t NP = e->onf.lay.n_params;
-    e->tile_points = e->impl == 2 ? 64 : onf_fma_tile_points(e->onf);
-    e->tiles = e->impl == 2 ? 1 : (int)((NTR + e->tile_points - 1) / e->tile_points);
+    e->tile_points = e->impl >= 2 ? 64 : onf_fma_tile_points(e->onf);
+    e->tiles = e->impl >= 2 ? 1 : (int)((NTR + e->tile_points - 1) / e->tile_points);
     const bool inj = c.rng_mode == 1;
     const size_t MU = inj ? (c.max_choice_uniforms > 0 ? c.max_choice_uniforms : 16 * C) : 0;
     d.P = (int)P; d.T = (int)T; d.D = (int)D; d.C = (int)C; d.NF = (int)NF; d.NC = (int)NC; d.NTR = (int)NTR; d.NW = (int)NW;
@@ -300,6 +326,14 @@ static int build_layout(nfopp_engine *e) {
         // the tensor path accumulates weight gradients in TMEM and applies Adam in the same kernel: no partials
         add_buffer(e, "onf_gpart", &d.onf_gpart, 'f', 1, 1, 4);
         add_buffer(e, "onf_wp", &d.onf_wp, 'b', P, onf_tc_packed_bytes(e->onf));
+    } else if (e->impl == 3) {
+        // wide path: per-layer grouped GEMMs; one reduced gradient per problem, operand copies of the weights and
+        // one activation workspace shared by the three ONF calls of a step
+        size_t nmax = NTR > NC ? NTR : NC;
+        if (T - 1 > nmax) nmax = T - 1;
+        add_buffer(e, "onf_gpart", &d.onf_gpart, 'f', P, 1, NP);
+        add_buffer(e, "onf_wp", &d.onf_wp, 'b', P, onf_wide_packed_bytes(e->onf));
+        add_buffer(e, "onf_ws", &d.onf_ws, 'b', onf_wide_workspace_bytes(e->onf, (int)P, (int)nmax, true));
     } else {
         add_buffer(e, "onf_gpart", &d.onf_gpart, 'f', P, e->tiles, NP);
     }
@@ -427,7 +461,7 @@ extern "C" int nfopp_engine_create(const nfopp_planner_config *cfg, void *worksp
         delete e;
         return NFOPP_ERR_CUDA;
     }
-    if ((rc = e->impl == 2 ? onf_tc_prepare(e->onf) : onf_fma_prepare(e->onf)) || (rc = resample_prepare(e->dev)) ||
+    if ((rc = e->impl == 3 ? onf_wide_prepare(e->onf) : e->impl == 2 ? onf_tc_prepare(e->onf) : onf_fma_prepare(e->onf)) || (rc = resample_prepare(e->dev)) ||
         (rc = traj_prepare(e->dev))) {
         delete e;
         return rc;
@@ -436,6 +470,9 @@ extern "C" int nfopp_engine_create(const nfopp_planner_config *cfg, void *worksp
     e->sp_dirty = true;
     e->pack_dirty = true;
     e->launches_per_step = e->impl == 2 ? 8 : 9;
+    if (e->impl == 3)       // 5 planner kernels + candidates forward + train (backward, Adam, re-pack) + path forward/input-gradient
+        e->launches_per_step = 5 + onf_wide_launch_count(e->onf, false, false) + onf_wide_launch_count(e->onf, true, true) + 2 +
+                               onf_wide_launch_count(e->onf, true, false);
     *out = e;
     return NFOPP_OK;
 }
@@ -497,8 +534,9 @@ extern "C" int nfopp_engine_set_counter(nfopp_engine *e, int which, int64_t valu
 
 // tensor path: (re)build the bf16 operand copy of the weights if the host may have written them
 static int ensure_packed(nfopp_engine *e, cudaStream_t s) {
-    if (e->impl != 2 || !e->pack_dirty) return NFOPP_OK;
-    int rc = onf_tc_pack(e->onf, e->dev.onf_w, e->dev.onf_wp, e->dev.P, s);
+    if (e->impl < 2 || !e->pack_dirty) return NFOPP_OK;
+    int rc = e->impl == 3 ? onf_wide_pack(e->onf, e->dev.onf_w, e->dev.onf_wp, e->dev.P, s)
+                          : onf_tc_pack(e->onf, e->dev.onf_w, e->dev.onf_wp, e->dev.P, s);
     if (rc) return rc;
     e->pack_dirty = false;
     e->launches += 1;
@@ -507,7 +545,13 @@ static int ensure_packed(nfopp_engine *e, cudaStream_t s) {
 
 // forward / input-gradient ONF launch of the engine through the chosen implementation
 static int engine_onf(nfopp_engine *e, OnfArgs &a, cudaStream_t s) {
-    if (e->impl != 2) return onf_fma_launch(a, e->dev.P, s);
+    if (e->impl == 1) return onf_fma_launch(a, e->dev.P, s);
+    if (e->impl == 3) {
+        OnfWideExtra x{};
+        x.packed = e->dev.onf_wp; x.workspace = e->dev.onf_ws;
+        a.sp = nullptr;
+        return onf_wide_launch(a, x, e->dev.P, s);
+    }
     OnfTcExtra x{};
     x.packed = e->dev.onf_wp;
     return onf_tc_launch(a, x, e->dev.P, s);
@@ -537,7 +581,14 @@ static int enqueue_train(nfopp_engine *e, bool warm, cudaStream_t s, cudaEvent_t
     }
     a.gpart = d.onf_gpart;
     a.sp = warm ? nullptr : d.sp;
-    rc = onf_fma_launch(a, d.P, s);
+    if (e->impl == 3) {
+        OnfWideExtra x{};
+        x.packed = d.onf_wp; x.workspace = d.onf_ws; x.grad_out = d.onf_gpart;
+        a.sp = nullptr;
+        rc = onf_wide_launch(a, x, d.P, s);
+    } else {
+        rc = onf_fma_launch(a, d.P, s);
+    }
     if (rc) return rc;
     if (ev) NFOPP_CHECK_CUDA(cudaEventRecord(ev[0], s));
     AdamArgs ad{};
@@ -548,6 +599,7 @@ static int enqueue_train(nfopp_engine *e, bool warm, cudaStream_t s, cudaEvent_t
     ad.warm = warm;
     rc = onf_adam_launch(ad, d.P, s);
     if (rc) return rc;
+    if (e->impl == 3 && (rc = onf_wide_pack(e->onf, d.onf_w, d.onf_wp, d.P, s))) return rc;    // refresh the operand copies
     if (ev) NFOPP_CHECK_CUDA(cudaEventRecord(ev[1], s));
     return NFOPP_OK;
 }
@@ -615,7 +667,7 @@ extern "C" int nfopp_engine_warmup(nfopp_engine *e, int iterations, void *stream
         if ((rc = launch_tick(e->dev, true, s))) return rc;
         e->host_sp.onf_step += 1;
         e->warm_iterations_done += 1;
-        e->launches += e->impl == 2 ? 4 : 5;
+        e->launches += e->impl == 2 ? 4 : e->impl == 3 ? 5 + onf_wide_launch_count(e->onf, true, true) : 5;
     }
     host_step_params(e);
     return NFOPP_OK;

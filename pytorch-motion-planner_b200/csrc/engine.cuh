@@ -37,7 +37,8 @@ struct EngineDev {
     // state
     StepParams *sp;
     float *onf_w, *onf_m, *onf_v, *onf_gpart;
-    unsigned char *onf_wp;                  // tensor path: bf16 hi/lo operand copy of the hidden-layer weights
+    unsigned char *onf_wp;                  // tensor paths: bf16 hi/lo operand copy of the hidden-layer weights
+    unsigned char *onf_ws;                  // wide path: activation / gradient operand tiles
     float *traj, *traj_m, *traj_v, *prev_traj, *lam, *mu, *start, *goal;
     double *buf_pos, *buf_age;
     int32_t *buf_n;

@@ -50,6 +50,20 @@ int onf_tc_prepare(const OnfDims &d);
 int onf_tc_pack(const OnfDims &d, const float *weights, unsigned char *packed, int P, cudaStream_t stream);
 int onf_tc_launch(const OnfArgs &a, const OnfTcExtra &x, int P, cudaStream_t stream);
 
+// wide / deep networks and large point sets (onf_wide.cu): per-layer grouped GEMMs on tcgen05 with streamed weights
+struct OnfWideExtra {
+    const unsigned char *packed;   // [P, onf_wide_packed_bytes] bf16 hi/lo operand copies (forward and input-gradient layouts)
+    unsigned char *workspace;      // onf_wide_workspace_bytes(d, P, n, want_bwd): activation / gradient operand tiles
+    float *grad_out;               // [P, n_params] weight gradient, or null
+};
+bool onf_wide_supported(const OnfDims &d);
+size_t onf_wide_packed_bytes(const OnfDims &d);     // per problem (256-byte multiple)
+size_t onf_wide_workspace_bytes(const OnfDims &d, int P, int n, bool want_bwd);
+int onf_wide_prepare(const OnfDims &d);
+int onf_wide_pack(const OnfDims &d, const float *weights, unsigned char *packed, int P, cudaStream_t stream);
+int onf_wide_launch(const OnfArgs &a, const OnfWideExtra &x, int P, cudaStream_t stream);
+int onf_wide_launch_count(const OnfDims &d, bool want_bwd, bool want_wgrad);
+
 int onf_fma_tile_points(const OnfDims &d);          // 32, 16 or 0 (does not fit)
 int onf_fma_prepare(const OnfDims &d);               // one-time kernel attributes (outside graph capture)
 int onf_fma_launch(OnfArgs a, int P, cudaStream_t stream);

@@ -1,0 +1,975 @@
+// onf_wide.cu - K2 for WIDE / DEEP fields and LARGE point sets (BASELINE configs 4 and 5: hidden 64..512, up to
+// 8 hidden layers, 2^8..2^24 points per weight set): every dense contraction of ONF.forward (onf_model.py:33-50)
+// and of its autograd backward is a grouped GEMM on tcgen05 with the POINT index on the UMMA M axis (128 TMEM
+// lanes = 128 points) and the layer width on N (<= 256 per tile):
+//
+//   fwd   l : H_l [pt, out] = relu(sum_in  H_{l-1}[pt, in] W_l[out, in] + b_l)   A = H_{l-1} (K-major)  B = W_l (K-major)
+//   dgrad l : G_{l-1}[pt,in] = 1[H_{l-1}>0] sum_out G_l[pt,out] W_l[out,in]      A = G_l     (K-major)  B = W_l (MN-major)
+//   wgrad l : dW_l[out, in] = sum_pt G_l[pt, out] H_{l-1}[pt, in]                A = G_l     (MN-major) B = H_{l-1} (MN-major)
+//
+// (the encoder gradients, the output-layer gradient and every bias gradient are wgrad jobs too: B = [u0,u1,theta,1],
+// B = dL/dz, B = ones).  Weights do not fit shared memory at these widths, so they are STREAMED: a producer warp
+// issues bulk async copies (TMA) of K-chunks of the packed weights and of the activation tiles into a 4-stage ring,
+// one warp issues the MMAs, four warps run the epilogue out of a double-buffered TMEM accumulator (bias + ReLU +
+// bf16 hi/lo split -> the next layer's operand, or ReLU mask, or fp32 gradient).  Kernels are persistent (one CTA
+// per SM walks a list of tiles).
+//
+// Precision: as in onf_tc.cu every fp32 operand is a bf16 hi + bf16 lo pair and every product three kind::f16
+// MMAs accumulated in fp32 (~3e-6 relative).
+//
+// Operand storage in global memory = the shared-memory layout (SWIZZLE_NONE core blocks, tc05.cuh), so a stage is
+// a handful of contiguous bulk copies:
+//   activations [P][n_pad/64 tiles][hi|lo][C/8 column octets][64 points][8 columns] bf16      (tile = C*256 bytes)
+//   Wf_l (fwd)  [n-tile of 256 out][hi|lo][in/8 octets][out rows][8 in]                       K-chunk contiguous
+//   Wd_l (dgrad)[n-tile of 256 in ][hi|lo][out/8 octets][in/8 octets][8 out][8 in]            K-chunk contiguous
+#include "onf.cuh"
+#include "tc05.cuh"
+
+namespace nfopp {
+using namespace tc05;
+
+namespace {
+
+constexpr int WG_THREADS = 192;          // warp 0: producer, warp 1: MMA issue + TMEM owner, warps 2..5: epilogue
+constexpr int WG_KC = 32;                // K per stage (fwd / dgrad)
+constexpr int WG_STAGES = 4;
+constexpr int WG_NT = 256;               // N per tile
+constexpr int WG_A_STAGE = 128 * WG_KC * 4;       // 128 points x KC x (hi + lo)
+constexpr int WG_B_STAGE = WG_NT * WG_KC * 4;
+constexpr int WG_STAGE = WG_A_STAGE + WG_B_STAGE;
+constexpr int WG_SMEM = WG_STAGES * WG_STAGE + 256;
+
+constexpr int WW_STAGES = 2;             // wgrad: one stage = one 64-point tile of A (128 columns) and B (<= 256 columns)
+constexpr int WW_A_STAGE = 128 * 64 * 4;
+constexpr int WW_B_STAGE = WG_NT * 64 * 4;
+constexpr int WW_STAGE = WW_A_STAGE + WW_B_STAGE;
+constexpr int WW_ONES = 2048;            // [2 octets][64 points][8] bf16 1.0
+constexpr int WW_SMEM = WW_STAGES * WW_STAGE + WW_ONES + 256;
+
+__host__ __device__ inline int ru16i(int x) { return (x + 15) / 16 * 16; }
+
+struct WideDims {
+    int F, A, FIN, H, L, K1, Hp;
+    int kin[NFOPP_MAX_LAYERS];            // padded input width of layer l
+    int kin_real[NFOPP_MAX_LAYERS];
+    size_t wf_off[NFOPP_MAX_LAYERS], wd_off[NFOPP_MAX_LAYERS];
+    size_t packed_bytes;
+};
+
+inline bool make_wide_dims(const OnfDims &d, WideDims *out) {
+    WideDims w{};
+    w.F = d.lay.f_pos; w.A = d.lay.n_angle; w.FIN = d.lay.f_in; w.H = d.H; w.L = d.L;
+    w.K1 = ru16i(w.FIN); w.Hp = ru16i(w.H);
+    size_t off = 0;
+    for (int l = 0; l < w.L; ++l) {
+        w.kin[l] = l == 0 ? w.K1 : w.Hp;
+        w.kin_real[l] = l == 0 ? w.FIN : w.H;
+        const size_t bytes = (size_t)w.Hp * w.kin[l] * 4;
+        w.wf_off[l] = off; off += bytes;
+        w.wd_off[l] = off; off += bytes;
+    }
+    w.packed_bytes = off;
+    *out = w;
+    return w.Hp <= 1024 && w.L >= 1 && w.L <= NFOPP_MAX_LAYERS && (w.H % 4) == 0;
+}
+
+// sin of the feature argument, the same arithmetic as onf_tc.cu (phase folded into pc; cos = sin(. + pi/2))
+__device__ __forceinline__ float w_reduce_2pi(float x) {
+    const float k = rintf(x * 0.15915494309189535f);
+    float r = fmaf(k, -6.2831854820251465f, x);
+    return fmaf(k, 1.7484555e-7f, r);
+}
+struct FeatParams { float pa[8], pb[8], pc[8]; };
+// parameters of features 8*co .. 8*co+7 of problem blob W
+__device__ __forceinline__ void load_feat_params(const float *W, const OnfDims &d, int co, FeatParams &fp) {
+    const nfopp_onf_layout &L = d.lay;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int f = co * 8 + i;
+        float pa = 0.f, pb = 0.f, pc = 0.f;
+        if (f < L.f_pos) {
+            pa = __ldg(W + L.off_enc_w + 2 * f);
+            pb = __ldg(W + L.off_enc_w + 2 * f + 1);
+            pc = __ldg(W + L.off_enc_b + f) + ((d.use_cos && f >= 100) ? 1.57079632679489662f : 0.f);
+        } else if (f < L.f_in) {
+            const int k = f - L.f_pos;
+            const float b = __ldg(W + L.off_ang_b + k), fr = __ldg(W + L.off_ang_f + k);
+            pb = fr;
+            pc = fmaf(b, fr, k >= L.n_angle / 2 ? 1.57079632679489662f : 0.f);
+        }
+        fp.pa[i] = pa; fp.pb[i] = pb; fp.pc[i] = pc;
+    }
+}
+
+__device__ __forceinline__ void unpack8(const uint4 &hi, const uint4 &lo, float *v) {
+    const uint32_t h[4] = {hi.x, hi.y, hi.z, hi.w}, l[4] = {lo.x, lo.y, lo.z, lo.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        v[2 * i] = __uint_as_float(h[i] << 16) + __uint_as_float(l[i] << 16);
+        v[2 * i + 1] = __uint_as_float(h[i] & 0xFFFF0000u) + __uint_as_float(l[i] & 0xFFFF0000u);
+    }
+}
+
+// ---- fp32 blob -> packed operand copies ------------------------------------------------------------------------
+struct WidePackArgs {
+    OnfDims d;
+    WideDims w;
+    const float *weights;
+    unsigned char *packed;
+};
+
+__global__ void __launch_bounds__(256) wide_pack_kernel(const WidePackArgs a) {
+    const int p = blockIdx.y;
+    const WideDims &w = a.w;
+    const float *W = a.weights + (size_t)p * a.d.lay.n_params;
+    unsigned char *out = a.packed + (size_t)p * ((w.packed_bytes + 255) / 256 * 256);
+    const int gid = blockIdx.x * blockDim.x + threadIdx.x, gstride = gridDim.x * blockDim.x;
+    for (int l = 0; l < w.L; ++l) {
+        const int K = w.kin[l], kr = w.kin_real[l], items = w.Hp * (K / 8);
+        for (int item = gid; item < items; item += gstride) {
+            const int o = item / (K / 8), io = item - o * (K / 8);
+            float v[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                const int i = io * 8 + e;
+                v[e] = (o < w.H && i < kr) ? W[a.d.lay.off_w[l] + (size_t)o * kr + i] : 0.f;
+            }
+            uint4 hi, lo;
+            split8(v, hi, lo);
+            {   // Wf: n-tile over out
+                const int nt = o / WG_NT, ow = min(WG_NT, w.Hp - nt * WG_NT), oo = o - nt * WG_NT;
+                unsigned char *b = out + w.wf_off[l] + (size_t)nt * WG_NT * K * 4;
+                const size_t off = (size_t)io * ow * 16 + (size_t)oo * 16;
+                *reinterpret_cast<uint4 *>(b + off) = hi;
+                *reinterpret_cast<uint4 *>(b + (size_t)K * ow * 2 + off) = lo;
+            }
+            {   // Wd: n-tile over in
+                const int i0 = io * 8, nt = i0 / WG_NT, iw = min(WG_NT, K - nt * WG_NT), ii = i0 - nt * WG_NT;
+                unsigned char *b = out + w.wd_off[l] + (size_t)nt * WG_NT * w.Hp * 4;
+                const size_t off = (size_t)(o / 8) * iw * 16 + (size_t)(ii / 8) * 128 + (o % 8) * 16;
+                *reinterpret_cast<uint4 *>(b + off) = hi;
+                *reinterpret_cast<uint4 *>(b + (size_t)w.Hp * iw * 2 + off) = lo;
+            }
+        }
+    }
+}
+
+// ---- encoding: x -> E tiles (+ U16 = [u0, u1, theta, 1] for the encoder gradients) -------------------------------
+struct WideEncArgs {
+    OnfDims d;
+    const float *weights, *x;
+    const int32_t *count;
+    int n, x_stride, T64, K1;
+    unsigned char *E, *U16;      // U16 may be null
+};
+
+__global__ void __launch_bounds__(256) wide_enc_kernel(const WideEncArgs a) {
+    const int p = blockIdx.y, t = blockIdx.x, tid = threadIdx.x;
+    const nfopp_onf_layout &L = a.d.lay;
+    const float *W = a.weights + (size_t)p * L.n_params;
+    const int cnt = a.count ? a.count[p] : a.n;
+    __shared__ float su0[64], su1[64], sth[64];
+    if (tid < 64) {
+        const int idx = t * 64 + tid;
+        float x0 = 0.f, x1 = 0.f, x2 = 0.f;
+        if (idx < cnt) {
+            const float *xp = a.x + ((size_t)p * a.n + idx) * a.x_stride;
+            x0 = xp[0]; x1 = xp[1];
+            if (L.in_dim == 3) x2 = xp[2];
+        }
+        su0[tid] = (x0 - a.d.mean) / a.d.sigma;
+        su1[tid] = (x1 - a.d.mean) / a.d.sigma;
+        sth[tid] = x2;
+    }
+    __syncthreads();
+    const size_t tile = (size_t)p * a.T64 + t;
+    unsigned char *Et = a.E + tile * a.K1 * 256;
+    const int nco = a.K1 / 8;
+    for (int item = tid; item < nco * 64; item += 256) {
+        const int co = item >> 6, pt = item & 63;
+        const bool valid = t * 64 + pt < cnt;
+        FeatParams fp;
+        load_feat_params(W, a.d, co, fp);
+        const float u0 = su0[pt], u1 = su1[pt], th = sth[pt];
+        float e[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int f = co * 8 + i;
+            const float arg = fmaf(f < L.f_pos ? u1 : th, fp.pb[i], fmaf(u0, fp.pa[i], fp.pc[i]));
+            e[i] = (valid && f < L.f_in) ? __sinf(w_reduce_2pi(arg)) : 0.f;
+        }
+        uint4 hi, lo;
+        split8(e, hi, lo);
+        *reinterpret_cast<uint4 *>(Et + co * 1024 + pt * 16) = hi;
+        *reinterpret_cast<uint4 *>(Et + a.K1 * 128 + co * 1024 + pt * 16) = lo;
+    }
+    if (a.U16 && tid < 128) {
+        const int co = tid >> 6, pt = tid & 63;
+        const bool valid = t * 64 + pt < cnt;
+        float e[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        if (co == 0 && valid) { e[0] = su0[pt]; e[1] = su1[pt]; e[2] = sth[pt]; e[3] = 1.f; }
+        uint4 hi, lo;
+        split8(e, hi, lo);
+        unsigned char *Ut = a.U16 + tile * 16 * 256;
+        *reinterpret_cast<uint4 *>(Ut + co * 1024 + pt * 16) = hi;
+        *reinterpret_cast<uint4 *>(Ut + 16 * 128 + co * 1024 + pt * 16) = lo;
+    }
+}
+
+// ---- fwd / dgrad GEMM ------------------------------------------------------------------------------------------
+struct WideGemmArgs {
+    const unsigned char *A;       // activations in: [P][T64][CA*256]
+    int CA;
+    const unsigned char *Wpk;     // packed weights of this layer (problem 0); problems are w_stride bytes apart
+    size_t w_stride;
+    int K;                        // reduction length (multiple of 16)
+    int Nfull;                    // output width (multiple of 16) = column count of Out
+    unsigned char *Out;
+    const float *weights;         // fp32 blobs [P][n_params]
+    int n_params;
+    int bias_off, n_valid;        // fwd: bias offset in the blob, real output width
+    const unsigned char *Mask;    // dgrad: H_{l-1} tiles (ReLU mask) or null
+    const float *gbar;            // dgrad of layer 0: + gbar[pt] * W[skip_off + col], col < skip_n   (skip connection)
+    int skip_off, skip_n;
+    int P, T64;
+};
+
+__device__ __forceinline__ void wmma3(uint32_t tmem_d, uint64_t ah, uint64_t al, uint64_t bh, uint64_t bl, uint32_t idesc,
+                                      bool accumulate, uint32_t issue) {
+    mma_bf16(tmem_d, ah, bh, idesc, accumulate ? 1u : 0u, issue);
+    mma_bf16(tmem_d, al, bh, idesc, 1u, issue);
+    mma_bf16(tmem_d, ah, bl, idesc, 1u, issue);
+}
+
+// MODE 0: forward layer, 1: input-gradient layer
+template <int MODE>
+__global__ void __launch_bounds__(WG_THREADS, 1) wide_gemm_kernel(const WideGemmArgs a) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + WG_STAGES * WG_STAGE);
+    uint64_t *full = bars, *empty = bars + WG_STAGES, *tfull = bars + 2 * WG_STAGES, *tempty = tfull + 2;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tempty + 2);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int NTL = (a.Nfull + WG_NT - 1) / WG_NT, RB = a.T64 / 2;
+    const int items = a.P * RB * NTL;
+    const int nstages = (a.K + WG_KC - 1) / WG_KC;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < WG_STAGES; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 1); }
+        for (int b = 0; b < 2; ++b) { mbar_init(tfull + b, 1); mbar_init(tempty + b, 4); }
+        fence_mbar_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_slot, 512);
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp == 0) {
+        // ---------------- producer: bulk copies of the A (activation) and B (weight) K-chunks ----------------
+        uint32_t it = 0;
+        for (int item = blockIdx.x; item < items; item += gridDim.x) {
+            const int nt = item % NTL, rb = (item / NTL) % RB, p = item / (NTL * RB);
+            const int NTw = min(WG_NT, a.Nfull - nt * WG_NT);
+            const unsigned char *At = a.A + ((size_t)p * a.T64 + 2 * rb) * a.CA * 256;
+            const unsigned char *Wp = a.Wpk + (size_t)p * a.w_stride + (size_t)nt * WG_NT * a.K * 4;
+            for (int st = 0; st < nstages; ++st, ++it) {
+                const int s = it % WG_STAGES;
+                mbar_wait(empty + s, ((it / WG_STAGES) & 1) ^ 1);
+                const int k0 = st * WG_KC, kc = min(WG_KC, a.K - k0), nj = kc / 8;
+                unsigned char *As = smem + s * WG_STAGE, *Bs = As + WG_A_STAGE;
+                if (lane == 0) mbar_expect_tx(full + s, (uint32_t)(128 * kc * 4 + NTw * kc * 4));
+                __syncwarp();
+                if (lane < 4 * nj) {
+                    const int j = lane % nj, pl = (lane / nj) & 1, t = lane / (2 * nj);
+                    bulk_g2s(As + pl * (WG_A_STAGE / 2) + j * 2048 + t * 1024,
+                             At + (size_t)t * a.CA * 256 + (size_t)pl * a.CA * 128 + (size_t)(k0 / 8 + j) * 1024, 1024, full + s);
+                } else if (lane >= 16 && lane < 18) {
+                    const int pl = lane - 16;
+                    bulk_g2s(Bs + pl * (WG_B_STAGE / 2), Wp + (size_t)pl * a.K * NTw * 2 + (size_t)(k0 / 8) * NTw * 16,
+                             (uint32_t)(kc * NTw * 2), full + s);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ---------------- MMA issue ----------------
+        const uint32_t lead = elect_one();
+        uint32_t it = 0, tile_it = 0;
+        for (int item = blockIdx.x; item < items; item += gridDim.x, ++tile_it) {
+            const int nt = item % NTL;
+            const int NTw = min(WG_NT, a.Nfull - nt * WG_NT);
+            const uint32_t buf = tile_it & 1;
+            mbar_wait(tempty + buf, ((tile_it >> 1) & 1) ^ 1);
+            fence_after_sync();
+            const uint32_t d_tmem = tmem + buf * 256;
+            const uint32_t idesc = instr_desc_bf16(128, NTw, 0, MODE == 1 ? 1 : 0);
+            const uint32_t bstep = 2u * NTw * 16u;
+            for (int st = 0; st < nstages; ++st, ++it) {
+                const int s = it % WG_STAGES;
+                mbar_wait(full + s, (it / WG_STAGES) & 1);
+                fence_after_sync();
+                const int kc = min(WG_KC, a.K - st * WG_KC);
+                const uint32_t As = smem_u32(smem + s * WG_STAGE), Bs = As + WG_A_STAGE;
+                for (int ks = 0; ks < kc / 16; ++ks) {
+                    const uint64_t ah = desc_kmajor(As + ks * 4096, 128, 2048);
+                    const uint64_t al = desc_kmajor(As + WG_A_STAGE / 2 + ks * 4096, 128, 2048);
+                    uint64_t bh, bl;
+                    if (MODE == 0) {
+                        bh = desc_kmajor(Bs + ks * bstep, 128, NTw * 16);
+                        bl = desc_kmajor(Bs + WG_B_STAGE / 2 + ks * bstep, 128, NTw * 16);
+                    } else {
+                        bh = desc_mnmajor(Bs + ks * bstep, NTw * 16, 128);
+                        bl = desc_mnmajor(Bs + WG_B_STAGE / 2 + ks * bstep, NTw * 16, 128);
+                    }
+                    wmma3(d_tmem, ah, al, bh, bl, idesc, st > 0 || ks > 0, lead);
+                }
+                mma_commit(empty + s, lead);
+            }
+            mma_commit(tfull + buf, lead);
+        }
+    } else {
+        // ---------------- epilogue: TMEM -> bias/ReLU or mask -> bf16 hi/lo operand tiles in global memory ----------------
+        const int q = warp & 3;
+        uint32_t tile_it = 0;
+        for (int item = blockIdx.x; item < items; item += gridDim.x, ++tile_it) {
+            const int nt = item % NTL, rb = (item / NTL) % RB, p = item / (NTL * RB);
+            const int NTw = min(WG_NT, a.Nfull - nt * WG_NT);
+            const uint32_t buf = tile_it & 1;
+            mbar_wait(tfull + buf, (tile_it >> 1) & 1);
+            fence_after_sync();
+            const int row = q * 32 + lane, r = row & 63;
+            const size_t tile = (size_t)p * a.T64 + 2 * rb + (row >> 6);
+            unsigned char *Ot = a.Out + tile * a.Nfull * 256;
+            const unsigned char *Mt = (MODE == 1 && a.Mask) ? a.Mask + tile * a.Nfull * 256 : nullptr;
+            const float *Wb = a.weights + (size_t)p * a.n_params;
+            const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + buf * 256;
+            float gb = 0.f;
+            if (MODE == 1 && a.gbar) gb = a.gbar[((size_t)p * a.T64 + 2 * rb) * 64 + row];
+            for (int c0 = 0; c0 < NTw; c0 += 16) {
+                float v[16];
+                tmem_ld16(taddr + c0, v);
+                const int col0 = nt * WG_NT + c0;
+                if (MODE == 0) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        const int col = col0 + i;
+                        v[i] = col < a.n_valid ? fmaxf(v[i] + __ldg(Wb + a.bias_off + col), 0.f) : 0.f;
+                    }
+                } else {
+                    if (a.gbar) {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) {
+                            const int col = col0 + i;
+                            if (col < a.skip_n) v[i] = fmaf(gb, __ldg(Wb + a.skip_off + col), v[i]);
+                        }
+                    }
+                    if (Mt) {
+                        const uint4 m0 = *reinterpret_cast<const uint4 *>(Mt + (col0 / 8) * 1024 + r * 16);
+                        const uint4 m1 = *reinterpret_cast<const uint4 *>(Mt + (col0 / 8 + 1) * 1024 + r * 16);
+                        const uint32_t mw[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) {
+                            const uint32_t bits = (mw[i >> 1] >> ((i & 1) * 16)) & 0x7FFFu;
+                            v[i] = bits != 0 ? v[i] : 0.f;
+                        }
+                    }
+                }
+                uint4 h0, l0, h1, l1;
+                split8(v, h0, l0);
+                split8(v + 8, h1, l1);
+                unsigned char *o = Ot + (col0 / 8) * 1024 + r * 16;
+                *reinterpret_cast<uint4 *>(o) = h0;
+                *reinterpret_cast<uint4 *>(o + 1024) = h1;
+                *reinterpret_cast<uint4 *>(o + a.Nfull * 128) = l0;
+                *reinterpret_cast<uint4 *>(o + a.Nfull * 128 + 1024) = l1;
+            }
+            fence_before_sync();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty + buf);
+        }
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem, 512);
+}
+
+// ---- weight-gradient GEMM: dst[m, j] (+)= sum_pt A[pt, m] B[pt, j] ------------------------------------------------
+struct WideWgradArgs {
+    const unsigned char *A;
+    int CA;                      // columns of A (M, walked in blocks of 128)
+    const unsigned char *B;
+    int CB;                      // columns of B (N, walked in tiles of 256)
+    float *dst;                  // [P] x dst_pstride floats
+    size_t dst_pstride;
+    int dst_off, dst_ld, rows_valid, cols_valid;
+    int bias_off;                // >= 0: one more N tile with B = ones -> dst[bias_off + m] (+)= sum_pt A[pt, m]
+    int P, T64, splits;
+};
+
+__global__ void __launch_bounds__(WG_THREADS, 1) wide_wgrad_kernel(const WideWgradArgs a) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    unsigned char *ones = smem + WW_STAGES * WW_STAGE;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(ones + WW_ONES);
+    uint64_t *full = bars, *empty = bars + WW_STAGES, *tfull = bars + 2 * WW_STAGES, *tempty = tfull + 1;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tempty + 1);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int MB = (a.CA + 127) / 128, NTL = (a.CB + WG_NT - 1) / WG_NT, NTT = NTL + (a.bias_off >= 0 ? 1 : 0);
+    const int tps = (a.T64 + a.splits - 1) / a.splits;        // 64-point tiles per split
+    const int items = a.P * MB * NTT * a.splits;
+    for (int i = threadIdx.x; i < WW_ONES / 4; i += WG_THREADS) reinterpret_cast<uint32_t *>(ones)[i] = 0x3F803F80u;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < WW_STAGES; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 1); }
+        mbar_init(tfull, 1);
+        mbar_init(tempty, 4);
+        fence_mbar_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_slot, 256);
+    fence_proxy_async();
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem = *tmem_slot;
+
+    // item -> (p, mb, nt, split); split fastest so the splits of one output tile run concurrently on different SMs
+    auto decode = [&](int item, int &p, int &mb, int &nt, int &t0, int &t1) {
+        const int sp = item % a.splits;
+        nt = (item / a.splits) % NTT;
+        mb = (item / (a.splits * NTT)) % MB;
+        p = item / (a.splits * NTT * MB);
+        t0 = sp * tps;
+        t1 = min(a.T64, t0 + tps);
+    };
+
+    if (warp == 0) {
+        uint32_t it = 0;
+        for (int item = blockIdx.x; item < items; item += gridDim.x) {
+            int p, mb, nt, t0, t1;
+            decode(item, p, mb, nt, t0, t1);
+            const bool bias_tile = nt == NTL;
+            const int MA = min(128, a.CA - 128 * mb), NB = bias_tile ? 0 : min(WG_NT, a.CB - nt * WG_NT);
+            for (int t = t0; t < t1; ++t, ++it) {
+                const int s = it % WW_STAGES;
+                mbar_wait(empty + s, ((it / WW_STAGES) & 1) ^ 1);
+                unsigned char *As = smem + s * WW_STAGE, *Bs = As + WW_A_STAGE;
+                const size_t tile = (size_t)p * a.T64 + t;
+                if (lane == 0) mbar_expect_tx(full + s, (uint32_t)((MA + NB) * 64 * 4));
+                __syncwarp();
+                if (lane < 2) {
+                    bulk_g2s(As + lane * (WW_A_STAGE / 2), a.A + tile * a.CA * 256 + (size_t)lane * a.CA * 128 + (size_t)mb * 16 * 1024,
+                             (uint32_t)(MA * 128), full + s);
+                } else if (lane < 4 && NB > 0) {
+                    const int pl = lane - 2;
+                    bulk_g2s(Bs + pl * (WW_B_STAGE / 2), a.B + tile * a.CB * 256 + (size_t)pl * a.CB * 128 + (size_t)nt * 32 * 1024,
+                             (uint32_t)(NB * 128), full + s);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        const uint32_t lead = elect_one();
+        uint32_t it = 0, tile_it = 0;
+        const uint32_t ones_u = smem_u32(ones);
+        for (int item = blockIdx.x; item < items; item += gridDim.x, ++tile_it) {
+            int p, mb, nt, t0, t1;
+            decode(item, p, mb, nt, t0, t1);
+            const bool bias_tile = nt == NTL;
+            const int NB = bias_tile ? 16 : min(WG_NT, a.CB - nt * WG_NT);
+            mbar_wait(tempty, (tile_it & 1) ^ 1);
+            fence_after_sync();
+            const uint32_t idesc = instr_desc_bf16(128, NB, 1, 1);
+            bool started = false;
+            for (int t = t0; t < t1; ++t, ++it) {
+                const int s = it % WW_STAGES;
+                mbar_wait(full + s, (it / WW_STAGES) & 1);
+                fence_after_sync();
+                const uint32_t As = smem_u32(smem + s * WW_STAGE), Bs = As + WW_A_STAGE;
+#pragma unroll
+                for (int ks = 0; ks < 4; ++ks) {
+                    const uint64_t ah = desc_mnmajor(As + ks * 256, 128, 1024);
+                    const uint64_t al = desc_mnmajor(As + WW_A_STAGE / 2 + ks * 256, 128, 1024);
+                    if (bias_tile) {
+                        const uint64_t bo = desc_mnmajor(ones_u + ks * 256, 128, 1024);
+                        mma_bf16(tmem, ah, bo, idesc, started ? 1u : 0u, lead);
+                        mma_bf16(tmem, al, bo, idesc, 1u, lead);
+                    } else {
+                        const uint64_t bh = desc_mnmajor(Bs + ks * 256, 128, 1024);
+                        const uint64_t bl = desc_mnmajor(Bs + WW_B_STAGE / 2 + ks * 256, 128, 1024);
+                        wmma3(tmem, ah, al, bh, bl, idesc, started, lead);
+                    }
+                    started = true;
+                }
+                mma_commit(empty + s, lead);
+            }
+            mma_commit(tfull, lead);
+        }
+    } else {
+        const int q = warp & 3;
+        uint32_t tile_it = 0;
+        for (int item = blockIdx.x; item < items; item += gridDim.x, ++tile_it) {
+            int p, mb, nt, t0, t1;
+            decode(item, p, mb, nt, t0, t1);
+            const bool bias_tile = nt == NTL;
+            const int NB = bias_tile ? 16 : min(WG_NT, a.CB - nt * WG_NT);
+            mbar_wait(tfull, tile_it & 1);
+            fence_after_sync();
+            const int m = mb * 128 + q * 32 + lane;
+            float *D = a.dst + (size_t)p * a.dst_pstride;
+            const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16);
+            const bool has_work = t1 > t0;
+            for (int c0 = 0; c0 < NB; c0 += 16) {
+                float v[16];
+                tmem_ld16(taddr + c0, v);
+                if (m >= a.rows_valid || !has_work) continue;
+                if (bias_tile) {
+                    if (c0 == 0) {
+                        if (a.splits > 1) atomicAdd(D + a.bias_off + m, v[0]);
+                        else D[a.bias_off + m] = v[0];
+                    }
+                    continue;
+                }
+                const int j0 = nt * WG_NT + c0;
+                float *drow = D + a.dst_off + (size_t)m * a.dst_ld + j0;
+                if (a.splits > 1) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i)
+                        if (j0 + i < a.cols_valid) atomicAdd(drow + i, v[i]);
+                } else if ((a.dst_ld & 3) == 0 && (a.dst_off & 3) == 0) {
+#pragma unroll
+                    for (int i4 = 0; i4 < 4; ++i4)
+                        if (j0 + 4 * i4 + 3 < a.cols_valid)
+                            *reinterpret_cast<float4 *>(drow + 4 * i4) = make_float4(v[4 * i4], v[4 * i4 + 1], v[4 * i4 + 2], v[4 * i4 + 3]);
+                        else
+                            for (int i = 4 * i4; i < 4 * i4 + 4; ++i)
+                                if (j0 + i < a.cols_valid) drow[i] = v[i];
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i)
+                        if (j0 + i < a.cols_valid) drow[i] = v[i];
+                }
+            }
+            fence_before_sync();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty);
+        }
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem, 256);
+}
+
+// ---- logit, dL/dz and the gradient of the last hidden layer ------------------------------------------------------
+struct WideOutArgs {
+    OnfDims d;
+    const float *weights;
+    const int32_t *count;
+    const unsigned char *HL, *E;
+    int Hp, K1, n, T64;
+    int want_bwd, gbar_mode;
+    const float *gz, *aux;
+    float wc, beta;
+    float *z_out;
+    float *gbar;                 // [P][T64*64]
+    unsigned char *G16;          // dL/dz as a 16-column operand (column 0), or null
+    unsigned char *GL;           // gradient w.r.t. the last hidden layer's output (post-ReLU mask applied)
+    float *grad;                 // [P][n_params]: += d b_out, or null
+};
+
+__global__ void __launch_bounds__(256) wide_out_kernel(const WideOutArgs a) {
+    const int p = blockIdx.y, t = blockIdx.x, tid = threadIdx.x, pt = tid & 63, part = tid >> 6;
+    const nfopp_onf_layout &L = a.d.lay;
+    const int H = a.d.H;
+    const float *W = a.weights + (size_t)p * L.n_params;
+    const float *w3 = W + L.off_w_out;
+    const int cnt = a.count ? a.count[p] : a.n;
+    const int idx = t * 64 + pt;
+    const bool valid = idx < cnt;
+    const size_t tile = (size_t)p * a.T64 + t;
+    const unsigned char *Ht = a.HL + tile * a.Hp * 256, *Et = a.E + tile * a.K1 * 256;
+    __shared__ float zs[4][64];
+    __shared__ float gs[64];
+    float acc = 0.f;
+    for (int co = part; co < a.Hp / 8; co += 4) {
+        const uint4 hi = *reinterpret_cast<const uint4 *>(Ht + co * 1024 + pt * 16);
+        const uint4 lo = *reinterpret_cast<const uint4 *>(Ht + a.Hp * 128 + co * 1024 + pt * 16);
+        float v[8];
+        unpack8(hi, lo, v);
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+            if (co * 8 + i < H) acc = fmaf(v[i], __ldg(w3 + co * 8 + i), acc);
+    }
+    for (int co = part; co < a.K1 / 8; co += 4) {
+        const uint4 hi = *reinterpret_cast<const uint4 *>(Et + co * 1024 + pt * 16);
+        const uint4 lo = *reinterpret_cast<const uint4 *>(Et + a.K1 * 128 + co * 1024 + pt * 16);
+        float v[8];
+        unpack8(hi, lo, v);
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+            if (co * 8 + i < L.f_in) acc = fmaf(v[i], __ldg(w3 + H + co * 8 + i), acc);
+    }
+    zs[part][pt] = acc;
+    __syncthreads();
+    if (part == 0) {
+        const float z = (zs[0][pt] + zs[1][pt]) + (zs[2][pt] + zs[3][pt]) + W[L.off_b_out];
+        const size_t gi = (size_t)p * a.n + idx;
+        if (valid && a.z_out) a.z_out[gi] = z;
+        float gb = 0.f;
+        if (valid && a.want_bwd) {                      // dL/dz, as in onf_tc.cu
+            if (a.gbar_mode == 0) gb = a.gz[gi];
+            else if (a.gbar_mode == 1) gb = (sigmoid_f(z) - a.aux[gi]) / (float)cnt;
+            else {
+                const float zb = z * a.beta;
+                const float ez = expf(zb);
+                gb = a.wc * (zb > 20.f ? 1.f : ez / (ez + 1.f));
+                if (a.gbar_mode == 3) {
+                    const float th = tanhf(z);
+                    gb += a.aux[gi] * (1.f - th * th);
+                }
+            }
+        }
+        gs[pt] = gb;
+        if (a.want_bwd) {
+            a.gbar[tile * 64 + pt] = gb;
+            if (a.G16) {
+                float e[8] = {gb, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+                uint4 hi, lo;
+                split8(e, hi, lo);
+                const uint4 zero = make_uint4(0, 0, 0, 0);
+                unsigned char *Gt = a.G16 + tile * 16 * 256;
+                *reinterpret_cast<uint4 *>(Gt + pt * 16) = hi;
+                *reinterpret_cast<uint4 *>(Gt + 1024 + pt * 16) = zero;
+                *reinterpret_cast<uint4 *>(Gt + 2048 + pt * 16) = lo;
+                *reinterpret_cast<uint4 *>(Gt + 3072 + pt * 16) = zero;
+            }
+            if (a.grad) {
+                const float s = warp_sum(gb);
+                if ((tid & 31) == 0 && s != 0.f) atomicAdd(a.grad + (size_t)p * L.n_params + L.off_b_out, s);
+            }
+        }
+    }
+    if (!a.want_bwd) return;
+    __syncthreads();
+    unsigned char *Gt = a.GL + tile * a.Hp * 256;
+    const float gb = gs[pt];
+    for (int co = part; co < a.Hp / 8; co += 4) {
+        const uint4 hi = *reinterpret_cast<const uint4 *>(Ht + co * 1024 + pt * 16);
+        const uint32_t mw[4] = {hi.x, hi.y, hi.z, hi.w};
+        float v[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int col = co * 8 + i;
+            const uint32_t bits = (mw[i >> 1] >> ((i & 1) * 16)) & 0x7FFFu;
+            v[i] = (col < H && bits != 0) ? gb * __ldg(w3 + col) : 0.f;
+        }
+        uint4 oh, ol;
+        split8(v, oh, ol);
+        *reinterpret_cast<uint4 *>(Gt + co * 1024 + pt * 16) = oh;
+        *reinterpret_cast<uint4 *>(Gt + a.Hp * 128 + co * 1024 + pt * 16) = ol;
+    }
+}
+
+// ---- encoding backward: dL/dE -> dL/d(arg) (the A operand of the encoder-gradient job) and dL/dx ------------------
+struct WideEbwdArgs {
+    OnfDims d;
+    const float *weights, *x;
+    const int32_t *count;
+    unsigned char *GE;           // in: dL/dE tiles; out (write_g0): dL/d(arg) tiles, in place
+    int K1, n, x_stride, T64, write_g0;
+    float *gx_out;               // [P][n][x_stride] or null
+};
+
+__global__ void __launch_bounds__(256) wide_ebwd_kernel(const WideEbwdArgs a) {
+    const int p = blockIdx.y, t = blockIdx.x, tid = threadIdx.x, pt = tid & 63, part = tid >> 6;
+    const nfopp_onf_layout &L = a.d.lay;
+    const float *W = a.weights + (size_t)p * L.n_params;
+    const int cnt = a.count ? a.count[p] : a.n;
+    const int idx = t * 64 + pt;
+    const bool valid = idx < cnt;
+    float x0 = 0.f, x1 = 0.f, x2 = 0.f;
+    if (valid) {
+        const float *xp = a.x + ((size_t)p * a.n + idx) * a.x_stride;
+        x0 = xp[0]; x1 = xp[1];
+        if (L.in_dim == 3) x2 = xp[2];
+    }
+    const float u0 = (x0 - a.d.mean) / a.d.sigma, u1 = (x1 - a.d.mean) / a.d.sigma, th = x2;
+    unsigned char *Gt = a.GE + ((size_t)p * a.T64 + t) * a.K1 * 256;
+    float g0 = 0.f, g1 = 0.f, g2 = 0.f;
+    for (int co = part; co < a.K1 / 8; co += 4) {
+        unsigned char *ph = Gt + co * 1024 + pt * 16, *pl = ph + a.K1 * 128;
+        float v[8];
+        unpack8(*reinterpret_cast<const uint4 *>(ph), *reinterpret_cast<const uint4 *>(pl), v);
+        FeatParams fp;
+        load_feat_params(W, a.d, co, fp);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int f = co * 8 + i;
+            const bool fourier = f < L.f_pos;
+            const float arg = fmaf(fourier ? u1 : th, fp.pb[i], fmaf(u0, fp.pa[i], fp.pc[i]));
+            const float gp = (valid && f < L.f_in) ? v[i] * __cosf(w_reduce_2pi(arg)) : 0.f;
+            v[i] = gp;
+            if (fourier) { g0 = fmaf(gp, fp.pa[i], g0); g1 = fmaf(gp, fp.pb[i], g1); }
+            else g2 = fmaf(gp, fp.pb[i], g2);
+        }
+        if (a.write_g0) {
+            uint4 hi, lo;
+            split8(v, hi, lo);
+            *reinterpret_cast<uint4 *>(ph) = hi;
+            *reinterpret_cast<uint4 *>(pl) = lo;
+        }
+    }
+    if (!a.gx_out) return;
+    __shared__ float red[3][4][64];
+    red[0][part][pt] = g0; red[1][part][pt] = g1; red[2][part][pt] = g2;
+    __syncthreads();
+    if (part == 0 && valid) {
+        float s[3];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) s[c] = (red[c][0][pt] + red[c][1][pt]) + (red[c][2][pt] + red[c][3][pt]);
+        float *out = a.gx_out + ((size_t)p * a.n + idx) * a.x_stride;
+        out[0] = s[0] / a.d.sigma;
+        out[1] = s[1] / a.d.sigma;
+        if (L.in_dim == 3) out[2] = s[2];
+        for (int c = L.in_dim; c < a.x_stride; ++c) out[c] = 0.f;
+    }
+}
+
+// ---- encoder gradients: raw[f][0..3] = sum_pt gp[pt,f] * [u0, u1, theta, 1] -> blob order ---------------------------
+struct WideAsmArgs {
+    OnfDims d;
+    const float *weights, *raw;   // raw [P][K1][16]
+    float *grad;
+    int K1;
+};
+
+__global__ void __launch_bounds__(256) wide_asm_kernel(const WideAsmArgs a) {
+    const int p = blockIdx.y, f = blockIdx.x * blockDim.x + threadIdx.x;
+    const nfopp_onf_layout &L = a.d.lay;
+    if (f >= L.f_in) return;
+    const float *r = a.raw + ((size_t)p * a.K1 + f) * 16;
+    const float *W = a.weights + (size_t)p * L.n_params;
+    float *G = a.grad + (size_t)p * L.n_params;
+    if (f < L.f_pos) {
+        G[L.off_enc_w + 2 * f] = r[0];
+        G[L.off_enc_w + 2 * f + 1] = r[1];
+        G[L.off_enc_b + f] = a.d.bias ? r[3] : 0.f;
+    } else {
+        const int k = f - L.f_pos;
+        G[L.off_ang_b + k] = W[L.off_ang_f + k] * r[3];                  // d/d b_k = f_k * sum gp
+        G[L.off_ang_f + k] = fmaf(W[L.off_ang_b + k], r[3], r[2]);       // d/d f_k = sum gp * (theta + b_k)   (trained: SURVEY 8 a3)
+    }
+}
+
+int g_sm_count = 0;
+int sm_count() {
+    if (!g_sm_count) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev);
+        if (g_sm_count <= 0) g_sm_count = 148;
+    }
+    return g_sm_count;
+}
+
+size_t align256(size_t x) { return (x + 255) / 256 * 256; }
+
+struct WideWorkspace {
+    size_t E, U16, H[NFOPP_MAX_LAYERS], G[2], GE, G16, gbar, raw, total;
+};
+
+void wide_workspace(const WideDims &w, int P, int n, bool bwd, WideWorkspace *ws) {
+    const size_t T64 = (size_t)(n + 127) / 128 * 2, tiles = (size_t)P * T64;
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off += align256(bytes); return o; };
+    ws->E = take(tiles * w.K1 * 256);
+    const int nh = bwd ? w.L : (w.L < 2 ? w.L : 2);
+    for (int l = 0; l < NFOPP_MAX_LAYERS; ++l) ws->H[l] = 0;
+    for (int l = 0; l < nh; ++l) ws->H[l] = take(tiles * w.Hp * 256);
+    if (!bwd)
+        for (int l = 2; l < w.L; ++l) ws->H[l] = ws->H[l & 1];
+    if (bwd) {
+        ws->U16 = take(tiles * 16 * 256);
+        ws->G[0] = take(tiles * w.Hp * 256);
+        ws->G[1] = take(tiles * w.Hp * 256);
+        ws->GE = take(tiles * w.K1 * 256);
+        ws->G16 = take(tiles * 16 * 256);
+        ws->gbar = take(tiles * 64 * 4);
+        ws->raw = take((size_t)P * w.K1 * 16 * 4);
+    } else {
+        ws->U16 = ws->G[0] = ws->G[1] = ws->GE = ws->G16 = ws->gbar = ws->raw = 0;
+    }
+    ws->total = off;
+}
+
+}  // namespace
+
+// ---- host side -----------------------------------------------------------------------------------------------------
+bool onf_wide_supported(const OnfDims &d) {
+    WideDims w;
+    return make_wide_dims(d, &w);
+}
+
+size_t onf_wide_packed_bytes(const OnfDims &d) {
+    WideDims w;
+    return make_wide_dims(d, &w) ? align256(w.packed_bytes) : 0;
+}
+
+size_t onf_wide_workspace_bytes(const OnfDims &d, int P, int n, bool bwd) {
+    WideDims w;
+    if (!make_wide_dims(d, &w)) return 0;
+    WideWorkspace ws;
+    wide_workspace(w, P, n, bwd, &ws);
+    return ws.total;
+}
+
+int onf_wide_prepare(const OnfDims &d) {
+    WideDims w;
+    NFOPP_REQUIRE(make_wide_dims(d, &w), "onf(wide): hidden=%d layers=%d unsupported (hidden %% 4 == 0, <= 1024)", d.H, d.L);
+    NFOPP_CHECK_CUDA(cudaFuncSetAttribute(wide_gemm_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM));
+    NFOPP_CHECK_CUDA(cudaFuncSetAttribute(wide_gemm_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM));
+    NFOPP_CHECK_CUDA(cudaFuncSetAttribute(wide_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WW_SMEM));
+    sm_count();
+    return NFOPP_OK;
+}
+
+int onf_wide_pack(const OnfDims &d, const float *weights, unsigned char *packed, int P, cudaStream_t stream) {
+    WidePackArgs a{};
+    a.d = d;
+    NFOPP_REQUIRE(make_wide_dims(d, &a.w), "onf(wide): unsupported network shape");
+    a.weights = weights; a.packed = packed;
+    if (P == 0) return NFOPP_OK;
+    int max_items = 0;
+    for (int l = 0; l < a.w.L; ++l) max_items = max(max_items, a.w.Hp * (a.w.kin[l] / 8));
+    dim3 grid((max_items + 255) / 256, P);
+    wide_pack_kernel<<<grid, 256, 0, stream>>>(a);
+    NFOPP_CHECK_CUDA(cudaGetLastError());
+    return NFOPP_OK;
+}
+
+static int launch_wgrad(WideWgradArgs g, cudaStream_t s) {
+    const int MB = (g.CA + 127) / 128, NTT = (g.CB + WG_NT - 1) / WG_NT + (g.bias_off >= 0 ? 1 : 0);
+    const int base = g.P * MB * NTT;
+    int splits = (2 * sm_count() + base - 1) / base;
+    if (splits > g.T64) splits = g.T64;
+    if (splits < 1) splits = 1;
+    g.splits = splits;
+    const int items = base * splits;
+    wide_wgrad_kernel<<<items < sm_count() ? items : sm_count(), WG_THREADS, WW_SMEM, s>>>(g);
+    NFOPP_CHECK_CUDA(cudaGetLastError());
+    return NFOPP_OK;
+}
+
+int onf_wide_launch_count(const OnfDims &d, bool want_bwd, bool want_wgrad) {
+    if (!want_bwd) return 2 + d.L;
+    return 2 + d.L + d.L + 1 + (want_wgrad ? d.L + 6 : 0);
+}
+
+// One ONF call (forward, or forward + backward): a fixed sequence of launches on `stream`.
+int onf_wide_launch(const OnfArgs &o, const OnfWideExtra &x, int P, cudaStream_t stream) {
+    WideDims w;
+    NFOPP_REQUIRE(make_wide_dims(o.d, &w), "onf(wide): unsupported network shape");
+    NFOPP_REQUIRE(x.packed && x.workspace, "onf(wide): packed operand copy / workspace missing");
+    if (o.n == 0 || P == 0) return NFOPP_OK;
+    const bool bwd = o.want_bwd != 0, wgrad = bwd && x.grad_out != nullptr, want_gx = bwd && o.gx_out != nullptr;
+    const nfopp_onf_layout &L = o.d.lay;
+    WideWorkspace ws;
+    wide_workspace(w, P, o.n, bwd, &ws);
+    unsigned char *base = x.workspace;
+    const int T64 = (o.n + 127) / 128 * 2;
+    const int x_stride = o.x_stride ? o.x_stride : L.in_dim;
+    const int grid_g = sm_count();
+
+    {
+        WideEncArgs e{};
+        e.d = o.d; e.weights = o.weights; e.x = o.x; e.count = o.count; e.n = o.n; e.x_stride = x_stride; e.T64 = T64; e.K1 = w.K1;
+        e.E = base + ws.E; e.U16 = wgrad ? base + ws.U16 : nullptr;
+        wide_enc_kernel<<<dim3(T64, P), 256, 0, stream>>>(e);
+        NFOPP_CHECK_CUDA(cudaGetLastError());
+    }
+    auto gemm_items = [&](int Nfull) { return P * (T64 / 2) * ((Nfull + WG_NT - 1) / WG_NT); };
+    for (int l = 0; l < w.L; ++l) {
+        WideGemmArgs g{};
+        g.A = l == 0 ? base + ws.E : base + ws.H[l - 1]; g.CA = w.kin[l];
+        g.Wpk = x.packed + w.wf_off[l]; g.w_stride = align256(w.packed_bytes);
+        g.K = w.kin[l]; g.Nfull = w.Hp; g.Out = base + ws.H[l];
+        g.weights = o.weights; g.n_params = L.n_params; g.bias_off = L.off_b[l]; g.n_valid = w.H;
+        g.P = P; g.T64 = T64;
+        const int items = gemm_items(g.Nfull);
+        wide_gemm_kernel<0><<<items < grid_g ? items : grid_g, WG_THREADS, WG_SMEM, stream>>>(g);
+        NFOPP_CHECK_CUDA(cudaGetLastError());
+    }
+    if (wgrad) {
+        NFOPP_CHECK_CUDA(cudaMemsetAsync(x.grad_out, 0, (size_t)P * L.n_params * sizeof(float), stream));
+        NFOPP_CHECK_CUDA(cudaMemsetAsync(base + ws.raw, 0, (size_t)P * w.K1 * 16 * sizeof(float), stream));
+    }
+    int cur = 0;
+    {
+        WideOutArgs u{};
+        u.d = o.d; u.weights = o.weights; u.count = o.count; u.HL = base + ws.H[w.L - 1]; u.E = base + ws.E;
+        u.Hp = w.Hp; u.K1 = w.K1; u.n = o.n; u.T64 = T64; u.want_bwd = bwd; u.gbar_mode = o.gbar_mode; u.gz = o.gz; u.aux = o.aux;
+        u.wc = o.wc; u.beta = o.beta; u.z_out = o.z_out;
+        if (bwd) {
+            u.gbar = reinterpret_cast<float *>(base + ws.gbar);
+            u.G16 = wgrad ? base + ws.G16 : nullptr;
+            u.GL = base + ws.G[cur];
+            u.grad = wgrad ? x.grad_out : nullptr;
+        }
+        wide_out_kernel<<<dim3(T64, P), 256, 0, stream>>>(u);
+        NFOPP_CHECK_CUDA(cudaGetLastError());
+    }
+    if (!bwd) return NFOPP_OK;
+    int rc;
+    WideWgradArgs wg{};
+    wg.P = P; wg.T64 = T64; wg.dst = x.grad_out; wg.dst_pstride = L.n_params;
+    if (wgrad) {
+        // output layer: d w_out[:H] = sum_pt H_L * gbar ; d w_out[H:] = sum_pt E * gbar     (onf_model.py:48-49)
+        WideWgradArgs j = wg;
+        j.A = base + ws.H[w.L - 1]; j.CA = w.Hp; j.B = base + ws.G16; j.CB = 16;
+        j.dst_off = L.off_w_out; j.dst_ld = 1; j.rows_valid = w.H; j.cols_valid = 1; j.bias_off = -1;
+        if ((rc = launch_wgrad(j, stream))) return rc;
+        j.A = base + ws.E; j.CA = w.K1; j.dst_off = L.off_w_out + w.H; j.rows_valid = w.FIN;
+        if ((rc = launch_wgrad(j, stream))) return rc;
+    }
+    for (int l = w.L - 1; l >= 0; --l) {
+        if (wgrad) {
+            WideWgradArgs j = wg;
+            j.A = base + ws.G[cur]; j.CA = w.Hp; j.B = l == 0 ? base + ws.E : base + ws.H[l - 1]; j.CB = w.kin[l];
+            j.dst_off = L.off_w[l]; j.dst_ld = w.kin_real[l]; j.rows_valid = w.H; j.cols_valid = w.kin_real[l];
+            j.bias_off = L.off_b[l];
+            if ((rc = launch_wgrad(j, stream))) return rc;
+        }
+        if (l == 0 && !want_gx && !wgrad) break;
+        WideGemmArgs g{};
+        g.A = base + ws.G[cur]; g.CA = w.Hp;
+        g.Wpk = x.packed + w.wd_off[l]; g.w_stride = align256(w.packed_bytes);
+        g.K = w.Hp; g.Nfull = w.kin[l];
+        g.weights = o.weights; g.n_params = L.n_params;
+        g.P = P; g.T64 = T64;
+        if (l > 0) {
+            g.Out = base + ws.G[cur ^ 1]; g.Mask = base + ws.H[l - 1];
+        } else {
+            g.Out = base + ws.GE; g.gbar = reinterpret_cast<const float *>(base + ws.gbar);
+            g.skip_off = L.off_w_out + w.H; g.skip_n = w.FIN;
+        }
+        const int items = gemm_items(g.Nfull);
+        wide_gemm_kernel<1><<<items < grid_g ? items : grid_g, WG_THREADS, WG_SMEM, stream>>>(g);
+        NFOPP_CHECK_CUDA(cudaGetLastError());
+        cur ^= 1;
+    }
+    {
+        WideEbwdArgs e{};
+        e.d = o.d; e.weights = o.weights; e.x = o.x; e.count = o.count; e.GE = base + ws.GE; e.K1 = w.K1; e.n = o.n;
+        e.x_stride = x_stride; e.T64 = T64; e.write_g0 = wgrad; e.gx_out = o.gx_out;
+        wide_ebwd_kernel<<<dim3(T64, P), 256, 0, stream>>>(e);
+        NFOPP_CHECK_CUDA(cudaGetLastError());
+    }
+    if (wgrad) {
+        WideWgradArgs j = wg;
+        j.A = base + ws.GE; j.CA = w.K1; j.B = base + ws.U16; j.CB = 16;
+        j.dst = reinterpret_cast<float *>(base + ws.raw); j.dst_pstride = (size_t)w.K1 * 16;
+        j.dst_off = 0; j.dst_ld = 16; j.rows_valid = w.K1; j.cols_valid = 16; j.bias_off = -1;
+        if ((rc = launch_wgrad(j, stream))) return rc;
+        WideAsmArgs s{};
+        s.d = o.d; s.weights = o.weights; s.raw = reinterpret_cast<const float *>(base + ws.raw); s.grad = x.grad_out; s.K1 = w.K1;
+        wide_asm_kernel<<<dim3((w.FIN + 255) / 256, P), 256, 0, stream>>>(s);
+        NFOPP_CHECK_CUDA(cudaGetLastError());
+    }
+    return NFOPP_OK;
+}
+
+}  // namespace nfopp

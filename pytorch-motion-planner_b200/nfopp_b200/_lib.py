@@ -51,6 +51,7 @@ SIGNATURES = {
     "nfopp_label_rectangle": (_I, [_P, _I, _I, _P, _P, _I, _I, _P, _P, _P, _P]),
     "nfopp_label_grid": (_I, [_P, _I, _I, _I, _P, _I, _I, _I, C.c_double, C.c_double, C.c_double, _P, _P, _P]),
     "nfopp_onf_scratch_bytes": (_I, [C.POINTER(OnfConfig), _I, _I, C.POINTER(C.c_size_t)]),
+    "nfopp_onf_scratch_bytes_n": (_I, [C.POINTER(OnfConfig), _I, _I, _I, _I, C.POINTER(C.c_size_t)]),
     "nfopp_onf_forward": (_I, [C.POINTER(OnfConfig), _P, _P, _P, _I, _I, _P, _I, _P, _P]),
     "nfopp_onf_tiles": (_I, [C.POINTER(OnfConfig), _I, _I]),
     "nfopp_onf_backward": (_I, [C.POINTER(OnfConfig), _P, _P, _P, _I, _I, _I, _P, _P, C.c_float, C.c_float, _P, _P,
@@ -96,7 +97,7 @@ def lib():
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(handle, name)
             fn.restype, fn.argtypes = res, args
-        if handle.nfopp_abi_version() != 2:
+        if handle.nfopp_abi_version() != 3:
             raise NfoppError("libnfopp.so ABI version mismatch")
         _lib = handle
     return _lib
@@ -114,11 +115,12 @@ def check(rc):
     raise NfoppError(f"libnfopp error {rc}: {msg}")
 
 
-def onf_scratch(cfg, problems, impl, device):
-    """Device scratch an ONF forward/backward call of `impl` needs (tensor path: bf16 operand copy of the weights)."""
+def onf_scratch(cfg, problems, impl, device, n=0, want_bwd=True):
+    """Device scratch an ONF forward/backward call of `impl` on `n` points per problem needs (tensor paths: bf16
+    operand copy of the weights; wide path: also its activation / gradient operand tiles)."""
     import torch
     nbytes = C.c_size_t()
-    check(lib().nfopp_onf_scratch_bytes(C.byref(cfg), problems, impl, C.byref(nbytes)))
+    check(lib().nfopp_onf_scratch_bytes_n(C.byref(cfg), problems, n, impl, int(want_bwd), C.byref(nbytes)))
     return torch.empty(max(int(nbytes.value), 16), dtype=torch.uint8, device=device)
 
 

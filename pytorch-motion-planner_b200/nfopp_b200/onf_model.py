@@ -25,7 +25,7 @@ class _OnfFunction(torch.autograd.Function):
         xin = x[:, :module.in_dim].detach().to(torch.float32).contiguous()
         z = torch.empty(n, dtype=torch.float32, device=flat.device)
         with torch.cuda.device(flat.device):
-            scratch = L.onf_scratch(cfg, 1, module.impl, flat.device)
+            scratch = L.onf_scratch(cfg, 1, module.impl, flat.device, n, False)
             L.check(L.lib().nfopp_onf_forward(C.byref(cfg), L.ptr(flat), L.ptr(xin), None, 1, n, L.ptr(z),
                                               module.impl, L.ptr(scratch), L.stream_ptr()))
         ctx.module, ctx.xin, ctx.x_cols = module, xin, x.shape[1]
@@ -47,7 +47,7 @@ class _OnfFunction(torch.autograd.Function):
         gxin = torch.empty(n, module.in_dim, dtype=torch.float32, device=flat.device)
         with torch.cuda.device(flat.device):
             s = L.stream_ptr()
-            scratch = L.onf_scratch(cfg, 1, impl, flat.device)
+            scratch = L.onf_scratch(cfg, 1, impl, flat.device, n, True)
             L.check(lib.nfopp_onf_backward(C.byref(cfg), L.ptr(flat), L.ptr(xin), None, 1, n, 0, L.ptr(gz), None,
                                            0.0, 1.0, None, L.ptr(gxin), L.ptr(gpart), impl, L.ptr(scratch), s))
             L.check(lib.nfopp_onf_reduce_grad(C.byref(cfg), L.ptr(gpart), None, 1, n, impl, L.ptr(gflat), s))

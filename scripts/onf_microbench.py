@@ -26,7 +26,7 @@ def run(cc, impl, w, x, mode, gz=None, aux=None, want_w=True, want_x=True, reps=
     P, n, D = x.shape
     lib = L.lib()
     s = L.stream_ptr()
-    scratch = L.onf_scratch(cc, P, impl, "cuda")
+    scratch = L.onf_scratch(cc, P, impl, "cuda", n, True)
     tiles = lib.nfopp_onf_tiles(C.byref(cc), n, impl)
     z = torch.zeros(P, n, device="cuda")
     gx = torch.zeros(P, n, D, device="cuda") if want_x else None

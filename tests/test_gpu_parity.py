@@ -99,7 +99,7 @@ def test_labels_empty_input():
 
 
 # ---------------------------------------------------------------------------------------- K2 ONF
-IMPLS = {"fma": 1, "tensor": 2}     # CUDA-core fp32 path / tcgen05 path (bf16 hi/lo split operands, TMEM accumulators)
+IMPLS = {"fma": 1, "tensor": 2, "wide": 3}     # CUDA-core fp32 / fused tcgen05 kernel (reference shape) / tcgen05 grouped GEMMs per layer
 
 
 def _onf_call(cfg, w, x, gz=None, mode=0, aux=None, wc=0.0, beta=1.0, count=None, impl=0):
@@ -113,7 +113,7 @@ def _onf_call(cfg, w, x, gz=None, mode=0, aux=None, wc=0.0, beta=1.0, count=None
     z = torch.zeros(P, n, device="cuda")
     s = L.stream_ptr()
     dcount = None if count is None else torch.tensor(count, dtype=torch.int32, device="cuda")
-    scratch = L.onf_scratch(cc, P, impl, "cuda")
+    scratch = L.onf_scratch(cc, P, impl, "cuda", n, True)
     L.check(L.lib().nfopp_onf_forward(C.byref(cc), L.ptr(dw), L.ptr(dx), L.ptr(dcount), P, n, L.ptr(z), impl,
                                       L.ptr(scratch), s))
     if gz is None and mode == 0:
@@ -134,7 +134,7 @@ def _onf_call(cfg, w, x, gz=None, mode=0, aux=None, wc=0.0, beta=1.0, count=None
     return z.cpu(), gx.cpu(), gw.cpu()
 
 
-@pytest.mark.parametrize("impl", ["fma", "tensor"])
+@pytest.mark.parametrize("impl", ["fma", "tensor", "wide"])
 @pytest.mark.parametrize("name", ["holonomic", "car", "image"])
 def test_onf_matches_reference_golden(name, impl):
     fx = U.load("onf.npz")
@@ -153,7 +153,11 @@ def test_onf_matches_reference_golden(name, impl):
     (256, 4, True, True, 77, "fma"), (100, 2, True, False, 1, "fma"),
     # tensor path: tiles of 64 points with ragged tails (209 = 3*64+17, 65, 16, 1), narrow and odd widths
     (100, 2, True, True, 209, "tensor"), (64, 2, False, False, 33, "tensor"), (100, 2, True, False, 1, "tensor"),
-    (108, 2, False, True, 65, "tensor"), (32, 2, True, True, 16, "tensor"), (100, 2, True, True, 500, "tensor")])
+    (108, 2, False, True, 65, "tensor"), (32, 2, True, True, 16, "tensor"), (100, 2, True, True, 500, "tensor"),
+    # wide path: per-layer grouped GEMMs, 128-point row blocks with ragged tails, 1..8 layers, widths up to 512 (two N tiles)
+    (100, 2, True, True, 209, "wide"), (64, 2, False, False, 33, "wide"), (256, 4, True, True, 77, "wide"),
+    (256, 4, True, True, 1000, "wide"), (512, 2, True, True, 300, "wide"), (128, 1, True, False, 129, "wide"),
+    (384, 3, False, True, 130, "wide"), (64, 8, True, True, 257, "wide")])
 def test_onf_vs_oracle_shapes_and_ragged_counts(hidden, layers, use_cos, angle, n, impl):
     cfg = O.OnfConfig(mean=0.3, sigma=1.7, use_cos=use_cos, angle=angle, hidden=hidden, layers=layers)
     gen = torch.Generator().manual_seed(hidden + n)
@@ -182,13 +186,14 @@ def test_onf_impl_auto_and_unsupported_shapes():
     assert L.lib().nfopp_onf_tiles(C.byref(ref), 209, 1) == 7
     wide = OnfSpec(0.0, 1.0, True, True, 256, 4).to_c()
     assert L.lib().nfopp_onf_tiles(C.byref(wide), 209, 2) < 0
-    assert L.lib().nfopp_onf_tiles(C.byref(wide), 209, 0) == L.lib().nfopp_onf_tiles(C.byref(wide), 209, 1) > 0
+    assert L.lib().nfopp_onf_tiles(C.byref(wide), 209, 0) == L.lib().nfopp_onf_tiles(C.byref(wide), 209, 3) == 1    # auto -> wide
+    assert L.lib().nfopp_onf_tiles(C.byref(wide), 209, 1) > 1
     nbytes = C.c_size_t()
     with pytest.raises(ValueError):
         L.check(L.lib().nfopp_onf_scratch_bytes(C.byref(wide), 4, 2, C.byref(nbytes)))
 
 
-@pytest.mark.parametrize("impl", ["fma", "tensor"])
+@pytest.mark.parametrize("impl", ["fma", "tensor", "wide"])
 def test_onf_fused_gbar_modes_and_adam(impl):
     """BCE / path / path_mu upstream gradients computed in-kernel, then the fused reduce+Adam update."""
     impl = IMPLS[impl]
@@ -215,7 +220,7 @@ def test_onf_fused_gbar_modes_and_adam(impl):
     from nfopp_b200.engine import OnfSpec
     cc = OnfSpec(cfg.mean, cfg.sigma, cfg.use_cos, cfg.angle).to_c()
     tiles = L.lib().nfopp_onf_tiles(C.byref(cc), n, impl)
-    scratch = L.onf_scratch(cc, P, impl, "cuda")
+    scratch = L.onf_scratch(cc, P, impl, "cuda", n, True)
     dw, dm, dv = w.cuda(), torch.zeros_like(w).cuda(), torch.zeros_like(w).cuda()
     dx, dy = x.cuda(), y.cuda()
     gpart = torch.zeros(P, tiles, w.shape[1], device="cuda")
