@@ -37,7 +37,7 @@ constexpr int WG_NT = 256;               // N per tile
 constexpr int WG_A_STAGE = 128 * WG_KC * 4;       // 128 points x KC x (hi + lo)
 constexpr int WG_B_STAGE = WG_NT * WG_KC * 4;
 constexpr int WG_STAGE = WG_A_STAGE + WG_B_STAGE;
-constexpr int WG_SMEM = WG_STAGES * WG_STAGE + 256;
+constexpr int WG_SMEM = WG_STAGES * WG_STAGE + 256 + 2 * WG_NT * 4;   // + double-buffered per-tile bias / skip weights
 
 constexpr int WW_STAGES = 2;             // wgrad: one stage = one 64-point tile of A (128 columns) and B (<= 256 columns)
 constexpr int WW_A_STAGE = 128 * 64 * 4;
@@ -248,6 +248,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wide_gemm_kernel(const WideGemm
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + WG_STAGES * WG_STAGE);
     uint64_t *full = bars, *empty = bars + WG_STAGES, *tfull = bars + 2 * WG_STAGES, *tempty = tfull + 2;
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tempty + 2);
+    float *svec = reinterpret_cast<float *>(smem + WG_STAGES * WG_STAGE + 256);    // [2][WG_NT] bias (fwd) / skip weights (dgrad)
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int NTL = (a.Nfull + WG_NT - 1) / WG_NT, RB = a.T64 / 2;
     const int items = a.P * RB * NTL;
@@ -333,33 +334,45 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wide_gemm_kernel(const WideGemm
             const int nt = item % NTL, rb = (item / NTL) % RB, p = item / (NTL * RB);
             const int NTw = min(WG_NT, a.Nfull - nt * WG_NT);
             const uint32_t buf = tile_it & 1;
-            mbar_wait(tfull + buf, (tile_it >> 1) & 1);
-            fence_after_sync();
             const int row = q * 32 + lane, r = row & 63;
             const size_t tile = (size_t)p * a.T64 + 2 * rb + (row >> 6);
             unsigned char *Ot = a.Out + tile * a.Nfull * 256;
             const unsigned char *Mt = (MODE == 1 && a.Mask) ? a.Mask + tile * a.Nfull * 256 : nullptr;
             const float *Wb = a.weights + (size_t)p * a.n_params;
             const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + buf * 256;
+            // per-tile vector (bias of the forward layer / skip-connection weights of the first layer's input gradient),
+            // zero beyond the real width: staged once per tile instead of one global load per element
+            float *sv = svec + buf * WG_NT;
+            const bool use_vec = MODE == 0 || a.gbar != nullptr;
+            if (use_vec) {
+                const int et = threadIdx.x - 64, voff = MODE == 0 ? a.bias_off : a.skip_off, vn = MODE == 0 ? a.n_valid : a.skip_n;
+                for (int c = et; c < NTw; c += 128) {
+                    const int col = nt * WG_NT + c;
+                    sv[c] = col < vn ? __ldg(Wb + voff + col) : 0.f;
+                }
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+            }
             float gb = 0.f;
             if (MODE == 1 && a.gbar) gb = a.gbar[((size_t)p * a.T64 + 2 * rb) * 64 + row];
+            mbar_wait(tfull + buf, (tile_it >> 1) & 1);
+            fence_after_sync();
             for (int c0 = 0; c0 < NTw; c0 += 16) {
                 float v[16];
                 tmem_ld16(taddr + c0, v);
                 const int col0 = nt * WG_NT + c0;
-                if (MODE == 0) {
+                float sb[16];
+                if (use_vec) {
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) {
-                        const int col = col0 + i;
-                        v[i] = col < a.n_valid ? fmaxf(v[i] + __ldg(Wb + a.bias_off + col), 0.f) : 0.f;
-                    }
+                    for (int i4 = 0; i4 < 4; ++i4) *reinterpret_cast<float4 *>(sb + 4 * i4) = *reinterpret_cast<const float4 *>(sv + c0 + 4 * i4);
+                }
+                if (MODE == 0) {
+                    // padded columns: the weights are zero there, so D = 0 and relu(0 + 0) = 0
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i] + sb[i], 0.f);
                 } else {
                     if (a.gbar) {
 #pragma unroll
-                        for (int i = 0; i < 16; ++i) {
-                            const int col = col0 + i;
-                            if (col < a.skip_n) v[i] = fmaf(gb, __ldg(Wb + a.skip_off + col), v[i]);
-                        }
+                        for (int i = 0; i < 16; ++i) v[i] = fmaf(gb, sb[i], v[i]);
                     }
                     if (Mt) {
                         const uint4 m0 = *reinterpret_cast<const uint4 *>(Mt + (col0 / 8) * 1024 + r * 16);
@@ -399,9 +412,13 @@ struct WideWgradArgs {
     int CB;                      // columns of B (N, walked in tiles of 256)
     float *dst;                  // [P] x dst_pstride floats
     size_t dst_pstride;
-    int dst_off, dst_ld, rows_valid, cols_valid;
-    int bias_off;                // >= 0: one more N tile with B = ones -> dst[bias_off + m] (+)= sum_pt A[pt, m]
+    int dst_off, dst_ld, row_lo, rows_valid, cols_valid;   // rows row_lo <= m < rows_valid, columns j < cols_valid are stored
+    int bias_off;                // >= 0: one more N tile with B = ones -> dst[bias_off + m] = sum_pt A[pt, m]
     int P, T64, splits;
+    // splits > 1: split s of the point range stores its partial sums at partial + s * partial_sstride (same offsets as
+    // dst); wide_reduce_kernel adds the splits in fixed order afterwards - deterministic, no atomics
+    float *partial;
+    size_t partial_sstride;
 };
 
 __global__ void __launch_bounds__(WG_THREADS, 1) wide_wgrad_kernel(const WideWgradArgs a) {
@@ -429,8 +446,9 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wide_wgrad_kernel(const WideWgr
     const uint32_t tmem = *tmem_slot;
 
     // item -> (p, mb, nt, split); split fastest so the splits of one output tile run concurrently on different SMs
-    auto decode = [&](int item, int &p, int &mb, int &nt, int &t0, int &t1) {
+    auto decode = [&](int item, int &p, int &mb, int &nt, int &t0, int &t1, int *split = nullptr) {
         const int sp = item % a.splits;
+        if (split) *split = sp;
         nt = (item / a.splits) % NTT;
         mb = (item / (a.splits * NTT)) % MB;
         p = item / (a.splits * NTT * MB);
@@ -503,34 +521,27 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wide_wgrad_kernel(const WideWgr
         const int q = warp & 3;
         uint32_t tile_it = 0;
         for (int item = blockIdx.x; item < items; item += gridDim.x, ++tile_it) {
-            int p, mb, nt, t0, t1;
-            decode(item, p, mb, nt, t0, t1);
+            int p, mb, nt, t0, t1, sp;
+            decode(item, p, mb, nt, t0, t1, &sp);
             const bool bias_tile = nt == NTL;
             const int NB = bias_tile ? 16 : min(WG_NT, a.CB - nt * WG_NT);
             mbar_wait(tfull, tile_it & 1);
             fence_after_sync();
             const int m = mb * 128 + q * 32 + lane;
-            float *D = a.dst + (size_t)p * a.dst_pstride;
+            float *D = (a.splits > 1 ? a.partial + (size_t)sp * a.partial_sstride : a.dst) + (size_t)p * a.dst_pstride;
             const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16);
-            const bool has_work = t1 > t0;
+            const bool has_work = t1 > t0;          // an empty split leaves its (zeroed) partial untouched
             for (int c0 = 0; c0 < NB; c0 += 16) {
                 float v[16];
                 tmem_ld16(taddr + c0, v);
-                if (m >= a.rows_valid || !has_work) continue;
+                if (m < a.row_lo || m >= a.rows_valid || !has_work) continue;
                 if (bias_tile) {
-                    if (c0 == 0) {
-                        if (a.splits > 1) atomicAdd(D + a.bias_off + m, v[0]);
-                        else D[a.bias_off + m] = v[0];
-                    }
+                    if (c0 == 0) D[a.bias_off + m] = v[0];
                     continue;
                 }
                 const int j0 = nt * WG_NT + c0;
                 float *drow = D + a.dst_off + (size_t)m * a.dst_ld + j0;
-                if (a.splits > 1) {
-#pragma unroll
-                    for (int i = 0; i < 16; ++i)
-                        if (j0 + i < a.cols_valid) atomicAdd(drow + i, v[i]);
-                } else if ((a.dst_ld & 3) == 0 && (a.dst_off & 3) == 0) {
+                if ((a.dst_ld & 3) == 0 && (a.dst_off & 3) == 0) {
 #pragma unroll
                     for (int i4 = 0; i4 < 4; ++i4)
                         if (j0 + 4 * i4 + 3 < a.cols_valid)
@@ -568,7 +579,6 @@ struct WideOutArgs {
     float *gbar;                 // [P][T64*64]
     unsigned char *G16;          // dL/dz as a 16-column operand (column 0), or null
     unsigned char *GL;           // gradient w.r.t. the last hidden layer's output (post-ReLU mask applied)
-    float *grad;                 // [P][n_params]: += d b_out, or null
 };
 
 __global__ void __launch_bounds__(256) wide_out_kernel(const WideOutArgs a) {
@@ -636,10 +646,6 @@ __global__ void __launch_bounds__(256) wide_out_kernel(const WideOutArgs a) {
                 *reinterpret_cast<uint4 *>(Gt + 1024 + pt * 16) = zero;
                 *reinterpret_cast<uint4 *>(Gt + 2048 + pt * 16) = lo;
                 *reinterpret_cast<uint4 *>(Gt + 3072 + pt * 16) = zero;
-            }
-            if (a.grad) {
-                const float s = warp_sum(gb);
-                if ((tid & 31) == 0 && s != 0.f) atomicAdd(a.grad + (size_t)p * L.n_params + L.off_b_out, s);
             }
         }
     }
@@ -755,6 +761,20 @@ __global__ void __launch_bounds__(256) wide_asm_kernel(const WideAsmArgs a) {
     }
 }
 
+// dst[i] = sum over splits (fixed order) of partial[s][i]
+__global__ void __launch_bounds__(256) wide_reduce_kernel(const float *partial, size_t sstride, int splits, float *dst, size_t n4) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+        float4 acc = reinterpret_cast<const float4 *>(partial)[i];
+        for (int s = 1; s < splits; ++s) {
+            const float4 v = reinterpret_cast<const float4 *>(partial + (size_t)s * sstride)[i];
+            acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+        }
+        reinterpret_cast<float4 *>(dst)[i] = acc;
+    }
+}
+
+size_t align256(size_t x) { return (x + 255) / 256 * 256; }
+
 int g_sm_count = 0;
 int sm_count() {
     if (!g_sm_count) {
@@ -766,13 +786,13 @@ int sm_count() {
     return g_sm_count;
 }
 
-size_t align256(size_t x) { return (x + 255) / 256 * 256; }
-
 struct WideWorkspace {
-    size_t E, U16, H[NFOPP_MAX_LAYERS], G[2], GE, G16, gbar, raw, total;
+    size_t E, U16, H[NFOPP_MAX_LAYERS], G[2], GE, G16, gbar, raw, partial, total;
+    int splits;                  // point-range splits of every weight-gradient job of the call
+    size_t partial_sstride;      // floats between splits: [P][n_params] gradient partial, then [P][K1*16] encoder partial
 };
 
-void wide_workspace(const WideDims &w, int P, int n, bool bwd, WideWorkspace *ws) {
+void wide_workspace(const WideDims &w, int n_params, int P, int n, bool bwd, WideWorkspace *ws) {
     const size_t T64 = (size_t)(n + 127) / 128 * 2, tiles = (size_t)P * T64;
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off += align256(bytes); return o; };
@@ -790,8 +810,18 @@ void wide_workspace(const WideDims &w, int P, int n, bool bwd, WideWorkspace *ws
         ws->G16 = take(tiles * 16 * 256);
         ws->gbar = take(tiles * 64 * 4);
         ws->raw = take((size_t)P * w.K1 * 16 * 4);
+        // enough work items to fill the GPU twice over when there are few problems: split the point range
+        const int wmax = w.K1 > w.Hp ? w.K1 : w.Hp;
+        const int base = P * ((w.Hp + 127) / 128) * ((wmax + WG_NT - 1) / WG_NT + 1);
+        int splits = (2 * sm_count() + base - 1) / base;
+        if (splits > (int)T64) splits = (int)T64;
+        ws->splits = splits < 1 ? 1 : splits;
+        ws->partial_sstride = (size_t)P * ((size_t)n_params + (size_t)w.K1 * 16);
+        ws->partial = ws->splits > 1 ? take((size_t)ws->splits * ws->partial_sstride * 4) : 0;
     } else {
-        ws->U16 = ws->G[0] = ws->G[1] = ws->GE = ws->G16 = ws->gbar = ws->raw = 0;
+        ws->U16 = ws->G[0] = ws->G[1] = ws->GE = ws->G16 = ws->gbar = ws->raw = ws->partial = 0;
+        ws->splits = 1;
+        ws->partial_sstride = 0;
     }
     ws->total = off;
 }
@@ -813,7 +843,7 @@ size_t onf_wide_workspace_bytes(const OnfDims &d, int P, int n, bool bwd) {
     WideDims w;
     if (!make_wide_dims(d, &w)) return 0;
     WideWorkspace ws;
-    wide_workspace(w, P, n, bwd, &ws);
+    wide_workspace(w, d.lay.n_params, P, n, bwd, &ws);
     return ws.total;
 }
 
@@ -841,14 +871,9 @@ int onf_wide_pack(const OnfDims &d, const float *weights, unsigned char *packed,
     return NFOPP_OK;
 }
 
-static int launch_wgrad(WideWgradArgs g, cudaStream_t s) {
+static int launch_wgrad(const WideWgradArgs &g, cudaStream_t s) {
     const int MB = (g.CA + 127) / 128, NTT = (g.CB + WG_NT - 1) / WG_NT + (g.bias_off >= 0 ? 1 : 0);
-    const int base = g.P * MB * NTT;
-    int splits = (2 * sm_count() + base - 1) / base;
-    if (splits > g.T64) splits = g.T64;
-    if (splits < 1) splits = 1;
-    g.splits = splits;
-    const int items = base * splits;
+    const int items = g.P * MB * NTT * g.splits;
     wide_wgrad_kernel<<<items < sm_count() ? items : sm_count(), WG_THREADS, WW_SMEM, s>>>(g);
     NFOPP_CHECK_CUDA(cudaGetLastError());
     return NFOPP_OK;
@@ -856,7 +881,7 @@ static int launch_wgrad(WideWgradArgs g, cudaStream_t s) {
 
 int onf_wide_launch_count(const OnfDims &d, bool want_bwd, bool want_wgrad) {
     if (!want_bwd) return 2 + d.L;
-    return 2 + d.L + d.L + 1 + (want_wgrad ? d.L + 6 : 0);
+    return 2 + d.L + d.L + 1 + (want_wgrad ? d.L + 8 : 0);     // upper bound (the two split reductions run only when splits > 1)
 }
 
 // One ONF call (forward, or forward + backward): a fixed sequence of launches on `stream`.
@@ -868,7 +893,7 @@ int onf_wide_launch(const OnfArgs &o, const OnfWideExtra &x, int P, cudaStream_t
     const bool bwd = o.want_bwd != 0, wgrad = bwd && x.grad_out != nullptr, want_gx = bwd && o.gx_out != nullptr;
     const nfopp_onf_layout &L = o.d.lay;
     WideWorkspace ws;
-    wide_workspace(w, P, o.n, bwd, &ws);
+    wide_workspace(w, L.n_params, P, o.n, bwd, &ws);
     unsigned char *base = x.workspace;
     const int T64 = (o.n + 127) / 128 * 2;
     const int x_stride = o.x_stride ? o.x_stride : L.in_dim;
@@ -893,9 +918,14 @@ int onf_wide_launch(const OnfArgs &o, const OnfWideExtra &x, int P, cudaStream_t
         wide_gemm_kernel<0><<<items < grid_g ? items : grid_g, WG_THREADS, WG_SMEM, stream>>>(g);
         NFOPP_CHECK_CUDA(cudaGetLastError());
     }
+    float *raw = reinterpret_cast<float *>(base + ws.raw);
+    float *partial = reinterpret_cast<float *>(base + ws.partial);
     if (wgrad) {
+        // every element of the gradient is stored exactly once (by a wgrad job or by the encoder assembly) except the
+        // alignment padding of the blob, and with splits > 1 a split with no points stores nothing: start from zero
         NFOPP_CHECK_CUDA(cudaMemsetAsync(x.grad_out, 0, (size_t)P * L.n_params * sizeof(float), stream));
-        NFOPP_CHECK_CUDA(cudaMemsetAsync(base + ws.raw, 0, (size_t)P * w.K1 * 16 * sizeof(float), stream));
+        NFOPP_CHECK_CUDA(cudaMemsetAsync(raw, 0, (size_t)P * w.K1 * 16 * sizeof(float), stream));
+        if (ws.splits > 1) NFOPP_CHECK_CUDA(cudaMemsetAsync(partial, 0, (size_t)ws.splits * ws.partial_sstride * sizeof(float), stream));
     }
     int cur = 0;
     {
@@ -907,7 +937,6 @@ int onf_wide_launch(const OnfArgs &o, const OnfWideExtra &x, int P, cudaStream_t
             u.gbar = reinterpret_cast<float *>(base + ws.gbar);
             u.G16 = wgrad ? base + ws.G16 : nullptr;
             u.GL = base + ws.G[cur];
-            u.grad = wgrad ? x.grad_out : nullptr;
         }
         wide_out_kernel<<<dim3(T64, P), 256, 0, stream>>>(u);
         NFOPP_CHECK_CUDA(cudaGetLastError());
@@ -916,6 +945,7 @@ int onf_wide_launch(const OnfArgs &o, const OnfWideExtra &x, int P, cudaStream_t
     int rc;
     WideWgradArgs wg{};
     wg.P = P; wg.T64 = T64; wg.dst = x.grad_out; wg.dst_pstride = L.n_params;
+    wg.splits = ws.splits; wg.partial = partial; wg.partial_sstride = ws.partial_sstride; wg.row_lo = 0;
     if (wgrad) {
         // output layer: d w_out[:H] = sum_pt H_L * gbar ; d w_out[H:] = sum_pt E * gbar     (onf_model.py:48-49)
         WideWgradArgs j = wg;
@@ -923,6 +953,9 @@ int onf_wide_launch(const OnfArgs &o, const OnfWideExtra &x, int P, cudaStream_t
         j.dst_off = L.off_w_out; j.dst_ld = 1; j.rows_valid = w.H; j.cols_valid = 1; j.bias_off = -1;
         if ((rc = launch_wgrad(j, stream))) return rc;
         j.A = base + ws.E; j.CA = w.K1; j.dst_off = L.off_w_out + w.H; j.rows_valid = w.FIN;
+        if ((rc = launch_wgrad(j, stream))) return rc;
+        // d b_out = sum_pt 1 * gbar: row 3 of U16^T G16 (U16 column 3 is the ones column)
+        j.A = base + ws.U16; j.CA = 16; j.dst_off = L.off_b_out - 3; j.row_lo = 3; j.rows_valid = 4;
         if ((rc = launch_wgrad(j, stream))) return rc;
     }
     for (int l = w.L - 1; l >= 0; --l) {
@@ -961,9 +994,18 @@ int onf_wide_launch(const OnfArgs &o, const OnfWideExtra &x, int P, cudaStream_t
     if (wgrad) {
         WideWgradArgs j = wg;
         j.A = base + ws.GE; j.CA = w.K1; j.B = base + ws.U16; j.CB = 16;
-        j.dst = reinterpret_cast<float *>(base + ws.raw); j.dst_pstride = (size_t)w.K1 * 16;
+        j.dst = raw; j.dst_pstride = (size_t)w.K1 * 16;
+        j.partial = partial + (size_t)P * L.n_params;             // the encoder partials follow the gradient partials
         j.dst_off = 0; j.dst_ld = 16; j.rows_valid = w.K1; j.cols_valid = 16; j.bias_off = -1;
         if ((rc = launch_wgrad(j, stream))) return rc;
+        if (ws.splits > 1) {
+            const size_t n4g = (size_t)P * L.n_params / 4, n4r = (size_t)P * w.K1 * 16 / 4;
+            wide_reduce_kernel<<<(unsigned)((n4g + 255) / 256 < 4096 ? (n4g + 255) / 256 : 4096), 256, 0, stream>>>(
+                partial, ws.partial_sstride, ws.splits, x.grad_out, n4g);
+            wide_reduce_kernel<<<(unsigned)((n4r + 255) / 256), 256, 0, stream>>>(partial + (size_t)P * L.n_params, ws.partial_sstride,
+                                                                                   ws.splits, raw, n4r);
+            NFOPP_CHECK_CUDA(cudaGetLastError());
+        }
         WideAsmArgs s{};
         s.d = o.d; s.weights = o.weights; s.raw = reinterpret_cast<const float *>(base + ws.raw); s.grad = x.grad_out; s.K1 = w.K1;
         wide_asm_kernel<<<dim3((w.FIN + 255) / 256, P), 256, 0, stream>>>(s);

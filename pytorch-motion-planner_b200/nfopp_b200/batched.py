@@ -125,3 +125,28 @@ def corridor_config(problems: int, seed=0, **overrides) -> EngineConfig:
         checker="circle", env_shared=False, max_obstacles=20, robot_radius=0.3, checker_bounds=(0.0, 3.0, 0.0, 3.0),
         border=(-0.1, 3.1, -0.1, 3.1), rng_mode="philox", seed=seed)
     return replace(cfg, **overrides)
+
+
+def forest_config(problems: int, rows=100, cols=100, cell=0.03, seed=0, **overrides) -> EngineConfig:
+    """BASELINE config 3: random-obstacle worlds (forest-style occupancy grids, one per problem, obstacle_ratio 0.03,
+    notebooks/benchmark/forest_experiment.ipynb:98,424), point robot labelled by the notebook's grid checker
+    (onf_planner_image_map.ipynb:65-80), reference ONF and scripts/run_planner.py hyper-parameters."""
+    w, h = cols * cell, rows * cell
+    cfg = corridor_config(problems, seed=seed, checker="grid", env_shared=False, grid_shape=(rows, cols),
+                          grid_origin=(0.0, 0.0), grid_cell=cell, checker_bounds=(0.0, w, 0.0, h),
+                          border=(-0.1, w + 0.1, -0.1, h + 0.1), direction_delta_weight=0.0)
+    return replace(cfg, **overrides)
+
+
+def gridmap_wide_config(problems: int, rows=1000, cols=1000, cell=0.003, seed=0, hidden=256, layers=4,
+                        **overrides) -> EngineConfig:
+    """BASELINE config 4: ONE synthetic 1000x1000 occupancy grid (bench-mr style, obstacle ratio 0.1, seed 1) shared
+    by all problems, wide ONF (4x256 hidden, 200 Fourier + 20 heading features) -> tcgen05 grouped-GEMM path.
+    The map is scaled into the reference's 3 m x 3 m test world (cell = 3 mm) so that the reference's
+    hyper-parameters (offsets 1.5 / 0.02 m, sigma = 1) keep their meaning."""
+    w, h = cols * cell, rows * cell
+    cfg = corridor_config(problems, seed=seed, checker="grid", env_shared=True, grid_shape=(rows, cols),
+                          grid_origin=(0.0, 0.0), grid_cell=cell, checker_bounds=(0.0, w, 0.0, h),
+                          border=(-0.1, w + 0.1, -0.1, h + 0.1), direction_delta_weight=0.0,
+                          onf=OnfSpec(mean=0.0, sigma=1.0, use_cos=True, angle=True, hidden=hidden, layers=layers))
+    return replace(cfg, **overrides)

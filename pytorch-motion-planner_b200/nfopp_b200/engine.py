@@ -101,7 +101,9 @@ class EngineConfig:
     rng_mode: str = "philox"            # "philox" (on-device) | "inject" (host supplies every variate)
     seed: int = 0
     max_choice_uniforms: int = 0
-    onf_impl: str = "auto"              # ONF kernels: "auto" (tcgen05 when the shape allows) | "fma" | "tensor"
+    # ONF kernels: "auto" | "fma" (CUDA cores) | "tensor" (fused tcgen05 kernel, reference network shape) |
+    # "wide" (tcgen05 grouped GEMM per layer: wide / deep networks); auto = tensor when the shape fits, else wide
+    onf_impl: str = "auto"
 
     @property
     def dim(self):
@@ -135,7 +137,7 @@ class EngineConfig:
         c.border = (C.c_double * 4)(*self.border)
         c.rng_mode = {"philox": 0, "inject": 1}[self.rng_mode]
         c.seed, c.max_choice_uniforms = self.seed, self.max_choice_uniforms
-        c.onf_impl = {"auto": 0, "fma": 1, "tensor": 2}[self.onf_impl]
+        c.onf_impl = {"auto": 0, "fma": 1, "tensor": 2, "wide": 3}[self.onf_impl]
         return c
 
 

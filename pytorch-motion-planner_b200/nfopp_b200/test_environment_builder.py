@@ -87,3 +87,38 @@ class TestEnvironmentBuilder(object):
                 g &= (cx - pt[0]) ** 2 + (cy - pt[1]) ** 2 > (4 * cell) ** 2
             grids[i] = g
         return starts, goals, (0.0, w, 0.0, h), grids, (0.0, 0.0), cell
+
+    @staticmethod
+    def make_blob_grid(rows=1000, cols=1000, obstacle_ratio=0.1, cell=0.003, blob_cells=24, seed=1):
+        """One large synthetic occupancy grid (BASELINE config 4): square blobs of `blob_cells` cells dropped
+        uniformly until ~obstacle_ratio of the map is occupied (bench-mr's random-grid generator is in a missing
+        submodule; this is our own, documented in DESIGN.md).  Returns (grid uint8 [rows, cols], origin, cell)."""
+        rs = np.random.RandomState(seed)
+        grid = np.zeros((rows, cols), dtype=np.uint8)
+        n_blobs = int(obstacle_ratio * rows * cols / (blob_cells * blob_cells))
+        for _ in range(n_blobs):
+            r, c = rs.randint(0, rows - blob_cells), rs.randint(0, cols - blob_cells)
+            grid[r:r + blob_cells, c:c + blob_cells] = 1
+        return grid, (0.0, 0.0), cell
+
+    @staticmethod
+    def free_endpoints(grid, cell, problems, seed=0, margin_cells=40):
+        """Start / goal poses for `problems` problems on one shared grid: start in the lower-left quarter, goal in the
+        upper-right quarter, both in free cells with a free neighbourhood of +-3 cells; problem i uses
+        RandomState(seed + i)."""
+        rows, cols = grid.shape
+        occ = grid > 0
+        starts = np.zeros((problems, 3), dtype=np.float32)
+        goals = np.zeros((problems, 3), dtype=np.float32)
+
+        def free(rs, r0, r1, c0, c1):
+            while True:
+                r, c = rs.randint(r0, r1), rs.randint(c0, c1)
+                if not occ[max(r - 3, 0):r + 4, max(c - 3, 0):c + 4].any():
+                    return (c + 0.5) * cell, (r + 0.5) * cell
+        for i in range(problems):
+            rs = np.random.RandomState(seed + i)
+            m = margin_cells
+            starts[i, :2] = free(rs, m, rows // 3, m, cols // 3)
+            goals[i, :2] = free(rs, 2 * rows // 3, rows - m, 2 * cols // 3, cols - m)
+        return starts, goals

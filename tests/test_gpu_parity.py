@@ -372,3 +372,106 @@ def test_batch_problems_are_independent_and_deterministic(impl):
     torch.cuda.synchronize()
     assert torch.equal(g["traj"], runs[0]), "CUDA-graph replay differs from plain launches"
     assert g.counter("step_count") == 15
+
+
+# ---------------------------------------------------------------------------------------- wide ONF on occupancy grids
+def _grid_case(hidden, layers, seed=5, rows=200, cols=200, cell=0.015, onf_lr=5e-3):
+    """BASELINE config 4 in miniature: one occupancy grid, constrained planner, wide ONF.  The reference's ONF is
+    hard-wired to 2x100 (onf_model.py:18-23); the oracle's generalised restatement is bit-identical to it at that
+    shape (tests/test_oracle_golden.py) and is the checker for other widths."""
+    from nfopp_b200.test_environment_builder import TestEnvironmentBuilder as B
+    from oracle.planner import LiveSource, OraclePlanner, PlannerConfig
+    grid, (ox, oy), cell = B.make_blob_grid(rows, cols, 0.1, cell, blob_cells=12, seed=seed)
+    starts, goals = B.free_endpoints(grid, cell, 1, seed=seed, margin_cells=10)
+    w, h = cols * cell, rows * cell
+    bounds, border = (0.0, w, 0.0, h), (-0.1, w + 0.1, -0.1, h + 0.1)
+    ocfg = O.OnfConfig(mean=0.0, sigma=1.0, use_cos=True, angle=True, hidden=hidden, layers=layers)
+    pc = PlannerConfig(constrained=True, onf=ocfg, onf_lr=onf_lr, onf_betas=(0.9, 0.9), traj_lr=1e-2, traj_betas=(0.9, 0.9),
+                       init_collision_iteration=0, angle_offset=0.3)
+    blob = O.init_blob(ocfg, True, torch.Generator().manual_seed(seed))
+    op = OraclePlanner(pc, blob, lambda p: OC.grid_labels(p, grid, ox, oy, cell, bounds))
+    src = LiveSource(np.random.RandomState(seed), torch.Generator().manual_seed(seed))
+    op.init(starts[0], goals[0], border, src)
+    return op, src, pc, grid, cell, bounds, border
+
+
+def _grid_engine(pc, grid, cell, bounds, border, **over):
+    from _gpu_util import onf_spec
+    from nfopp_b200.engine import EngineConfig, PlannerEngine
+    kw = dict(problems=1, constrained=True, trajectory_length=pc.trajectory_length, onf=onf_spec(pc.onf), onf_lr=pc.onf_lr,
+              onf_betas=pc.onf_betas, traj_lr=pc.traj_lr, traj_betas=pc.traj_betas, init_collision_iteration=0,
+              angle_offset=pc.angle_offset, checker="grid", env_shared=True, grid_shape=grid.shape, grid_origin=(0.0, 0.0),
+              grid_cell=cell, checker_bounds=bounds, border=border, rng_mode="inject", max_choice_uniforms=4096)
+    kw.update(over)
+    eng = PlannerEngine(EngineConfig(**kw))
+    eng.set_grid(grid)
+    return eng
+
+
+@pytest.mark.parametrize("onf_lr", [5e-3, 1e-9])
+@pytest.mark.parametrize("hidden,layers,impl", [(256, 4, "wide"), (128, 3, "wide"), (100, 2, "wide"), (128, 3, "fma")])
+def test_lockstep_wide_onf_on_grid_map(hidden, layers, impl, onf_lr):
+    """Lock-step against the oracle on a grid map with a wide / deep ONF: the oracle's state before steps 0, 1, 10, 11 is
+    loaded into the engine, one GPU step runs on the oracle's variates, the post-step states are compared.
+
+    A wide ReLU network has thousands of (point, unit) pre-activations within rounding of zero and thousands of weights
+    whose gradient is within rounding of zero; either flips a mask / the sign of an Adam step (+-lr) - the chaos
+    BASELINE.md documents for the reference itself.  So: with the real learning rate the smooth quantities (labels,
+    indices, Adam moments) are compared and the trajectory half of the step is checked for CONSISTENCY with the
+    engine's own post-Adam weights; with lr ~ 0 (weights frozen) the whole post-step state is compared tightly."""
+    import copy
+    from _gpu_util import compare_state, load_state
+    op, src, pc, grid, cell, bounds, border = _grid_case(hidden, layers, onf_lr=onf_lr)
+    frozen = onf_lr < 1e-6
+    for k in range(12):
+        before = copy.deepcopy(op.state)
+        var = op.step(src)
+        if k not in (0, 1, 10, 11):
+            continue
+        eng = _grid_engine(pc, grid, cell, bounds, border, onf_impl=impl)
+        load_state(eng, before)
+        eng.inject_variates(var)
+        eng.step(1)
+        torch.cuda.synchronize()
+        n = int(eng["train_n"][0])
+        assert np.array_equal(eng["train_pos"][0, :n].cpu().numpy(), op.last["train_positions"]), "sampled poses"
+        assert np.array_equal(eng["train_y"][0, :n].cpu().numpy() > 0.5, op.last["train_labels"]), "labels"
+        if len(before["buf_pos"]) + 99 >= 100:
+            assert np.array_equal(eng["choice_idx"][0].cpu().numpy(), np.asarray(op.last["choice_idx"])), "sampled indices"
+        assert int(eng["status"][0]) == 0
+        traj_keys = ("traj", "traj_m", "traj_v", "lam", "mu")
+        compare_state(eng, op.state, STATE_TOL, skip=("w",) + (() if frozen else traj_keys))
+        m_ref = np.abs(op.state["m"].numpy())
+        em = max(U.relerr(eng["onf_m"][0].cpu().numpy(), op.state["m"].numpy()), 1e-7)
+        bound = onf_lr * np.minimum(3.0, 8 * em * m_ref.max() / np.maximum(m_ref, 1e-30)) + 1e-6
+        dw = np.abs(eng["onf_w"][0].cpu().numpy() - op.state["w"].numpy())
+        assert bool((dw <= bound).all()), float((dw / bound).max())
+        if not frozen:
+            # the path launch must have seen the weights Adam just wrote (operand copies refreshed): recompute its
+            # logits through the stateless API from the engine's current weights
+            q = eng["path_q"][0, :pc.trajectory_length - 1].cpu()
+            z, _, _ = _onf_call(pc.onf, eng["onf_w"].cpu(), q[None], impl=IMPLS[impl])
+            assert U.relerr(eng["path_z"][0].cpu(), z[0]) < 1e-5
+            for key in traj_keys:        # and the trajectory half stays close to the oracle's despite the +-lr weight noise
+                assert U.relerr(eng[key][0].cpu().numpy(), np.asarray(op.state[key])) < 5e-2, key
+        eng.close()
+
+
+def test_wide_engine_graph_replay_and_batch_independence():
+    """P problems on one shared grid with the wide path: CUDA-graph replay == plain launches; problems differ."""
+    from nfopp_b200.batched import BatchedPlanner, gridmap_wide_config
+    from nfopp_b200.test_environment_builder import TestEnvironmentBuilder as B
+    grid, _, cell = B.make_blob_grid(200, 200, 0.1, 0.015, blob_cells=12, seed=2)
+    starts, goals = B.free_endpoints(grid, cell, 6, seed=3, margin_cells=10)
+    outs = []
+    for graph in (False, True):
+        cfg = gridmap_wide_config(6, rows=200, cols=200, cell=cell, seed=9, hidden=128, layers=3)
+        bp = BatchedPlanner(cfg)
+        bp.init(starts, goals, grids=grid)
+        bp.step(6, graph=graph)
+        torch.cuda.synchronize()
+        outs.append(bp.paths().clone())
+        assert bool(torch.isfinite(outs[-1]).all())
+        assert int(np.abs(bp.status()).max()) == 0
+    assert torch.equal(outs[0], outs[1])
+    assert not torch.equal(outs[0][0], outs[0][1])
