@@ -33,41 +33,93 @@ UNIT = "problem-steps/s"
 PROBLEMS_PER_GPU = 1024
 
 
-def workload_config(problems, onf_impl="auto"):
+WORKLOADS = ("corridor", "forest", "gridmap-wide")
+
+
+def workload_config(problems, onf_impl="auto", workload="corridor"):
     tensor = onf_impl != "fma"
-    return {"workload": "configs[1]: corridor, non-holonomic forward-only ConstrainedNERFOptPlanner",
-            "problems_per_gpu": problems, "trajectory_length": 100, "onf": "F_in=220 (200 Fourier + 20 angle), 2x100 hidden",
-            "samples_per_step": 209, "checker": "disc r=0.3 vs 20 obstacle points per problem",
-            "rng": "on-device Philox4x32-10",
-            "onf_impl": "tensor (tcgen05, bf16 hi/lo split operands, fp32 TMEM accumulators, fused Adam)" if tensor
-            else "fma (CUDA-core fp32)",
-            "launch": f"CUDA graph of {8 if tensor else 9} kernels per step",
-            "l2": "per-step working set (ONF w/m/v fp32 + bf16 operand copy, ~0.55 GB at 1024 problems) exceeds the 126 MB L2"
-            if tensor else
-            "per-step working set (ONF w/m/v + gradient partials, ~1.3 GB at 1024 problems) exceeds the 126 MB L2"}
+    if workload == "corridor":
+        cfg = {"workload": "configs[1]: corridor, non-holonomic forward-only ConstrainedNERFOptPlanner",
+               "onf": "F_in=220 (200 Fourier + 20 angle), 2x100 hidden",
+               "checker": "disc r=0.3 vs 20 obstacle points per problem"}
+        impl = "tensor (fused tcgen05 kernel, bf16 hi/lo split operands, fp32 TMEM accumulators, fused Adam)"
+        ws = "ONF w/m/v fp32 + bf16 operand copy, ~0.55 GB at 1024 problems"
+    elif workload == "forest":
+        cfg = {"workload": "configs[2]: random-obstacle worlds (100x100 occupancy grid per problem, obstacle ratio 0.03), "
+                           "ConstrainedNERFOptPlanner, each problem its own ONF",
+               "onf": "F_in=220 (200 Fourier + 20 angle), 2x100 hidden",
+               "checker": "point robot vs the problem's own 100x100 occupancy grid (notebook MapCollisionChecker)"}
+        impl = "tensor (fused tcgen05 kernel, bf16 hi/lo split operands, fp32 TMEM accumulators, fused Adam)"
+        ws = "ONF w/m/v fp32 + bf16 operand copy, ~0.55 GB at 1024 problems"
+    else:
+        cfg = {"workload": "configs[3]: one synthetic 1000x1000 occupancy grid shared by all problems, wide ONF",
+               "onf": "F_in=220 (200 Fourier + 20 angle), 4x256 hidden",
+               "checker": "point robot vs one shared 1000x1000 occupancy grid (obstacle ratio 0.1, seed 1)"}
+        impl = "wide (tcgen05 grouped GEMM per layer, streamed bf16 hi/lo split weights, fp32 TMEM accumulators)"
+        ws = "ONF w/m/v/grad fp32 + operand copies (5 MB per problem) + activation tiles"
+    cfg.update({"problems_per_gpu": problems, "trajectory_length": 100, "samples_per_step": 209,
+                "rng": "on-device Philox4x32-10", "onf_impl": impl if tensor else "fma (CUDA-core fp32)",
+                "launch": "one CUDA graph per step",
+                "l2": f"per-step working set ({ws}) exceeds the 126 MB L2"})
+    return cfg
+
+
+def build_workload(workload, count, lo):
+    """-> (EngineConfig, init kwargs, {engine buffer name: host array} copied H2D every e2e step)."""
+    import numpy as np
+    from nfopp_b200.batched import corridor_config, forest_config, gridmap_wide_config
+    from nfopp_b200.test_environment_builder import TestEnvironmentBuilder as B
+    if workload == "corridor":
+        starts, goals, _, obstacles = B.make_corridor_batch(count, seed=lo)
+        return corridor_config(count, seed=1234 + lo), dict(obstacles=obstacles), starts, goals, {"obstacles": obstacles}
+    if workload == "forest":
+        starts, goals, _, grids, _, cell = B.make_random_grid_batch(count, seed=lo)
+        return forest_config(count, cell=cell, seed=1234 + lo), dict(grids=grids), starts, goals, {"grid": grids}
+    grid, _, cell = B.make_blob_grid()
+    starts, goals = B.free_endpoints(grid, cell, count, seed=lo)
+    return gridmap_wide_config(count, cell=cell, seed=1234 + lo), dict(grids=grid), starts, goals, {"grid": grid[None]}
+
+
+def onf_microbench(points=1 << 18, per_problem=4096, hidden=256, layers=4, reps=5):
+    """BASELINE metric part 2 (config 5, one bounded case; scripts/onf_sweep.py is the full sweep): ONF forward +
+    weight-gradient + input-gradient on `points` points in weight sets of `per_problem`, wide network."""
+    import torch
+    sys.path.insert(0, os.path.join(ROOT, "scripts"))
+    import onf_sweep
+    r = onf_sweep.bench_case(hidden, layers, per_problem, points, 3, reps, torch.Generator().manual_seed(0))
+    return {"mpts_per_s": r["mpts_per_s"], "tflops_algorithmic": r["tflops"], "ms": r["ms"], "points": r["points"],
+            "points_per_weight_set": per_problem, "onf": f"{layers}x{hidden} hidden, F_in=220",
+            "flops": "6 x MAC x points (SURVEY 8d); the bf16 hi/lo split issues 3x as many MMAs"}
 
 
 # ----------------------------------------------------------------------------------------- CPU baseline
 def _oracle_worker(args):
-    """Runs the CPU oracle (reference restatement) on one corridor problem for `budget` seconds."""
-    seed, budget = args
+    """Runs the CPU oracle (reference restatement) on one problem of the workload for `budget` seconds."""
+    seed, budget, workload = args
     import numpy as np
     import torch
     torch.set_num_threads(1)
     from oracle import checkers as OC
     from oracle import onf as O
     from oracle.planner import LiveSource, OraclePlanner, PlannerConfig
-    from nfopp_b200.test_environment_builder import TestEnvironmentBuilder
-    starts, goals, bounds, obstacles = TestEnvironmentBuilder.make_corridor_batch(1, seed=seed)
-    ocfg = O.OnfConfig(mean=0.0, sigma=1.0, use_cos=True, angle=True)
-    cfg = PlannerConfig(constrained=True, onf=ocfg, onf_lr=5e-2, onf_betas=(0.9, 0.9), traj_lr=1e-2,
-                        traj_betas=(0.9, 0.9), init_collision_iteration=0, angle_offset=0.3,
-                        direction_delta_weight=100.0)
+    cfg, init_kw, starts, goals, _ = build_workload(workload, 1, seed)
+    ocfg = O.OnfConfig(mean=cfg.onf.mean, sigma=cfg.onf.sigma, use_cos=cfg.onf.use_cos, angle=cfg.onf.angle,
+                       hidden=cfg.onf.hidden, layers=cfg.onf.layers)
+    pc = PlannerConfig(constrained=True, onf=ocfg, onf_lr=cfg.onf_lr, onf_betas=cfg.onf_betas, traj_lr=cfg.traj_lr,
+                       traj_betas=cfg.traj_betas, init_collision_iteration=0, angle_offset=cfg.angle_offset,
+                       direction_delta_weight=cfg.direction_delta_weight)
     blob = O.init_blob(ocfg, True, torch.Generator().manual_seed(seed))
-    op = OraclePlanner(cfg, blob, lambda p: OC.circle_labels(p, obstacles[0], 0.3, (0, 3, 0, 3)))
+    if workload == "corridor":
+        obstacles = init_kw["obstacles"]
+        label = lambda p: OC.circle_labels(p, obstacles[0], cfg.robot_radius, cfg.checker_bounds)   # noqa: E731
+    else:
+        grid = np.asarray(init_kw["grids"])
+        grid = grid[0] if grid.ndim == 3 else grid
+        label = lambda p: OC.grid_labels(p, grid, 0.0, 0.0, cfg.grid_cell, cfg.checker_bounds)      # noqa: E731
+    op = OraclePlanner(pc, blob, label)
     src = LiveSource(np.random.RandomState(seed), torch.Generator().manual_seed(seed))
-    op.init(starts[0], goals[0], bounds, src)
-    for _ in range(20):
+    op.init(starts[0], goals[0], cfg.border, src)
+    for _ in range(5 if workload == "gridmap-wide" else 20):
         op.step(src)
     n, t0 = 0, time.perf_counter()
     while time.perf_counter() - t0 < budget:
@@ -76,15 +128,15 @@ def _oracle_worker(args):
     return n, time.perf_counter() - t0
 
 
-def cpu_baseline(cores, budget):
+def cpu_baseline(cores, budget, workload="corridor"):
     """problem-steps/s of the oracle with `cores` independent single-thread processes (the only way the
     reference batches)."""
     ctx = mp.get_context("spawn")
     with ctx.Pool(cores) as pool:
-        res = pool.map(_oracle_worker, [(i, budget) for i in range(cores)])
+        res = pool.map(_oracle_worker, [(i, budget, workload) for i in range(cores)])
     value = sum(n / t for n, t in res)
     return {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"{cores} independent corridor problems x {budget:.0f} s of oracle planner.step() each "
+            "sample": f"{cores} independent {workload} problems x {budget:.0f} s of oracle planner.step() each "
                       f"({sum(n for n, _ in res)} steps), 1 torch thread per process"}
 
 
@@ -165,9 +217,8 @@ def run_ours(args):
     import numpy as np
     import torch
     import torch.distributed as dist
-    from nfopp_b200.batched import BatchedPlanner, corridor_config, shard_range
+    from nfopp_b200.batched import BatchedPlanner, shard_range
     from nfopp_b200.engine import onf_segments
-    from nfopp_b200.test_environment_builder import TestEnvironmentBuilder
 
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
@@ -177,11 +228,11 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     P = args.problems
     lo, hi = shard_range(P * world, rank, world)            # this rank's problem ids (weak scaling)
-    starts, goals, bounds, obstacles = TestEnvironmentBuilder.make_corridor_batch(hi - lo, seed=lo)
-    cfg = corridor_config(hi - lo, seed=1234 + lo)
-    cfg.onf_impl = args.onf_impl
+    cfg, init_kw, starts, goals, host_env = build_workload(args.workload, hi - lo, lo)
+    if args.onf_impl != "auto":
+        cfg.onf_impl = args.onf_impl
     planner = BatchedPlanner(cfg, device=f"cuda:{local}")
-    planner.init(starts, goals, obstacles=obstacles)
+    planner.init(starts, goals, **init_kw)
     eng = planner.engine
 
     def barrier():
@@ -211,16 +262,18 @@ def run_ours(args):
     value = P * world * args.steps / (ms * 1e-3)
 
     # ---- end-to-end through the host-facing API with HOST buffers ------------------------------------
-    h_obs = torch.as_tensor(obstacles).pin_memory()
+    h_env = {k: torch.as_tensor(np.ascontiguousarray(v)).to(eng[k].dtype).reshape(eng[k].shape).pin_memory()
+             for k, v in host_env.items()}
     h_start, h_goal = torch.as_tensor(starts).pin_memory(), torch.as_tensor(goals).pin_memory()
     h_paths = torch.empty(hi - lo, 102, 3, dtype=torch.float32).pin_memory()
     d_paths = torch.empty(hi - lo, 102, 3, dtype=torch.float32, device="cuda")
-    h2d = h_obs.numel() * 8 + (h_start.numel() + h_goal.numel()) * 4
+    h2d = sum(v.numel() * v.element_size() for v in h_env.values()) + (h_start.numel() + h_goal.numel()) * 4
     d2h = h_paths.numel() * 4
 
     def e2e_steps(k):
         for _ in range(k):
-            eng["obstacles"].copy_(h_obs, non_blocking=True)      # update_obstacle_points for every problem
+            for name, h in h_env.items():                         # update_obstacle_points / the map, for every problem
+                eng[name].copy_(h, non_blocking=True)
             eng["start"].copy_(h_start, non_blocking=True)
             eng["goal"].copy_(h_goal, non_blocking=True)
             planner.step(1)
@@ -258,26 +311,30 @@ def run_ours(args):
     train_ms = prof["onf_train_fwd_bwd"]
     flops_launch = 3 * 2 * mac * 209 * (hi - lo)                           # fwd + dgrad + wgrad over 209 points
     achieved = flops_launch / (train_ms * 1e-3) / 1e12
-    tensor = "onf_wp" in eng.buffers
+    impl = "wide" if "onf_ws" in eng.buffers else "tensor" if "onf_wp" in eng.buffers else "fma"
+    tensor = impl != "fma"
     traffic = None
     try:
         traffic = json.load(open(os.path.join(ROOT, "profiles", "roofline_traffic.json"))).get(
-            "onf_train_fwd_bwd_tensor" if tensor else "onf_train_fwd_bwd")
+            {"tensor": "onf_train_fwd_bwd_tensor", "wide": "onf_train_fwd_bwd_wide", "fma": "onf_train_fwd_bwd"}[impl])
     except Exception:
         pass
+    kernel_label = {"tensor": "onf_tc_kernel (ONF train fwd+bwd+Adam, fused tcgen05 kernel; algorithmic flops, the split "
+                              "products issue 3x as many MMAs)",
+                    "wide": "wide_gemm_kernel<0|1> + wide_wgrad_kernel (ONF train fwd+bwd as per-layer tcgen05 grouped GEMMs, "
+                            "one roofline entry for the whole train call; algorithmic flops, 3x as many MMAs issued)",
+                    "fma": "onf_tile_kernel (ONF train fwd+bwd, FMA path)"}[impl]
     step_bytes = (24 * n_params + 15_000) * (hi - lo)                     # bytes / problem-step
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32 (tensor path: bf16 hi/lo split products, fp32 accumulate)" if tensor else "f32",
-        "data": "synthetic", "config": workload_config(P, "tensor" if tensor else "fma"),
+        "data": "synthetic", "config": workload_config(P, impl, args.workload),
         "clocks": clocks.summary(),
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "steps": e2e_k, "ms_per_step": ms_e2e / e2e_k},
         "gpu_launches": int(launches),
-        "roofline": {"kernel": "onf_tc_kernel (ONF train fwd+bwd+Adam, tcgen05 path; algorithmic flops, the split "
-                               "products issue 3x as many MMAs)" if tensor else
-                     "onf_tile_kernel (ONF train fwd+bwd, FMA path)", "bound": "tensor",
+        "roofline": {"kernel": kernel_label, "bound": "tensor",
                      "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved / peak_tf,
                      "traffic": traffic, "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained (of measured)"
                      if peaks else "fallback",
@@ -288,9 +345,14 @@ def run_ours(args):
         "kernel_ms": prof,
         "paths_finite": finite, "paths_gathered": list(all_paths.shape),
     }
+    if world == 1 and not args.no_onf_microbench:
+        mb = onf_microbench()
+        mb["frac_of_bf16_peak"] = mb["tflops_algorithmic"] / peaks.get("bf16_tflops", 1590.0)
+        mb["peak"] = peaks.get("bf16_tflops", 1590.0)
+        line["onf_fwd_bwd"] = mb
     if world == 1 and not args.no_cpu_baseline:
         cores = max(1, min(os.cpu_count() or 1, 32))
-        line["cpu_baseline"] = cpu_baseline(cores, args.cpu_seconds)
+        line["cpu_baseline"] = cpu_baseline(cores, args.cpu_seconds, args.workload)
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -306,11 +368,11 @@ def run_reference(args):
         return
     cores = max(1, os.cpu_count() or 1)
     budget = max(2.0, min(30.0, args.cpu_seconds))
-    base = cpu_baseline(cores, budget)
+    base = cpu_baseline(cores, budget, args.workload)
     line = {"impl": "reference", "metric": METRIC, "value": base["value"], "unit": UNIT,
             "n_gpus": int(os.environ.get("WORLD_SIZE", args.gpus)), "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1e3 * cores / base["value"], "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args.problems),
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args.problems, "auto", args.workload),
             "cpu_baseline": base,
             "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
@@ -325,7 +387,10 @@ def main():
     ap.add_argument("--problems", type=int, default=PROBLEMS_PER_GPU, help="problems per GPU")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--onf-impl", default="auto", choices=["auto", "fma", "tensor"],
+    ap.add_argument("--no-onf-microbench", action="store_true")
+    ap.add_argument("--workload", default="corridor", choices=list(WORKLOADS),
+                    help="corridor = BASELINE configs[1] (the headline), forest = configs[2], gridmap-wide = configs[3]")
+    ap.add_argument("--onf-impl", default="auto", choices=["auto", "fma", "tensor", "wide"],
                     help="ONF kernels: tcgen05 tensor path (default for the reference network shape) or CUDA-core FMA")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
