@@ -353,7 +353,7 @@ def run_ours(args):
     if world == 1 and not args.no_cpu_baseline:
         cores = max(1, min(os.cpu_count() or 1, 32))
         line["cpu_baseline"] = cpu_baseline(cores, args.cpu_seconds, args.workload)
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -375,10 +375,25 @@ def run_reference(args):
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args.problems, "auto", args.workload),
             "cpu_baseline": base,
             "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
+
+
+_OUT = sys.stdout
+
+
+def emit(line):
+    """The ONE JSON line of the contract, on the process's real stdout."""
+    _OUT.write(json.dumps(line) + "\n")
+    _OUT.flush()
 
 
 def main():
+    global _OUT
+    # libraries (NCCL prints "NCCL version ..." on stdout) must not pollute the one-JSON-line contract: keep a private
+    # handle on the real stdout and point fd 1 at stderr for everything else
+    _OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    sys.stdout = sys.stderr
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
