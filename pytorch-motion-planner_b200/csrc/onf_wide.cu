@@ -22,6 +22,8 @@
 //   activations [P][n_pad/64 tiles][hi|lo][C/8 column octets][64 points][8 columns] bf16      (tile = C*256 bytes)
 //   Wf_l (fwd)  [n-tile of 256 out][hi|lo][in/8 octets][out rows][8 in]                       K-chunk contiguous
 //   Wd_l (dgrad)[n-tile of 256 in ][hi|lo][out/8 octets][in/8 octets][8 out][8 in]            K-chunk contiguous
+#include <stdlib.h>
+
 #include "onf.cuh"
 #include "tc05.cuh"
 
@@ -414,7 +416,8 @@ struct WideWgradArgs {
     size_t dst_pstride;
     int dst_off, dst_ld, row_lo, rows_valid, cols_valid;   // rows row_lo <= m < rows_valid, columns j < cols_valid are stored
     int bias_off;                // >= 0: one more N tile with B = ones -> dst[bias_off + m] = sum_pt A[pt, m]
-    int P, T64, splits;
+    int P, T64, splits;          // T64 = operand tiles per problem, TP points each
+    int TP;
     // splits > 1: split s of the point range stores its partial sums at partial + s * partial_sstride (same offsets as
     // dst); wide_reduce_kernel adds the splits in fixed order afterwards - deterministic, no atomics
     float *partial;
@@ -429,7 +432,8 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wide_wgrad_kernel(const WideWgr
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tempty + 1);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int MB = (a.CA + 127) / 128, NTL = (a.CB + WG_NT - 1) / WG_NT, NTT = NTL + (a.bias_off >= 0 ? 1 : 0);
-    const int tps = (a.T64 + a.splits - 1) / a.splits;        // 64-point tiles per split
+    const int TP = a.TP;                                      // points per operand tile (64 per-layer path, 32 chain path)
+    const int tps = (a.T64 + a.splits - 1) / a.splits;        // tiles per split
     const int items = a.P * MB * NTT * a.splits;
     for (int i = threadIdx.x; i < WW_ONES / 4; i += WG_THREADS) reinterpret_cast<uint32_t *>(ones)[i] = 0x3F803F80u;
     if (threadIdx.x == 0) {
@@ -468,15 +472,15 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wide_wgrad_kernel(const WideWgr
                 mbar_wait(empty + s, ((it / WW_STAGES) & 1) ^ 1);
                 unsigned char *As = smem + s * WW_STAGE, *Bs = As + WW_A_STAGE;
                 const size_t tile = (size_t)p * a.T64 + t;
-                if (lane == 0) mbar_expect_tx(full + s, (uint32_t)((MA + NB) * 64 * 4));
+                if (lane == 0) mbar_expect_tx(full + s, (uint32_t)((MA + NB) * TP * 4));
                 __syncwarp();
                 if (lane < 2) {
-                    bulk_g2s(As + lane * (WW_A_STAGE / 2), a.A + tile * a.CA * 256 + (size_t)lane * a.CA * 128 + (size_t)mb * 16 * 1024,
-                             (uint32_t)(MA * 128), full + s);
+                    bulk_g2s(As + lane * (WW_A_STAGE / 2), a.A + tile * a.CA * TP * 4 + (size_t)lane * a.CA * TP * 2 + (size_t)mb * 16 * TP * 16,
+                             (uint32_t)(MA * TP * 2), full + s);
                 } else if (lane < 4 && NB > 0) {
                     const int pl = lane - 2;
-                    bulk_g2s(Bs + pl * (WW_B_STAGE / 2), a.B + tile * a.CB * 256 + (size_t)pl * a.CB * 128 + (size_t)nt * 32 * 1024,
-                             (uint32_t)(NB * 128), full + s);
+                    bulk_g2s(Bs + pl * (WW_B_STAGE / 2), a.B + tile * a.CB * TP * 4 + (size_t)pl * a.CB * TP * 2 + (size_t)nt * 32 * TP * 16,
+                             (uint32_t)(NB * TP * 2), full + s);
                 }
             }
         }
@@ -498,17 +502,17 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wide_wgrad_kernel(const WideWgr
                 mbar_wait(full + s, (it / WW_STAGES) & 1);
                 fence_after_sync();
                 const uint32_t As = smem_u32(smem + s * WW_STAGE), Bs = As + WW_A_STAGE;
-#pragma unroll
-                for (int ks = 0; ks < 4; ++ks) {
-                    const uint64_t ah = desc_mnmajor(As + ks * 256, 128, 1024);
-                    const uint64_t al = desc_mnmajor(As + WW_A_STAGE / 2 + ks * 256, 128, 1024);
+                const uint32_t scol = (uint32_t)a.TP * 16u;
+                for (int ks = 0; ks < a.TP / 16; ++ks) {
+                    const uint64_t ah = desc_mnmajor(As + ks * 256, 128, scol);
+                    const uint64_t al = desc_mnmajor(As + WW_A_STAGE / 2 + ks * 256, 128, scol);
                     if (bias_tile) {
-                        const uint64_t bo = desc_mnmajor(ones_u + ks * 256, 128, 1024);
+                        const uint64_t bo = desc_mnmajor(ones_u + ks * 256, 128, scol);
                         mma_bf16(tmem, ah, bo, idesc, started ? 1u : 0u, lead);
                         mma_bf16(tmem, al, bo, idesc, 1u, lead);
                     } else {
-                        const uint64_t bh = desc_mnmajor(Bs + ks * 256, 128, 1024);
-                        const uint64_t bl = desc_mnmajor(Bs + WW_B_STAGE / 2 + ks * 256, 128, 1024);
+                        const uint64_t bh = desc_mnmajor(Bs + ks * 256, 128, scol);
+                        const uint64_t bl = desc_mnmajor(Bs + WW_B_STAGE / 2 + ks * 256, 128, scol);
                         wmma3(tmem, ah, al, bh, bl, idesc, started, lead);
                     }
                     started = true;
@@ -761,6 +765,572 @@ __global__ void __launch_bounds__(256) wide_asm_kernel(const WideAsmArgs a) {
     }
 }
 
+// ======================================================================================================================
+// Fused chain (hidden <= 256): encode -> L forward layers -> logit, dL/dz -> L input-gradient layers -> encoding backward
+// in ONE persistent kernel.  A 128-point row block stays in shared memory as the bf16 hi/lo A operand of every GEMM
+// (written in place by the epilogue of the previous one); only the weights stream (bulk copies, 5-stage ring of K=16
+// chunks).  Activations and gradients are still written to global memory once - they are the operands of the
+// weight-gradient GEMMs - but never read back by the chain (except the ReLU masks), which halves the HBM traffic of the
+// per-layer path.  Operand tiles here hold 32 points: [P][n/32][hi|lo][C/8][32 points][8] (one wgrad stage = one tile).
+// ======================================================================================================================
+constexpr int WC_THREADS = 320;          // warp 0 producer, warp 1 MMA issue + TMEM, warps 2..9 epilogue (2 per lane quarter)
+constexpr int WC_EPI = 256;
+constexpr int WC_STAGES = 5;
+constexpr int WC_STAGE = 16 * WG_NT * 4;             // K = 16 x N <= 256 x (hi + lo)
+constexpr int WC_ACT = 128 * 256 * 4;                // 128 points x K <= 256 x (hi + lo)
+constexpr int WC_ACT_PLANE = WC_ACT / 2;
+constexpr int WC_MISC_FLOATS = 5 * 256 + 2 * 128 + 3 * 2 * 128;   // pa pb pc svecA svecB | zpart | red
+constexpr int WC_SMEM = WC_ACT + WC_STAGES * WC_STAGE + 256 + WC_MISC_FLOATS * 4;
+
+struct WideChainArgs {
+    OnfDims d;
+    WideDims w;
+    const float *weights;
+    const unsigned char *packed;
+    size_t w_stride;
+    const float *x;
+    const int32_t *count;
+    int n, x_stride, P, T32, RB;
+    int want_bwd, want_wgrad, want_gx, gbar_mode;
+    const float *gz, *aux;
+    float wc, beta;
+    float *z_out, *gx_out;
+    unsigned char *E, *U16, *H[NFOPP_MAX_LAYERS], *G[NFOPP_MAX_LAYERS], *GE, *G16;
+    // per (problem, row block, lane quarter) partial sums over the quarter's 32 points of everything that is a plain
+    // reduction over points: bias gradients, output-layer gradient, encoder gradients (summed in fixed order afterwards)
+    float *auxp;
+};
+
+// layout of one aux vector (floats): db[L][Hp] | dw_out_h[Hp] | dw_out_e[K1] | enc0[K1] | enc1[K1] | enc2[K1] | db_out[16]
+__host__ __device__ inline int aux_db(const WideDims &w, int l) { return l * w.Hp; }
+__host__ __device__ inline int aux_dw3h(const WideDims &w) { return w.L * w.Hp; }
+__host__ __device__ inline int aux_dw3e(const WideDims &w) { return (w.L + 1) * w.Hp; }
+__host__ __device__ inline int aux_enc(const WideDims &w, int k) { return (w.L + 1) * w.Hp + (1 + k) * w.K1; }
+__host__ __device__ inline int aux_db3(const WideDims &w) { return (w.L + 1) * w.Hp + 4 * w.K1; }
+__host__ __device__ inline int aux_len(const WideDims &w) { return (w.L + 1) * w.Hp + 4 * w.K1 + 16; }
+
+// column sums over the 32 lanes of a warp for 16 columns: every lane returns sum_lanes v[lane >> 1] (v is clobbered)
+__device__ __forceinline__ float wcolsum16(float (&v)[16], int lane) {
+#pragma unroll
+    for (int o = 16; o >= 2; o >>= 1) {
+        const bool up = (lane & o) != 0;
+        const int h = o >> 1;
+#pragma unroll
+        for (int c = 0; c < h; ++c) {
+            const float keep = up ? v[c + h] : v[c];
+            const float send = up ? v[c] : v[c + h];
+            v[c] = keep + __shfl_xor_sync(0xffffffffu, send, o);
+        }
+    }
+    return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 1);
+}
+
+__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+
+// phase ph of an item: forward layer ph (ph < L) or input-gradient layer 2L-1-ph
+__device__ __forceinline__ void chain_phase(const WideDims &w, int ph, bool &dg, int &l, int &K, int &N) {
+    dg = ph >= w.L;
+    l = dg ? 2 * w.L - 1 - ph : ph;
+    K = dg ? w.Hp : w.kin[l];
+    N = dg ? w.kin[l] : w.Hp;
+}
+
+__global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideChainArgs a) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    unsigned char *act = smem, *ring = smem + WC_ACT;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(ring + WC_STAGES * WC_STAGE);
+    uint64_t *full = bars, *empty = bars + WC_STAGES, *tfull = bars + 2 * WC_STAGES, *act_ready = tfull + 1;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(act_ready + 1);
+    float *fm = reinterpret_cast<float *>(ring + WC_STAGES * WC_STAGE + 256);
+    float *s_pa = fm, *s_pb = fm + 256, *s_pc = fm + 512, *svecA = fm + 768, *svecB = fm + 1024, *zpart = fm + 1280, *red = fm + 1536;
+    const WideDims &w = a.w;
+    const nfopp_onf_layout &L = a.d.lay;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int items = a.P * a.RB;
+    const bool bwd = a.want_bwd != 0;
+    const int nph = bwd ? ((a.want_gx || a.want_wgrad) ? 2 * w.L : 2 * w.L - 1) : w.L;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < WC_STAGES; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 1); }
+        mbar_init(tfull, 1);
+        mbar_init(act_ready, WC_EPI / 32);
+        fence_mbar_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_slot, 256);
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp == 0) {
+        // ---------------- producer: the weight stream ----------------
+        uint32_t it = 0;
+        for (int item = blockIdx.x; item < items; item += gridDim.x) {
+            const int p = item / a.RB;
+            const unsigned char *Wp = a.packed + (size_t)p * a.w_stride;
+            for (int ph = 0; ph < nph; ++ph) {
+                bool dg; int l, K, N;
+                chain_phase(w, ph, dg, l, K, N);
+                const unsigned char *Wl = Wp + (dg ? w.wd_off[l] : w.wf_off[l]);
+                for (int st = 0; st < K / 16; ++st, ++it) {
+                    const int s = it % WC_STAGES;
+                    mbar_wait(empty + s, ((it / WC_STAGES) & 1) ^ 1);
+                    if (lane == 0) mbar_expect_tx(full + s, (uint32_t)(N * 64));
+                    __syncwarp();
+                    if (lane < 2)
+                        bulk_g2s(ring + s * WC_STAGE + lane * (WC_STAGE / 2), Wl + (size_t)lane * K * N * 2 + (size_t)st * N * 32,
+                                 (uint32_t)(N * 32), full + s);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ---------------- MMA issue ----------------
+        const uint32_t lead = elect_one();
+        const uint32_t act_u = smem_u32(act), ring_u = smem_u32(ring);
+        uint32_t it = 0, gph = 0;
+        for (int item = blockIdx.x; item < items; item += gridDim.x) {
+            for (int ph = 0; ph < nph; ++ph, ++gph) {
+                bool dg; int l, K, N;
+                chain_phase(w, ph, dg, l, K, N);
+                mbar_wait(act_ready, gph & 1);          // A operand written, accumulator drained
+                fence_after_sync();
+                const uint32_t idesc = instr_desc_bf16(128, N, 0, dg ? 1 : 0);
+                for (int st = 0; st < K / 16; ++st, ++it) {
+                    const int s = it % WC_STAGES;
+                    mbar_wait(full + s, (it / WC_STAGES) & 1);
+                    fence_after_sync();
+                    const uint32_t Bs = ring_u + s * WC_STAGE;
+                    const uint64_t ah = desc_kmajor(act_u + st * 4096, 128, 2048);
+                    const uint64_t al = desc_kmajor(act_u + WC_ACT_PLANE + st * 4096, 128, 2048);
+                    const uint64_t bh = dg ? desc_mnmajor(Bs, N * 16, 128) : desc_kmajor(Bs, 128, N * 16);
+                    const uint64_t bl = dg ? desc_mnmajor(Bs + WC_STAGE / 2, N * 16, 128) : desc_kmajor(Bs + WC_STAGE / 2, 128, N * 16);
+                    wmma3(tmem, ah, al, bh, bl, idesc, st > 0, lead);
+                    mma_commit(empty + s, lead);
+                }
+                mma_commit(tfull, lead);
+            }
+        }
+    } else {
+        // ---------------- epilogue warps: encoding, bias/ReLU, logit, dL/dz, masks, encoding backward ----------------
+        const int et = threadIdx.x - 64, q = warp & 3, half = (warp - 2) >> 2, row = q * 32 + lane, r32 = row & 31;
+        const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16);
+        const bool wgrad = a.want_wgrad != 0;
+        auto signal_act_ready = [&]() {
+            fence_proxy_async();
+            fence_before_sync();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(act_ready);
+        };
+        // store 16 columns (col0..col0+15) of this thread's point: A operand in shared memory and/or 32-point tile in global
+        auto store16 = [&](const float *v, int col0, bool to_act, unsigned char *gt, int C) {
+            uint4 h0, l0, h1, l1;
+            split8(v, h0, l0);
+            split8(v + 8, h1, l1);
+            if (to_act) {
+                unsigned char *o = act + (col0 / 8) * 2048 + row * 16;
+                *reinterpret_cast<uint4 *>(o) = h0;
+                *reinterpret_cast<uint4 *>(o + 2048) = h1;
+                *reinterpret_cast<uint4 *>(o + WC_ACT_PLANE) = l0;
+                *reinterpret_cast<uint4 *>(o + WC_ACT_PLANE + 2048) = l1;
+            }
+            if (gt) {
+                unsigned char *o = gt + (col0 / 8) * 512 + r32 * 16;
+                *reinterpret_cast<uint4 *>(o) = h0;
+                *reinterpret_cast<uint4 *>(o + 512) = h1;
+                *reinterpret_cast<uint4 *>(o + C * 64) = l0;
+                *reinterpret_cast<uint4 *>(o + C * 64 + 512) = l1;
+            }
+        };
+        uint32_t gph = 0;
+        int cur_p = -1;
+        for (int item = blockIdx.x; item < items; item += gridDim.x) {
+            const int p = item / a.RB, rb = item - p * a.RB;
+            const float *W = a.weights + (size_t)p * L.n_params;
+            const int cnt = a.count ? a.count[p] : a.n;
+            const int idx = rb * 128 + row;
+            const bool valid = idx < cnt;
+            const size_t t32 = (size_t)p * a.T32 + rb * 4 + (row >> 5);
+            float *auxv = wgrad ? a.auxp + (((size_t)p * a.RB + rb) * 4 + q) * aux_len(w) : nullptr;
+            // column sums of 16 values per lane over the warp's 32 points -> aux[off + col]
+            auto put_colsum = [&](float (&t)[16], int off) {
+                const float sum = wcolsum16(t, lane);
+                if ((lane & 1) == 0) auxv[off + (lane >> 1)] = sum;
+            };
+            // ---- per-problem feature parameters, skip-connection weights ----
+            epi_bar();                                      // everyone is done with the previous item's vectors
+            if (p != cur_p) {
+                for (int f = et; f < w.K1; f += WC_EPI) {
+                    float pa = 0.f, pb = 0.f, pc = 0.f;
+                    if (f < L.f_pos) {
+                        pa = W[L.off_enc_w + 2 * f];
+                        pb = W[L.off_enc_w + 2 * f + 1];
+                        pc = W[L.off_enc_b + f] + ((a.d.use_cos && f >= 100) ? 1.57079632679489662f : 0.f);
+                    } else if (f < L.f_in) {
+                        const int k = f - L.f_pos;
+                        const float b = W[L.off_ang_b + k], fr = W[L.off_ang_f + k];
+                        pb = fr;
+                        pc = fmaf(b, fr, k >= L.n_angle / 2 ? 1.57079632679489662f : 0.f);
+                    }
+                    s_pa[f] = pa; s_pb[f] = pb; s_pc[f] = pc;
+                }
+                cur_p = p;
+            }
+            for (int f = et; f < w.K1; f += WC_EPI) svecA[f] = f < L.f_in ? W[L.off_w_out + w.H + f] : 0.f;
+            epi_bar();
+            float x0 = 0.f, x1 = 0.f, x2 = 0.f;
+            if (valid) {
+                const float *xp = a.x + ((size_t)p * a.n + idx) * a.x_stride;
+                x0 = xp[0]; x1 = xp[1];
+                if (L.in_dim == 3) x2 = xp[2];
+            }
+            const float u0 = (x0 - a.d.mean) / a.d.sigma, u1 = (x1 - a.d.mean) / a.d.sigma, th = x2;
+            // ---- encoding (onf_model.py:37-46) -> A operand of layer 0, skip term of the logit ----
+            float zp = 0.f;
+            {
+                const int nch = w.K1 / 16, c_lo = half ? (nch + 1) / 2 : 0, c_hi = half ? nch : (nch + 1) / 2;
+                unsigned char *Et = bwd && wgrad ? a.E + t32 * w.K1 * 128 : nullptr;
+                for (int ch = c_lo; ch < c_hi; ++ch) {
+                    float e[16];
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        const int f = ch * 16 + i;
+                        const float arg = fmaf(f < L.f_pos ? u1 : th, s_pb[f], fmaf(u0, s_pa[f], s_pc[f]));
+                        e[i] = (valid && f < L.f_in) ? __sinf(w_reduce_2pi(arg)) : 0.f;
+                        zp = fmaf(e[i], svecA[f], zp);
+                    }
+                    store16(e, ch * 16, true, Et, w.K1);
+                }
+            }
+            signal_act_ready();
+            float gb = 0.f;
+            for (int ph = 0; ph < nph; ++ph, ++gph) {
+                bool dg; int l, K, N;
+                chain_phase(w, ph, dg, l, K, N);
+                // ---- per-phase vectors ----
+                epi_bar();                                  // previous phase's vectors are dead
+                if (!dg) {
+                    for (int c = et; c < N; c += WC_EPI) svecA[c] = c < w.H ? W[L.off_b[l] + c] : 0.f;
+                    if (l == w.L - 1)
+                        for (int c = et; c < N; c += WC_EPI) svecB[c] = c < w.H ? W[L.off_w_out + c] : 0.f;
+                } else if (l == 0) {
+                    for (int c = et; c < N; c += WC_EPI) svecA[c] = c < L.f_in ? W[L.off_w_out + w.H + c] : 0.f;
+                }
+                epi_bar();
+                const int nch = N / 16, c_lo = half ? (nch + 1) / 2 : 0, c_hi = half ? nch : (nch + 1) / 2;
+                mbar_wait(tfull, gph & 1);
+                fence_after_sync();
+                if (!dg) {
+                    const bool last = l == w.L - 1;
+                    unsigned char *Ht = bwd ? a.H[l] + t32 * w.Hp * 128 : nullptr;     // masks (and wgrad operands)
+                    for (int ch = c_lo; ch < c_hi; ++ch) {
+                        float v[16];
+                        tmem_ld16(taddr + ch * 16, v);
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i] + svecA[ch * 16 + i], 0.f);
+                        if (last) {
+#pragma unroll
+                            for (int i = 0; i < 16; ++i) zp = fmaf(v[i], svecB[ch * 16 + i], zp);
+                        }
+                        store16(v, ch * 16, !last, last ? nullptr : Ht, w.Hp);      // H_L itself is not needed again
+                    }
+                    if (last) {
+                        // ---- logit (onf_model.py:48-49), dL/dz ----
+                        zpart[half * 128 + row] = zp;
+                        epi_bar();
+                        const float z = zpart[row] + zpart[128 + row] + W[L.off_b_out];
+                        const size_t gi = (size_t)p * a.n + idx;
+                        if (half == 0 && valid && a.z_out) a.z_out[gi] = z;
+                        if (bwd) {
+                            if (valid) {
+                                if (a.gbar_mode == 0) gb = a.gz[gi];
+                                else if (a.gbar_mode == 1) gb = (sigmoid_f(z) - a.aux[gi]) / (float)cnt;
+                                else {
+                                    const float zb = z * a.beta;
+                                    const float ez = expf(zb);
+                                    gb = a.wc * (zb > 20.f ? 1.f : ez / (ez + 1.f));
+                                    if (a.gbar_mode == 3) {
+                                        const float tz = tanhf(z);
+                                        gb += a.aux[gi] * (1.f - tz * tz);
+                                    }
+                                }
+                            }
+                            if (wgrad && half == 0) {
+                                const float sgb = warp_sum(gb);
+                                if (lane == 0) auxv[aux_db3(w)] = sgb;
+                            }
+                            // second pass over the accumulator: gradient w.r.t. the last hidden layer's pre-activation
+                            unsigned char *Gt = wgrad ? a.G[l] + t32 * w.Hp * 128 : nullptr;
+                            for (int ch = c_lo; ch < c_hi; ++ch) {
+                                float v[16], t[16];
+                                tmem_ld16(taddr + ch * 16, v);
+#pragma unroll
+                                for (int i = 0; i < 16; ++i) {
+                                    const float h = fmaxf(v[i] + svecA[ch * 16 + i], 0.f);
+                                    t[i] = gb * h;                                        // d w_out[:H] = sum_pt gbar * H_L
+                                    v[i] = h > 0.f ? gb * svecB[ch * 16 + i] : 0.f;
+                                }
+                                store16(v, ch * 16, true, Gt, w.Hp);
+                                if (wgrad) {
+                                    put_colsum(t, aux_dw3h(w) + ch * 16);
+                                    put_colsum(v, aux_db(w, l) + ch * 16);                // d b_L = sum_pt G_L
+                                }
+                            }
+                        }
+                    }
+                } else if (l > 0) {
+                    // ---- input gradient of layer l -> ReLU mask of layer l-1 -> A operand of the next phase ----
+                    const unsigned char *Mt = a.H[l - 1] + t32 * w.Hp * 128;
+                    unsigned char *Gt = wgrad ? a.G[l - 1] + t32 * w.Hp * 128 : nullptr;
+                    for (int ch = c_lo; ch < c_hi; ++ch) {
+                        float v[16];
+                        const uint4 m0 = *reinterpret_cast<const uint4 *>(Mt + (ch * 2) * 512 + r32 * 16);
+                        const uint4 m1 = *reinterpret_cast<const uint4 *>(Mt + (ch * 2 + 1) * 512 + r32 * 16);
+                        tmem_ld16(taddr + ch * 16, v);
+                        const uint32_t mw[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) {
+                            const uint32_t bits = (mw[i >> 1] >> ((i & 1) * 16)) & 0x7FFFu;
+                            v[i] = bits != 0 ? v[i] : 0.f;
+                        }
+                        store16(v, ch * 16, true, Gt, w.Hp);
+                        if (wgrad) put_colsum(v, aux_db(w, l - 1) + ch * 16);             // d b_{l-1} = sum_pt G_{l-1}
+                    }
+                } else {
+                    // ---- dL/dE (+ skip connection) -> encoding backward: dL/d(arg) for the encoder gradients, dL/dx ----
+                    float g0 = 0.f, g1 = 0.f, g2 = 0.f;
+                    for (int ch = c_lo; ch < c_hi; ++ch) {
+                        float v[16], te[16], t0[16], t1[16];
+                        tmem_ld16(taddr + ch * 16, v);
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) {
+                            const int f = ch * 16 + i;
+                            const bool fourier = f < L.f_pos;
+                            const float pa = s_pa[f], pb = s_pb[f];
+                            const float xx = fourier ? u1 : th;
+                            const float rr = w_reduce_2pi(fmaf(xx, pb, fmaf(u0, pa, s_pc[f])));
+                            const bool on = valid && f < L.f_in;
+                            const float ge = fmaf(gb, svecA[f], v[i]);
+                            const float gp = on ? ge * __cosf(rr) : 0.f;
+                            te[i] = on ? gb * __sinf(rr) : 0.f;              // d w_out[H:] = sum_pt gbar * E
+                            t0[i] = gp * u0;                                  // encoder: sum gp*u0, sum gp*x1, sum gp
+                            t1[i] = gp * xx;
+                            v[i] = gp;
+                            if (fourier) { g0 = fmaf(gp, pa, g0); g1 = fmaf(gp, pb, g1); }
+                            else g2 = fmaf(gp, pb, g2);
+                        }
+                        if (wgrad) {
+                            put_colsum(te, aux_dw3e(w) + ch * 16);
+                            put_colsum(t0, aux_enc(w, 0) + ch * 16);
+                            put_colsum(t1, aux_enc(w, 1) + ch * 16);
+                            put_colsum(v, aux_enc(w, 2) + ch * 16);
+                        }
+                    }
+                    if (a.gx_out) {
+                        red[(0 * 2 + half) * 128 + row] = g0;
+                        red[(1 * 2 + half) * 128 + row] = g1;
+                        red[(2 * 2 + half) * 128 + row] = g2;
+                        epi_bar();
+                        if (half == 0 && valid) {
+                            float *out = a.gx_out + ((size_t)p * a.n + idx) * a.x_stride;
+                            out[0] = (red[row] + red[128 + row]) / a.d.sigma;
+                            out[1] = (red[256 + row] + red[384 + row]) / a.d.sigma;
+                            if (L.in_dim == 3) out[2] = red[512 + row] + red[640 + row];
+                            for (int c = L.in_dim; c < a.x_stride; ++c) out[c] = 0.f;
+                        }
+                    }
+                }
+                if (ph + 1 < nph) signal_act_ready();
+                else fence_before_sync();
+            }
+        }
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem, 256);
+}
+
+// ---- fixed-order sum of the aux partials over (row block, lane quarter) -> gradient blob --------------------------------
+struct WideAuxArgs {
+    OnfDims d;
+    WideDims w;
+    const float *weights, *aux;
+    float *grad;
+    int RB;
+};
+
+__global__ void __launch_bounds__(256) wide_aux_kernel(const WideAuxArgs a) {
+    const int p = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+    const WideDims &w = a.w;
+    const nfopp_onf_layout &L = a.d.lay;
+    const int n = aux_len(w);
+    if (i >= n) return;
+    const float *src = a.aux + (size_t)p * a.RB * 4 * n + i;
+    float s = 0.f;
+    for (int r = 0; r < a.RB * 4; ++r) s += src[(size_t)r * n];
+    float *G = a.grad + (size_t)p * L.n_params;
+    const float *W = a.weights + (size_t)p * L.n_params;
+    if (i < aux_dw3h(w)) {
+        const int l = i / w.Hp, c = i - l * w.Hp;
+        if (c < w.H) G[L.off_b[l] + c] = s;
+    } else if (i < aux_dw3e(w)) {
+        const int c = i - aux_dw3h(w);
+        if (c < w.H) G[L.off_w_out + c] = s;
+    } else if (i < aux_enc(w, 0)) {
+        const int f = i - aux_dw3e(w);
+        if (f < L.f_in) G[L.off_w_out + w.H + f] = s;
+    } else if (i < aux_db3(w)) {
+        const int k = (i - aux_enc(w, 0)) / w.K1, f = i - aux_enc(w, k);
+        if (f < L.f_pos) {
+            if (k == 0) G[L.off_enc_w + 2 * f] = s;
+            else if (k == 1) G[L.off_enc_w + 2 * f + 1] = s;
+            else G[L.off_enc_b + f] = a.d.bias ? s : 0.f;
+        } else if (f < L.f_in && k >= 1) {
+            // heading features: d b_k = f_k * sum gp ; d f_k = sum gp * (theta + b_k)   (two aux entries -> two-term sums)
+            const int kk = f - L.f_pos;
+            const float *s2 = a.aux + (size_t)p * a.RB * 4 * n + aux_enc(w, 2) + f;
+            float sgp = 0.f;
+            for (int r = 0; r < a.RB * 4; ++r) sgp += s2[(size_t)r * n];
+            if (k == 1) G[L.off_ang_f + kk] = fmaf(W[L.off_ang_b + kk], sgp, s);
+            else G[L.off_ang_b + kk] = W[L.off_ang_f + kk] * sgp;
+        }
+    } else if (i == aux_db3(w)) {
+        G[L.off_b_out] = s;
+    }
+}
+
+// ---- weight gradients of ALL hidden layers in one launch, one 256 x N tile per CTA (TMEM: 2 x 256 columns) -------------
+// item = (problem, layer, split of the point range); A = G_l (M = out), B = H_{l-1} or E (N = in), both MN-major views of
+// 32-point operand tiles; every operand byte is read once per point (the 128-row-per-CTA kernel reads B twice).
+constexpr int W2_STAGES = 3;
+constexpr int W2_HALF = 256 * 32 * 2;                // one plane of one operand: 256 columns x 32 points x bf16
+constexpr int W2_STAGE = 4 * W2_HALF;                // A hi | A lo | B hi | B lo
+constexpr int W2_SMEM = W2_STAGES * W2_STAGE + 256;
+
+struct WideWgrad2Args {
+    WideDims w;
+    const unsigned char *G[NFOPP_MAX_LAYERS], *Hin[NFOPP_MAX_LAYERS];    // A = G[l] (C = Hp), B = Hin[l] (C = kin[l])
+    int off_w[NFOPP_MAX_LAYERS];
+    float *dst;
+    size_t dst_pstride;
+    int P, T32, splits;
+    float *partial;
+    size_t partial_sstride;
+};
+
+__global__ void __launch_bounds__(WG_THREADS, 1) wide_wgrad2_kernel(const WideWgrad2Args a) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + W2_STAGES * W2_STAGE);
+    uint64_t *full = bars, *empty = bars + W2_STAGES, *tfull = bars + 2 * W2_STAGES, *tempty = tfull + 1;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tempty + 1);
+    const WideDims &w = a.w;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int tps = (a.T32 + a.splits - 1) / a.splits;
+    const int items = a.P * w.L * a.splits;
+    const int MB = (w.Hp + 127) / 128;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < W2_STAGES; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 1); }
+        mbar_init(tfull, 1);
+        mbar_init(tempty, 4);
+        fence_mbar_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_slot, 512);
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem = *tmem_slot;
+    auto decode = [&](int item, int &p, int &l, int &sp, int &t0, int &t1) {
+        sp = item % a.splits;
+        l = (item / a.splits) % w.L;
+        p = item / (a.splits * w.L);
+        t0 = sp * tps;
+        t1 = min(a.T32, t0 + tps);
+    };
+    if (warp == 0) {
+        uint32_t it = 0;
+        for (int item = blockIdx.x; item < items; item += gridDim.x) {
+            int p, l, sp, t0, t1;
+            decode(item, p, l, sp, t0, t1);
+            const int CB = w.kin[l];
+            for (int t = t0; t < t1; ++t, ++it) {
+                const int s = it % W2_STAGES;
+                mbar_wait(empty + s, ((it / W2_STAGES) & 1) ^ 1);
+                unsigned char *st = smem + s * W2_STAGE;
+                const size_t tile = (size_t)p * a.T32 + t;
+                if (lane == 0) mbar_expect_tx(full + s, (uint32_t)((w.Hp + CB) * 128));
+                __syncwarp();
+                if (lane < 2) bulk_g2s(st + lane * W2_HALF, a.G[l] + tile * w.Hp * 128 + (size_t)lane * w.Hp * 64, (uint32_t)(w.Hp * 64), full + s);
+                else if (lane < 4)
+                    bulk_g2s(st + lane * W2_HALF, a.Hin[l] + tile * CB * 128 + (size_t)(lane - 2) * CB * 64, (uint32_t)(CB * 64), full + s);
+            }
+        }
+    } else if (warp == 1) {
+        const uint32_t lead = elect_one();
+        uint32_t it = 0, tile_it = 0;
+        for (int item = blockIdx.x; item < items; item += gridDim.x, ++tile_it) {
+            int p, l, sp, t0, t1;
+            decode(item, p, l, sp, t0, t1);
+            const int NB = w.kin[l];
+            mbar_wait(tempty, (tile_it & 1) ^ 1);
+            fence_after_sync();
+            const uint32_t idesc = instr_desc_bf16(128, NB, 1, 1);
+            bool started = false;
+            for (int t = t0; t < t1; ++t, ++it) {
+                const int s = it % W2_STAGES;
+                mbar_wait(full + s, (it / W2_STAGES) & 1);
+                fence_after_sync();
+                const uint32_t st = smem_u32(smem + s * W2_STAGE);
+#pragma unroll
+                for (int ks = 0; ks < 2; ++ks) {
+                    const uint64_t bh = desc_mnmajor(st + 2 * W2_HALF + ks * 256, 128, 512);
+                    const uint64_t bl = desc_mnmajor(st + 3 * W2_HALF + ks * 256, 128, 512);
+                    for (int mb = 0; mb < MB; ++mb) {
+                        const uint64_t ah = desc_mnmajor(st + mb * 16 * 512 + ks * 256, 128, 512);
+                        const uint64_t al = desc_mnmajor(st + W2_HALF + mb * 16 * 512 + ks * 256, 128, 512);
+                        wmma3(tmem + mb * 256, ah, al, bh, bl, idesc, started, lead);
+                    }
+                    started = true;
+                }
+                mma_commit(empty + s, lead);
+            }
+            mma_commit(tfull, lead);
+        }
+    } else {
+        const int q = warp & 3;
+        uint32_t tile_it = 0;
+        for (int item = blockIdx.x; item < items; item += gridDim.x, ++tile_it) {
+            int p, l, sp, t0, t1;
+            decode(item, p, l, sp, t0, t1);
+            const int NB = w.kin[l], ld = w.kin_real[l];
+            mbar_wait(tfull, tile_it & 1);
+            fence_after_sync();
+            float *D = (a.splits > 1 ? a.partial + (size_t)sp * a.partial_sstride : a.dst) + (size_t)p * a.dst_pstride + a.off_w[l];
+            const bool has_work = t1 > t0;
+            for (int mb = 0; mb < MB; ++mb) {
+                const int m = mb * 128 + q * 32 + lane;
+                const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + mb * 256;
+                for (int c0 = 0; c0 < NB; c0 += 16) {
+                    float v[16];
+                    tmem_ld16(taddr + c0, v);
+                    if (m >= w.H || !has_work) continue;
+                    float *drow = D + (size_t)m * ld + c0;
+#pragma unroll
+                    for (int i4 = 0; i4 < 4; ++i4)
+                        if (c0 + 4 * i4 + 3 < ld)
+                            *reinterpret_cast<float4 *>(drow + 4 * i4) = make_float4(v[4 * i4], v[4 * i4 + 1], v[4 * i4 + 2], v[4 * i4 + 3]);
+                        else
+                            for (int i = 4 * i4; i < 4 * i4 + 4; ++i)
+                                if (c0 + i < ld) drow[i] = v[i];
+                }
+            }
+            fence_before_sync();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty);
+        }
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem, 512);
+}
+
 // dst[i] = sum over splits (fixed order) of partial[s][i]
 __global__ void __launch_bounds__(256) wide_reduce_kernel(const float *partial, size_t sstride, int splits, float *dst, size_t n4) {
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
@@ -787,12 +1357,23 @@ int sm_count() {
 }
 
 struct WideWorkspace {
-    size_t E, U16, H[NFOPP_MAX_LAYERS], G[2], GE, G16, gbar, raw, partial, total;
+    size_t E, U16, H[NFOPP_MAX_LAYERS], G[NFOPP_MAX_LAYERS], GE, G16, gbar, raw, partial, aux, total;
     int splits;                  // point-range splits of every weight-gradient job of the call
     size_t partial_sstride;      // floats between splits: [P][n_params] gradient partial, then [P][K1*16] encoder partial
 };
 
+// the fused chain kernel holds a 128-point row block of <= 256 columns in shared memory
+bool wide_use_chain(const WideDims &w) {
+    static int enabled = -1;
+    if (enabled < 0) {
+        const char *e = getenv("NFOPP_WIDE_CHAIN");
+        enabled = (e && e[0] == '0') ? 0 : 1;
+    }
+    return enabled && w.Hp <= 256 && w.K1 <= 256;
+}
+
 void wide_workspace(const WideDims &w, int n_params, int P, int n, bool bwd, WideWorkspace *ws) {
+    const bool chain = wide_use_chain(w);
     const size_t T64 = (size_t)(n + 127) / 128 * 2, tiles = (size_t)P * T64;
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off += align256(bytes); return o; };
@@ -804,8 +1385,8 @@ void wide_workspace(const WideDims &w, int n_params, int P, int n, bool bwd, Wid
         for (int l = 2; l < w.L; ++l) ws->H[l] = ws->H[l & 1];
     if (bwd) {
         ws->U16 = take(tiles * 16 * 256);
-        ws->G[0] = take(tiles * w.Hp * 256);
-        ws->G[1] = take(tiles * w.Hp * 256);
+        for (int l = 0; l < NFOPP_MAX_LAYERS; ++l) ws->G[l] = 0;
+        for (int l = 0; l < (chain ? w.L : 2); ++l) ws->G[l] = take(tiles * w.Hp * 256);    // chain: every layer's gradient is kept for wgrad
         ws->GE = take(tiles * w.K1 * 256);
         ws->G16 = take(tiles * 16 * 256);
         ws->gbar = take(tiles * 64 * 4);
@@ -818,8 +1399,10 @@ void wide_workspace(const WideDims &w, int n_params, int P, int n, bool bwd, Wid
         ws->splits = splits < 1 ? 1 : splits;
         ws->partial_sstride = (size_t)P * ((size_t)n_params + (size_t)w.K1 * 16);
         ws->partial = ws->splits > 1 ? take((size_t)ws->splits * ws->partial_sstride * 4) : 0;
+        ws->aux = chain ? take((size_t)P * (T64 / 2) * 4 * aux_len(w) * 4) : 0;
     } else {
-        ws->U16 = ws->G[0] = ws->G[1] = ws->GE = ws->G16 = ws->gbar = ws->raw = ws->partial = 0;
+        ws->U16 = ws->GE = ws->G16 = ws->gbar = ws->raw = ws->partial = ws->aux = 0;
+        for (int l = 0; l < NFOPP_MAX_LAYERS; ++l) ws->G[l] = 0;
         ws->splits = 1;
         ws->partial_sstride = 0;
     }
@@ -853,6 +1436,8 @@ int onf_wide_prepare(const OnfDims &d) {
     NFOPP_CHECK_CUDA(cudaFuncSetAttribute(wide_gemm_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM));
     NFOPP_CHECK_CUDA(cudaFuncSetAttribute(wide_gemm_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM));
     NFOPP_CHECK_CUDA(cudaFuncSetAttribute(wide_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WW_SMEM));
+    NFOPP_CHECK_CUDA(cudaFuncSetAttribute(wide_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WC_SMEM));
+    NFOPP_CHECK_CUDA(cudaFuncSetAttribute(wide_wgrad2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, W2_SMEM));
     sm_count();
     return NFOPP_OK;
 }
@@ -898,6 +1483,55 @@ int onf_wide_launch(const OnfArgs &o, const OnfWideExtra &x, int P, cudaStream_t
     const int T64 = (o.n + 127) / 128 * 2;
     const int x_stride = o.x_stride ? o.x_stride : L.in_dim;
     const int grid_g = sm_count();
+
+    if (wide_use_chain(w)) {
+        // ---- fused chain: ONE kernel for encode -> forward -> dL/dz -> input gradients -> encoding backward ----
+        float *raw = reinterpret_cast<float *>(base + ws.raw);
+        float *partial = reinterpret_cast<float *>(base + ws.partial);
+        const int T32 = 2 * T64;
+        if (wgrad) {
+            NFOPP_CHECK_CUDA(cudaMemsetAsync(x.grad_out, 0, (size_t)P * L.n_params * sizeof(float), stream));
+            NFOPP_CHECK_CUDA(cudaMemsetAsync(raw, 0, (size_t)P * w.K1 * 16 * sizeof(float), stream));
+            if (ws.splits > 1)
+                NFOPP_CHECK_CUDA(cudaMemsetAsync(partial, 0, (size_t)ws.splits * ws.partial_sstride * sizeof(float), stream));
+        }
+        WideChainArgs c{};
+        c.d = o.d; c.w = w; c.weights = o.weights; c.packed = x.packed; c.w_stride = align256(w.packed_bytes);
+        c.x = o.x; c.count = o.count; c.n = o.n; c.x_stride = x_stride; c.P = P; c.T32 = T32; c.RB = T64 / 2;
+        c.want_bwd = bwd; c.want_wgrad = wgrad; c.want_gx = want_gx; c.gbar_mode = o.gbar_mode; c.gz = o.gz; c.aux = o.aux;
+        c.wc = o.wc; c.beta = o.beta; c.z_out = o.z_out; c.gx_out = o.gx_out;
+        c.E = base + ws.E; c.U16 = base + ws.U16; c.GE = base + ws.GE; c.G16 = base + ws.G16;
+        c.auxp = reinterpret_cast<float *>(base + ws.aux);
+        for (int l = 0; l < w.L; ++l) { c.H[l] = base + ws.H[l]; c.G[l] = base + ws.G[l]; }
+        const int items = P * c.RB;
+        wide_chain_kernel<<<items < grid_g ? items : grid_g, WC_THREADS, WC_SMEM, stream>>>(c);
+        NFOPP_CHECK_CUDA(cudaGetLastError());
+        if (!wgrad) return NFOPP_OK;
+        {   // hidden-layer weight gradients: one launch, 256 x N tile per CTA
+            WideWgrad2Args g{};
+            g.w = w; g.dst = x.grad_out; g.dst_pstride = L.n_params; g.P = P; g.T32 = T32; g.splits = ws.splits;
+            g.partial = partial; g.partial_sstride = ws.partial_sstride;
+            for (int l = 0; l < w.L; ++l) {
+                g.G[l] = base + ws.G[l]; g.Hin[l] = l == 0 ? base + ws.E : base + ws.H[l - 1]; g.off_w[l] = L.off_w[l];
+            }
+            const int witems = P * w.L * ws.splits;
+            wide_wgrad2_kernel<<<witems < grid_g ? witems : grid_g, WG_THREADS, W2_SMEM, stream>>>(g);
+            NFOPP_CHECK_CUDA(cudaGetLastError());
+        }
+        if (ws.splits > 1) {
+            const size_t n4g = (size_t)P * L.n_params / 4;
+            wide_reduce_kernel<<<(unsigned)((n4g + 255) / 256 < 4096 ? (n4g + 255) / 256 : 4096), 256, 0, stream>>>(
+                partial, ws.partial_sstride, ws.splits, x.grad_out, n4g);
+            NFOPP_CHECK_CUDA(cudaGetLastError());
+        }
+        // biases, output layer, encoder: fixed-order sum of the chain kernel's per-row-block partials
+        WideAuxArgs ax{};
+        ax.d = o.d; ax.w = w; ax.weights = o.weights; ax.aux = reinterpret_cast<const float *>(base + ws.aux); ax.grad = x.grad_out;
+        ax.RB = T64 / 2;
+        wide_aux_kernel<<<dim3((aux_len(w) + 255) / 256, P), 256, 0, stream>>>(ax);
+        NFOPP_CHECK_CUDA(cudaGetLastError());
+        return NFOPP_OK;
+    }
 
     {
         WideEncArgs e{};
@@ -945,7 +1579,7 @@ int onf_wide_launch(const OnfArgs &o, const OnfWideExtra &x, int P, cudaStream_t
     int rc;
     WideWgradArgs wg{};
     wg.P = P; wg.T64 = T64; wg.dst = x.grad_out; wg.dst_pstride = L.n_params;
-    wg.splits = ws.splits; wg.partial = partial; wg.partial_sstride = ws.partial_sstride; wg.row_lo = 0;
+    wg.splits = ws.splits; wg.partial = partial; wg.partial_sstride = ws.partial_sstride; wg.row_lo = 0; wg.TP = 64;
     if (wgrad) {
         // output layer: d w_out[:H] = sum_pt H_L * gbar ; d w_out[H:] = sum_pt E * gbar     (onf_model.py:48-49)
         WideWgradArgs j = wg;
