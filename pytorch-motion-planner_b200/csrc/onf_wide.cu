@@ -773,13 +773,14 @@ __global__ void __launch_bounds__(256) wide_asm_kernel(const WideAsmArgs a) {
 // weight-gradient GEMMs - but never read back by the chain (except the ReLU masks), which halves the HBM traffic of the
 // per-layer path.  Operand tiles here hold 32 points: [P][n/32][hi|lo][C/8][32 points][8] (one wgrad stage = one tile).
 // ======================================================================================================================
-constexpr int WC_THREADS = 320;          // warp 0 producer, warp 1 MMA issue + TMEM, warps 2..9 epilogue (2 per lane quarter)
-constexpr int WC_EPI = 256;
+constexpr int WC_PARTS = 4;              // epilogue warps per TMEM lane quarter (each takes 1/WC_PARTS of the columns)
+constexpr int WC_EPI = 128 * WC_PARTS;
+constexpr int WC_THREADS = 64 + WC_EPI;  // warp 0 producer, warp 1 MMA issue + TMEM, then the epilogue warps
 constexpr int WC_STAGES = 5;
 constexpr int WC_STAGE = 16 * WG_NT * 4;             // K = 16 x N <= 256 x (hi + lo)
 constexpr int WC_ACT = 128 * 256 * 4;                // 128 points x K <= 256 x (hi + lo)
 constexpr int WC_ACT_PLANE = WC_ACT / 2;
-constexpr int WC_MISC_FLOATS = 5 * 256 + 2 * 128 + 3 * 2 * 128;   // pa pb pc svecA svecB | zpart | red
+constexpr int WC_MISC_FLOATS = 5 * 256 + WC_PARTS * 128 + 3 * WC_PARTS * 128;   // pa pb pc svecA svecB | zpart | red
 constexpr int WC_SMEM = WC_ACT + WC_STAGES * WC_STAGE + 256 + WC_MISC_FLOATS * 4;
 
 struct WideChainArgs {
@@ -790,7 +791,7 @@ struct WideChainArgs {
     size_t w_stride;
     const float *x;
     const int32_t *count;
-    int n, x_stride, P, T32, RB;
+    int n, x_stride, P, T32, RB, CL;
     int want_bwd, want_wgrad, want_gx, gbar_mode;
     const float *gz, *aux;
     float wc, beta;
@@ -825,7 +826,7 @@ __device__ __forceinline__ float wcolsum16(float (&v)[16], int lane) {
     return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 1);
 }
 
-__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, %0;" ::"n"(WC_EPI) : "memory"); }
 
 // phase ph of an item: forward layer ph (ph < L) or input-gradient layer 2L-1-ph
 __device__ __forceinline__ void chain_phase(const WideDims &w, int ph, bool &dg, int &l, int &K, int &N) {
@@ -842,15 +843,20 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
     uint64_t *full = bars, *empty = bars + WC_STAGES, *tfull = bars + 2 * WC_STAGES, *act_ready = tfull + 1;
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(act_ready + 1);
     float *fm = reinterpret_cast<float *>(ring + WC_STAGES * WC_STAGE + 256);
-    float *s_pa = fm, *s_pb = fm + 256, *s_pc = fm + 512, *svecA = fm + 768, *svecB = fm + 1024, *zpart = fm + 1280, *red = fm + 1536;
+    float *s_pa = fm, *s_pb = fm + 256, *s_pc = fm + 512, *svecA = fm + 768, *svecB = fm + 1024, *zpart = fm + 1280, *red = fm + 1280 + WC_PARTS * 128;
     const WideDims &w = a.w;
     const nfopp_onf_layout &L = a.d.lay;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int items = a.P * a.RB;
+    // clusters of CL CTAs walk the same problem (CL consecutive row blocks): every weight chunk is read from L2 once per
+    // cluster and multicast into the shared memory of all its CTAs (each CTA issues 1/CL of every stage)
+    const int CL = a.CL, rank = CL > 1 ? (int)cluster_ctarank() : 0;
+    const uint16_t cmask = (uint16_t)((1u << CL) - 1u);
+    const int RBG = (a.RB + CL - 1) / CL;              // row-block groups per problem
+    const int items = a.P * RBG, cid = blockIdx.x / CL, ncl = gridDim.x / CL;
     const bool bwd = a.want_bwd != 0;
     const int nph = bwd ? ((a.want_gx || a.want_wgrad) ? 2 * w.L : 2 * w.L - 1) : w.L;
     if (threadIdx.x == 0) {
-        for (int s = 0; s < WC_STAGES; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 1); }
+        for (int s = 0; s < WC_STAGES; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, CL); }
         mbar_init(tfull, 1);
         mbar_init(act_ready, WC_EPI / 32);
         fence_mbar_init();
@@ -858,14 +864,15 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
     if (warp == 1) tmem_alloc(tmem_slot, 256);
     fence_before_sync();
     __syncthreads();
+    if (CL > 1) cluster_sync_all();                    // every CTA's barriers exist before anyone multicasts into them
     fence_after_sync();
     const uint32_t tmem = *tmem_slot;
 
     if (warp == 0) {
         // ---------------- producer: the weight stream ----------------
         uint32_t it = 0;
-        for (int item = blockIdx.x; item < items; item += gridDim.x) {
-            const int p = item / a.RB;
+        for (int item = cid; item < items; item += ncl) {
+            const int p = item / RBG;
             const unsigned char *Wp = a.packed + (size_t)p * a.w_stride;
             for (int ph = 0; ph < nph; ++ph) {
                 bool dg; int l, K, N;
@@ -876,9 +883,17 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
                     mbar_wait(empty + s, ((it / WC_STAGES) & 1) ^ 1);
                     if (lane == 0) mbar_expect_tx(full + s, (uint32_t)(N * 64));
                     __syncwarp();
-                    if (lane < 2)
-                        bulk_g2s(ring + s * WC_STAGE + lane * (WC_STAGE / 2), Wl + (size_t)lane * K * N * 2 + (size_t)st * N * 32,
-                                 (uint32_t)(N * 32), full + s);
+                    if (CL == 1) {
+                        if (lane < 2)
+                            bulk_g2s(ring + s * WC_STAGE + lane * (WC_STAGE / 2), Wl + (size_t)lane * K * N * 2 + (size_t)st * N * 32,
+                                     (uint32_t)(N * 32), full + s);
+                    } else if (lane == 0) {
+                        // this CTA's slice of the stage: plane = slice / (CL/2), part of the plane's chunk = slice % (CL/2)
+                        const int per = CL / 2, pl = rank / per, part = rank - pl * per, bytes = N * 32 / per;
+                        bulk_g2s_multicast(ring + s * WC_STAGE + pl * (WC_STAGE / 2) + part * bytes,
+                                           Wl + (size_t)pl * K * N * 2 + (size_t)st * N * 32 + (size_t)part * bytes, (uint32_t)bytes, full + s,
+                                           cmask);
+                    }
                 }
             }
         }
@@ -887,7 +902,7 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
         const uint32_t lead = elect_one();
         const uint32_t act_u = smem_u32(act), ring_u = smem_u32(ring);
         uint32_t it = 0, gph = 0;
-        for (int item = blockIdx.x; item < items; item += gridDim.x) {
+        for (int item = cid; item < items; item += ncl) {
             for (int ph = 0; ph < nph; ++ph, ++gph) {
                 bool dg; int l, K, N;
                 chain_phase(w, ph, dg, l, K, N);
@@ -904,14 +919,18 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
                     const uint64_t bh = dg ? desc_mnmajor(Bs, N * 16, 128) : desc_kmajor(Bs, 128, N * 16);
                     const uint64_t bl = dg ? desc_mnmajor(Bs + WC_STAGE / 2, N * 16, 128) : desc_kmajor(Bs + WC_STAGE / 2, 128, N * 16);
                     wmma3(tmem, ah, al, bh, bl, idesc, st > 0, lead);
-                    mma_commit(empty + s, lead);
+                    if (CL == 1) mma_commit(empty + s, lead);
+                    else mma_commit_multicast(empty + s, cmask, lead);
                 }
                 mma_commit(tfull, lead);
             }
         }
     } else {
         // ---------------- epilogue warps: encoding, bias/ReLU, logit, dL/dz, masks, encoding backward ----------------
-        const int et = threadIdx.x - 64, q = warp & 3, half = (warp - 2) >> 2, row = q * 32 + lane, r32 = row & 31;
+        const int et = threadIdx.x - 64, q = warp & 3, part = (warp - 2) >> 2, row = q * 32 + lane, r32 = row & 31;
+        // this warp's share of `nch` 16-column chunks
+        auto chunk_lo = [&](int nch) { return (nch * part) / WC_PARTS; };
+        auto chunk_hi = [&](int nch) { return (nch * (part + 1)) / WC_PARTS; };
         const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16);
         const bool wgrad = a.want_wgrad != 0;
         auto signal_act_ready = [&]() {
@@ -942,18 +961,20 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
         };
         uint32_t gph = 0;
         int cur_p = -1;
-        for (int item = blockIdx.x; item < items; item += gridDim.x) {
-            const int p = item / a.RB, rb = item - p * a.RB;
+        for (int item = cid; item < items; item += ncl) {
+            const int p = item / RBG, rb = (item - p * RBG) * CL + rank;
+            const bool live = rb < a.RB;                   // a cluster's last group may hold fewer than CL row blocks: the spare
+                                                           // CTAs keep the weight-stream protocol going on dummy (all-invalid) rows
             const float *W = a.weights + (size_t)p * L.n_params;
             const int cnt = a.count ? a.count[p] : a.n;
             const int idx = rb * 128 + row;
-            const bool valid = idx < cnt;
-            const size_t t32 = (size_t)p * a.T32 + rb * 4 + (row >> 5);
-            float *auxv = wgrad ? a.auxp + (((size_t)p * a.RB + rb) * 4 + q) * aux_len(w) : nullptr;
+            const bool valid = live && idx < cnt;
+            const size_t t32 = live ? (size_t)p * a.T32 + rb * 4 + (row >> 5) : 0;
+            float *auxv = (wgrad && live) ? a.auxp + (((size_t)p * a.RB + rb) * 4 + q) * aux_len(w) : nullptr;
             // column sums of 16 values per lane over the warp's 32 points -> aux[off + col]
             auto put_colsum = [&](float (&t)[16], int off) {
                 const float sum = wcolsum16(t, lane);
-                if ((lane & 1) == 0) auxv[off + (lane >> 1)] = sum;
+                if (auxv && (lane & 1) == 0) auxv[off + (lane >> 1)] = sum;
             };
             // ---- per-problem feature parameters, skip-connection weights ----
             epi_bar();                                      // everyone is done with the previous item's vectors
@@ -986,8 +1007,8 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
             // ---- encoding (onf_model.py:37-46) -> A operand of layer 0, skip term of the logit ----
             float zp = 0.f;
             {
-                const int nch = w.K1 / 16, c_lo = half ? (nch + 1) / 2 : 0, c_hi = half ? nch : (nch + 1) / 2;
-                unsigned char *Et = bwd && wgrad ? a.E + t32 * w.K1 * 128 : nullptr;
+                const int nch = w.K1 / 16, c_lo = chunk_lo(nch), c_hi = chunk_hi(nch);
+                unsigned char *Et = (bwd && wgrad && live) ? a.E + t32 * w.K1 * 128 : nullptr;
                 for (int ch = c_lo; ch < c_hi; ++ch) {
                     float e[16];
 #pragma unroll
@@ -1015,12 +1036,12 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
                     for (int c = et; c < N; c += WC_EPI) svecA[c] = c < L.f_in ? W[L.off_w_out + w.H + c] : 0.f;
                 }
                 epi_bar();
-                const int nch = N / 16, c_lo = half ? (nch + 1) / 2 : 0, c_hi = half ? nch : (nch + 1) / 2;
+                const int nch = N / 16, c_lo = chunk_lo(nch), c_hi = chunk_hi(nch);
                 mbar_wait(tfull, gph & 1);
                 fence_after_sync();
                 if (!dg) {
                     const bool last = l == w.L - 1;
-                    unsigned char *Ht = bwd ? a.H[l] + t32 * w.Hp * 128 : nullptr;     // masks (and wgrad operands)
+                    unsigned char *Ht = (bwd && live) ? a.H[l] + t32 * w.Hp * 128 : nullptr;     // masks (and wgrad operands)
                     for (int ch = c_lo; ch < c_hi; ++ch) {
                         float v[16];
                         tmem_ld16(taddr + ch * 16, v);
@@ -1034,11 +1055,13 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
                     }
                     if (last) {
                         // ---- logit (onf_model.py:48-49), dL/dz ----
-                        zpart[half * 128 + row] = zp;
+                        zpart[part * 128 + row] = zp;
                         epi_bar();
-                        const float z = zpart[row] + zpart[128 + row] + W[L.off_b_out];
+                        float z = W[L.off_b_out];
+#pragma unroll
+                        for (int k = 0; k < WC_PARTS; ++k) z += zpart[k * 128 + row];
                         const size_t gi = (size_t)p * a.n + idx;
-                        if (half == 0 && valid && a.z_out) a.z_out[gi] = z;
+                        if (part == 0 && valid && a.z_out) a.z_out[gi] = z;
                         if (bwd) {
                             if (valid) {
                                 if (a.gbar_mode == 0) gb = a.gz[gi];
@@ -1053,12 +1076,12 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
                                     }
                                 }
                             }
-                            if (wgrad && half == 0) {
+                            if (wgrad && part == 0) {
                                 const float sgb = warp_sum(gb);
-                                if (lane == 0) auxv[aux_db3(w)] = sgb;
+                                if (lane == 0 && auxv) auxv[aux_db3(w)] = sgb;
                             }
                             // second pass over the accumulator: gradient w.r.t. the last hidden layer's pre-activation
-                            unsigned char *Gt = wgrad ? a.G[l] + t32 * w.Hp * 128 : nullptr;
+                            unsigned char *Gt = (wgrad && live) ? a.G[l] + t32 * w.Hp * 128 : nullptr;
                             for (int ch = c_lo; ch < c_hi; ++ch) {
                                 float v[16], t[16];
                                 tmem_ld16(taddr + ch * 16, v);
@@ -1078,8 +1101,8 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
                     }
                 } else if (l > 0) {
                     // ---- input gradient of layer l -> ReLU mask of layer l-1 -> A operand of the next phase ----
-                    const unsigned char *Mt = a.H[l - 1] + t32 * w.Hp * 128;
-                    unsigned char *Gt = wgrad ? a.G[l - 1] + t32 * w.Hp * 128 : nullptr;
+                    const unsigned char *Mt = a.H[l - 1] + t32 * w.Hp * 128;        // dummy rows read tile 0: harmless
+                    unsigned char *Gt = (wgrad && live) ? a.G[l - 1] + t32 * w.Hp * 128 : nullptr;
                     for (int ch = c_lo; ch < c_hi; ++ch) {
                         float v[16];
                         const uint4 m0 = *reinterpret_cast<const uint4 *>(Mt + (ch * 2) * 512 + r32 * 16);
@@ -1125,15 +1148,20 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
                         }
                     }
                     if (a.gx_out) {
-                        red[(0 * 2 + half) * 128 + row] = g0;
-                        red[(1 * 2 + half) * 128 + row] = g1;
-                        red[(2 * 2 + half) * 128 + row] = g2;
+                        red[(0 * WC_PARTS + part) * 128 + row] = g0;
+                        red[(1 * WC_PARTS + part) * 128 + row] = g1;
+                        red[(2 * WC_PARTS + part) * 128 + row] = g2;
                         epi_bar();
-                        if (half == 0 && valid) {
+                        if (part == 0 && valid) {
                             float *out = a.gx_out + ((size_t)p * a.n + idx) * a.x_stride;
-                            out[0] = (red[row] + red[128 + row]) / a.d.sigma;
-                            out[1] = (red[256 + row] + red[384 + row]) / a.d.sigma;
-                            if (L.in_dim == 3) out[2] = red[512 + row] + red[640 + row];
+                            float sg[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+                            for (int c = 0; c < 3; ++c)
+#pragma unroll
+                                for (int k = 0; k < WC_PARTS; ++k) sg[c] += red[(c * WC_PARTS + k) * 128 + row];
+                            out[0] = sg[0] / a.d.sigma;
+                            out[1] = sg[1] / a.d.sigma;
+                            if (L.in_dim == 3) out[2] = sg[2];
                             for (int c = L.in_dim; c < a.x_stride; ++c) out[c] = 0.f;
                         }
                     }
@@ -1145,6 +1173,7 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
     }
     fence_before_sync();
     __syncthreads();
+    if (CL > 1) cluster_sync_all();                    // no peer may still multicast into / arrive on this CTA's shared memory
     if (warp == 1) tmem_dealloc(tmem, 256);
 }
 
@@ -1456,6 +1485,39 @@ int onf_wide_pack(const OnfDims &d, const float *weights, unsigned char *packed,
     return NFOPP_OK;
 }
 
+// NFOPP_CHAIN_CLUSTER = 1 | 2 | 4 (default 1): CTAs per cluster of the fused chain kernel
+static int chain_cluster_size() {
+    static int cl = 0;
+    if (!cl) {
+        const char *e = getenv("NFOPP_CHAIN_CLUSTER");
+        cl = e ? atoi(e) : 1;      // measured on B200: the weight stream is not the bottleneck, multicast does not pay
+        if (cl != 1 && cl != 2 && cl != 4) cl = 1;
+    }
+    return cl;
+}
+// co-resident clusters of the chain kernel (1 CTA per SM): asked from the occupancy API once per cluster size
+static int chain_max_clusters(int CL) {
+    static int cached[5] = {0, 0, 0, 0, 0};
+    if (!cached[CL]) {
+        int n = 0;
+        if (CL == 1) n = sm_count();
+        else {
+            cudaLaunchConfig_t cfg{};
+            cfg.gridDim = dim3(sm_count() / CL * CL); cfg.blockDim = dim3(WC_THREADS); cfg.dynamicSmemBytes = WC_SMEM;
+            cudaLaunchAttribute at[1];
+            at[0].id = cudaLaunchAttributeClusterDimension;
+            at[0].val.clusterDim.x = CL; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+            cfg.attrs = at; cfg.numAttrs = 1;
+            if (cudaOccupancyMaxActiveClusters(&n, wide_chain_kernel, &cfg) != cudaSuccess || n <= 0) {
+                cudaGetLastError();
+                n = sm_count() / CL / 2;
+            }
+        }
+        cached[CL] = n > 0 ? n : 1;
+    }
+    return cached[CL];
+}
+
 static int launch_wgrad(const WideWgradArgs &g, cudaStream_t s) {
     const int MB = (g.CA + 127) / 128, NTT = (g.CB + WG_NT - 1) / WG_NT + (g.bias_off >= 0 ? 1 : 0);
     const int items = g.P * MB * NTT * g.splits;
@@ -1503,9 +1565,23 @@ int onf_wide_launch(const OnfArgs &o, const OnfWideExtra &x, int P, cudaStream_t
         c.E = base + ws.E; c.U16 = base + ws.U16; c.GE = base + ws.GE; c.G16 = base + ws.G16;
         c.auxp = reinterpret_cast<float *>(base + ws.aux);
         for (int l = 0; l < w.L; ++l) { c.H[l] = base + ws.H[l]; c.G[l] = base + ws.G[l]; }
-        const int items = P * c.RB;
-        wide_chain_kernel<<<items < grid_g ? items : grid_g, WC_THREADS, WC_SMEM, stream>>>(c);
-        NFOPP_CHECK_CUDA(cudaGetLastError());
+        {
+            // cluster size: as many CTAs sharing one weight stream as the problem has row blocks (<= 4)
+            int CL = chain_cluster_size();
+            while (CL > 1 && c.RB < CL) CL /= 2;
+            c.CL = CL;
+            const int groups = P * ((c.RB + CL - 1) / CL);
+            cudaLaunchConfig_t cfg{};
+            cfg.blockDim = dim3(WC_THREADS); cfg.dynamicSmemBytes = WC_SMEM; cfg.stream = stream;
+            cudaLaunchAttribute at[1];
+            at[0].id = cudaLaunchAttributeClusterDimension;
+            at[0].val.clusterDim.x = CL; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+            cfg.attrs = at; cfg.numAttrs = 1;
+            int max_clusters = chain_max_clusters(CL);
+            const int ncl = groups < max_clusters ? groups : max_clusters;
+            cfg.gridDim = dim3(ncl * CL);
+            NFOPP_CHECK_CUDA(cudaLaunchKernelEx(&cfg, wide_chain_kernel, c));
+        }
         if (!wgrad) return NFOPP_OK;
         {   // hidden-layer weight gradients: one launch, 256 x N tile per CTA
             WideWgrad2Args g{};

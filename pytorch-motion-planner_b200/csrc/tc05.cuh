@@ -59,6 +59,24 @@ __device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, u
                  : "memory");
 }
 
+// ---- thread-block clusters: multicast bulk copy (one L2 read feeds the shared memory of every CTA in ctaMask, at the
+// same CTA-relative offsets, signalling the mbarrier at the same offset in each of them) ----------------------------
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void bulk_g2s_multicast(void *dst_smem, const void *src_gmem, uint32_t bytes, uint64_t *bar, uint16_t cta_mask) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1], %2, [%3], %4;" ::"r"(
+            smem_u32(dst_smem)),
+        "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)), "h"(cta_mask)
+        : "memory");
+}
+
 // ---- TMEM ------------------------------------------------------------------------------------------
 // one full warp; writes the TMEM base address to *dst_smem
 __device__ __forceinline__ void tmem_alloc(uint32_t *dst_smem, uint32_t ncols) {
@@ -163,6 +181,16 @@ __device__ __forceinline__ void mma_commit(uint64_t *bar, uint32_t issue = 1) {
         "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}"
         :
         : "r"(smem_u32(bar)), "r"(issue)
+        : "memory");
+}
+// the same, arriving on the mbarrier at this CTA-relative offset in every CTA of cta_mask (cluster launch)
+__device__ __forceinline__ void mma_commit_multicast(uint64_t *bar, uint16_t cta_mask, uint32_t issue = 1) {
+    asm volatile(
+        "{\n\t.reg .pred q;\n\t"
+        "setp.ne.b32 q, %1, 0;\n\t"
+        "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %2;\n\t}"
+        :
+        : "r"(smem_u32(bar)), "r"(issue), "h"(cta_mask)
         : "memory");
 }
 // 1-D descriptor arithmetic: a descriptor whose start address is moved by `bytes` (no carry out of the 14-bit field
