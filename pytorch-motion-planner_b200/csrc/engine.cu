@@ -333,7 +333,9 @@ static int build_layout(nfopp_engine *e) {
         if (T - 1 > nmax) nmax = T - 1;
         add_buffer(e, "onf_gpart", &d.onf_gpart, 'f', P, 1, NP);
         add_buffer(e, "onf_wp", &d.onf_wp, 'b', P, onf_wide_packed_bytes(e->onf));
-        add_buffer(e, "onf_ws", &d.onf_ws, 'b', onf_wide_workspace_bytes(e->onf, (int)P, (int)nmax, true));
+        // [MiB, 2^20] so that the int32 dims survive workspaces beyond 2 GiB
+        const size_t ws_bytes = onf_wide_workspace_bytes(e->onf, (int)P, (int)nmax, true);
+        add_buffer(e, "onf_ws", &d.onf_ws, 'b', (ws_bytes + (1u << 20) - 1) >> 20, (size_t)1 << 20);
     } else {
         add_buffer(e, "onf_gpart", &d.onf_gpart, 'f', P, e->tiles, NP);
     }
@@ -470,9 +472,12 @@ extern "C" int nfopp_engine_create(const nfopp_planner_config *cfg, void *worksp
     e->sp_dirty = true;
     e->pack_dirty = true;
     e->launches_per_step = e->impl == 2 ? 8 : 9;
-    if (e->impl == 3)       // 5 planner kernels + candidates forward + train (backward, Adam, re-pack) + path forward/input-gradient
-        e->launches_per_step = 5 + onf_wide_launch_count(e->onf, false, false) + onf_wide_launch_count(e->onf, true, true) + 2 +
-                               onf_wide_launch_count(e->onf, true, false);
+    if (e->impl == 3) {     // 5 planner kernels + candidates forward + train (backward, Adam + re-pack) + path forward/input-gradient
+        const EngineDev &d = e->dev;
+        e->launches_per_step = 5 + onf_wide_launch_count(e->onf, d.P, d.NC, false, false) +
+                               onf_wide_launch_count(e->onf, d.P, d.NTR, true, true) + 1 +
+                               onf_wide_launch_count(e->onf, d.P, d.T - 1, true, false);
+    }
     *out = e;
     return NFOPP_OK;
 }
@@ -591,6 +596,13 @@ static int enqueue_train(nfopp_engine *e, bool warm, cudaStream_t s, cudaEvent_t
     }
     if (rc) return rc;
     if (ev) NFOPP_CHECK_CUDA(cudaEventRecord(ev[0], s));
+    if (e->impl == 3) {
+        // Adam + operand-copy refresh in one pass over w/m/v/grad
+        if ((rc = onf_wide_adam_pack(e->onf, d.onf_w, d.onf_m, d.onf_v, d.onf_gpart, d.onf_wp, d.sp, warm, w1, beta2, w2, eps, d.P, s)))
+            return rc;
+        if (ev) NFOPP_CHECK_CUDA(cudaEventRecord(ev[1], s));
+        return NFOPP_OK;
+    }
     AdamArgs ad{};
     ad.w = d.onf_w; ad.m = d.onf_m; ad.v = d.onf_v; ad.gpart = d.onf_gpart; ad.count = d.train_n; ad.n = d.NTR;
     ad.tp = e->tile_points; ad.tiles = e->tiles; ad.n_params = e->onf.lay.n_params;
@@ -599,7 +611,6 @@ static int enqueue_train(nfopp_engine *e, bool warm, cudaStream_t s, cudaEvent_t
     ad.warm = warm;
     rc = onf_adam_launch(ad, d.P, s);
     if (rc) return rc;
-    if (e->impl == 3 && (rc = onf_wide_pack(e->onf, d.onf_w, d.onf_wp, d.P, s))) return rc;    // refresh the operand copies
     if (ev) NFOPP_CHECK_CUDA(cudaEventRecord(ev[1], s));
     return NFOPP_OK;
 }
@@ -667,7 +678,7 @@ extern "C" int nfopp_engine_warmup(nfopp_engine *e, int iterations, void *stream
         if ((rc = launch_tick(e->dev, true, s))) return rc;
         e->host_sp.onf_step += 1;
         e->warm_iterations_done += 1;
-        e->launches += e->impl == 2 ? 4 : e->impl == 3 ? 5 + onf_wide_launch_count(e->onf, true, true) : 5;
+        e->launches += e->impl == 2 ? 4 : e->impl == 3 ? 4 + onf_wide_launch_count(e->onf, e->dev.P, e->dev.NTR, true, true) : 5;
     }
     host_step_params(e);
     return NFOPP_OK;

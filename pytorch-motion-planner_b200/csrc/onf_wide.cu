@@ -118,6 +118,12 @@ struct WidePackArgs {
     WideDims w;
     const float *weights;
     unsigned char *packed;
+    // fused Adam (engine): adam_m != null -> weights/m/v are updated from `grad` first (adam_w aliases weights)
+    float *adam_w, *adam_m, *adam_v;
+    const float *grad;
+    const StepParams *sp;
+    int warm;
+    float w1, beta2, w2, eps;
 };
 
 __global__ void __launch_bounds__(256) wide_pack_kernel(const WidePackArgs a) {
@@ -126,32 +132,103 @@ __global__ void __launch_bounds__(256) wide_pack_kernel(const WidePackArgs a) {
     const float *W = a.weights + (size_t)p * a.d.lay.n_params;
     unsigned char *out = a.packed + (size_t)p * ((w.packed_bytes + 255) / 256 * 256);
     const int gid = blockIdx.x * blockDim.x + threadIdx.x, gstride = gridDim.x * blockDim.x;
-    for (int l = 0; l < w.L; ++l) {
-        const int K = w.kin[l], kr = w.kin_real[l], items = w.Hp * (K / 8);
-        for (int item = gid; item < items; item += gstride) {
-            const int o = item / (K / 8), io = item - o * (K / 8);
-            float v[8];
+    float step_size = 0.f, bc2_sqrt = 1.f;
+    if (a.adam_m) {
+        if (!a.warm && !a.sp->do_train) return;
+        step_size = a.sp->onf_step_size;
+        bc2_sqrt = a.sp->onf_bc2_sqrt;
+        // everything that is not a hidden-layer matrix (encoder, biases, output layer): plain Adam
+        const nfopp_onf_layout &L = a.d.lay;
+        const size_t po = (size_t)p * L.n_params;
+        for (int i4 = gid; i4 < L.n_params / 4; i4 += gstride) {
+            const int e = 4 * i4;
+            bool matrix = false;
+            for (int l = 0; l < w.L; ++l) matrix |= e >= L.off_w[l] && e < L.off_b[l];
+            if (matrix) continue;
+            const float4 g = *reinterpret_cast<const float4 *>(a.grad + po + e);
+            float4 x = *reinterpret_cast<float4 *>(a.adam_w + po + e), m = *reinterpret_cast<float4 *>(a.adam_m + po + e),
+                   vv = *reinterpret_cast<float4 *>(a.adam_v + po + e);
+            float xs[4] = {x.x, x.y, x.z, x.w}, gs[4] = {g.x, g.y, g.z, g.w}, ms[4] = {m.x, m.y, m.z, m.w}, vs[4] = {vv.x, vv.y, vv.z, vv.w};
 #pragma unroll
-            for (int e = 0; e < 8; ++e) {
-                const int i = io * 8 + e;
-                v[e] = (o < w.H && i < kr) ? W[a.d.lay.off_w[l] + (size_t)o * kr + i] : 0.f;
+            for (int c = 0; c < 4; ++c) {
+                ms[c] = fmaf(a.w1, gs[c] - ms[c], ms[c]);
+                vs[c] = fmaf(a.w2 * gs[c], gs[c], vs[c] * a.beta2);
+                const float denom = sqrtf(vs[c]) / bc2_sqrt + a.eps;
+                xs[c] = fmaf(-step_size, ms[c] / denom, xs[c]);
             }
-            uint4 hi, lo;
-            split8(v, hi, lo);
-            {   // Wf: n-tile over out
-                const int nt = o / WG_NT, ow = min(WG_NT, w.Hp - nt * WG_NT), oo = o - nt * WG_NT;
-                unsigned char *b = out + w.wf_off[l] + (size_t)nt * WG_NT * K * 4;
-                const size_t off = (size_t)io * ow * 16 + (size_t)oo * 16;
-                *reinterpret_cast<uint4 *>(b + off) = hi;
-                *reinterpret_cast<uint4 *>(b + (size_t)K * ow * 2 + off) = lo;
+            *reinterpret_cast<float4 *>(a.adam_w + po + e) = make_float4(xs[0], xs[1], xs[2], xs[3]);
+            *reinterpret_cast<float4 *>(a.adam_m + po + e) = make_float4(ms[0], ms[1], ms[2], ms[3]);
+            *reinterpret_cast<float4 *>(a.adam_v + po + e) = make_float4(vs[0], vs[1], vs[2], vs[3]);
+        }
+    }
+    // hidden-layer matrices in tiles of 32 out-rows x 8 in-octets: phase 1 walks a row (in-octet fastest: coalesced fp32
+    // traffic for Adam), phase 2 walks a column (out-row fastest: the operand copies are contiguous along the out index)
+    __shared__ uint4 t_hi[8][33], t_lo[8][33];
+    const int tid = threadIdx.x;
+    for (int l = 0; l < w.L; ++l) {
+        const int K = w.kin[l], kr = w.kin_real[l], KO = K / 8;
+        const int ot_n = (w.Hp + 31) / 32, it_n = (KO + 7) / 8;
+        for (int tile = blockIdx.x; tile < ot_n * it_n; tile += gridDim.x) {
+            const int o0 = (tile / it_n) * 32, io0 = (tile % it_n) * 8;
+            {
+                const int io = io0 + (tid & 7), o = o0 + (tid >> 3);
+                float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+                if (o < w.H && io < KO) {
+#pragma unroll
+                    for (int h4 = 0; h4 < 2; ++h4) {
+                        const int i = io * 8 + 4 * h4;
+                        if (i >= kr) continue;
+                        const size_t e = (size_t)a.d.lay.off_w[l] + (size_t)o * kr + i;
+                        float4 x = *reinterpret_cast<const float4 *>(W + e);
+                        if (a.adam_m) {
+                            // torch.optim.Adam on these four weights, then the operand copies from the NEW values
+                            const size_t ge = (size_t)p * a.d.lay.n_params + e;
+                            const float4 g = *reinterpret_cast<const float4 *>(a.grad + ge);
+                            float4 m = *reinterpret_cast<float4 *>(a.adam_m + ge), vv = *reinterpret_cast<float4 *>(a.adam_v + ge);
+                            float xs[4] = {x.x, x.y, x.z, x.w}, gs[4] = {g.x, g.y, g.z, g.w}, ms[4] = {m.x, m.y, m.z, m.w},
+                                  vs[4] = {vv.x, vv.y, vv.z, vv.w};
+#pragma unroll
+                            for (int c = 0; c < 4; ++c) {
+                                ms[c] = fmaf(a.w1, gs[c] - ms[c], ms[c]);
+                                vs[c] = fmaf(a.w2 * gs[c], gs[c], vs[c] * a.beta2);
+                                const float denom = sqrtf(vs[c]) / bc2_sqrt + a.eps;
+                                xs[c] = fmaf(-step_size, ms[c] / denom, xs[c]);
+                            }
+                            x = make_float4(xs[0], xs[1], xs[2], xs[3]);
+                            *reinterpret_cast<float4 *>(a.adam_w + ge) = x;
+                            *reinterpret_cast<float4 *>(a.adam_m + ge) = make_float4(ms[0], ms[1], ms[2], ms[3]);
+                            *reinterpret_cast<float4 *>(a.adam_v + ge) = make_float4(vs[0], vs[1], vs[2], vs[3]);
+                        }
+                        v[4 * h4] = x.x; v[4 * h4 + 1] = x.y; v[4 * h4 + 2] = x.z; v[4 * h4 + 3] = x.w;
+                    }
+                }
+                uint4 hi, lo;
+                split8(v, hi, lo);
+                t_hi[tid & 7][tid >> 3] = hi;
+                t_lo[tid & 7][tid >> 3] = lo;
             }
-            {   // Wd: n-tile over in
-                const int i0 = io * 8, nt = i0 / WG_NT, iw = min(WG_NT, K - nt * WG_NT), ii = i0 - nt * WG_NT;
-                unsigned char *b = out + w.wd_off[l] + (size_t)nt * WG_NT * w.Hp * 4;
-                const size_t off = (size_t)(o / 8) * iw * 16 + (size_t)(ii / 8) * 128 + (o % 8) * 16;
-                *reinterpret_cast<uint4 *>(b + off) = hi;
-                *reinterpret_cast<uint4 *>(b + (size_t)w.Hp * iw * 2 + off) = lo;
+            __syncthreads();
+            {
+                const int io = io0 + (tid >> 5), o = o0 + (tid & 31);
+                if (o < w.Hp && io < KO) {
+                    const uint4 hi = t_hi[tid >> 5][tid & 31], lo = t_lo[tid >> 5][tid & 31];
+                    {   // Wf: n-tile over out
+                        const int nt = o / WG_NT, ow = min(WG_NT, w.Hp - nt * WG_NT), oo = o - nt * WG_NT;
+                        unsigned char *b = out + w.wf_off[l] + (size_t)nt * WG_NT * K * 4;
+                        const size_t off = (size_t)io * ow * 16 + (size_t)oo * 16;
+                        *reinterpret_cast<uint4 *>(b + off) = hi;
+                        *reinterpret_cast<uint4 *>(b + (size_t)K * ow * 2 + off) = lo;
+                    }
+                    {   // Wd: n-tile over in
+                        const int i0 = io * 8, nt = i0 / WG_NT, iw = min(WG_NT, K - nt * WG_NT), ii = i0 - nt * WG_NT;
+                        unsigned char *b = out + w.wd_off[l] + (size_t)nt * WG_NT * w.Hp * 4;
+                        const size_t off = (size_t)(o / 8) * iw * 16 + (size_t)(ii / 8) * 128 + (o % 8) * 16;
+                        *reinterpret_cast<uint4 *>(b + off) = hi;
+                        *reinterpret_cast<uint4 *>(b + (size_t)w.Hp * iw * 2 + off) = lo;
+                    }
+                }
             }
+            __syncthreads();
         }
     }
 }
@@ -1477,9 +1554,9 @@ int onf_wide_pack(const OnfDims &d, const float *weights, unsigned char *packed,
     NFOPP_REQUIRE(make_wide_dims(d, &a.w), "onf(wide): unsupported network shape");
     a.weights = weights; a.packed = packed;
     if (P == 0) return NFOPP_OK;
-    int max_items = 0;
-    for (int l = 0; l < a.w.L; ++l) max_items = max(max_items, a.w.Hp * (a.w.kin[l] / 8));
-    dim3 grid((max_items + 255) / 256, P);
+    int max_tiles = 0;
+    for (int l = 0; l < a.w.L; ++l) max_tiles = max(max_tiles, ((a.w.Hp + 31) / 32) * ((a.w.kin[l] / 8 + 7) / 8));
+    dim3 grid(max_tiles, P);
     wide_pack_kernel<<<grid, 256, 0, stream>>>(a);
     NFOPP_CHECK_CUDA(cudaGetLastError());
     return NFOPP_OK;
@@ -1518,6 +1595,23 @@ static int chain_max_clusters(int CL) {
     return cached[CL];
 }
 
+// engine: Adam on the whole blob fused with the refresh of the operand copies (one pass over w/m/v/grad)
+int onf_wide_adam_pack(const OnfDims &d, float *weights, float *m, float *v, const float *grad, unsigned char *packed,
+                       const StepParams *sp, int warm, float w1, float beta2, float w2, float eps, int P, cudaStream_t stream) {
+    WidePackArgs a{};
+    a.d = d;
+    NFOPP_REQUIRE(make_wide_dims(d, &a.w), "onf(wide): unsupported network shape");
+    NFOPP_REQUIRE(weights && m && v && grad && packed && sp, "onf_wide_adam_pack: bad arguments");
+    a.weights = weights; a.packed = packed; a.adam_w = weights; a.adam_m = m; a.adam_v = v; a.grad = grad; a.sp = sp; a.warm = warm;
+    a.w1 = w1; a.beta2 = beta2; a.w2 = w2; a.eps = eps;
+    int max_tiles = 0;
+    for (int l = 0; l < a.w.L; ++l) max_tiles = max(max_tiles, ((a.w.Hp + 31) / 32) * ((a.w.kin[l] / 8 + 7) / 8));
+    dim3 grid(max_tiles, P);
+    wide_pack_kernel<<<grid, 256, 0, stream>>>(a);
+    NFOPP_CHECK_CUDA(cudaGetLastError());
+    return NFOPP_OK;
+}
+
 static int launch_wgrad(const WideWgradArgs &g, cudaStream_t s) {
     const int MB = (g.CA + 127) / 128, NTT = (g.CB + WG_NT - 1) / WG_NT + (g.bias_off >= 0 ? 1 : 0);
     const int items = g.P * MB * NTT * g.splits;
@@ -1526,9 +1620,16 @@ static int launch_wgrad(const WideWgradArgs &g, cudaStream_t s) {
     return NFOPP_OK;
 }
 
-int onf_wide_launch_count(const OnfDims &d, bool want_bwd, bool want_wgrad) {
+// kernels one onf_wide_launch issues (memsets not counted)
+int onf_wide_launch_count(const OnfDims &d, int P, int n, bool want_bwd, bool want_wgrad) {
+    WideDims w;
+    if (!make_wide_dims(d, &w)) return 0;
+    WideWorkspace ws;
+    wide_workspace(w, d.lay.n_params, P, n, want_bwd, &ws);
+    const int red = ws.splits > 1 ? 1 : 0;
+    if (wide_use_chain(w)) return 1 + (want_bwd && want_wgrad ? 2 + red : 0);
     if (!want_bwd) return 2 + d.L;
-    return 2 + d.L + d.L + 1 + (want_wgrad ? d.L + 8 : 0);     // upper bound (the two split reductions run only when splits > 1)
+    return 2 + d.L + d.L + 1 + (want_wgrad ? d.L + 5 + 2 * red : 0);
 }
 
 // One ONF call (forward, or forward + backward): a fixed sequence of launches on `stream`.
