@@ -59,7 +59,7 @@ struct UniformSource {
 struct ChoiceScratch {
     double *p, *cdf, *u;     // [n], [n], [size]
     int *newv, *found, *mark;  // [size], [size], [n]
-    int *ctl;                // [4]: n_uniq, consumed, exhausted, tmp
+    int *ctl;                // [4 + 32]: n_uniq, consumed, exhausted, tmp | per-warp counts of the compaction
 };
 
 // numpy.random.RandomState.choice(n, size, replace, p) (mtrand.pyx, legacy); block-cooperative.
@@ -77,9 +77,19 @@ __device__ int choice_block(const ChoiceScratch &sc, int n, int size, bool repla
         for (int i = tid; i < k; i += nt) sc.u[i] = src.get(consumed + i, &sc.ctl[2]);
         for (int i = tid; i < n; i += nt) sc.mark[i] = 0x7fffffff;
         __syncthreads();
-        if (tid == 0) {                      // np.cumsum: strictly sequential float64 adds
-            double acc = 0.0;
-            for (int i = 0; i < n; ++i) { acc = __dadd_rn(acc, sc.p[i]); sc.cdf[i] = acc; }
+        if (tid == 0) {                      // np.cumsum: strictly sequential float64 adds (the order is the contract);
+            double acc = 0.0;                // operands are fetched 8 at a time so only the adds sit on the dependent chain
+            int i = 0;
+            for (; i + 8 <= n; i += 8) {
+                double v[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[j] = sc.p[i + j];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) { acc = __dadd_rn(acc, v[j]); v[j] = acc; }
+#pragma unroll
+                for (int j = 0; j < 8; ++j) sc.cdf[i + j] = v[j];
+            }
+            for (; i < n; ++i) { acc = __dadd_rn(acc, sc.p[i]); sc.cdf[i] = acc; }
         }
         __syncthreads();
         const double last = sc.cdf[n - 1];
@@ -92,16 +102,28 @@ __device__ int choice_block(const ChoiceScratch &sc, int n, int size, bool repla
             if (!replace) atomicMin(&sc.mark[v], i);
         }
         __syncthreads();
-        if (tid == 0) {
-            int c = n_uniq;
-            if (replace) {
-                for (int i = 0; i < k; ++i) sc.found[c++] = sc.newv[i];
-            } else {                         // np.unique(return_index) + sort: first occurrences in draw order
-                for (int i = 0; i < k; ++i)
-                    if (sc.mark[sc.newv[i]] == i) sc.found[c++] = sc.newv[i];
+        // np.unique(return_index) + sort: first occurrences in draw order = an order-preserving compaction of the
+        // draws whose mark is their own index (all draws when sampling with replacement): ballot + prefix over warps
+        {
+            int *wcount = &sc.ctl[4];                       // [nt / 32] (carve_choice reserves 4 + 32 ints)
+            const int lane = tid & 31, wid = tid >> 5, nw = (nt + 31) >> 5;
+            int base = n_uniq;
+            for (int i0 = 0; i0 < k; i0 += nt) {            // k <= size; one round when size <= blockDim
+                const int i = i0 + tid;
+                const bool keep = i < k && (replace || sc.mark[sc.newv[i]] == i);
+                const unsigned bal = __ballot_sync(0xffffffffu, keep);
+                if (lane == 0) wcount[wid] = __popc(bal);
+                __syncthreads();
+                int off = base;
+                for (int w = 0; w < wid; ++w) off += wcount[w];
+                if (keep) sc.found[off + __popc(bal & ((1u << lane) - 1u))] = sc.newv[i];
+                for (int w = 0; w < nw; ++w) base += wcount[w];
+                __syncthreads();
             }
-            sc.ctl[0] = c;
-            sc.ctl[1] = consumed + k;
+            if (tid == 0) {
+                sc.ctl[0] = base;
+                sc.ctl[1] = consumed + k;
+            }
         }
         __syncthreads();
     }
@@ -109,7 +131,7 @@ __device__ int choice_block(const ChoiceScratch &sc, int n, int size, bool repla
 }
 
 __host__ __device__ static size_t choice_smem_bytes(int n, int size) {
-    return (size_t)(2 * n + size) * sizeof(double) + (size_t)(2 * size + n + 4) * sizeof(int);
+    return (size_t)(2 * n + size) * sizeof(double) + (size_t)(2 * size + n + 4 + 32) * sizeof(int);
 }
 
 __device__ ChoiceScratch carve_choice(unsigned char *base, int n, int size) {
