@@ -377,6 +377,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
         mbar_expect_tx(s.bars, (uint32_t)t.packed_bytes);
         bulk_g2s(s.w1h, src, 2 * t.w1_half, s.bars);
         bulk_g2s(s.w2h, src + 2 * t.w1_half, 2 * t.w2_half, s.bars);
+        if (a.adam_w != nullptr && want_bwd) {
+            // the Adam epilogue streams this problem's w / m / v once: start pulling them into L2 now, under the compute
+            const size_t po = (size_t)p * L.n_params;
+            const uint32_t bytes = (uint32_t)(L.n_params * sizeof(float)) & ~15u;
+            bulk_prefetch_l2(a.adam_w + po, bytes);
+            bulk_prefetch_l2(a.adam_m + po, bytes);
+            bulk_prefetch_l2(a.adam_v + po, bytes);
+        }
     }
     for (int f = tid; f < K1; f += TC_THREADS) {
         float pa = 0.f, pb = 0.f, pc = 0.f;

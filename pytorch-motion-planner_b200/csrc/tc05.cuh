@@ -59,6 +59,11 @@ __device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, u
                  : "memory");
 }
 
+// asynchronous prefetch of a contiguous global range into L2 (size multiple of 16 bytes)
+__device__ __forceinline__ void bulk_prefetch_l2(const void *src_gmem, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src_gmem), "r"(bytes) : "memory");
+}
+
 // ---- thread-block clusters: multicast bulk copy (one L2 read feeds the shared memory of every CTA in ctaMask, at the
 // same CTA-relative offsets, signalling the mbarrier at the same offset in each of them) ----------------------------
 __device__ __forceinline__ uint32_t cluster_ctarank() {
