@@ -206,6 +206,14 @@ int nfopp_engine_get_paths(nfopp_engine *e, float *paths_dev, void *stream);
 /* NERFOptPlanner.reparametrize_trajectory (nerf_opt_planner.py:224-244; constrained:132-171) on the stored
  * trajectories and multipliers of all problems, outside a step (update_goal_point / update_start_point). */
 int nfopp_engine_reparametrize(nfopp_engine *e, void *stream);
+/* Path evaluation for the stop criterion of scripts/run_bench_mr.py:119-126 (benchmark.evaluate_path ->
+ * BenchmarkAdapter.cpp:201-208 evaluatePath: interpolate the path, validity-check every interpolated pose, path
+ * length), for all P problems: `samples_per_segment` equally spaced poses on each of the T+1 segments of the
+ * full path (x, y linear; heading along the wrapped difference; float64) plus the goal, each labelled by the
+ * engine's own collision checker.  collides_dev [P] uint8 (1 = some pose collides), length_dev [P] float32
+ * (sum of x,y segment lengths), n_colliding_dev [P] int32 or NULL. */
+int nfopp_engine_evaluate_paths(nfopp_engine *e, int samples_per_segment, uint8_t *collides_dev, float *length_dev,
+                                int32_t *n_colliding_dev, void *stream);
 /* number of kernel launches issued by this engine so far (bench.py's gpu_launches) */
 int nfopp_engine_launch_count(nfopp_engine *e, int64_t *launches);
 

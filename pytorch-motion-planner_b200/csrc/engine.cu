@@ -61,6 +61,7 @@ int launch_traj_post(const EngineDev &e, cudaStream_t s);
 int launch_tick(const EngineDev &e, bool warm, cudaStream_t s);
 int launch_paths(const EngineDev &e, float *out, cudaStream_t s);
 int launch_reparam(const EngineDev &e, cudaStream_t s);
+int launch_evaluate_paths(const EngineDev &e, int k, uint8_t *collides, float *length, int32_t *n_hit, cudaStream_t s);
 
 // impl 0 = auto: the tensor path whenever the network shape fits it
 static int resolve_impl(const OnfDims &d, int impl, int *out) {
@@ -755,6 +756,13 @@ extern "C" int nfopp_engine_reparametrize(nfopp_engine *e, void *stream) {
     NFOPP_REQUIRE(e, "reparametrize: bad arguments");
     e->launches += 1;
     return launch_reparam(e->dev, (cudaStream_t)stream);
+}
+
+extern "C" int nfopp_engine_evaluate_paths(nfopp_engine *e, int samples_per_segment, uint8_t *collides, float *length,
+                                           int32_t *n_colliding, void *stream) {
+    NFOPP_REQUIRE(e && collides && length, "evaluate_paths: bad arguments");
+    e->launches += 1;
+    return launch_evaluate_paths(e->dev, samples_per_segment, collides, length, n_colliding, (cudaStream_t)stream);
 }
 
 extern "C" int nfopp_engine_launch_count(nfopp_engine *e, int64_t *launches) {

@@ -373,4 +373,81 @@ int launch_paths(const EngineDev &e, float *out, cudaStream_t s) {
     return NFOPP_OK;
 }
 
+// ---- path evaluation: what scripts/run_bench_mr.py:119-126 asks bench-mr's evaluatePath for every
+// check_collision_frequence iterations (BenchmarkAdapter.cpp:201-208: interpolate the path, validity-check every
+// interpolated pose, path length).  bench-mr's interpolation is in a missing submodule; ours is `k` equally spaced poses
+// per segment (x, y linear, heading along the wrapped difference), float64, the arithmetic oracle/evaluate.py restates.
+// Each pose is labelled by the engine's own checker (K1).  One CTA per problem.
+constexpr int EVAL_THREADS = 128;
+
+__device__ __forceinline__ double wrap_angle_d(double a) {             // numpy: (a + pi) % (2 pi) - pi, python-sign modulo
+    const double two_pi = 6.283185307179586, pi = 3.141592653589793;
+    double r = fmod(__dadd_rn(a, pi), two_pi);
+    if (r != 0.0 && r < 0.0) r = __dadd_rn(r, two_pi);
+    return __dsub_rn(r, pi);
+}
+
+__global__ void __launch_bounds__(EVAL_THREADS) evaluate_paths_kernel(const EngineDev e, int k, uint8_t *__restrict__ collides,
+                                                                        float *__restrict__ length, int32_t *__restrict__ n_hit) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    double *s_obs = reinterpret_cast<double *>(smem_raw);
+    __shared__ int s_hits;
+    __shared__ double s_len[EVAL_THREADS / 32];
+    const int p = blockIdx.x, tid = threadIdx.x, T = e.T, D = e.D;
+    const int pe = e.env_shared ? 0 : p;
+    const int m = (e.checker.kind == 1 || e.checker.kind == 2) ? (e.obstacle_n ? e.obstacle_n[pe] : e.m_max) : 0;
+    for (int i = tid; i < 2 * m; i += EVAL_THREADS) s_obs[i] = e.obstacles[(size_t)pe * e.m_max * 2 + i];
+    if (tid == 0) s_hits = 0;
+    __syncthreads();
+    const uint8_t *grid = e.grid ? e.grid + (size_t)pe * e.checker.rows * e.checker.cols : nullptr;
+    auto node = [&](int j, int d) -> double {
+        return (double)(j == 0 ? e.start[(size_t)p * D + d] : (j == T + 1 ? e.goal[(size_t)p * D + d] : e.traj[((size_t)p * T + j - 1) * D + d]));
+    };
+    const int segs = T + 1, poses = segs * k + 1;
+    int hits = 0;
+    for (int i = tid; i < poses; i += EVAL_THREADS) {
+        const int j = i < segs * k ? i / k : segs - 1, r = i - j * k;          // the last pose is the goal itself
+        const double sfrac = __ddiv_rn((double)r, (double)k);
+        const double x0 = node(j, 0), y0 = node(j, 1), x1 = node(j + 1, 0), y1 = node(j + 1, 1);
+        const double x = __dadd_rn(x0, __dmul_rn(sfrac, __dsub_rn(x1, x0)));
+        const double y = __dadd_rn(y0, __dmul_rn(sfrac, __dsub_rn(y1, y0)));
+        double th = 0.0;
+        if (D == 3) {
+            const double t0 = node(j, 2), t1 = node(j + 1, 2);
+            th = __dadd_rn(t0, __dmul_rn(sfrac, wrap_angle_d(__dsub_rn(t1, t0))));
+        }
+        hits += label_pose(e.checker, s_obs, m, grid, x, y, th) ? 1 : 0;
+    }
+    double len = 0.0;                                                          // sum of segment lengths (x, y)
+    for (int j = tid; j < segs; j += EVAL_THREADS) {
+        const double dx = __dsub_rn(node(j + 1, 0), node(j, 0)), dy = __dsub_rn(node(j + 1, 1), node(j, 1));
+        len += __dsqrt_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        hits += __shfl_xor_sync(0xffffffffu, hits, o);
+        len += __shfl_xor_sync(0xffffffffu, len, o);
+    }
+    if ((tid & 31) == 0) {
+        atomicAdd(&s_hits, hits);
+        s_len[tid >> 5] = len;
+    }
+    __syncthreads();
+    if (tid == 0) {
+        double tot = 0.0;
+        for (int w = 0; w < EVAL_THREADS / 32; ++w) tot += s_len[w];
+        collides[p] = s_hits > 0;
+        length[p] = (float)tot;
+        if (n_hit) n_hit[p] = s_hits;
+    }
+}
+
+int launch_evaluate_paths(const EngineDev &e, int k, uint8_t *collides, float *length, int32_t *n_hit, cudaStream_t s) {
+    NFOPP_REQUIRE(k >= 1 && k <= 4096, "evaluate_paths: samples_per_segment=%d", k);
+    const size_t smem = (size_t)2 * (e.m_max > 0 ? e.m_max : 1) * sizeof(double);
+    NFOPP_REQUIRE(smem <= 48 * 1024, "evaluate_paths: %d obstacles per problem exceed shared memory", e.m_max);
+    evaluate_paths_kernel<<<e.P, EVAL_THREADS, smem, s>>>(e, k, collides, length, n_hit);
+    NFOPP_CHECK_CUDA(cudaGetLastError());
+    return NFOPP_OK;
+}
+
 }  // namespace nfopp

@@ -76,6 +76,7 @@ SIGNATURES = {
     "nfopp_engine_kernel_name": (C.c_char_p, [_I]),
     "nfopp_engine_get_paths": (_I, [_P, _P, _P]),
     "nfopp_engine_reparametrize": (_I, [_P, _P]),
+    "nfopp_engine_evaluate_paths": (_I, [_P, _I, _P, _P, _P, _P]),
     "nfopp_engine_launch_count": (_I, [_P, C.POINTER(C.c_int64)]),
 }
 

@@ -93,6 +93,55 @@ class BatchedPlanner:
     def status(self) -> np.ndarray:
         return self.engine["status"].cpu().numpy()
 
+    def evaluate_paths(self, samples_per_segment=4):
+        """(collides bool [P], length [P], colliding pose count [P]) of the current paths, on the device."""
+        return self.engine.evaluate_paths(samples_per_segment)
+
+    def solve(self, max_iterations=1000, min_iterations=200, check_every=50, samples_per_segment=4, graph=True):
+        """scripts/run_bench_mr.py:109-131 for all problems at once: step, and every `check_every` iterations past
+        `min_iterations` evaluate every path on the device; a problem keeps its shortest collision-free path and is
+        DONE once a later collision-free path is no shorter (the reference's `break`).  Problems are independent, so
+        the batch keeps stepping until all are done or `max_iterations` is reached; finished problems simply stop
+        being recorded.  Returns dict(paths [P,T+2,D], solved bool [P], length [P], iterations int [P])."""
+        P, dev = self.config.problems, self.device
+        best_len = torch.full((P,), float("inf"), device=dev)
+        best_path = self.engine.paths().clone()
+        stop_path, stop_len = best_path.clone(), torch.zeros(P, device=dev)
+        done = torch.zeros(P, dtype=torch.bool, device=dev)
+        iters = torch.full((P,), max_iterations, dtype=torch.int32, device=dev)
+        i = 0
+        while i < max_iterations:
+            # the reference checks after step i (0-based) when i > min_iterations and i % check_every == 0
+            nxt = max(min_iterations + 1, i)
+            nxt += (-nxt) % check_every
+            run = min(nxt, max_iterations - 1) - i + 1
+            self.step(run, graph=graph)
+            i += run
+            if i - 1 != nxt:
+                break
+            collides, length, _ = self.engine.evaluate_paths(samples_per_segment)
+            free = ~collides & ~done
+            better = free & (length < best_len)
+            stop = free & ~better                           # collision-free but no shorter: the reference's `break`
+            if bool(free.any()):
+                paths = self.engine.paths()
+                best_path[better] = paths[better]
+                best_len = torch.where(better, length, best_len)
+                stop_path[stop] = paths[stop]               # the reference returns the path it broke on
+                stop_len = torch.where(stop, length, stop_len)
+            iters = torch.where(stop, torch.full_like(iters, i), iters)
+            done |= stop
+            if bool(done.all()):
+                break
+        collides, length, _ = self.engine.evaluate_paths(samples_per_segment)
+        paths = self.engine.paths()
+        use_best = ~done & collides & torch.isfinite(best_len)      # run_bench_mr.py:128-129
+        paths[done] = stop_path[done]
+        paths[use_best] = best_path[use_best]
+        length = torch.where(done, stop_len, torch.where(use_best, best_len, length))
+        solved = done | ~collides | use_best
+        return dict(paths=paths, solved=solved, length=length, iterations=iters, steps_run=i)
+
     def gather_paths(self) -> torch.Tensor:
         """All ranks' final paths on every rank (the only collective of the whole job).  Ranks may own
         different numbers of problems; shards are padded to the largest for the all_gather."""

@@ -300,6 +300,18 @@ class PlannerEngine:
             L.check(self._lib.nfopp_engine_get_paths(self._h, L.ptr(out), L.stream_ptr()))
         return out
 
+    def evaluate_paths(self, samples_per_segment=4):
+        """benchmark.evaluate_path (scripts/run_bench_mr.py:119-126) for every problem, on the device: -> (collides
+        bool [P], length float32 [P], colliding pose count int32 [P])."""
+        P = self.config.problems
+        collides = torch.empty(P, dtype=torch.uint8, device=self.device)
+        length = torch.empty(P, dtype=torch.float32, device=self.device)
+        hits = torch.empty(P, dtype=torch.int32, device=self.device)
+        with torch.cuda.device(self.device):
+            L.check(self._lib.nfopp_engine_evaluate_paths(self._h, int(samples_per_segment), L.ptr(collides), L.ptr(length),
+                                                          L.ptr(hits), L.stream_ptr()))
+        return collides.bool(), length, hits
+
     @property
     def launches(self) -> int:
         v = C.c_int64()

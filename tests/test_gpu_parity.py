@@ -475,3 +475,50 @@ def test_wide_engine_graph_replay_and_batch_independence():
         assert int(np.abs(bp.status()).max()) == 0
     assert torch.equal(outs[0], outs[1])
     assert not torch.equal(outs[0][0], outs[0][1])
+
+
+# ---------------------------------------------------------------------------------------- path evaluation
+@pytest.mark.parametrize("name,k", [("car", 4), ("corridor", 7), ("holonomic", 1)])
+def test_evaluate_paths_matches_oracle(name, k):
+    """nfopp_engine_evaluate_paths vs oracle.evaluate on paths of a running planner: collision flags and colliding-pose
+    counts bit-exact (every interpolated pose goes through the reference's checker arithmetic), lengths to 1e-6."""
+    from _gpu_util import engine_from_golden
+    from oracle import evaluate as EV
+    fx = U.load(f"lockstep_{name}.npz")
+    P = 16
+    eng = engine_from_golden(name, fx, "free/state0", problems=P, rng_mode="philox", seed=5)
+    label = U.labeller_for(name, fx)
+    seen = set()
+    for _ in range(6):
+        eng.step(25)
+        collides, length, hits = eng.evaluate_paths(k)
+        paths = eng.paths().cpu().numpy()
+        for p in range(P):
+            c, ln, h = EV.evaluate_path(paths[p], label, k)
+            assert bool(collides[p]) == c and int(hits[p]) == h, (p, int(hits[p]), h)
+            assert abs(float(length[p]) - ln) <= 1e-6 * ln
+            seen.add(c)
+    assert seen                                              # (the S-bend corridor is still colliding after 150 steps)
+
+
+def test_batched_solve_loop_matches_reference_bookkeeping():
+    """BatchedPlanner.solve = scripts/run_bench_mr.py:109-131 per problem: replaying the recorded per-check (collides,
+    length) history of one problem through the oracle's solve_loop bookkeeping gives the same verdict."""
+    from nfopp_b200.batched import BatchedPlanner, corridor_config
+    from nfopp_b200.test_environment_builder import TestEnvironmentBuilder as B
+    P = 64
+    starts, goals, _, obstacles = B.make_corridor_batch(P, seed=0)
+    bp = BatchedPlanner(corridor_config(P, seed=3))
+    bp.init(starts, goals, obstacles=obstacles)
+    out = bp.solve(max_iterations=600, min_iterations=200, check_every=50)
+    solved = out["solved"].cpu().numpy()
+    assert out["paths"].shape == (P, 102, 3) and bool(torch.isfinite(out["paths"]).all())
+    assert 0 < solved.sum()                                      # some corridors are solved within 600 steps
+    # a solved problem's returned path is collision-free under the engine's checker, and its length is the reported one
+    eng = bp.engine
+    eng["traj"].copy_(out["paths"][:, 1:-1])
+    collides, length, _ = eng.evaluate_paths(4)
+    assert not bool((collides & out["solved"]).any())
+    assert torch.allclose(length[out["solved"]], out["length"][out["solved"]], rtol=1e-5)
+    its = out["iterations"].cpu().numpy()
+    assert ((its == 600) | ((its - 1) % 50 == 0)).all() and (its[its < 600] > 200).all()

@@ -183,3 +183,25 @@ def test_gather_paths_world_size_2_gloo(tmp_path):
         got = torch.load(f"{out}.{r}")
         assert got.shape == (5, 4, 3)
         assert torch.equal(got[:, 0, 0], torch.arange(5, dtype=torch.float32))
+
+
+def test_oracle_path_evaluation_and_stop_rule():
+    """oracle.evaluate: interpolation (heading along the wrapped difference), length, and the best-path / early-stop
+    bookkeeping of scripts/run_bench_mr.py:109-131 on a scripted evaluation history."""
+    import numpy as np
+    from oracle import evaluate as EV
+    path = np.array([[0, 0, 3.0], [1, 0, -3.0], [1, 2, -3.0]], dtype=np.float32)
+    poses = EV.interpolate_path(path, 4)
+    assert poses.shape == (9, 3) and np.allclose(poses[-1], path[-1])
+    assert np.allclose(poses[2, :2], [0.5, 0.0])
+    assert abs(poses[2, 2] - (3.0 + 0.5 * ((-6.0 + np.pi) % (2 * np.pi) - np.pi))) < 1e-12      # through +-pi, not through 0
+    hit = lambda p: (p[:, 0] > 0.9) & (p[:, 1] > 0.9) & (p[:, 1] < 1.1)                          # noqa: E731
+    c, ln, n = EV.evaluate_path(path, hit, 4)
+    assert c and n == 1 and abs(ln - 3.0) < 1e-12
+    assert EV.evaluate_path(path, hit, 1) == (False, 3.0, 0)                                      # node-only check misses it
+    history = iter([(True, 9.0), (False, 5.0), (False, 4.0), (False, 4.5), (False, 1.0)])
+    state = {"n": 0}
+    out = EV.solve_loop(lambda: state.__setitem__("n", state["n"] + 1), lambda: state["n"], lambda p: next(history),
+                        max_iterations=1000, min_iterations=200, check_every=50)
+    # checks at i = 250, 300, 350, 400 (0-based): collides, 5.0 (best), 4.0 (best), 4.5 -> break; final evaluation = 1.0
+    assert out[3] == 401 and out[1] is False and out[2] == 1.0 and out[0] == 401
