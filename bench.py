@@ -294,6 +294,23 @@ def run_ours(args):
     barrier()
     finite = bool(torch.isfinite(eng.paths()).all())
     all_paths = planner.gather_paths()                           # the one collective of the job (NCCL)
+
+    # ---- problems SOLVED per second at the reference's stop rule (scripts/run_bench_mr.py:64-66,109-131): fresh planners,
+    # <= 1000 iterations, >= 200, path evaluated on the device every 50 iterations, stop at a collision-free path that no
+    # longer shortens ----
+    solve = None
+    if not args.no_solve:
+        solver = BatchedPlanner(cfg, device=f"cuda:{local}")
+        solver.init(starts, goals, **init_kw)
+        res = {}
+        ms_solve = timed(lambda k: res.update(solver.solve(max_iterations=1000, min_iterations=200, check_every=50)), 0)
+        counts = torch.tensor([float(res["solved"].sum()), float(res["steps_run"])], device="cuda")
+        if world > 1:
+            dist.all_reduce(counts, op=dist.ReduceOp.SUM)
+        solve = {"problems": P * world, "solved": int(counts[0]), "seconds": ms_solve * 1e-3,
+                 "solved_per_s": float(counts[0]) / (ms_solve * 1e-3), "steps_run_per_gpu": float(counts[1]) / world,
+                 "rule": "run_bench_mr.py: max 1000 / min 200 iterations, evaluate every 50 (4 poses per segment through the "
+                         "collision checker), stop at a collision-free path that is no shorter than the best"}
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -345,6 +362,8 @@ def run_ours(args):
         "kernel_ms": prof,
         "paths_finite": finite, "paths_gathered": list(all_paths.shape),
     }
+    if solve:
+        line["solve"] = solve
     if world == 1 and not args.no_onf_microbench:
         mb = onf_microbench()
         mb["frac_of_bf16_peak"] = mb["tflops_algorithmic"] / peaks.get("bf16_tflops", 1590.0)
@@ -403,6 +422,7 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-onf-microbench", action="store_true")
+    ap.add_argument("--no-solve", action="store_true", help="skip the problems-solved-per-second run")
     ap.add_argument("--workload", default="corridor", choices=list(WORKLOADS),
                     help="corridor = BASELINE configs[1] (the headline), forest = configs[2], gridmap-wide = configs[3]")
     ap.add_argument("--onf-impl", default="auto", choices=["auto", "fma", "tensor", "wide"],
