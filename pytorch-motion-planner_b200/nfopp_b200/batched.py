@@ -93,6 +93,31 @@ class BatchedPlanner:
     def status(self) -> np.ndarray:
         return self.engine["status"].cpu().numpy()
 
+    # ---- warm re-planning for all problems (receding-horizon use, ros/goal_planner_adapter.py:44-53) ----------------
+    def _snap(self, points, to_goal: bool):
+        """update_goal_point / update_start_point (nerf_opt_planner.py:202-218; constrained:178-194) vectorised over
+        problems: the tail (head) of every trajectory from its node nearest to the new goal (start) is snapped onto
+        it, then every trajectory is re-parametrised and the step counter reset."""
+        eng, cfg = self.engine, self.config
+        pts = torch.as_tensor(np.asarray(points, dtype=np.float32)).to(self.device).reshape(cfg.problems, cfg.dim)
+        (eng["goal"] if to_goal else eng["start"]).copy_(pts)
+        traj = eng["traj"]                                                  # [P, T, D]
+        cols = 2 if cfg.constrained else cfg.dim                            # constrained: x, y only (:181,:190)
+        k = torch.argmin(((traj[..., :cols] - pts[:, None, :cols]) ** 2).sum(-1), dim=1)
+        if cfg.constrained:
+            k = torch.clamp(k + 1, max=traj.shape[1])
+        idx = torch.arange(traj.shape[1], device=self.device)[None, :]
+        mask = (idx >= k[:, None]) if to_goal else (idx < k[:, None])
+        traj.copy_(torch.where(mask[..., None], pts[:, None, :], traj))
+        eng.reparametrize()
+        eng.set_counter("step_count", 0)
+
+    def update_goal_points(self, goal_points):
+        self._snap(goal_points, True)
+
+    def update_start_points(self, start_points):
+        self._snap(start_points, False)
+
     def evaluate_paths(self, samples_per_segment=4):
         """(collides bool [P], length [P], colliding pose count [P]) of the current paths, on the device."""
         return self.engine.evaluate_paths(samples_per_segment)

@@ -300,6 +300,12 @@ class PlannerEngine:
             L.check(self._lib.nfopp_engine_get_paths(self._h, L.ptr(out), L.stream_ptr()))
         return out
 
+    def reparametrize(self):
+        """NERFOptPlanner.reparametrize_trajectory (nerf_opt_planner.py:224-244; constrained:132-171) for all problems,
+        outside a step."""
+        with torch.cuda.device(self.device):
+            L.check(self._lib.nfopp_engine_reparametrize(self._h, L.stream_ptr()))
+
     def evaluate_paths(self, samples_per_segment=4):
         """benchmark.evaluate_path (scripts/run_bench_mr.py:119-126) for every problem, on the device: -> (collides
         bool [P], length float32 [P], colliding pose count int32 [P])."""

@@ -143,3 +143,49 @@ def test_batched_jittered_corridors_run_through_cuda_graph():
     assert np.allclose(paths[:, 0], starts) and np.allclose(paths[:, -1], goals)
     assert (planner.status() == 0).all()
     assert planner.engine.counter("step_count") == 100
+
+
+def test_batched_warm_replanning_matches_single_problem_api():
+    """BatchedPlanner.update_goal_points / update_start_points (receding-horizon re-planning for all problems) give,
+    problem by problem, what the reference-facing P=1 planner's update_goal_point / update_start_point give."""
+    from nfopp_b200.batched import BatchedPlanner, corridor_config
+    from nfopp_b200.test_environment_builder import TestEnvironmentBuilder as B
+    P = 4
+    starts, goals, _, obstacles = B.make_corridor_batch(P, seed=2)
+    bp = BatchedPlanner(corridor_config(P, seed=5))
+    bp.init(starts, goals, obstacles=obstacles)
+    bp.step(30)
+    before = bp.engine["traj"].clone()
+    lam0, mu0 = bp.engine["lam"].clone().cpu(), bp.engine["mu"].clone().cpu()
+    new_goals = goals.copy(); new_goals[:, 0] -= 0.3; new_goals[:, 1] += 0.2
+    new_starts = starts.copy(); new_starts[:, 0] += 0.25
+    bp.update_goal_points(new_goals)
+    bp.update_start_points(new_starts)
+    after = bp.engine["traj"].clone()
+    assert bp.engine.counter("step_count") == 0 and bool(torch.isfinite(after).all())
+    # same operations through single-problem engines
+    for p in range(P):
+        one = BatchedPlanner(corridor_config(1, seed=5))
+        one.init(starts[p:p + 1], goals[p:p + 1], obstacles=obstacles[p:p + 1])
+        one.engine["traj"].copy_(before[p:p + 1])
+        one.update_goal_points(new_goals[p:p + 1])
+        one.update_start_points(new_starts[p:p + 1])
+        assert torch.equal(one.engine["traj"][0], after[p]), p
+    # and the oracle's restatement of constrained_nerf_opt_planner.py:178-194 + :132-171
+    from oracle import trajectory as TR
+    for p in range(P):
+        traj, lam, mu = before[p].cpu().clone(), lam0[p].clone(), mu0[p].clone()
+        st, go = torch.tensor(starts[p]), torch.tensor(new_goals[p])
+        k = min(int(torch.argmin(((traj[:, :2] - go[None, :2]) ** 2).sum(1))) + 1, traj.shape[0])
+        traj[k:] = go
+        traj, lam, mu = TR.reparam_constrained(traj, st, go, lam, mu)
+        st = torch.tensor(new_starts[p])
+        k = min(int(torch.argmin(((traj[:, :2] - st[None, :2]) ** 2).sum(1))) + 1, traj.shape[0])
+        traj[:k] = st
+        traj, lam, mu = TR.reparam_constrained(traj, st, go, lam, mu)
+        assert float((traj - after[p].cpu()).abs().max()) < 1e-5, p
+        assert float((lam - bp.engine["lam"][p].cpu()).abs().max()) < 1e-5
+    paths = bp.get_path()
+    assert np.allclose(paths[:, 0], new_starts) and np.allclose(paths[:, -1], new_goals)
+    bp.step(5)
+    assert np.isfinite(bp.get_path()).all()
