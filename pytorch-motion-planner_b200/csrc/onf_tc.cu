@@ -33,6 +33,18 @@
 namespace nfopp {
 using namespace tc05;
 
+// optional phase trace (build with -DNFOPP_TC_TRACE; scripts/tc_trace.py): clock64 stamps of the group leaders of two CTAs
+#ifdef NFOPP_TC_TRACE
+__device__ long long g_tc_trace[3][2][2][96];   // [launch kind: fwd | train | path][first / last CTA][group][slot]
+#define TC_TRACE(slot)                                                                                      \
+    do {                                                                                                    \
+        if ((tid & (TC_GT - 1)) == 0 && tid < TC_WORKERS && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1) && (slot) < 96) \
+            g_tc_trace[!a.want_bwd ? 0 : ((a.grad_out || a.adam_w) ? 1 : 2)][blockIdx.x == 0 ? 0 : 1][tid / TC_GT][(slot)] = clock64();                           \
+    } while (0)
+#else
+#define TC_TRACE(slot) do { } while (0)
+#endif
+
 constexpr int TC_WORKERS = 512;                  // 2 groups x 8 epilogue warps
 constexpr int TC_THREADS = TC_WORKERS + 32;      // + 1 MMA-issue warp
 constexpr int TC_GT = 256;                       // threads per group
@@ -356,6 +368,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
     const bool want_gx = want_bwd && a.gx_out != nullptr;
     const int F = t.F, FIN = t.FIN, H = t.H, K1 = t.K1, KH = t.KH;
     const bool is_issuer = warp == TC_WORKERS / 32;
+    TC_TRACE(0);
 
     TcShared s(smem_raw, t);
     const float *W = a.weights + (size_t)p * L.n_params;
@@ -411,6 +424,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
     __syncthreads();
     fence_after_sync();
     const uint32_t tmem = *s.tmem_slot;
+    TC_TRACE(1);
 
     // worker identity (the issuer warp computes harmless values)
     const int g = (warp >> 3) & 1, gt = tid & (TC_GT - 1), lw = warp & 7;
@@ -436,6 +450,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
             const int nv = min(TC_TP, cnt - n0);
             const int Nt = ru16(nv);
             const bool cols_on = c0 < Nt;
+            const int tsl = 2 + 16 * (tile >> 1);
+            TC_TRACE(tsl);
             // ---- P0: inputs (onf_model.py:37-38) ----
             if (gt < TC_TP) {
                 float x0 = 0.f, x1 = 0.f, x2 = 0.f;
@@ -449,6 +465,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
                 G.th[gt] = x2;
             }
             group_sync(g);
+            TC_TRACE(tsl + 1);
             // ---- P1: encoding (CUDA cores) feeding fwd1 in groups of 128 features ----
             {
                 const int n = gt & 31, oc = gt >> 5;         // point, feature octet (0..7) within a 64-feature half group
@@ -491,10 +508,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
                         }
                     }
                     signal_ready(G.ready);                // -> fwd1(fg)
+                    TC_TRACE(tsl + 2 + fg);
                 }
             }
             // ---- P2: epilogue 1: bias + ReLU -> H1 operand; row H = skip term of the logit ----
             wait_done(G.done, ph_done);
+            TC_TRACE(tsl + 4);
             if (cols_on) {
                 float v[16];
                 tmem_ld16(tw + c0, v);
@@ -512,8 +531,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
                 if (row < KH) store_row16(G.h1h, G.h1l, row, c0, v, S_PT);
             }
             signal_ready(G.ready);                        // -> fwd2
+            TC_TRACE(tsl + 5);
             // ---- P4: epilogue 2: logit, dL/dz, gH2 operand ----
             wait_done(G.done, ph_done);
+            TC_TRACE(tsl + 6);
             float r2[16];
             if (cols_on) {
                 tmem_ld16(tw + 32 + c0, r2);
@@ -531,6 +552,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
                 if ((lane & 1) == 0) G.zp[q * TC_TP + c0 + (lane >> 1)] = zs;
             }
             group_sync(g);
+            TC_TRACE(tsl + 7);
             if (gt < TC_TP) {
                 const int n = gt;
                 const float z = G.zp[n] + G.zp[TC_TP + n] + G.zp[2 * TC_TP + n] + G.zp[3 * TC_TP + n] + G.skip[n] + s.b3[0];
@@ -555,6 +577,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
                 acc_db3 += gb;
             }
             group_sync(g);
+            TC_TRACE(tsl + 8);
             if (!want_bwd) continue;
             if (cols_on) {
                 float v[16];
@@ -569,8 +592,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
                 if (row < KH) store_row16(G.rh, G.rl, row, c0, v, S_PT);
             }
             signal_ready(G.ready);                        // -> wgrad2 + dgrad2
+            TC_TRACE(tsl + 9);
             // ---- P6: epilogue 3: ReLU mask of layer 1 -> gH1 operand (in place over H1); row H := dL/dz ----
             wait_done(G.done, ph_done);
+            TC_TRACE(tsl + 10);
             if (cols_on) {
                 float v[16];
                 tmem_ld16(tw + c0, v);
@@ -595,8 +620,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
                 if (row < KH) store_row16(G.h1h, G.h1l, row, c0, v, S_PT);
             }
             signal_ready(G.ready);                        // -> dgrad1
+            TC_TRACE(tsl + 11);
             // ---- P8/P9: epilogue 4: encoding backward (+ input gradient), E^T operand, wgrad1 per feature block ----
             wait_done(G.done, ph_done);
+            TC_TRACE(tsl + 12);
 #pragma unroll 1
             for (int mb = 0; mb < t.MB; ++mb) {
                 const int f = 128 * mb + row;
@@ -670,6 +697,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
                         }
                     }
                     signal_ready(G.ready);                // -> wgrad1(mb)
+                    TC_TRACE(tsl + 13 + mb);
                     if (mb + 1 >= t.MB) pending_aux = true;
                 }
             }
@@ -691,15 +719,18 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
                 }
             }
             group_sync(g);             // G.u0/u1/th, zp, gx are rewritten by the group's next tile
+            TC_TRACE(tsl + 15);
         }
         if (pending_aux) {             // the last wgrad1 of this group
             mbar_wait(G.aux, ph_aux);
             ph_aux ^= 1;
         }
     }
+    TC_TRACE(80);
     fence_before_sync();
     __syncthreads();
     fence_after_sync();
+    TC_TRACE(81);
 
     // ---- weight gradients: TMEM accumulators -> shared memory in blob order -> coalesced Adam / gradient store ----
     if (want_wgrad) {
@@ -770,6 +801,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
             }
         }
         __syncthreads();
+        TC_TRACE(82);
         const size_t po = (size_t)p * L.n_params;
         if (a.adam_w == nullptr) {
             float4 *dst = reinterpret_cast<float4 *>(a.grad_out + po);
@@ -811,6 +843,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
                 }
             }
             __syncthreads();
+            TC_TRACE(83);
             // refresh the packed operand copy: item = (matrix, column octet, row) -> 16 B of hi + 16 B of lo
             unsigned char *pk = a.packed_out + (size_t)p * t.packed_bytes;
             const int rows = KH, n1 = (K1 / 8) * rows, n2 = (KH / 8) * rows;
@@ -846,6 +879,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
     }
     fence_before_sync();
     __syncthreads();
+    TC_TRACE(84);
     if (is_issuer) tmem_dealloc(tmem, 512);
 }
 
@@ -900,3 +934,9 @@ int onf_tc_launch(const OnfArgs &o, const OnfTcExtra &x, int P, cudaStream_t str
 }
 
 }  // namespace nfopp
+
+#ifdef NFOPP_TC_TRACE
+extern "C" int nfopp_debug_tc_trace(long long *host_out) {
+    return (int)cudaMemcpyFromSymbol(host_out, nfopp::g_tc_trace, sizeof(nfopp::g_tc_trace));
+}
+#endif
