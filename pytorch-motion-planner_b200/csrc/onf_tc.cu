@@ -63,7 +63,7 @@ struct TcDims {
 
 __host__ __device__ inline int ru16(int x) { return (x + 15) / 16 * 16; }
 
-constexpr int TC_GRP_FLOATS = 5 * TC_TP + 4 * TC_TP + 4 * TC_TP * 3;     // u0,u1,th,skip,gbar | zp | gx
+constexpr int TC_GRP_FLOATS = 8 * TC_TP + 4 * TC_TP + 4 * TC_TP * 3;     // u0,u1,th (x2: next tile prefetched),skip,gbar | zp | gx
 
 __host__ __device__ inline bool tc_make_dims(const OnfDims &d, TcDims *out) {
     TcDims t{};
@@ -211,15 +211,13 @@ struct TcShared {
 };
 struct TcGroup {
     unsigned char *h1h, *h1l, *rh, *rl;      // H1 / gH1 operand, scratch region (E ring / gH2 / E^T)
-    float *u0, *u1, *th, *skip, *gbar, *zp, *gx;
+    float *in0, *skip, *gbar, *zp, *gx;            // in0: [2][u0 | u1 | th] input buffers (this tile / next tile)
     uint64_t *ready, *done, *aux;
     __device__ TcGroup(unsigned char *base, const TcDims &t, const TcShared &s, int g) {
         h1h = base + t.off_grp + g * t.grp_bytes; h1l = h1h + t.h1_half;
         rh = h1l + t.h1_half; rl = rh + TC_RHALF;
         float *f = s.grp_f + g * TC_GRP_FLOATS;
-        u0 = f; f += TC_TP;
-        u1 = f; f += TC_TP;
-        th = f; f += TC_TP;
+        in0 = f; f += 6 * TC_TP;
         skip = f; f += TC_TP;
         gbar = f; f += TC_TP;
         zp = f; f += 4 * TC_TP;
@@ -445,6 +443,18 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
         const float my_b1 = row < H ? s.b1[row] : 0.f, my_b2 = row < H ? s.b2[row] : 0.f, my_w3 = row < H ? s.w3h[row] : 0.f;
         const int n_tiles = (cnt + TC_TP - 1) / TC_TP;
         const int c0 = 16 * cq;                            // this warp's 16 columns of the tile
+        if (gt < TC_TP) {                                  // inputs of the group's first tile
+            float x0 = 0.f, x1 = 0.f, x2 = 0.f;
+            if (g * TC_TP + gt < cnt) {
+                const float *xp = a.x + ((size_t)p * a.n + g * TC_TP + gt) * a.x_stride;
+                x0 = xp[0]; x1 = xp[1];
+                if (L.in_dim == 3) x2 = xp[2];
+            }
+            G.in0[gt] = (x0 - d.mean) / d.sigma;
+            G.in0[TC_TP + gt] = (x1 - d.mean) / d.sigma;
+            G.in0[2 * TC_TP + gt] = x2;
+        }
+        group_sync(g);
         for (int tile = g; tile < n_tiles; tile += 2) {
             const int n0 = tile * TC_TP;
             const int nv = min(TC_TP, cnt - n0);
@@ -452,24 +462,28 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
             const bool cols_on = c0 < Nt;
             const int tsl = 2 + 16 * (tile >> 1);
             TC_TRACE(tsl);
-            // ---- P0: inputs (onf_model.py:37-38) ----
+            // ---- P0: this tile's inputs were staged by the previous tile (or before the loop); threads gt < 32 now
+            // fetch the next tile's inputs (onf_model.py:37-38) and this tile's label / upstream gradient, consumed later ----
+            float *cu0 = G.in0 + ((tile >> 1) & 1) * 3 * TC_TP, *cu1 = cu0 + TC_TP, *cth = cu1 + TC_TP;
+            float nx0 = 0.f, nx1 = 0.f, nx2 = 0.f, my_aux = 0.f;
             if (gt < TC_TP) {
-                float x0 = 0.f, x1 = 0.f, x2 = 0.f;
-                if (gt < nv) {
-                    const float *xp = a.x + ((size_t)p * a.n + n0 + gt) * a.x_stride;
-                    x0 = xp[0]; x1 = xp[1];
-                    if (L.in_dim == 3) x2 = xp[2];
+                const int nn = n0 + 2 * TC_TP + gt;
+                if (nn < cnt) {
+                    const float *xp = a.x + ((size_t)p * a.n + nn) * a.x_stride;
+                    nx0 = xp[0]; nx1 = xp[1];
+                    if (L.in_dim == 3) nx2 = xp[2];
                 }
-                G.u0[gt] = (x0 - d.mean) / d.sigma;
-                G.u1[gt] = (x1 - d.mean) / d.sigma;
-                G.th[gt] = x2;
+                if (gt < nv && want_bwd) {
+                    const size_t gi = (size_t)p * a.n + n0 + gt;
+                    if (a.gbar_mode == 0) my_aux = a.gz[gi];
+                    else if (a.gbar_mode != 2) my_aux = a.aux[gi];
+                }
             }
-            group_sync(g);
             TC_TRACE(tsl + 1);
             // ---- P1: encoding (CUDA cores) feeding fwd1 in groups of 128 features ----
             {
                 const int n = gt & 31, oc = gt >> 5;         // point, feature octet (0..7) within a 64-feature half group
-                const float u0 = G.u0[n], u1 = G.u1[n], th = G.th[n];
+                const float u0 = cu0[n], u1 = cu1[n], th = cth[n];
 #pragma unroll 1
                 for (int fg = 0; fg < t.MB; ++fg) {
                     uint4 ehi[2], elo[2];
@@ -514,6 +528,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
             // ---- P2: epilogue 1: bias + ReLU -> H1 operand; row H = skip term of the logit ----
             wait_done(G.done, ph_done);
             TC_TRACE(tsl + 4);
+            if (gt < TC_TP) {                             // next tile's inputs -> the other input buffer
+                float *nu = G.in0 + (((tile >> 1) & 1) ^ 1) * 3 * TC_TP;
+                nu[gt] = (nx0 - d.mean) / d.sigma;
+                nu[TC_TP + gt] = (nx1 - d.mean) / d.sigma;
+                nu[2 * TC_TP + gt] = nx2;
+            }
             if (cols_on) {
                 float v[16];
                 tmem_ld16(tw + c0, v);
@@ -561,15 +581,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
                 if (valid && a.z_out) a.z_out[gi] = z;
                 float gb = 0.f;
                 if (valid && want_bwd) {                        // dL/dz
-                    if (a.gbar_mode == 0) gb = a.gz[gi];
-                    else if (a.gbar_mode == 1) gb = (sigmoid_f(z) - a.aux[gi]) / (float)cnt;
+                    if (a.gbar_mode == 0) gb = my_aux;
+                    else if (a.gbar_mode == 1) gb = (sigmoid_f(z) - my_aux) / (float)cnt;
                     else {
                         const float zb = z * a.beta;
                         const float ez = expf(zb);
                         gb = a.wc * (zb > 20.f ? 1.f : ez / (ez + 1.f));
                         if (a.gbar_mode == 3) {
                             const float th = tanhf(z);
-                            gb += a.aux[gi] * (1.f - th * th);
+                            gb += my_aux * (1.f - th * th);
                         }
                     }
                 }
@@ -640,10 +660,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
                     if (cols_on) {
                         float v[16], xu[16], x1[16];
                         tmem_ld16(tw + 32 * mb + c0, v);
-                        const float *x1src = fourier ? G.u1 : G.th;
+                        const float *x1src = fourier ? cu1 : cth;
 #pragma unroll
                         for (int i4 = 0; i4 < 4; ++i4) {
-                            *reinterpret_cast<float4 *>(xu + 4 * i4) = *reinterpret_cast<const float4 *>(G.u0 + c0 + 4 * i4);
+                            *reinterpret_cast<float4 *>(xu + 4 * i4) = *reinterpret_cast<const float4 *>(cu0 + c0 + 4 * i4);
                             *reinterpret_cast<float4 *>(x1 + 4 * i4) = *reinterpret_cast<const float4 *>(x1src + c0 + 4 * i4);
                         }
 #pragma unroll
@@ -718,7 +738,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
                     for (int c = L.in_dim; c < a.x_stride; ++c) out[c] = 0.f;   // pose columns the ONF does not read
                 }
             }
-            group_sync(g);             // G.u0/u1/th, zp, gx are rewritten by the group's next tile
+            group_sync(g);             // zp, gx, skip, gbar are rewritten by the group's next tile
             TC_TRACE(tsl + 15);
         }
         if (pending_aux) {             // the last wgrad1 of this group
