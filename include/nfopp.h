@@ -214,6 +214,14 @@ int nfopp_engine_reparametrize(nfopp_engine *e, void *stream);
  * (sum of x,y segment lengths), n_colliding_dev [P] int32 or NULL. */
 int nfopp_engine_evaluate_paths(nfopp_engine *e, int samples_per_segment, uint8_t *collides_dev, float *length_dev,
                                 int32_t *n_colliding_dev, void *stream);
+/* Path-quality statistics of every problem's current path, the numbers BenchmarkAdapter::evaluate
+ * (benchmark/bench_mr_binding/BenchmarkAdapter.cpp:68-103) files per plan: stats_dev [P, 8] float32 =
+ * {path length (x,y), max curvature, normalised curvature (sum of curvature x arc length), angle over length,
+ * OMPL smoothness, cusps (computeCusps, BenchmarkAdapter.cpp:105-135, yaw change > cusp_angle_threshold),
+ * min clearing, mean clearing} on the T+2 path nodes in float64.  Clearing = distance from the pose to the nearest
+ * obstacle of the engine's checker (disc / box / occupied cell within +-clearing_window_cells / boundary), 0 in collision. */
+int nfopp_engine_path_statistics(nfopp_engine *e, double cusp_angle_threshold, int clearing_window_cells,
+                                 float *stats_dev, void *stream);
 /* number of kernel launches issued by this engine so far (bench.py's gpu_launches) */
 int nfopp_engine_launch_count(nfopp_engine *e, int64_t *launches);
 

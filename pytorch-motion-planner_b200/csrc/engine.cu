@@ -62,6 +62,7 @@ int launch_tick(const EngineDev &e, bool warm, cudaStream_t s);
 int launch_paths(const EngineDev &e, float *out, cudaStream_t s);
 int launch_reparam(const EngineDev &e, cudaStream_t s);
 int launch_evaluate_paths(const EngineDev &e, int k, uint8_t *collides, float *length, int32_t *n_hit, cudaStream_t s);
+int launch_path_statistics(const EngineDev &e, double cusp_threshold, int window, float *out, cudaStream_t s);
 
 // impl 0 = auto: the tensor path whenever the network shape fits it
 static int resolve_impl(const OnfDims &d, int impl, int *out) {
@@ -756,6 +757,13 @@ extern "C" int nfopp_engine_reparametrize(nfopp_engine *e, void *stream) {
     NFOPP_REQUIRE(e, "reparametrize: bad arguments");
     e->launches += 1;
     return launch_reparam(e->dev, (cudaStream_t)stream);
+}
+
+extern "C" int nfopp_engine_path_statistics(nfopp_engine *e, double cusp_angle_threshold, int clearing_window_cells, float *stats,
+                                            void *stream) {
+    NFOPP_REQUIRE(e && stats, "path_statistics: bad arguments");
+    e->launches += 1;
+    return launch_path_statistics(e->dev, cusp_angle_threshold, clearing_window_cells, stats, (cudaStream_t)stream);
 }
 
 extern "C" int nfopp_engine_evaluate_paths(nfopp_engine *e, int samples_per_segment, uint8_t *collides, float *length,

@@ -450,4 +450,137 @@ int launch_evaluate_paths(const EngineDev &e, int k, uint8_t *collides, float *l
     return NFOPP_OK;
 }
 
+// ---- path-quality statistics: the numbers BenchmarkAdapter::evaluate (BenchmarkAdapter.cpp:68-103) files
+// per path - length, max / normalised curvature, angle over length, OMPL smoothness, cusps, clearing - on the T+2 nodes
+// of every problem's path (x, y; float64).  computeCusps follows BenchmarkAdapter.cpp:105-135 line by line; the other
+// metrics live in the missing bench-mr / OMPL submodules and are restated from their published definitions
+// (oracle/path_stats.py is the CPU restatement; parity unpinned for those).  One warp per problem.
+constexpr int STATS_PER_PROBLEM = 8;   // length, max curvature, normalised curvature, aol, smoothness, cusps, min / mean clearing
+
+__device__ __forceinline__ double norm_angle_d(double a) {   // PlannerUtils::normalizeAngle: into [-pi, pi)
+    const double two_pi = 6.283185307179586, pi = 3.141592653589793;
+    a = fmod(a + pi, two_pi);
+    if (a < 0.0) a += two_pi;
+    return a - pi;
+}
+
+__device__ __forceinline__ double warp_sum_d(double v) {
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ double warp_max_d(double v) {
+    for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+__device__ __forceinline__ double warp_min_d(double v) {
+    for (int o = 16; o > 0; o >>= 1) v = fmin(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// distance from a pose to the nearest obstacle of the engine's environment (>= 0 outside, 0 in collision)
+__device__ double clearing_distance(const EngineDev &e, int pe, int m, double x, double y, double th, int window) {
+    const CheckerParams &c = e.checker;
+    double best = 1e30;
+    if (c.kind == 1 || c.kind == 2) {
+        const double *obs = e.obstacles + (size_t)pe * e.m_max * 2;
+        const double ct = cos(th), st = sin(th);
+        for (int i = 0; i < m; ++i) {
+            const double dx = obs[2 * i] - x, dy = obs[2 * i + 1] - y;
+            double dist;
+            if (c.kind == 1) {
+                dist = sqrt(dx * dx + dy * dy) - c.radius;
+            } else {                                              // obstacle point in the robot frame vs the box
+                const double rx = ct * dx + st * dy, ry = -st * dx + ct * dy;
+                const double ex = fmax(fmax(c.box[0] - rx, rx - c.box[1]), 0.0), ey = fmax(fmax(c.box[2] - ry, ry - c.box[3]), 0.0);
+                dist = sqrt(ex * ex + ey * ey);
+            }
+            best = fmin(best, dist);
+        }
+    } else if (c.kind == 3) {
+        const uint8_t *grid = e.grid + (size_t)pe * c.rows * c.cols;
+        const int cx = (int)floor((x - c.ox) / c.cell), cy = (int)floor((y - c.oy) / c.cell);
+        for (int iy = max(cy - window, 0); iy <= min(cy + window, c.rows - 1); ++iy)
+            for (int ix = max(cx - window, 0); ix <= min(cx + window, c.cols - 1); ++ix)
+                if (grid[(size_t)iy * c.cols + ix] > 0) {
+                    // nearest point of the occupied cell's square [ox + ix cell, +cell] x [oy + iy cell, +cell]
+                    const double x0 = c.ox + ix * c.cell, y0 = c.oy + iy * c.cell;
+                    const double ex = fmax(fmax(x0 - x, x - (x0 + c.cell)), 0.0), ey = fmax(fmax(y0 - y, y - (y0 + c.cell)), 0.0);
+                    best = fmin(best, sqrt(ex * ex + ey * ey));
+                }
+        best = fmin(best, (double)window * c.cell);               // nothing inside the search window
+    }
+    if (c.has_bounds) best = fmin(best, fmin(fmin(x - c.bounds[0], c.bounds[1] - x), fmin(y - c.bounds[2], c.bounds[3] - y)));
+    return fmax(best, 0.0);
+}
+
+__global__ void __launch_bounds__(128) path_statistics_kernel(const EngineDev e, double cusp_threshold, int window, float *__restrict__ out) {
+    const int p = blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (p >= e.P) return;
+    const int T = e.T, D = e.D, n = T + 2;
+    const int pe = e.env_shared ? 0 : p;
+    const int m = (e.checker.kind == 1 || e.checker.kind == 2) ? (e.obstacle_n ? e.obstacle_n[pe] : e.m_max) : 0;
+    auto node = [&](int j, int d) -> double {
+        return (double)(j == 0 ? e.start[(size_t)p * D + d] : (j == T + 1 ? e.goal[(size_t)p * D + d] : e.traj[((size_t)p * T + j - 1) * D + d]));
+    };
+    double len = 0.0, kmax = 0.0, knorm = 0.0, smooth = 0.0, cmin = 1e30, csum = 0.0;
+    for (int j = lane; j < n; j += 32) {
+        const double x = node(j, 0), y = node(j, 1);
+        if (j + 1 < n) {
+            const double dx = node(j + 1, 0) - x, dy = node(j + 1, 1) - y;
+            len += sqrt(dx * dx + dy * dy);
+        }
+        if (j >= 1 && j + 1 < n) {
+            const double ax = x - node(j - 1, 0), ay = y - node(j - 1, 1), bx = node(j + 1, 0) - x, by = node(j + 1, 1) - y;
+            const double a = sqrt(ax * ax + ay * ay), b = sqrt(bx * bx + by * by);
+            const double cx = ax + bx, cy = ay + by, c = sqrt(cx * cx + cy * cy);
+            if (a > 1e-12 && b > 1e-12 && c > 1e-12) {            // Menger curvature of (p_{j-1}, p_j, p_{j+1})
+                const double kj = 2.0 * fabs(ax * by - ay * bx) / (a * b * c);
+                kmax = fmax(kmax, kj);
+                knorm += kj * 0.5 * (a + b);
+            }
+            if (a > 0.0 && b > 0.0) {                             // ompl::geometric::PathGeometric::smoothness
+                const double acv = (a * a + b * b - c * c) / (2.0 * a * b);
+                if (acv > -1.0 && acv < 1.0) {
+                    const double ang = 3.141592653589793 - acos(acv);
+                    const double kk = 2.0 * ang / (a + b);
+                    smooth += kk * kk;
+                }
+            }
+        }
+        const double cd = clearing_distance(e, pe, m, x, y, D == 3 ? node(j, 2) : 0.0, window);
+        cmin = fmin(cmin, cd);
+        csum += cd;
+    }
+    len = warp_sum_d(len); kmax = warp_max_d(kmax); knorm = warp_sum_d(knorm); smooth = warp_sum_d(smooth);
+    cmin = warp_min_d(cmin); csum = warp_sum_d(csum);
+    if (lane == 0) {
+        // BenchmarkAdapter::computeCusps (BenchmarkAdapter.cpp:105-135) + the summed heading change for angle-over-length
+        int cusps = 0, prev = 0, cur = 0, next = 0;
+        double turn = 0.0;
+        auto dist = [&](int i, int j) { const double dx = node(i, 0) - node(j, 0), dy = node(i, 1) - node(j, 1); return sqrt(dx * dx + dy * dy); };
+        while (next < n) {
+            if (dist(prev, cur) <= 0.0) { ++cur; ++next; if (cur >= n) break; }
+            else if (dist(cur, next) <= 0.0) { ++next; }
+            else {
+                const double yaw_prev = atan2(node(cur, 1) - node(prev, 1), node(cur, 0) - node(prev, 0));
+                const double yaw_next = atan2(node(next, 1) - node(cur, 1), node(next, 0) - node(cur, 0));
+                const double change = fabs(norm_angle_d(yaw_next - yaw_prev));
+                if (change > cusp_threshold) ++cusps;
+                turn += change;
+                prev = cur; cur = next; ++next;
+            }
+        }
+        float *o = out + (size_t)p * STATS_PER_PROBLEM;
+        o[0] = (float)len; o[1] = (float)kmax; o[2] = (float)knorm; o[3] = (float)(len > 0.0 ? turn / len : 0.0);
+        o[4] = (float)smooth; o[5] = (float)cusps; o[6] = (float)cmin; o[7] = (float)(csum / n);
+    }
+}
+
+int launch_path_statistics(const EngineDev &e, double cusp_threshold, int window, float *out, cudaStream_t s) {
+    NFOPP_REQUIRE(window >= 0 && window <= 4096, "path_statistics: clearing window=%d cells", window);
+    path_statistics_kernel<<<(e.P + 3) / 4, 128, 0, s>>>(e, cusp_threshold, window, out);
+    NFOPP_CHECK_CUDA(cudaGetLastError());
+    return NFOPP_OK;
+}
+
 }  // namespace nfopp

@@ -77,6 +77,7 @@ SIGNATURES = {
     "nfopp_engine_get_paths": (_I, [_P, _P, _P]),
     "nfopp_engine_reparametrize": (_I, [_P, _P]),
     "nfopp_engine_evaluate_paths": (_I, [_P, _I, _P, _P, _P, _P]),
+    "nfopp_engine_path_statistics": (_I, [_P, C.c_double, _I, _P, _P]),
     "nfopp_engine_launch_count": (_I, [_P, C.POINTER(C.c_int64)]),
 }
 

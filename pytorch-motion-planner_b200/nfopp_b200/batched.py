@@ -122,6 +122,10 @@ class BatchedPlanner:
         """(collides bool [P], length [P], colliding pose count [P]) of the current paths, on the device."""
         return self.engine.evaluate_paths(samples_per_segment)
 
+    def path_statistics(self, **kw):
+        """bench-mr PathStatistics of the current paths (BenchmarkAdapter.cpp:68-135) -> {name: float32 [P]}."""
+        return self.engine.path_statistics(**kw)
+
     def solve(self, max_iterations=1000, min_iterations=200, check_every=50, samples_per_segment=4, graph=True):
         """scripts/run_bench_mr.py:109-131 for all problems at once: step, and every `check_every` iterations past
         `min_iterations` evaluate every path on the device; a problem keeps its shortest collision-free path and is

@@ -318,6 +318,18 @@ class PlannerEngine:
                                                           L.ptr(hits), L.stream_ptr()))
         return collides.bool(), length, hits
 
+    PATH_STATS = ("path_length", "max_curvature", "normalized_curvature", "aol", "smoothness", "cusps",
+                  "min_clearing_distance", "mean_clearing_distance")
+
+    def path_statistics(self, cusp_angle_threshold=60.0 * 3.141592653589793 / 180.0, clearing_window_cells=64):
+        """The per-plan statistics BenchmarkAdapter::evaluate files (BenchmarkAdapter.cpp:68-135), for every problem's
+        current path, on the device -> {name: float32 [P]} (names as in bench-mr's PathStatistics)."""
+        out = torch.empty(self.config.problems, len(self.PATH_STATS), dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            L.check(self._lib.nfopp_engine_path_statistics(self._h, float(cusp_angle_threshold), int(clearing_window_cells),
+                                                           L.ptr(out), L.stream_ptr()))
+        return {k: out[:, i] for i, k in enumerate(self.PATH_STATS)}
+
     @property
     def launches(self) -> int:
         v = C.c_int64()

@@ -522,3 +522,49 @@ def test_batched_solve_loop_matches_reference_bookkeeping():
     assert torch.allclose(length[out["solved"]], out["length"][out["solved"]], rtol=1e-5)
     its = out["iterations"].cpu().numpy()
     assert ((its == 600) | ((its - 1) % 50 == 0)).all() and (its[its < 600] > 200).all()
+
+
+# ---------------------------------------------------------------------------------------- path statistics
+@pytest.mark.parametrize("name", ["car", "corridor", "holonomic"])
+def test_path_statistics_match_oracle(name):
+    """nfopp_engine_path_statistics vs oracle.path_stats (BenchmarkAdapter.cpp:68-135 restated) on paths of a running
+    planner: cusp counts exact, the float64 metrics to 1e-4 relative (float32 outputs)."""
+    from _gpu_util import engine_from_golden
+    from oracle import path_stats as PS
+    fx = U.load(f"lockstep_{name}.npz")
+    P = 8
+    eng = engine_from_golden(name, fx, "free/state0", problems=P, rng_mode="philox", seed=9)
+    obs, bounds = fx["meta/obstacles"], tuple(float(b) for b in fx["meta/bounds"])
+    env = dict(kind="rectangle", obstacles=obs, box=(-0.3, 0.2, -0.3, 0.2), bounds=bounds) if name == "car" else \
+        dict(kind="circle", obstacles=obs, radius=0.3, bounds=bounds)
+    for _ in range(3):
+        eng.step(40)
+        stats = {k: v.cpu().numpy() for k, v in eng.path_statistics(cusp_angle_threshold=np.pi / 3).items()}
+        paths = eng.paths().cpu().numpy()
+        for p in range(P):
+            ref = PS.path_statistics(paths[p], np.pi / 3, **env)
+            assert int(stats["cusps"][p]) == int(ref["cusps"])
+            for k, v in ref.items():
+                assert abs(float(stats[k][p]) - v) <= 1e-4 * max(abs(v), 1e-3), (k, p, float(stats[k][p]), v)
+
+
+def test_path_statistics_on_occupancy_grid():
+    """clearing distances against occupied cells (grid checker) + the straight-line known answers."""
+    from nfopp_b200.batched import BatchedPlanner, forest_config
+    from nfopp_b200.test_environment_builder import TestEnvironmentBuilder as B
+    from oracle import path_stats as PS
+    P = 6
+    starts, goals, _, grids, _, cell = B.make_random_grid_batch(P, seed=2)
+    cfg = forest_config(P, cell=cell, seed=4)
+    bp = BatchedPlanner(cfg)
+    bp.init(starts, goals, grids=grids)
+    st0 = {k: v.cpu().numpy() for k, v in bp.path_statistics().items()}
+    assert np.all(st0["cusps"] == 0) and np.all(st0["max_curvature"] < 1e-3)       # straight-line initial paths
+    bp.step(30)
+    stats = {k: v.cpu().numpy() for k, v in bp.path_statistics(clearing_window_cells=16).items()}
+    paths = bp.get_path()
+    for p in range(P):
+        ref = PS.path_statistics(paths[p], np.pi / 3, kind="grid", grid=np.asarray(grids[p]), cell=cfg.grid_cell,
+                                 bounds=cfg.checker_bounds, window=16)
+        for k, v in ref.items():
+            assert abs(float(stats[k][p]) - v) <= 1e-4 * max(abs(v), 1e-3), (k, p, float(stats[k][p]), v)

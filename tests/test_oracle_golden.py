@@ -77,3 +77,18 @@ def test_short_free_run_matches_reference_path(name):
     for k in range(10):
         op.step(RecordedSource(U.variates_from(fx, f"free/var{k}")))
         assert np.abs(op.get_path() - fx[f"free/path{k}"]).max() < 1e-3, k
+
+
+def test_path_statistics_known_answers():
+    """oracle.path_stats on closed-form paths: unit half circle (curvature 1, turn pi), a zig-zag with duplicate nodes
+    (BenchmarkAdapter.cpp:105-135 skips duplicates: two cusps at the 60 degree threshold)."""
+    from oracle.path_stats import path_statistics
+    t = np.linspace(0, np.pi, 200)
+    s = path_statistics(np.stack([np.cos(t), np.sin(t), t], 1), kind="circle", obstacles=np.zeros((1, 2)), radius=0.3,
+                        bounds=(-2, 2, -2, 2))
+    assert abs(s["max_curvature"] - 1) < 1e-6 and abs(s["path_length"] - np.pi) < 1e-3 and s["cusps"] == 0
+    assert abs(s["aol"] * s["path_length"] - np.pi * 198 / 199) < 1e-9 and abs(s["min_clearing_distance"] - 0.7) < 1e-12
+    z = path_statistics(np.array([[0, 0], [1, 0], [1, 0], [0.2, 0.1], [2, 2.0]]))
+    assert z["cusps"] == 2 and z["path_length"] > 4.4
+    line = path_statistics(np.stack([np.linspace(0, 3, 20), np.zeros(20)], 1))
+    assert line["max_curvature"] == 0 and line["smoothness"] == 0 and line["cusps"] == 0
