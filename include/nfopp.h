@@ -214,6 +214,18 @@ int nfopp_engine_reparametrize(nfopp_engine *e, void *stream);
  * (sum of x,y segment lengths), n_colliding_dev [P] int32 or NULL. */
 int nfopp_engine_evaluate_paths(nfopp_engine *e, int samples_per_segment, uint8_t *collides_dev, float *length_dev,
                                 int32_t *n_colliding_dev, void *stream);
+/* AstarTrajectoryInitializer.initialize_trajectory (astar/astar_trajectory_initializer.py:15-46) for all P problems:
+ * the engine's collision checker labels the centres of an x_cells x y_cells grid over the checker boundaries (cell size
+ * `resolution`, heading 3 pi / 4), A* (astar/jps.py search with jps=False: 8-connected, sqrt(2) diagonals, Euclidean
+ * heuristic, heap order (key, (row, col))) runs from every problem's start cell to its goal cell, and the cell path
+ * (+ start, goal) is re-parametrised to the T trajectory points by utils/math.py:57-65 (quadratic interpolating
+ * spline).  Writes x, y of the stored trajectories; headings are left as they are.  start_cells_dev / goal_cells_dev
+ * [P, 2] int32 (row = y cell, column = x cell; computed by the caller with the reference's float32 floor division),
+ * workspace_dev from nfopp_engine_astar_workspace_bytes, path_cells_dev [P] int32 (cells on each A* path) or NULL. */
+int nfopp_engine_astar_workspace_bytes(nfopp_engine *e, int x_cells, int y_cells, size_t *bytes);
+int nfopp_engine_init_astar(nfopp_engine *e, int x_cells, int y_cells, double resolution, const int32_t *start_cells_dev,
+                            const int32_t *goal_cells_dev, void *workspace_dev, size_t workspace_bytes,
+                            int32_t *path_cells_dev, void *stream);
 /* Path-quality statistics of every problem's current path, the numbers BenchmarkAdapter::evaluate
  * (benchmark/bench_mr_binding/BenchmarkAdapter.cpp:68-103) files per plan: stats_dev [P, 8] float32 =
  * {path length (x,y), max curvature, normalised curvature (sum of curvature x arc length), angle over length,

@@ -64,7 +64,8 @@ class BatchedPlanner:
         self.device = self.engine.device
         self._use_normal_init = use_normal_init
 
-    def init(self, start_points, goal_points, obstacles=None, obstacle_counts=None, grids=None, onf_weights=None):
+    def init(self, start_points, goal_points, obstacles=None, obstacle_counts=None, grids=None, onf_weights=None,
+             astar_resolution=None):
         """start/goal: [P, D]; obstacles [P|1, M, 2] or grids [P|1, rows, cols]; onf_weights [P, n_params] or
         None (fresh initialisation seeded by config.seed)."""
         eng = self.engine
@@ -78,6 +79,8 @@ class BatchedPlanner:
                                            self.config.seed + 7919, self.device)
         eng["onf_w"].copy_(torch.as_tensor(onf_weights).to(self.device))
         eng.init_trajectories()
+        if astar_resolution is not None:               # AstarTrajectoryInitializer (scripts/run_bench_mr.py:23-26)
+            eng.init_astar(astar_resolution)
         eng.warmup(self.config.init_collision_iteration)
         eng.set_counter("step_count", 0)
 

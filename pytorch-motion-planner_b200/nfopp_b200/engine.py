@@ -259,6 +259,36 @@ class PlannerEngine:
             goal_angle = wrap_angle(goal[:, 2] - start[:, 2]) + start[:, 2]
             traj[:, :, 2] = batched_linspace(start[:, 2], goal_angle, n)[:, 1:-1]
 
+    def init_astar(self, resolution):
+        """AstarTrajectoryInitializer.initialize_trajectory (astar/astar_trajectory_initializer.py:15-46) for every problem,
+        on the device: checker-labelled cell grid -> A* (astar/jps.py, jps=False) -> quadratic re-parametrisation into the
+        x, y of the trajectories (call after init_trajectories, which sets the headings).  -> int32 [P] cells per A* path."""
+        if self.config.checker_bounds is None:
+            raise ValueError("A* initialisation needs collision-checker boundaries (get_boundaries)")
+        b = tuple(float(v) for v in self.config.checker_bounds)
+        res = float(resolution)
+        # grid shape and start / goal cells exactly as the reference computes them (:29-34: python floor division on the
+        # boundaries, float32 floor division on the float32 end points)
+        x_cells = int((b[1] - b[0]) // res) + 1
+        y_cells = int((b[3] - b[2]) // res) + 1
+        cells = []
+        for name in ("start", "goal"):
+            pt = self[name].detach().cpu().numpy().astype(np.float32)
+            cx = ((pt[:, 0] - np.float32(b[0])) // np.float32(res)).astype(np.int64)
+            cy = ((pt[:, 1] - np.float32(b[2])) // np.float32(res)).astype(np.int64)
+            if ((cx < 0) | (cx >= x_cells) | (cy < 0) | (cy >= y_cells)).any():
+                raise IndexError(f"A* initialisation: a {name} point lies outside the collision-checker boundaries {b}")
+            cells.append(torch.as_tensor(np.stack([cy, cx], 1).astype(np.int32)).to(self.device))
+        nbytes = C.c_size_t()
+        L.check(self._lib.nfopp_engine_astar_workspace_bytes(self._h, x_cells, y_cells, C.byref(nbytes)))
+        ws = torch.empty(int(nbytes.value), dtype=torch.uint8, device=self.device)
+        path_cells = torch.empty(self.config.problems, dtype=torch.int32, device=self.device)
+        with torch.cuda.device(self.device):
+            L.check(self._lib.nfopp_engine_init_astar(self._h, x_cells, y_cells, res, L.ptr(cells[0]), L.ptr(cells[1]), L.ptr(ws),
+                                                      C.c_size_t(ws.numel()), L.ptr(path_cells), L.stream_ptr()))
+            torch.cuda.current_stream().synchronize()          # the workspace is freed on return
+        return path_cells
+
     # ---- counters ------------------------------------------------------------------------------------
     def counter(self, name) -> int:
         v = C.c_int64()

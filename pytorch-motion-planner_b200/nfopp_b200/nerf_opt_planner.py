@@ -107,7 +107,11 @@ class NERFOptPlanner(ContinuousPlanner):
         eng = self._engine
         eng.set_endpoints(np.asarray(start_point, dtype=np.float32)[:d], np.asarray(goal_point, dtype=np.float32)[:d])
         self._start_point, self._goal_point = eng["start"], eng["goal"]
-        eng.init_trajectories()
+        initializer = getattr(self, "_trajectory_initializer", None)
+        if hasattr(initializer, "initialize_engine"):          # AstarTrajectoryInitializer
+            initializer.initialize_engine(eng)
+        else:
+            eng.init_trajectories()
         eng.warmup(self._init_collision_iteration)
         eng.set_counter("step_count", 0)
 

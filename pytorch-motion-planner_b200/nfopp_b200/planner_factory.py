@@ -4,6 +4,7 @@ import torch
 from .constrained_nerf_opt_planner import ConstrainedNERFOptPlanner
 from .nerf_opt_planner import NERFOptPlanner
 from .onf_model import ONF
+from .astar_trajectory_initializer import AstarTrajectoryInitializer
 from .trajectory_initializer import TrajectoryInitializer
 from .utils.attribute_dict import AttributeDict
 from .utils.universal_factory import UniversalFactory
@@ -40,7 +41,7 @@ class PlannerFactory(object):
         """planner_factory.py:62-77: every component is resolved by name from the nested config."""
         if parameters is None:
             parameters = DEFAULT_PARAMETERS
-        factory = UniversalFactory([ONF, ConstrainedNERFOptPlanner, TrajectoryInitializer])
+        factory = UniversalFactory([ONF, ConstrainedNERFOptPlanner, TrajectoryInitializer, AstarTrajectoryInitializer])
         device = parameters["device"]
         model = factory.make_from_parameters(parameters["collision_model"]).to(device)
         model_optimizer = torch.optim.Adam(model.parameters(), **parameters["collision_optimizer"])

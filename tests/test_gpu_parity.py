@@ -568,3 +568,80 @@ def test_path_statistics_on_occupancy_grid():
                                  bounds=cfg.checker_bounds, window=16)
         for k, v in ref.items():
             assert abs(float(stats[k][p]) - v) <= 1e-4 * max(abs(v), 1e-3), (k, p, float(stats[k][p]), v)
+
+
+# ---------------------------------------------------------------------------------------- A* initialiser
+def test_astar_initialiser_matches_reference():
+    """nfopp_engine_init_astar vs the live reference's AstarTrajectoryInitializer (tests/golden/astar.npz, made by
+    oracle/make_golden_astar.py): number of cells on the A* path exact, initial x, y trajectory within 2e-6 (float32
+    outputs of a float64 spline; the oracle restatement matches the reference bit for bit), headings as the reference."""
+    from _gpu_util import engine_config
+    from nfopp_b200.engine import PlannerEngine
+    from oracle import astar as A
+    from oracle import checkers as OC
+    fx = U.load("astar.npz")
+    lock = U.load("lockstep_car.npz")
+    for name in [str(n) for n in fx["names"]]:
+        g = lambda k: fx[f"{name}/{k}"]                                      # noqa: E731
+        kind, bounds, res, T = str(g("kind")), tuple(float(b) for b in g("bounds")), float(g("resolution")), int(g("T"))
+        obs, start, goal = g("obstacles"), g("start"), g("goal")
+        P = 3                                                                # problem 1: reversed, problem 2: other goal
+        starts = np.stack([start, goal, start]).astype(np.float32)
+        goals = np.stack([goal, start, np.array([start[0], goal[1], 0.0], dtype=np.float32)])
+        cfg = engine_config("car", lock, rng_mode="philox", problems=P, trajectory_length=T, checker=kind,
+                            checker_bounds=bounds, border=bounds, max_obstacles=max(64, len(obs)))
+        eng = PlannerEngine(cfg)
+        eng.set_obstacles(obs)
+        eng.set_endpoints(starts, goals)
+        eng.init_trajectories()
+        theta0 = eng["traj"][:, :, 2].clone()
+        n_cells = eng.init_astar(res).cpu().numpy()
+        traj = eng["traj"].cpu().numpy()
+        assert n_cells[0] == len(g("cells")) and np.isfinite(traj).all()
+        assert np.abs(traj[0, :, :2] - g("trajectory")[:, :2]).max() <= 2e-6, name
+        assert np.abs(traj[0, :, 2] - g("trajectory")[:, 2]).max() <= 1e-6       # initialize_angle (trajectory_initializer.py:21-29)
+        assert torch.equal(eng["traj"][:, :, 2], theta0)
+        label = (lambda p: OC.rectangle_labels(p, obs, (-0.3, 0.2, -0.3, 0.2), bounds)) if kind == "rectangle" else \
+            (lambda p: OC.circle_labels(p, obs, 0.3, bounds))
+        for p in (1, 2):                                                     # the other problems against the oracle
+            xy, cells, _ = A.initial_trajectory_xy(starts[p], goals[p], bounds, res, label, T)
+            assert n_cells[p] == len(cells), (name, p)
+            assert np.abs(traj[p, :, :2] - xy).max() <= 2e-6, (name, p)
+        eng.close()
+
+
+def test_astar_initialiser_through_the_factory_and_on_a_grid():
+    """PlannerFactory resolves AstarTrajectoryInitializer by name (scripts/run_bench_mr.py:23-26); BatchedPlanner.init with
+    astar_resolution on occupancy grids gives collision-free cell paths where the straight line collides."""
+    from nfopp_b200.batched import BatchedPlanner, forest_config
+    from nfopp_b200.test_environment_builder import TestEnvironmentBuilder as B
+    from oracle import astar as A
+    from oracle import checkers as OC
+    P = 5
+    starts, goals, _, grids, _, cell = B.make_random_grid_batch(P, seed=11)
+    cfg = forest_config(P, cell=cell, seed=3)
+    bp = BatchedPlanner(cfg)
+    bp.init(starts, goals, grids=grids, astar_resolution=4 * cell)
+    paths = bp.get_path()
+    assert np.isfinite(paths).all()
+    for p in range(P):
+        grid = np.asarray(grids[p])
+        label = lambda q: OC.grid_labels(q, grid, 0.0, 0.0, cfg.grid_cell, cfg.checker_bounds)   # noqa: E731
+        xy, _, _ = A.initial_trajectory_xy(np.asarray(starts[p], dtype=np.float32), np.asarray(goals[p], dtype=np.float32),
+                                           cfg.checker_bounds, 4 * cell, label, cfg.trajectory_length)
+        assert np.abs(paths[p, 1:-1, :2] - xy).max() <= 2e-6, p
+    # single-problem API: factory config with the A* initialiser
+    from nfopp_b200.collision_checker import CircleDirectedCollisionChecker
+    from nfopp_b200.planner_factory import DEFAULT_PARAMETERS, PlannerFactory
+    from nfopp_b200.utils.attribute_dict import AttributeDict
+    params = AttributeDict(DEFAULT_PARAMETERS)
+    params["trajectory_initializer"] = AttributeDict(name="AstarTrajectoryInitializer", resolution=0.25)
+    params["device"] = "cuda"
+    fx = U.load("astar.npz")
+    cc = CircleDirectedCollisionChecker(0.3, (0.0, 3.0, 0.0, 3.0))
+    cc.update_obstacle_points(fx["disc_coarse/obstacles"])
+    planner = PlannerFactory.make_constrained_onf_planner(cc, params)
+    planner.init(fx["disc_coarse/start"], fx["disc_coarse/goal"], (0.0, 3.0, 0.0, 3.0))
+    path = planner.get_path()
+    assert path.shape == (102, 3)
+    assert np.abs(path[1:-1, :2] - fx["disc_coarse/trajectory"][:, :2]).max() <= 2e-6

@@ -92,3 +92,21 @@ def test_path_statistics_known_answers():
     assert z["cusps"] == 2 and z["path_length"] > 4.4
     line = path_statistics(np.stack([np.linspace(0, 3, 20), np.zeros(20)], 1))
     assert line["max_curvature"] == 0 and line["smoothness"] == 0 and line["cusps"] == 0
+
+
+def test_astar_oracle_matches_reference_fixture():
+    """oracle/astar.py against tests/golden/astar.npz (recorded from the live reference's AstarTrajectoryInitializer and
+    scipy's interp1d): labelled matrix and cell path exact, trajectory bit-identical after the float32 cast."""
+    from oracle import astar as A
+    fx = U.load("astar.npz")
+    for name in [str(n) for n in fx["names"]]:
+        g = lambda k: fx[f"{name}/{k}"]                                      # noqa: E731
+        bounds, res, obs = tuple(float(b) for b in g("bounds")), float(g("resolution")), g("obstacles")
+        label = (lambda p: C.rectangle_labels(p, obs, (-0.3, 0.2, -0.3, 0.2), bounds)) if str(g("kind")) == "rectangle" else \
+            (lambda p: C.circle_labels(p, obs, 0.3, bounds))
+        xy, cells, matrix = A.initial_trajectory_xy(g("start"), g("goal"), bounds, res, label, int(g("T")))
+        assert np.array_equal(matrix, g("matrix")) and np.array_equal(cells, g("cells"))
+        assert np.array_equal(A.cells_to_points(cells, bounds, res), g("cell_points"))
+        assert np.array_equal(xy, g("trajectory")[:, :2]), name
+    # the unreachable goal returns the path to the last expanded state (jps.py:321-322), not an error
+    assert not np.array_equal(fx["disc_blocked/cells"][-1], A.point_cells(fx["disc_blocked/goal"][:2], (0, 3, 0, 3), 0.25)[::-1])
