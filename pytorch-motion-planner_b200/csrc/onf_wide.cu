@@ -917,8 +917,8 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
     extern __shared__ __align__(128) unsigned char smem[];
     unsigned char *act = smem, *ring = smem + WC_ACT;
     uint64_t *bars = reinterpret_cast<uint64_t *>(ring + WC_STAGES * WC_STAGE);
-    uint64_t *full = bars, *empty = bars + WC_STAGES, *tfull = bars + 2 * WC_STAGES, *act_ready = tfull + 1;
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(act_ready + 1);
+    uint64_t *full = bars, *empty = bars + WC_STAGES, *tfull = bars + 2 * WC_STAGES, *act_ready = tfull + 1;   // act_ready[4]: one per 64-column group
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(act_ready + 4);
     float *fm = reinterpret_cast<float *>(ring + WC_STAGES * WC_STAGE + 256);
     float *s_pa = fm, *s_pb = fm + 256, *s_pc = fm + 512, *svecA = fm + 768, *svecB = fm + 1024, *zpart = fm + 1280, *red = fm + 1280 + WC_PARTS * 128;
     const WideDims &w = a.w;
@@ -935,10 +935,10 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
     if (threadIdx.x == 0) {
         for (int s = 0; s < WC_STAGES; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, CL); }
         mbar_init(tfull, 1);
-        mbar_init(act_ready, WC_EPI / 32);
+        for (int g = 0; g < 4; ++g) mbar_init(act_ready + g, WC_EPI / 32);
         fence_mbar_init();
     }
-    if (warp == 1) tmem_alloc(tmem_slot, 256);
+    if (warp == 1) tmem_alloc(tmem_slot, 512);         // two 256-column accumulators, alternating by phase
     fence_before_sync();
     __syncthreads();
     if (CL > 1) cluster_sync_all();                    // every CTA's barriers exist before anyone multicasts into them
@@ -978,15 +978,20 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
         // ---------------- MMA issue ----------------
         const uint32_t lead = elect_one();
         const uint32_t act_u = smem_u32(act), ring_u = smem_u32(ring);
-        uint32_t it = 0, gph = 0;
+        uint32_t it = 0, gph = 0, apar = 0;                 // apar: phase parity bit of each act_ready barrier
         for (int item = cid; item < items; item += ncl) {
             for (int ph = 0; ph < nph; ++ph, ++gph) {
                 bool dg; int l, K, N;
                 chain_phase(w, ph, dg, l, K, N);
-                mbar_wait(act_ready, gph & 1);          // A operand written, accumulator drained
-                fence_after_sync();
                 const uint32_t idesc = instr_desc_bf16(128, N, 0, dg ? 1 : 0);
+                const uint32_t acc = tmem + (gph & 1) * 256;   // the epilogue may still be reading the other accumulator
                 for (int st = 0; st < K / 16; ++st, ++it) {
+                    if ((st & 3) == 0) {                    // the 64 A-operand columns of this K group have been written
+                        const int g = st >> 2;
+                        mbar_wait(act_ready + g, (apar >> g) & 1);
+                        apar ^= 1u << g;
+                        fence_after_sync();
+                    }
                     const int s = it % WC_STAGES;
                     mbar_wait(full + s, (it / WC_STAGES) & 1);
                     fence_after_sync();
@@ -995,7 +1000,7 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
                     const uint64_t al = desc_kmajor(act_u + WC_ACT_PLANE + st * 4096, 128, 2048);
                     const uint64_t bh = dg ? desc_mnmajor(Bs, N * 16, 128) : desc_kmajor(Bs, 128, N * 16);
                     const uint64_t bl = dg ? desc_mnmajor(Bs + WC_STAGE / 2, N * 16, 128) : desc_kmajor(Bs + WC_STAGE / 2, 128, N * 16);
-                    wmma3(tmem, ah, al, bh, bl, idesc, st > 0, lead);
+                    wmma3(acc, ah, al, bh, bl, idesc, st > 0, lead);
                     if (CL == 1) mma_commit(empty + s, lead);
                     else mma_commit_multicast(empty + s, cmask, lead);
                 }
@@ -1005,16 +1010,15 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
     } else {
         // ---------------- epilogue warps: encoding, bias/ReLU, logit, dL/dz, masks, encoding backward ----------------
         const int et = threadIdx.x - 64, q = warp & 3, part = (warp - 2) >> 2, row = q * 32 + lane, r32 = row & 31;
-        // this warp's share of `nch` 16-column chunks
-        auto chunk_lo = [&](int nch) { return (nch * part) / WC_PARTS; };
-        auto chunk_hi = [&](int nch) { return (nch * (part + 1)) / WC_PARTS; };
         const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16);
         const bool wgrad = a.want_wgrad != 0;
-        auto signal_act_ready = [&]() {
+        // the epilogue warps sweep the columns in order (chunk = 16 columns, group = 4 chunks, one chunk per `part`): as soon
+        // as a 64-column group of the next A operand is in shared memory the MMA warp starts the next phase's K steps on it
+        auto signal_group = [&](int g) {
             fence_proxy_async();
             fence_before_sync();
             __syncwarp();
-            if (lane == 0) mbar_arrive(act_ready);
+            if (lane == 0) mbar_arrive(act_ready + g);
         };
         // store 16 columns (col0..col0+15) of this thread's point: A operand in shared memory and/or 32-point tile in global
         auto store16 = [&](const float *v, int col0, bool to_act, unsigned char *gt, int C) {
@@ -1084,21 +1088,24 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
             // ---- encoding (onf_model.py:37-46) -> A operand of layer 0, skip term of the logit ----
             float zp = 0.f;
             {
-                const int nch = w.K1 / 16, c_lo = chunk_lo(nch), c_hi = chunk_hi(nch);
+                const int nch = w.K1 / 16;
                 unsigned char *Et = (bwd && wgrad && live) ? a.E + t32 * w.K1 * 128 : nullptr;
-                for (int ch = c_lo; ch < c_hi; ++ch) {
-                    float e[16];
+                for (int g = 0; 4 * g < nch; ++g) {
+                    const int ch = 4 * g + part;
+                    if (ch < nch) {
+                        float e[16];
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) {
-                        const int f = ch * 16 + i;
-                        const float arg = fmaf(f < L.f_pos ? u1 : th, s_pb[f], fmaf(u0, s_pa[f], s_pc[f]));
-                        e[i] = (valid && f < L.f_in) ? __sinf(w_reduce_2pi(arg)) : 0.f;
-                        zp = fmaf(e[i], svecA[f], zp);
+                        for (int i = 0; i < 16; ++i) {
+                            const int f = ch * 16 + i;
+                            const float arg = fmaf(f < L.f_pos ? u1 : th, s_pb[f], fmaf(u0, s_pa[f], s_pc[f]));
+                            e[i] = (valid && f < L.f_in) ? __sinf(w_reduce_2pi(arg)) : 0.f;
+                            zp = fmaf(e[i], svecA[f], zp);
+                        }
+                        store16(e, ch * 16, true, Et, w.K1);
                     }
-                    store16(e, ch * 16, true, Et, w.K1);
+                    signal_group(g);
                 }
             }
-            signal_act_ready();
             float gb = 0.f;
             for (int ph = 0; ph < nph; ++ph, ++gph) {
                 bool dg; int l, K, N;
@@ -1113,22 +1120,28 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
                     for (int c = et; c < N; c += WC_EPI) svecA[c] = c < L.f_in ? W[L.off_w_out + w.H + c] : 0.f;
                 }
                 epi_bar();
-                const int nch = N / 16, c_lo = chunk_lo(nch), c_hi = chunk_hi(nch);
+                const int nch = N / 16;
+                const bool more = ph + 1 < nph;             // a next phase consumes what this one writes to shared memory
+                const uint32_t tacc = taddr + (gph & 1) * 256;
                 mbar_wait(tfull, gph & 1);
                 fence_after_sync();
                 if (!dg) {
                     const bool last = l == w.L - 1;
                     unsigned char *Ht = (bwd && live) ? a.H[l] + t32 * w.Hp * 128 : nullptr;     // masks (and wgrad operands)
-                    for (int ch = c_lo; ch < c_hi; ++ch) {
-                        float v[16];
-                        tmem_ld16(taddr + ch * 16, v);
+                    for (int g = 0; 4 * g < nch; ++g) {
+                        const int ch = 4 * g + part;
+                        if (ch < nch) {
+                            float v[16];
+                            tmem_ld16(tacc + ch * 16, v);
 #pragma unroll
-                        for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i] + svecA[ch * 16 + i], 0.f);
-                        if (last) {
+                            for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i] + svecA[ch * 16 + i], 0.f);
+                            if (last) {
 #pragma unroll
-                            for (int i = 0; i < 16; ++i) zp = fmaf(v[i], svecB[ch * 16 + i], zp);
+                                for (int i = 0; i < 16; ++i) zp = fmaf(v[i], svecB[ch * 16 + i], zp);
+                            }
+                            store16(v, ch * 16, !last, last ? nullptr : Ht, w.Hp);      // H_L itself is not needed again
                         }
-                        store16(v, ch * 16, !last, last ? nullptr : Ht, w.Hp);      // H_L itself is not needed again
+                        if (!last && more) signal_group(g);
                     }
                     if (last) {
                         // ---- logit (onf_model.py:48-49), dL/dz ----
@@ -1159,19 +1172,25 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
                             }
                             // second pass over the accumulator: gradient w.r.t. the last hidden layer's pre-activation
                             unsigned char *Gt = (wgrad && live) ? a.G[l] + t32 * w.Hp * 128 : nullptr;
-                            for (int ch = c_lo; ch < c_hi; ++ch) {
-                                float v[16], t[16];
-                                tmem_ld16(taddr + ch * 16, v);
+                            for (int g = 0; 4 * g < nch; ++g) {
+                                const int ch = 4 * g + part;
+                                if (ch < nch) {
+                                    float v[16], t[16];
+                                    tmem_ld16(tacc + ch * 16, v);
 #pragma unroll
-                                for (int i = 0; i < 16; ++i) {
-                                    const float h = fmaxf(v[i] + svecA[ch * 16 + i], 0.f);
-                                    t[i] = gb * h;                                        // d w_out[:H] = sum_pt gbar * H_L
-                                    v[i] = h > 0.f ? gb * svecB[ch * 16 + i] : 0.f;
-                                }
-                                store16(v, ch * 16, true, Gt, w.Hp);
-                                if (wgrad) {
-                                    put_colsum(t, aux_dw3h(w) + ch * 16);
-                                    put_colsum(v, aux_db(w, l) + ch * 16);                // d b_L = sum_pt G_L
+                                    for (int i = 0; i < 16; ++i) {
+                                        const float h = fmaxf(v[i] + svecA[ch * 16 + i], 0.f);
+                                        t[i] = gb * h;                                        // d w_out[:H] = sum_pt gbar * H_L
+                                        v[i] = h > 0.f ? gb * svecB[ch * 16 + i] : 0.f;
+                                    }
+                                    store16(v, ch * 16, true, Gt, w.Hp);
+                                    if (more) signal_group(g);                            // (before the column sums: MMA starts earlier)
+                                    if (wgrad) {
+                                        put_colsum(t, aux_dw3h(w) + ch * 16);
+                                        put_colsum(v, aux_db(w, l) + ch * 16);                // d b_L = sum_pt G_L
+                                    }
+                                } else if (more) {
+                                    signal_group(g);
                                 }
                             }
                         }
@@ -1180,26 +1199,32 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
                     // ---- input gradient of layer l -> ReLU mask of layer l-1 -> A operand of the next phase ----
                     const unsigned char *Mt = a.H[l - 1] + t32 * w.Hp * 128;        // dummy rows read tile 0: harmless
                     unsigned char *Gt = (wgrad && live) ? a.G[l - 1] + t32 * w.Hp * 128 : nullptr;
-                    for (int ch = c_lo; ch < c_hi; ++ch) {
-                        float v[16];
-                        const uint4 m0 = *reinterpret_cast<const uint4 *>(Mt + (ch * 2) * 512 + r32 * 16);
-                        const uint4 m1 = *reinterpret_cast<const uint4 *>(Mt + (ch * 2 + 1) * 512 + r32 * 16);
-                        tmem_ld16(taddr + ch * 16, v);
-                        const uint32_t mw[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+                    for (int g = 0; 4 * g < nch; ++g) {
+                        const int ch = 4 * g + part;
+                        if (ch < nch) {
+                            float v[16];
+                            const uint4 m0 = *reinterpret_cast<const uint4 *>(Mt + (ch * 2) * 512 + r32 * 16);
+                            const uint4 m1 = *reinterpret_cast<const uint4 *>(Mt + (ch * 2 + 1) * 512 + r32 * 16);
+                            tmem_ld16(tacc + ch * 16, v);
+                            const uint32_t mw[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
 #pragma unroll
-                        for (int i = 0; i < 16; ++i) {
-                            const uint32_t bits = (mw[i >> 1] >> ((i & 1) * 16)) & 0x7FFFu;
-                            v[i] = bits != 0 ? v[i] : 0.f;
+                            for (int i = 0; i < 16; ++i) {
+                                const uint32_t bits = (mw[i >> 1] >> ((i & 1) * 16)) & 0x7FFFu;
+                                v[i] = bits != 0 ? v[i] : 0.f;
+                            }
+                            store16(v, ch * 16, true, Gt, w.Hp);
+                            if (more) signal_group(g);
+                            if (wgrad) put_colsum(v, aux_db(w, l - 1) + ch * 16);             // d b_{l-1} = sum_pt G_{l-1}
+                        } else if (more) {
+                            signal_group(g);
                         }
-                        store16(v, ch * 16, true, Gt, w.Hp);
-                        if (wgrad) put_colsum(v, aux_db(w, l - 1) + ch * 16);             // d b_{l-1} = sum_pt G_{l-1}
                     }
                 } else {
                     // ---- dL/dE (+ skip connection) -> encoding backward: dL/d(arg) for the encoder gradients, dL/dx ----
                     float g0 = 0.f, g1 = 0.f, g2 = 0.f;
-                    for (int ch = c_lo; ch < c_hi; ++ch) {
+                    for (int ch = part; ch < nch; ch += WC_PARTS) {
                         float v[16], te[16], t0[16], t1[16];
-                        tmem_ld16(taddr + ch * 16, v);
+                        tmem_ld16(tacc + ch * 16, v);
 #pragma unroll
                         for (int i = 0; i < 16; ++i) {
                             const int f = ch * 16 + i;
@@ -1243,15 +1268,14 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
                         }
                     }
                 }
-                if (ph + 1 < nph) signal_act_ready();
-                else fence_before_sync();
+                if (!more) fence_before_sync();
             }
         }
     }
     fence_before_sync();
     __syncthreads();
     if (CL > 1) cluster_sync_all();                    // no peer may still multicast into / arrive on this CTA's shared memory
-    if (warp == 1) tmem_dealloc(tmem, 256);
+    if (warp == 1) tmem_dealloc(tmem, 512);
 }
 
 // ---- fixed-order sum of the aux partials over (row block, lane quarter) -> gradient blob --------------------------------
