@@ -903,6 +903,14 @@ __device__ __forceinline__ float wcolsum16(float (&v)[16], int lane) {
     return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 1);
 }
 
+// optional phase trace of the chain kernel (build with -DNFOPP_TC_TRACE: `make trace`; scripts/wide_trace.py)
+#ifdef NFOPP_TC_TRACE
+__device__ long long g_wc_trace[96];
+#define WC_TRACE(cond, slot) do { if ((cond) && blockIdx.x == 0 && (slot) < 96) g_wc_trace[(slot)] = clock64(); } while (0)
+#else
+#define WC_TRACE(cond, slot) do { } while (0)
+#endif
+
 __device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, %0;" ::"n"(WC_EPI) : "memory"); }
 
 // phase ph of an item: forward layer ph (ph < L) or input-gradient layer 2L-1-ph
@@ -991,6 +999,7 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
                         mbar_wait(act_ready + g, (apar >> g) & 1);
                         apar ^= 1u << g;
                         fence_after_sync();
+                        WC_TRACE(lane == 0 && item == cid + 2 * ncl && g == 0, 64 + 2 * ph);
                     }
                     const int s = it % WC_STAGES;
                     mbar_wait(full + s, (it / WC_STAGES) & 1);
@@ -1005,6 +1014,7 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
                     else mma_commit_multicast(empty + s, cmask, lead);
                 }
                 mma_commit(tfull, lead);
+                WC_TRACE(lane == 0 && item == cid + 2 * ncl, 65 + 2 * ph);
             }
         }
     } else {
@@ -1110,6 +1120,8 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
             for (int ph = 0; ph < nph; ++ph, ++gph) {
                 bool dg; int l, K, N;
                 chain_phase(w, ph, dg, l, K, N);
+                const bool tr = threadIdx.x == 64 && item == cid + 2 * ncl;
+                WC_TRACE(tr, 8 * ph);
                 // ---- per-phase vectors ----
                 epi_bar();                                  // previous phase's vectors are dead
                 if (!dg) {
@@ -1123,8 +1135,10 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
                 const int nch = N / 16;
                 const bool more = ph + 1 < nph;             // a next phase consumes what this one writes to shared memory
                 const uint32_t tacc = taddr + (gph & 1) * 256;
+                WC_TRACE(tr, 8 * ph + 1);
                 mbar_wait(tfull, gph & 1);
                 fence_after_sync();
+                WC_TRACE(tr, 8 * ph + 2);
                 if (!dg) {
                     const bool last = l == w.L - 1;
                     unsigned char *Ht = (bwd && live) ? a.H[l] + t32 * w.Hp * 128 : nullptr;     // masks (and wgrad operands)
@@ -1142,6 +1156,7 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
                             store16(v, ch * 16, !last, last ? nullptr : Ht, w.Hp);      // H_L itself is not needed again
                         }
                         if (!last && more) signal_group(g);
+                        WC_TRACE(tr, 8 * ph + 3 + g);
                     }
                     if (last) {
                         // ---- logit (onf_model.py:48-49), dL/dz ----
@@ -1218,6 +1233,7 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
                         } else if (more) {
                             signal_group(g);
                         }
+                        WC_TRACE(tr, 8 * ph + 3 + g);
                     }
                 } else {
                     // ---- dL/dE (+ skip connection) -> encoding backward: dL/d(arg) for the encoder gradients, dL/dx ----
@@ -1268,6 +1284,7 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
                         }
                     }
                 }
+                WC_TRACE(tr, 8 * ph + 7);
                 if (!more) fence_before_sync();
             }
         }
@@ -1850,3 +1867,9 @@ int onf_wide_launch(const OnfArgs &o, const OnfWideExtra &x, int P, cudaStream_t
 }
 
 }  // namespace nfopp
+
+#ifdef NFOPP_TC_TRACE
+extern "C" int nfopp_debug_wc_trace(long long *host_out) {
+    return (int)cudaMemcpyFromSymbol(host_out, nfopp::g_wc_trace, sizeof(nfopp::g_wc_trace));
+}
+#endif
