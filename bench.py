@@ -307,7 +307,15 @@ def run_ours(args):
         counts = torch.tensor([float(res["solved"].sum()), float(res["steps_run"])], device="cuda")
         if world > 1:
             dist.all_reduce(counts, op=dist.ReduceOp.SUM)
-        solve = {"problems": P * world, "solved": int(counts[0]), "seconds": ms_solve * 1e-3,
+        # per-plan statistics of the solved paths (BenchmarkAdapter.cpp:68-135), outside the timed region, rank 0's shard
+        quality = None
+        if bool(res["solved"].any()):
+            solver.engine["traj"].copy_(res["paths"][:, 1:-1])
+            st = solver.path_statistics()
+            sel = res["solved"]
+            quality = {k: float(v[sel].mean()) for k, v in st.items()}
+            quality["of"] = "mean over rank 0's solved problems"
+        solve = {"problems": P * world, "solved": int(counts[0]), "seconds": ms_solve * 1e-3, "path_quality": quality,
                  "solved_per_s": float(counts[0]) / (ms_solve * 1e-3), "steps_run_per_gpu": float(counts[1]) / world,
                  "rule": "run_bench_mr.py: max 1000 / min 200 iterations, evaluate every 50 (4 poses per segment through the "
                          "collision checker), stop at a collision-free path that is no shorter than the best"}

@@ -610,6 +610,37 @@ def test_astar_initialiser_matches_reference():
         eng.close()
 
 
+def test_astar_initialiser_edge_cases():
+    """start and goal in the same cell (A* path = one cell, a 3-point spline), and an end point outside the checker
+    boundaries (the reference indexes the matrix out of range: IndexError here, before any launch)."""
+    from _gpu_util import engine_config
+    from nfopp_b200.engine import PlannerEngine
+    from oracle import astar as A
+    from oracle import checkers as OC
+    lock = U.load("lockstep_car.npz")
+    bounds, res, T = (0.0, 3.0, 0.0, 3.0), 0.5, 12
+    obs = np.array([[1.5, 1.5]])
+    cfg = engine_config("car", lock, rng_mode="philox", problems=2, trajectory_length=T, checker="circle",
+                        checker_bounds=bounds, border=bounds)
+    eng = PlannerEngine(cfg)
+    eng.set_obstacles(obs)
+    starts = np.array([[0.55, 0.55, 0.0], [0.2, 2.8, 1.0]], dtype=np.float32)
+    goals = np.array([[0.9, 0.8, 0.5], [2.8, 0.2, -1.0]], dtype=np.float32)
+    eng.set_endpoints(starts, goals)
+    eng.init_trajectories()
+    n_cells = eng.init_astar(res).cpu().numpy()
+    traj = eng["traj"].cpu().numpy()
+    label = lambda p: OC.circle_labels(p, obs, 0.3, bounds)                  # noqa: E731
+    for p in range(2):
+        xy, cells, _ = A.initial_trajectory_xy(starts[p], goals[p], bounds, res, label, T)
+        assert n_cells[p] == len(cells) and np.abs(traj[p, :, :2] - xy).max() <= 2e-6, p
+    assert n_cells[0] == 1
+    eng.set_endpoints(starts, np.array([[3.7, 0.8, 0.5], [2.8, 0.2, -1.0]], dtype=np.float32))
+    with pytest.raises(IndexError):
+        eng.init_astar(res)
+    eng.close()
+
+
 def test_astar_initialiser_through_the_factory_and_on_a_grid():
     """PlannerFactory resolves AstarTrajectoryInitializer by name (scripts/run_bench_mr.py:23-26); BatchedPlanner.init with
     astar_resolution on occupancy grids gives collision-free cell paths where the straight line collides."""
