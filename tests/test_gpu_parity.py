@@ -676,3 +676,66 @@ def test_astar_initialiser_through_the_factory_and_on_a_grid():
     path = planner.get_path()
     assert path.shape == (102, 3)
     assert np.abs(path[1:-1, :2] - fx["disc_coarse/trajectory"][:, :2]).max() <= 2e-6
+
+
+# ---------------------------------------------------------------------------------------- BASELINE's full sizes
+def _full_size_checks(bp, label_problem, steps, sample_every):
+    """size-independent properties of a running batch: every training label of every problem equals the reference
+    checker's on the very poses the engine labelled (bit-exact), training sets are complete and finite, the resampled
+    replay buffer keeps its capacity, paths stay finite, no problem raised a status flag."""
+    eng = bp.engine
+    bp.step(steps)
+    torch.cuda.synchronize()
+    P = eng.config.problems
+    n = eng["train_n"].cpu().numpy()
+    pos = eng["train_pos"].cpu().numpy()
+    y = eng["train_y"].cpu().numpy() > 0.5
+    assert (n == n[0]).all() and n[0] == pos.shape[1]                        # 99 coarse + 100 replay + 10 uniform
+    assert np.isfinite(pos).all()
+    flips = 0
+    for p in range(0, P, sample_every):
+        flips += int((label_problem(p, pos[p, :n[p]]) != y[p, :n[p]]).sum())
+    assert flips == 0, f"{flips} collision labels differ from the reference checker"
+    assert (eng["buf_n"].cpu().numpy() == eng.config.collision_point_count).all()
+    assert bool(torch.isfinite(bp.paths()).all()) and int(np.abs(bp.status()).max()) == 0
+    return y.mean()
+
+
+def test_full_size_corridor_batch_1024_problems():
+    """BASELINE configs[1] at its full size (1024 corridor problems, one obstacle set each): the properties above for every
+    problem, plus batch-size independence - problems 0..7 of the 1024 evolve bit-identically in a batch of 8."""
+    from nfopp_b200.batched import BatchedPlanner, corridor_config, init_onf_weights
+    from nfopp_b200.test_environment_builder import TestEnvironmentBuilder as B
+    from oracle import checkers as OC
+    P = 1024
+    starts, goals, _, obstacles = B.make_corridor_batch(P, seed=0)
+    cfg = corridor_config(P, seed=21)
+    w0 = init_onf_weights(cfg.onf, P, True, 99, "cuda")
+    bp = BatchedPlanner(cfg)
+    bp.init(starts, goals, obstacles=obstacles, onf_weights=w0)
+    frac = _full_size_checks(bp, lambda p, q: OC.circle_labels(q, np.asarray(obstacles[p]), cfg.robot_radius, cfg.checker_bounds),
+                             steps=12, sample_every=1)
+    assert 0.0 < frac < 1.0                                                  # both classes present
+    small = BatchedPlanner(corridor_config(8, seed=21))
+    small.init(starts[:8], goals[:8], obstacles=obstacles[:8], onf_weights=w0[:8])
+    small.step(12)
+    torch.cuda.synchronize()
+    for name in ("traj", "onf_w", "lam", "mu"):
+        assert torch.equal(small.engine[name], bp.engine[name][:8]), name
+
+
+def test_full_size_forest_batch_16384_problems():
+    """BASELINE configs[2] at its full size: 16 384 random-obstacle worlds (one 100 x 100 occupancy grid each), each with its
+    own ONF; labels of a 1-in-64 sample of the problems checked bit-exact against the reference's grid checker."""
+    from nfopp_b200.batched import BatchedPlanner, forest_config
+    from nfopp_b200.test_environment_builder import TestEnvironmentBuilder as B
+    from oracle import checkers as OC
+    P = 16384
+    starts, goals, _, grids, _, cell = B.make_random_grid_batch(P, seed=0)
+    cfg = forest_config(P, cell=cell, seed=5)
+    bp = BatchedPlanner(cfg)
+    bp.init(starts, goals, grids=grids)
+    _full_size_checks(bp, lambda p, q: OC.grid_labels(q, np.asarray(grids[p]), 0.0, 0.0, cfg.grid_cell, cfg.checker_bounds),
+                      steps=6, sample_every=64)
+    w = bp.engine["onf_w"]
+    assert not torch.equal(w[0], w[1]) and bool(torch.isfinite(w).all())
