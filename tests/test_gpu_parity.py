@@ -739,3 +739,46 @@ def test_full_size_forest_batch_16384_problems():
                       steps=6, sample_every=64)
     w = bp.engine["onf_w"]
     assert not torch.equal(w[0], w[1]) and bool(torch.isfinite(w).all())
+
+
+def test_full_size_wide_onf_linearity_and_permutation():
+    """BASELINE configs[4] shape (4 x 256 hidden, 2^20 points in 16 weight sets): size-independent properties of the
+    tensor-core ONF - the backward pass is linear in the upstream gradient (doubling dL/dz doubles every gradient bit for
+    bit: powers of two pass through the bf16 hi/lo split exactly), logits follow a permutation of the points exactly and
+    the weight gradient is permutation-invariant up to summation order."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "scripts"))
+    import onf_sweep
+    from nfopp_b200 import _lib as L
+    from nfopp_b200.engine import OnfSpec
+    P, n, H, layers, impl = 16, 65536, 256, 4, 3
+    gen = torch.Generator().manual_seed(3)
+    cc = OnfSpec(0.0, 1.0, True, True, H, layers).to_c()
+    w8, lay = onf_sweep.init_weights(cc, 8, gen)
+    w = w8.repeat(2, 1)[:P].contiguous().cuda()
+    x = torch.rand(P, n, 3, generator=gen)
+    x[..., :2] *= 3.0
+    x[..., 2] *= 6.2831853
+    x = x.cuda()
+    gz = (torch.randn(P, n, generator=gen) * 1e-3).cuda()
+    lib, s = L.lib(), L.stream_ptr()
+    scratch = L.onf_scratch(cc, P, impl, "cuda", n, True)
+
+    def run(xx, gg):
+        z = torch.zeros(P, n, device="cuda")
+        gx = torch.zeros(P, n, 3, device="cuda")
+        gw = torch.zeros(P, lay.n_params, device="cuda")
+        L.check(lib.nfopp_onf_backward(C.byref(cc), L.ptr(w), L.ptr(xx), None, P, n, 0, L.ptr(gg), None, 0.0, 1.0, L.ptr(z),
+                                       L.ptr(gx), L.ptr(gw), impl, L.ptr(scratch), s))
+        torch.cuda.synchronize()
+        return z, gx, gw
+
+    z1, gx1, gw1 = run(x, gz)
+    z2, gx2, gw2 = run(x, 2 * gz)
+    assert bool(torch.isfinite(gw1).all()) and float(gw1.abs().max()) > 0
+    assert torch.equal(z1, z2) and torch.equal(gx2, 2 * gx1) and torch.equal(gw2, 2 * gw1)
+    perm = torch.randperm(n, generator=gen).cuda()
+    z3, gx3, gw3 = run(x[:, perm].contiguous(), gz[:, perm].contiguous())
+    assert torch.equal(z3, z1[:, perm]) and torch.equal(gx3, gx1[:, perm])
+    assert float((gw3 - gw1).abs().max()) <= 1e-5 * float(gw1.abs().max())
