@@ -59,7 +59,8 @@ def workload_config(problems, onf_impl="auto", workload="corridor"):
         ws = "ONF w/m/v/grad fp32 + operand copies (5 MB per problem) + activation tiles"
     cfg.update({"problems_per_gpu": problems, "trajectory_length": 100, "samples_per_step": 209,
                 "rng": "on-device Philox4x32-10", "onf_impl": impl if tensor else "fma (CUDA-core fp32)",
-                "launch": "one CUDA graph per step",
+                "launch": "one CUDA graph per step" + ("" if workload == "gridmap-wide" else
+                                                       ", two lanes (independent problem ranges on parallel streams inside the graph)"),
                 "l2": f"per-step working set ({ws}) exceeds the 126 MB L2"})
     return cfg
 

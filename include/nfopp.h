@@ -234,6 +234,11 @@ int nfopp_engine_init_astar(nfopp_engine *e, int x_cells, int y_cells, double re
  * obstacle of the engine's checker (disc / box / occupied cell within +-clearing_window_cells / boundary), 0 in collision. */
 int nfopp_engine_path_statistics(nfopp_engine *e, double cusp_angle_threshold, int clearing_window_cells,
                                  float *stats_dev, void *stream);
+/* Lanes of the graphed step (default 1): the problems are split into `lanes` contiguous ranges, each enqueued on its own
+ * stream inside the step's CUDA graph (fork / join around the single counter tick).  The reference's problems are
+ * independent (one planner object each), so there is no cross-lane dependency; results are bit-identical for any lane
+ * count (per-problem RNG streams keep their global problem index).  Tensor / FMA ONF paths only. */
+int nfopp_engine_set_lanes(nfopp_engine *e, int lanes);
 /* number of kernel launches issued by this engine so far (bench.py's gpu_launches) */
 int nfopp_engine_launch_count(nfopp_engine *e, int64_t *launches);
 

@@ -254,10 +254,16 @@ struct nfopp_engine {
     StepParams host_sp;
     bool sp_dirty;
     int64_t launches;
-    int launches_per_step;
+    int launches_per_step, launches_per_step_1;     // with the current lane count / with one lane
     cudaGraph_t graph;
     cudaGraphExec_t graph_exec;
     int warm_iterations_done;
+    // lanes: the problems of a graphed step split into contiguous ranges, each enqueued on its own stream inside the one
+    // CUDA graph (fork / join): independent problems have no cross-lane dependency, so the latency-bound small kernels and
+    // the HBM-bound Adam phase of one lane overlap the tensor phases of another
+    int lanes;
+    std::vector<cudaStream_t> lane_streams;
+    std::vector<cudaEvent_t> lane_events;     // [0] fork, [l] join of lane l
 };
 
 static void host_step_params(nfopp_engine *e) {
@@ -283,6 +289,25 @@ static void add_buffer(nfopp_engine *e, const char *name, T **slot, char dtype, 
     b.dims[0] = (int32_t)d0; b.dims[1] = (int32_t)d1; b.dims[2] = (int32_t)d2;
     b.offset = 0;
     e->buffers.push_back(b);
+}
+
+// device view of problems [p0, p0 + count): every per-problem buffer advanced by p0 rows, P = count, RNG streams keep their
+// global problem index (p_base)
+static EngineDev slice_problems(const nfopp_engine *e, int p0, int count) {
+    EngineDev d = e->dev;
+    const int P = e->dev.P;
+    for (const BufferInfo &b : e->buffers) {
+        const bool shared = b.name == "step_params" || b.name == "inv_hessian_t" || b.name == "lin_s" || b.name == "onf_ws" ||
+                            (b.name == "onf_gpart" && e->impl != 1) ||
+                            ((b.name == "obstacles" || b.name == "obstacle_n" || b.name == "grid") && e->dev.env_shared);
+        if (shared || b.dims[0] != P) continue;
+        const size_t field = (size_t)(reinterpret_cast<const char *>(b.slot) - reinterpret_cast<const char *>(&e->dev));
+        void **dst = reinterpret_cast<void **>(reinterpret_cast<char *>(&d) + field);
+        *dst = static_cast<char *>(*b.slot) + (size_t)p0 * (b.bytes / P);
+    }
+    d.P = count;
+    d.p_base = e->dev.p_base + p0;
+    return d;
 }
 
 static int validate(const nfopp_planner_config *c, OnfDims *onf, int *impl) {
@@ -483,6 +508,8 @@ extern "C" int nfopp_engine_create(const nfopp_planner_config *cfg, void *worksp
                                onf_wide_launch_count(e->onf, d.P, d.NTR, true, true) + 1 +
                                onf_wide_launch_count(e->onf, d.P, d.T - 1, true, false);
     }
+    e->launches_per_step_1 = e->launches_per_step;
+    e->lanes = 1;
     *out = e;
     return NFOPP_OK;
 }
@@ -491,6 +518,8 @@ extern "C" int nfopp_engine_destroy(nfopp_engine *e) {
     if (!e) return NFOPP_OK;
     if (e->graph_exec) cudaGraphExecDestroy(e->graph_exec);
     if (e->graph) cudaGraphDestroy(e->graph);
+    for (cudaStream_t st : e->lane_streams) cudaStreamDestroy(st);
+    for (cudaEvent_t ev : e->lane_events) cudaEventDestroy(ev);
     delete e;
     return NFOPP_OK;
 }
@@ -554,22 +583,21 @@ static int ensure_packed(nfopp_engine *e, cudaStream_t s) {
 }
 
 // forward / input-gradient ONF launch of the engine through the chosen implementation
-static int engine_onf(nfopp_engine *e, OnfArgs &a, cudaStream_t s) {
-    if (e->impl == 1) return onf_fma_launch(a, e->dev.P, s);
+static int engine_onf(nfopp_engine *e, const EngineDev &d, OnfArgs &a, cudaStream_t s) {
+    if (e->impl == 1) return onf_fma_launch(a, d.P, s);
     if (e->impl == 3) {
         OnfWideExtra x{};
-        x.packed = e->dev.onf_wp; x.workspace = e->dev.onf_ws;
+        x.packed = d.onf_wp; x.workspace = d.onf_ws;
         a.sp = nullptr;
-        return onf_wide_launch(a, x, e->dev.P, s);
+        return onf_wide_launch(a, x, d.P, s);
     }
     OnfTcExtra x{};
-    x.packed = e->dev.onf_wp;
-    return onf_tc_launch(a, x, e->dev.P, s);
+    x.packed = d.onf_wp;
+    return onf_tc_launch(a, x, d.P, s);
 }
 
 // one ONF training update on train_x/train_y/train_n (nerf_opt_planner.py:83-90)
-static int enqueue_train(nfopp_engine *e, bool warm, cudaStream_t s, cudaEvent_t *ev = nullptr) {
-    const EngineDev &d = e->dev;
+static int enqueue_train(nfopp_engine *e, const EngineDev &d, bool warm, cudaStream_t s, cudaEvent_t *ev = nullptr) {
     OnfArgs a{};
     a.d = e->onf; a.weights = d.onf_w; a.x = d.train_x; a.count = d.train_n; a.n = d.NTR; a.x_stride = d.D;
     a.want_bwd = 1; a.gbar_mode = 1; a.aux = d.train_y; a.z_out = d.train_z;
@@ -624,8 +652,7 @@ static const char *const kStepKernelNames[9] = {"sample_pre", "onf_forward_candi
                                                 "onf_train_fwd_bwd", "onf_reduce_adam", "traj_pre",
                                                 "onf_path_fwd_dgrad", "traj_post", "tick"};
 
-static int enqueue_step(nfopp_engine *e, cudaStream_t s, cudaEvent_t *ev = nullptr) {
-    const EngineDev &d = e->dev;
+static int enqueue_step(nfopp_engine *e, const EngineDev &d, cudaStream_t s, cudaEvent_t *ev = nullptr, bool tick = true) {
     int rc;
     int evi = 0;
 #define NFOPP_MARK() do { if (ev) NFOPP_CHECK_CUDA(cudaEventRecord(ev[evi++], s)); } while (0)
@@ -638,14 +665,14 @@ static int enqueue_step(nfopp_engine *e, cudaStream_t s, cudaEvent_t *ev = nullp
         OnfArgs a{};
         a.d = e->onf; a.weights = d.onf_w; a.x = d.cand_x; a.count = d.cand_n; a.n = d.NC; a.x_stride = d.D;
         a.z_out = d.cand_z; a.sp = d.sp;
-        if ((rc = engine_onf(e, a, s))) return rc;
+        if ((rc = engine_onf(e, d, a, s))) return rc;
     }
     NFOPP_MARK();
     // (3) weighted resampling of the replay buffer + ground-truth labels  :126-133, :86
     if ((rc = launch_resample_label(d, 1, s))) return rc;
     NFOPP_MARK();
     // (4,5) BCE training step of the ONF: fwd+bwd per tile, then reduce + Adam   :83-90
-    if ((rc = enqueue_train(e, false, s, ev ? &ev[evi] : nullptr))) return rc;
+    if ((rc = enqueue_train(e, d, false, s, ev ? &ev[evi] : nullptr))) return rc;
     if (ev) evi += 2;
     // (6) collision sample points on the path                 :113-117 / constrained:78-83
     if ((rc = launch_traj_pre(d, s))) return rc;
@@ -657,16 +684,57 @@ static int enqueue_step(nfopp_engine *e, cudaStream_t s, cudaEvent_t *ev = nullp
         a.want_bwd = 1;
         a.gbar_mode = d.constrained ? 3 : 2; a.aux = d.path_mu; a.wc = d.collision_weight;
         a.beta = d.constrained ? d.beta : 1.f; a.z_out = d.path_z; a.gx_out = d.path_gq;
-        if ((rc = engine_onf(e, a, s))) return rc;
+        if ((rc = engine_onf(e, d, a, s))) return rc;
     }
     NFOPP_MARK();
     // (8) trajectory gradient, preconditioner, Adam, multipliers, re-parametrisation  :143-155,224-244
     if ((rc = launch_traj_post(d, s))) return rc;
     NFOPP_MARK();
     // (9) counters
-    if ((rc = launch_tick(d, false, s))) return rc;
+    if (tick && (rc = launch_tick(d, false, s))) return rc;
     NFOPP_MARK();
 #undef NFOPP_MARK
+    return NFOPP_OK;
+}
+
+// one step of all problems inside a stream capture: lanes > 1 fork the problem ranges onto the lane streams and join them
+// before the (single) counter tick
+static int enqueue_step_lanes(nfopp_engine *e, cudaStream_t s) {
+    const int L = e->lanes, P = e->dev.P;
+    if (L <= 1) return enqueue_step(e, e->dev, s);
+    int rc = NFOPP_OK;
+    NFOPP_CHECK_CUDA(cudaEventRecord(e->lane_events[0], s));
+    for (int l = 0; l < L && !rc; ++l) {
+        const int p0 = (int)((long long)P * l / L), p1 = (int)((long long)P * (l + 1) / L);
+        const EngineDev d = slice_problems(e, p0, p1 - p0);
+        cudaStream_t ls = l == 0 ? s : e->lane_streams[l];
+        if (l > 0) NFOPP_CHECK_CUDA(cudaStreamWaitEvent(ls, e->lane_events[0], 0));
+        rc = enqueue_step(e, d, ls, nullptr, false);
+        if (l > 0 && !rc) NFOPP_CHECK_CUDA(cudaEventRecord(e->lane_events[l], ls));
+    }
+    for (int l = 1; l < L; ++l) NFOPP_CHECK_CUDA(cudaStreamWaitEvent(s, e->lane_events[l], 0));   // (joins even after an error)
+    if (rc) return rc;
+    return launch_tick(e->dev, false, s);
+}
+
+extern "C" int nfopp_engine_set_lanes(nfopp_engine *e, int lanes) {
+    NFOPP_REQUIRE(e && lanes >= 1 && lanes <= 16, "set_lanes: lanes=%d", lanes);
+    NFOPP_REQUIRE(lanes == 1 || e->impl != 3, "set_lanes: the wide ONF path shares one activation workspace between its problems");
+    if (lanes > e->dev.P) lanes = e->dev.P;
+    if (lanes == e->lanes) return NFOPP_OK;
+    if (e->graph_exec) { cudaGraphExecDestroy(e->graph_exec); e->graph_exec = nullptr; }
+    if (e->graph) { cudaGraphDestroy(e->graph); e->graph = nullptr; }
+    while ((int)e->lane_streams.size() < lanes) {
+        cudaStream_t st = nullptr;
+        cudaEvent_t ev = nullptr;
+        NFOPP_CHECK_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+        NFOPP_CHECK_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+        e->lane_streams.push_back(st);
+        e->lane_events.push_back(ev);
+    }
+    e->lanes = lanes;
+    const int per_lane = e->launches_per_step_1 - 1;           // everything but the tick runs once per lane
+    e->launches_per_step = lanes > 1 ? per_lane * lanes + 1 : e->launches_per_step_1;
     return NFOPP_OK;
 }
 
@@ -679,7 +747,7 @@ extern "C" int nfopp_engine_warmup(nfopp_engine *e, int iterations, void *stream
     for (int it = 0; it < iterations; ++it) {
         if ((rc = launch_warm_sample(e->dev, 1000000 + e->warm_iterations_done, s))) return rc;
         if ((rc = launch_resample_label(e->dev, 0, s))) return rc;
-        if ((rc = enqueue_train(e, true, s))) return rc;
+        if ((rc = enqueue_train(e, e->dev, true, s))) return rc;
         if ((rc = launch_tick(e->dev, true, s))) return rc;
         e->host_sp.onf_step += 1;
         e->warm_iterations_done += 1;
@@ -698,7 +766,7 @@ extern "C" int nfopp_engine_step(nfopp_engine *e, int n_steps, int use_graph, vo
     if (use_graph && !e->graph_exec) {
         NFOPP_REQUIRE(s != nullptr, "step: CUDA-graph capture needs a non-default stream");
         NFOPP_CHECK_CUDA(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
-        rc = enqueue_step(e, s);
+        rc = enqueue_step_lanes(e, s);
         cudaError_t ce = cudaStreamEndCapture(s, &e->graph);
         if (rc) return rc;
         NFOPP_CHECK_CUDA(ce);
@@ -707,7 +775,7 @@ extern "C" int nfopp_engine_step(nfopp_engine *e, int n_steps, int use_graph, vo
     for (int it = 0; it < n_steps; ++it) {
         if (use_graph) {
             NFOPP_CHECK_CUDA(cudaGraphLaunch(e->graph_exec, s));
-        } else if ((rc = enqueue_step(e, s))) {
+        } else if ((rc = enqueue_step(e, e->dev, s))) {
             return rc;
         }
         StepParams &sp = e->host_sp;
@@ -728,7 +796,7 @@ extern "C" int nfopp_engine_profile_step(nfopp_engine *e, float *ms_out, int n_o
     if ((rc = ensure_packed(e, s))) return rc;
     cudaEvent_t ev[10];
     for (auto &x : ev) NFOPP_CHECK_CUDA(cudaEventCreate(&x));
-    rc = enqueue_step(e, s, ev);
+    rc = enqueue_step(e, e->dev, s, ev);
     if (!rc) {
         cudaError_t ce = cudaStreamSynchronize(s);
         if (ce != cudaSuccess) { set_error("profile_step: %s", cudaGetErrorString(ce)); rc = NFOPP_ERR_CUDA; }

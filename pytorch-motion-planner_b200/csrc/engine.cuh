@@ -20,6 +20,7 @@ struct StepParams {
 
 struct EngineDev {
     // configuration (by value)
+    int p_base;                            // global index of this view's problem 0 (lanes: RNG streams stay per global problem)
     int P, T, D, C, NF, NC, NTR, NW;       // C = collision_point_count, NF = random_field_points,
                                            // NC = C + T-1 (candidates), NTR = train capacity, NW = warm-up points
     int constrained, rng_mode, max_choice_u;

@@ -206,12 +206,12 @@ __global__ void __launch_bounds__(SAMPLE_THREADS) sample_pre_kernel(const Engine
             zf[2] = D == 3 ? e.var_fine_th[(size_t)p * n + i] : 0.0;
         } else {
             double u0, u1, w0, w1;
-            rng_uniform2(e.seed, p, sp.step_count, RNG_T_SAMPLE, i, &u0, &u1);
+            rng_uniform2(e.seed, e.p_base + p, sp.step_count, RNG_T_SAMPLE, i, &u0, &u1);
             t = (float)u0;
-            rng_normal2(e.seed, p, sp.step_count, RNG_COARSE, 2 * i, &zc[0], &zc[1]);
-            rng_normal2(e.seed, p, sp.step_count, RNG_COARSE, 2 * i + 1, &zc[2], &w0);
-            rng_normal2(e.seed, p, sp.step_count, RNG_FINE, 2 * i, &zf[0], &zf[1]);
-            rng_normal2(e.seed, p, sp.step_count, RNG_FINE, 2 * i + 1, &zf[2], &w1);
+            rng_normal2(e.seed, e.p_base + p, sp.step_count, RNG_COARSE, 2 * i, &zc[0], &zc[1]);
+            rng_normal2(e.seed, e.p_base + p, sp.step_count, RNG_COARSE, 2 * i + 1, &zc[2], &w0);
+            rng_normal2(e.seed, e.p_base + p, sp.step_count, RNG_FINE, 2 * i, &zf[0], &zf[1]);
+            rng_normal2(e.seed, e.p_base + p, sp.step_count, RNG_FINE, 2 * i + 1, &zf[2], &w1);
         }
         const float omt = __fsub_rn(1.f, t);
         for (int d = 0; d < D; ++d) {
@@ -239,8 +239,8 @@ __global__ void __launch_bounds__(SAMPLE_THREADS) sample_pre_kernel(const Engine
             u[2] = D == 3 ? e.var_field_th[(size_t)p * e.NF + i] : 0.0;
         } else {
             double w;
-            rng_uniform2(e.seed, p, sp.step_count, RNG_FIELD, 2 * i, &u[0], &u[1]);
-            rng_uniform2(e.seed, p, sp.step_count, RNG_FIELD, 2 * i + 1, &u[2], &w);
+            rng_uniform2(e.seed, e.p_base + p, sp.step_count, RNG_FIELD, 2 * i, &u[0], &u[1]);
+            rng_uniform2(e.seed, e.p_base + p, sp.step_count, RNG_FIELD, 2 * i + 1, &u[2], &w);
         }
         double *o = tr + (size_t)(n + new_n + i) * D;
         o[0] = __dadd_rn(e.border[0], __dmul_rn(u[0], __dsub_rn(e.border[1], e.border[0])));
@@ -266,8 +266,8 @@ __global__ void __launch_bounds__(SAMPLE_THREADS) warm_sample_kernel(const Engin
             u[2] = D == 3 ? e.var_warm_th[(size_t)p * e.NW + i] : 0.0;
         } else {
             double w;
-            rng_uniform2(e.seed, p, iteration, RNG_WARM, 2 * i, &u[0], &u[1]);
-            rng_uniform2(e.seed, p, iteration, RNG_WARM, 2 * i + 1, &u[2], &w);
+            rng_uniform2(e.seed, e.p_base + p, iteration, RNG_WARM, 2 * i, &u[0], &u[1]);
+            rng_uniform2(e.seed, e.p_base + p, iteration, RNG_WARM, 2 * i + 1, &u[2], &w);
         }
         double *o = tr + (size_t)i * D;
         o[0] = __dadd_rn(e.border[0], __dmul_rn(u[0], __dsub_rn(e.border[1], e.border[0])));
@@ -330,7 +330,7 @@ __global__ void __launch_bounds__(RESAMPLE_THREADS) resample_label_kernel(const 
             __syncthreads();
             const bool replace = total_big < C;
             UniformSource src{e.rng_mode == 1 ? e.var_choice_u + (size_t)p * e.max_choice_u : nullptr, e.max_choice_u,
-                              e.seed, (uint32_t)p, (uint32_t)sp.step_count};
+                              e.seed, (uint32_t)(e.p_base + p), (uint32_t)sp.step_count};
             int used = choice_block(sc, nc, C, replace, src);             // :131
             if (tid == 0) {
                 e.choice_used[p] = used;

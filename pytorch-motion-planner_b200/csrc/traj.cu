@@ -23,7 +23,7 @@ __global__ void __launch_bounds__(TRAJ_THREADS) traj_pre_kernel(const EngineDev 
         if (e.rng_mode == 1) {
             t = e.var_t_path[(size_t)p * n + i];
         } else {
-            uint4 r = Philox(e.seed)(i, RNG_T_PATH, sp.step_count, p);
+            uint4 r = Philox(e.seed)(i, RNG_T_PATH, sp.step_count, e.p_base + p);
             t = e.constrained ? (float)(r.x >> 8) * (1.0f / 16777216.0f)      // torch.rand float32: 24 bits
                               : (float)u53(r.x, r.y);                           // np.random.rand -> float32
         }

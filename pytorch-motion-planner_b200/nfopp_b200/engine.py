@@ -314,6 +314,11 @@ class PlannerEngine:
             else:
                 L.check(self._lib.nfopp_engine_step(self._h, int(n_steps), 0, L.stream_ptr()))
 
+    def set_lanes(self, lanes: int):
+        """Split the graphed step into `lanes` independent problem ranges on parallel streams inside the one CUDA graph
+        (bit-identical results; overlaps the small latency-bound kernels of one lane with the ONF kernels of another)."""
+        L.check(self._lib.nfopp_engine_set_lanes(self._h, int(lanes)))
+
     def profile_step(self) -> dict:
         """One un-graphed step with CUDA events between its kernels -> {kernel name: milliseconds}."""
         ms = (C.c_float * 9)()

@@ -22,7 +22,7 @@ def run(problems, lanes, steps, warmup, workload):
     pls = []
     for i in range(lanes):
         cfg, env, starts, goals, _ = B.build_workload(workload, per, i * per)
-        pl = BatchedPlanner(cfg)
+        pl = BatchedPlanner(cfg, lanes=1)
         pl.init(starts, goals, **env)
         pls.append(pl)
     lib = L.lib()
@@ -61,6 +61,21 @@ def main():
     args = ap.parse_args()
     for lanes in args.lanes:
         run(args.problems, lanes, args.steps, args.warmup, args.workload)
+    # lanes inside one engine + one CUDA graph (nfopp_engine_set_lanes)
+    for lanes in args.lanes:
+        cfg, env, starts, goals, _ = B.build_workload(args.workload, args.problems, 0)
+        pl = BatchedPlanner(cfg, lanes=lanes)
+        pl.init(starts, goals, **env)
+        pl.step(args.warmup)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        pl.step(args.steps)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / args.steps
+        print(f"{args.workload}: in-graph lanes {lanes}: {ms:.4f} ms/step  {args.problems / ms * 1e3:.0f} problem-steps/s", flush=True)
+        pl.engine.close()
 
 
 if __name__ == "__main__":

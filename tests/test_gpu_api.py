@@ -189,3 +189,28 @@ def test_batched_warm_replanning_matches_single_problem_api():
     assert np.allclose(paths[:, 0], new_starts) and np.allclose(paths[:, -1], new_goals)
     bp.step(5)
     assert np.isfinite(bp.get_path()).all()
+
+
+@pytest.mark.gpu
+def test_lanes_are_bit_identical_to_a_single_stream():
+    """nfopp_engine_set_lanes: the graphed step split into parallel problem ranges gives, bit for bit, the state of the
+    single-stream graph (per-problem RNG streams keep their global problem index) - for even and uneven splits."""
+    import torch
+    from nfopp_b200.batched import BatchedPlanner, corridor_config, init_onf_weights
+    from nfopp_b200.test_environment_builder import TestEnvironmentBuilder as B
+    P = 70
+    starts, goals, _, obstacles = B.make_corridor_batch(P, seed=4)
+    cfg = corridor_config(P, seed=8)
+    w0 = init_onf_weights(cfg.onf, P, True, 5, "cuda")
+    states = []
+    for lanes in (1, 2, 3):
+        bp = BatchedPlanner(cfg, lanes=lanes)
+        bp.init(starts, goals, obstacles=obstacles, onf_weights=w0)
+        bp.step(14)
+        torch.cuda.synchronize()
+        assert bp.engine.counter("step_count") == 14
+        states.append({k: bp.engine[k].clone() for k in ("traj", "onf_w", "onf_m", "lam", "mu", "buf_pos", "train_y")})
+        bp.engine.close()
+    for st in states[1:]:
+        for k, v in st.items():
+            assert torch.equal(v, states[0][k]), k
