@@ -237,7 +237,8 @@ int nfopp_engine_path_statistics(nfopp_engine *e, double cusp_angle_threshold, i
 /* Lanes of the graphed step (default 1): the problems are split into `lanes` contiguous ranges, each enqueued on its own
  * stream inside the step's CUDA graph (fork / join around the single counter tick).  The reference's problems are
  * independent (one planner object each), so there is no cross-lane dependency; results are bit-identical for any lane
- * count (per-problem RNG streams keep their global problem index).  Tensor / FMA ONF paths only. */
+ * count (per-problem RNG streams keep their global problem index; on the wide ONF path every lane takes its own slice of
+ * the activation workspace and the call fails if the slices do not fit). */
 int nfopp_engine_set_lanes(nfopp_engine *e, int lanes);
 /* number of kernel launches issued by this engine so far (bench.py's gpu_launches) */
 int nfopp_engine_launch_count(nfopp_engine *e, int64_t *launches);

@@ -264,6 +264,7 @@ struct nfopp_engine {
     int lanes;
     std::vector<cudaStream_t> lane_streams;
     std::vector<cudaEvent_t> lane_events;     // [0] fork, [l] join of lane l
+    size_t lane_ws_stride;                    // wide path: bytes between the lanes' activation workspaces
 };
 
 static void host_step_params(nfopp_engine *e) {
@@ -291,14 +292,23 @@ static void add_buffer(nfopp_engine *e, const char *name, T **slot, char dtype, 
     e->buffers.push_back(b);
 }
 
+// kernel launches of one step over P problems (incl. the counter tick)
+static int step_launches(const nfopp_engine *e, int P) {
+    if (e->impl != 3) return e->impl == 2 ? 8 : 9;
+    // 5 planner kernels + candidates forward + train (backward, Adam + re-pack) + path forward/input-gradient
+    const EngineDev &d = e->dev;
+    return 5 + onf_wide_launch_count(e->onf, P, d.NC, false, false) + onf_wide_launch_count(e->onf, P, d.NTR, true, true) + 1 +
+           onf_wide_launch_count(e->onf, P, d.T - 1, true, false);
+}
+
 // device view of problems [p0, p0 + count): every per-problem buffer advanced by p0 rows, P = count, RNG streams keep their
 // global problem index (p_base)
-static EngineDev slice_problems(const nfopp_engine *e, int p0, int count) {
+static EngineDev slice_problems(const nfopp_engine *e, int p0, int count, int lane) {
     EngineDev d = e->dev;
     const int P = e->dev.P;
     for (const BufferInfo &b : e->buffers) {
         const bool shared = b.name == "step_params" || b.name == "inv_hessian_t" || b.name == "lin_s" || b.name == "onf_ws" ||
-                            (b.name == "onf_gpart" && e->impl != 1) ||
+                            (b.name == "onf_gpart" && e->impl == 2) ||
                             ((b.name == "obstacles" || b.name == "obstacle_n" || b.name == "grid") && e->dev.env_shared);
         if (shared || b.dims[0] != P) continue;
         const size_t field = (size_t)(reinterpret_cast<const char *>(b.slot) - reinterpret_cast<const char *>(&e->dev));
@@ -307,6 +317,7 @@ static EngineDev slice_problems(const nfopp_engine *e, int p0, int count) {
     }
     d.P = count;
     d.p_base = e->dev.p_base + p0;
+    if (e->impl == 3) d.onf_ws = e->dev.onf_ws + (size_t)lane * e->lane_ws_stride;   // wide path: one activation workspace per lane
     return d;
 }
 
@@ -501,13 +512,7 @@ extern "C" int nfopp_engine_create(const nfopp_planner_config *cfg, void *worksp
     e->host_sp = StepParams{};
     e->sp_dirty = true;
     e->pack_dirty = true;
-    e->launches_per_step = e->impl == 2 ? 8 : 9;
-    if (e->impl == 3) {     // 5 planner kernels + candidates forward + train (backward, Adam + re-pack) + path forward/input-gradient
-        const EngineDev &d = e->dev;
-        e->launches_per_step = 5 + onf_wide_launch_count(e->onf, d.P, d.NC, false, false) +
-                               onf_wide_launch_count(e->onf, d.P, d.NTR, true, true) + 1 +
-                               onf_wide_launch_count(e->onf, d.P, d.T - 1, true, false);
-    }
+    e->launches_per_step = step_launches(e, e->dev.P);
     e->launches_per_step_1 = e->launches_per_step;
     e->lanes = 1;
     *out = e;
@@ -706,7 +711,7 @@ static int enqueue_step_lanes(nfopp_engine *e, cudaStream_t s) {
     NFOPP_CHECK_CUDA(cudaEventRecord(e->lane_events[0], s));
     for (int l = 0; l < L && !rc; ++l) {
         const int p0 = (int)((long long)P * l / L), p1 = (int)((long long)P * (l + 1) / L);
-        const EngineDev d = slice_problems(e, p0, p1 - p0);
+        const EngineDev d = slice_problems(e, p0, p1 - p0, l);
         cudaStream_t ls = l == 0 ? s : e->lane_streams[l];
         if (l > 0) NFOPP_CHECK_CUDA(cudaStreamWaitEvent(ls, e->lane_events[0], 0));
         rc = enqueue_step(e, d, ls, nullptr, false);
@@ -719,9 +724,21 @@ static int enqueue_step_lanes(nfopp_engine *e, cudaStream_t s) {
 
 extern "C" int nfopp_engine_set_lanes(nfopp_engine *e, int lanes) {
     NFOPP_REQUIRE(e && lanes >= 1 && lanes <= 16, "set_lanes: lanes=%d", lanes);
-    NFOPP_REQUIRE(lanes == 1 || e->impl != 3, "set_lanes: the wide ONF path shares one activation workspace between its problems");
     if (lanes > e->dev.P) lanes = e->dev.P;
     if (lanes == e->lanes) return NFOPP_OK;
+    if (e->impl == 3 && lanes > 1) {
+        // every lane needs its own activation workspace inside the one that was sized for all problems
+        const EngineDev &d = e->dev;
+        int nmax = d.NTR > d.NC ? d.NTR : d.NC;
+        if (d.T - 1 > nmax) nmax = d.T - 1;
+        const int pmax = (d.P + lanes - 1) / lanes;
+        const size_t stride = (onf_wide_workspace_bytes(e->onf, pmax, nmax, true) + 255) / 256 * 256;
+        size_t have = 0;
+        for (const BufferInfo &b : e->buffers) if (b.name == "onf_ws") have = b.bytes;
+        NFOPP_REQUIRE(stride * lanes <= have, "set_lanes: %d lanes need %zu bytes of wide-ONF workspace, the engine has %zu", lanes,
+                      stride * lanes, have);
+        e->lane_ws_stride = stride;
+    }
     if (e->graph_exec) { cudaGraphExecDestroy(e->graph_exec); e->graph_exec = nullptr; }
     if (e->graph) { cudaGraphDestroy(e->graph); e->graph = nullptr; }
     while ((int)e->lane_streams.size() < lanes) {
@@ -733,8 +750,11 @@ extern "C" int nfopp_engine_set_lanes(nfopp_engine *e, int lanes) {
         e->lane_events.push_back(ev);
     }
     e->lanes = lanes;
-    const int per_lane = e->launches_per_step_1 - 1;           // everything but the tick runs once per lane
-    e->launches_per_step = lanes > 1 ? per_lane * lanes + 1 : e->launches_per_step_1;
+    e->launches_per_step = 1;                                  // the tick; everything else runs once per lane
+    for (int l = 0; l < lanes; ++l) {
+        const int P = e->dev.P, p0 = (int)((long long)P * l / lanes), p1 = (int)((long long)P * (l + 1) / lanes);
+        e->launches_per_step += step_launches(e, p1 - p0) - 1;
+    }
     return NFOPP_OK;
 }
 

@@ -63,7 +63,9 @@ class BatchedPlanner:
         self.engine = PlannerEngine(config, device=device)
         # lanes of the graphed step: 2 independent problem ranges once each still fills the GPU's SMs (measured on B200, 1024
         # corridor problems: 1.104 ms/step with 1 lane, 1.047 with 2, 1.070 with 4)
-        self.lanes = (2 if config.problems >= 296 else 1) if lanes == "auto" else int(lanes)
+        # (the wide ONF path's persistent kernels gain nothing from lanes: 4.78 -> 4.98 ms/step at 2 lanes, so auto keeps 1)
+        narrow = config.onf_impl in ("fma", "tensor") or (config.onf_impl == "auto" and config.onf.layers == 2 and config.onf.hidden <= 111)
+        self.lanes = (2 if config.problems >= 296 and narrow else 1) if lanes == "auto" else int(lanes)
         if self.lanes > 1:
             try:
                 self.engine.set_lanes(self.lanes)

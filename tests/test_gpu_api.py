@@ -214,3 +214,30 @@ def test_lanes_are_bit_identical_to_a_single_stream():
     for st in states[1:]:
         for k, v in st.items():
             assert torch.equal(v, states[0][k]), k
+
+
+@pytest.mark.gpu
+def test_lanes_on_the_wide_onf_path():
+    """lanes with the wide (streamed-weights) ONF: every lane gets its own activation workspace; the lanes' results agree
+    with the single-stream run to rounding (the weight-gradient split-K count depends on the problems per launch, so the
+    summation order - not the algorithm - may differ) and an over-subscribed lane count is refused, not mis-run."""
+    import torch
+    from nfopp_b200.batched import BatchedPlanner, gridmap_wide_config
+    from nfopp_b200.test_environment_builder import TestEnvironmentBuilder as B
+    grid, _, cell = B.make_blob_grid(200, 200, 0.1, 0.015, blob_cells=12, seed=2)
+    P = 12
+    starts, goals = B.free_endpoints(grid, cell, P, seed=3, margin_cells=10)
+    outs = []
+    for lanes in (1, 2, 3):
+        cfg = gridmap_wide_config(P, rows=200, cols=200, cell=cell, seed=9, hidden=128, layers=3)
+        bp = BatchedPlanner(cfg, lanes=lanes)
+        bp.init(starts, goals, grids=grid)
+        bp.step(3)
+        torch.cuda.synchronize()
+        outs.append((bp.paths().clone(), bp.engine["onf_w"].clone(), bp.engine["train_y"].clone()))
+        assert bool(torch.isfinite(outs[-1][0]).all()) and int(np.abs(bp.status()).max()) == 0
+        bp.engine.close()
+    for paths, w, y in outs[1:]:
+        assert torch.equal(y, outs[0][2])                                   # same samples, same labels
+        assert float((paths - outs[0][0]).abs().max()) < 1e-4
+        assert float((w - outs[0][1]).abs().max()) < 1e-3 * float(outs[0][1].abs().max())
