@@ -1030,25 +1030,26 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
             __syncwarp();
             if (lane == 0) mbar_arrive(act_ready + g);
         };
-        // store 16 columns (col0..col0+15) of this thread's point: A operand in shared memory and/or 32-point tile in global
-        auto store16 = [&](const float *v, int col0, bool to_act, unsigned char *gt, int C) {
-            uint4 h0, l0, h1, l1;
-            split8(v, h0, l0);
-            split8(v + 8, h1, l1);
-            if (to_act) {
-                unsigned char *o = act + (col0 / 8) * 2048 + row * 16;
-                *reinterpret_cast<uint4 *>(o) = h0;
-                *reinterpret_cast<uint4 *>(o + 2048) = h1;
-                *reinterpret_cast<uint4 *>(o + WC_ACT_PLANE) = l0;
-                *reinterpret_cast<uint4 *>(o + WC_ACT_PLANE + 2048) = l1;
-            }
-            if (gt) {
-                unsigned char *o = gt + (col0 / 8) * 512 + r32 * 16;
-                *reinterpret_cast<uint4 *>(o) = h0;
-                *reinterpret_cast<uint4 *>(o + 512) = h1;
-                *reinterpret_cast<uint4 *>(o + C * 64) = l0;
-                *reinterpret_cast<uint4 *>(o + C * 64 + 512) = l1;
-            }
+        // 16 columns (col0..col0+15) of this thread's point: bf16 hi/lo split, A operand in shared memory, 32-point tile in
+        // global memory.  The global stores are issued AFTER the group has been signalled (the proxy fence of the signal
+        // otherwise waits for them too)
+        auto split16 = [&](const float *v, uint4 (&s)[4]) {
+            split8(v, s[0], s[1]);
+            split8(v + 8, s[2], s[3]);
+        };
+        auto put_act = [&](const uint4 (&s)[4], int col0) {
+            unsigned char *o = act + (col0 / 8) * 2048 + row * 16;
+            *reinterpret_cast<uint4 *>(o) = s[0];
+            *reinterpret_cast<uint4 *>(o + 2048) = s[2];
+            *reinterpret_cast<uint4 *>(o + WC_ACT_PLANE) = s[1];
+            *reinterpret_cast<uint4 *>(o + WC_ACT_PLANE + 2048) = s[3];
+        };
+        auto put_tile = [&](const uint4 (&s)[4], int col0, unsigned char *gt, int C) {
+            unsigned char *o = gt + (col0 / 8) * 512 + r32 * 16;
+            *reinterpret_cast<uint4 *>(o) = s[0];
+            *reinterpret_cast<uint4 *>(o + 512) = s[2];
+            *reinterpret_cast<uint4 *>(o + C * 64) = s[1];
+            *reinterpret_cast<uint4 *>(o + C * 64 + 512) = s[3];
         };
         uint32_t gph = 0;
         int cur_p = -1;
@@ -1111,9 +1112,14 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
                             e[i] = (valid && f < L.f_in) ? __sinf(w_reduce_2pi(arg)) : 0.f;
                             zp = fmaf(e[i], svecA[f], zp);
                         }
-                        store16(e, ch * 16, true, Et, w.K1);
+                        uint4 sp[4];
+                        split16(e, sp);
+                        put_act(sp, ch * 16);
+                        signal_group(g);
+                        if (Et) put_tile(sp, ch * 16, Et, w.K1);
+                    } else {
+                        signal_group(g);
                     }
-                    signal_group(g);
                 }
             }
             float gb = 0.f;
@@ -1153,9 +1159,16 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
 #pragma unroll
                                 for (int i = 0; i < 16; ++i) zp = fmaf(v[i], svecB[ch * 16 + i], zp);
                             }
-                            store16(v, ch * 16, !last, last ? nullptr : Ht, w.Hp);      // H_L itself is not needed again
+                            if (!last) {                                                // H_L itself is not needed again
+                                uint4 sp[4];
+                                split16(v, sp);
+                                put_act(sp, ch * 16);
+                                if (more) signal_group(g);
+                                if (Ht) put_tile(sp, ch * 16, Ht, w.Hp);
+                            }
+                        } else if (!last && more) {
+                            signal_group(g);
                         }
-                        if (!last && more) signal_group(g);
                         WC_TRACE(tr, 8 * ph + 3 + g);
                     }
                     if (last) {
@@ -1198,8 +1211,11 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
                                         t[i] = gb * h;                                        // d w_out[:H] = sum_pt gbar * H_L
                                         v[i] = h > 0.f ? gb * svecB[ch * 16 + i] : 0.f;
                                     }
-                                    store16(v, ch * 16, true, Gt, w.Hp);
+                                    uint4 sp[4];
+                                    split16(v, sp);
+                                    put_act(sp, ch * 16);
                                     if (more) signal_group(g);                            // (before the column sums: MMA starts earlier)
+                                    if (Gt) put_tile(sp, ch * 16, Gt, w.Hp);
                                     if (wgrad) {
                                         put_colsum(t, aux_dw3h(w) + ch * 16);
                                         put_colsum(v, aux_db(w, l) + ch * 16);                // d b_L = sum_pt G_L
@@ -1227,8 +1243,11 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
                                 const uint32_t bits = (mw[i >> 1] >> ((i & 1) * 16)) & 0x7FFFu;
                                 v[i] = bits != 0 ? v[i] : 0.f;
                             }
-                            store16(v, ch * 16, true, Gt, w.Hp);
+                            uint4 sp[4];
+                            split16(v, sp);
+                            put_act(sp, ch * 16);
                             if (more) signal_group(g);
+                            if (Gt) put_tile(sp, ch * 16, Gt, w.Hp);
                             if (wgrad) put_colsum(v, aux_db(w, l - 1) + ch * 16);             // d b_{l-1} = sum_pt G_{l-1}
                         } else if (more) {
                             signal_group(g);
