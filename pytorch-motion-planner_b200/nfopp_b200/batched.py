@@ -204,6 +204,73 @@ class BatchedPlanner:
         return torch.cat([p[:int(c)] for p, c in zip(parts, counts)], 0)
 
 
+class HostStepPipeline:
+    """planner.step() driven from HOST buffers: what a caller of the reference does every control cycle -
+    `update_obstacle_points` (ros/planner_adapter.py, scripts/run_planner.py) or a new map, new start / goal, `step()`,
+    `get_path()` - for all problems at once, with the transfers taken off the compute stream.
+
+    Every step's inputs go pinned host -> device staging buffers on a copy-in stream, are moved into the engine's buffers
+    by a device copy on the compute stream, and the step's paths go device -> pinned host on a copy-out stream; both
+    directions use two alternating buffer sets, so the copies of steps k-1 / k+1 run under the kernels of step k.  Results
+    are identical to copying synchronously (tests/test_gpu_api.py)."""
+
+    def __init__(self, planner: "BatchedPlanner", names):
+        eng = planner.engine
+        self.planner, self.names = planner, tuple(names)
+        cfg = planner.config
+        with torch.cuda.device(eng.device):
+            self.stage = [{k: torch.empty_like(eng[k]) for k in self.names} for _ in range(2)]
+            shape = (cfg.problems, cfg.trajectory_length + 2, cfg.dim)
+            self.d_paths = [torch.empty(shape, dtype=torch.float32, device=eng.device) for _ in range(2)]
+            self.h_paths = [torch.empty(shape, dtype=torch.float32).pin_memory() for _ in range(2)]
+            self.in_stream, self.out_stream = torch.cuda.Stream(eng.device), torch.cuda.Stream(eng.device)
+            self._ev = {k: [torch.cuda.Event() for _ in range(2)] for k in ("loaded", "consumed", "ready", "drained")}
+        self.count = 0
+        self.h2d_bytes = sum(eng[k].numel() * eng[k].element_size() for k in self.names)
+        self.d2h_bytes = self.h_paths[0].numel() * 4
+
+    def pinned(self, name, value) -> torch.Tensor:
+        """`value` as a pinned host tensor of the engine buffer's dtype and shape (so the copy is one async DMA)."""
+        ref = self.planner.engine[name]
+        return torch.as_tensor(np.ascontiguousarray(value)).to(ref.dtype).reshape(ref.shape).pin_memory()
+
+    def step(self, host_inputs) -> torch.Tensor:
+        """Enqueue one step fed from `host_inputs` ({engine buffer name: pinned host tensor}); returns the pinned host
+        tensor this step's paths are being written to - valid after `synchronize()` and until two steps later."""
+        eng, ev = self.planner.engine, self._ev
+        i, b = self.count, self.count & 1
+        main = torch.cuda.current_stream(eng.device)
+        if i == 0:
+            self.in_stream.wait_stream(main)
+        with torch.cuda.stream(self.in_stream):
+            if i >= 2:
+                self.in_stream.wait_event(ev["consumed"][b])     # step i-2 has taken its inputs out of this staging set
+            for name in self.names:
+                self.stage[b][name].copy_(host_inputs[name], non_blocking=True)
+            ev["loaded"][b].record(self.in_stream)
+        main.wait_event(ev["loaded"][b])
+        for name in self.names:
+            eng[name].copy_(self.stage[b][name], non_blocking=True)
+        ev["consumed"][b].record(main)
+        self.planner.step(1)
+        if i >= 2:
+            main.wait_event(ev["drained"][b])                    # the read-back of step i-2 has left this device buffer
+        eng.paths(out=self.d_paths[b])
+        ev["ready"][b].record(main)
+        with torch.cuda.stream(self.out_stream):
+            self.out_stream.wait_event(ev["ready"][b])
+            self.h_paths[b].copy_(self.d_paths[b], non_blocking=True)
+            ev["drained"][b].record(self.out_stream)
+        self.count += 1
+        return self.h_paths[b]
+
+    def synchronize(self):
+        eng = self.planner.engine
+        main = torch.cuda.current_stream(eng.device)
+        main.wait_stream(self.out_stream)
+        main.synchronize()
+
+
 def corridor_config(problems: int, seed=0, **overrides) -> EngineConfig:
     """BASELINE config 2: scripts/run_planner.py hyper-parameters (:14-55), forward-only
     (direction_delta_weight=100, scripts/run_bench_mr.py:60), disc robot r=0.3 in jittered S-bend corridors."""

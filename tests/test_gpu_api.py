@@ -241,3 +241,44 @@ def test_lanes_on_the_wide_onf_path():
         assert torch.equal(y, outs[0][2])                                   # same samples, same labels
         assert float((paths - outs[0][0]).abs().max()) < 1e-4
         assert float((w - outs[0][1]).abs().max()) < 1e-3 * float(outs[0][1].abs().max())
+
+
+@pytest.mark.gpu
+def test_host_step_pipeline_equals_synchronous_copies():
+    """HostStepPipeline (inputs staged on a copy stream, paths read back on another, alternating buffers) gives, bit for bit,
+    the paths of copying each step's obstacle set / start / goal synchronously and reading the paths back with get_path()
+    - with the obstacle sets CHANGING every step, so a copy that ran a step early or late would show."""
+    import torch
+    from nfopp_b200.batched import BatchedPlanner, HostStepPipeline, corridor_config, init_onf_weights
+    from nfopp_b200.test_environment_builder import TestEnvironmentBuilder as B
+    P, K = 40, 9
+    starts, goals, _, obstacles = B.make_corridor_batch(P, seed=11)
+    cfg = corridor_config(P, seed=3)
+    w0 = init_onf_weights(cfg.onf, P, True, 6, "cuda")
+    rng = np.random.default_rng(0)
+    moving = [np.asarray(obstacles) + rng.normal(0.0, 0.05, np.asarray(obstacles).shape) for _ in range(K)]
+
+    sync = BatchedPlanner(cfg)
+    sync.init(starts, goals, obstacles=obstacles, onf_weights=w0)
+    want = []
+    for k in range(K):
+        sync.engine["obstacles"].copy_(torch.as_tensor(moving[k]).to(sync.engine["obstacles"].dtype).reshape(sync.engine["obstacles"].shape))
+        sync.step(1)
+        want.append(sync.get_path())
+    sync.engine.close()
+
+    piped = BatchedPlanner(cfg)
+    piped.init(starts, goals, obstacles=obstacles, onf_weights=w0)
+    pipe = HostStepPipeline(piped, ["obstacles", "start", "goal"])
+    h_start, h_goal = pipe.pinned("start", piped.engine["start"].cpu()), pipe.pinned("goal", piped.engine["goal"].cpu())
+    h_obs = [pipe.pinned("obstacles", m) for m in moving]
+    got = []
+    for k in range(K):
+        out = pipe.step({"obstacles": h_obs[k], "start": h_start, "goal": h_goal})
+        if k % 3 == 2 or k == K - 1:                      # read some steps back without draining the pipeline every step
+            pipe.synchronize()
+            got.append((k, out.numpy().copy()))
+    assert pipe.h2d_bytes > 0 and pipe.d2h_bytes == want[0].nbytes
+    for k, paths in got:
+        assert np.array_equal(paths, want[k]), k
+    piped.engine.close()
