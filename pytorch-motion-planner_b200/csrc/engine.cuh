@@ -18,6 +18,11 @@ struct StepParams {
     float traj_step_size, traj_bc2_sqrt;   // same for k = traj_step+1
 };
 
+// obstacle sets up to this many points per problem are staged in shared memory by the kernels that label poses; larger
+// ones (ros/grid_map.py:14-20 turns an occupancy grid into up to ~1e5 occupied-cell centres) are read through L1 / L2
+constexpr int OBS_SMEM_POINTS = 2048;
+__host__ __device__ inline int obs_staged_points(int m_max) { return m_max <= OBS_SMEM_POINTS ? (m_max > 0 ? m_max : 1) : 1; }
+
 struct EngineDev {
     // configuration (by value)
     int p_base;                            // global index of this view's problem 0 (lanes: RNG streams stay per global problem)

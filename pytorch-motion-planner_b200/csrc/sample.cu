@@ -352,13 +352,16 @@ __global__ void __launch_bounds__(RESAMPLE_THREADS) resample_label_kernel(const 
     // ---- labels (collision_checker/*.py) + float32 copy for the ONF (:99) ----
     const int pe = e.env_shared ? 0 : p;
     const int m = (e.checker.kind == 1 || e.checker.kind == 2) ? (e.obstacle_n ? e.obstacle_n[pe] : e.m_max) : 0;
-    for (int k = tid; k < 2 * m; k += RESAMPLE_THREADS) s_obs[k] = e.obstacles[(size_t)pe * e.m_max * 2 + k];
+    const bool staged = e.m_max <= OBS_SMEM_POINTS;
+    const double *obs = staged ? s_obs : e.obstacles + (size_t)pe * e.m_max * 2;
+    if (staged)
+        for (int k = tid; k < 2 * m; k += RESAMPLE_THREADS) s_obs[k] = e.obstacles[(size_t)pe * e.m_max * 2 + k];
     __syncthreads();
     const uint8_t *grid = e.grid ? e.grid + (size_t)pe * e.checker.rows * e.checker.cols : nullptr;
     const int nt = e.train_n[p];
     for (int i = tid; i < nt; i += RESAMPLE_THREADS) {
         double x = tr[(size_t)i * D], y = tr[(size_t)i * D + 1], th = D == 3 ? tr[(size_t)i * D + 2] : 0.0;
-        bool hit = label_pose(e.checker, s_obs, m, grid, x, y, th);
+        bool hit = label_pose(e.checker, obs, m, grid, x, y, th);
         e.train_y[(size_t)p * e.NTR + i] = hit ? 1.f : 0.f;
         for (int d = 0; d < D; ++d) e.train_x[((size_t)p * e.NTR + i) * D + d] = (float)tr[(size_t)i * D + d];
     }
@@ -376,11 +379,11 @@ int launch_warm_sample(const EngineDev &e, int iteration, cudaStream_t s) {
     return NFOPP_OK;
 }
 size_t resample_smem_bytes(const EngineDev &e) {
-    return ((choice_smem_bytes(e.NC, e.C) + 15) / 16) * 16 + (size_t)2 * (e.m_max > 0 ? e.m_max : 1) * sizeof(double);
+    return ((choice_smem_bytes(e.NC, e.C) + 15) / 16) * 16 + (size_t)2 * obs_staged_points(e.m_max) * sizeof(double);
 }
 int resample_prepare(const EngineDev &e) {
     size_t smem = resample_smem_bytes(e);
-    NFOPP_REQUIRE(smem <= 227 * 1024, "resample: %d obstacles per problem exceed shared memory", e.m_max);
+    NFOPP_REQUIRE(smem <= 227 * 1024, "resample: %zu bytes of shared memory", smem);
     if (smem > 48 * 1024)
         NFOPP_CHECK_CUDA(cudaFuncSetAttribute(resample_label_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                               (int)smem));

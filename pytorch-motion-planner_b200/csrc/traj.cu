@@ -396,7 +396,10 @@ __global__ void __launch_bounds__(EVAL_THREADS) evaluate_paths_kernel(const Engi
     const int p = blockIdx.x, tid = threadIdx.x, T = e.T, D = e.D;
     const int pe = e.env_shared ? 0 : p;
     const int m = (e.checker.kind == 1 || e.checker.kind == 2) ? (e.obstacle_n ? e.obstacle_n[pe] : e.m_max) : 0;
-    for (int i = tid; i < 2 * m; i += EVAL_THREADS) s_obs[i] = e.obstacles[(size_t)pe * e.m_max * 2 + i];
+    const bool staged = e.m_max <= OBS_SMEM_POINTS;
+    const double *obs = staged ? s_obs : e.obstacles + (size_t)pe * e.m_max * 2;
+    if (staged)
+        for (int i = tid; i < 2 * m; i += EVAL_THREADS) s_obs[i] = e.obstacles[(size_t)pe * e.m_max * 2 + i];
     if (tid == 0) s_hits = 0;
     __syncthreads();
     const uint8_t *grid = e.grid ? e.grid + (size_t)pe * e.checker.rows * e.checker.cols : nullptr;
@@ -416,7 +419,7 @@ __global__ void __launch_bounds__(EVAL_THREADS) evaluate_paths_kernel(const Engi
             const double t0 = node(j, 2), t1 = node(j + 1, 2);
             th = __dadd_rn(t0, __dmul_rn(sfrac, wrap_angle_d(__dsub_rn(t1, t0))));
         }
-        hits += label_pose(e.checker, s_obs, m, grid, x, y, th) ? 1 : 0;
+        hits += label_pose(e.checker, obs, m, grid, x, y, th) ? 1 : 0;
     }
     double len = 0.0;                                                          // sum of segment lengths (x, y)
     for (int j = tid; j < segs; j += EVAL_THREADS) {
@@ -443,8 +446,7 @@ __global__ void __launch_bounds__(EVAL_THREADS) evaluate_paths_kernel(const Engi
 
 int launch_evaluate_paths(const EngineDev &e, int k, uint8_t *collides, float *length, int32_t *n_hit, cudaStream_t s) {
     NFOPP_REQUIRE(k >= 1 && k <= 4096, "evaluate_paths: samples_per_segment=%d", k);
-    const size_t smem = (size_t)2 * (e.m_max > 0 ? e.m_max : 1) * sizeof(double);
-    NFOPP_REQUIRE(smem <= 48 * 1024, "evaluate_paths: %d obstacles per problem exceed shared memory", e.m_max);
+    const size_t smem = (size_t)2 * obs_staged_points(e.m_max) * sizeof(double);
     evaluate_paths_kernel<<<e.P, EVAL_THREADS, smem, s>>>(e, k, collides, length, n_hit);
     NFOPP_CHECK_CUDA(cudaGetLastError());
     return NFOPP_OK;

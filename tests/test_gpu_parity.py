@@ -782,3 +782,50 @@ def test_full_size_wide_onf_linearity_and_permutation():
     z3, gx3, gw3 = run(x[:, perm].contiguous(), gz[:, perm].contiguous())
     assert torch.equal(z3, z1[:, perm]) and torch.equal(gx3, gx1[:, perm])
     assert float((gw3 - gw1).abs().max()) <= 1e-5 * float(gw1.abs().max())
+
+
+# ------------------------------------------------------------ large obstacle clouds (ros/grid_map.py -> disc checker)
+@pytest.mark.gpu
+def test_disc_robot_against_a_large_occupancy_point_cloud():
+    """ros/grid_map.py turns an occupancy grid into one obstacle point per occupied cell (here ~6 k points,
+    beyond the 2048 the kernels stage in shared memory, shared by all problems).  The engine's labels of its own training
+    poses and its path evaluation stay bit-exact against the oracle's circle checker."""
+    from nfopp_b200.batched import BatchedPlanner, corridor_config
+    from nfopp_b200.grid_map import GridMap
+    from nfopp_b200.test_environment_builder import TestEnvironmentBuilder as B
+    from nfopp_b200.utils.position2 import Position2
+    from oracle import checkers as C
+    from oracle import evaluate as EV
+    grid, _, cell = B.make_blob_grid(200, 200, 0.15, 0.015, blob_cells=10, seed=4)
+    gm = GridMap(np.asarray(grid, dtype=np.float32), cell, Position2(0.0, 0.0, 0.0))
+    cloud = gm.as_point_cloud()
+    assert 2048 < len(cloud) < 20000
+    P = 6
+    starts, goals = B.free_endpoints(grid, cell, P, seed=2, margin_cells=12)
+    starts = np.concatenate([starts[:, :2], np.zeros((P, 1))], 1)
+    goals = np.concatenate([goals[:, :2], np.zeros((P, 1))], 1)
+    bounds = gm.boundaries
+    cfg = corridor_config(P, seed=7, env_shared=True, max_obstacles=len(cloud), robot_radius=0.03,
+                          checker_bounds=bounds, border=bounds)
+    bp = BatchedPlanner(cfg)
+    bp.init(starts, goals, obstacles=cloud)
+    eng = bp.engine
+    label = lambda poses: C.circle_labels(poses, cloud, 0.03, bounds)
+    seen = set()
+    for _ in range(3):
+        bp.step(2, graph=False)
+        torch.cuda.synchronize()
+        n = eng["train_n"].cpu().numpy()
+        pos, y = eng["train_pos"].cpu().numpy(), eng["train_y"].cpu().numpy()
+        for p in range(P):
+            want = label(pos[p, :n[p]])
+            assert np.array_equal(y[p, :n[p]] > 0.5, want), p
+            seen.update(want.tolist())
+    assert seen == {False, True}
+    collides, length, hits = eng.evaluate_paths(3)
+    paths = eng.paths().cpu().numpy()
+    for p in range(P):
+        c, ln, h = EV.evaluate_path(paths[p], label, 3)
+        assert bool(collides[p]) == c and int(hits[p]) == h
+        assert abs(float(length[p]) - ln) <= 1e-6 * ln
+    eng.close()

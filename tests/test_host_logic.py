@@ -205,3 +205,19 @@ def test_oracle_path_evaluation_and_stop_rule():
                         max_iterations=1000, min_iterations=200, check_every=50)
     # checks at i = 250, 300, 350, 400 (0-based): collides, 5.0 (best), 4.0 (best), 4.5 -> break; final evaluation = 1.0
     assert out[3] == 401 and out[1] is False and out[2] == 1.0 and out[0] == 401
+
+
+def test_grid_map_point_cloud_known_answers():
+    """GridMap (ros/grid_map.py:6-40): occupied-cell centres in (x, y) = (column, row) order through the origin pose,
+    map boundaries, OccupancyGrid payload decoding (-1 = unknown -> free, 0..100 -> 0..1, threshold 0.5).  The point
+    order and values were checked bit-for-bit against the live reference when this test was written."""
+    from nfopp_b200.grid_map import GridMap
+    from nfopp_b200.utils.position2 import Position2
+    g = GridMap.from_occupancy_data(np.array([0, 100, -1, 50, 51, 0]), 3, 2, 0.5, Position2(1.0, 2.0, 0.0))
+    assert np.array_equal(g.as_point_cloud(), np.array([[1.75, 2.25], [1.75, 2.75]]))
+    assert g.boundaries == (1.0, 2.5, 2.0, 3.0)
+    assert g.as_point_cloud() is g.as_point_cloud()                      # cached, as in the reference
+    m = np.zeros((4, 5), dtype=np.float32)
+    m[3, 0] = m[0, 4] = 1.0
+    pts = GridMap(m, 0.2, Position2(0.0, 0.0, np.pi / 2)).as_point_cloud()    # rotated origin: (x, y) -> (-y, x)
+    assert np.allclose(pts, np.array([[-0.1, 0.9], [-0.7, 0.1]]), atol=1e-12)
