@@ -240,6 +240,17 @@ int nfopp_engine_path_statistics(nfopp_engine *e, double cusp_angle_threshold, i
  * count (per-problem RNG streams keep their global problem index; on the wide ONF path every lane takes its own slice of
  * the activation workspace and the call fails if the slices do not fit). */
 int nfopp_engine_set_lanes(nfopp_engine *e, int lanes);
+/* PathPostprocessor.process (ros/path_postprocessor.py:13-71) for P paths of n nodes each (what the ROS adapter does to a
+ * path before publishing it): nodes closer than minimal_distance to their successor are dropped, the path is
+ * re-sampled every distance_step metres along its chord-length parametrisation with scipy's quadratic interpolating
+ * spline (headings unfolded first, utils/math.py:38-43), and the leading poses up to a direction flip within the first six
+ * segments are removed.  paths_dev [P, n, 3] float32 (nfopp_engine_get_paths), out_dev [P, max_points, 3] float64,
+ * count_dev [P] int32: poses written; -1 = fewer than 3 distinct nodes (scipy raises there); -k (k > max_points) = the
+ * path needs k poses, nothing written.  workspace_dev from nfopp_postprocess_workspace_bytes.  Not engine-bound. */
+int nfopp_postprocess_workspace_bytes(int P, int n, size_t *bytes);
+int nfopp_postprocess_paths(const float *paths_dev, int P, int n, double minimal_distance, double distance_step,
+                            int max_points, void *workspace_dev, size_t workspace_bytes, double *out_dev,
+                            int32_t *count_dev, void *stream);
 /* number of kernel launches issued by this engine so far (bench.py's gpu_launches) */
 int nfopp_engine_launch_count(nfopp_engine *e, int64_t *launches);
 

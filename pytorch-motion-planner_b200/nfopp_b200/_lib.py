@@ -80,6 +80,8 @@ SIGNATURES = {
     "nfopp_engine_astar_workspace_bytes": (_I, [_P, _I, _I, C.POINTER(C.c_size_t)]),
     "nfopp_engine_init_astar": (_I, [_P, _I, _I, C.c_double, _P, _P, _P, C.c_size_t, _P, _P]),
     "nfopp_engine_path_statistics": (_I, [_P, C.c_double, _I, _P, _P]),
+    "nfopp_postprocess_workspace_bytes": (_I, [_I, _I, _P]),
+    "nfopp_postprocess_paths": (_I, [_P, _I, _I, C.c_double, C.c_double, _I, _P, C.c_size_t, _P, _P, _P]),
     "nfopp_engine_set_lanes": (_I, [_P, _I]),
     "nfopp_engine_launch_count": (_I, [_P, C.POINTER(C.c_int64)]),
 }

@@ -141,6 +141,12 @@ class BatchedPlanner:
         """bench-mr PathStatistics of the current paths (BenchmarkAdapter.cpp:68-135) -> {name: float32 [P]}."""
         return self.engine.path_statistics(**kw)
 
+    def postprocess_paths(self, minimal_distance=0.001, distance_step=0.05, max_points=None):
+        """PathPostprocessor.process (ros/path_postprocessor.py:13-26) for every problem's current path (3-D poses only) ->
+        (poses [P, max_points, 3] float64, counts [P] int32), on the device."""
+        from .path_postprocessor import PathPostprocessor
+        return PathPostprocessor(minimal_distance, distance_step, self.device).process_batch(self.engine.paths(), max_points)
+
     def solve(self, max_iterations=1000, min_iterations=200, check_every=50, samples_per_segment=4, graph=True):
         """scripts/run_bench_mr.py:109-131 for all problems at once: step, and every `check_every` iterations past
         `min_iterations` evaluate every path on the device; a problem keeps its shortest collision-free path and is

@@ -4,6 +4,7 @@ oracle and with the golden vectors produced by the unmodified reference.
 Bars (north_star): collision labels and sampled indices bit-exact; ONF outputs and gradients within 1e-3
 relative (measured: ~1e-6 on the fp32 FMA path); lock-step state within 1e-3; short free runs within
 1e-2 m / 1e-2 rad."""
+import os
 import ctypes as C
 
 import numpy as np
@@ -829,3 +830,55 @@ def test_disc_robot_against_a_large_occupancy_point_cloud():
         assert bool(collides[p]) == c and int(hits[p]) == h
         assert abs(float(length[p]) - ln) <= 1e-6 * ln
     eng.close()
+
+
+# ---------------------------------------------------------------------------------------- PathPostprocessor
+@pytest.mark.gpu
+def test_path_postprocessor_matches_reference_golden():
+    """nfopp_postprocess_paths vs the live reference's PathPostprocessor.process (tests/golden/postprocess.npz): the same
+    number of poses (integer decisions: distance filter, point count, direction filter - exact) and the poses to 1e-9
+    (float64 spline; the reference solves the collocation system with LAPACK, the kernel by banded elimination)."""
+    from nfopp_b200.path_postprocessor import PathPostprocessor
+    from nfopp_b200.utils.position2 import Position2
+    fx = np.load(os.path.join(os.path.dirname(__file__), "golden", "postprocess.npz"))
+    for name in fx["names"]:
+        path, want = fx[f"{name}/path"], fx[f"{name}/result"]
+        min_d, step = (float(v) for v in fx[f"{name}/params"])
+        pp = PathPostprocessor(min_d, step)
+        got = pp.process(Position2.from_vec(path.copy())).as_vec()
+        assert got.shape == want.shape, (name, got.shape, want.shape)
+        assert np.abs(got - want).max() <= 1e-9, (name, np.abs(got - want).max())
+    # paths of fewer than 3 nodes come back unchanged (:14-15)
+    two = Position2.from_vec(np.array([[0, 0, 0], [1, 0, 0]], dtype=np.float32))
+    assert PathPostprocessor().process(two) is two
+
+
+@pytest.mark.gpu
+def test_path_postprocessor_batch_vs_oracle_on_planner_paths():
+    """BatchedPlanner.postprocess_paths on the paths of a running corridor batch (ragged pose counts) vs
+    oracle/postprocess.py path by path; a degenerate path (all nodes equal) is flagged -1 instead of mis-fitted; a too small
+    output buffer is refused."""
+    from nfopp_b200.batched import BatchedPlanner, corridor_config
+    from nfopp_b200.path_postprocessor import PathPostprocessor
+    from nfopp_b200.test_environment_builder import TestEnvironmentBuilder as B
+    from oracle import postprocess as PP
+    P = 48
+    starts, goals, _, obstacles = B.make_corridor_batch(P, seed=21)
+    bp = BatchedPlanner(corridor_config(P, seed=2))
+    bp.init(starts, goals, obstacles=obstacles)
+    bp.step(60)
+    paths = bp.get_path()
+    out, count = bp.postprocess_paths()
+    out, count = out.cpu().numpy(), count.cpu().numpy()
+    assert len(set(count.tolist())) > 1                                   # ragged
+    for p in range(P):
+        want = PP.process(paths[p])
+        assert count[p] == len(want), (p, count[p], len(want))
+        assert np.abs(out[p, :count[p]] - want).max() <= 1e-9, p
+        assert not out[p, count[p]:].any()
+    bp.engine.close()
+    stuck = np.tile(np.array([[1.0, 2.0, 0.5]], dtype=np.float32), (1, 30, 1))
+    _, c = PathPostprocessor().process_batch(stuck)
+    assert int(c[0]) == -1
+    with pytest.raises(ValueError):
+        PathPostprocessor(distance_step=0.001).process_batch(paths[:2], max_points=paths.shape[1])

@@ -1,5 +1,7 @@
 """CPU: the oracle restatement against the golden vectors produced by the unmodified reference
 (oracle/make_golden.py).  This is what pins the oracle on machines without /root/reference."""
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -110,3 +112,26 @@ def test_astar_oracle_matches_reference_fixture():
         assert np.array_equal(xy, g("trajectory")[:, :2]), name
     # the unreachable goal returns the path to the last expanded state (jps.py:321-322), not an error
     assert not np.array_equal(fx["disc_blocked/cells"][-1], A.point_cells(fx["disc_blocked/goal"][:2], (0, 3, 0, 3), 0.25)[::-1])
+
+
+def test_postprocess_oracle_matches_reference_fixture():
+    """oracle/postprocess.py vs tests/golden/postprocess.npz (PathPostprocessor.process of the live reference on seven
+    float32 paths: smooth, looping through +-pi, reversing start, nearly / exactly repeated nodes, coarse filter, short,
+    dense output): same number of poses, values to 1e-9."""
+    from oracle import postprocess as PP
+    fx = np.load(os.path.join(os.path.dirname(__file__), "golden", "postprocess.npz"))
+    dropped_more_than_one = False
+    for name in fx["names"]:
+        path, want = fx[f"{name}/path"], fx[f"{name}/result"]
+        min_d, step = fx[f"{name}/params"]
+        got = PP.process(path, float(min_d), float(step))
+        assert got.shape == want.shape, name
+        assert np.abs(got - want).max() <= 1e-9, name
+        # the cases exercise both filters
+        traj = PP.filter_trajectory(np.array(path, dtype=np.float32), float(min_d))
+        if name in ("jitter_dups", "coarse_filter"):
+            assert len(traj) < len(path)
+        full = int(np.sum(PP.chord_lengths(traj)) / float(step))
+        dropped_more_than_one |= full - len(want) > 1
+    assert dropped_more_than_one                       # reverse_start: the direction filter removed the backing-up poses
+    assert PP.process(np.zeros((2, 3), np.float32)).shape == (2, 3)
