@@ -312,7 +312,23 @@ def run_ours(args):
             sel = res["solved"]
             quality = {k: float(v[sel].mean()) for k, v in st.items()}
             quality["of"] = "mean over rank 0's solved problems"
+        # SURVEY 8(d) M1, second half: problems solved per second at a FIXED 500-step budget (fresh planners, one
+        # evaluation of every path at the end)
+        fixed = BatchedPlanner(cfg, device=f"cuda:{local}")
+        fixed.init(starts, goals, **init_kw)
+        ok = {}
+
+        def run_fixed(_):
+            fixed.step(500)
+            ok["free"] = ~fixed.evaluate_paths(4)[0]
+        ms_fixed = timed(run_fixed, 0)
+        n_fixed = torch.tensor([float(ok["free"].sum())], device="cuda")
+        if world > 1:
+            dist.all_reduce(n_fixed, op=dist.ReduceOp.SUM)
+        fixed.engine.close()
         solve = {"problems": P * world, "solved": int(counts[0]), "seconds": ms_solve * 1e-3, "path_quality": quality,
+                 "fixed_500_steps": {"solved": int(n_fixed[0]), "seconds": ms_fixed * 1e-3,
+                                     "solved_per_s": float(n_fixed[0]) / (ms_fixed * 1e-3)},
                  "solved_per_s": float(counts[0]) / (ms_solve * 1e-3), "steps_run_per_gpu": float(counts[1]) / world,
                  "rule": "run_bench_mr.py: max 1000 / min 200 iterations, evaluate every 50 (4 poses per segment through the "
                          "collision checker), stop at a collision-free path that is no shorter than the best"}
