@@ -16,6 +16,7 @@
 //                           interior points go to the trajectory buffer as float32.
 // oracle/astar.py is the CPU restatement (pinned bit-for-bit against the live reference and scipy).
 #include "engine.cuh"
+#include "spline.cuh"
 
 namespace nfopp {
 
@@ -165,17 +166,6 @@ __global__ void __launch_bounds__(32) astar_search_kernel(const AstarArgs a) {
 }
 
 // ---- 3. reparametrize_path: quadratic interpolating spline through the path, T+2 equally spaced parameters ----------
-// the three quadratic B-spline basis functions that are non-zero on [t[j], t[j+1]) (oracle/astar.py:_basis3)
-__device__ __forceinline__ void basis3(const double *t, double x, int j, double &n0, double &n1, double &n2) {
-    const double left1 = x - t[j], right1 = t[j + 1] - x;
-    const double b0 = right1 / (right1 + left1), b1 = left1 / (right1 + left1);
-    const double left2 = x - t[j - 1], right2 = t[j + 2] - x;
-    n0 = b0 * right1 / (right1 + left2);
-    const double tmp = b0 * left2 / (right1 + left2);
-    n1 = tmp + b1 * right2 / (right2 + left1);
-    n2 = b1 * left1 / (right2 + left1);
-}
-
 __global__ void __launch_bounds__(32) astar_spline_kernel(const AstarArgs a) {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     const EngineDev &e = a.e;
@@ -210,62 +200,20 @@ __global__ void __launch_bounds__(32) astar_spline_kernel(const AstarArgs a) {
     }
     const double total = param[n - 1];
     for (int i = 0; i < n; ++i) param[i] = __ddiv_rn(param[i], total);
-    // not-a-knot knots of make_interp_spline(k=2): x0 x3, interior midpoints without the first and last, xn x3
-    t[0] = t[1] = t[2] = param[0];
-    for (int i = 1; i + 2 < n; ++i) t[2 + i] = (param[i + 1] + param[i]) / 2;
-    t[n] = t[n + 1] = t[n + 2] = param[n - 1];
-    auto interval = [&](double x) {
-        int j = 2;
-        while (j < n - 1 && t[j + 1] <= x) ++j;
-        return j;
-    };
-    // collocation matrix (row i: B_{j-2..j}(x_i)) in band storage, right-hand sides = the points
     for (int i = 0; i < n; ++i) {
-        for (int k = 0; k < 5; ++k) band[5 * i + k] = 0.0;
-        const int j = interval(param[i]);
-        double n0, n1, n2;
-        basis3(t, param[i], j, n0, n1, n2);
-        const int c0 = j - 2 - (i - 2);                                  // band column of matrix column j-2
-        if (c0 >= 0 && c0 < 5) band[5 * i + c0] = n0;
-        if (c0 + 1 >= 0 && c0 + 1 < 5) band[5 * i + c0 + 1] = n1;
-        if (c0 + 2 >= 0 && c0 + 2 < 5) band[5 * i + c0 + 2] = n2;
         coef[2 * i] = (double)pts[2 * i];
         coef[2 * i + 1] = (double)pts[2 * i + 1];
     }
-    // banded Gaussian elimination (totally positive collocation matrix: stable without pivoting)
-    for (int k = 0; k < n; ++k) {
-        const double piv = band[5 * k + 2];
-        for (int i = k + 1; i <= k + 2 && i < n; ++i) {
-            const int ck = 2 - (i - k);                                  // band column of matrix column k in row i
-            const double f = band[5 * i + ck] / piv;
-            if (f == 0.0) continue;
-            for (int c = 0; c <= 2; ++c) {                               // matrix columns k .. k+2
-                const int ci = ck + c;
-                if (ci < 5) band[5 * i + ci] -= f * band[5 * k + 2 + c];
-            }
-            coef[2 * i] -= f * coef[2 * k];
-            coef[2 * i + 1] -= f * coef[2 * k + 1];
-        }
-    }
-    for (int i = n - 1; i >= 0; --i) {
-        double s0 = coef[2 * i], s1 = coef[2 * i + 1];
-        for (int c = 1; c <= 2 && i + c < n; ++c) {
-            s0 -= band[5 * i + 2 + c] * coef[2 * (i + c)];
-            s1 -= band[5 * i + 2 + c] * coef[2 * (i + c) + 1];
-        }
-        coef[2 * i] = s0 / band[5 * i + 2];
-        coef[2 * i + 1] = s1 / band[5 * i + 2];
-    }
+    quad_spline_fit<2>(n, param, t, band, coef);
     // evaluation at linspace(0, 1, T+2)[1:-1] (numpy: i * step)
     const double step = __ddiv_rn(1.0, (double)(T + 1));
+    int j = 2;
     for (int q = 1; q <= T; ++q) {
-        const double x = __dmul_rn((double)q, step);
-        const int j = interval(x);
-        double n0, n1, n2;
-        basis3(t, x, j, n0, n1, n2);
+        double y[2];
+        quad_spline_eval<2>(t, n, coef, __dmul_rn((double)q, step), j, y);
         float *dst = e.traj + ((size_t)p * T + (q - 1)) * D;
-        dst[0] = (float)(n0 * coef[2 * (j - 2)] + n1 * coef[2 * (j - 1)] + n2 * coef[2 * j]);
-        dst[1] = (float)(n0 * coef[2 * (j - 2) + 1] + n1 * coef[2 * (j - 1) + 1] + n2 * coef[2 * j + 1]);
+        dst[0] = (float)y[0];
+        dst[1] = (float)y[1];
     }
 }
 

@@ -13,6 +13,7 @@
 //                                       (the first pose always is)
 // oracle/postprocess.py is the CPU restatement (pinned against the live reference, tests/golden/postprocess.npz).
 #include "common.cuh"
+#include "spline.cuh"
 
 namespace nfopp {
 
@@ -87,23 +88,6 @@ __device__ __forceinline__ double np_wrap_f64(double a) {
     double m = fmod(a + pi, two_pi);
     if (m != 0.0 && m < 0.0) m += two_pi;
     return m - pi;
-}
-
-// the three quadratic B-spline basis functions that are non-zero on [t[j], t[j+1]) (oracle/astar.py:_basis3)
-__device__ __forceinline__ void pp_basis3(const double *t, double x, int j, double &n0, double &n1, double &n2) {
-    const double left1 = x - t[j], right1 = t[j + 1] - x;
-    const double b0 = right1 / (right1 + left1), b1 = left1 / (right1 + left1);
-    const double left2 = x - t[j - 1], right2 = t[j + 2] - x;
-    n0 = b0 * right1 / (right1 + left2);
-    const double tmp = b0 * left2 / (right1 + left2);
-    n1 = tmp + b1 * right2 / (right2 + left1);
-    n2 = b1 * left1 / (right2 + left1);
-}
-
-__device__ __forceinline__ int pp_interval(const double *t, int n, double x, int from) {
-    int j = from;
-    while (j < n - 1 && t[j + 1] <= x) ++j;
-    return j;
 }
 
 __global__ void __launch_bounds__(32) postprocess_kernel(const PostArgs a) {
@@ -182,49 +166,15 @@ __global__ void __launch_bounds__(32) postprocess_kernel(const PostArgs a) {
         }
     }
     // ---- 4. quadratic interpolating spline through (param, pts) ----
-    t[0] = t[1] = t[2] = param[0];
-    for (int i = 1; i + 2 < m; ++i) t[2 + i] = (param[i + 1] + param[i]) / 2;
-    t[m] = t[m + 1] = t[m + 2] = param[m - 1];
-    for (int i = 0; i < m; ++i) {
-        for (int k = 0; k < 5; ++k) band[5 * i + k] = 0.0;
-        const int j = pp_interval(t, m, param[i], 2);
-        double n0, n1, n2;
-        pp_basis3(t, param[i], j, n0, n1, n2);
-        const int c0 = j - 2 - (i - 2);                               // band column of matrix column j-2
-        if (c0 >= 0 && c0 < 5) band[5 * i + c0] = n0;
-        if (c0 + 1 >= 0 && c0 + 1 < 5) band[5 * i + c0 + 1] = n1;
-        if (c0 + 2 >= 0 && c0 + 2 < 5) band[5 * i + c0 + 2] = n2;
+    for (int i = 0; i < m; ++i)
         for (int c = 0; c < 3; ++c) coef[3 * i + c] = (double)pts[3 * i + c];
-    }
-    for (int k = 0; k < m; ++k) {                                     // totally positive matrix: stable without pivoting
-        const double piv = band[5 * k + 2];
-        for (int i = k + 1; i <= k + 2 && i < m; ++i) {
-            const int ck = 2 - (i - k);
-            const double f = band[5 * i + ck] / piv;
-            if (f == 0.0) continue;
-            for (int c = 0; c <= 2; ++c) {
-                const int ci = ck + c;
-                if (ci < 5) band[5 * i + ci] -= f * band[5 * k + 2 + c];
-            }
-            for (int c = 0; c < 3; ++c) coef[3 * i + c] -= f * coef[3 * k + c];
-        }
-    }
-    for (int i = m - 1; i >= 0; --i) {
-        for (int c = 0; c < 3; ++c) {
-            double s = coef[3 * i + c];
-            for (int d = 1; d <= 2 && i + d < m; ++d) s -= band[5 * i + 2 + d] * coef[3 * (i + d) + c];
-            coef[3 * i + c] = s / band[5 * i + 2];
-        }
-    }
+    quad_spline_fit<3>(m, param, t, band, coef);
     const double step = __ddiv_rn(1.0, (double)(count - 1));           // numpy linspace: arange * step, last = stop
     int j = 2;
     for (int q = 0; q < count; ++q) {
-        const double x = q == count - 1 ? 1.0 : __dmul_rn((double)q, step);
-        j = pp_interval(t, m, x, j);
-        double n0, n1, n2;
-        pp_basis3(t, x, j, n0, n1, n2);
-        for (int c = 0; c < 3; ++c)
-            out[3 * q + c] = n0 * coef[3 * (j - 2) + c] + n1 * coef[3 * (j - 1) + c] + n2 * coef[3 * j + c];
+        double y[3];
+        quad_spline_eval<3>(t, m, coef, q == count - 1 ? 1.0 : __dmul_rn((double)q, step), j, y);
+        for (int c = 0; c < 3; ++c) out[3 * q + c] = y[c];
     }
     // ---- 5. direction filter at the head of the path ----
     int first = 1;
