@@ -670,7 +670,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
                         for (int i = 0; i < 16; ++i) {
                             const float r = reduce_2pi(feature_arg(ppa, ppb, ppc, xu[i], x1[i]));
                             const float gp = f_on ? v[i] * __cosf(r) : 0.f;
-                            ev[i] = want_wgrad ? __sinf(r) : 0.f;            // E^T operand of wgrad1 only
+                            ev[i] = __sinf(r);
                             gq[i] = gp;
                             ta = fmaf(gp, xu[i], ta);
                             tb = fmaf(gp, x1[i], tb);
@@ -680,10 +680,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) onf_tc_kernel(const OnfTcArgs a
 #pragma unroll
                         for (int i = 0; i < 16; ++i) { ev[i] = 0.f; gq[i] = 0.f; }
                     }
-                    if (want_wgrad) {
-                        split8(ev, ehi[0], elo[0]);
-                        split8(ev + 8, ehi[1], elo[1]);
-                    }
+                    split8(ev, ehi[0], elo[0]);
+                    split8(ev + 8, ehi[1], elo[1]);
                 }
                 if (!fourier) {                                      // heading features: d ang_b = f_k * sum gp,
                     const float b = f < FIN ? s.ang_b[f - F] : 0.f;  // d ang_f = sum gp * (theta + b_k)  (trained)
