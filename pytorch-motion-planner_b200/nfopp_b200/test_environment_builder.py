@@ -89,6 +89,44 @@ class TestEnvironmentBuilder(object):
         return starts, goals, (0.0, w, 0.0, h), grids, (0.0, 0.0), cell
 
     @staticmethod
+    def make_corridor_grid_batch(problems, rows=100, cols=100, radius=3, branches=100, cell=0.03, seed=0):
+        """Corridor mazes in the style of bench-mr's random corridor grids (notebooks/corridor_experiment.ipynb:91,407:
+        100x100 cells, radius 3, 100 branches, seeds 2..11).  bench-mr's generator lives in a missing submodule; this is our
+        own with the same parameters: the map starts fully occupied, the first node is a random cell, and every branch
+        carves an L-shaped corridor (first along x, then along y, `radius` cells to either side) from the nearest existing
+        node to a new random cell.  Start = the first node, goal = the node farthest from it; headings point along the
+        start -> goal chord.  Problem i uses RandomState(seed + i).
+        Returns (starts [P,3], goals [P,3], bounds, grids [P,rows,cols] uint8, origin, cell)."""
+        grids = np.ones((problems, rows, cols), dtype=np.uint8)
+        starts = np.zeros((problems, 3), dtype=np.float32)
+        goals = np.zeros((problems, 3), dtype=np.float32)
+        lo, hi_r, hi_c = radius + 1, rows - radius - 1, cols - radius - 1
+        for i in range(problems):
+            rs = np.random.RandomState(seed + i)
+            g = grids[i]
+            nodes = [(rs.randint(lo, hi_r), rs.randint(lo, hi_c))]
+
+            def carve(r, c):
+                g[r - radius:r + radius + 1, c - radius:c + radius + 1] = 0
+            carve(*nodes[0])
+            for _ in range(branches):
+                tr, tc = rs.randint(lo, hi_r), rs.randint(lo, hi_c)
+                r, c = min(nodes, key=lambda n: (n[0] - tr) ** 2 + (n[1] - tc) ** 2)
+                while c != tc:
+                    c += 1 if tc > c else -1
+                    carve(r, c)
+                while r != tr:
+                    r += 1 if tr > r else -1
+                    carve(r, c)
+                nodes.append((tr, tc))
+            r0, c0 = nodes[0]
+            r1, c1 = max(nodes, key=lambda n: (n[0] - r0) ** 2 + (n[1] - c0) ** 2)
+            heading = np.arctan2(r1 - r0, c1 - c0)
+            starts[i] = ((c0 + 0.5) * cell, (r0 + 0.5) * cell, heading)
+            goals[i] = ((c1 + 0.5) * cell, (r1 + 0.5) * cell, heading)
+        return starts, goals, (0.0, cols * cell, 0.0, rows * cell), grids, (0.0, 0.0), cell
+
+    @staticmethod
     def make_blob_grid(rows=1000, cols=1000, obstacle_ratio=0.1, cell=0.003, blob_cells=24, seed=1):
         """One large synthetic occupancy grid (BASELINE config 4): square blobs of `blob_cells` cells dropped
         uniformly until ~obstacle_ratio of the map is occupied (bench-mr's random-grid generator is in a missing

@@ -221,3 +221,31 @@ def test_grid_map_point_cloud_known_answers():
     m[3, 0] = m[0, 4] = 1.0
     pts = GridMap(m, 0.2, Position2(0.0, 0.0, np.pi / 2)).as_point_cloud()    # rotated origin: (x, y) -> (-y, x)
     assert np.allclose(pts, np.array([[-0.1, 0.9], [-0.7, 0.1]]), atol=1e-12)
+
+
+def test_corridor_maze_generator_is_seeded_and_connected():
+    """make_corridor_grid_batch (bench-mr-style corridor mazes, own generator): deterministic per (seed, problem index),
+    start and goal lie in free cells of the same connected component, corridors are 2 * radius + 1 cells wide."""
+    from collections import deque
+    from nfopp_b200.test_environment_builder import TestEnvironmentBuilder as B
+    s1, g1, bounds, grids, origin, cell = B.make_corridor_grid_batch(3, seed=2)
+    s2, g2, _, grids2, _, _ = B.make_corridor_grid_batch(2, seed=3)
+    assert np.array_equal(grids[1], grids2[0]) and np.array_equal(s1[1], s2[0]) and np.array_equal(g1[1], g2[0])
+    assert bounds == (0.0, 3.0, 0.0, 3.0) and grids.shape == (3, 100, 100) and grids.dtype == np.uint8
+    for i in range(3):
+        g = grids[i]
+        assert 0.2 < g.mean() < 0.8
+        rc = lambda pt: (int(pt[1] / cell), int(pt[0] / cell))
+        (r0, c0), (r1, c1) = rc(s1[i]), rc(g1[i])
+        assert not g[r0 - 3:r0 + 4, c0 - 3:c0 + 4].any() and not g[r1 - 3:r1 + 4, c1 - 3:c1 + 4].any()
+        seen = np.zeros_like(g, dtype=bool)
+        seen[r0, c0] = True
+        todo = deque([(r0, c0)])
+        while todo:
+            r, c = todo.popleft()
+            for dr, dc in ((1, 0), (-1, 0), (0, 1), (0, -1)):
+                rr, cc = r + dr, c + dc
+                if 0 <= rr < 100 and 0 <= cc < 100 and not g[rr, cc] and not seen[rr, cc]:
+                    seen[rr, cc] = True
+                    todo.append((rr, cc))
+        assert seen[r1, c1]
