@@ -77,7 +77,7 @@ class BatchedPlanner:
         self._use_normal_init = use_normal_init
 
     def init(self, start_points, goal_points, obstacles=None, obstacle_counts=None, grids=None, onf_weights=None,
-             astar_resolution=None):
+             astar_resolution=None, init_angles_with_trajectory=False):
         """start/goal: [P, D]; obstacles [P|1, M, 2] or grids [P|1, rows, cols]; onf_weights [P, n_params] or
         None (fresh initialisation seeded by config.seed)."""
         eng = self.engine
@@ -93,6 +93,9 @@ class BatchedPlanner:
         eng.init_trajectories()
         if astar_resolution is not None:               # AstarTrajectoryInitializer (scripts/run_bench_mr.py:23-26)
             eng.init_astar(astar_resolution)
+        if init_angles_with_trajectory and self.config.dim == 3:     # trajectory_initializer.py:28-44, all problems at once
+            from .trajectory_initializer import blend_headings_with_path_direction
+            blend_headings_with_path_direction(eng["traj"], eng["start"], eng["goal"])
         eng.warmup(self.config.init_collision_iteration)
         eng.set_counter("step_count", 0)
 

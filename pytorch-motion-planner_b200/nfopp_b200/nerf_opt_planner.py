@@ -112,6 +112,9 @@ class NERFOptPlanner(ContinuousPlanner):
             initializer.initialize_engine(eng)
         else:
             eng.init_trajectories()
+        if d == 3 and getattr(initializer, "_init_angles_with_trajectory", False):     # trajectory_initializer.py:28-44
+            from .trajectory_initializer import blend_headings_with_path_direction
+            blend_headings_with_path_direction(eng["traj"], eng["start"], eng["goal"])
         eng.warmup(self._init_collision_iteration)
         eng.set_counter("step_count", 0)
 

@@ -282,3 +282,28 @@ def test_host_step_pipeline_equals_synchronous_copies():
     for k, paths in got:
         assert np.array_equal(paths, want[k]), k
     piped.engine.close()
+
+
+@pytest.mark.gpu
+def test_init_angles_with_trajectory_on_the_device():
+    """init_angles_with_trajectory=True through BatchedPlanner.init (A* x, y, then headings pulled towards the direction of
+    travel): equals the host helper applied to the same trajectories, end headings untouched, planner steps stay finite."""
+    import torch
+    from nfopp_b200.batched import BatchedPlanner, corridor_config
+    from nfopp_b200.test_environment_builder import TestEnvironmentBuilder as B
+    from nfopp_b200.trajectory_initializer import blend_headings_with_path_direction
+    P = 8
+    starts, goals, _, obstacles = B.make_corridor_batch(P, seed=31)
+    plain = BatchedPlanner(corridor_config(P, seed=1))
+    plain.init(starts, goals, obstacles=obstacles, astar_resolution=0.25)
+    want = blend_headings_with_path_direction(plain.engine["traj"].cpu().clone(), plain.engine["start"].cpu(), plain.engine["goal"].cpu())
+    bp = BatchedPlanner(corridor_config(P, seed=1))
+    bp.init(starts, goals, obstacles=obstacles, astar_resolution=0.25, init_angles_with_trajectory=True)
+    got = bp.engine["traj"].cpu()
+    assert torch.allclose(got, want, atol=2e-6)
+    assert not torch.allclose(got[..., 2], plain.engine["traj"].cpu()[..., 2], atol=1e-3)      # the S-bend path does turn
+    assert torch.equal(got[..., :2], plain.engine["traj"].cpu()[..., :2])
+    bp.step(20)
+    assert bool(torch.isfinite(bp.paths()).all())
+    plain.engine.close()
+    bp.engine.close()

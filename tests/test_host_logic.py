@@ -249,3 +249,39 @@ def test_corridor_maze_generator_is_seeded_and_connected():
                     seen[rr, cc] = True
                     todo.append((rr, cc))
         assert seen[r1, c1]
+
+
+def test_trajectory_initializer_with_path_direction_headings_matches_reference():
+    """TrajectoryInitializer(init_angles_with_trajectory=True) (trajectory_initializer.py:12-44) vs the live reference's
+    outputs (tests/golden/init_angles.npz): straight-line initialisation and heading initialisation over curved x, y, even
+    and odd trajectory lengths; and the batched form used by BatchedPlanner gives the same rows."""
+    from nfopp_b200.trajectory_initializer import TrajectoryInitializer, blend_headings_with_path_direction
+    fx = np.load(os.path.join(os.path.dirname(__file__), "golden", "init_angles.npz"))
+    rows = []
+    for name in fx["names"]:
+        traj = torch.tensor(fx[f"{name}/before"])
+        start, goal = torch.tensor(fx[f"{name}/start"]), torch.tensor(fx[f"{name}/goal"])
+        init = TrajectoryInitializer(None, init_angles_with_trajectory=True)
+        if bool(fx[f"{name}/curved"]):
+            init.initialize_angle(traj, start, goal)
+        else:
+            init.initialize_trajectory(traj, start, goal)
+        assert np.abs(traj.numpy() - fx[f"{name}/after"]).max() <= 2e-6, name
+        rows.append((name, traj))
+    # batch of two equal-length problems through the batched helper
+    a, b = "line_even", "curved"
+    plain = TrajectoryInitializer(None)
+    batch = []
+    for name in (a, b):
+        t = torch.tensor(fx[f"{name}/before"])
+        if bool(fx[f"{name}/curved"]):
+            plain.initialize_angle(t, torch.tensor(fx[f"{name}/start"]), torch.tensor(fx[f"{name}/goal"]))
+        else:
+            plain.initialize_trajectory(t, torch.tensor(fx[f"{name}/start"]), torch.tensor(fx[f"{name}/goal"]))
+        batch.append(t)
+    batch = torch.stack(batch)
+    starts = torch.cat([torch.tensor(fx[f"{n}/start"]) for n in (a, b)])
+    goals = torch.cat([torch.tensor(fx[f"{n}/goal"]) for n in (a, b)])
+    blend_headings_with_path_direction(batch, starts, goals)
+    for i, name in enumerate((a, b)):
+        assert np.abs(batch[i].numpy() - fx[f"{name}/after"]).max() <= 2e-6, name
