@@ -143,7 +143,7 @@ def golden_choice():
     print("choice:", len(out) // 3, "cases")
 
 
-def golden_lockstep(name, steps, free_run=10, **overrides):
+def golden_lockstep(name, steps, free_run=10, tag=None, **overrides):
     """Chain of reference states around the given step indices + the variates of each step, plus a short
     free run (initial state, all variates, reference path)."""
     planner, env, checker = RB.make_reference_case(name, **overrides)
@@ -166,8 +166,46 @@ def golden_lockstep(name, steps, free_run=10, **overrides):
         if k < free_run:
             out.update({f"free/var{k}/{kk}": _np(v) for kk, v in rec.items()})
             out[f"free/path{k}"] = planner.get_path()
-    np.savez_compressed(os.path.join(OUT, f"lockstep_{name}.npz"), **out)
-    print(name, "lockstep fixture:", os.path.getsize(os.path.join(OUT, f"lockstep_{name}.npz")) // 1024, "KiB")
+    fname = f"lockstep_{tag or name}.npz"
+    np.savez_compressed(os.path.join(OUT, fname), **out)
+    print(tag or name, "lockstep fixture:", os.path.getsize(os.path.join(OUT, fname)) // 1024, "KiB")
+
+
+def golden_warmup(name, iterations, **overrides):
+    """ONF warm-up (nerf_opt_planner.py:181-187,197-200): init() walked by hand on the UNMODIFIED reference planner -
+    start / goal / border, _init_trajectory(), then `iterations` x {_sample_random_field_points(init_collision_points)
+    (:135-141; constrained :173-176) -> _optimize_collision_model(positions) (:76-91)} - with the planner's full state
+    snapshotted before the loop and after every iteration, and every iteration's uniforms, sampled points and labels."""
+    planner, env, checker = RB.make_reference_case(name, call_init=False, init_collision_iteration=iterations, **overrides)
+    cfg = RB.planner_config_of(planner)
+    assert cfg.init_collision_iteration == iterations
+    planner._start_point = torch.tensor(env.start_point.astype(np.float32))[None]
+    planner._goal_point = torch.tensor(env.goal_point.astype(np.float32))[None]
+    planner._random_sample_border = env.bounds
+    planner._init_trajectory()
+    out = {"meta/iterations": np.array(iterations), "meta/obstacles": np.asarray(checker._obstacle_points),
+           "meta/bounds": np.asarray(checker._boundaries, dtype=np.float64),
+           "meta/init_collision_points": np.array(cfg.init_collision_points)}
+    out.update(_flat_state("warm/before", RB.snapshot(planner)))
+    for i in range(iterations):
+        with RB.record_variates(cfg.constrained, cfg.trajectory_length, order=["warm_xy", "warm_th"]) as rec:
+            positions = planner._sample_random_field_points(planner._init_collision_points)
+            planner._optimize_collision_model(positions)
+        out.update(_flat_state(f"warm/after{i}", RB.snapshot(planner)))
+        out.update({f"warm/var{i}/{kk}": _np(v) for kk, v in rec.items() if kk.startswith("warm_")})
+        out[f"warm/labels{i}"] = np.asarray(planner.truth_collision, dtype=bool)
+        cp = planner.checked_positions
+        out[f"warm/checked{i}"] = cp.as_vec() if hasattr(cp, "as_vec") else np.asarray(cp)
+    planner._step_count = 0
+    # the first planner step after the warm-up (separate step counters: the ONF optimiser is at `iterations`, the
+    # trajectory optimiser at 0)
+    out.update(_flat_state("step0/before", RB.snapshot(planner)))
+    with RB.record_variates(cfg.constrained, cfg.trajectory_length) as rec:
+        planner.step()
+    out.update(_flat_state("step0/after", RB.snapshot(planner)))
+    out.update({f"step0/var/{kk}": _np(v) for kk, v in rec.items()})
+    np.savez_compressed(os.path.join(OUT, f"warmup_{name}.npz"), **out)
+    print(name, "warm-up fixture:", os.path.getsize(os.path.join(OUT, f"warmup_{name}.npz")) // 1024, "KiB")
 
 
 def main():
@@ -179,6 +217,11 @@ def main():
     golden_lockstep("car", steps=[0, 1, 10])
     golden_lockstep("corridor", steps=[1, 10])
     golden_lockstep("holonomic", steps=[0, 1, 10], init_collision_iteration=2)
+    # training every 2nd step, re-parametrisation every 3rd (nerf_opt_planner.py:62,66)
+    golden_lockstep("corridor", steps=[0, 1, 2, 3], free_run=6, tag="corridor_freq", optimize_collision_model_freq=2,
+                    reparametrize_trajectory_freq=3)
+    golden_warmup("holonomic", 3)          # planner_factory.py:59 runs 400 of these; the image-map notebook 3
+    golden_warmup("car", 3)
 
 
 if __name__ == "__main__":

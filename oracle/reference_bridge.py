@@ -66,10 +66,11 @@ RUN_PLANNER_PARAMETERS = dict(
                  angle_offset=0.3, boundary_weight=1, collision_multipliers_lr=1e-3))
 
 
-def make_reference_case(name: str, torch_seed=100, numpy_seed=400, **planner_overrides):
+def make_reference_case(name: str, torch_seed=100, numpy_seed=400, call_init=True, **planner_overrides):
     """name in {'car' (scripts/run_planner.py as written), 'corridor' (config 2: S-bend walls, disc robot,
     forward-only), 'holonomic' (PlannerFactory.make_onf_planner + circle checker)}.
-    Returns (planner, env, checker) with init() already called."""
+    Returns (planner, env, checker) with init() already called (call_init=False: not yet - the warm-up fixture
+    walks init() by hand)."""
     ref = load_reference()
     torch.random.manual_seed(torch_seed)
     np.random.seed(numpy_seed)
@@ -97,8 +98,9 @@ def make_reference_case(name: str, torch_seed=100, numpy_seed=400, **planner_ove
         params["planner"].update(planner_overrides)
         checker.update_obstacle_points(env.obstacle_points)
         planner = pf.make_constrained_onf_planner(checker, attribute_dict(**params))
-    with _quiet():
-        planner.init(env.start_point, env.goal_point, env.bounds)
+    if call_init:
+        with _quiet():
+            planner.init(env.start_point, env.goal_point, env.bounds)
     return planner, env, checker
 
 
@@ -184,12 +186,14 @@ def snapshot(planner) -> dict:
 
 
 @contextlib.contextmanager
-def record_variates(constrained: bool, T: int):
+def record_variates(constrained: bool, T: int, order=None):
     """Patches numpy's legacy global RNG entry points and torch.rand while a reference step() runs and
-    records what it draws, keyed as the oracle's sources expect."""
+    records what it draws, keyed as the oracle's sources expect.  `order` overrides the
+    names of the numpy draws (warm-up iterations draw only the uniform field points)."""
     rec = {"choice_u": np.zeros(0)}
-    order = (["t_sample", "coarse_xy", "coarse_th", "fine_xy", "fine_th", "field_xy", "field_th"] if constrained
-             else ["t_sample", "coarse_xy", "fine_xy", "field_xy", "t_path"])
+    if order is None:
+        order = (["t_sample", "coarse_xy", "coarse_th", "fine_xy", "fine_th", "field_xy", "field_th"] if constrained
+                 else ["t_sample", "coarse_xy", "fine_xy", "field_xy", "t_path"])
     pos = [0]
     real = dict(rand=np.random.rand, randn=np.random.randn, choice=np.random.choice, trand=torch.rand)
 

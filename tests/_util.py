@@ -45,6 +45,13 @@ PLANNER_CFGS = {
 }
 
 
+import dataclasses
+# nerf_opt_planner.py:62,66 with both frequencies off their defaults (tests/golden/lockstep_corridor_freq.npz)
+PLANNER_CFGS["corridor_freq"] = dataclasses.replace(PLANNER_CFGS["corridor"], optimize_collision_model_freq=2,
+                                                    reparametrize_trajectory_freq=3)
+ONF_CFGS["corridor_freq"] = ONF_CFGS["corridor"]
+
+
 def labeller_for(name, fx):
     obs, bounds = fx["meta/obstacles"], tuple(fx["meta/bounds"])
     if name == "car":

@@ -296,7 +296,7 @@ def test_choice_indices_bit_exact():
 
 # ---------------------------------------------------------------------------------------- planner step
 @pytest.mark.parametrize("impl", ["fma", "tensor"])
-@pytest.mark.parametrize("name", ["car", "corridor", "holonomic"])
+@pytest.mark.parametrize("name", ["car", "corridor", "holonomic", "corridor_freq"])
 def test_lockstep_against_reference_states(name, impl):
     """Import the reference's full state at step k, run ONE GPU step with the reference's variates, compare
     the post-step state with the reference's (golden) and with the oracle's."""
@@ -308,10 +308,13 @@ def test_lockstep_against_reference_states(name, impl):
         eng.inject_variates(var)
         eng.step(1)
         torch.cuda.synchronize()
-        n = int(eng["train_n"][0])
-        assert n == len(fx[f"step{k}/labels"])
-        assert np.array_equal(eng["train_pos"][0, :n].cpu().numpy(), fx[f"step{k}/checked"]), "sampled poses"
-        assert np.array_equal(eng["train_y"][0, :n].cpu().numpy() > 0.5, fx[f"step{k}/labels"]), "labels"
+        if "t_sample" in var:              # a field-training step (optimize_collision_model_freq, nerf_opt_planner.py:62)
+            n = int(eng["train_n"][0])
+            assert n == len(fx[f"step{k}/labels"])
+            assert np.array_equal(eng["train_pos"][0, :n].cpu().numpy(), fx[f"step{k}/checked"]), "sampled poses"
+            assert np.array_equal(eng["train_y"][0, :n].cpu().numpy() > 0.5, fx[f"step{k}/labels"]), "labels"
+        else:
+            assert torch.equal(eng["onf_w"][0].cpu(), U.state_from(fx, f"step{k}/before")["w"]), "weights moved on a non-training step"
         if "choice_idx" in var:
             assert np.array_equal(eng["choice_idx"][0].cpu().numpy(), var["choice_idx"]), "sampled indices"
             assert int(eng["choice_used"][0]) == len(var["choice_u"])
@@ -320,15 +323,53 @@ def test_lockstep_against_reference_states(name, impl):
         # Adam moves weights by ~lr*sign(g) where |g| ~ 0 (first steps): compare weights against an absolute
         # bound of 1e-3 of one Adam step, the smooth moments relatively
         compare_state(eng, after, STATE_TOL, skip=("w",))
-        # weights: an Adam step is lr*m^/(sqrt(v^)+eps), |step| <~ 3 lr, so a max-norm gradient error em moves element
-        # i by at most ~lr*em*max|m|/|m_i| (first order; factor 8 of slack) - tight where the gradient is not negligible
-        lr = U.PLANNER_CFGS[name].onf_lr
-        m_ref = np.abs(after["m"].numpy())
-        em = max(U.relerr(eng["onf_m"][0].cpu().numpy(), after["m"].numpy()), 1e-7)
-        bound = lr * np.minimum(3.0, 8 * em * m_ref.max() / np.maximum(m_ref, 1e-30)) + 1e-6
-        dw = np.abs(eng["onf_w"][0].cpu().numpy() - after["w"].numpy())
-        assert bool((dw <= bound).all()), float((dw / bound).max())
-        assert float(dw[m_ref > 1e-2 * m_ref.max()].max()) < 2e-2 * lr
+        if "t_sample" in var:
+            _adam_weight_check(eng, after, U.PLANNER_CFGS[name].onf_lr)
+
+
+def _adam_weight_check(eng, after, lr):
+    """weights after an Adam step: |step| <~ 3 lr, and a max-norm gradient error em moves element i by at most
+    ~lr*em*max|m|/|m_i| (first order; factor 8 of slack) - tight where the gradient is not negligible."""
+    m_ref = np.abs(after["m"].numpy())
+    em = max(U.relerr(eng["onf_m"][0].cpu().numpy(), after["m"].numpy()), 1e-7)
+    bound = lr * np.minimum(3.0, 8 * em * m_ref.max() / np.maximum(m_ref, 1e-30)) + 1e-6
+    dw = np.abs(eng["onf_w"][0].cpu().numpy() - after["w"].numpy())
+    assert bool((dw <= bound).all()), float((dw / bound).max())
+    assert float(dw[m_ref > 1e-2 * m_ref.max()].max()) < 2e-2 * lr
+
+
+@pytest.mark.parametrize("impl", ["fma", "tensor"])
+@pytest.mark.parametrize("name", ["holonomic", "car"])
+def test_warmup_against_reference_states(name, impl):
+    """_init_collision_model (nerf_opt_planner.py:197-200) in lock-step with the reference - every
+    warm-up iteration's 100 uniform field points (:135-141; constrained :173-176) and labels bit-exact, the ONF
+    weights / Adam moments and the ONF optimiser's own step counter after each iteration, then the first planner step
+    after the warm-up (ONF optimiser at step 3, trajectory optimiser at step 0)."""
+    from _gpu_util import compare_state, engine_from_golden
+    fx = U.load(f"warmup_{name}.npz")
+    nw = int(fx["meta/init_collision_points"])
+    eng = engine_from_golden(name, fx, "warm/before", onf_impl=impl, init_collision_points=nw)
+    lr = U.PLANNER_CFGS[name].onf_lr
+    for i in range(int(fx["meta/iterations"])):
+        eng.inject_variates(U.variates_from(fx, f"warm/var{i}"))
+        eng.warmup(1)
+        torch.cuda.synchronize()
+        assert int(eng["train_n"][0]) == nw
+        assert np.array_equal(eng["train_pos"][0, :nw].cpu().numpy(), fx[f"warm/checked{i}"]), "warm-up field points"
+        assert np.array_equal(eng["train_y"][0, :nw].cpu().numpy() > 0.5, fx[f"warm/labels{i}"]), "warm-up labels"
+        after = U.state_from(fx, f"warm/after{i}")
+        compare_state(eng, after, STATE_TOL, skip=("w",))     # incl. onf_step == i + 1, traj_step == step_count == 0
+        _adam_weight_check(eng, after, lr)
+        assert eng.counter("has_prev") == 0
+        # lock-step: continue from the reference's own state
+        from _gpu_util import load_state
+        load_state(eng, after)
+    eng.inject_variates(U.variates_from(fx, "step0/var"))
+    eng.step(1)
+    torch.cuda.synchronize()
+    after = U.state_from(fx, "step0/after")
+    compare_state(eng, after, STATE_TOL, skip=("w",))
+    _adam_weight_check(eng, after, lr)
 
 
 @pytest.mark.parametrize("impl", ["fma", "tensor"])
