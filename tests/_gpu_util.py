@@ -30,7 +30,8 @@ def engine_config(name, fx, rng_mode="inject", problems=1, **over) -> EngineConf
         collision_beta=pc.collision_beta, direction_delta_weight=pc.direction_delta_weight,
         checker="rectangle" if name == "car" else "circle", env_shared=True, max_obstacles=max(64, len(obs)),
         robot_radius=0.3, box=(-0.3, 0.2, -0.3, 0.2), checker_bounds=tuple(float(b) for b in fx["meta/bounds"]),
-        border=tuple(float(b) for b in fx["free/state0/border"]), rng_mode=rng_mode, max_choice_uniforms=4096)
+        border=tuple(float(b) for b in fx["free/state0/border" if "free/state0/border" in fx.files else "warm/before/border"]),
+        rng_mode=rng_mode, max_choice_uniforms=4096)
     kw.update(over)
     return EngineConfig(**kw)
 
