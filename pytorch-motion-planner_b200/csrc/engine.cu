@@ -151,10 +151,12 @@ static int onf_api_launch(const OnfDims &d, OnfArgs &a, int P, int impl, void *s
         return onf_wide_launch(a, x, P, s);
     }
     if ((rc = onf_tc_prepare(d))) return rc;
-    if ((rc = onf_tc_pack(d, a.weights, static_cast<unsigned char *>(scratch), P, s))) return rc;
+    const int variant = onf_tc_variant(d, grad_out ? a.n : 0);
+    if ((rc = onf_tc_pack(d, a.weights, static_cast<unsigned char *>(scratch), P, s, variant))) return rc;
     OnfTcExtra x{};
     x.packed = static_cast<const unsigned char *>(scratch);
     x.grad_out = grad_out;
+    x.variant = variant;
     if (grad_out) NFOPP_CHECK_CUDA(cudaMemsetAsync(grad_out, 0, (size_t)P * d.lay.n_params * sizeof(float), s));
     return onf_tc_launch(a, x, P, s);
 }
@@ -249,6 +251,7 @@ struct nfopp_engine {
     unsigned char *workspace;
     size_t workspace_bytes;
     int impl;                 // 1 FMA, 2 tensor (resolved)
+    int tc_variant;           // tensor path: 0 first generation (onf_tc.cu), 1 streamed single-tile kernel (onf_tcs.cu)
     bool pack_dirty;          // tensor path: onf_wp must be rebuilt from onf_w before the next launch
     int tile_points, tiles;
     StepParams host_sp;
@@ -509,6 +512,7 @@ extern "C" int nfopp_engine_create(const nfopp_planner_config *cfg, void *worksp
         delete e;
         return rc;
     }
+    e->tc_variant = e->impl == 2 ? onf_tc_variant(e->onf, e->dev.NTR) : 0;
     e->host_sp = StepParams{};
     e->sp_dirty = true;
     e->pack_dirty = true;
@@ -580,7 +584,7 @@ extern "C" int nfopp_engine_set_counter(nfopp_engine *e, int which, int64_t valu
 static int ensure_packed(nfopp_engine *e, cudaStream_t s) {
     if (e->impl < 2 || !e->pack_dirty) return NFOPP_OK;
     int rc = e->impl == 3 ? onf_wide_pack(e->onf, e->dev.onf_w, e->dev.onf_wp, e->dev.P, s)
-                          : onf_tc_pack(e->onf, e->dev.onf_w, e->dev.onf_wp, e->dev.P, s);
+                          : onf_tc_pack(e->onf, e->dev.onf_w, e->dev.onf_wp, e->dev.P, s, e->tc_variant);
     if (rc) return rc;
     e->pack_dirty = false;
     e->launches += 1;
@@ -598,6 +602,7 @@ static int engine_onf(nfopp_engine *e, const EngineDev &d, OnfArgs &a, cudaStrea
     }
     OnfTcExtra x{};
     x.packed = d.onf_wp;
+    x.variant = e->tc_variant;
     return onf_tc_launch(a, x, d.P, s);
 }
 
@@ -615,6 +620,7 @@ static int enqueue_train(nfopp_engine *e, const EngineDev &d, bool warm, cudaStr
         OnfTcExtra x{};
         x.packed = d.onf_wp; x.adam_w = d.onf_w; x.adam_m = d.onf_m; x.adam_v = d.onf_v; x.packed_out = d.onf_wp;
         x.w1 = w1; x.beta2 = beta2; x.w2 = w2; x.eps = eps; x.warm = warm;
+        x.variant = e->tc_variant;
         if ((rc = onf_tc_launch(a, x, d.P, s))) return rc;
         if (ev) {
             NFOPP_CHECK_CUDA(cudaEventRecord(ev[0], s));

@@ -42,13 +42,25 @@ struct OnfTcExtra {
     unsigned char *packed_out;     // operand copy rewritten by the fused Adam
     float w1, beta2, w2, eps;      // 1-beta1, beta2, 1-beta2, eps; step size / bias correction come from StepParams
     int warm;                      // warm-up iteration: ignore StepParams::do_train
+    int variant;                   // 0: first generation (onf_tc.cu, bf16 operands, resident weights); 1: streamed (onf_tcs.cu, fp16)
 };
 
 bool onf_tc_supported(const OnfDims &d);            // 2 hidden layers, hidden <= 111, f_in <= 224
 size_t onf_tc_packed_bytes(const OnfDims &d);       // per problem
 int onf_tc_prepare(const OnfDims &d);
-int onf_tc_pack(const OnfDims &d, const float *weights, unsigned char *packed, int P, cudaStream_t stream);
+int onf_tc_pack(const OnfDims &d, const float *weights, unsigned char *packed, int P, cudaStream_t stream, int variant);
 int onf_tc_launch(const OnfArgs &a, const OnfTcExtra &x, int P, cudaStream_t stream);
+// second generation (onf_tcs.cu): whole problem in one 224-point tile, weights streamed, fp16 hi/lo operands (forward three
+// passes, backward one).  Same packed layout and size as the first generation, different element type: the operand copy
+// must be packed by the variant that reads it.
+bool onf_tcs_supported(const OnfDims &d);
+int onf_tcs_tile_points();
+int onf_tcs_prepare(const OnfDims &d);
+int onf_tcs_pack(const OnfDims &d, const float *weights, unsigned char *packed, int P, cudaStream_t stream);
+int onf_tcs_launch(const OnfArgs &a, const OnfTcExtra &x, int P, cudaStream_t stream);
+// which generation serves a tensor-path call whose weight-gradient launches see at most n_wgrad points per problem
+// (0: no weight gradients).  NFOPP_TC_LEGACY=1 in the environment forces the first generation.
+int onf_tc_variant(const OnfDims &d, int n_wgrad);
 
 // wide / deep networks and large point sets (onf_wide.cu): per-layer grouped GEMMs on tcgen05 with streamed weights
 struct OnfWideExtra {

@@ -27,6 +27,8 @@
 // of the problem; the epilogue streams them out once - either as a plain gradient or straight through Adam
 // (torch.optim.Adam, planner_factory.py:68), which also rewrites the bf16 hi/lo operand copy of the weights.
 // Nothing like the FMA path's per-tile gradient partials ever reaches HBM.
+#include <stdlib.h>
+
 #include "onf.cuh"
 #include "tc05.cuh"
 
@@ -914,7 +916,16 @@ size_t onf_tc_packed_bytes(const OnfDims &d) {
     return tc_make_dims(d, &t) ? (size_t)t.packed_bytes : 0;
 }
 
+int onf_tc_variant(const OnfDims &d, int n_wgrad) {
+    static const bool legacy = [] { const char *e = getenv("NFOPP_TC_LEGACY"); return e && e[0] == '1'; }();
+    return (!legacy && onf_tcs_supported(d) && n_wgrad <= onf_tcs_tile_points()) ? 1 : 0;
+}
+
 int onf_tc_prepare(const OnfDims &d) {
+    if (onf_tcs_supported(d)) {
+        const int rc = onf_tcs_prepare(d);
+        if (rc) return rc;
+    }
     TcDims t;
     NFOPP_REQUIRE(tc_make_dims(d, &t), "onf(tensor): needs 2 hidden layers, hidden <= 111, f_in <= 224 (hidden=%d layers=%d)", d.H,
                   d.L);
@@ -922,7 +933,8 @@ int onf_tc_prepare(const OnfDims &d) {
     return NFOPP_OK;
 }
 
-int onf_tc_pack(const OnfDims &d, const float *weights, unsigned char *packed, int P, cudaStream_t stream) {
+int onf_tc_pack(const OnfDims &d, const float *weights, unsigned char *packed, int P, cudaStream_t stream, int variant) {
+    if (variant == 1) return onf_tcs_pack(d, weights, packed, P, stream);
     TcPackArgs a{};
     a.d = d;
     NFOPP_REQUIRE(tc_make_dims(d, &a.t), "onf(tensor): unsupported network shape");
@@ -936,6 +948,7 @@ int onf_tc_pack(const OnfDims &d, const float *weights, unsigned char *packed, i
 }
 
 int onf_tc_launch(const OnfArgs &o, const OnfTcExtra &x, int P, cudaStream_t stream) {
+    if (x.variant == 1) return onf_tcs_launch(o, x, P, stream);
     OnfTcArgs a{};
     a.d = o.d;
     NFOPP_REQUIRE(tc_make_dims(o.d, &a.t), "onf(tensor): unsupported network shape");

@@ -1,0 +1,978 @@
+// onf_tcs.cu - K2, fused tensor path, second generation: the whole problem in ONE tile, weights STREAMED.
+//
+// onf_tc.cu keeps a problem's hidden-layer weights resident in shared memory (150 KB), which leaves room for only two
+// 32-point tiles in flight: ~1000 tcgen05.mma of N = 32 per problem and 14 latency-bound handshakes per 32 points.  Here
+// the operand roles are the same (HIDDEN index on the UMMA M axis = TMEM lanes, POINT index on N) but
+//   * ALL points of the problem (<= 224: 209 training samples, 199 candidates, 99 path points) form ONE tile, so every
+//     GEMM of onf_model.py:33-50 and of its backward is a handful of 128 x Nt x 16 MMAs (~190 per training call) and every
+//     epilogue stage runs once per problem on all 16 worker warps;
+//   * the weights are not resident: a producer warp streams the packed operand copy (L2-resident, 150 KB) through an
+//     8-stage ring of K = 16 chunks for the forward GEMMs and as three 25 KB blocks for the backward GEMMs;
+//   * operands are fp16 hi/lo: the FORWARD products stay three-pass (hi*hi + lo*hi + hi*lo, ~1e-7) because the ReLU
+//     masks must not flip against the fp32 reference, the BACKWARD products (masks already fixed: input gradients and
+//     weight gradients, two thirds of the flops) are ONE pass of hi parts with the upstream gradient scaled to [1, 2) by
+//     a power of two per tile (fp16 has no range to spare at dL/dz ~ 1/N) and unscaled in fp32 in the epilogues;
+//   * weight gradients are produced once per problem (K = all points), so their TMEM accumulators need not persist
+//     across tiles: dW2 and the two halves of dW1 take 336 columns next to ONE 224-column work accumulator.
+//
+//   fwd1   D1[j,n]  = sum_k W1p[j,k] E[n,k]     A = W1p chunk (K-major, ring)   B = E chunk  (K-major, ring)   3 passes
+//   fwd2   D2[i,n]  = sum_j W2p[i,j] H1[j,n]    A = W2p chunk (K-major, ring)   B = H1       (MN-major)        3 passes
+//   wgrad2 dW2[i,j] = sum_n gH2[i,n] H1[j,n]    A = gH2       (K-major)         B = H1 hi    (K-major)         1 pass
+//   dgrad2 gD1[j,n] = sum_i W2p[i,j] gH2[i,n]   A = W2p hi    (MN-major, slot)  B = gH2      (MN-major)        1 pass
+//   dgrad1 gE[k,n]  = sum_j W1p[j,k] gH1[j,n]   A = W1p hi    (MN-major, slot)  B = gH1      (MN-major)        1 pass, 2 blocks
+//   wgrad1 dW1[j,k] = sum_n gH1[j,n] E[n,k]     A = gH1       (K-major)         B = E^T      (K-major)         1 pass, 2 blocks
+//
+// Row H of W1p holds the skip weights w_out[H:] (onf_model.py:48-49) exactly as in onf_tc.cu, so the skip term, its input
+// gradient and its weight gradient fall out of fwd1 / dgrad1 / wgrad1.  Biases, ReLU, logit, dL/dz (BCE
+// nerf_opt_planner.py:85-90, path terms constrained...:87-97), the Fourier / heading encoding and its backward run on
+// the CUDA cores, one TMEM lane (hidden unit or feature) per thread.  The epilogue stages the gradient blob in shared
+// memory and streams it through Adam (planner_factory.py:68), rewriting the fp16 operand copy - as onf_tc.cu does.
+//
+// Supported: 2 hidden layers, hidden <= 111, f_in <= 224 (the reference's network shapes).  Forward and input-gradient
+// calls take any point count (tiles of 224); weight gradients need count <= 224 (the planner's 209; larger API calls
+// go to the first-generation kernel).
+#include "onf.cuh"
+#include "tc05.cuh"
+
+namespace nfopp {
+using namespace tc05;
+
+// optional phase trace (build with -DNFOPP_TC_TRACE; scripts/tcs_trace.py): clock64 stamps of worker thread 0, the issue
+// warp and the weight-stream warp of the first and last CTA
+#ifdef NFOPP_TC_TRACE
+__device__ long long g_ts_trace[3][2][3][64];   // [launch kind: fwd | train | path][first / last CTA][worker | issuer | producer][slot]
+#define TS_TRACE(role, slot)                                                                                              \
+    do {                                                                                                                \
+        if ((threadIdx.x & 31) == 0 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1) && (slot) < 64 &&               \
+            ((role) != 0 || threadIdx.x == 0))                                                                          \
+            g_ts_trace[!a.want_bwd ? 0 : ((a.grad_out || a.adam_w) ? 1 : 2)][blockIdx.x == 0 ? 0 : 1][(role)][(slot)] = clock64(); \
+    } while (0)
+#else
+#define TS_TRACE(role, slot) do { } while (0)
+#endif
+
+constexpr int TS_WORKERS = 512;                 // 16 epilogue / encoding warps
+constexpr int TS_THREADS = TS_WORKERS + 64;     // + MMA-issue warp + weight-stream warp
+constexpr int TS_NT = 224;                      // points per tile
+constexpr uint32_t TS_SPT = TS_NT * 16;         // S_row of the point-indexed operand buffers [hidden / 8][point / 8][8][8]
+constexpr int TS_WST = 8;                       // weight ring stages (K = 16 chunk of W, hi + lo)
+constexpr int TS_EST = 4;                       // encoding ring slots (16 features x Nt points, hi + lo)
+constexpr uint32_t TS_TM_A = 0, TS_TM_DW2 = TS_NT;   // TMEM columns: work accumulator | dW2 [KH] | dW1 block 0 [FB0]
+constexpr int TS_GX_BYTES = 4 * TS_NT * 3 * 4;  // per-lane-quarter partials of the input gradient
+
+struct TsDims {
+    int F, A, FIN, H, K1, KH, MB, FB0;           // MB feature blocks of FB0 (last one shorter) for dgrad1 / wgrad1
+    int S_colW, w1_half, w2_half;                // packed operand copy: [W1 hi | W1 lo | W2 hi | W2 lo], each [k / 8][row][8]
+    int h1_half, e_slot, w_stage, b_slot, S_ET;
+    int off_h1h, off_h1l, off_r, off_w, off_gx, off_misc, misc_floats, smem_bytes, packed_bytes;
+};
+
+__host__ __device__ inline int ts_ru16(int x) { return (x + 15) / 16 * 16; }
+__host__ __device__ inline int ts_max(int a, int b) { return a > b ? a : b; }
+
+__host__ __device__ inline bool ts_make_dims(const OnfDims &d, TsDims *out) {
+    TsDims t{};
+    t.F = d.lay.f_pos; t.A = d.lay.n_angle; t.FIN = d.lay.f_in; t.H = d.H;
+    t.K1 = ts_ru16(t.FIN); t.KH = ts_ru16(t.H + 1);
+    t.MB = t.K1 > 128 ? 2 : 1;
+    t.FB0 = t.MB == 2 ? ts_ru16(t.K1 / 2) : t.K1;
+    t.S_colW = t.KH * 16;
+    t.w1_half = (t.K1 / 8) * t.S_colW;
+    t.w2_half = (t.KH / 8) * t.S_colW;
+    t.h1_half = (t.KH / 8) * (int)TS_SPT;
+    t.S_ET = t.FB0 * 16;
+    t.e_slot = 4 * (int)TS_SPT;                  // 2 feature octets x (hi, lo)
+    t.w_stage = 4 * t.S_colW;                    // 2 column octets x (hi, lo)
+    t.b_slot = 16 * t.S_colW;                    // a 128-row MN-major A operand never reads past its slot
+    t.off_h1h = 0;
+    t.off_h1l = t.h1_half;
+    t.off_r = t.off_h1l + ts_max(t.h1_half, (TS_NT / 8) * t.S_ET);            // H1 lo, later E^T
+    t.off_w = t.off_r + ts_max(TS_EST * t.e_slot, t.h1_half);                 // encoding ring, later gH2
+    t.off_gx = t.off_w + t.b_slot;                                            // (slot 1 is dead when gx partials are written)
+    t.off_misc = t.off_w + ts_max(ts_max(TS_WST * t.w_stage, 2 * t.b_slot), t.b_slot + TS_GX_BYTES);
+    t.misc_floats = 3 * t.K1 + 32 + 3 * t.KH + 8 + 10 * TS_NT + 32;
+    t.smem_bytes = t.off_misc + t.misc_floats * 4 + 64 * 8 + 16;
+    t.packed_bytes = 2 * t.w1_half + 2 * t.w2_half;
+    *out = t;
+    // the epilogue stages the whole gradient blob (+ 20 KB of per-unit partial sums) over the dead operand buffers
+    const int stage_bytes = ((d.lay.n_params + 31) / 32 * 32 + 10 * 512) * 4;
+    return d.L == 2 && t.KH <= 128 && t.K1 <= 256 && t.H >= 8 && (int)TS_TM_DW2 + t.KH + t.FB0 <= 512 &&
+           t.smem_bytes <= 227 * 1024 && stage_bytes <= t.off_misc;
+}
+
+struct OnfTsArgs {
+    OnfDims d;
+    TsDims t;
+    const float *weights;          // [P, n_params] fp32 blob
+    const unsigned char *packed;   // [P, packed_bytes] fp16 hi/lo operand copy of W1p / W2p
+    const float *x;
+    const int32_t *count;
+    const StepParams *sp;
+    int n, x_stride;
+    int want_bwd;
+    int gbar_mode;
+    const float *gz, *aux;
+    float wc, beta;
+    float *z_out, *gx_out;
+    float *grad_out;
+    float *adam_w, *adam_m, *adam_v;
+    unsigned char *packed_out;
+    float w1, beta2, w2, eps;
+    int warm;
+};
+
+struct TsPackArgs {
+    OnfDims d;
+    TsDims t;
+    const float *weights;
+    unsigned char *packed;
+};
+
+// fp32 blob -> packed fp16 hi/lo operands (API entry points and engine start; the training kernel keeps the copy current)
+__global__ void __launch_bounds__(256) onf_tcs_pack_kernel(const TsPackArgs a) {
+    const int p = blockIdx.y;
+    const TsDims &t = a.t;
+    const nfopp_onf_layout &L = a.d.lay;
+    const float *W = a.weights + (size_t)p * L.n_params;
+    unsigned char *out = a.packed + (size_t)p * t.packed_bytes;
+    const int rows = t.KH;
+    const int n1 = (t.K1 / 8) * rows, n2 = (t.KH / 8) * rows;
+    for (int item = blockIdx.x * blockDim.x + threadIdx.x; item < n1 + n2; item += gridDim.x * blockDim.x) {
+        const bool second = item >= n1;
+        const int it = second ? item - n1 : item;
+        const int oct = it / rows, r = it - oct * rows;
+        float v[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            const int c = oct * 8 + e;
+            float val = 0.f;
+            if (!second) {
+                if (c < t.FIN) {
+                    if (r < t.H) val = W[L.off_w[0] + r * t.FIN + c];
+                    else if (r == t.H) val = W[L.off_w_out + t.H + c];
+                }
+            } else if (r < t.H && c < t.H) {
+                val = W[L.off_w[1] + r * t.H + c];
+            }
+            v[e] = val;
+        }
+        uint4 hi, lo;
+        split8h(v, hi, lo);
+        unsigned char *base = out + (second ? 2 * t.w1_half : 0);
+        const int half = second ? t.w2_half : t.w1_half;
+        const int off = oct * t.S_colW + (r / 8) * 128 + (r % 8) * 16;
+        *reinterpret_cast<uint4 *>(base + off) = hi;
+        *reinterpret_cast<uint4 *>(base + half + off) = lo;
+    }
+}
+
+// ---- device helpers ------------------------------------------------------------------------------------
+// column sums over the 32 lanes of a warp for 16 columns: lane 2c (and 2c+1) returns sum_lanes v[c]
+__device__ __forceinline__ float ts_colsum16(float (&v)[16], int lane) {
+#pragma unroll
+    for (int o = 16; o >= 2; o >>= 1) {
+        const bool up = (lane & o) != 0;
+        const int h = o >> 1;
+#pragma unroll
+        for (int c = 0; c < h; ++c) {
+            const float keep = up ? v[c + h] : v[c];
+            const float send = up ? v[c] : v[c + h];
+            v[c] = keep + __shfl_xor_sync(0xffffffffu, send, o);
+        }
+    }
+    return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 1);
+}
+__device__ __forceinline__ float ts_feature_arg(float pa, float pb, float pc, float u0, float x1) {
+    return fmaf(x1, pb, fmaf(u0, pa, pc));
+}
+__device__ __forceinline__ float ts_reduce_2pi(float x) {
+    const float k = rintf(x * 0.15915494309189535f);
+    float r = fmaf(k, -6.2831854820251465f, x);
+    return fmaf(k, 1.7484555e-7f, r);
+}
+
+struct TsShared {
+    unsigned char *h1h, *h1l, *r, *w, *gxp;
+    // per input feature f < K1: arg = x1 * pb + u0 * pa + pc  (x1 = u1 for Fourier features, theta for heading features;
+    // pc carries the bias and +pi/2 for cosine features, so every feature is sin(arg) with derivative cos(arg))
+    float *pa, *pb, *pc, *ang_b, *b1, *b2, *w3h, *scal, *in0, *aux, *skip, *gbar, *zp, *red;
+    uint64_t *wfull, *wempty, *efull, *eempty, *bfull, *bempty, *ready, *done, *tile_free;
+    uint32_t *tmem_slot;
+    __device__ TsShared(unsigned char *base, const TsDims &t) {
+        h1h = base + t.off_h1h; h1l = base + t.off_h1l; r = base + t.off_r; w = base + t.off_w; gxp = base + t.off_gx;
+        float *f = reinterpret_cast<float *>(base + t.off_misc);
+        pa = f; f += t.K1;
+        pb = f; f += t.K1;
+        pc = f; f += t.K1;
+        ang_b = f; f += 32;
+        b1 = f; f += t.KH;
+        b2 = f; f += t.KH;
+        w3h = f; f += t.KH;
+        scal = f; f += 8;                           // [0] b3, [1] S (gradient operand scale), [2] 1 / S
+        in0 = f; f += 3 * TS_NT;                    // u0 | u1 | theta
+        aux = f; f += TS_NT;
+        skip = f; f += TS_NT;
+        gbar = f; f += TS_NT;
+        zp = f; f += 4 * TS_NT;
+        red = f; f += 32;
+        uint64_t *b = reinterpret_cast<uint64_t *>(f);
+        wfull = b; b += TS_WST;
+        wempty = b; b += TS_WST;
+        efull = b; b += TS_EST;
+        eempty = b; b += TS_EST;
+        bfull = b; b += 2;
+        bempty = b; b += 2;
+        ready = b++; done = b++; tile_free = b++;
+        tmem_slot = reinterpret_cast<uint32_t *>(b);
+    }
+};
+
+// three-pass split product: D (+)= Ahi*Bhi + Alo*Bhi + Ahi*Blo
+__device__ __forceinline__ void ts_mma3(uint32_t tmem_d, uint64_t ah, uint64_t al, uint64_t bh, uint64_t bl, uint32_t idesc,
+                                        bool accumulate, uint32_t issue) {
+    mma_bf16(tmem_d, ah, bh, idesc, accumulate ? 1u : 0u, issue);
+    mma_bf16(tmem_d, al, bh, idesc, 1u, issue);
+    mma_bf16(tmem_d, ah, bl, idesc, 1u, issue);
+}
+// K loop of a single-pass GEMM, descriptors advanced by constant strides
+__device__ __forceinline__ void ts_kloop1(uint32_t tmem_d, uint64_t a, uint64_t b, uint32_t a_step, uint32_t b_step, int ksteps,
+                                          uint32_t idesc, uint32_t issue) {
+    const uint64_t da = a_step >> 4, db = b_step >> 4;
+#pragma unroll 1
+    for (int ks = 0; ks < ksteps; ++ks) {
+        mma_bf16(tmem_d, a, b, idesc, ks > 0 ? 1u : 0u, issue);
+        a += da; b += db;
+    }
+}
+
+__device__ __forceinline__ void ts_worker_sync() { asm volatile("bar.sync 1, %0;" ::"r"(TS_WORKERS) : "memory"); }
+// a worker warp has finished writing MMA operands (generic proxy) / reading TMEM: publish to the async side
+__device__ __forceinline__ void ts_signal(uint64_t *bar) {
+    fence_proxy_async();
+    fence_before_sync();
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0) mbar_arrive(bar);
+}
+__device__ __forceinline__ void ts_wait(uint64_t *bar, uint32_t use) {     // wait for completion number `use` (0-based)
+    mbar_wait(bar, use & 1u);
+    fence_after_sync();
+}
+
+// store 16 consecutive columns (col0 .. col0+15) of row `row` into a [row / 8][col / 8][row % 8][col % 8] operand buffer
+__device__ __forceinline__ void ts_store_row16_hl(unsigned char *hi_buf, unsigned char *lo_buf, int row, int col0, const float *v) {
+    uint4 h0, l0, h1, l1;
+    split8h(v, h0, l0);
+    split8h(v + 8, h1, l1);
+    const int off = (row >> 3) * TS_SPT + (col0 >> 3) * 128 + (row & 7) * 16;
+    *reinterpret_cast<uint4 *>(hi_buf + off) = h0;
+    *reinterpret_cast<uint4 *>(hi_buf + off + 128) = h1;
+    *reinterpret_cast<uint4 *>(lo_buf + off) = l0;
+    *reinterpret_cast<uint4 *>(lo_buf + off + 128) = l1;
+}
+__device__ __forceinline__ void ts_store_row16_h(unsigned char *hi_buf, int row, int col0, const float *v) {
+    const int off = (row >> 3) * TS_SPT + (col0 >> 3) * 128 + (row & 7) * 16;
+    *reinterpret_cast<uint4 *>(hi_buf + off) = pack8h(v);
+    *reinterpret_cast<uint4 *>(hi_buf + off + 128) = pack8h(v + 8);
+}
+
+// ---- the weight-stream warp (one elected lane): forward ring, then the three backward blocks -------------------------
+__device__ __forceinline__ void ts_producer(const OnfTsArgs &a, const TsShared &s, const unsigned char *src, int n_tiles, bool want_bwd) {
+    const TsDims &t = a.t;
+    const int c1 = t.K1 / 16, c2 = t.KH / 16;
+    uint32_t wc = 0, b0 = 0, b1 = 0;
+    for (int tile = 0; tile < n_tiles; ++tile) {
+        if (tile > 0 && want_bwd) ts_wait(s.tile_free, tile - 1);       // slots / gx partials of the previous tile are dead
+        for (int c = 0; c < c1 + c2; ++c, ++wc) {
+            const uint32_t st = wc % TS_WST, k = wc / TS_WST;
+            if (k > 0) ts_wait(s.wempty + st, k - 1);
+            unsigned char *dst = s.w + st * t.w_stage;
+            const bool second = c >= c1;
+            const unsigned char *g = src + (second ? 2 * t.w1_half : 0) + (size_t)(second ? c - c1 : c) * 2 * t.S_colW;
+            const int half = second ? t.w2_half : t.w1_half;
+            mbar_expect_tx(s.wfull + st, (uint32_t)t.w_stage);
+            bulk_g2s(dst, g, 2 * t.S_colW, s.wfull + st);
+            bulk_g2s(dst + 2 * t.S_colW, g + half, 2 * t.S_colW, s.wfull + st);
+        }
+        TS_TRACE(2, 1);
+        if (!want_bwd) continue;
+        // every forward MMA that reads the ring has completed before the ring is reused as two big slots
+        for (uint32_t c = wc > TS_WST ? wc - TS_WST : 0; c < wc; ++c) ts_wait(s.wempty + c % TS_WST, c / TS_WST);
+        TS_TRACE(2, 2);
+        mbar_expect_tx(s.bfull + 0, (uint32_t)t.w2_half);
+        bulk_g2s(s.w, src + 2 * t.w1_half, t.w2_half, s.bfull + 0);                     // W2 hi -> slot 0
+        const int len0 = t.FB0 / 8 * t.S_colW;
+        mbar_expect_tx(s.bfull + 1, (uint32_t)len0);
+        bulk_g2s(s.w + t.b_slot, src, len0, s.bfull + 1);                               // W1 hi, feature block 0 -> slot 1
+        if (t.MB == 2) {
+            ts_wait(s.bempty, b0++);                                                    // dgrad2 has read slot 0
+            const int len1 = (t.K1 - t.FB0) / 8 * t.S_colW;
+            mbar_expect_tx(s.bfull + 0, (uint32_t)len1);
+            bulk_g2s(s.w, src + len0, len1, s.bfull + 0);                               // W1 hi, feature block 1 -> slot 0
+        }
+        TS_TRACE(2, 3);
+        (void)b1;
+    }
+}
+
+// ---- the MMA-issue warp ----------------------------------------------------------------------------------------------
+__device__ __forceinline__ void ts_issuer(const OnfTsArgs &a, const TsShared &s, uint32_t tmem, int cnt, int n_tiles, bool want_bwd,
+                                          bool want_wgrad) {
+    const TsDims &t = a.t;
+    const uint32_t lead = elect_one();
+    TS_TRACE(1, 0);
+    const uint32_t h1h = smem_u32(s.h1h), h1l = smem_u32(s.h1l), rr = smem_u32(s.r), ww = smem_u32(s.w);
+    const uint32_t tmA = tmem + TS_TM_A, tmDW2 = tmem + TS_TM_DW2, tmDW1a = tmem + TS_TM_DW2 + t.KH;
+    const int c1 = t.K1 / 16, c2 = t.KH / 16;
+    uint32_t wc = 0, ec = 0, nready = 0, nb0 = 0, nb1 = 0;
+    for (int tile = 0; tile < n_tiles; ++tile) {
+        const int Nt = ts_ru16(min(TS_NT, cnt - tile * TS_NT));
+        // fwd1: D1[j,n] (+)= W1p[j,k] E[n,k], one K = 16 chunk of the weight ring and of the encoding ring at a time
+        for (int ks = 0; ks < c1; ++ks, ++wc, ++ec) {
+            const uint32_t st = wc % TS_WST, sl = ec % TS_EST;
+            ts_wait(s.wfull + st, wc / TS_WST);
+            ts_wait(s.efull + sl, ec / TS_EST);
+            const uint32_t wb = ww + st * t.w_stage, eb = rr + sl * t.e_slot;
+            ts_mma3(tmA, desc_kmajor(wb, 128, t.S_colW), desc_kmajor(wb + 2 * t.S_colW, 128, t.S_colW), desc_kmajor(eb, 128, TS_SPT),
+                    desc_kmajor(eb + 2 * TS_SPT, 128, TS_SPT), instr_desc_f16(128, Nt, 0, 0), ks > 0, lead);
+            mma_commit(s.wempty + st, lead);
+            mma_commit(s.eempty + sl, lead);
+        }
+        mma_commit(s.done, lead);
+        TS_TRACE(1, 1);
+        // fwd2: D2[i,n] = W2p[i,j] H1[j,n]
+        ts_wait(s.ready, nready++);
+        TS_TRACE(1, 2);
+        for (int ks = 0; ks < c2; ++ks, ++wc) {
+            const uint32_t st = wc % TS_WST;
+            ts_wait(s.wfull + st, wc / TS_WST);
+            const uint32_t wb = ww + st * t.w_stage;
+            ts_mma3(tmA, desc_kmajor(wb, 128, t.S_colW), desc_kmajor(wb + 2 * t.S_colW, 128, t.S_colW),
+                    desc_mnmajor(h1h + ks * 2 * TS_SPT, TS_SPT, 128), desc_mnmajor(h1l + ks * 2 * TS_SPT, TS_SPT, 128),
+                    instr_desc_f16(128, Nt, 0, 1), ks > 0, lead);
+            mma_commit(s.wempty + st, lead);
+        }
+        mma_commit(s.done, lead);
+        TS_TRACE(1, 3);
+        if (!want_bwd) continue;
+        // wgrad2: dW2[i,j] = gH2[i,n] H1[j,n];   dgrad2: gD1[j,n] = W2p[i,j] gH2[i,n]     (gH2 lives in the old encoding ring)
+        ts_wait(s.ready, nready++);
+        TS_TRACE(1, 4);
+        ts_wait(s.bfull + 0, nb0++);
+        TS_TRACE(1, 5);
+        if (want_wgrad)
+            ts_kloop1(tmDW2, desc_kmajor(rr, TS_SPT, 128), desc_kmajor(h1h, TS_SPT, 128), 256, 256, Nt / 16, instr_desc_f16(128, t.KH, 0, 0),
+                      lead);
+        ts_kloop1(tmA, desc_mnmajor(ww, 128, t.S_colW), desc_mnmajor(rr, TS_SPT, 128), 256, 2 * TS_SPT, c2, instr_desc_f16(128, Nt, 1, 1), lead);
+        mma_commit(s.bempty, lead);
+        mma_commit(s.done, lead);
+        TS_TRACE(1, 6);
+        // dgrad1, feature block 0: gE[k,n] = W1p[j,k] gH1[j,n]      (gH1 in place over H1 hi)
+        ts_wait(s.ready, nready++);
+        TS_TRACE(1, 7);
+        ts_wait(s.bfull + 1, nb1++);
+        TS_TRACE(1, 8);
+        ts_kloop1(tmA, desc_mnmajor(ww + t.b_slot, 128, t.S_colW), desc_mnmajor(h1h, TS_SPT, 128), 256, 2 * TS_SPT, c2,
+                  instr_desc_f16(128, Nt, 1, 1), lead);
+        mma_commit(s.done, lead);
+        for (int mb = 0; mb < t.MB; ++mb) {
+            ts_wait(s.ready, nready++);                 // block mb of gE consumed, E^T of block mb written
+            TS_TRACE(1, 9 + 2 * mb);
+            if (want_wgrad)                             // wgrad1: dW1[j, block mb] = gH1[j,n] E[n, block mb]
+                ts_kloop1(mb == 0 ? tmDW1a : tmA, desc_kmajor(h1h, TS_SPT, 128), desc_kmajor(h1l, 128, t.S_ET), 256, 2 * t.S_ET, Nt / 16,
+                          instr_desc_f16(128, min(t.FB0, t.K1 - mb * t.FB0), 0, 0), lead);
+            if (mb + 1 < t.MB) {
+                ts_wait(s.bfull + 0, nb0++);
+                ts_kloop1(tmA, desc_mnmajor(ww, 128, t.S_colW), desc_mnmajor(h1h, TS_SPT, 128), 256, 2 * TS_SPT, c2,
+                          instr_desc_f16(128, Nt, 1, 1), lead);
+            }
+            if (want_wgrad || mb + 1 < t.MB) mma_commit(s.done, lead);
+            TS_TRACE(1, 10 + 2 * mb);
+        }
+    }
+}
+
+// Thread layout: 18 warps.  Warps 0..15 are workers: warp = 4*cq + q, q = TMEM lane quarter (rows 32q..32q+31), cq = which
+// 16-column chunks of the tile (cq, cq+4, ...); a thread owns one hidden unit / feature (`row`).  Warp 16 issues every
+// tcgen05.mma, warp 17 streams the weights.
+__global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs a) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const OnfDims &d = a.d;
+    const TsDims &t = a.t;
+    const nfopp_onf_layout &L = d.lay;
+    const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (a.sp && !a.warm && !a.sp->do_train) return;    // engine: not a field-training step
+    const int cnt = a.count ? a.count[p] : a.n;
+    if (cnt <= 0) return;
+    const bool want_bwd = a.want_bwd != 0;
+    const bool want_wgrad = want_bwd && (a.grad_out != nullptr || a.adam_w != nullptr);
+    const bool want_gx = want_bwd && a.gx_out != nullptr;
+    const int F = t.F, FIN = t.FIN, H = t.H, K1 = t.K1, KH = t.KH;
+    const bool is_issuer = warp == TS_WORKERS / 32, is_producer = warp == TS_WORKERS / 32 + 1;
+    const int n_tiles = (cnt + TS_NT - 1) / TS_NT;
+
+    TsShared s(smem_raw, t);
+    const float *W = a.weights + (size_t)p * L.n_params;
+    TS_TRACE(0, 0);
+
+    // ---- one-time setup: barriers, TMEM, per-feature / per-unit fp32 parameters ----
+    if (tid == 0) {
+        for (int i = 0; i < TS_WST; ++i) { mbar_init(s.wfull + i, 1); mbar_init(s.wempty + i, 1); }
+        for (int i = 0; i < TS_EST; ++i) { mbar_init(s.efull + i, TS_WORKERS / 32); mbar_init(s.eempty + i, 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(s.bfull + i, 1); mbar_init(s.bempty + i, 1); }
+        mbar_init(s.ready, TS_WORKERS / 32);
+        mbar_init(s.done, 1);
+        mbar_init(s.tile_free, TS_WORKERS / 32);
+        fence_mbar_init();
+    }
+    if (is_issuer) tmem_alloc(s.tmem_slot, 512);
+    if (is_producer && lane == 0 && a.adam_w != nullptr && want_bwd) {
+        // the Adam epilogue streams this problem's w / m / v once: start pulling them into L2 now, under the compute
+        const size_t po = (size_t)p * L.n_params;
+        const uint32_t bytes = (uint32_t)(L.n_params * sizeof(float)) & ~15u;
+        bulk_prefetch_l2(a.adam_w + po, bytes);
+        bulk_prefetch_l2(a.adam_m + po, bytes);
+        bulk_prefetch_l2(a.adam_v + po, bytes);
+    }
+    for (int f = tid; f < K1; f += TS_THREADS) {
+        float pa = 0.f, pb = 0.f, pc = 0.f;
+        if (f < F) {
+            pa = W[L.off_enc_w + 2 * f];
+            pb = W[L.off_enc_w + 2 * f + 1];
+            pc = W[L.off_enc_b + f] + ((d.use_cos && f >= 100) ? 1.57079632679489662f : 0.f);
+        } else if (f < FIN) {
+            const int k = f - F;
+            const float b = W[L.off_ang_b + k], fr = W[L.off_ang_f + k];
+            s.ang_b[k] = b;
+            pb = fr;
+            pc = fmaf(b, fr, k >= t.A / 2 ? 1.57079632679489662f : 0.f);
+        }
+        s.pa[f] = pa; s.pb[f] = pb; s.pc[f] = pc;
+    }
+    for (int i = tid; i < KH; i += TS_THREADS) {
+        s.b1[i] = i < H ? W[L.off_b[0] + i] : 0.f;
+        s.b2[i] = i < H ? W[L.off_b[1] + i] : 0.f;
+        s.w3h[i] = i < H ? W[L.off_w_out + i] : 0.f;
+    }
+    if (tid == 0) { s.scal[0] = W[L.off_b_out]; s.scal[1] = 1.f; s.scal[2] = 1.f; }
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem = *s.tmem_slot;
+    TS_TRACE(0, 1);
+
+    // worker identity (the two service warps compute harmless values)
+    const int q = warp & 3, cq = (warp >> 2) & 3;
+    const int row = q * 32 + lane;
+    const uint32_t tm_lane = tmem + ((uint32_t)(q * 32) << 16);
+    // thread-local gradient accumulators (hidden unit `row`; features row of block 0 / block 1; point tid)
+    float acc_db1 = 0.f, acc_db2 = 0.f, acc_dw3 = 0.f, acc_db3 = 0.f;
+    float fa0 = 0.f, fb0 = 0.f, fc0 = 0.f, fa1 = 0.f, fb1 = 0.f, fc1 = 0.f;
+
+    if (is_issuer) {
+        ts_issuer(a, s, tmem, cnt, n_tiles, want_bwd, want_wgrad);
+    } else if (is_producer) {
+        if (lane == 0) ts_producer(a, s, a.packed + (size_t)p * t.packed_bytes, n_tiles, want_bwd);
+    } else {
+        const uint32_t tA = tm_lane + TS_TM_A;
+        uint32_t ndone = 0, ec = 0;
+        const float my_b1 = row < H ? s.b1[row] : 0.f, my_b2 = row < H ? s.b2[row] : 0.f, my_w3 = row < H ? s.w3h[row] : 0.f;
+        float *u0s = s.in0, *u1s = s.in0 + TS_NT, *ths = s.in0 + 2 * TS_NT;
+        for (int tile = 0; tile < n_tiles; ++tile) {
+            const int n0 = tile * TS_NT;
+            const int nv = min(TS_NT, cnt - n0);
+            const int Nt = ts_ru16(nv);
+            const int nch = Nt / 16;
+            // ---- P0: inputs of the tile (onf_model.py:37-38), labels / upstream gradients ----
+            if (tid < TS_NT) {
+                float x0 = 0.f, x1 = 0.f, x2 = 0.f, ax = 0.f;
+                if (tid < nv) {
+                    const size_t gi = (size_t)p * a.n + n0 + tid;
+                    const float *xp = a.x + gi * a.x_stride;
+                    x0 = xp[0]; x1 = xp[1];
+                    if (L.in_dim == 3) x2 = xp[2];
+                    if (want_bwd) {
+                        if (a.gbar_mode == 0) ax = a.gz[gi];
+                        else if (a.gbar_mode != 2) ax = a.aux[gi];
+                    }
+                }
+                u0s[tid] = (x0 - d.mean) / d.sigma;
+                u1s[tid] = (x1 - d.mean) / d.sigma;
+                ths[tid] = x2;
+                s.aux[tid] = ax;
+            }
+            ts_worker_sync();
+            TS_TRACE(0, 2);
+            // ---- P1: encoding (CUDA cores) feeding fwd1 in chunks of 16 features: thread = (point, feature octet) ----
+            {
+                const bool e_on = tid < 2 * Nt;
+                const int fo = tid >= Nt ? 1 : 0, n = tid - fo * Nt;
+                const float u0 = e_on ? u0s[n] : 0.f, u1 = e_on ? u1s[n] : 0.f, th = e_on ? ths[n] : 0.f;
+#pragma unroll 1
+                for (int ks = 0; ks < K1 / 16; ++ks, ++ec) {
+                    const uint32_t sl = ec % TS_EST;
+                    uint4 ehi, elo;
+                    if (e_on) {
+                        const int f0 = 16 * ks + 8 * fo;
+                        float e[8], pa[8], pb[8], pc[8];
+                        *reinterpret_cast<float4 *>(pa) = *reinterpret_cast<const float4 *>(s.pa + f0);
+                        *reinterpret_cast<float4 *>(pa + 4) = *reinterpret_cast<const float4 *>(s.pa + f0 + 4);
+                        *reinterpret_cast<float4 *>(pb) = *reinterpret_cast<const float4 *>(s.pb + f0);
+                        *reinterpret_cast<float4 *>(pb + 4) = *reinterpret_cast<const float4 *>(s.pb + f0 + 4);
+                        *reinterpret_cast<float4 *>(pc) = *reinterpret_cast<const float4 *>(s.pc + f0);
+                        *reinterpret_cast<float4 *>(pc + 4) = *reinterpret_cast<const float4 *>(s.pc + f0 + 4);
+#pragma unroll
+                        for (int i = 0; i < 8; ++i)
+                            e[i] = __sinf(ts_reduce_2pi(ts_feature_arg(pa[i], pb[i], pc[i], u0, f0 + i < F ? u1 : th)));
+                        split8h(e, ehi, elo);
+                    }
+                    if (ec >= TS_EST) ts_wait(s.eempty + sl, ec / TS_EST - 1);      // fwd1 of the chunk that used this slot is done
+                    if (e_on) {
+                        unsigned char *eb = s.r + sl * t.e_slot + fo * TS_SPT + n * 16;
+                        *reinterpret_cast<uint4 *>(eb) = ehi;
+                        *reinterpret_cast<uint4 *>(eb + 2 * TS_SPT) = elo;
+                    }
+                    ts_signal(s.efull + sl);
+                }
+            }
+            TS_TRACE(0, 3);
+            // ---- P2: epilogue 1: bias + ReLU -> H1 operand (hi, lo); row H = skip term of the logit ----
+            ts_wait(s.done, ndone++);
+            TS_TRACE(0, 4);
+            for (int ch = cq; ch < nch; ch += 4) {
+                const int c0 = 16 * ch;
+                float v[16];
+                tmem_ld16(tA + c0, v);
+                if (row < H) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) v[i] = fminf(fmaxf(v[i] + my_b1, 0.f), 60000.f);
+                } else {
+                    if (row == H) {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) s.skip[c0 + i] = v[i];
+                    }
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) v[i] = 0.f;
+                }
+                if (row < KH) ts_store_row16_hl(s.h1h, s.h1l, row, c0, v);
+            }
+            ts_signal(s.ready);                           // -> fwd2
+            TS_TRACE(0, 5);
+            // ---- P3: epilogue 2, first pass: logit partial sums over the hidden units of each lane quarter ----
+            ts_wait(s.done, ndone++);
+            TS_TRACE(0, 6);
+            for (int ch = cq; ch < nch; ch += 4) {
+                const int c0 = 16 * ch;
+                float pz[16];
+                tmem_ld16(tA + c0, pz);
+#pragma unroll
+                for (int i = 0; i < 16; ++i) pz[i] = row < H ? my_w3 * fmaxf(pz[i] + my_b2, 0.f) : 0.f;
+                const float zs = ts_colsum16(pz, lane);
+                if ((lane & 1) == 0) s.zp[q * TS_NT + c0 + (lane >> 1)] = zs;
+            }
+            ts_worker_sync();
+            TS_TRACE(0, 7);
+            if (tid < TS_NT) {
+                const int n = tid;
+                const bool valid = n < nv;
+                float gb = 0.f;
+                if (n < Nt) {
+                    const float z = s.zp[n] + s.zp[TS_NT + n] + s.zp[2 * TS_NT + n] + s.zp[3 * TS_NT + n] + s.skip[n] + s.scal[0];
+                    const size_t gi = (size_t)p * a.n + n0 + n;
+                    if (valid && a.z_out) a.z_out[gi] = z;
+                    if (valid && want_bwd) {                        // dL/dz
+                        const float ax = s.aux[n];
+                        if (a.gbar_mode == 0) gb = ax;
+                        else if (a.gbar_mode == 1) gb = (sigmoid_f(z) - ax) / (float)cnt;
+                        else {
+                            const float zb = z * a.beta;
+                            const float ez = expf(zb);
+                            gb = a.wc * (zb > 20.f ? 1.f : ez / (ez + 1.f));
+                            if (a.gbar_mode == 3) {
+                                const float th = tanhf(z);
+                                gb += ax * (1.f - th * th);
+                            }
+                        }
+                    }
+                }
+                s.gbar[n] = gb;
+                acc_db3 += gb;
+                if (want_bwd) {                                     // largest |dL/dz| of the tile -> power-of-two operand scale
+                    float m = fabsf(gb);
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+                    if (lane == 0) s.red[warp] = m;
+                }
+            }
+            TS_TRACE(0, 8);
+            if (!want_bwd) {
+                ts_worker_sync();                         // zp / skip / inputs are rewritten by the next tile
+                continue;
+            }
+            ts_worker_sync();
+            if (tid == 0) {
+                float m = 0.f;
+                for (int i = 0; i < TS_NT / 32; ++i) m = fmaxf(m, s.red[i]);
+                // S = 2^-floor(log2 m): the largest scaled |dL/dz| lies in [1, 2); non-finite or zero -> 1
+                int e = (int)((__float_as_uint(m) >> 23) & 0xFFu) - 127;
+                if (!(m > 0.f) || e > 100) e = 0;
+                if (e < -100) e = -100;
+                s.scal[1] = __uint_as_float((uint32_t)(127 - e) << 23);
+                s.scal[2] = __uint_as_float((uint32_t)(127 + e) << 23);
+            }
+            ts_worker_sync();
+            const float S = s.scal[1], invS = s.scal[2];
+            // ---- P4: epilogue 2, second pass: gH2 = dL/dz * w3 * 1[h2 > 0] (scaled, fp16) -> old encoding ring ----
+            for (int ch = cq; ch < nch; ch += 4) {
+                const int c0 = 16 * ch;
+                float r2[16], v[16];
+                tmem_ld16(tA + c0, r2);
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    const float h2 = row < H ? fmaxf(r2[i] + my_b2, 0.f) : 0.f;
+                    const float gb = s.gbar[c0 + i];
+                    acc_dw3 = fmaf(gb, h2, acc_dw3);
+                    const float gg = h2 > 0.f ? gb * my_w3 : 0.f;
+                    acc_db2 += gg;
+                    v[i] = gg * S;
+                }
+                if (row < KH) ts_store_row16_h(s.r, row, c0, v);
+            }
+            ts_signal(s.ready);                           // -> wgrad2 + dgrad2
+            TS_TRACE(0, 9);
+            // ---- P5: epilogue 3: ReLU mask of layer 1 -> gH1 operand (in place over H1 hi); row H := dL/dz ----
+            ts_wait(s.done, ndone++);
+            TS_TRACE(0, 10);
+            for (int ch = cq; ch < nch; ch += 4) {
+                const int c0 = 16 * ch;
+                float v[16];
+                tmem_ld16(tA + c0, v);
+                if (row < H) {
+                    const int off = (row >> 3) * TS_SPT + (c0 >> 3) * 128 + (row & 7) * 16;
+                    const uint4 m0 = *reinterpret_cast<const uint4 *>(s.h1h + off);
+                    const uint4 m1 = *reinterpret_cast<const uint4 *>(s.h1h + off + 128);
+                    const uint32_t mw[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+                    float sum = 0.f;
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        const uint32_t bits = (mw[i >> 1] >> ((i & 1) * 16)) & 0x7FFFu;
+                        v[i] = bits != 0 ? fminf(fmaxf(v[i], -60000.f), 60000.f) : 0.f;
+                        sum += v[i];
+                    }
+                    acc_db1 = fmaf(sum, invS, acc_db1);
+                } else if (row == H) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) v[i] = s.gbar[c0 + i] * S;
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) v[i] = 0.f;
+                }
+                if (row < KH) ts_store_row16_h(s.h1h, row, c0, v);
+            }
+            ts_signal(s.ready);                           // -> dgrad1 (block 0)
+            TS_TRACE(0, 11);
+            // ---- P6: epilogue 4 per feature block: encoding backward (+ input gradient), E^T operand, wgrad1 ----
+#pragma unroll 1
+            for (int mb = 0; mb < t.MB; ++mb) {
+                ts_wait(s.done, ndone++);                 // gE of block mb (and wgrad1 of block mb - 1: E^T is free again)
+                TS_TRACE(0, 12 + 2 * mb);
+                const int fb = mb * t.FB0;
+                const int pf = min(t.FB0, K1 - fb);       // features of this block that are MMA rows
+                const int f = fb + row;
+                const bool f_on = row < pf;
+                const bool fourier = f < F;
+                const float ppa = f_on ? s.pa[f] : 0.f, ppb = f_on ? s.pb[f] : 0.f, ppc = f_on ? s.pc[f] : 0.f;
+                const float ew0 = (f_on && fourier) ? ppa : 0.f, ew1 = (f_on && fourier) ? ppb : 0.f,
+                            eaf = (f_on && !fourier && f < FIN) ? ppb : 0.f;
+                const float *x1src = fourier ? u1s : ths;
+                float ta = 0.f, tb = 0.f, tc = 0.f;      // sum gp*u0, sum gp*x1, sum gp
+                float *gxp = reinterpret_cast<float *>(s.gxp);
+                for (int ch = cq; ch < nch; ch += 4) {
+                    const int c0 = 16 * ch;
+                    float v[16], gq[16], ev[16];
+                    tmem_ld16(tA + c0, v);
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        const float xu = u0s[c0 + i], x1 = x1src[c0 + i];
+                        const float r = ts_reduce_2pi(ts_feature_arg(ppa, ppb, ppc, xu, x1));
+                        const float gp = f_on ? v[i] * invS * __cosf(r) : 0.f;
+                        ev[i] = f_on ? __sinf(r) : 0.f;
+                        gq[i] = gp;
+                        ta = fmaf(gp, xu, ta);
+                        tb = fmaf(gp, x1, tb);
+                        tc += gp;
+                    }
+                    if (want_gx) {
+                        // gx[n] = (sum_f gp[f,n] * We[f,c]) / sigma ; g_theta[n] = sum_k gp[k,n] * f_k   (reduce over lanes)
+                        float cv[16];
+                        float *dst = gxp + ((size_t)q * TS_NT + c0 + (lane >> 1)) * 3;
+#pragma unroll
+                        for (int c = 0; c < 3; ++c) {
+                            const float wgt = c == 0 ? ew0 : c == 1 ? ew1 : eaf;
+#pragma unroll
+                            for (int i = 0; i < 16; ++i) cv[i] = gq[i] * wgt;
+                            const float sum = ts_colsum16(cv, lane);
+                            if ((lane & 1) == 0) dst[c] = mb == 0 ? sum : dst[c] + sum;
+                        }
+                    }
+                    if (want_wgrad && row < t.FB0) {     // E^T operand [point / 8][feature][8 points]
+#pragma unroll
+                        for (int o = 0; o < 2; ++o) {
+                            const int off = ((c0 >> 3) + o) * t.S_ET + (row >> 3) * 128 + (row & 7) * 16;
+                            *reinterpret_cast<uint4 *>(s.h1l + off) = pack8h(ev + 8 * o);
+                        }
+                    }
+                }
+                if (f_on && !fourier) {                   // heading features: d ang_b = f_k * sum gp,
+                    const float b = f < FIN ? s.ang_b[f - F] : 0.f;   // d ang_f = sum gp * (theta + b_k)  (trained)
+                    tb = fmaf(b, tc, tb);
+                    ta = eaf * tc;
+                }
+                if (mb == 0) { fa0 += ta; fb0 += tb; fc0 += tc; }
+                else { fa1 += ta; fb1 += tb; fc1 += tc; }
+                ts_signal(s.ready);                       // -> wgrad1(mb), dgrad1(mb + 1)
+                TS_TRACE(0, 13 + 2 * mb);
+            }
+            if (want_gx) {
+                ts_worker_sync();
+                if (tid < nv) {
+                    const int n = tid;
+                    const float *gxp = reinterpret_cast<const float *>(s.gxp);
+                    float g0 = 0.f, g1 = 0.f, g2 = 0.f;
+#pragma unroll
+                    for (int qq = 0; qq < 4; ++qq) {
+                        const float *src = gxp + ((size_t)qq * TS_NT + n) * 3;
+                        g0 += src[0]; g1 += src[1]; g2 += src[2];
+                    }
+                    float *out = a.gx_out + ((size_t)p * a.n + n0 + n) * a.x_stride;
+                    out[0] = g0 / d.sigma;
+                    out[1] = g1 / d.sigma;
+                    if (L.in_dim == 3) out[2] = g2;
+                    for (int c = L.in_dim; c < a.x_stride; ++c) out[c] = 0.f;   // pose columns the ONF does not read
+                }
+            }
+            if (want_wgrad) ts_wait(s.done, ndone++);     // the last wgrad1
+            TS_TRACE(0, 16);
+            ts_worker_sync();                             // zp, gx, skip, gbar, inputs are rewritten by the next tile
+            ts_signal(s.tile_free);
+        }
+    }
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    TS_TRACE(0, 20);
+
+    // ---- weight gradients: TMEM accumulators -> shared memory in blob order -> coalesced Adam / gradient store ----
+    if (want_wgrad) {
+        // every MMA has completed: the operand buffers are dead, shared memory [0, n_params) floats now holds the
+        // gradient of the whole parameter blob (same element order as the fp32 weights)
+        const float invS = s.scal[2];
+        float *G = reinterpret_cast<float *>(smem_raw);
+        float *red = G + ((L.n_params + 31) & ~31);                    // [10][4][128] partial per-unit sums
+        __syncthreads();                                               // invS read before the staging area is cleared
+        const int np4 = L.n_params / 4;
+        for (int i = tid; i < np4; i += TS_THREADS) reinterpret_cast<float4 *>(G)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        const bool is_worker = warp < TS_WORKERS / 32;
+        if (is_worker) {
+            float *r0 = red + cq * 128 + row;
+            r0[0 * 512] = acc_db1; r0[1 * 512] = acc_db2; r0[2 * 512] = acc_dw3;
+            r0[3 * 512] = fa0; r0[4 * 512] = fb0; r0[5 * 512] = fc0;
+            r0[6 * 512] = fa1; r0[7 * 512] = fb1; r0[8 * 512] = fc1;
+            if (tid < TS_NT) {
+                const float s3 = warp_sum(acc_db3);
+                if (lane == 0) red[9 * 512 + warp] = s3;
+            }
+        }
+        __syncthreads();
+        // dW1: rows j < H -> mlp.0.weight[j,:], row H -> mlp2.0.weight[0, H:];  dW2: rows i < H -> mlp.2.weight[i,:]
+        for (int ch = cq; ch < (is_worker ? K1 / 16 : 0); ch += 4) {
+            float g[16];
+            const int f0 = 16 * ch;
+            tmem_ld16(tm_lane + (f0 < t.FB0 ? TS_TM_DW2 + KH + f0 : TS_TM_A + (f0 - t.FB0)), g);
+            if (row <= H) {
+                float *dst = G + (row < H ? L.off_w[0] + row * FIN : L.off_w_out + H) + f0;
+#pragma unroll
+                for (int c4 = 0; c4 < 4; ++c4)
+                    if (f0 + 4 * c4 < FIN)
+                        *reinterpret_cast<float4 *>(dst + 4 * c4) =
+                            make_float4(g[4 * c4] * invS, g[4 * c4 + 1] * invS, g[4 * c4 + 2] * invS, g[4 * c4 + 3] * invS);
+            }
+        }
+        for (int ch = cq; ch < (is_worker ? KH / 16 : 0); ch += 4) {
+            float g[16];
+            tmem_ld16(tm_lane + TS_TM_DW2 + 16 * ch, g);
+            if (row < H) {
+                float *dst = G + L.off_w[1] + row * H + 16 * ch;
+#pragma unroll
+                for (int c4 = 0; c4 < 4; ++c4)
+                    if (16 * ch + 4 * c4 < H)
+                        *reinterpret_cast<float4 *>(dst + 4 * c4) =
+                            make_float4(g[4 * c4] * invS, g[4 * c4 + 1] * invS, g[4 * c4 + 2] * invS, g[4 * c4 + 3] * invS);
+            }
+        }
+        if (tid < 128) {
+            auto tot = [&](int qn) {
+                const float *r = red + qn * 512 + tid;
+                return (r[0] + r[128]) + (r[256] + r[384]);
+            };
+            if (tid < H) {
+                G[L.off_b[0] + tid] = tot(0);
+                G[L.off_b[1] + tid] = tot(1);
+                G[L.off_w_out + tid] = tot(2);
+            }
+            for (int mb = 0; mb < t.MB; ++mb) {
+                const int f = mb * t.FB0 + tid;
+                const bool on = tid < min(t.FB0, K1 - mb * t.FB0);
+                const float ga = tot(3 + 3 * mb), gb = tot(4 + 3 * mb), gc = tot(5 + 3 * mb);
+                if (on && f < F) {
+                    G[L.off_enc_w + 2 * f] = ga;
+                    G[L.off_enc_w + 2 * f + 1] = gb;
+                    G[L.off_enc_b + f] = d.bias ? gc : 0.f;
+                } else if (on && f < FIN) {
+                    G[L.off_ang_b + f - F] = ga;
+                    G[L.off_ang_f + f - F] = gb;
+                }
+            }
+            if (tid == 0) {
+                float g3 = 0.f;
+                for (int i = 0; i < TS_NT / 32; ++i) g3 += red[9 * 512 + i];
+                G[L.off_b_out] = g3;
+            }
+        }
+        __syncthreads();
+        TS_TRACE(0, 21);
+        const size_t po = (size_t)p * L.n_params;
+        if (a.adam_w == nullptr) {
+            float4 *dst = reinterpret_cast<float4 *>(a.grad_out + po);
+            for (int i = tid; i < np4; i += TS_THREADS) dst[i] = reinterpret_cast<const float4 *>(G)[i];
+        } else {
+            // torch.optim.Adam (_single_tensor_adam) over the whole blob, fully coalesced; the new weights replace the
+            // gradient in shared memory and are re-split into the fp16 operand copy below
+            const float step_size = a.sp->onf_step_size, inv_bc2 = 1.f / a.sp->onf_bc2_sqrt;
+            float4 *w4 = reinterpret_cast<float4 *>(a.adam_w + po), *m4 = reinterpret_cast<float4 *>(a.adam_m + po),
+                   *v4 = reinterpret_cast<float4 *>(a.adam_v + po);
+            constexpr int U = 4;
+            for (int i0 = tid; i0 < np4; i0 += U * TS_THREADS) {
+                float4 wv[U], mv[U], vv[U];
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    const int i = i0 + u * TS_THREADS;
+                    if (i < np4) { wv[u] = w4[i]; mv[u] = m4[i]; vv[u] = v4[i]; }
+                }
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    const int i = i0 + u * TS_THREADS;
+                    if (i >= np4) continue;
+                    const float4 g4 = reinterpret_cast<const float4 *>(G)[i];
+                    float gg[4] = {g4.x, g4.y, g4.z, g4.w}, ww[4] = {wv[u].x, wv[u].y, wv[u].z, wv[u].w},
+                          mm[4] = {mv[u].x, mv[u].y, mv[u].z, mv[u].w}, v2[4] = {vv[u].x, vv[u].y, vv[u].z, vv[u].w};
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        mm[c] = fmaf(a.w1, gg[c] - mm[c], mm[c]);
+                        v2[c] = fmaf(a.w2 * gg[c], gg[c], v2[c] * a.beta2);
+                        float sq;
+                        asm("sqrt.approx.f32 %0, %1;" : "=f"(sq) : "f"(v2[c]));
+                        const float denom = fmaf(sq, inv_bc2, a.eps);
+                        ww[c] = fmaf(-step_size, __fdividef(mm[c], denom), ww[c]);
+                    }
+                    w4[i] = make_float4(ww[0], ww[1], ww[2], ww[3]);
+                    m4[i] = make_float4(mm[0], mm[1], mm[2], mm[3]);
+                    v4[i] = make_float4(v2[0], v2[1], v2[2], v2[3]);
+                    reinterpret_cast<float4 *>(G)[i] = make_float4(ww[0], ww[1], ww[2], ww[3]);
+                }
+            }
+            __syncthreads();
+            TS_TRACE(0, 22);
+            // refresh the packed operand copy: item = (matrix, column octet, row) -> 16 B of hi + 16 B of lo
+            unsigned char *pk = a.packed_out + (size_t)p * t.packed_bytes;
+            const int rows = KH, n1 = (K1 / 8) * rows, n2 = (KH / 8) * rows;
+            for (int item = tid; item < n1 + n2; item += TS_THREADS) {
+                const bool second = item >= n1;
+                const int it = second ? item - n1 : item;
+                const int oct = it / rows, r = it - oct * rows;
+                const int kdim = second ? H : FIN;
+                float v[8];
+                const float *src = nullptr;
+                if (!second) {
+                    if (r < H) src = G + L.off_w[0] + r * FIN;
+                    else if (r == H) src = G + L.off_w_out + H;
+                } else if (r < H) {
+                    src = G + L.off_w[1] + r * H;
+                }
+#pragma unroll
+                for (int h4 = 0; h4 < 2; ++h4) {
+                    const int c = oct * 8 + 4 * h4;
+                    float4 x4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (src && c < kdim) x4 = *reinterpret_cast<const float4 *>(src + c);
+                    v[4 * h4] = x4.x; v[4 * h4 + 1] = x4.y; v[4 * h4 + 2] = x4.z; v[4 * h4 + 3] = x4.w;
+                }
+                uint4 hi, lo;
+                split8h(v, hi, lo);
+                unsigned char *base = pk + (second ? 2 * t.w1_half : 0);
+                const int half = second ? t.w2_half : t.w1_half;
+                const int off = oct * t.S_colW + (r >> 3) * 128 + (r & 7) * 16;
+                *reinterpret_cast<uint4 *>(base + off) = hi;
+                *reinterpret_cast<uint4 *>(base + half + off) = lo;
+            }
+        }
+    }
+    fence_before_sync();
+    __syncthreads();
+    TS_TRACE(0, 23);
+    if (is_issuer) tmem_dealloc(tmem, 512);
+}
+
+// ---- host side ---------------------------------------------------------------------------------------------
+bool onf_tcs_supported(const OnfDims &d) {
+    TsDims t;
+    return ts_make_dims(d, &t);
+}
+int onf_tcs_tile_points() { return TS_NT; }
+
+int onf_tcs_prepare(const OnfDims &d) {
+    TsDims t;
+    NFOPP_REQUIRE(ts_make_dims(d, &t), "onf(tensor, streamed): needs 2 hidden layers, hidden <= 111, f_in <= 224 (hidden=%d layers=%d)",
+                  d.H, d.L);
+    NFOPP_CHECK_CUDA(cudaFuncSetAttribute(onf_tcs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, t.smem_bytes));
+    return NFOPP_OK;
+}
+
+int onf_tcs_pack(const OnfDims &d, const float *weights, unsigned char *packed, int P, cudaStream_t stream) {
+    TsPackArgs a{};
+    a.d = d;
+    NFOPP_REQUIRE(ts_make_dims(d, &a.t), "onf(tensor, streamed): unsupported network shape");
+    a.weights = weights; a.packed = packed;
+    if (P == 0) return NFOPP_OK;
+    const int items = (a.t.K1 / 8 + a.t.KH / 8) * a.t.KH;
+    dim3 grid((items + 255) / 256, P);
+    onf_tcs_pack_kernel<<<grid, 256, 0, stream>>>(a);
+    NFOPP_CHECK_CUDA(cudaGetLastError());
+    return NFOPP_OK;
+}
+
+int onf_tcs_launch(const OnfArgs &o, const OnfTcExtra &x, int P, cudaStream_t stream) {
+    OnfTsArgs a{};
+    a.d = o.d;
+    NFOPP_REQUIRE(ts_make_dims(o.d, &a.t), "onf(tensor, streamed): unsupported network shape");
+    a.weights = o.weights; a.packed = x.packed; a.x = o.x; a.count = o.count; a.sp = o.sp;
+    a.n = o.n; a.x_stride = o.x_stride ? o.x_stride : o.d.lay.in_dim;
+    a.want_bwd = o.want_bwd; a.gbar_mode = o.gbar_mode; a.gz = o.gz; a.aux = o.aux; a.wc = o.wc; a.beta = o.beta;
+    a.z_out = o.z_out; a.gx_out = o.gx_out; a.grad_out = x.grad_out;
+    a.adam_w = x.adam_w; a.adam_m = x.adam_m; a.adam_v = x.adam_v; a.packed_out = x.packed_out;
+    a.w1 = x.w1; a.beta2 = x.beta2; a.w2 = x.w2; a.eps = x.eps; a.warm = x.warm;
+    NFOPP_REQUIRE(a.packed, "onf(tensor): packed operand copy missing");
+    NFOPP_REQUIRE(!a.adam_w || (a.sp && a.packed_out), "onf(tensor): fused Adam needs step parameters and the packed copy");
+    NFOPP_REQUIRE(!(a.want_bwd && (a.grad_out || a.adam_w)) || a.n <= TS_NT,
+                  "onf(tensor, streamed): weight gradients need at most %d points per problem (got %d)", TS_NT, a.n);
+    if (a.n == 0 || P == 0) return NFOPP_OK;
+    onf_tcs_kernel<<<P, TS_THREADS, a.t.smem_bytes, stream>>>(a);
+    NFOPP_CHECK_CUDA(cudaGetLastError());
+    return NFOPP_OK;
+}
+
+}  // namespace nfopp
+
+#ifdef NFOPP_TC_TRACE
+extern "C" int nfopp_debug_tcs_trace(long long *host_out) {
+    return (int)cudaMemcpyFromSymbol(host_out, nfopp::g_ts_trace, sizeof(nfopp::g_ts_trace));
+}
+#endif

@@ -11,6 +11,7 @@
 // One tcgen05.mma consumes K = 16: advance the start address by 2*S_col (K-major) or 2*S_row (MN-major).
 #pragma once
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -156,6 +157,17 @@ __host__ __device__ __forceinline__ uint32_t instr_desc_bf16(int M, int N, int a
     d |= (uint32_t)(M >> 4) << 24;
     return d;
 }
+// the same with A/B = fp16 (format code 0): 11-bit significands, so a hi/lo split carries 22 bits and ONE pass of hi parts
+// already has the accuracy of tf32
+__host__ __device__ __forceinline__ uint32_t instr_desc_f16(int M, int N, int a_mn_major, int b_mn_major) {
+    uint32_t d = 0;
+    d |= 1u << 4;                       // D format f32; A, B format f16 = 0
+    d |= (uint32_t)(a_mn_major & 1) << 15;
+    d |= (uint32_t)(b_mn_major & 1) << 16;
+    d |= (uint32_t)(N >> 3) << 17;
+    d |= (uint32_t)(M >> 4) << 24;
+    return d;
+}
 // one lane of a converged warp (warp-uniform control flow around it keeps descriptor arithmetic on the uniform path)
 __device__ __forceinline__ uint32_t elect_one() {
     uint32_t pred;
@@ -222,6 +234,29 @@ __device__ __forceinline__ void split8(const float *x, uint4 &hi, uint4 &lo) {
     split2(x[2], x[3], hi.y, lo.y);
     split2(x[4], x[5], hi.z, lo.z);
     split2(x[6], x[7], hi.w, lo.w);
+}
+
+// ---- fp32 -> (fp16 hi, fp16 lo) split: x ~= hi + lo with ~2^-22 relative error (|x| < 65504; below ~2^-3 the lo part is an
+// fp16 subnormal and the error is absolute, 2^-25) ------------------------------------------------------
+__device__ __forceinline__ uint32_t pack_h2(float x0, float x1) {
+    const __half2 h = __floats2half2_rn(x0, x1);            // element 0 in the low half
+    return *reinterpret_cast<const uint32_t *>(&h);
+}
+__device__ __forceinline__ void split2h(float x0, float x1, uint32_t &hi, uint32_t &lo) {
+    const __half2 h = __floats2half2_rn(x0, x1);
+    const float2 f = __half22float2(h);
+    hi = *reinterpret_cast<const uint32_t *>(&h);
+    lo = pack_h2(x0 - f.x, x1 - f.y);
+}
+__device__ __forceinline__ void split8h(const float *x, uint4 &hi, uint4 &lo) {
+    split2h(x[0], x[1], hi.x, lo.x);
+    split2h(x[2], x[3], hi.y, lo.y);
+    split2h(x[4], x[5], hi.z, lo.z);
+    split2h(x[6], x[7], hi.w, lo.w);
+}
+// hi parts only (single-pass operands)
+__device__ __forceinline__ uint4 pack8h(const float *x) {
+    return make_uint4(pack_h2(x[0], x[1]), pack_h2(x[2], x[3]), pack_h2(x[4], x[5]), pack_h2(x[6], x[7]));
 }
 
 }  // namespace tc05

@@ -1,0 +1,66 @@
+#!/usr/bin/env python
+"""Phase trace of the streamed fused ONF kernel (onf_tcs.cu built with -DNFOPP_TC_TRACE: `make -C .../csrc trace`).
+Runs the corridor workload for a few steps and prints, for the first and last CTA of the three ONF launches of a step
+(candidates forward, train, path), the clock64 stamps of worker thread 0, the MMA-issue warp and the weight-stream warp
+relative to the CTA's start.  Diagnostic only - the product library is libnfopp.so.   python scripts/tcs_trace.py"""
+import argparse
+import ctypes as C
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "pytorch-motion-planner_b200")):
+    sys.path.insert(0, p)
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+from nfopp_b200 import _lib as L  # noqa: E402
+
+L.LIB_PATH = os.path.join(os.path.dirname(L.LIB_PATH), "libnfopp_trace.so")
+import bench as B  # noqa: E402
+
+WORKER = {0: "start", 1: "setup done", 2: "inputs staged", 3: "encode done", 4: "fwd1 done", 5: "ep1 signalled", 6: "fwd2 done",
+          7: "logit partials", 8: "dL/dz", 9: "gH2 signalled", 10: "wgrad2+dgrad2 done", 11: "ep3 signalled",
+          12: "dgrad1(0) done", 13: "ep4(0) signalled", 14: "dgrad1(1) done", 15: "ep4(1) signalled", 16: "wgrad1 done",
+          20: "CTA sync", 21: "TMEM drained", 22: "Adam done", 23: "repack done"}
+ISSUER = {0: "start", 1: "fwd1 issued", 2: "ep1 ready", 3: "fwd2 issued", 4: "gH2 ready", 5: "W2 slot full", 6: "bwdA issued",
+          7: "gH1 ready", 8: "W1 slot full", 9: "ep4(0) ready", 10: "wgrad1(0)+dgrad1(1) issued", 11: "ep4(1) ready",
+          12: "wgrad1(1) issued"}
+PRODUCER = {1: "fwd ring streamed", 2: "fwd ring drained", 3: "bwd blocks issued"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--problems", type=int, default=1024)
+    ap.add_argument("--steps", type=int, default=12)
+    args = ap.parse_args()
+    cfg, env, starts, goals, _ = B.build_workload("corridor", args.problems, 0)
+    from nfopp_b200.batched import BatchedPlanner
+    pl = BatchedPlanner(cfg)
+    pl.init(starts, goals, **env)
+    pl.step(args.steps)
+    torch.cuda.synchronize()
+    lib = L.lib()
+    lib.nfopp_debug_tcs_trace.restype = C.c_int
+    lib.nfopp_debug_tcs_trace.argtypes = [C.c_void_p]
+    buf = np.zeros((3, 2, 3, 64), dtype=np.int64)
+    rc = lib.nfopp_debug_tcs_trace(buf.ctypes.data_as(C.c_void_p))
+    assert rc == 0, rc
+    for kind, kname in enumerate(["candidates fwd", "train", "path fwd+dgrad"]):
+        for ci, cname in enumerate(["first CTA", "last CTA"]):
+            t = buf[kind, ci]
+            t0 = t[0, 0]
+            print(f"== {kname} / {cname}")
+            for role, names in enumerate([WORKER, ISSUER, PRODUCER]):
+                prev, parts = t0, []
+                for k in sorted(names):
+                    v = t[role, k]
+                    if v == 0 or v < t0:
+                        continue
+                    parts.append(f"{names[k]} @{v - t0} (+{v - prev})")
+                    prev = v
+                print(f"  {['worker', 'issuer', 'producer'][role]:8s}: " + " | ".join(parts))
+
+
+if __name__ == "__main__":
+    main()
