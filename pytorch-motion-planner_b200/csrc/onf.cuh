@@ -50,11 +50,10 @@ size_t onf_tc_packed_bytes(const OnfDims &d);       // per problem
 int onf_tc_prepare(const OnfDims &d);
 int onf_tc_pack(const OnfDims &d, const float *weights, unsigned char *packed, int P, cudaStream_t stream, int variant);
 int onf_tc_launch(const OnfArgs &a, const OnfTcExtra &x, int P, cudaStream_t stream);
-// second generation (onf_tcs.cu): whole problem in one 224-point tile, weights streamed, fp16 hi/lo operands (forward three
-// passes, backward one).  Same packed layout and size as the first generation, different element type: the operand copy
+// second generation (onf_tcs.cu): 112-point tiles, weights streamed, fp16 hi/lo operands, every product three passes, any
+// point count.  Same packed layout and size as the first generation, different element type: the operand copy
 // must be packed by the variant that reads it.
 bool onf_tcs_supported(const OnfDims &d);
-int onf_tcs_tile_points();
 int onf_tcs_prepare(const OnfDims &d);
 int onf_tcs_pack(const OnfDims &d, const float *weights, unsigned char *packed, int P, cudaStream_t stream);
 int onf_tcs_launch(const OnfArgs &a, const OnfTcExtra &x, int P, cudaStream_t stream);

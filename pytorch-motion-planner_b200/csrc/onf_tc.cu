@@ -918,7 +918,8 @@ size_t onf_tc_packed_bytes(const OnfDims &d) {
 
 int onf_tc_variant(const OnfDims &d, int n_wgrad) {
     static const bool legacy = [] { const char *e = getenv("NFOPP_TC_LEGACY"); return e && e[0] == '1'; }();
-    return (!legacy && onf_tcs_supported(d) && n_wgrad <= onf_tcs_tile_points()) ? 1 : 0;
+    (void)n_wgrad;
+    return (!legacy && onf_tcs_supported(d)) ? 1 : 0;
 }
 
 int onf_tc_prepare(const OnfDims &d) {

@@ -1,26 +1,29 @@
-// onf_tcs.cu - K2, fused tensor path, second generation: the whole problem in ONE tile, weights STREAMED.
+// onf_tcs.cu - K2, fused tensor path, second generation: 112-point tiles, weights STREAMED, every product exact.
 //
 // onf_tc.cu keeps a problem's hidden-layer weights resident in shared memory (150 KB), which leaves room for only two
 // 32-point tiles in flight: ~1000 tcgen05.mma of N = 32 per problem and 14 latency-bound handshakes per 32 points.  Here
 // the operand roles are the same (HIDDEN index on the UMMA M axis = TMEM lanes, POINT index on N) but
-//   * ALL points of the problem (<= 224: 209 training samples, 199 candidates, 99 path points) form ONE tile, so every
-//     GEMM of onf_model.py:33-50 and of its backward is a handful of 128 x Nt x 16 MMAs (~190 per training call) and every
-//     epilogue stage runs once per problem on all 16 worker warps;
-//   * the weights are not resident: a producer warp streams the packed operand copy (L2-resident, 150 KB) through an
-//     8-stage ring of K = 16 chunks for the forward GEMMs and as three 25 KB blocks for the backward GEMMs;
-//   * operands are fp16 hi/lo: the FORWARD products stay three-pass (hi*hi + lo*hi + hi*lo, ~1e-7) because the ReLU
-//     masks must not flip against the fp32 reference, the BACKWARD products (masks already fixed: input gradients and
-//     weight gradients, two thirds of the flops) are ONE pass of hi parts with the upstream gradient scaled to [1, 2) by
-//     a power of two per tile (fp16 has no range to spare at dL/dz ~ 1/N) and unscaled in fp32 in the epilogues;
-//   * weight gradients are produced once per problem (K = all points), so their TMEM accumulators need not persist
-//     across tiles: dW2 and the two halves of dW1 take 336 columns next to ONE 224-column work accumulator.
+//   * a tile is 112 points (a problem's 209 training samples = 2 tiles, its 99 path points = 1), so every GEMM of
+//     onf_model.py:33-50 and of its backward is a handful of 128 x 112 x 16 MMAs and every epilogue stage runs once per
+//     tile on all 16 worker warps;
+//   * the weights are not resident: a producer warp streams the packed operand copy (L2-resident, 150 KB per problem)
+//     through an 8-stage ring of K = 16 chunks for the forward GEMMs and as hi / lo blocks of 25 KB for the backward GEMMs;
+//   * operands are fp16 hi/lo pairs and EVERY product is three MMAs (hi*hi + lo*hi + hi*lo, fp32 accumulate, ~1e-7):
+//     a one-pass backward was built and measured first (profiles/r02a_tcs_bwd1_*: gradients 2e-4 .. 1.5e-3 of the max
+//     norm, four parity tests red) and the emulation in profiles/r02_precision_emulation.json shows that every backward
+//     operand (gradient, weight, activation) needs its lo part for a 3x margin under the 1e-3 bar;
+//   * the upstream gradient is scaled by a power of two chosen BEFORE the forward from a bound of |dL/dz| (BCE: 1 / N;
+//     path terms: collision weight + max multiplier; external: max |gz|), so fp16 keeps its range and the weight-gradient
+//     accumulators of all tiles share one scale; epilogues unscale in fp32;
+//   * weight-gradient accumulators (dW2: 112, dW1: 224 TMEM columns) persist across the tiles of a problem next to ONE
+//     112-column work accumulator, so any point count is supported.
 //
-//   fwd1   D1[j,n]  = sum_k W1p[j,k] E[n,k]     A = W1p chunk (K-major, ring)   B = E chunk  (K-major, ring)   3 passes
-//   fwd2   D2[i,n]  = sum_j W2p[i,j] H1[j,n]    A = W2p chunk (K-major, ring)   B = H1       (MN-major)        3 passes
-//   wgrad2 dW2[i,j] = sum_n gH2[i,n] H1[j,n]    A = gH2       (K-major)         B = H1 hi    (K-major)         1 pass
-//   dgrad2 gD1[j,n] = sum_i W2p[i,j] gH2[i,n]   A = W2p hi    (MN-major, slot)  B = gH2      (MN-major)        1 pass
-//   dgrad1 gE[k,n]  = sum_j W1p[j,k] gH1[j,n]   A = W1p hi    (MN-major, slot)  B = gH1      (MN-major)        1 pass, 2 blocks
-//   wgrad1 dW1[j,k] = sum_n gH1[j,n] E[n,k]     A = gH1       (K-major)         B = E^T      (K-major)         1 pass, 2 blocks
+//   fwd1   D1[j,n]  = sum_k W1p[j,k] E[n,k]     A = W1p chunk (K-major, ring)    B = E chunk  (K-major, ring)
+//   fwd2   D2[i,n]  = sum_j W2p[i,j] H1[j,n]    A = W2p chunk (K-major, ring)    B = H1       (MN-major)
+//   wgrad2 dW2[i,j]+= sum_n gH2[i,n] H1[j,n]    A = gH2       (K-major)          B = H1       (K-major)
+//   dgrad2 gD1[j,n] = sum_i W2p[i,j] gH2[i,n]   A = W2p       (MN-major, slots)  B = gH2      (MN-major)
+//   dgrad1 gE[k,n]  = sum_j W1p[j,k] gH1[j,n]   A = W1p       (MN-major, slots)  B = gH1      (MN-major)   2 feature blocks
+//   wgrad1 dW1[j,k]+= sum_n gH1[j,n] E[n,k]     A = gH1       (K-major)          B = E^T      (K-major)    2 feature blocks
 //
 // Row H of W1p holds the skip weights w_out[H:] (onf_model.py:48-49) exactly as in onf_tc.cu, so the skip term, its input
 // gradient and its weight gradient fall out of fwd1 / dgrad1 / wgrad1.  Biases, ReLU, logit, dL/dz (BCE
@@ -28,9 +31,7 @@
 // the CUDA cores, one TMEM lane (hidden unit or feature) per thread.  The epilogue stages the gradient blob in shared
 // memory and streams it through Adam (planner_factory.py:68), rewriting the fp16 operand copy - as onf_tc.cu does.
 //
-// Supported: 2 hidden layers, hidden <= 111, f_in <= 224 (the reference's network shapes).  Forward and input-gradient
-// calls take any point count (tiles of 224); weight gradients need count <= 224 (the planner's 209; larger API calls
-// go to the first-generation kernel).
+// Supported: 2 hidden layers, hidden <= 111, f_in <= 256 (the reference's network shapes), any point count.
 #include "onf.cuh"
 #include "tc05.cuh"
 
@@ -53,18 +54,18 @@ __device__ long long g_ts_trace[3][2][3][64];   // [launch kind: fwd | train | p
 
 constexpr int TS_WORKERS = 512;                 // 16 epilogue / encoding warps
 constexpr int TS_THREADS = TS_WORKERS + 64;     // + MMA-issue warp + weight-stream warp
-constexpr int TS_NT = 224;                      // points per tile
+constexpr int TS_NT = 112;                      // points per tile
 constexpr uint32_t TS_SPT = TS_NT * 16;         // S_row of the point-indexed operand buffers [hidden / 8][point / 8][8][8]
 constexpr int TS_WST = 8;                       // weight ring stages (K = 16 chunk of W, hi + lo)
-constexpr int TS_EST = 4;                       // encoding ring slots (16 features x Nt points, hi + lo)
-constexpr uint32_t TS_TM_A = 0, TS_TM_DW2 = TS_NT;   // TMEM columns: work accumulator | dW2 [KH] | dW1 block 0 [FB0]
-constexpr int TS_GX_BYTES = 4 * TS_NT * 3 * 4;  // per-lane-quarter partials of the input gradient
+constexpr int TS_EF = 64;                       // features per encoding slot (2 slots)
+constexpr uint32_t TS_TM_A = 0, TS_TM_DW2 = TS_NT, TS_TM_DW1 = 2 * TS_NT;   // TMEM columns: work | dW2 [KH] | dW1 [K1]
+constexpr int TS_GX_FLOATS = 4 * TS_NT * 3;     // per-lane-quarter partials of the input gradient
 
 struct TsDims {
     int F, A, FIN, H, K1, KH, MB, FB0;           // MB feature blocks of FB0 (last one shorter) for dgrad1 / wgrad1
     int S_colW, w1_half, w2_half;                // packed operand copy: [W1 hi | W1 lo | W2 hi | W2 lo], each [k / 8][row][8]
-    int h1_half, e_slot, w_stage, b_slot, S_ET;
-    int off_h1h, off_h1l, off_r, off_w, off_gx, off_misc, misc_floats, smem_bytes, packed_bytes;
+    int h1_half, e_half, w_stage, b_slot, S_ET, et_half;
+    int off_h1h, off_h1l, off_r, off_w, off_misc, misc_floats, smem_bytes, packed_bytes;
 };
 
 __host__ __device__ inline int ts_ru16(int x) { return (x + 15) / 16 * 16; }
@@ -81,23 +82,23 @@ __host__ __device__ inline bool ts_make_dims(const OnfDims &d, TsDims *out) {
     t.w2_half = (t.KH / 8) * t.S_colW;
     t.h1_half = (t.KH / 8) * (int)TS_SPT;
     t.S_ET = t.FB0 * 16;
-    t.e_slot = 4 * (int)TS_SPT;                  // 2 feature octets x (hi, lo)
+    t.et_half = (TS_NT / 8) * t.S_ET;            // E^T of one feature block: [point / 8][feature][8 points]
+    t.e_half = (TS_EF / 8) * (int)TS_SPT;        // one encoding slot, hi (or lo) part
     t.w_stage = 4 * t.S_colW;                    // 2 column octets x (hi, lo)
     t.b_slot = 16 * t.S_colW;                    // a 128-row MN-major A operand never reads past its slot
     t.off_h1h = 0;
     t.off_h1l = t.h1_half;
-    t.off_r = t.off_h1l + ts_max(t.h1_half, (TS_NT / 8) * t.S_ET);            // H1 lo, later E^T
-    t.off_w = t.off_r + ts_max(TS_EST * t.e_slot, t.h1_half);                 // encoding ring, later gH2
-    t.off_gx = t.off_w + t.b_slot;                                            // (slot 1 is dead when gx partials are written)
-    t.off_misc = t.off_w + ts_max(ts_max(TS_WST * t.w_stage, 2 * t.b_slot), t.b_slot + TS_GX_BYTES);
-    t.misc_floats = 3 * t.K1 + 32 + 3 * t.KH + 8 + 10 * TS_NT + 32;
+    t.off_r = 2 * t.h1_half;                     // encoding ring (2 slots, hi + lo) | gH2 hi, lo | E^T hi, lo
+    t.off_w = t.off_r + ts_max(ts_max(4 * t.e_half, 2 * t.h1_half), 2 * t.et_half);
+    const int operands = t.off_w + ts_max(TS_WST * t.w_stage, 2 * t.b_slot);
+    // the epilogue stages the whole gradient blob (+ 20 KB of per-unit partial sums) over the dead operand buffers
+    const int stage_bytes = ((d.lay.n_params + 31) / 32 * 32 + 10 * 512) * 4;
+    t.off_misc = ts_max(operands, (stage_bytes + 127) / 128 * 128);
+    t.misc_floats = 3 * t.K1 + 32 + 3 * t.KH + 8 + 10 * TS_NT + TS_GX_FLOATS + 32;
     t.smem_bytes = t.off_misc + t.misc_floats * 4 + 64 * 8 + 16;
     t.packed_bytes = 2 * t.w1_half + 2 * t.w2_half;
     *out = t;
-    // the epilogue stages the whole gradient blob (+ 20 KB of per-unit partial sums) over the dead operand buffers
-    const int stage_bytes = ((d.lay.n_params + 31) / 32 * 32 + 10 * 512) * 4;
-    return d.L == 2 && t.KH <= 128 && t.K1 <= 256 && t.H >= 8 && (int)TS_TM_DW2 + t.KH + t.FB0 <= 512 &&
-           t.smem_bytes <= 227 * 1024 && stage_bytes <= t.off_misc;
+    return d.L == 2 && t.KH <= TS_NT && t.K1 <= 256 && t.H >= 8 && (int)TS_TM_DW1 + t.K1 <= 512 && t.smem_bytes <= 227 * 1024;
 }
 
 struct OnfTsArgs {
@@ -182,24 +183,23 @@ __device__ __forceinline__ float ts_colsum16(float (&v)[16], int lane) {
     }
     return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 1);
 }
-__device__ __forceinline__ float ts_feature_arg(float pa, float pb, float pc, float u0, float x1) {
-    return fmaf(x1, pb, fmaf(u0, pa, pc));
-}
-__device__ __forceinline__ float ts_reduce_2pi(float x) {
-    const float k = rintf(x * 0.15915494309189535f);
-    float r = fmaf(k, -6.2831854820251465f, x);
-    return fmaf(k, 1.7484555e-7f, r);
+// 2^-floor(log2 m) for m > 0 (1 for zero / non-finite m): a bound m of |dL/dz| maps to [1, 2)
+__device__ __forceinline__ float ts_pow2_scale(float m) {
+    int e = (int)((__float_as_uint(m) >> 23) & 0xFFu) - 127;
+    if (!(m > 0.f) || e > 100) e = 0;
+    if (e < -100) e = -100;
+    return __uint_as_float((uint32_t)(127 - e) << 23);
 }
 
 struct TsShared {
-    unsigned char *h1h, *h1l, *r, *w, *gxp;
+    unsigned char *h1h, *h1l, *r, *w;
     // per input feature f < K1: arg = x1 * pb + u0 * pa + pc  (x1 = u1 for Fourier features, theta for heading features;
     // pc carries the bias and +pi/2 for cosine features, so every feature is sin(arg) with derivative cos(arg))
-    float *pa, *pb, *pc, *ang_b, *b1, *b2, *w3h, *scal, *in0, *aux, *skip, *gbar, *zp, *red;
-    uint64_t *wfull, *wempty, *efull, *eempty, *bfull, *bempty, *ready, *done, *tile_free;
+    float *pa, *pb, *pc, *ang_b, *b1, *b2, *w3h, *scal, *in0, *aux, *skip, *gbar, *zp, *gxp, *red;
+    uint64_t *wfull, *wempty, *efull, *eempty, *bfull, *bempty, *ready, *done;
     uint32_t *tmem_slot;
     __device__ TsShared(unsigned char *base, const TsDims &t) {
-        h1h = base + t.off_h1h; h1l = base + t.off_h1l; r = base + t.off_r; w = base + t.off_w; gxp = base + t.off_gx;
+        h1h = base + t.off_h1h; h1l = base + t.off_h1l; r = base + t.off_r; w = base + t.off_w;
         float *f = reinterpret_cast<float *>(base + t.off_misc);
         pa = f; f += t.K1;
         pb = f; f += t.K1;
@@ -214,34 +214,31 @@ struct TsShared {
         skip = f; f += TS_NT;
         gbar = f; f += TS_NT;
         zp = f; f += 4 * TS_NT;
+        gxp = f; f += TS_GX_FLOATS;
         red = f; f += 32;
         uint64_t *b = reinterpret_cast<uint64_t *>(f);
         wfull = b; b += TS_WST;
         wempty = b; b += TS_WST;
-        efull = b; b += TS_EST;
-        eempty = b; b += TS_EST;
+        efull = b; b += 2;
+        eempty = b; b += 2;
         bfull = b; b += 2;
-        bempty = b; b += 2;
-        ready = b++; done = b++; tile_free = b++;
+        bempty = b++;
+        ready = b++; done = b++;
         tmem_slot = reinterpret_cast<uint32_t *>(b);
     }
 };
 
-// three-pass split product: D (+)= Ahi*Bhi + Alo*Bhi + Ahi*Blo
-__device__ __forceinline__ void ts_mma3(uint32_t tmem_d, uint64_t ah, uint64_t al, uint64_t bh, uint64_t bl, uint32_t idesc,
-                                        bool accumulate, uint32_t issue) {
-    mma_bf16(tmem_d, ah, bh, idesc, accumulate ? 1u : 0u, issue);
-    mma_bf16(tmem_d, al, bh, idesc, 1u, issue);
-    mma_bf16(tmem_d, ah, bl, idesc, 1u, issue);
-}
-// K loop of a single-pass GEMM, descriptors advanced by constant strides
-__device__ __forceinline__ void ts_kloop1(uint32_t tmem_d, uint64_t a, uint64_t b, uint32_t a_step, uint32_t b_step, int ksteps,
-                                          uint32_t idesc, uint32_t issue) {
+// K loop of a three-pass split product, descriptors advanced by constant strides:
+// D (+)= sum_k Ahi*Bhi + Alo*Bhi + Ahi*Blo
+__device__ __forceinline__ void ts_kloop3(uint32_t tmem_d, uint64_t ah, uint64_t al, uint64_t bh, uint64_t bl, uint32_t a_step,
+                                          uint32_t b_step, int ksteps, uint32_t idesc, bool accumulate, uint32_t issue) {
     const uint64_t da = a_step >> 4, db = b_step >> 4;
 #pragma unroll 1
     for (int ks = 0; ks < ksteps; ++ks) {
-        mma_bf16(tmem_d, a, b, idesc, ks > 0 ? 1u : 0u, issue);
-        a += da; b += db;
+        mma_bf16(tmem_d, ah, bh, idesc, (accumulate || ks > 0) ? 1u : 0u, issue);
+        mma_bf16(tmem_d, al, bh, idesc, 1u, issue);
+        mma_bf16(tmem_d, ah, bl, idesc, 1u, issue);
+        ah += da; al += da; bh += db; bl += db;
     }
 }
 
@@ -258,8 +255,8 @@ __device__ __forceinline__ void ts_wait(uint64_t *bar, uint32_t use) {     // wa
     fence_after_sync();
 }
 
-// store 16 consecutive columns (col0 .. col0+15) of row `row` into a [row / 8][col / 8][row % 8][col % 8] operand buffer
-__device__ __forceinline__ void ts_store_row16_hl(unsigned char *hi_buf, unsigned char *lo_buf, int row, int col0, const float *v) {
+// store 16 consecutive columns (col0 .. col0+15) of row `row` into [row / 8][col / 8][row % 8][col % 8] operand buffers
+__device__ __forceinline__ void ts_store_row16(unsigned char *hi_buf, unsigned char *lo_buf, int row, int col0, const float *v) {
     uint4 h0, l0, h1, l1;
     split8h(v, h0, l0);
     split8h(v + 8, h1, l1);
@@ -269,19 +266,19 @@ __device__ __forceinline__ void ts_store_row16_hl(unsigned char *hi_buf, unsigne
     *reinterpret_cast<uint4 *>(lo_buf + off) = l0;
     *reinterpret_cast<uint4 *>(lo_buf + off + 128) = l1;
 }
-__device__ __forceinline__ void ts_store_row16_h(unsigned char *hi_buf, int row, int col0, const float *v) {
-    const int off = (row >> 3) * TS_SPT + (col0 >> 3) * 128 + (row & 7) * 16;
-    *reinterpret_cast<uint4 *>(hi_buf + off) = pack8h(v);
-    *reinterpret_cast<uint4 *>(hi_buf + off + 128) = pack8h(v + 8);
-}
 
-// ---- the weight-stream warp (one elected lane): forward ring, then the three backward blocks -------------------------
+// ---- the weight-stream warp (one elected lane): forward ring, then the backward blocks (hi -> slot 0, lo -> slot 1) -------
 __device__ __forceinline__ void ts_producer(const OnfTsArgs &a, const TsShared &s, const unsigned char *src, int n_tiles, bool want_bwd) {
     const TsDims &t = a.t;
     const int c1 = t.K1 / 16, c2 = t.KH / 16;
-    uint32_t wc = 0, b0 = 0, b1 = 0;
+    uint32_t wc = 0, nbe = 0;
+    auto block = [&](const unsigned char *hi, int half, int bytes) {      // one weight block, hi and lo parts
+        mbar_expect_tx(s.bfull + 0, (uint32_t)bytes);
+        bulk_g2s(s.w, hi, bytes, s.bfull + 0);
+        mbar_expect_tx(s.bfull + 1, (uint32_t)bytes);
+        bulk_g2s(s.w + t.b_slot, hi + half, bytes, s.bfull + 1);
+    };
     for (int tile = 0; tile < n_tiles; ++tile) {
-        if (tile > 0 && want_bwd) ts_wait(s.tile_free, tile - 1);       // slots / gx partials of the previous tile are dead
         for (int c = 0; c < c1 + c2; ++c, ++wc) {
             const uint32_t st = wc % TS_WST, k = wc / TS_WST;
             if (k > 0) ts_wait(s.wempty + st, k - 1);
@@ -298,19 +295,16 @@ __device__ __forceinline__ void ts_producer(const OnfTsArgs &a, const TsShared &
         // every forward MMA that reads the ring has completed before the ring is reused as two big slots
         for (uint32_t c = wc > TS_WST ? wc - TS_WST : 0; c < wc; ++c) ts_wait(s.wempty + c % TS_WST, c / TS_WST);
         TS_TRACE(2, 2);
-        mbar_expect_tx(s.bfull + 0, (uint32_t)t.w2_half);
-        bulk_g2s(s.w, src + 2 * t.w1_half, t.w2_half, s.bfull + 0);                     // W2 hi -> slot 0
+        block(src + 2 * t.w1_half, t.w2_half, t.w2_half);                           // W2 -> dgrad2
+        ts_wait(s.bempty, nbe++);
         const int len0 = t.FB0 / 8 * t.S_colW;
-        mbar_expect_tx(s.bfull + 1, (uint32_t)len0);
-        bulk_g2s(s.w + t.b_slot, src, len0, s.bfull + 1);                               // W1 hi, feature block 0 -> slot 1
+        block(src, t.w1_half, len0);                                                // W1, feature block 0 -> dgrad1
+        ts_wait(s.bempty, nbe++);
         if (t.MB == 2) {
-            ts_wait(s.bempty, b0++);                                                    // dgrad2 has read slot 0
-            const int len1 = (t.K1 - t.FB0) / 8 * t.S_colW;
-            mbar_expect_tx(s.bfull + 0, (uint32_t)len1);
-            bulk_g2s(s.w, src + len0, len1, s.bfull + 0);                               // W1 hi, feature block 1 -> slot 0
+            block(src + len0, t.w1_half, (t.K1 - t.FB0) / 8 * t.S_colW);            // W1, feature block 1
+            ts_wait(s.bempty, nbe++);
         }
         TS_TRACE(2, 3);
-        (void)b1;
     }
 }
 
@@ -321,21 +315,32 @@ __device__ __forceinline__ void ts_issuer(const OnfTsArgs &a, const TsShared &s,
     const uint32_t lead = elect_one();
     TS_TRACE(1, 0);
     const uint32_t h1h = smem_u32(s.h1h), h1l = smem_u32(s.h1l), rr = smem_u32(s.r), ww = smem_u32(s.w);
-    const uint32_t tmA = tmem + TS_TM_A, tmDW2 = tmem + TS_TM_DW2, tmDW1a = tmem + TS_TM_DW2 + t.KH;
-    const int c1 = t.K1 / 16, c2 = t.KH / 16;
-    uint32_t wc = 0, ec = 0, nready = 0, nb0 = 0, nb1 = 0;
+    const uint32_t s0 = ww, s1 = ww + t.b_slot;                      // backward weight slots: hi, lo
+    const uint32_t tmA = tmem + TS_TM_A, tmDW2 = tmem + TS_TM_DW2, tmDW1 = tmem + TS_TM_DW1;
+    const int c2 = t.KH / 16;
+    const int n_slots = (t.K1 + TS_EF - 1) / TS_EF;
+    uint32_t wc = 0, ec = 0, nready = 0, nbf = 0;
     for (int tile = 0; tile < n_tiles; ++tile) {
         const int Nt = ts_ru16(min(TS_NT, cnt - tile * TS_NT));
-        // fwd1: D1[j,n] (+)= W1p[j,k] E[n,k], one K = 16 chunk of the weight ring and of the encoding ring at a time
-        for (int ks = 0; ks < c1; ++ks, ++wc, ++ec) {
-            const uint32_t st = wc % TS_WST, sl = ec % TS_EST;
-            ts_wait(s.wfull + st, wc / TS_WST);
-            ts_wait(s.efull + sl, ec / TS_EST);
-            const uint32_t wb = ww + st * t.w_stage, eb = rr + sl * t.e_slot;
-            ts_mma3(tmA, desc_kmajor(wb, 128, t.S_colW), desc_kmajor(wb + 2 * t.S_colW, 128, t.S_colW), desc_kmajor(eb, 128, TS_SPT),
-                    desc_kmajor(eb + 2 * TS_SPT, 128, TS_SPT), instr_desc_f16(128, Nt, 0, 0), ks > 0, lead);
-            mma_commit(s.wempty + st, lead);
-            mma_commit(s.eempty + sl, lead);
+        const bool acc = tile > 0;                                   // weight-gradient accumulators persist across tiles
+        // fwd1: D1[j,n] (+)= W1p[j,k] E[n,k]: one encoding slot (64 features) = up to 4 ring stages of K = 16
+        for (int sl = 0; sl < n_slots; ++sl, ++ec) {
+            const uint32_t es = ec & 1u;
+            ts_wait(s.efull + es, ec >> 1);
+            const uint32_t eb = rr + es * 2 * t.e_half;
+            const int ksl = min(TS_EF, t.K1 - sl * TS_EF) / 16;
+            for (int ks = 0; ks < ksl; ++ks, ++wc) {
+                const uint32_t st = wc % TS_WST;
+                ts_wait(s.wfull + st, wc / TS_WST);
+                const uint32_t wb = ww + st * t.w_stage;
+                const uint32_t idesc = instr_desc_f16(128, Nt, 0, 0);
+                const bool first = sl == 0 && ks == 0;
+                mma_bf16(tmA, desc_kmajor(wb, 128, t.S_colW), desc_kmajor(eb + ks * 2 * TS_SPT, 128, TS_SPT), idesc, first ? 0u : 1u, lead);
+                mma_bf16(tmA, desc_kmajor(wb + 2 * t.S_colW, 128, t.S_colW), desc_kmajor(eb + ks * 2 * TS_SPT, 128, TS_SPT), idesc, 1u, lead);
+                mma_bf16(tmA, desc_kmajor(wb, 128, t.S_colW), desc_kmajor(eb + t.e_half + ks * 2 * TS_SPT, 128, TS_SPT), idesc, 1u, lead);
+                mma_commit(s.wempty + st, lead);
+            }
+            mma_commit(s.eempty + es, lead);
         }
         mma_commit(s.done, lead);
         TS_TRACE(1, 1);
@@ -346,44 +351,54 @@ __device__ __forceinline__ void ts_issuer(const OnfTsArgs &a, const TsShared &s,
             const uint32_t st = wc % TS_WST;
             ts_wait(s.wfull + st, wc / TS_WST);
             const uint32_t wb = ww + st * t.w_stage;
-            ts_mma3(tmA, desc_kmajor(wb, 128, t.S_colW), desc_kmajor(wb + 2 * t.S_colW, 128, t.S_colW),
-                    desc_mnmajor(h1h + ks * 2 * TS_SPT, TS_SPT, 128), desc_mnmajor(h1l + ks * 2 * TS_SPT, TS_SPT, 128),
-                    instr_desc_f16(128, Nt, 0, 1), ks > 0, lead);
+            ts_kloop3(tmA, desc_kmajor(wb, 128, t.S_colW), desc_kmajor(wb + 2 * t.S_colW, 128, t.S_colW),
+                      desc_mnmajor(h1h + ks * 2 * TS_SPT, TS_SPT, 128), desc_mnmajor(h1l + ks * 2 * TS_SPT, TS_SPT, 128), 0, 0, 1,
+                      instr_desc_f16(128, Nt, 0, 1), ks > 0, lead);
             mma_commit(s.wempty + st, lead);
         }
         mma_commit(s.done, lead);
         TS_TRACE(1, 3);
         if (!want_bwd) continue;
-        // wgrad2: dW2[i,j] = gH2[i,n] H1[j,n];   dgrad2: gD1[j,n] = W2p[i,j] gH2[i,n]     (gH2 lives in the old encoding ring)
+        // wgrad2: dW2[i,j] += gH2[i,n] H1[j,n];   dgrad2: gD1[j,n] = W2p[i,j] gH2[i,n]     (gH2 hi, lo in the old encoding ring)
         ts_wait(s.ready, nready++);
         TS_TRACE(1, 4);
-        ts_wait(s.bfull + 0, nb0++);
-        TS_TRACE(1, 5);
         if (want_wgrad)
-            ts_kloop1(tmDW2, desc_kmajor(rr, TS_SPT, 128), desc_kmajor(h1h, TS_SPT, 128), 256, 256, Nt / 16, instr_desc_f16(128, t.KH, 0, 0),
-                      lead);
-        ts_kloop1(tmA, desc_mnmajor(ww, 128, t.S_colW), desc_mnmajor(rr, TS_SPT, 128), 256, 2 * TS_SPT, c2, instr_desc_f16(128, Nt, 1, 1), lead);
+            ts_kloop3(tmDW2, desc_kmajor(rr, TS_SPT, 128), desc_kmajor(rr + t.h1_half, TS_SPT, 128), desc_kmajor(h1h, TS_SPT, 128),
+                      desc_kmajor(h1l, TS_SPT, 128), 256, 256, Nt / 16, instr_desc_f16(128, t.KH, 0, 0), acc, lead);
+        ts_wait(s.bfull + 0, nbf);
+        ts_wait(s.bfull + 1, nbf);
+        ++nbf;
+        TS_TRACE(1, 5);
+        ts_kloop3(tmA, desc_mnmajor(s0, 128, t.S_colW), desc_mnmajor(s1, 128, t.S_colW), desc_mnmajor(rr, TS_SPT, 128),
+                  desc_mnmajor(rr + t.h1_half, TS_SPT, 128), 256, 2 * TS_SPT, c2, instr_desc_f16(128, Nt, 1, 1), false, lead);
         mma_commit(s.bempty, lead);
         mma_commit(s.done, lead);
         TS_TRACE(1, 6);
-        // dgrad1, feature block 0: gE[k,n] = W1p[j,k] gH1[j,n]      (gH1 in place over H1 hi)
+        // dgrad1, feature block 0: gE[k,n] = W1p[j,k] gH1[j,n]      (gH1 hi, lo in place over H1 hi, lo)
         ts_wait(s.ready, nready++);
         TS_TRACE(1, 7);
-        ts_wait(s.bfull + 1, nb1++);
+        ts_wait(s.bfull + 0, nbf);
+        ts_wait(s.bfull + 1, nbf);
+        ++nbf;
         TS_TRACE(1, 8);
-        ts_kloop1(tmA, desc_mnmajor(ww + t.b_slot, 128, t.S_colW), desc_mnmajor(h1h, TS_SPT, 128), 256, 2 * TS_SPT, c2,
-                  instr_desc_f16(128, Nt, 1, 1), lead);
+        ts_kloop3(tmA, desc_mnmajor(s0, 128, t.S_colW), desc_mnmajor(s1, 128, t.S_colW), desc_mnmajor(h1h, TS_SPT, 128),
+                  desc_mnmajor(h1l, TS_SPT, 128), 256, 2 * TS_SPT, c2, instr_desc_f16(128, Nt, 1, 1), false, lead);
+        mma_commit(s.bempty, lead);
         mma_commit(s.done, lead);
         for (int mb = 0; mb < t.MB; ++mb) {
-            ts_wait(s.ready, nready++);                 // block mb of gE consumed, E^T of block mb written
+            ts_wait(s.ready, nready++);                 // block mb of gE consumed, E^T of block mb written (hi, lo)
             TS_TRACE(1, 9 + 2 * mb);
-            if (want_wgrad)                             // wgrad1: dW1[j, block mb] = gH1[j,n] E[n, block mb]
-                ts_kloop1(mb == 0 ? tmDW1a : tmA, desc_kmajor(h1h, TS_SPT, 128), desc_kmajor(h1l, 128, t.S_ET), 256, 2 * t.S_ET, Nt / 16,
-                          instr_desc_f16(128, min(t.FB0, t.K1 - mb * t.FB0), 0, 0), lead);
+            if (want_wgrad)                             // wgrad1: dW1[j, block mb] += gH1[j,n] E[n, block mb]
+                ts_kloop3(tmDW1 + mb * t.FB0, desc_kmajor(h1h, TS_SPT, 128), desc_kmajor(h1l, TS_SPT, 128), desc_kmajor(rr, 128, t.S_ET),
+                          desc_kmajor(rr + t.et_half, 128, t.S_ET), 256, 2 * t.S_ET, Nt / 16,
+                          instr_desc_f16(128, min(t.FB0, t.K1 - mb * t.FB0), 0, 0), acc, lead);
             if (mb + 1 < t.MB) {
-                ts_wait(s.bfull + 0, nb0++);
-                ts_kloop1(tmA, desc_mnmajor(ww, 128, t.S_colW), desc_mnmajor(h1h, TS_SPT, 128), 256, 2 * TS_SPT, c2,
-                          instr_desc_f16(128, Nt, 1, 1), lead);
+                ts_wait(s.bfull + 0, nbf);
+                ts_wait(s.bfull + 1, nbf);
+                ++nbf;
+                ts_kloop3(tmA, desc_mnmajor(s0, 128, t.S_colW), desc_mnmajor(s1, 128, t.S_colW), desc_mnmajor(h1h, TS_SPT, 128),
+                          desc_mnmajor(h1l, TS_SPT, 128), 256, 2 * TS_SPT, c2, instr_desc_f16(128, Nt, 1, 1), false, lead);
+                mma_commit(s.bempty, lead);
             }
             if (want_wgrad || mb + 1 < t.MB) mma_commit(s.done, lead);
             TS_TRACE(1, 10 + 2 * mb);
@@ -391,8 +406,30 @@ __device__ __forceinline__ void ts_issuer(const OnfTsArgs &a, const TsShared &s,
     }
 }
 
+// one octet of encoded features for one point: e[i] = sin(x1 * pb + u0 * pa + pc), x1 = u1 (Fourier) or theta (heading)
+__device__ __forceinline__ void ts_encode8(const TsShared &s, int f0, int F, float u0, float u1, float th, uint4 &hi, uint4 &lo) {
+    float e[8], pa[8], pb[8], pc[8];
+    *reinterpret_cast<float4 *>(pa) = *reinterpret_cast<const float4 *>(s.pa + f0);
+    *reinterpret_cast<float4 *>(pa + 4) = *reinterpret_cast<const float4 *>(s.pa + f0 + 4);
+    *reinterpret_cast<float4 *>(pb) = *reinterpret_cast<const float4 *>(s.pb + f0);
+    *reinterpret_cast<float4 *>(pb + 4) = *reinterpret_cast<const float4 *>(s.pb + f0 + 4);
+    *reinterpret_cast<float4 *>(pc) = *reinterpret_cast<const float4 *>(s.pc + f0);
+    *reinterpret_cast<float4 *>(pc + 4) = *reinterpret_cast<const float4 *>(s.pc + f0 + 4);
+    if (f0 + 8 <= F) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) e[i] = __sinf(fmaf(u1, pb[i], fmaf(u0, pa[i], pc[i])));
+    } else if (f0 >= F) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) e[i] = __sinf(fmaf(th, pb[i], pc[i]));
+    } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) e[i] = __sinf(fmaf(f0 + i < F ? u1 : th, pb[i], fmaf(u0, pa[i], pc[i])));
+    }
+    split8h(e, hi, lo);
+}
+
 // Thread layout: 18 warps.  Warps 0..15 are workers: warp = 4*cq + q, q = TMEM lane quarter (rows 32q..32q+31), cq = which
-// 16-column chunks of the tile (cq, cq+4, ...); a thread owns one hidden unit / feature (`row`).  Warp 16 issues every
+// 16-column chunks of the tile (cq, cq+4); a thread owns one hidden unit / feature (`row`).  Warp 16 issues every
 // tcgen05.mma, warp 17 streams the weights.
 __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs a) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -414,14 +451,13 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
     const float *W = a.weights + (size_t)p * L.n_params;
     TS_TRACE(0, 0);
 
-    // ---- one-time setup: barriers, TMEM, per-feature / per-unit fp32 parameters ----
+    // ---- one-time setup: barriers, TMEM, per-feature / per-unit fp32 parameters, gradient operand scale ----
     if (tid == 0) {
         for (int i = 0; i < TS_WST; ++i) { mbar_init(s.wfull + i, 1); mbar_init(s.wempty + i, 1); }
-        for (int i = 0; i < TS_EST; ++i) { mbar_init(s.efull + i, TS_WORKERS / 32); mbar_init(s.eempty + i, 1); }
-        for (int i = 0; i < 2; ++i) { mbar_init(s.bfull + i, 1); mbar_init(s.bempty + i, 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(s.efull + i, TS_WORKERS / 32); mbar_init(s.eempty + i, 1); mbar_init(s.bfull + i, 1); }
+        mbar_init(s.bempty, 1);
         mbar_init(s.ready, TS_WORKERS / 32);
         mbar_init(s.done, 1);
-        mbar_init(s.tile_free, TS_WORKERS / 32);
         fence_mbar_init();
     }
     if (is_issuer) tmem_alloc(s.tmem_slot, 512);
@@ -453,11 +489,35 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
         s.b2[i] = i < H ? W[L.off_b[1] + i] : 0.f;
         s.w3h[i] = i < H ? W[L.off_w_out + i] : 0.f;
     }
-    if (tid == 0) { s.scal[0] = W[L.off_b_out]; s.scal[1] = 1.f; s.scal[2] = 1.f; }
+    {
+        // bound of |dL/dz| over the problem -> power-of-two scale of the fp16 gradient operands (one scale for all tiles:
+        // the weight-gradient accumulators are shared): external gz / multipliers are scanned, BCE is bounded by 1 / N
+        float m = 0.f;
+        if (want_bwd && (a.gbar_mode == 0 || a.gbar_mode == 3)) {
+            const float *src = (a.gbar_mode == 0 ? a.gz : a.aux) + (size_t)p * a.n;
+            for (int i = tid; i < cnt; i += TS_THREADS) m = fmaxf(m, fabsf(src[i]));
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+        if (lane == 0) s.red[warp] = m;
+    }
     fence_before_sync();
     __syncthreads();
     fence_after_sync();
+    if (tid == 0) {
+        float m = 0.f;
+        for (int i = 0; i < TS_THREADS / 32; ++i) m = fmaxf(m, s.red[i]);
+        if (a.gbar_mode == 1) m = 1.f / (float)cnt;
+        else if (a.gbar_mode == 2) m = fabsf(a.wc);
+        else if (a.gbar_mode == 3) m += fabsf(a.wc);
+        const float S = want_bwd ? ts_pow2_scale(m) : 1.f;
+        s.scal[0] = W[L.off_b_out];
+        s.scal[1] = S;
+        s.scal[2] = 1.f / S;
+    }
+    __syncthreads();
     const uint32_t tmem = *s.tmem_slot;
+    const float S = s.scal[1], invS = s.scal[2];
     TS_TRACE(0, 1);
 
     // worker identity (the two service warps compute harmless values)
@@ -477,6 +537,7 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
         uint32_t ndone = 0, ec = 0;
         const float my_b1 = row < H ? s.b1[row] : 0.f, my_b2 = row < H ? s.b2[row] : 0.f, my_w3 = row < H ? s.w3h[row] : 0.f;
         float *u0s = s.in0, *u1s = s.in0 + TS_NT, *ths = s.in0 + 2 * TS_NT;
+        const int n_slots = (K1 + TS_EF - 1) / TS_EF;
         for (int tile = 0; tile < n_tiles; ++tile) {
             const int n0 = tile * TS_NT;
             const int nv = min(TS_NT, cnt - n0);
@@ -502,36 +563,30 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
             }
             ts_worker_sync();
             TS_TRACE(0, 2);
-            // ---- P1: encoding (CUDA cores) feeding fwd1 in chunks of 16 features: thread = (point, feature octet) ----
+            // ---- P1: encoding (CUDA cores) feeding fwd1 in slots of 64 features: thread = (point, feature octets g, g+4) ----
             {
-                const bool e_on = tid < 2 * Nt;
-                const int fo = tid >= Nt ? 1 : 0, n = tid - fo * Nt;
+                const int g = tid / Nt, n = tid - g * Nt;
+                const bool e_on = g < 4;
                 const float u0 = e_on ? u0s[n] : 0.f, u1 = e_on ? u1s[n] : 0.f, th = e_on ? ths[n] : 0.f;
 #pragma unroll 1
-                for (int ks = 0; ks < K1 / 16; ++ks, ++ec) {
-                    const uint32_t sl = ec % TS_EST;
-                    uint4 ehi, elo;
-                    if (e_on) {
-                        const int f0 = 16 * ks + 8 * fo;
-                        float e[8], pa[8], pb[8], pc[8];
-                        *reinterpret_cast<float4 *>(pa) = *reinterpret_cast<const float4 *>(s.pa + f0);
-                        *reinterpret_cast<float4 *>(pa + 4) = *reinterpret_cast<const float4 *>(s.pa + f0 + 4);
-                        *reinterpret_cast<float4 *>(pb) = *reinterpret_cast<const float4 *>(s.pb + f0);
-                        *reinterpret_cast<float4 *>(pb + 4) = *reinterpret_cast<const float4 *>(s.pb + f0 + 4);
-                        *reinterpret_cast<float4 *>(pc) = *reinterpret_cast<const float4 *>(s.pc + f0);
-                        *reinterpret_cast<float4 *>(pc + 4) = *reinterpret_cast<const float4 *>(s.pc + f0 + 4);
-#pragma unroll
-                        for (int i = 0; i < 8; ++i)
-                            e[i] = __sinf(ts_reduce_2pi(ts_feature_arg(pa[i], pb[i], pc[i], u0, f0 + i < F ? u1 : th)));
-                        split8h(e, ehi, elo);
+                for (int sl = 0; sl < n_slots; ++sl, ++ec) {
+                    const uint32_t es = ec & 1u;
+                    const int fa = TS_EF * sl + 8 * g, fb = fa + 32;
+                    const bool on_a = e_on && fa < K1, on_b = e_on && fb < K1;
+                    uint4 ah = {}, al = {}, bh = {}, bl = {};
+                    if (on_a) ts_encode8(s, fa, F, u0, u1, th, ah, al);
+                    if (on_b) ts_encode8(s, fb, F, u0, u1, th, bh, bl);
+                    if (ec >= 2) ts_wait(s.eempty + es, (ec >> 1) - 1);        // fwd1 of the slot's previous use is done
+                    unsigned char *eb = s.r + es * 2 * t.e_half + g * TS_SPT + n * 16;
+                    if (on_a) {
+                        *reinterpret_cast<uint4 *>(eb) = ah;
+                        *reinterpret_cast<uint4 *>(eb + t.e_half) = al;
                     }
-                    if (ec >= TS_EST) ts_wait(s.eempty + sl, ec / TS_EST - 1);      // fwd1 of the chunk that used this slot is done
-                    if (e_on) {
-                        unsigned char *eb = s.r + sl * t.e_slot + fo * TS_SPT + n * 16;
-                        *reinterpret_cast<uint4 *>(eb) = ehi;
-                        *reinterpret_cast<uint4 *>(eb + 2 * TS_SPT) = elo;
+                    if (on_b) {
+                        *reinterpret_cast<uint4 *>(eb + 4 * TS_SPT) = bh;
+                        *reinterpret_cast<uint4 *>(eb + 4 * TS_SPT + t.e_half) = bl;
                     }
-                    ts_signal(s.efull + sl);
+                    ts_signal(s.efull + es);
                 }
             }
             TS_TRACE(0, 3);
@@ -553,7 +608,7 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
 #pragma unroll
                     for (int i = 0; i < 16; ++i) v[i] = 0.f;
                 }
-                if (row < KH) ts_store_row16_hl(s.h1h, s.h1l, row, c0, v);
+                if (row < KH) ts_store_row16(s.h1h, s.h1l, row, c0, v);
             }
             ts_signal(s.ready);                           // -> fwd2
             TS_TRACE(0, 5);
@@ -573,13 +628,12 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
             TS_TRACE(0, 7);
             if (tid < TS_NT) {
                 const int n = tid;
-                const bool valid = n < nv;
                 float gb = 0.f;
-                if (n < Nt) {
+                if (n < nv) {
                     const float z = s.zp[n] + s.zp[TS_NT + n] + s.zp[2 * TS_NT + n] + s.zp[3 * TS_NT + n] + s.skip[n] + s.scal[0];
                     const size_t gi = (size_t)p * a.n + n0 + n;
-                    if (valid && a.z_out) a.z_out[gi] = z;
-                    if (valid && want_bwd) {                        // dL/dz
+                    if (a.z_out) a.z_out[gi] = z;
+                    if (want_bwd) {                                 // dL/dz
                         const float ax = s.aux[n];
                         if (a.gbar_mode == 0) gb = ax;
                         else if (a.gbar_mode == 1) gb = (sigmoid_f(z) - ax) / (float)cnt;
@@ -588,40 +642,19 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
                             const float ez = expf(zb);
                             gb = a.wc * (zb > 20.f ? 1.f : ez / (ez + 1.f));
                             if (a.gbar_mode == 3) {
-                                const float th = tanhf(z);
-                                gb += ax * (1.f - th * th);
+                                const float tz = tanhf(z);
+                                gb += ax * (1.f - tz * tz);
                             }
                         }
                     }
                 }
                 s.gbar[n] = gb;
                 acc_db3 += gb;
-                if (want_bwd) {                                     // largest |dL/dz| of the tile -> power-of-two operand scale
-                    float m = fabsf(gb);
-#pragma unroll
-                    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-                    if (lane == 0) s.red[warp] = m;
-                }
             }
+            ts_worker_sync();
             TS_TRACE(0, 8);
-            if (!want_bwd) {
-                ts_worker_sync();                         // zp / skip / inputs are rewritten by the next tile
-                continue;
-            }
-            ts_worker_sync();
-            if (tid == 0) {
-                float m = 0.f;
-                for (int i = 0; i < TS_NT / 32; ++i) m = fmaxf(m, s.red[i]);
-                // S = 2^-floor(log2 m): the largest scaled |dL/dz| lies in [1, 2); non-finite or zero -> 1
-                int e = (int)((__float_as_uint(m) >> 23) & 0xFFu) - 127;
-                if (!(m > 0.f) || e > 100) e = 0;
-                if (e < -100) e = -100;
-                s.scal[1] = __uint_as_float((uint32_t)(127 - e) << 23);
-                s.scal[2] = __uint_as_float((uint32_t)(127 + e) << 23);
-            }
-            ts_worker_sync();
-            const float S = s.scal[1], invS = s.scal[2];
-            // ---- P4: epilogue 2, second pass: gH2 = dL/dz * w3 * 1[h2 > 0] (scaled, fp16) -> old encoding ring ----
+            if (!want_bwd) continue;
+            // ---- P4: epilogue 2, second pass: gH2 = dL/dz * w3 * 1[h2 > 0] (scaled, fp16 hi + lo) -> old encoding ring ----
             for (int ch = cq; ch < nch; ch += 4) {
                 const int c0 = 16 * ch;
                 float r2[16], v[16];
@@ -635,11 +668,11 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
                     acc_db2 += gg;
                     v[i] = gg * S;
                 }
-                if (row < KH) ts_store_row16_h(s.r, row, c0, v);
+                if (row < KH) ts_store_row16(s.r, s.r + t.h1_half, row, c0, v);
             }
             ts_signal(s.ready);                           // -> wgrad2 + dgrad2
             TS_TRACE(0, 9);
-            // ---- P5: epilogue 3: ReLU mask of layer 1 -> gH1 operand (in place over H1 hi); row H := dL/dz ----
+            // ---- P5: epilogue 3: ReLU mask of layer 1 -> gH1 operand (in place over H1 hi, lo); row H := dL/dz ----
             ts_wait(s.done, ndone++);
             TS_TRACE(0, 10);
             for (int ch = cq; ch < nch; ch += 4) {
@@ -666,11 +699,11 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
 #pragma unroll
                     for (int i = 0; i < 16; ++i) v[i] = 0.f;
                 }
-                if (row < KH) ts_store_row16_h(s.h1h, row, c0, v);
+                if (row < KH) ts_store_row16(s.h1h, s.h1l, row, c0, v);
             }
             ts_signal(s.ready);                           // -> dgrad1 (block 0)
             TS_TRACE(0, 11);
-            // ---- P6: epilogue 4 per feature block: encoding backward (+ input gradient), E^T operand, wgrad1 ----
+            // ---- P6: epilogue 4 per feature block: encoding backward (+ input gradient), E^T operand (hi, lo), wgrad1 ----
 #pragma unroll 1
             for (int mb = 0; mb < t.MB; ++mb) {
                 ts_wait(s.done, ndone++);                 // gE of block mb (and wgrad1 of block mb - 1: E^T is free again)
@@ -684,44 +717,51 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
                 const float ew0 = (f_on && fourier) ? ppa : 0.f, ew1 = (f_on && fourier) ? ppb : 0.f,
                             eaf = (f_on && !fourier && f < FIN) ? ppb : 0.f;
                 const float *x1src = fourier ? u1s : ths;
-                float ta = 0.f, tb = 0.f, tc = 0.f;      // sum gp*u0, sum gp*x1, sum gp
-                float *gxp = reinterpret_cast<float *>(s.gxp);
+                float ta = 0.f, tb = 0.f, tc = 0.f;      // sum gp*u0, sum gp*x1, sum gp  (all still scaled by S)
                 for (int ch = cq; ch < nch; ch += 4) {
                     const int c0 = 16 * ch;
-                    float v[16], gq[16], ev[16];
+                    float v[16], ev[16], xu[16], x1[16];
                     tmem_ld16(tA + c0, v);
 #pragma unroll
+                    for (int i4 = 0; i4 < 4; ++i4) {
+                        *reinterpret_cast<float4 *>(xu + 4 * i4) = *reinterpret_cast<const float4 *>(u0s + c0 + 4 * i4);
+                        *reinterpret_cast<float4 *>(x1 + 4 * i4) = *reinterpret_cast<const float4 *>(x1src + c0 + 4 * i4);
+                    }
+#pragma unroll
                     for (int i = 0; i < 16; ++i) {
-                        const float xu = u0s[c0 + i], x1 = x1src[c0 + i];
-                        const float r = ts_reduce_2pi(ts_feature_arg(ppa, ppb, ppc, xu, x1));
-                        const float gp = f_on ? v[i] * invS * __cosf(r) : 0.f;
-                        ev[i] = f_on ? __sinf(r) : 0.f;
-                        gq[i] = gp;
-                        ta = fmaf(gp, xu, ta);
-                        tb = fmaf(gp, x1, tb);
+                        const float arg = fmaf(x1[i], ppb, fmaf(xu[i], ppa, ppc));
+                        const float gp = (f_on ? v[i] : 0.f) * __cosf(arg);      // rows beyond the block hold garbage
+                        ev[i] = __sinf(arg);                                       // (= 0 there: pa = pb = pc = 0)
+                        v[i] = gp;
+                        ta = fmaf(gp, xu[i], ta);
+                        tb = fmaf(gp, x1[i], tb);
                         tc += gp;
                     }
                     if (want_gx) {
                         // gx[n] = (sum_f gp[f,n] * We[f,c]) / sigma ; g_theta[n] = sum_k gp[k,n] * f_k   (reduce over lanes)
                         float cv[16];
-                        float *dst = gxp + ((size_t)q * TS_NT + c0 + (lane >> 1)) * 3;
+                        float *dst = s.gxp + ((size_t)q * TS_NT + c0 + (lane >> 1)) * 3;
 #pragma unroll
                         for (int c = 0; c < 3; ++c) {
                             const float wgt = c == 0 ? ew0 : c == 1 ? ew1 : eaf;
 #pragma unroll
-                            for (int i = 0; i < 16; ++i) cv[i] = gq[i] * wgt;
+                            for (int i = 0; i < 16; ++i) cv[i] = v[i] * wgt;
                             const float sum = ts_colsum16(cv, lane);
                             if ((lane & 1) == 0) dst[c] = mb == 0 ? sum : dst[c] + sum;
                         }
                     }
-                    if (want_wgrad && row < t.FB0) {     // E^T operand [point / 8][feature][8 points]
+                    if (want_wgrad && row < t.FB0) {     // E^T operand [point / 8][feature][8 points], hi and lo
 #pragma unroll
                         for (int o = 0; o < 2; ++o) {
                             const int off = ((c0 >> 3) + o) * t.S_ET + (row >> 3) * 128 + (row & 7) * 16;
-                            *reinterpret_cast<uint4 *>(s.h1l + off) = pack8h(ev + 8 * o);
+                            uint4 eh, el;
+                            split8h(ev + 8 * o, eh, el);
+                            *reinterpret_cast<uint4 *>(s.r + off) = eh;
+                            *reinterpret_cast<uint4 *>(s.r + t.et_half + off) = el;
                         }
                     }
                 }
+                ta *= invS; tb *= invS; tc *= invS;
                 if (f_on && !fourier) {                   // heading features: d ang_b = f_k * sum gp,
                     const float b = f < FIN ? s.ang_b[f - F] : 0.f;   // d ang_f = sum gp * (theta + b_k)  (trained)
                     tb = fmaf(b, tc, tb);
@@ -736,24 +776,22 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
                 ts_worker_sync();
                 if (tid < nv) {
                     const int n = tid;
-                    const float *gxp = reinterpret_cast<const float *>(s.gxp);
                     float g0 = 0.f, g1 = 0.f, g2 = 0.f;
 #pragma unroll
                     for (int qq = 0; qq < 4; ++qq) {
-                        const float *src = gxp + ((size_t)qq * TS_NT + n) * 3;
+                        const float *src = s.gxp + ((size_t)qq * TS_NT + n) * 3;
                         g0 += src[0]; g1 += src[1]; g2 += src[2];
                     }
                     float *out = a.gx_out + ((size_t)p * a.n + n0 + n) * a.x_stride;
-                    out[0] = g0 / d.sigma;
-                    out[1] = g1 / d.sigma;
-                    if (L.in_dim == 3) out[2] = g2;
+                    out[0] = g0 * invS / d.sigma;
+                    out[1] = g1 * invS / d.sigma;
+                    if (L.in_dim == 3) out[2] = g2 * invS;
                     for (int c = L.in_dim; c < a.x_stride; ++c) out[c] = 0.f;   // pose columns the ONF does not read
                 }
             }
-            if (want_wgrad) ts_wait(s.done, ndone++);     // the last wgrad1
+            if (want_wgrad) ts_wait(s.done, ndone++);     // the last wgrad1: E^T (= the encoding ring) and gH1 are free again
             TS_TRACE(0, 16);
             ts_worker_sync();                             // zp, gx, skip, gbar, inputs are rewritten by the next tile
-            ts_signal(s.tile_free);
         }
     }
     fence_before_sync();
@@ -765,10 +803,8 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
     if (want_wgrad) {
         // every MMA has completed: the operand buffers are dead, shared memory [0, n_params) floats now holds the
         // gradient of the whole parameter blob (same element order as the fp32 weights)
-        const float invS = s.scal[2];
         float *G = reinterpret_cast<float *>(smem_raw);
         float *red = G + ((L.n_params + 31) & ~31);                    // [10][4][128] partial per-unit sums
-        __syncthreads();                                               // invS read before the staging area is cleared
         const int np4 = L.n_params / 4;
         for (int i = tid; i < np4; i += TS_THREADS) reinterpret_cast<float4 *>(G)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         const bool is_worker = warp < TS_WORKERS / 32;
@@ -777,8 +813,8 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
             r0[0 * 512] = acc_db1; r0[1 * 512] = acc_db2; r0[2 * 512] = acc_dw3;
             r0[3 * 512] = fa0; r0[4 * 512] = fb0; r0[5 * 512] = fc0;
             r0[6 * 512] = fa1; r0[7 * 512] = fb1; r0[8 * 512] = fc1;
-            if (tid < TS_NT) {
-                const float s3 = warp_sum(acc_db3);
+            if (tid < 128) {                                           // (acc_db3 lives in threads 0 .. TS_NT-1, zero elsewhere)
+                const float s3 = warp_sum(tid < TS_NT ? acc_db3 : 0.f);
                 if (lane == 0) red[9 * 512 + warp] = s3;
             }
         }
@@ -787,7 +823,7 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
         for (int ch = cq; ch < (is_worker ? K1 / 16 : 0); ch += 4) {
             float g[16];
             const int f0 = 16 * ch;
-            tmem_ld16(tm_lane + (f0 < t.FB0 ? TS_TM_DW2 + KH + f0 : TS_TM_A + (f0 - t.FB0)), g);
+            tmem_ld16(tm_lane + TS_TM_DW1 + f0, g);
             if (row <= H) {
                 float *dst = G + (row < H ? L.off_w[0] + row * FIN : L.off_w_out + H) + f0;
 #pragma unroll
@@ -834,7 +870,7 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
             }
             if (tid == 0) {
                 float g3 = 0.f;
-                for (int i = 0; i < TS_NT / 32; ++i) g3 += red[9 * 512 + i];
+                for (int i = 0; i < 4; ++i) g3 += red[9 * 512 + i];
                 G[L.off_b_out] = g3;
             }
         }
@@ -926,11 +962,10 @@ bool onf_tcs_supported(const OnfDims &d) {
     TsDims t;
     return ts_make_dims(d, &t);
 }
-int onf_tcs_tile_points() { return TS_NT; }
 
 int onf_tcs_prepare(const OnfDims &d) {
     TsDims t;
-    NFOPP_REQUIRE(ts_make_dims(d, &t), "onf(tensor, streamed): needs 2 hidden layers, hidden <= 111, f_in <= 224 (hidden=%d layers=%d)",
+    NFOPP_REQUIRE(ts_make_dims(d, &t), "onf(tensor, streamed): needs 2 hidden layers, hidden <= 111, f_in <= 256 (hidden=%d layers=%d)",
                   d.H, d.L);
     NFOPP_CHECK_CUDA(cudaFuncSetAttribute(onf_tcs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, t.smem_bytes));
     return NFOPP_OK;
@@ -961,8 +996,6 @@ int onf_tcs_launch(const OnfArgs &o, const OnfTcExtra &x, int P, cudaStream_t st
     a.w1 = x.w1; a.beta2 = x.beta2; a.w2 = x.w2; a.eps = x.eps; a.warm = x.warm;
     NFOPP_REQUIRE(a.packed, "onf(tensor): packed operand copy missing");
     NFOPP_REQUIRE(!a.adam_w || (a.sp && a.packed_out), "onf(tensor): fused Adam needs step parameters and the packed copy");
-    NFOPP_REQUIRE(!(a.want_bwd && (a.grad_out || a.adam_w)) || a.n <= TS_NT,
-                  "onf(tensor, streamed): weight gradients need at most %d points per problem (got %d)", TS_NT, a.n);
     if (a.n == 0 || P == 0) return NFOPP_OK;
     onf_tcs_kernel<<<P, TS_THREADS, a.t.smem_bytes, stream>>>(a);
     NFOPP_CHECK_CUDA(cudaGetLastError());

@@ -19,7 +19,7 @@ def main():
         w = torch.stack([O.init_blob(cfg, True, gen) for _ in range(P)])
         x = torch.rand(P, n, cfg.in_dim, generator=gen) * 3
         gz = torch.randn(P, n, generator=gen) / n
-        want_gw = n <= 224
+        want_gw = True
         try:
             if want_gw:
                 z, gx, gw = T._onf_call(cfg, w, x, gz, impl=2)
