@@ -41,8 +41,8 @@ PROBLEMS_PER_GPU = 1024
 
 
 WORKLOADS = ("corridor", "forest", "gridmap-wide")
-TENSOR_IMPL = ("tensor (fused tcgen05 kernel, one 224-point tile per problem, streamed fp16 hi/lo weights: forward 3 passes, "
-               "backward 1 pass of hi parts with a power-of-two gradient scale, fp32 TMEM accumulators, fused Adam)")
+TENSOR_IMPL = ("tensor (fused tcgen05 kernel, 112-point tiles, streamed fp16 hi/lo weights, every product 3 MMA passes "
+               "(hi.hi + lo.hi + hi.lo), static power-of-two gradient scale, fp32 TMEM accumulators, fused Adam)")
 FOREST_TOTAL = 16384            # BASELINE configs[2]: problems of the whole job, sharded over the GPUs
 
 
@@ -419,7 +419,7 @@ def roofline_block(m, count, peaks):
         "tensor_view": {"achieved": flops_launch / (train_ms * 1e-3) / 1e12, "peak": peak_tf, "unit": "TFLOP/s",
                         "frac": flops_launch / (train_ms * 1e-3) / 1e12 / peak_tf,
                         "algorithmic_flops_per_launch": flops_launch,
-                        "note": "6 x MAC x points; the forward products issue 3 MMAs each (fp16 hi/lo), the backward 1"},
+                        "note": "6 x MAC x points; every product issues 3 MMAs (fp16 hi/lo split), not counted here"},
         "dominant_kernel": max(prof, key=prof.get),
         "kernel_share_of_step": prof["onf_train_fwd_bwd"] / max(sum(prof.values()), 1e-9),
     }
@@ -603,7 +603,7 @@ def run_ours(args):
     line = {
         "metric": METRIC, "value": m["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": m["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32 (tensor path: fp16 hi/lo split products - forward 3 passes, backward 1 - fp32 accumulate)" if impl != "fma" else "f32",
+        "dtype": "f32 (tensor path: fp16 hi/lo split products, 3 MMA passes each, fp32 accumulate)" if impl != "fma" else "f32",
         "data": "synthetic", "config": workload_config(P, impl, args.workload),
         "clocks": m["clocks"], "e2e": m["e2e"], "gpu_launches": m["launches"],
         "roofline": roof, "kernel_ms": m["prof"], "streams": streams,

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define NFOPP_ABI_VERSION 3
+#define NFOPP_ABI_VERSION 4
 #define NFOPP_MAX_LAYERS 8
 
 typedef enum {
@@ -240,6 +240,13 @@ int nfopp_engine_path_statistics(nfopp_engine *e, double cusp_angle_threshold, i
  * count (per-problem RNG streams keep their global problem index; on the wide ONF path every lane takes its own slice of
  * the activation workspace and the call fails if the slices do not fit). */
 int nfopp_engine_set_lanes(nfopp_engine *e, int lanes);
+/* NERFOptPlanner.set_boundaries (nerf_opt_planner.py:220-222: the rectangle the uniform field points are drawn from) and
+ * CollisionChecker.update_boundaries (collision_checker/collision_checker.py:24-25: the rectangle outside of which every pose
+ * collides) on a live engine, without re-creating it: both are part of the kernels' arguments, so the captured step graph is
+ * dropped and re-captured by the next nfopp_engine_step.  sample_border (x0,x1,y0,y1) or NULL = unchanged;
+ * checker_bounds_mode: -1 unchanged, 0 the checker has no boundaries, 1 use checker_bounds (x0,x1,y0,y1).  State, counters
+ * and the ONF operand copy are untouched. */
+int nfopp_engine_set_bounds(nfopp_engine *e, const double *sample_border, int checker_bounds_mode, const double *checker_bounds);
 /* PathPostprocessor.process (ros/path_postprocessor.py:13-71) for P paths of n nodes each (what the ROS adapter does to a
  * path before publishing it): nodes closer than minimal_distance to their successor are dropped, the path is
  * re-sampled every distance_step metres along its chord-length parametrisation with scipy's quadratic interpolating

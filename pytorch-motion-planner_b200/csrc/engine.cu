@@ -764,6 +764,23 @@ extern "C" int nfopp_engine_set_lanes(nfopp_engine *e, int lanes) {
     return NFOPP_OK;
 }
 
+extern "C" int nfopp_engine_set_bounds(nfopp_engine *e, const double *sample_border, int checker_bounds_mode,
+                                       const double *checker_bounds) {
+    NFOPP_REQUIRE(e && checker_bounds_mode >= -1 && checker_bounds_mode <= 1, "set_bounds: bad arguments");
+    NFOPP_REQUIRE(checker_bounds_mode != 1 || checker_bounds, "set_bounds: checker_bounds missing");
+    if (sample_border)
+        for (int i = 0; i < 4; ++i) e->cfg.border[i] = sample_border[i];
+    if (checker_bounds_mode >= 0) {
+        e->cfg.has_bounds = checker_bounds_mode;
+        for (int i = 0; i < 4; ++i) e->cfg.bounds[i] = checker_bounds_mode ? checker_bounds[i] : 0.0;
+    }
+    fill_dev_config(e);
+    // kernel arguments are captured by value: the next graphed step re-captures
+    if (e->graph_exec) { cudaGraphExecDestroy(e->graph_exec); e->graph_exec = nullptr; }
+    if (e->graph) { cudaGraphDestroy(e->graph); e->graph = nullptr; }
+    return NFOPP_OK;
+}
+
 extern "C" int nfopp_engine_warmup(nfopp_engine *e, int iterations, void *stream) {
     NFOPP_REQUIRE(e && iterations >= 0, "warmup: bad arguments");
     cudaStream_t s = (cudaStream_t)stream;

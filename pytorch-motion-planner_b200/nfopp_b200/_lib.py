@@ -83,6 +83,7 @@ SIGNATURES = {
     "nfopp_postprocess_workspace_bytes": (_I, [_I, _I, _P]),
     "nfopp_postprocess_paths": (_I, [_P, _I, _I, C.c_double, C.c_double, _I, _P, C.c_size_t, _P, _P, _P]),
     "nfopp_engine_set_lanes": (_I, [_P, _I]),
+    "nfopp_engine_set_bounds": (_I, [_P, _P, _I, _P]),
     "nfopp_engine_launch_count": (_I, [_P, C.POINTER(C.c_int64)]),
 }
 
@@ -104,7 +105,7 @@ def lib():
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(handle, name)
             fn.restype, fn.argtypes = res, args
-        if handle.nfopp_abi_version() != 3:
+        if handle.nfopp_abi_version() != 4:
             raise NfoppError("libnfopp.so ABI version mismatch")
         _lib = handle
     return _lib

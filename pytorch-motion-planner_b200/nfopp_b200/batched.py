@@ -6,6 +6,8 @@ is the one exchange (torch.distributed all_gather of the final [P_local, T+2, D]
 import math
 from dataclasses import replace
 
+import os
+
 import numpy as np
 import torch
 
@@ -65,6 +67,8 @@ class BatchedPlanner:
         # corridor problems: 1.104 ms/step with 1 lane, 1.047 with 2, 1.070 with 4)
         # (the wide ONF path's persistent kernels gain nothing from lanes: 4.78 -> 4.98 ms/step at 2 lanes, so auto keeps 1)
         narrow = config.onf_impl in ("fma", "tensor") or (config.onf_impl == "auto" and config.onf.layers == 2 and config.onf.hidden <= 111)
+        if lanes == "auto" and os.environ.get("NFOPP_LANES"):      # profiling: one launch per kernel over all problems
+            lanes = int(os.environ["NFOPP_LANES"])
         self.lanes = (2 if config.problems >= 296 and narrow else 1) if lanes == "auto" else int(lanes)
         if self.lanes > 1:
             try:

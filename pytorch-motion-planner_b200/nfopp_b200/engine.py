@@ -319,6 +319,22 @@ class PlannerEngine:
         (bit-identical results; overlaps the small latency-bound kernels of one lane with the ONF kernels of another)."""
         L.check(self._lib.nfopp_engine_set_lanes(self._h, int(lanes)))
 
+    def set_bounds(self, border=None, checker_bounds="unchanged"):
+        """set_boundaries (nerf_opt_planner.py:220-222) / update_boundaries (collision_checker.py:24-25) on the live engine:
+        the step graph is re-captured, nothing else changes."""
+        b = None if border is None else (C.c_double * 4)(*[float(v) for v in border])
+        if checker_bounds == "unchanged":
+            mode, cb = -1, None
+        elif checker_bounds is None:
+            mode, cb = 0, None
+        else:
+            mode, cb = 1, (C.c_double * 4)(*[float(v) for v in checker_bounds])
+        L.check(self._lib.nfopp_engine_set_bounds(self._h, b, mode, cb))
+        if border is not None:
+            self.config.border = tuple(float(v) for v in border)
+        if mode >= 0:
+            self.config.checker_bounds = None if mode == 0 else tuple(float(v) for v in checker_bounds)
+
     def profile_step(self) -> dict:
         """One un-graphed step with CUDA events between its kernels -> {kernel name: milliseconds}."""
         ms = (C.c_float * 9)()

@@ -39,6 +39,9 @@ class NERFOptPlanner(ContinuousPlanner):
         self._rng_mode, self._seed, self._use_graph = rng_mode, seed, use_graph
         self._engine = None
         self._checker_version = -1
+        self._checker_spec = None          # engine_spec() the live engine was built from
+        self._optimizer_key = None         # (lr, betas, eps) of both optimisers the live engine was built from
+        self._weights_version = -1
         d = trajectory.shape[1]
         self._start_point = torch.zeros(1, d, device=self._device)
         self._goal_point = torch.zeros(1, d, device=self._device)
@@ -47,10 +50,29 @@ class NERFOptPlanner(ContinuousPlanner):
     def _extra_config(self):
         return {}
 
+    SUPPORTED_CHECKERS = ("CollisionChecker (boundary only)", "CircleCollisionChecker", "CircleDirectedCollisionChecker",
+                          "RectangleCollisionChecker", "GridCollisionChecker (the notebook's MapCollisionChecker)")
+
+    def _checker_engine_spec(self):
+        """The reference calls collision_checker.check_collision(positions) on ANY object every step
+        (nerf_opt_planner.py:93-96).  Here labelling runs inside the CUDA step, so the checker must be one whose arithmetic
+        exists as a device kernel; a user-defined checker cannot be called from the GPU and there is no CPU fallback."""
+        cc = self._collision_checker
+        if not hasattr(cc, "engine_spec"):
+            raise TypeError(f"collision checker {type(cc).__name__} cannot run inside the CUDA planner step: supported are "
+                            f"nfopp_b200.collision_checker.{{{', '.join(self.SUPPORTED_CHECKERS)}}} "
+                            "(labelling is a device kernel; there is no CPU fallback - see INTEGRATION.md)")
+        return cc.engine_spec()
+
+    def _optimizer_hyperparameters(self):
+        og = self._collision_optimizer.param_groups[0]
+        tg = self._trajectory_optimizer.param_groups[0]
+        return (float(og["lr"]), tuple(og["betas"]), float(og["eps"]), float(tg["lr"]), tuple(tg["betas"]))
+
     def _engine_config(self) -> EngineConfig:
         og = self._collision_optimizer.param_groups[0]
         tg = self._trajectory_optimizer.param_groups[0]
-        spec = self._collision_checker.engine_spec()
+        spec = self._checker_engine_spec()
         obstacles = np.asarray(self._collision_checker._obstacle_points).reshape(-1, 2)
         seed = self._seed if self._seed is not None else int(np.random.randint(0, 2 ** 31 - 1))
         cfg = EngineConfig(
@@ -65,10 +87,12 @@ class NERFOptPlanner(ContinuousPlanner):
             optimize_collision_model_freq=self._optimize_collision_model_freq,
             random_field_points=self._random_field_points, course_random_offset=self._course_random_offset,
             collision_point_count=self._collision_point_count, env_shared=True,
-            max_obstacles=max(64, len(obstacles)), border=tuple(float(b) for b in self._random_sample_border),
+            max_obstacles=max(64, 2 * len(obstacles)), border=tuple(float(b) for b in self._random_sample_border),
             rng_mode=self._rng_mode, seed=seed, **self._extra_config())
         for k, v in spec.items():
             setattr(cfg, k, v)
+        self._checker_spec = dict(spec)
+        self._optimizer_key = self._optimizer_hyperparameters()
         return cfg
 
     def _build_engine(self, keep_state=False):
@@ -89,10 +113,26 @@ class NERFOptPlanner(ContinuousPlanner):
         self._sync_environment(force=True)
 
     def _sync_environment(self, force=False):
+        """The reference re-reads obstacle points AND boundaries on every check_collision call
+        (collision_checker/*.py); here both live in the engine, so every change of the checker is carried over: new
+        boundaries through nfopp_engine_set_bounds, a cloud that outgrew the obstacle buffer (ros/collision_checker_adapter.py
+        feeds a lidar cloud of a different size on every callback) or any other change of the checker's geometry by
+        re-creating the engine around the exported state."""
         cc = self._collision_checker
         if not force and cc._version == self._checker_version:
             return
         eng = self._engine
+        if not force:
+            spec = self._checker_engine_spec()
+            old = self._checker_spec or {}
+            changed = {k for k in spec if spec[k] != old.get(k)}
+            n_obs = len(np.asarray(cc._obstacle_points).reshape(-1, 2)) if cc.kind in ("circle", "rectangle") else 0
+            if changed - {"checker_bounds"} or n_obs > eng.config.max_obstacles:
+                self._build_engine(keep_state=True)          # (ends in _sync_environment(force=True))
+                return
+            if "checker_bounds" in changed:
+                eng.set_bounds(checker_bounds=spec["checker_bounds"])
+                self._checker_spec = dict(spec)
         if cc.kind in ("circle", "rectangle"):
             eng.set_obstacles(np.asarray(cc._obstacle_points, dtype=np.float64).reshape(-1, 2))
         elif cc.kind == "grid":
@@ -101,9 +141,18 @@ class NERFOptPlanner(ContinuousPlanner):
 
     # ---- ContinuousPlanner API -----------------------------------------------------------------------
     def init(self, start_point, goal_point, boundaries):
+        """nerf_opt_planner.py:181-187: new end points, a fresh initial trajectory, the ONF warm-up and step_count = 0 -
+        nothing else.  On a second init() (a new goal, ros/goal_planner_adapter.py:36) the optimisers' moments and step
+        counters, the replay buffer, _previous_trajectory and the multipliers persist, as they do in the reference."""
         d = self._trajectory.shape[1]
         self._random_sample_border = boundaries
-        self._build_engine()
+        if self._engine is None:
+            self._build_engine()
+        elif self._optimizer_hyperparameters() != self._optimizer_key:
+            self._build_engine(keep_state=True)
+        else:
+            self._engine.set_bounds(border=boundaries)
+            self._sync_environment()
         eng = self._engine
         eng.set_endpoints(np.asarray(start_point, dtype=np.float32)[:d], np.asarray(goal_point, dtype=np.float32)[:d])
         self._start_point, self._goal_point = eng["start"], eng["goal"]
@@ -123,10 +172,17 @@ class NERFOptPlanner(ContinuousPlanner):
             raise RuntimeError("call init(start_point, goal_point, boundaries) before step()")
         timer.tick("step")
         self._sync_environment()
+        # the reference steps caller-owned torch.optim.Adam objects (planner_factory.py:54-58,68-70): a caller may change
+        # param_groups[0]["lr" | "betas" | "eps"] between steps - carry it over (engine re-created around its state)
+        if self._optimizer_hyperparameters() != self._optimizer_key:
+            self._build_engine(keep_state=True)
         # the caller holds the ONF module whose parameters are views of the engine's weights (planner._collision_model,
-        # scripts/run_planner.py:72-73) and may have written them: have the tensor path refresh its operand copy
-        self._engine.invalidate_weights()
+        # scripts/run_planner.py:72-73): only when torch has written into them since the last step (a version counter
+        # moved) does the tensor path have to rebuild its operand copy
+        if self._collision_model.weights_version() != self._weights_version:
+            self._engine.invalidate_weights()
         self._engine.step(1, graph=self._use_graph and self._rng_mode == "philox")
+        self._weights_version = self._collision_model.weights_version()
         timer.tock("step")
 
     def full_trajectory(self):
@@ -136,9 +192,10 @@ class NERFOptPlanner(ContinuousPlanner):
         return self.full_trajectory().detach().cpu().numpy()
 
     def set_boundaries(self, boundaries):
+        """nerf_opt_planner.py:220-222: store the sampling rectangle, reset the step counter (no engine re-creation)."""
         self._random_sample_border = boundaries
         if self._engine is not None:
-            self._build_engine(keep_state=True)
+            self._engine.set_bounds(border=boundaries)
             self._engine.set_counter("step_count", 0)
 
     def reparametrize_trajectory(self):

@@ -144,6 +144,12 @@ class ONF(nn.Module):
             self._repack()
         return self._flat
 
+    def weights_version(self):
+        """Changes whenever torch wrote into the weights: through the packed blob or through any parameter (each parameter
+        keeps its own version counter - `.data = view` does not share the blob's).  Kernel-side updates do not move it."""
+        flat = self.packed_parameters()
+        return (flat._version,) + tuple(p._version for _, p in self._param_segments())
+
     # ---- reference call signature ---------------------------------------------------------------------
     def forward(self, x):
         flat = self.packed_parameters()

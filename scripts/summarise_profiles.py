@@ -100,8 +100,18 @@ def main():
             wr = to_bytes(d["dram__bytes_write.sum"], d["_units"]["dram__bytes_write.sum"])
             p = os.path.join(ROOT, "profiles", "roofline_traffic.json")
             t = json.load(open(p)) if os.path.exists(p) else {}
-            t[a.traffic_key] = rd + wr
-            t[a.traffic_key + "_detail"] = {"read": rd, "write": wr, "source": f"{name} launch {a.traffic_launch} ({a.note})"}
+            import sys
+            sys.path.insert(0, ROOT)
+            import bench                                          # the sha bench.py will compare against at run time
+            commit = subprocess.run(["git", "-C", ROOT, "rev-parse", "--short", "HEAD"], capture_output=True, text=True).stdout.strip()
+            dirty = subprocess.run(["git", "-C", ROOT, "status", "--porcelain", "--", "pytorch-motion-planner_b200/csrc"],
+                                   capture_output=True, text=True).stdout.strip()
+            t[a.traffic_key] = {
+                "bytes": rd + wr, "read": rd, "write": wr, "sources_sha": bench.kernel_sources_sha(),
+                "commit": commit + ("+uncommitted csrc changes" if dirty else ""),
+                "source": f"{name} launch {a.traffic_launch} ({a.note})",
+                "launch_shape": f"grid {int(d.get('launch__grid_size', 0))} x block {int(d.get('launch__block_size', 0))}, "
+                                f"{d.get('gpu__time_duration.sum')} {d['_units'].get('gpu__time_duration.sum')} under ncu"}
             json.dump(t, open(p, "w"), indent=1)
 
 

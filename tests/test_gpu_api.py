@@ -307,3 +307,117 @@ def test_init_angles_with_trajectory_on_the_device():
     assert bool(torch.isfinite(bp.paths()).all())
     plain.engine.close()
     bp.engine.close()
+
+
+# ---------------------------------------------------------------------------------------- drop-in surface between steps
+def _car_planner(**planner_over):
+    from nfopp_b200.collision_checker import RectangleCollisionChecker
+    from nfopp_b200.planner_factory import PlannerFactory
+    from nfopp_b200.test_environment_builder import TestEnvironmentBuilder
+    np.random.seed(400); torch.manual_seed(100)
+    env = TestEnvironmentBuilder().make_car_environment()
+    checker = RectangleCollisionChecker((-0.3, 0.2, -0.3, 0.2), (0, 3, 0, 3))
+    checker.update_obstacle_points(env.obstacle_points)
+    params = _attr(RUN_PLANNER)
+    params["planner"].update(planner_over)
+    planner = PlannerFactory.make_constrained_onf_planner(checker, params)
+    return planner, env, checker
+
+
+@pytest.mark.gpu
+def test_environment_changes_between_steps_reach_the_engine():
+    """The reference re-reads obstacle points and boundaries on every check_collision call (collision_checker/*.py;
+    ros/collision_checker_adapter.py feeds a lidar cloud of a different size on every callback): a cloud that outgrows the
+    engine's obstacle buffer and new checker boundaries must both show up in the next step's labels."""
+    from oracle import checkers as OC
+    planner, env, checker = _car_planner()
+    planner.init(env.start_point, env.goal_point, env.bounds)
+    planner.step()
+    cap = planner._engine.config.max_obstacles
+    rs = np.random.RandomState(3)
+    cloud = np.concatenate([env.obstacle_points, rs.uniform(0.2, 2.8, size=(3 * cap, 2))], 0)     # larger than the buffer
+    checker.update_obstacle_points(cloud)
+    planner.step()
+    assert planner._engine.config.max_obstacles >= len(cloud)
+    poses, labels = planner._checked()
+    assert np.array_equal(labels, OC.rectangle_labels(poses, cloud, (-0.3, 0.2, -0.3, 0.2), (0, 3, 0, 3)))
+    assert planner._step_count == 2 and planner._engine.counter("onf_step") == 2                  # state carried over
+    eng_before = planner._engine
+    checker.update_boundaries((0.5, 2.5, 0.5, 2.5))
+    planner.step()
+    assert planner._engine is eng_before                                                          # bounds only: no re-creation
+    poses, labels = planner._checked()
+    assert np.array_equal(labels, OC.rectangle_labels(poses, cloud, (-0.3, 0.2, -0.3, 0.2), (0.5, 2.5, 0.5, 2.5)))
+    assert labels[(poses[:, 0] < 0.5) | (poses[:, 0] > 2.5)].all()
+    checker.update_obstacle_points(env.obstacle_points)                                           # and back to a small cloud
+    planner.step()
+    poses, labels = planner._checked()
+    assert np.array_equal(labels, OC.rectangle_labels(poses, env.obstacle_points, (-0.3, 0.2, -0.3, 0.2), (0.5, 2.5, 0.5, 2.5)))
+
+
+@pytest.mark.gpu
+def test_second_init_keeps_optimiser_state_and_replay_buffer():
+    """nerf_opt_planner.py:181-187: init() re-initialises the trajectory, warms the ONF up and resets step_count - the
+    optimisers' moments and step counters, the replay buffer, _previous_trajectory and the multipliers persist across goals
+    (ros/goal_planner_adapter.py:36 calls init() for every new goal)."""
+    planner, env, checker = _car_planner(init_collision_iteration=2)
+    planner.init(env.start_point, env.goal_point, env.bounds)
+    for _ in range(12):
+        planner.step()
+    eng = planner._engine
+    before = {k: eng[k].clone() for k in ("onf_m", "onf_v", "traj_m", "traj_v", "buf_pos", "buf_age", "lam", "mu", "prev_traj")}
+    w_before = eng["onf_w"].clone()
+    onf_step, traj_step = eng.counter("onf_step"), eng.counter("traj_step")
+    assert onf_step == 14 and traj_step == 12 and int(eng["buf_n"][0]) == 100
+    new_goal = np.array([2.2, 2.5, 0.3], dtype=np.float32)
+    planner.init(env.start_point, new_goal, env.bounds)
+    assert planner._engine is eng                                       # no re-allocation, no graph re-capture
+    assert planner._step_count == 0
+    assert eng.counter("onf_step") == onf_step + 2                      # the warm-up continued the ONF optimiser
+    assert eng.counter("traj_step") == traj_step and eng.counter("has_prev") == 1
+    for k in ("traj_m", "traj_v", "buf_pos", "buf_age", "lam", "mu", "prev_traj"):
+        assert torch.equal(eng[k], before[k]), k
+    assert not torch.equal(eng["onf_m"], before["onf_m"]) and not torch.equal(eng["onf_w"], w_before)   # two warm-up updates
+    path = planner.get_path()
+    assert np.allclose(path[0], env.start_point) and np.allclose(path[-1], new_goal)
+    assert np.allclose(path[1:-1, 0], np.linspace(env.start_point[0], new_goal[0], 102)[1:-1], atol=1e-6)
+    planner.step()
+    assert np.isfinite(planner.get_path()).all() and eng.counter("traj_step") == traj_step + 1
+
+
+@pytest.mark.gpu
+def test_live_optimisers_boundaries_and_unsupported_checkers():
+    """Callers of the reference own the torch.optim.Adam objects (planner_factory.py:54-58,68-70): a learning rate changed
+    between steps is picked up; set_boundaries (nerf_opt_planner.py:220-222) does not re-create the engine; a checker the
+    CUDA step cannot run is refused with a TypeError naming the supported ones; an untouched ONF is not re-packed."""
+    from nfopp_b200.planner_factory import PlannerFactory
+    planner, env, checker = _car_planner()
+    planner.init(env.start_point, env.goal_point, env.bounds)
+    planner.step()
+    launches = planner._engine.launches
+    planner.step()
+    per_step = planner._engine.launches - launches
+    planner.step()
+    assert planner._engine.launches - launches == 2 * per_step          # no extra pack launch when nobody wrote the weights
+    with torch.no_grad():
+        planner._collision_model.mlp[0].bias.add_(0.0)                  # an in-place write through the module's view
+    planner.step()
+    assert planner._engine.launches - launches == 3 * per_step + 1      # operand copy rebuilt once
+    eng = planner._engine
+    planner.set_boundaries((0.2, 2.8, 0.2, 2.8))
+    assert planner._engine is eng and planner._step_count == 0
+    planner.step()
+    uni = planner._checked()[0][-10:]                                   # the step's 10 uniform field points
+    assert (uni[:, :2] >= 0.2).all() and (uni[:, :2] <= 2.8).all()
+    planner._collision_optimizer.param_groups[0]["lr"] = 0.0
+    w = planner._engine["onf_w"].clone()
+    planner.step()
+    assert torch.equal(planner._engine["onf_w"], w), "lr = 0 on the caller's optimiser must freeze the ONF weights"
+    assert planner._engine.counter("step_count") == 2
+
+    class Homemade:
+        def check_collision(self, positions):
+            return np.zeros(len(positions), dtype=bool)
+    bad = PlannerFactory.make_constrained_onf_planner(Homemade(), _attr(RUN_PLANNER))
+    with pytest.raises(TypeError, match="RectangleCollisionChecker"):
+        bad.init(env.start_point, env.goal_point, env.bounds)
