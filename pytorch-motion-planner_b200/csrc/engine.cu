@@ -321,6 +321,12 @@ static EngineDev slice_problems(const nfopp_engine *e, int p0, int count, int la
     d.P = count;
     d.p_base = e->dev.p_base + p0;
     if (e->impl == 3) d.onf_ws = e->dev.onf_ws + (size_t)lane * e->lane_ws_stride;   // wide path: one activation workspace per lane
+    if (e->impl == 2 && e->dev.gslots > 0) {
+        // streamed tensor kernel: every lane owns an equal share of the gradient hand-over buffers
+        const int lanes = e->lanes > 0 ? e->lanes : 1;
+        d.gslots = e->dev.gslots / lanes > 0 ? e->dev.gslots / lanes : 1;
+        d.onf_gpart = e->dev.onf_gpart + (size_t)lane * d.gslots * 2 * e->onf.lay.n_params;
+    }
     return d;
 }
 
@@ -368,7 +374,11 @@ static int build_layout(nfopp_engine *e) {
     add_buffer(e, "onf_v", &d.onf_v, 'f', P, NP);
     if (e->impl == 2) {
         // the tensor path accumulates weight gradients in TMEM and applies Adam in the same kernel: no partials
-        add_buffer(e, "onf_gpart", &d.onf_gpart, 'f', 1, 1, 4);
+        // (streamed kernel: its persistent CTAs hand each problem's gradient to their optimiser warps through a pair of
+        // L2-resident buffers per CTA)
+        d.gslots = onf_tc_variant(e->onf, (int)NTR) == 1 ? (int)(P < (size_t)ONF_TCS_SCRATCH_SLOTS ? P : (size_t)ONF_TCS_SCRATCH_SLOTS) : 0;
+        if (d.gslots > 0) add_buffer(e, "onf_gpart", &d.onf_gpart, 'f', d.gslots, 2, NP);
+        else add_buffer(e, "onf_gpart", &d.onf_gpart, 'f', 1, 1, 4);
         add_buffer(e, "onf_wp", &d.onf_wp, 'b', P, onf_tc_packed_bytes(e->onf));
     } else if (e->impl == 3) {
         // wide path: per-layer grouped GEMMs; one reduced gradient per problem, operand copies of the weights and
@@ -619,6 +629,7 @@ static int enqueue_train(nfopp_engine *e, const EngineDev &d, bool warm, cudaStr
         a.sp = d.sp;
         OnfTcExtra x{};
         x.packed = d.onf_wp; x.adam_w = d.onf_w; x.adam_m = d.onf_m; x.adam_v = d.onf_v; x.packed_out = d.onf_wp;
+        x.gscratch = d.onf_gpart; x.gscratch_slots = d.gslots;
         x.w1 = w1; x.beta2 = beta2; x.w2 = w2; x.eps = eps; x.warm = warm;
         x.variant = e->tc_variant;
         if ((rc = onf_tc_launch(a, x, d.P, s))) return rc;

@@ -40,6 +40,7 @@ struct EngineDev {
     int reparam_freq, train_freq;
     CheckerParams checker;
     int env_shared, m_max;
+    int gslots;                            // streamed tensor kernel: gradient hand-over buffer pairs behind onf_gpart
     // state
     StepParams *sp;
     float *onf_w, *onf_m, *onf_v, *onf_gpart;

@@ -43,6 +43,8 @@ struct OnfTcExtra {
     float w1, beta2, w2, eps;      // 1-beta1, beta2, 1-beta2, eps; step size / bias correction come from StepParams
     int warm;                      // warm-up iteration: ignore StepParams::do_train
     int variant;                   // 0: first generation (onf_tc.cu, bf16 operands, resident weights); 1: streamed (onf_tcs.cu, fp16)
+    float *gscratch;               // streamed kernel with fused Adam: [gscratch_slots, 2, n_params] gradient hand-over buffers
+    int gscratch_slots;            //   (one pair per persistent CTA: the grid is capped at this many CTAs)
 };
 
 bool onf_tc_supported(const OnfDims &d);            // 2 hidden layers, hidden <= 111, f_in <= 224
@@ -55,6 +57,8 @@ int onf_tc_launch(const OnfArgs &a, const OnfTcExtra &x, int P, cudaStream_t str
 // must be packed by the variant that reads it.
 bool onf_tcs_supported(const OnfDims &d);
 int onf_tcs_prepare(const OnfDims &d);
+int onf_tcs_grid(int P, int slots);                 // CTAs of the persistent kernel for P problems (slots > 0: cap)
+constexpr int ONF_TCS_SCRATCH_SLOTS = 320;           // hand-over buffer pairs an engine owns (split evenly between its lanes)
 int onf_tcs_pack(const OnfDims &d, const float *weights, unsigned char *packed, int P, cudaStream_t stream);
 int onf_tcs_launch(const OnfArgs &a, const OnfTcExtra &x, int P, cudaStream_t stream);
 // which generation serves a tensor-path call whose weight-gradient launches see at most n_wgrad points per problem

@@ -32,6 +32,8 @@
 // memory and streams it through Adam (planner_factory.py:68), rewriting the fp16 operand copy - as onf_tc.cu does.
 //
 // Supported: 2 hidden layers, hidden <= 111, f_in <= 256 (the reference's network shapes), any point count.
+#include <stdlib.h>
+
 #include "onf.cuh"
 #include "tc05.cuh"
 
@@ -41,7 +43,7 @@ using namespace tc05;
 // optional phase trace (build with -DNFOPP_TC_TRACE; scripts/tcs_trace.py): clock64 stamps of worker thread 0, the issue
 // warp and the weight-stream warp of the first and last CTA
 #ifdef NFOPP_TC_TRACE
-__device__ long long g_ts_trace[3][2][3][64];   // [launch kind: fwd | train | path][first / last CTA][worker | issuer | producer][slot]
+__device__ long long g_ts_trace[3][2][4][64];   // [launch kind: fwd | train | path][first / last CTA][worker | issuer | producer | optimiser][slot]
 #define TS_TRACE(role, slot)                                                                                              \
     do {                                                                                                                \
         if ((threadIdx.x & 31) == 0 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1) && (slot) < 64 &&               \
@@ -51,9 +53,23 @@ __device__ long long g_ts_trace[3][2][3][64];   // [launch kind: fwd | train | p
 #else
 #define TS_TRACE(role, slot) do { } while (0)
 #endif
+#ifdef NFOPP_TC_TRACE
+#define TS_TRACE_VAL(role, slot, val)                                                                                    \
+    do {                                                                                                                \
+        if ((threadIdx.x & 31) == 0 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1))                                \
+            g_ts_trace[!a.want_bwd ? 0 : ((a.grad_out || a.adam_w) ? 1 : 2)][blockIdx.x == 0 ? 0 : 1][(role)][(slot)] = (val); \
+    } while (0)
+#define TS_CLOCK() clock64()
+#else
+#define TS_TRACE_VAL(role, slot, val) do { } while (0)
+#define TS_CLOCK() 0LL
+#endif
 
 constexpr int TS_WORKERS = 512;                 // 16 epilogue / encoding warps
-constexpr int TS_THREADS = TS_WORKERS + 64;     // + MMA-issue warp + weight-stream warp
+constexpr int TS_OPT_WARPS = 6;                 // optimiser warps (Adam + operand-copy refresh of the PREVIOUS problem)
+constexpr int TS_OPT = 32 * TS_OPT_WARPS;
+constexpr int TS_THREADS = TS_WORKERS + 64 + TS_OPT;   // + MMA-issue warp + weight-stream warp + optimiser warps
+constexpr int TS_REGS_WORKER = 88, TS_REGS_SERVICE = 64;   // setmaxnreg split of the 768 x 80 registers the CTA starts with: 512 x 88 + 256 x 64
 constexpr int TS_NT = 112;                      // points per tile
 constexpr uint32_t TS_SPT = TS_NT * 16;         // S_row of the point-indexed operand buffers [hidden / 8][point / 8][8][8]
 constexpr int TS_WST = 8;                       // weight ring stages (K = 16 chunk of W, hi + lo)
@@ -65,11 +81,12 @@ struct TsDims {
     int F, A, FIN, H, K1, KH, MB, FB0;           // MB feature blocks of FB0 (last one shorter) for dgrad1 / wgrad1
     int S_colW, w1_half, w2_half;                // packed operand copy: [W1 hi | W1 lo | W2 hi | W2 lo], each [k / 8][row][8]
     int h1_half, e_half, w_stage, b_slot, S_ET, et_half;
-    int off_h1h, off_h1l, off_r, off_w, off_misc, misc_floats, smem_bytes, packed_bytes;
+    int off_h1h, off_h1l, off_r, off_w, off_misc, misc_floats, off_bar, smem_bytes, packed_bytes;
 };
 
 __host__ __device__ inline int ts_ru16(int x) { return (x + 15) / 16 * 16; }
 __host__ __device__ inline int ts_max(int a, int b) { return a > b ? a : b; }
+__host__ __device__ inline int ts_min(int a, int b) { return a < b ? a : b; }
 
 __host__ __device__ inline bool ts_make_dims(const OnfDims &d, TsDims *out) {
     TsDims t{};
@@ -88,17 +105,16 @@ __host__ __device__ inline bool ts_make_dims(const OnfDims &d, TsDims *out) {
     t.b_slot = 16 * t.S_colW;                    // a 128-row MN-major A operand never reads past its slot
     t.off_h1h = 0;
     t.off_h1l = t.h1_half;
-    t.off_r = 2 * t.h1_half;                     // encoding ring (2 slots, hi + lo) | gH2 hi, lo | E^T hi, lo
-    t.off_w = t.off_r + ts_max(ts_max(4 * t.e_half, 2 * t.h1_half), 2 * t.et_half);
-    const int operands = t.off_w + ts_max(TS_WST * t.w_stage, 2 * t.b_slot);
-    // the epilogue stages the whole gradient blob (+ 20 KB of per-unit partial sums) over the dead operand buffers
-    const int stage_bytes = ((d.lay.n_params + 31) / 32 * 32 + 10 * 512) * 4;
-    t.off_misc = ts_max(operands, (stage_bytes + 127) / 128 * 128);
+    t.off_r = 2 * t.h1_half;                     // encoding ring (2 slots, hi + lo) | gH2 hi, lo | E^T hi, lo | per-unit partial sums
+    t.off_w = t.off_r + ts_max(ts_max(4 * t.e_half, 2 * t.h1_half), ts_max(2 * t.et_half, 10 * 512 * 4));
+    t.off_misc = t.off_w + ts_max(TS_WST * t.w_stage, 2 * t.b_slot);
     t.misc_floats = 3 * t.K1 + 32 + 3 * t.KH + 8 + 10 * TS_NT + TS_GX_FLOATS + 32;
-    t.smem_bytes = t.off_misc + t.misc_floats * 4 + 64 * 8 + 16;
+    t.off_bar = (t.off_misc + t.misc_floats * 4 + 127) / 128 * 128;
+    t.smem_bytes = t.off_bar + 64 * 8 + 16;
     t.packed_bytes = 2 * t.w1_half + 2 * t.w2_half;
     *out = t;
-    return d.L == 2 && t.KH <= TS_NT && t.K1 <= 256 && t.H >= 8 && (int)TS_TM_DW1 + t.K1 <= 512 && t.smem_bytes <= 227 * 1024;
+    return d.L == 2 && t.KH <= TS_NT && t.K1 <= 256 && t.H >= 8 && t.H % 4 == 0 && t.FIN % 4 == 0 &&
+           (int)TS_TM_DW1 + t.K1 <= 512 && t.smem_bytes <= 227 * 1024;
 }
 
 struct OnfTsArgs {
@@ -109,7 +125,7 @@ struct OnfTsArgs {
     const float *x;
     const int32_t *count;
     const StepParams *sp;
-    int n, x_stride;
+    int P, n, x_stride;
     int want_bwd;
     int gbar_mode;
     const float *gz, *aux;
@@ -117,9 +133,11 @@ struct OnfTsArgs {
     float *z_out, *gx_out;
     float *grad_out;
     float *adam_w, *adam_m, *adam_v;
+    float *gscratch;               // fused Adam: [gridDim.x, 2, n_params] gradient hand-over buffers (workers -> optimiser warps)
     unsigned char *packed_out;
     float w1, beta2, w2, eps;
     int warm;
+    int dbg;                       // trace builds: NFOPP_TCS_DBG bit 0 skips the operand-copy stores, bit 1 the w / m / v stores (timing only)
 };
 
 struct TsPackArgs {
@@ -196,7 +214,7 @@ struct TsShared {
     // per input feature f < K1: arg = x1 * pb + u0 * pa + pc  (x1 = u1 for Fourier features, theta for heading features;
     // pc carries the bias and +pi/2 for cosine features, so every feature is sin(arg) with derivative cos(arg))
     float *pa, *pb, *pc, *ang_b, *b1, *b2, *w3h, *scal, *in0, *aux, *skip, *gbar, *zp, *gxp, *red;
-    uint64_t *wfull, *wempty, *efull, *eempty, *bfull, *bempty, *ready, *done;
+    uint64_t *wfull, *wempty, *efull, *eempty, *bfull, *bempty, *ready, *done, *gfull, *gempty;
     uint32_t *tmem_slot;
     __device__ TsShared(unsigned char *base, const TsDims &t) {
         h1h = base + t.off_h1h; h1l = base + t.off_h1l; r = base + t.off_r; w = base + t.off_w;
@@ -208,7 +226,7 @@ struct TsShared {
         b1 = f; f += t.KH;
         b2 = f; f += t.KH;
         w3h = f; f += t.KH;
-        scal = f; f += 8;                           // [0] b3, [1] S (gradient operand scale), [2] 1 / S
+        scal = f; f += 8;                           // [0] b3
         in0 = f; f += 3 * TS_NT;                    // u0 | u1 | theta
         aux = f; f += TS_NT;
         skip = f; f += TS_NT;
@@ -216,7 +234,7 @@ struct TsShared {
         zp = f; f += 4 * TS_NT;
         gxp = f; f += TS_GX_FLOATS;
         red = f; f += 32;
-        uint64_t *b = reinterpret_cast<uint64_t *>(f);
+        uint64_t *b = reinterpret_cast<uint64_t *>(base + t.off_bar);
         wfull = b; b += TS_WST;
         wempty = b; b += TS_WST;
         efull = b; b += 2;
@@ -224,6 +242,8 @@ struct TsShared {
         bfull = b; b += 2;
         bempty = b++;
         ready = b++; done = b++;
+        gfull = b; b += 2;
+        gempty = b; b += 2;
         tmem_slot = reinterpret_cast<uint32_t *>(b);
     }
 };
@@ -267,9 +287,13 @@ __device__ __forceinline__ void ts_store_row16(unsigned char *hi_buf, unsigned c
     *reinterpret_cast<uint4 *>(lo_buf + off + 128) = l1;
 }
 
-// ---- the weight-stream warp (one elected lane): forward ring, then the backward blocks (hi -> slot 0, lo -> slot 1) -------
-__device__ __forceinline__ void ts_producer(const OnfTsArgs &a, const TsShared &s, const unsigned char *src, int n_tiles, bool want_bwd) {
+// ---- the weight-stream warp (one elected lane): per problem and tile the forward ring, then the backward blocks (hi ->
+// slot 0, lo -> slot 1).  The CTA is persistent: the ring runs on into the next problem's weights as soon as the last
+// backward block of this one has been consumed, and the operand copy + the small fp32 parameters of the problem after
+// that are pulled into L2 while this one computes.
+__device__ __forceinline__ void ts_producer(const OnfTsArgs &a, const TsShared &s, bool want_bwd) {
     const TsDims &t = a.t;
+    const nfopp_onf_layout &L = a.d.lay;
     const int c1 = t.K1 / 16, c2 = t.KH / 16;
     uint32_t wc = 0, nbe = 0;
     auto block = [&](const unsigned char *hi, int half, int bytes) {      // one weight block, hi and lo parts
@@ -278,39 +302,54 @@ __device__ __forceinline__ void ts_producer(const OnfTsArgs &a, const TsShared &
         mbar_expect_tx(s.bfull + 1, (uint32_t)bytes);
         bulk_g2s(s.w + t.b_slot, hi + half, bytes, s.bfull + 1);
     };
-    for (int tile = 0; tile < n_tiles; ++tile) {
-        for (int c = 0; c < c1 + c2; ++c, ++wc) {
-            const uint32_t st = wc % TS_WST, k = wc / TS_WST;
-            if (k > 0) ts_wait(s.wempty + st, k - 1);
-            unsigned char *dst = s.w + st * t.w_stage;
-            const bool second = c >= c1;
-            const unsigned char *g = src + (second ? 2 * t.w1_half : 0) + (size_t)(second ? c - c1 : c) * 2 * t.S_colW;
-            const int half = second ? t.w2_half : t.w1_half;
-            mbar_expect_tx(s.wfull + st, (uint32_t)t.w_stage);
-            bulk_g2s(dst, g, 2 * t.S_colW, s.wfull + st);
-            bulk_g2s(dst + 2 * t.S_colW, g + half, 2 * t.S_colW, s.wfull + st);
-        }
-        TS_TRACE(2, 1);
-        if (!want_bwd) continue;
-        // every forward MMA that reads the ring has completed before the ring is reused as two big slots
-        for (uint32_t c = wc > TS_WST ? wc - TS_WST : 0; c < wc; ++c) ts_wait(s.wempty + c % TS_WST, c / TS_WST);
-        TS_TRACE(2, 2);
-        block(src + 2 * t.w1_half, t.w2_half, t.w2_half);                           // W2 -> dgrad2
-        ts_wait(s.bempty, nbe++);
-        const int len0 = t.FB0 / 8 * t.S_colW;
-        block(src, t.w1_half, len0);                                                // W1, feature block 0 -> dgrad1
-        ts_wait(s.bempty, nbe++);
-        if (t.MB == 2) {
-            block(src + len0, t.w1_half, (t.K1 - t.FB0) / 8 * t.S_colW);            // W1, feature block 1
+    for (int p = blockIdx.x; p < a.P; p += gridDim.x) {
+        const int cnt = a.count ? a.count[p] : a.n;
+        if (cnt <= 0) continue;
+        const int n_tiles = (cnt + TS_NT - 1) / TS_NT;
+        const unsigned char *src = a.packed + (size_t)p * t.packed_bytes;
+        for (int tile = 0; tile < n_tiles; ++tile) {
+            for (int c = 0; c < c1 + c2; ++c, ++wc) {
+                const uint32_t st = wc % TS_WST, k = wc / TS_WST;
+                if (k > 0) ts_wait(s.wempty + st, k - 1);
+                unsigned char *dst = s.w + st * t.w_stage;
+                const bool second = c >= c1;
+                const unsigned char *g = src + (second ? 2 * t.w1_half : 0) + (size_t)(second ? c - c1 : c) * 2 * t.S_colW;
+                const int half = second ? t.w2_half : t.w1_half;
+                mbar_expect_tx(s.wfull + st, (uint32_t)t.w_stage);
+                bulk_g2s(dst, g, 2 * t.S_colW, s.wfull + st);
+                bulk_g2s(dst + 2 * t.S_colW, g + half, 2 * t.S_colW, s.wfull + st);
+            }
+            TS_TRACE(2, 1);
+            if (tile == 0 && p + (int)gridDim.x < a.P) {
+                // this CTA's next problem: operand copy and the fp32 parameters its set-up reads -> L2
+                const int pn = p + (int)gridDim.x;
+                bulk_prefetch_l2(a.packed + (size_t)pn * t.packed_bytes, (uint32_t)t.packed_bytes);
+                const float *Wn = a.weights + (size_t)pn * L.n_params;
+                bulk_prefetch_l2(Wn, (uint32_t)L.off_w[0] * 4u);
+                bulk_prefetch_l2(Wn + L.off_b[0], (uint32_t)t.H * 4u);
+                bulk_prefetch_l2(Wn + L.off_b[1], (uint32_t)(L.off_w_out + t.H - L.off_b[1]) * 4u);
+                bulk_prefetch_l2(Wn + L.off_b_out, 16u);
+            }
+            if (!want_bwd) continue;
+            // every forward MMA that reads the ring has completed before the ring is reused as two big slots
+            for (uint32_t c = wc > TS_WST ? wc - TS_WST : 0; c < wc; ++c) ts_wait(s.wempty + c % TS_WST, c / TS_WST);
+            TS_TRACE(2, 2);
+            block(src + 2 * t.w1_half, t.w2_half, t.w2_half);                           // W2 -> dgrad2
             ts_wait(s.bempty, nbe++);
+            const int len0 = t.FB0 / 8 * t.S_colW;
+            block(src, t.w1_half, len0);                                                // W1, feature block 0 -> dgrad1
+            ts_wait(s.bempty, nbe++);
+            if (t.MB == 2) {
+                block(src + len0, t.w1_half, (t.K1 - t.FB0) / 8 * t.S_colW);            // W1, feature block 1
+                ts_wait(s.bempty, nbe++);
+            }
+            TS_TRACE(2, 3);
         }
-        TS_TRACE(2, 3);
     }
 }
 
 // ---- the MMA-issue warp ----------------------------------------------------------------------------------------------
-__device__ __forceinline__ void ts_issuer(const OnfTsArgs &a, const TsShared &s, uint32_t tmem, int cnt, int n_tiles, bool want_bwd,
-                                          bool want_wgrad) {
+__device__ __forceinline__ void ts_issuer(const OnfTsArgs &a, const TsShared &s, uint32_t tmem, bool want_bwd, bool want_wgrad) {
     const TsDims &t = a.t;
     const uint32_t lead = elect_one();
     TS_TRACE(1, 0);
@@ -320,6 +359,10 @@ __device__ __forceinline__ void ts_issuer(const OnfTsArgs &a, const TsShared &s,
     const int c2 = t.KH / 16;
     const int n_slots = (t.K1 + TS_EF - 1) / TS_EF;
     uint32_t wc = 0, ec = 0, nready = 0, nbf = 0;
+    for (int p = blockIdx.x; p < a.P; p += gridDim.x) {
+    const int cnt = a.count ? a.count[p] : a.n;
+    if (cnt <= 0) continue;
+    const int n_tiles = (cnt + TS_NT - 1) / TS_NT;
     for (int tile = 0; tile < n_tiles; ++tile) {
         const int Nt = ts_ru16(min(TS_NT, cnt - tile * TS_NT));
         const bool acc = tile > 0;                                   // weight-gradient accumulators persist across tiles
@@ -404,6 +447,7 @@ __device__ __forceinline__ void ts_issuer(const OnfTsArgs &a, const TsShared &s,
             TS_TRACE(1, 10 + 2 * mb);
         }
     }
+    }
 }
 
 // one octet of encoded features for one point: e[i] = sin(x1 * pb + u0 * pa + pc), x1 = u1 (Fourier) or theta (heading)
@@ -428,527 +472,611 @@ __device__ __forceinline__ void ts_encode8(const TsShared &s, int f0, int F, flo
     split8h(e, hi, lo);
 }
 
-// Thread layout: 18 warps.  Warps 0..15 are workers: warp = 4*cq + q, q = TMEM lane quarter (rows 32q..32q+31), cq = which
+// ---- the optimiser warps: torch.optim.Adam (_single_tensor_adam, planner_factory.py:68) of the problem the workers have
+// just finished, while they compute the next one.  The gradient arrives in a per-CTA global buffer (L2), w / m / v come
+// straight from HBM (prefetched into L2 under the problem's tiles); the fp16 hi/lo operand copy of the new weights is written
+// in the same pass.
+__device__ __forceinline__ void ts_adam4(float4 &w, float4 &m, float4 &v, const float4 g, float w1, float beta2, float w2, float eps,
+                                         float step_size, float inv_bc2) {
+    float gg[4] = {g.x, g.y, g.z, g.w}, ww[4] = {w.x, w.y, w.z, w.w}, mm[4] = {m.x, m.y, m.z, m.w}, v2[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+        mm[c] = fmaf(w1, gg[c] - mm[c], mm[c]);
+        v2[c] = fmaf(w2 * gg[c], gg[c], v2[c] * beta2);
+        // (ftz forms: a denormal second moment is below eps^2 anyway and the denominator is at least eps, so the results
+        // are those of sqrt.approx / __fdividef without their denormal-range fix-up code)
+        float sq, rc;
+        asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(v2[c]));
+        const float denom = fmaf(sq, inv_bc2, eps);
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rc) : "f"(denom));
+        ww[c] = fmaf(-step_size, mm[c] * rc, ww[c]);
+    }
+    w = make_float4(ww[0], ww[1], ww[2], ww[3]);
+    m = make_float4(mm[0], mm[1], mm[2], mm[3]);
+    v = make_float4(v2[0], v2[1], v2[2], v2[3]);
+}
+
+// the four ranges of the blob outside W1 / W2 / the skip row
+__device__ __forceinline__ void ts_misc_ranges(const TsDims &t, const nfopp_onf_layout &L, int (&off)[4], int (&len)[4]) {
+    off[0] = 0; len[0] = L.off_w[0];
+    off[1] = L.off_b[0]; len[1] = L.off_w[1] - L.off_b[0];
+    off[2] = L.off_b[1]; len[2] = L.off_w_out + t.H - L.off_b[1];
+    off[3] = L.off_b_out; len[3] = L.n_params - L.off_b_out;
+}
+
+// one float4 of the blob in flight: gradient (hand-over buffer, L2), w / m / v (HBM or L2), where they go back
+struct TsItem {
+    float4 g, w, m, v;
+    int go;          // float offset in the blob (-1: nothing to update)
+    int poff;        // byte offset of the lane pair's 16 B in the operand copy (-1: none)
+};
+__device__ __forceinline__ float4 ts_ldcg4(const float *p) { return __ldcg(reinterpret_cast<const float4 *>(p)); }
+
+// The optimiser warps share a problem's parameters by interleaving 32-lane groups of "half-octets" (4 consecutive weights of
+// one row): lane pair (2i, 2i + 1) owns one column octet of one row of W1p / W2, so the fp32 loads and stores run through
+// the rows linearly (coalesced) and one shuffle per lane completes the 16 B of hi parts (even lane) / lo parts (odd lane) at
+// [octet][row] of the operand copy; a row's last octet may be half (or all) padding - zeros in the operand copy.  Loads of
+// the next group are issued before the arithmetic of the current one (registers as the staging buffer: no shared memory, no
+// bulk copies that would queue in front of the weight stream).
+__device__ __forceinline__ void ts_optimizer(const OnfTsArgs &a, const TsShared &s, int otid) {
+    const TsDims &t = a.t;
+    const nfopp_onf_layout &L = a.d.lay;
+    const int wo = otid >> 5, lane = otid & 31, hf = lane & 1;
+    const float step_size = a.sp->onf_step_size, inv_bc2 = 1.f / a.sp->onf_bc2_sqrt;
+    int it = 0;
+    int moff[4], mlen[4];
+    ts_misc_ranges(t, L, moff, mlen);
+    const int nhs1 = 2 * ((t.FIN + 7) / 8), nhs2 = 2 * ((t.H + 7) / 8);       // half-octet slots per row (incl. padding)
+    const int n1 = (t.H + 1) * nhs1, n2 = t.H * nhs2;
+    const int n3 = (mlen[0] + mlen[1] + mlen[2] + mlen[3]) / 4;
+    const int ntot = n1 + n2 + n3;
+    const float inv1 = 1.f / (float)nhs1, inv2 = 1.f / (float)nhs2;
+    for (int p = blockIdx.x; p < a.P; p += gridDim.x) {
+        const int cnt = a.count ? a.count[p] : a.n;
+        if (cnt <= 0) continue;
+        const size_t po = (size_t)p * L.n_params;
+        const float *G = a.gscratch + ((size_t)blockIdx.x * 2 + (it & 1)) * L.n_params;
+        float *gw = a.adam_w + po, *gm = a.adam_m + po, *gv = a.adam_v + po;
+        unsigned char *pk = a.packed_out + (size_t)p * t.packed_bytes;
+        if (otid == 0) {
+            // this problem's Adam state is needed when its tiles are done: pull it into L2 under them
+            const uint32_t bytes = (uint32_t)(L.n_params * sizeof(float)) & ~15u;
+            bulk_prefetch_l2(gw, bytes);
+            bulk_prefetch_l2(gm, bytes);
+            bulk_prefetch_l2(gv, bytes);
+        }
+        // flat index i of a half-octet: [0, n1) rows of W1p, [n1, n1 + n2) rows of W2, then the float4s of the other ranges
+        auto fetch = [&](int i) {
+            TsItem x;
+            x.go = -1; x.poff = -1;
+            if (i < n1 + n2) {
+                const bool second = i >= n1;
+                const int j = second ? i - n1 : i;
+                const int r = (int)(((float)j + 0.5f) * (second ? inv2 : inv1));
+                const int hs = j - r * (second ? nhs2 : nhs1);
+                const int rowlen = second ? t.H : t.FIN;
+                const int row_off = second ? L.off_w[1] + r * t.H : (r < t.H ? L.off_w[0] + r * t.FIN : L.off_w_out + t.H);
+                if (4 * hs < rowlen) x.go = row_off + 4 * hs;
+                x.poff = (second ? 2 * t.w1_half : 0) + (hf ? (second ? t.w2_half : t.w1_half) : 0) + (hs >> 1) * t.S_colW +
+                         (r >> 3) * 128 + (r & 7) * 16;
+            } else if (i < ntot) {
+                int j = 4 * (i - n1 - n2);
+                x.go = j < mlen[0] ? moff[0] + j
+                       : (j -= mlen[0]) < mlen[1] ? moff[1] + j
+                       : (j -= mlen[1]) < mlen[2] ? moff[2] + j : moff[3] + j - mlen[2];
+            }
+            const int ld = x.go >= 0 ? x.go : 0;
+            x.g = ts_ldcg4(G + ld);
+            x.w = ts_ldcg4(gw + ld);
+            x.m = ts_ldcg4(gm + ld);
+            x.v = ts_ldcg4(gv + ld);
+            return x;
+        };
+        ts_wait(s.gfull + (it & 1), (uint32_t)(it >> 1));
+        if (otid == 0) TS_TRACE(3, 1);
+        TsItem cur = fetch(wo * 32 + lane);
+        for (int base = wo * 32; base < ntot; base += TS_OPT) {          // warp-uniform trip count (shuffles inside)
+            TsItem nxt = cur;
+            if (base + TS_OPT < ntot) nxt = fetch(base + TS_OPT + lane);
+            const bool upd = cur.go >= 0;
+            ts_adam4(cur.w, cur.m, cur.v, cur.g, a.w1, a.beta2, a.w2, a.eps, step_size, inv_bc2);
+#ifdef NFOPP_TC_TRACE
+            if (upd && !(a.dbg & 2)) {
+#else
+            if (upd) {
+#endif
+                *reinterpret_cast<float4 *>(gw + cur.go) = cur.w;
+                *reinterpret_cast<float4 *>(gm + cur.go) = cur.m;
+                *reinterpret_cast<float4 *>(gv + cur.go) = cur.v;
+            }
+            if (base < n1 + n2) {                                        // (warp-uniform: n1, n2 are multiples of 32? no - see poff)
+                const float4 wq = upd ? cur.w : make_float4(0.f, 0.f, 0.f, 0.f);
+                uint32_t h0, l0, h1, l1;
+                split2h(wq.x, wq.y, h0, l0);
+                split2h(wq.z, wq.w, h1, l1);
+                // even lane keeps its hi parts and receives the partner's; odd lane keeps its lo parts and receives the partner's
+                const uint32_t s0 = hf ? h0 : l0, s1 = hf ? h1 : l1;
+                const uint32_t r0 = __shfl_xor_sync(0xffffffffu, s0, 1), r1 = __shfl_xor_sync(0xffffffffu, s1, 1);
+#ifdef NFOPP_TC_TRACE
+                if (cur.poff >= 0 && !(a.dbg & 1))
+#else
+                if (cur.poff >= 0)
+#endif
+                    *reinterpret_cast<uint4 *>(pk + cur.poff) = hf ? make_uint4(r0, r1, l0, l1) : make_uint4(h0, h1, r0, r1);
+            }
+            cur = nxt;
+        }
+        // every gradient value this warp needs is in its registers: once all warps say so the workers may overwrite the
+        // hand-over buffer
+        __syncwarp();
+        if (lane == 0) mbar_arrive(s.gempty + (it & 1));
+        if (otid == 0) TS_TRACE(3, 2);
+        ++it;
+    }
+}
+
+// Thread layout: 24 warps.  Warps 0..15 are workers: warp = 4*cq + q, q = TMEM lane quarter (rows 32q..32q+31), cq = which
 // 16-column chunks of the tile (cq, cq+4); a thread owns one hidden unit / feature (`row`).  Warp 16 issues every
-// tcgen05.mma, warp 17 streams the weights.
+// tcgen05.mma, warp 17 streams the weights, warps 18..23 are the optimiser.  The CTA is persistent: problems blockIdx.x,
+// blockIdx.x + gridDim.x, ...; all mbarrier phase counters run on across tiles and problems.
 __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs a) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const OnfDims &d = a.d;
     const TsDims &t = a.t;
     const nfopp_onf_layout &L = d.lay;
-    const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (a.sp && !a.warm && !a.sp->do_train) return;    // engine: not a field-training step
-    const int cnt = a.count ? a.count[p] : a.n;
-    if (cnt <= 0) return;
     const bool want_bwd = a.want_bwd != 0;
     const bool want_wgrad = want_bwd && (a.grad_out != nullptr || a.adam_w != nullptr);
     const bool want_gx = want_bwd && a.gx_out != nullptr;
+    const bool fused_adam = want_bwd && a.adam_w != nullptr;
     const int F = t.F, FIN = t.FIN, H = t.H, K1 = t.K1, KH = t.KH;
     const bool is_issuer = warp == TS_WORKERS / 32, is_producer = warp == TS_WORKERS / 32 + 1;
-    const int n_tiles = (cnt + TS_NT - 1) / TS_NT;
+    const bool is_worker = warp < TS_WORKERS / 32;
 
     TsShared s(smem_raw, t);
-    const float *W = a.weights + (size_t)p * L.n_params;
     TS_TRACE(0, 0);
 
-    // ---- one-time setup: barriers, TMEM, per-feature / per-unit fp32 parameters, gradient operand scale ----
+    // ---- one-time setup: barriers, TMEM ----
     if (tid == 0) {
         for (int i = 0; i < TS_WST; ++i) { mbar_init(s.wfull + i, 1); mbar_init(s.wempty + i, 1); }
         for (int i = 0; i < 2; ++i) { mbar_init(s.efull + i, TS_WORKERS / 32); mbar_init(s.eempty + i, 1); mbar_init(s.bfull + i, 1); }
         mbar_init(s.bempty, 1);
         mbar_init(s.ready, TS_WORKERS / 32);
         mbar_init(s.done, 1);
+        for (int i = 0; i < 2; ++i) { mbar_init(s.gfull + i, 1); mbar_init(s.gempty + i, TS_OPT_WARPS); }
         fence_mbar_init();
     }
     if (is_issuer) tmem_alloc(s.tmem_slot, 512);
-    if (is_producer && lane == 0 && a.adam_w != nullptr && want_bwd) {
-        // the Adam epilogue streams this problem's w / m / v once: start pulling them into L2 now, under the compute
-        const size_t po = (size_t)p * L.n_params;
-        const uint32_t bytes = (uint32_t)(L.n_params * sizeof(float)) & ~15u;
-        bulk_prefetch_l2(a.adam_w + po, bytes);
-        bulk_prefetch_l2(a.adam_m + po, bytes);
-        bulk_prefetch_l2(a.adam_v + po, bytes);
-    }
-    for (int f = tid; f < K1; f += TS_THREADS) {
-        float pa = 0.f, pb = 0.f, pc = 0.f;
-        if (f < F) {
-            pa = W[L.off_enc_w + 2 * f];
-            pb = W[L.off_enc_w + 2 * f + 1];
-            pc = W[L.off_enc_b + f] + ((d.use_cos && f >= 100) ? 1.57079632679489662f : 0.f);
-        } else if (f < FIN) {
-            const int k = f - F;
-            const float b = W[L.off_ang_b + k], fr = W[L.off_ang_f + k];
-            s.ang_b[k] = b;
-            pb = fr;
-            pc = fmaf(b, fr, k >= t.A / 2 ? 1.57079632679489662f : 0.f);
-        }
-        s.pa[f] = pa; s.pb[f] = pb; s.pc[f] = pc;
-    }
-    for (int i = tid; i < KH; i += TS_THREADS) {
-        s.b1[i] = i < H ? W[L.off_b[0] + i] : 0.f;
-        s.b2[i] = i < H ? W[L.off_b[1] + i] : 0.f;
-        s.w3h[i] = i < H ? W[L.off_w_out + i] : 0.f;
-    }
-    {
-        // bound of |dL/dz| over the problem -> power-of-two scale of the fp16 gradient operands (one scale for all tiles:
-        // the weight-gradient accumulators are shared): external gz / multipliers are scanned, BCE is bounded by 1 / N
-        float m = 0.f;
-        if (want_bwd && (a.gbar_mode == 0 || a.gbar_mode == 3)) {
-            const float *src = (a.gbar_mode == 0 ? a.gz : a.aux) + (size_t)p * a.n;
-            for (int i = tid; i < cnt; i += TS_THREADS) m = fmaxf(m, fabsf(src[i]));
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-        if (lane == 0) s.red[warp] = m;
-    }
     fence_before_sync();
     __syncthreads();
     fence_after_sync();
-    if (tid == 0) {
-        float m = 0.f;
-        for (int i = 0; i < TS_THREADS / 32; ++i) m = fmaxf(m, s.red[i]);
-        if (a.gbar_mode == 1) m = 1.f / (float)cnt;
-        else if (a.gbar_mode == 2) m = fabsf(a.wc);
-        else if (a.gbar_mode == 3) m += fabsf(a.wc);
-        const float S = want_bwd ? ts_pow2_scale(m) : 1.f;
-        s.scal[0] = W[L.off_b_out];
-        s.scal[1] = S;
-        s.scal[2] = 1.f / S;
-    }
-    __syncthreads();
     const uint32_t tmem = *s.tmem_slot;
-    const float S = s.scal[1], invS = s.scal[2];
     TS_TRACE(0, 1);
 
-    // worker identity (the two service warps compute harmless values)
+    // worker identity (the service warps compute harmless values)
     const int q = warp & 3, cq = (warp >> 2) & 3;
     const int row = q * 32 + lane;
     const uint32_t tm_lane = tmem + ((uint32_t)(q * 32) << 16);
-    // thread-local gradient accumulators (hidden unit `row`; features row of block 0 / block 1; point tid)
-    float acc_db1 = 0.f, acc_db2 = 0.f, acc_dw3 = 0.f, acc_db3 = 0.f;
-    float fa0 = 0.f, fb0 = 0.f, fc0 = 0.f, fa1 = 0.f, fb1 = 0.f, fc1 = 0.f;
 
-    if (is_issuer) {
-        ts_issuer(a, s, tmem, cnt, n_tiles, want_bwd, want_wgrad);
-    } else if (is_producer) {
-        if (lane == 0) ts_producer(a, s, a.packed + (size_t)p * t.packed_bytes, n_tiles, want_bwd);
+    // register split (the CTA starts with 65536 / 768 -> 80 registers per thread): the two service warpgroups (issuer, weight
+    // stream, optimiser) give registers back, the four worker warpgroups take them
+    if (!is_worker) {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(TS_REGS_SERVICE));
+        if (is_issuer) {
+            ts_issuer(a, s, tmem, want_bwd, want_wgrad);
+        } else if (is_producer) {
+            if (lane == 0) ts_producer(a, s, want_bwd);
+        } else if (fused_adam) {
+            ts_optimizer(a, s, tid - (TS_WORKERS + 64));
+        }
     } else {
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(TS_REGS_WORKER));
         const uint32_t tA = tm_lane + TS_TM_A;
         uint32_t ndone = 0, ec = 0;
-        const float my_b1 = row < H ? s.b1[row] : 0.f, my_b2 = row < H ? s.b2[row] : 0.f, my_w3 = row < H ? s.w3h[row] : 0.f;
+        int it = 0;
         float *u0s = s.in0, *u1s = s.in0 + TS_NT, *ths = s.in0 + 2 * TS_NT;
         const int n_slots = (K1 + TS_EF - 1) / TS_EF;
-        for (int tile = 0; tile < n_tiles; ++tile) {
-            const int n0 = tile * TS_NT;
-            const int nv = min(TS_NT, cnt - n0);
-            const int Nt = ts_ru16(nv);
-            const int nch = Nt / 16;
-            // ---- P0: inputs of the tile (onf_model.py:37-38), labels / upstream gradients ----
-            if (tid < TS_NT) {
-                float x0 = 0.f, x1 = 0.f, x2 = 0.f, ax = 0.f;
-                if (tid < nv) {
-                    const size_t gi = (size_t)p * a.n + n0 + tid;
-                    const float *xp = a.x + gi * a.x_stride;
-                    x0 = xp[0]; x1 = xp[1];
-                    if (L.in_dim == 3) x2 = xp[2];
-                    if (want_bwd) {
-                        if (a.gbar_mode == 0) ax = a.gz[gi];
-                        else if (a.gbar_mode != 2) ax = a.aux[gi];
-                    }
+        for (int p = blockIdx.x; p < a.P; p += gridDim.x) {
+            const int cnt = a.count ? a.count[p] : a.n;
+            if (cnt <= 0) continue;
+            const int n_tiles = (cnt + TS_NT - 1) / TS_NT;
+            const float *W = a.weights + (size_t)p * L.n_params;
+            // ---- per-problem setup: per-feature / per-unit fp32 parameters, gradient operand scale ----
+            for (int f = tid; f < K1; f += TS_WORKERS) {
+                float pa = 0.f, pb = 0.f, pc = 0.f;
+                if (f < F) {
+                    pa = W[L.off_enc_w + 2 * f];
+                    pb = W[L.off_enc_w + 2 * f + 1];
+                    pc = W[L.off_enc_b + f] + ((d.use_cos && f >= 100) ? 1.57079632679489662f : 0.f);
+                } else if (f < FIN) {
+                    const int k = f - F;
+                    const float b = W[L.off_ang_b + k], fr = W[L.off_ang_f + k];
+                    s.ang_b[k] = b;
+                    pb = fr;
+                    pc = fmaf(b, fr, k >= t.A / 2 ? 1.57079632679489662f : 0.f);
                 }
-                u0s[tid] = (x0 - d.mean) / d.sigma;
-                u1s[tid] = (x1 - d.mean) / d.sigma;
-                ths[tid] = x2;
-                s.aux[tid] = ax;
+                s.pa[f] = pa; s.pb[f] = pb; s.pc[f] = pc;
             }
-            ts_worker_sync();
-            TS_TRACE(0, 2);
-            // ---- P1: encoding (CUDA cores) feeding fwd1 in slots of 64 features: thread = (point, feature octets g, g+4) ----
+            for (int i = tid; i < KH; i += TS_WORKERS) {
+                s.b1[i] = i < H ? W[L.off_b[0] + i] : 0.f;
+                s.b2[i] = i < H ? W[L.off_b[1] + i] : 0.f;
+                s.w3h[i] = i < H ? W[L.off_w_out + i] : 0.f;
+            }
+            if (tid == 0) s.scal[0] = W[L.off_b_out];
             {
-                const int g = tid / Nt, n = tid - g * Nt;
-                const bool e_on = g < 4;
-                const float u0 = e_on ? u0s[n] : 0.f, u1 = e_on ? u1s[n] : 0.f, th = e_on ? ths[n] : 0.f;
-#pragma unroll 1
-                for (int sl = 0; sl < n_slots; ++sl, ++ec) {
-                    const uint32_t es = ec & 1u;
-                    const int fa = TS_EF * sl + 8 * g, fb = fa + 32;
-                    const bool on_a = e_on && fa < K1, on_b = e_on && fb < K1;
-                    uint4 ah = {}, al = {}, bh = {}, bl = {};
-                    if (on_a) ts_encode8(s, fa, F, u0, u1, th, ah, al);
-                    if (on_b) ts_encode8(s, fb, F, u0, u1, th, bh, bl);
-                    if (ec >= 2) ts_wait(s.eempty + es, (ec >> 1) - 1);        // fwd1 of the slot's previous use is done
-                    unsigned char *eb = s.r + es * 2 * t.e_half + g * TS_SPT + n * 16;
-                    if (on_a) {
-                        *reinterpret_cast<uint4 *>(eb) = ah;
-                        *reinterpret_cast<uint4 *>(eb + t.e_half) = al;
-                    }
-                    if (on_b) {
-                        *reinterpret_cast<uint4 *>(eb + 4 * TS_SPT) = bh;
-                        *reinterpret_cast<uint4 *>(eb + 4 * TS_SPT + t.e_half) = bl;
-                    }
-                    ts_signal(s.efull + es);
+                // bound of |dL/dz| over the problem -> power-of-two scale of the fp16 gradient operands (one scale for all
+                // tiles: the weight-gradient accumulators are shared): external gz / multipliers are scanned, BCE is bounded
+                // by 1 / N
+                float m = 0.f;
+                if (want_bwd && (a.gbar_mode == 0 || a.gbar_mode == 3)) {
+                    const float *src = (a.gbar_mode == 0 ? a.gz : a.aux) + (size_t)p * a.n;
+                    for (int i = tid; i < cnt; i += TS_WORKERS) m = fmaxf(m, fabsf(src[i]));
                 }
-            }
-            TS_TRACE(0, 3);
-            // ---- P2: epilogue 1: bias + ReLU -> H1 operand (hi, lo); row H = skip term of the logit ----
-            ts_wait(s.done, ndone++);
-            TS_TRACE(0, 4);
-            for (int ch = cq; ch < nch; ch += 4) {
-                const int c0 = 16 * ch;
-                float v[16];
-                tmem_ld16(tA + c0, v);
-                if (row < H) {
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) v[i] = fminf(fmaxf(v[i] + my_b1, 0.f), 60000.f);
-                } else {
-                    if (row == H) {
-#pragma unroll
-                        for (int i = 0; i < 16; ++i) s.skip[c0 + i] = v[i];
-                    }
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) v[i] = 0.f;
-                }
-                if (row < KH) ts_store_row16(s.h1h, s.h1l, row, c0, v);
-            }
-            ts_signal(s.ready);                           // -> fwd2
-            TS_TRACE(0, 5);
-            // ---- P3: epilogue 2, first pass: logit partial sums over the hidden units of each lane quarter ----
-            ts_wait(s.done, ndone++);
-            TS_TRACE(0, 6);
-            for (int ch = cq; ch < nch; ch += 4) {
-                const int c0 = 16 * ch;
-                float pz[16];
-                tmem_ld16(tA + c0, pz);
-#pragma unroll
-                for (int i = 0; i < 16; ++i) pz[i] = row < H ? my_w3 * fmaxf(pz[i] + my_b2, 0.f) : 0.f;
-                const float zs = ts_colsum16(pz, lane);
-                if ((lane & 1) == 0) s.zp[q * TS_NT + c0 + (lane >> 1)] = zs;
+                for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+                if (lane == 0) s.red[warp] = m;
             }
             ts_worker_sync();
-            TS_TRACE(0, 7);
-            if (tid < TS_NT) {
-                const int n = tid;
-                float gb = 0.f;
-                if (n < nv) {
-                    const float z = s.zp[n] + s.zp[TS_NT + n] + s.zp[2 * TS_NT + n] + s.zp[3 * TS_NT + n] + s.skip[n] + s.scal[0];
-                    const size_t gi = (size_t)p * a.n + n0 + n;
-                    if (a.z_out) a.z_out[gi] = z;
-                    if (want_bwd) {                                 // dL/dz
-                        const float ax = s.aux[n];
-                        if (a.gbar_mode == 0) gb = ax;
-                        else if (a.gbar_mode == 1) gb = (sigmoid_f(z) - ax) / (float)cnt;
-                        else {
-                            const float zb = z * a.beta;
-                            const float ez = expf(zb);
-                            gb = a.wc * (zb > 20.f ? 1.f : ez / (ez + 1.f));
-                            if (a.gbar_mode == 3) {
-                                const float tz = tanhf(z);
-                                gb += ax * (1.f - tz * tz);
+            float S = 1.f;
+            if (want_bwd) {
+                float m = 0.f;
+#pragma unroll
+                for (int i = 0; i < TS_WORKERS / 32; ++i) m = fmaxf(m, s.red[i]);
+                if (a.gbar_mode == 1) m = 1.f / (float)cnt;
+                else if (a.gbar_mode == 2) m = fabsf(a.wc);
+                else if (a.gbar_mode == 3) m += fabsf(a.wc);
+                S = ts_pow2_scale(m);
+            }
+            const float invS = 1.f / S;
+            const float my_b1 = row < H ? s.b1[row] : 0.f, my_b2 = row < H ? s.b2[row] : 0.f, my_w3 = row < H ? s.w3h[row] : 0.f;
+            // thread-local gradient accumulators (hidden unit `row`; features row of block 0 / block 1; point tid)
+            float acc_db1 = 0.f, acc_db2 = 0.f, acc_dw3 = 0.f, acc_db3 = 0.f;
+            float fa0 = 0.f, fb0 = 0.f, fc0 = 0.f, fa1 = 0.f, fb1 = 0.f, fc1 = 0.f;
+            TS_TRACE(0, 1);
+            for (int tile = 0; tile < n_tiles; ++tile) {
+                const int n0 = tile * TS_NT;
+                const int nv = min(TS_NT, cnt - n0);
+                const int Nt = ts_ru16(nv);
+                const int nch = Nt / 16;
+                // ---- P0: inputs of the tile (onf_model.py:37-38), labels / upstream gradients ----
+                if (tid < TS_NT) {
+                    float x0 = 0.f, x1 = 0.f, x2 = 0.f, ax = 0.f;
+                    if (tid < nv) {
+                        const size_t gi = (size_t)p * a.n + n0 + tid;
+                        const float *xp = a.x + gi * a.x_stride;
+                        x0 = xp[0]; x1 = xp[1];
+                        if (L.in_dim == 3) x2 = xp[2];
+                        if (want_bwd) {
+                            if (a.gbar_mode == 0) ax = a.gz[gi];
+                            else if (a.gbar_mode != 2) ax = a.aux[gi];
+                        }
+                    }
+                    u0s[tid] = (x0 - d.mean) / d.sigma;
+                    u1s[tid] = (x1 - d.mean) / d.sigma;
+                    ths[tid] = x2;
+                    s.aux[tid] = ax;
+                }
+                ts_worker_sync();
+                TS_TRACE(0, 2);
+                // ---- P1: encoding (CUDA cores) feeding fwd1 in slots of 64 features: thread = (point, feature octets g, g+4) ----
+                {
+                    const int g = tid / Nt, n = tid - g * Nt;
+                    const bool e_on = g < 4;
+                    const float u0 = e_on ? u0s[n] : 0.f, u1 = e_on ? u1s[n] : 0.f, th = e_on ? ths[n] : 0.f;
+    #pragma unroll 1
+                    for (int sl = 0; sl < n_slots; ++sl, ++ec) {
+                        const uint32_t es = ec & 1u;
+                        const int fa = TS_EF * sl + 8 * g, fb = fa + 32;
+                        const bool on_a = e_on && fa < K1, on_b = e_on && fb < K1;
+                        uint4 ah = {}, al = {}, bh = {}, bl = {};
+                        if (on_a) ts_encode8(s, fa, F, u0, u1, th, ah, al);
+                        if (on_b) ts_encode8(s, fb, F, u0, u1, th, bh, bl);
+                        if (ec >= 2) ts_wait(s.eempty + es, (ec >> 1) - 1);        // fwd1 of the slot's previous use is done
+                        unsigned char *eb = s.r + es * 2 * t.e_half + g * TS_SPT + n * 16;
+                        if (on_a) {
+                            *reinterpret_cast<uint4 *>(eb) = ah;
+                            *reinterpret_cast<uint4 *>(eb + t.e_half) = al;
+                        }
+                        if (on_b) {
+                            *reinterpret_cast<uint4 *>(eb + 4 * TS_SPT) = bh;
+                            *reinterpret_cast<uint4 *>(eb + 4 * TS_SPT + t.e_half) = bl;
+                        }
+                        ts_signal(s.efull + es);
+                    }
+                }
+                TS_TRACE(0, 3);
+                // ---- P2: epilogue 1: bias + ReLU -> H1 operand (hi, lo); row H = skip term of the logit ----
+                ts_wait(s.done, ndone++);
+                TS_TRACE(0, 4);
+                for (int ch = cq; ch < nch; ch += 4) {
+                    const int c0 = 16 * ch;
+                    float v[16];
+                    tmem_ld16(tA + c0, v);
+                    if (row < H) {
+    #pragma unroll
+                        for (int i = 0; i < 16; ++i) v[i] = fminf(fmaxf(v[i] + my_b1, 0.f), 60000.f);
+                    } else {
+                        if (row == H) {
+    #pragma unroll
+                            for (int i = 0; i < 16; ++i) s.skip[c0 + i] = v[i];
+                        }
+    #pragma unroll
+                        for (int i = 0; i < 16; ++i) v[i] = 0.f;
+                    }
+                    if (row < KH) ts_store_row16(s.h1h, s.h1l, row, c0, v);
+                }
+                ts_signal(s.ready);                           // -> fwd2
+                TS_TRACE(0, 5);
+                // ---- P3: epilogue 2, first pass: logit partial sums over the hidden units of each lane quarter ----
+                ts_wait(s.done, ndone++);
+                TS_TRACE(0, 6);
+                for (int ch = cq; ch < nch; ch += 4) {
+                    const int c0 = 16 * ch;
+                    float pz[16];
+                    tmem_ld16(tA + c0, pz);
+    #pragma unroll
+                    for (int i = 0; i < 16; ++i) pz[i] = row < H ? my_w3 * fmaxf(pz[i] + my_b2, 0.f) : 0.f;
+                    const float zs = ts_colsum16(pz, lane);
+                    if ((lane & 1) == 0) s.zp[q * TS_NT + c0 + (lane >> 1)] = zs;
+                }
+                ts_worker_sync();
+                TS_TRACE(0, 7);
+                if (tid < TS_NT) {
+                    const int n = tid;
+                    float gb = 0.f;
+                    if (n < nv) {
+                        const float z = s.zp[n] + s.zp[TS_NT + n] + s.zp[2 * TS_NT + n] + s.zp[3 * TS_NT + n] + s.skip[n] + s.scal[0];
+                        const size_t gi = (size_t)p * a.n + n0 + n;
+                        if (a.z_out) a.z_out[gi] = z;
+                        if (want_bwd) {                                 // dL/dz
+                            const float ax = s.aux[n];
+                            if (a.gbar_mode == 0) gb = ax;
+                            else if (a.gbar_mode == 1) gb = (sigmoid_f(z) - ax) / (float)cnt;
+                            else {
+                                const float zb = z * a.beta;
+                                const float ez = expf(zb);
+                                gb = a.wc * (zb > 20.f ? 1.f : ez / (ez + 1.f));
+                                if (a.gbar_mode == 3) {
+                                    const float tz = tanhf(z);
+                                    gb += ax * (1.f - tz * tz);
+                                }
                             }
                         }
                     }
+                    s.gbar[n] = gb;
+                    acc_db3 += gb;
                 }
-                s.gbar[n] = gb;
-                acc_db3 += gb;
-            }
-            ts_worker_sync();
-            TS_TRACE(0, 8);
-            if (!want_bwd) continue;
-            // ---- P4: epilogue 2, second pass: gH2 = dL/dz * w3 * 1[h2 > 0] (scaled, fp16 hi + lo) -> old encoding ring ----
-            for (int ch = cq; ch < nch; ch += 4) {
-                const int c0 = 16 * ch;
-                float r2[16], v[16];
-                tmem_ld16(tA + c0, r2);
-#pragma unroll
-                for (int i = 0; i < 16; ++i) {
-                    const float h2 = row < H ? fmaxf(r2[i] + my_b2, 0.f) : 0.f;
-                    const float gb = s.gbar[c0 + i];
-                    acc_dw3 = fmaf(gb, h2, acc_dw3);
-                    const float gg = h2 > 0.f ? gb * my_w3 : 0.f;
-                    acc_db2 += gg;
-                    v[i] = gg * S;
-                }
-                if (row < KH) ts_store_row16(s.r, s.r + t.h1_half, row, c0, v);
-            }
-            ts_signal(s.ready);                           // -> wgrad2 + dgrad2
-            TS_TRACE(0, 9);
-            // ---- P5: epilogue 3: ReLU mask of layer 1 -> gH1 operand (in place over H1 hi, lo); row H := dL/dz ----
-            ts_wait(s.done, ndone++);
-            TS_TRACE(0, 10);
-            for (int ch = cq; ch < nch; ch += 4) {
-                const int c0 = 16 * ch;
-                float v[16];
-                tmem_ld16(tA + c0, v);
-                if (row < H) {
-                    const int off = (row >> 3) * TS_SPT + (c0 >> 3) * 128 + (row & 7) * 16;
-                    const uint4 m0 = *reinterpret_cast<const uint4 *>(s.h1h + off);
-                    const uint4 m1 = *reinterpret_cast<const uint4 *>(s.h1h + off + 128);
-                    const uint32_t mw[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
-                    float sum = 0.f;
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) {
-                        const uint32_t bits = (mw[i >> 1] >> ((i & 1) * 16)) & 0x7FFFu;
-                        v[i] = bits != 0 ? fminf(fmaxf(v[i], -60000.f), 60000.f) : 0.f;
-                        sum += v[i];
-                    }
-                    acc_db1 = fmaf(sum, invS, acc_db1);
-                } else if (row == H) {
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) v[i] = s.gbar[c0 + i] * S;
-                } else {
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) v[i] = 0.f;
-                }
-                if (row < KH) ts_store_row16(s.h1h, s.h1l, row, c0, v);
-            }
-            ts_signal(s.ready);                           // -> dgrad1 (block 0)
-            TS_TRACE(0, 11);
-            // ---- P6: epilogue 4 per feature block: encoding backward (+ input gradient), E^T operand (hi, lo), wgrad1 ----
-#pragma unroll 1
-            for (int mb = 0; mb < t.MB; ++mb) {
-                ts_wait(s.done, ndone++);                 // gE of block mb (and wgrad1 of block mb - 1: E^T is free again)
-                TS_TRACE(0, 12 + 2 * mb);
-                const int fb = mb * t.FB0;
-                const int pf = min(t.FB0, K1 - fb);       // features of this block that are MMA rows
-                const int f = fb + row;
-                const bool f_on = row < pf;
-                const bool fourier = f < F;
-                const float ppa = f_on ? s.pa[f] : 0.f, ppb = f_on ? s.pb[f] : 0.f, ppc = f_on ? s.pc[f] : 0.f;
-                const float ew0 = (f_on && fourier) ? ppa : 0.f, ew1 = (f_on && fourier) ? ppb : 0.f,
-                            eaf = (f_on && !fourier && f < FIN) ? ppb : 0.f;
-                const float *x1src = fourier ? u1s : ths;
-                float ta = 0.f, tb = 0.f, tc = 0.f;      // sum gp*u0, sum gp*x1, sum gp  (all still scaled by S)
+                ts_worker_sync();
+                TS_TRACE(0, 8);
+                if (!want_bwd) continue;
+                // ---- P4: epilogue 2, second pass: gH2 = dL/dz * w3 * 1[h2 > 0] (scaled, fp16 hi + lo) -> old encoding ring ----
                 for (int ch = cq; ch < nch; ch += 4) {
                     const int c0 = 16 * ch;
-                    float v[16], ev[16], xu[16], x1[16];
-                    tmem_ld16(tA + c0, v);
-#pragma unroll
-                    for (int i4 = 0; i4 < 4; ++i4) {
-                        *reinterpret_cast<float4 *>(xu + 4 * i4) = *reinterpret_cast<const float4 *>(u0s + c0 + 4 * i4);
-                        *reinterpret_cast<float4 *>(x1 + 4 * i4) = *reinterpret_cast<const float4 *>(x1src + c0 + 4 * i4);
-                    }
-#pragma unroll
+                    float r2[16], v[16];
+                    tmem_ld16(tA + c0, r2);
+    #pragma unroll
                     for (int i = 0; i < 16; ++i) {
-                        const float arg = fmaf(x1[i], ppb, fmaf(xu[i], ppa, ppc));
-                        const float gp = (f_on ? v[i] : 0.f) * __cosf(arg);      // rows beyond the block hold garbage
-                        ev[i] = __sinf(arg);                                       // (= 0 there: pa = pb = pc = 0)
-                        v[i] = gp;
-                        ta = fmaf(gp, xu[i], ta);
-                        tb = fmaf(gp, x1[i], tb);
-                        tc += gp;
+                        const float h2 = row < H ? fmaxf(r2[i] + my_b2, 0.f) : 0.f;
+                        const float gb = s.gbar[c0 + i];
+                        acc_dw3 = fmaf(gb, h2, acc_dw3);
+                        const float gg = h2 > 0.f ? gb * my_w3 : 0.f;
+                        acc_db2 += gg;
+                        v[i] = gg * S;
                     }
-                    if (want_gx) {
-                        // gx[n] = (sum_f gp[f,n] * We[f,c]) / sigma ; g_theta[n] = sum_k gp[k,n] * f_k   (reduce over lanes)
-                        float cv[16];
-                        float *dst = s.gxp + ((size_t)q * TS_NT + c0 + (lane >> 1)) * 3;
-#pragma unroll
-                        for (int c = 0; c < 3; ++c) {
-                            const float wgt = c == 0 ? ew0 : c == 1 ? ew1 : eaf;
-#pragma unroll
-                            for (int i = 0; i < 16; ++i) cv[i] = v[i] * wgt;
-                            const float sum = ts_colsum16(cv, lane);
-                            if ((lane & 1) == 0) dst[c] = mb == 0 ? sum : dst[c] + sum;
+                    if (row < KH) ts_store_row16(s.r, s.r + t.h1_half, row, c0, v);
+                }
+                ts_signal(s.ready);                           // -> wgrad2 + dgrad2
+                TS_TRACE(0, 9);
+                // ---- P5: epilogue 3: ReLU mask of layer 1 -> gH1 operand (in place over H1 hi, lo); row H := dL/dz ----
+                ts_wait(s.done, ndone++);
+                TS_TRACE(0, 10);
+                for (int ch = cq; ch < nch; ch += 4) {
+                    const int c0 = 16 * ch;
+                    float v[16];
+                    tmem_ld16(tA + c0, v);
+                    if (row < H) {
+                        const int off = (row >> 3) * TS_SPT + (c0 >> 3) * 128 + (row & 7) * 16;
+                        const uint4 m0 = *reinterpret_cast<const uint4 *>(s.h1h + off);
+                        const uint4 m1 = *reinterpret_cast<const uint4 *>(s.h1h + off + 128);
+                        const uint32_t mw[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+                        float sum = 0.f;
+    #pragma unroll
+                        for (int i = 0; i < 16; ++i) {
+                            const uint32_t bits = (mw[i >> 1] >> ((i & 1) * 16)) & 0x7FFFu;
+                            v[i] = bits != 0 ? fminf(fmaxf(v[i], -60000.f), 60000.f) : 0.f;
+                            sum += v[i];
+                        }
+                        acc_db1 = fmaf(sum, invS, acc_db1);
+                    } else if (row == H) {
+    #pragma unroll
+                        for (int i = 0; i < 16; ++i) v[i] = s.gbar[c0 + i] * S;
+                    } else {
+    #pragma unroll
+                        for (int i = 0; i < 16; ++i) v[i] = 0.f;
+                    }
+                    if (row < KH) ts_store_row16(s.h1h, s.h1l, row, c0, v);
+                }
+                ts_signal(s.ready);                           // -> dgrad1 (block 0)
+                TS_TRACE(0, 11);
+                // ---- P6: epilogue 4 per feature block: encoding backward (+ input gradient), E^T operand (hi, lo), wgrad1 ----
+    #pragma unroll 1
+                for (int mb = 0; mb < t.MB; ++mb) {
+                    ts_wait(s.done, ndone++);                 // gE of block mb (and wgrad1 of block mb - 1: E^T is free again)
+                    TS_TRACE(0, 12 + 2 * mb);
+                    const int fb = mb * t.FB0;
+                    const int pf = min(t.FB0, K1 - fb);       // features of this block that are MMA rows
+                    const int f = fb + row;
+                    const bool f_on = row < pf;
+                    const bool fourier = f < F;
+                    const float ppa = f_on ? s.pa[f] : 0.f, ppb = f_on ? s.pb[f] : 0.f, ppc = f_on ? s.pc[f] : 0.f;
+                    const float ew0 = (f_on && fourier) ? ppa : 0.f, ew1 = (f_on && fourier) ? ppb : 0.f,
+                                eaf = (f_on && !fourier && f < FIN) ? ppb : 0.f;
+                    const float *x1src = fourier ? u1s : ths;
+                    float ta = 0.f, tb = 0.f, tc = 0.f;      // sum gp*u0, sum gp*x1, sum gp  (all still scaled by S)
+                    for (int ch = cq; ch < nch; ch += 4) {
+                        const int c0 = 16 * ch;
+                        float v[16], ev[16], xu[16], x1[16];
+                        tmem_ld16(tA + c0, v);
+    #pragma unroll
+                        for (int i4 = 0; i4 < 4; ++i4) {
+                            *reinterpret_cast<float4 *>(xu + 4 * i4) = *reinterpret_cast<const float4 *>(u0s + c0 + 4 * i4);
+                            *reinterpret_cast<float4 *>(x1 + 4 * i4) = *reinterpret_cast<const float4 *>(x1src + c0 + 4 * i4);
+                        }
+    #pragma unroll
+                        for (int i = 0; i < 16; ++i) {
+                            const float arg = fmaf(x1[i], ppb, fmaf(xu[i], ppa, ppc));
+                            const float gp = (f_on ? v[i] : 0.f) * __cosf(arg);      // rows beyond the block hold garbage
+                            ev[i] = __sinf(arg);                                       // (= 0 there: pa = pb = pc = 0)
+                            v[i] = gp;
+                            ta = fmaf(gp, xu[i], ta);
+                            tb = fmaf(gp, x1[i], tb);
+                            tc += gp;
+                        }
+                        if (want_gx) {
+                            // gx[n] = (sum_f gp[f,n] * We[f,c]) / sigma ; g_theta[n] = sum_k gp[k,n] * f_k   (reduce over lanes)
+                            float cv[16];
+                            float *dst = s.gxp + ((size_t)q * TS_NT + c0 + (lane >> 1)) * 3;
+    #pragma unroll
+                            for (int c = 0; c < 3; ++c) {
+                                const float wgt = c == 0 ? ew0 : c == 1 ? ew1 : eaf;
+    #pragma unroll
+                                for (int i = 0; i < 16; ++i) cv[i] = v[i] * wgt;
+                                const float sum = ts_colsum16(cv, lane);
+                                if ((lane & 1) == 0) dst[c] = mb == 0 ? sum : dst[c] + sum;
+                            }
+                        }
+                        if (want_wgrad && row < t.FB0) {     // E^T operand [point / 8][feature][8 points], hi and lo
+    #pragma unroll
+                            for (int o = 0; o < 2; ++o) {
+                                const int off = ((c0 >> 3) + o) * t.S_ET + (row >> 3) * 128 + (row & 7) * 16;
+                                uint4 eh, el;
+                                split8h(ev + 8 * o, eh, el);
+                                *reinterpret_cast<uint4 *>(s.r + off) = eh;
+                                *reinterpret_cast<uint4 *>(s.r + t.et_half + off) = el;
+                            }
                         }
                     }
-                    if (want_wgrad && row < t.FB0) {     // E^T operand [point / 8][feature][8 points], hi and lo
-#pragma unroll
-                        for (int o = 0; o < 2; ++o) {
-                            const int off = ((c0 >> 3) + o) * t.S_ET + (row >> 3) * 128 + (row & 7) * 16;
-                            uint4 eh, el;
-                            split8h(ev + 8 * o, eh, el);
-                            *reinterpret_cast<uint4 *>(s.r + off) = eh;
-                            *reinterpret_cast<uint4 *>(s.r + t.et_half + off) = el;
+                    ta *= invS; tb *= invS; tc *= invS;
+                    if (f_on && !fourier) {                   // heading features: d ang_b = f_k * sum gp,
+                        const float b = f < FIN ? s.ang_b[f - F] : 0.f;   // d ang_f = sum gp * (theta + b_k)  (trained)
+                        tb = fmaf(b, tc, tb);
+                        ta = eaf * tc;
+                    }
+                    if (mb == 0) { fa0 += ta; fb0 += tb; fc0 += tc; }
+                    else { fa1 += ta; fb1 += tb; fc1 += tc; }
+                    ts_signal(s.ready);                       // -> wgrad1(mb), dgrad1(mb + 1)
+                    TS_TRACE(0, 13 + 2 * mb);
+                }
+                if (want_gx) {
+                    ts_worker_sync();
+                    if (tid < nv) {
+                        const int n = tid;
+                        float g0 = 0.f, g1 = 0.f, g2 = 0.f;
+    #pragma unroll
+                        for (int qq = 0; qq < 4; ++qq) {
+                            const float *src = s.gxp + ((size_t)qq * TS_NT + n) * 3;
+                            g0 += src[0]; g1 += src[1]; g2 += src[2];
                         }
+                        float *out = a.gx_out + ((size_t)p * a.n + n0 + n) * a.x_stride;
+                        out[0] = g0 * invS / d.sigma;
+                        out[1] = g1 * invS / d.sigma;
+                        if (L.in_dim == 3) out[2] = g2 * invS;
+                        for (int c = L.in_dim; c < a.x_stride; ++c) out[c] = 0.f;   // pose columns the ONF does not read
                     }
                 }
-                ta *= invS; tb *= invS; tc *= invS;
-                if (f_on && !fourier) {                   // heading features: d ang_b = f_k * sum gp,
-                    const float b = f < FIN ? s.ang_b[f - F] : 0.f;   // d ang_f = sum gp * (theta + b_k)  (trained)
-                    tb = fmaf(b, tc, tb);
-                    ta = eaf * tc;
-                }
-                if (mb == 0) { fa0 += ta; fb0 += tb; fc0 += tc; }
-                else { fa1 += ta; fb1 += tb; fc1 += tc; }
-                ts_signal(s.ready);                       // -> wgrad1(mb), dgrad1(mb + 1)
-                TS_TRACE(0, 13 + 2 * mb);
+                if (want_wgrad) ts_wait(s.done, ndone++);     // the last wgrad1: E^T (= the encoding ring) and gH1 are free again
+                TS_TRACE(0, 16);
+                ts_worker_sync();                             // zp, gx, skip, gbar, inputs are rewritten by the next tile
             }
-            if (want_gx) {
+            TS_TRACE(0, 20);
+            if (!want_wgrad) continue;
+            // ---- weight gradients: TMEM accumulators -> global hand-over buffer (blob order) -> optimiser warps / caller ----
+            // every MMA of the problem has completed (the wait after the last wgrad1): the encoding ring is dead until the next
+            // problem's encoding and holds the per-unit partial sums [10][4][128]
+            {
+                float *red = reinterpret_cast<float *>(s.r);
+                float *r0 = red + cq * 128 + row;
+                r0[0 * 512] = acc_db1; r0[1 * 512] = acc_db2; r0[2 * 512] = acc_dw3;
+                r0[3 * 512] = fa0; r0[4 * 512] = fb0; r0[5 * 512] = fc0;
+                r0[6 * 512] = fa1; r0[7 * 512] = fb1; r0[8 * 512] = fc1;
+                if (tid < 128) {                                           // (acc_db3 lives in threads 0 .. TS_NT-1, zero elsewhere)
+                    const float s3 = warp_sum(tid < TS_NT ? acc_db3 : 0.f);
+                    if (lane == 0) red[9 * 512 + warp] = s3;
+                }
+                float *G = fused_adam ? a.gscratch + ((size_t)blockIdx.x * 2 + (it & 1)) * L.n_params : a.grad_out + (size_t)p * L.n_params;
+                if (fused_adam && it >= 2) ts_wait(s.gempty + (it & 1), (uint32_t)((it >> 1) - 1));   // the optimiser has read buffer it - 2
+                {
+                    // everything outside W1 / W2 / the skip row: zero first (alignment padding stays zero), totals below
+                    int moff[4], mlen[4];
+                    ts_misc_ranges(t, L, moff, mlen);
+#pragma unroll
+                    for (int r = 0; r < 4; ++r)
+                        for (int i = tid; i < mlen[r]; i += TS_WORKERS) G[moff[r] + i] = 0.f;
+                }
                 ts_worker_sync();
-                if (tid < nv) {
-                    const int n = tid;
-                    float g0 = 0.f, g1 = 0.f, g2 = 0.f;
+                // dW1: rows j < H -> mlp.0.weight[j,:], row H -> mlp2.0.weight[0, H:];  dW2: rows i < H -> mlp.2.weight[i,:]
+                for (int ch = cq; ch < K1 / 16; ch += 4) {
+                    float g[16];
+                    const int f0 = 16 * ch;
+                    tmem_ld16(tm_lane + TS_TM_DW1 + f0, g);
+                    if (row <= H) {
+                        float *dst = G + (row < H ? L.off_w[0] + row * FIN : L.off_w_out + H) + f0;
 #pragma unroll
-                    for (int qq = 0; qq < 4; ++qq) {
-                        const float *src = s.gxp + ((size_t)qq * TS_NT + n) * 3;
-                        g0 += src[0]; g1 += src[1]; g2 += src[2];
+                        for (int c4 = 0; c4 < 4; ++c4)
+                            if (f0 + 4 * c4 < FIN)
+                                *reinterpret_cast<float4 *>(dst + 4 * c4) =
+                                    make_float4(g[4 * c4] * invS, g[4 * c4 + 1] * invS, g[4 * c4 + 2] * invS, g[4 * c4 + 3] * invS);
                     }
-                    float *out = a.gx_out + ((size_t)p * a.n + n0 + n) * a.x_stride;
-                    out[0] = g0 * invS / d.sigma;
-                    out[1] = g1 * invS / d.sigma;
-                    if (L.in_dim == 3) out[2] = g2 * invS;
-                    for (int c = L.in_dim; c < a.x_stride; ++c) out[c] = 0.f;   // pose columns the ONF does not read
                 }
-            }
-            if (want_wgrad) ts_wait(s.done, ndone++);     // the last wgrad1: E^T (= the encoding ring) and gH1 are free again
-            TS_TRACE(0, 16);
-            ts_worker_sync();                             // zp, gx, skip, gbar, inputs are rewritten by the next tile
-        }
-    }
-    fence_before_sync();
-    __syncthreads();
-    fence_after_sync();
-    TS_TRACE(0, 20);
-
-    // ---- weight gradients: TMEM accumulators -> shared memory in blob order -> coalesced Adam / gradient store ----
-    if (want_wgrad) {
-        // every MMA has completed: the operand buffers are dead, shared memory [0, n_params) floats now holds the
-        // gradient of the whole parameter blob (same element order as the fp32 weights)
-        float *G = reinterpret_cast<float *>(smem_raw);
-        float *red = G + ((L.n_params + 31) & ~31);                    // [10][4][128] partial per-unit sums
-        const int np4 = L.n_params / 4;
-        for (int i = tid; i < np4; i += TS_THREADS) reinterpret_cast<float4 *>(G)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        const bool is_worker = warp < TS_WORKERS / 32;
-        if (is_worker) {
-            float *r0 = red + cq * 128 + row;
-            r0[0 * 512] = acc_db1; r0[1 * 512] = acc_db2; r0[2 * 512] = acc_dw3;
-            r0[3 * 512] = fa0; r0[4 * 512] = fb0; r0[5 * 512] = fc0;
-            r0[6 * 512] = fa1; r0[7 * 512] = fb1; r0[8 * 512] = fc1;
-            if (tid < 128) {                                           // (acc_db3 lives in threads 0 .. TS_NT-1, zero elsewhere)
-                const float s3 = warp_sum(tid < TS_NT ? acc_db3 : 0.f);
-                if (lane == 0) red[9 * 512 + warp] = s3;
-            }
-        }
-        __syncthreads();
-        // dW1: rows j < H -> mlp.0.weight[j,:], row H -> mlp2.0.weight[0, H:];  dW2: rows i < H -> mlp.2.weight[i,:]
-        for (int ch = cq; ch < (is_worker ? K1 / 16 : 0); ch += 4) {
-            float g[16];
-            const int f0 = 16 * ch;
-            tmem_ld16(tm_lane + TS_TM_DW1 + f0, g);
-            if (row <= H) {
-                float *dst = G + (row < H ? L.off_w[0] + row * FIN : L.off_w_out + H) + f0;
+                for (int ch = cq; ch < KH / 16; ch += 4) {
+                    float g[16];
+                    tmem_ld16(tm_lane + TS_TM_DW2 + 16 * ch, g);
+                    if (row < H) {
+                        float *dst = G + L.off_w[1] + row * H + 16 * ch;
 #pragma unroll
-                for (int c4 = 0; c4 < 4; ++c4)
-                    if (f0 + 4 * c4 < FIN)
-                        *reinterpret_cast<float4 *>(dst + 4 * c4) =
-                            make_float4(g[4 * c4] * invS, g[4 * c4 + 1] * invS, g[4 * c4 + 2] * invS, g[4 * c4 + 3] * invS);
-            }
-        }
-        for (int ch = cq; ch < (is_worker ? KH / 16 : 0); ch += 4) {
-            float g[16];
-            tmem_ld16(tm_lane + TS_TM_DW2 + 16 * ch, g);
-            if (row < H) {
-                float *dst = G + L.off_w[1] + row * H + 16 * ch;
-#pragma unroll
-                for (int c4 = 0; c4 < 4; ++c4)
-                    if (16 * ch + 4 * c4 < H)
-                        *reinterpret_cast<float4 *>(dst + 4 * c4) =
-                            make_float4(g[4 * c4] * invS, g[4 * c4 + 1] * invS, g[4 * c4 + 2] * invS, g[4 * c4 + 3] * invS);
-            }
-        }
-        if (tid < 128) {
-            auto tot = [&](int qn) {
-                const float *r = red + qn * 512 + tid;
-                return (r[0] + r[128]) + (r[256] + r[384]);
-            };
-            if (tid < H) {
-                G[L.off_b[0] + tid] = tot(0);
-                G[L.off_b[1] + tid] = tot(1);
-                G[L.off_w_out + tid] = tot(2);
-            }
-            for (int mb = 0; mb < t.MB; ++mb) {
-                const int f = mb * t.FB0 + tid;
-                const bool on = tid < min(t.FB0, K1 - mb * t.FB0);
-                const float ga = tot(3 + 3 * mb), gb = tot(4 + 3 * mb), gc = tot(5 + 3 * mb);
-                if (on && f < F) {
-                    G[L.off_enc_w + 2 * f] = ga;
-                    G[L.off_enc_w + 2 * f + 1] = gb;
-                    G[L.off_enc_b + f] = d.bias ? gc : 0.f;
-                } else if (on && f < FIN) {
-                    G[L.off_ang_b + f - F] = ga;
-                    G[L.off_ang_f + f - F] = gb;
-                }
-            }
-            if (tid == 0) {
-                float g3 = 0.f;
-                for (int i = 0; i < 4; ++i) g3 += red[9 * 512 + i];
-                G[L.off_b_out] = g3;
-            }
-        }
-        __syncthreads();
-        TS_TRACE(0, 21);
-        const size_t po = (size_t)p * L.n_params;
-        if (a.adam_w == nullptr) {
-            float4 *dst = reinterpret_cast<float4 *>(a.grad_out + po);
-            for (int i = tid; i < np4; i += TS_THREADS) dst[i] = reinterpret_cast<const float4 *>(G)[i];
-        } else {
-            // torch.optim.Adam (_single_tensor_adam) over the whole blob, fully coalesced; the new weights replace the
-            // gradient in shared memory and are re-split into the fp16 operand copy below
-            const float step_size = a.sp->onf_step_size, inv_bc2 = 1.f / a.sp->onf_bc2_sqrt;
-            float4 *w4 = reinterpret_cast<float4 *>(a.adam_w + po), *m4 = reinterpret_cast<float4 *>(a.adam_m + po),
-                   *v4 = reinterpret_cast<float4 *>(a.adam_v + po);
-            constexpr int U = 4;
-            for (int i0 = tid; i0 < np4; i0 += U * TS_THREADS) {
-                float4 wv[U], mv[U], vv[U];
-#pragma unroll
-                for (int u = 0; u < U; ++u) {
-                    const int i = i0 + u * TS_THREADS;
-                    if (i < np4) { wv[u] = w4[i]; mv[u] = m4[i]; vv[u] = v4[i]; }
-                }
-#pragma unroll
-                for (int u = 0; u < U; ++u) {
-                    const int i = i0 + u * TS_THREADS;
-                    if (i >= np4) continue;
-                    const float4 g4 = reinterpret_cast<const float4 *>(G)[i];
-                    float gg[4] = {g4.x, g4.y, g4.z, g4.w}, ww[4] = {wv[u].x, wv[u].y, wv[u].z, wv[u].w},
-                          mm[4] = {mv[u].x, mv[u].y, mv[u].z, mv[u].w}, v2[4] = {vv[u].x, vv[u].y, vv[u].z, vv[u].w};
-#pragma unroll
-                    for (int c = 0; c < 4; ++c) {
-                        mm[c] = fmaf(a.w1, gg[c] - mm[c], mm[c]);
-                        v2[c] = fmaf(a.w2 * gg[c], gg[c], v2[c] * a.beta2);
-                        float sq;
-                        asm("sqrt.approx.f32 %0, %1;" : "=f"(sq) : "f"(v2[c]));
-                        const float denom = fmaf(sq, inv_bc2, a.eps);
-                        ww[c] = fmaf(-step_size, __fdividef(mm[c], denom), ww[c]);
+                        for (int c4 = 0; c4 < 4; ++c4)
+                            if (16 * ch + 4 * c4 < H)
+                                *reinterpret_cast<float4 *>(dst + 4 * c4) =
+                                    make_float4(g[4 * c4] * invS, g[4 * c4 + 1] * invS, g[4 * c4 + 2] * invS, g[4 * c4 + 3] * invS);
                     }
-                    w4[i] = make_float4(ww[0], ww[1], ww[2], ww[3]);
-                    m4[i] = make_float4(mm[0], mm[1], mm[2], mm[3]);
-                    v4[i] = make_float4(v2[0], v2[1], v2[2], v2[3]);
-                    reinterpret_cast<float4 *>(G)[i] = make_float4(ww[0], ww[1], ww[2], ww[3]);
                 }
+                if (tid < 128) {
+                    auto tot = [&](int qn) {
+                        const float *r = red + qn * 512 + tid;
+                        return (r[0] + r[128]) + (r[256] + r[384]);
+                    };
+                    if (tid < H) {
+                        G[L.off_b[0] + tid] = tot(0);
+                        G[L.off_b[1] + tid] = tot(1);
+                        G[L.off_w_out + tid] = tot(2);
+                    }
+                    for (int mb = 0; mb < t.MB; ++mb) {
+                        const int f = mb * t.FB0 + tid;
+                        const bool on = tid < min(t.FB0, K1 - mb * t.FB0);
+                        const float ga = tot(3 + 3 * mb), gb = tot(4 + 3 * mb), gc = tot(5 + 3 * mb);
+                        if (on && f < F) {
+                            G[L.off_enc_w + 2 * f] = ga;
+                            G[L.off_enc_w + 2 * f + 1] = gb;
+                            G[L.off_enc_b + f] = d.bias ? gc : 0.f;
+                        } else if (on && f < FIN) {
+                            G[L.off_ang_b + f - F] = ga;
+                            G[L.off_ang_f + f - F] = gb;
+                        }
+                    }
+                    if (tid == 0) {
+                        float g3 = 0.f;
+                        for (int i = 0; i < 4; ++i) g3 += red[9 * 512 + i];
+                        G[L.off_b_out] = g3;
+                    }
+                }
+                fence_proxy_async_all();                  // the optimiser reads the buffer with bulk copies (async proxy)
+                fence_before_sync();
+                ts_worker_sync();                         // (also: `red` and the per-problem parameters are free again)
+                if (fused_adam && tid == 0) mbar_arrive(s.gfull + (it & 1));
+                ++it;
             }
-            __syncthreads();
-            TS_TRACE(0, 22);
-            // refresh the packed operand copy: item = (matrix, column octet, row) -> 16 B of hi + 16 B of lo
-            unsigned char *pk = a.packed_out + (size_t)p * t.packed_bytes;
-            const int rows = KH, n1 = (K1 / 8) * rows, n2 = (KH / 8) * rows;
-            for (int item = tid; item < n1 + n2; item += TS_THREADS) {
-                const bool second = item >= n1;
-                const int it = second ? item - n1 : item;
-                const int oct = it / rows, r = it - oct * rows;
-                const int kdim = second ? H : FIN;
-                float v[8];
-                const float *src = nullptr;
-                if (!second) {
-                    if (r < H) src = G + L.off_w[0] + r * FIN;
-                    else if (r == H) src = G + L.off_w_out + H;
-                } else if (r < H) {
-                    src = G + L.off_w[1] + r * H;
-                }
-#pragma unroll
-                for (int h4 = 0; h4 < 2; ++h4) {
-                    const int c = oct * 8 + 4 * h4;
-                    float4 x4 = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (src && c < kdim) x4 = *reinterpret_cast<const float4 *>(src + c);
-                    v[4 * h4] = x4.x; v[4 * h4 + 1] = x4.y; v[4 * h4 + 2] = x4.z; v[4 * h4 + 3] = x4.w;
-                }
-                uint4 hi, lo;
-                split8h(v, hi, lo);
-                unsigned char *base = pk + (second ? 2 * t.w1_half : 0);
-                const int half = second ? t.w2_half : t.w1_half;
-                const int off = oct * t.S_colW + (r >> 3) * 128 + (r & 7) * 16;
-                *reinterpret_cast<uint4 *>(base + off) = hi;
-                *reinterpret_cast<uint4 *>(base + half + off) = lo;
-            }
+            TS_TRACE(0, 21);
         }
     }
     fence_before_sync();
@@ -963,12 +1091,29 @@ bool onf_tcs_supported(const OnfDims &d) {
     return ts_make_dims(d, &t);
 }
 
+static int g_tcs_sms = 0;
+
 int onf_tcs_prepare(const OnfDims &d) {
     TsDims t;
     NFOPP_REQUIRE(ts_make_dims(d, &t), "onf(tensor, streamed): needs 2 hidden layers, hidden <= 111, f_in <= 256 (hidden=%d layers=%d)",
                   d.H, d.L);
     NFOPP_CHECK_CUDA(cudaFuncSetAttribute(onf_tcs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, t.smem_bytes));
+    int dev = 0;
+    NFOPP_CHECK_CUDA(cudaGetDevice(&dev));
+    NFOPP_CHECK_CUDA(cudaDeviceGetAttribute(&g_tcs_sms, cudaDevAttrMultiProcessorCount, dev));
     return NFOPP_OK;
+}
+
+// persistent grid: one CTA per SM (NFOPP_TCS_GRID overrides the cap, 0 = one CTA per problem)
+int onf_tcs_grid(int P, int slots) {
+    int cap = g_tcs_sms > 0 ? g_tcs_sms : 148;
+    if (const char *e = getenv("NFOPP_TCS_GRID")) {
+        const int v = atoi(e);
+        cap = v > 0 ? v : P;
+    }
+    int grid = P < cap ? P : cap;
+    if (slots > 0 && grid > slots) grid = slots;
+    return grid < 1 ? 1 : grid;
 }
 
 int onf_tcs_pack(const OnfDims &d, const float *weights, unsigned char *packed, int P, cudaStream_t stream) {
@@ -989,15 +1134,18 @@ int onf_tcs_launch(const OnfArgs &o, const OnfTcExtra &x, int P, cudaStream_t st
     a.d = o.d;
     NFOPP_REQUIRE(ts_make_dims(o.d, &a.t), "onf(tensor, streamed): unsupported network shape");
     a.weights = o.weights; a.packed = x.packed; a.x = o.x; a.count = o.count; a.sp = o.sp;
-    a.n = o.n; a.x_stride = o.x_stride ? o.x_stride : o.d.lay.in_dim;
+    a.P = P; a.n = o.n; a.x_stride = o.x_stride ? o.x_stride : o.d.lay.in_dim;
     a.want_bwd = o.want_bwd; a.gbar_mode = o.gbar_mode; a.gz = o.gz; a.aux = o.aux; a.wc = o.wc; a.beta = o.beta;
     a.z_out = o.z_out; a.gx_out = o.gx_out; a.grad_out = x.grad_out;
-    a.adam_w = x.adam_w; a.adam_m = x.adam_m; a.adam_v = x.adam_v; a.packed_out = x.packed_out;
+    a.adam_w = x.adam_w; a.adam_m = x.adam_m; a.adam_v = x.adam_v; a.packed_out = x.packed_out; a.gscratch = x.gscratch;
     a.w1 = x.w1; a.beta2 = x.beta2; a.w2 = x.w2; a.eps = x.eps; a.warm = x.warm;
+    if (const char *e = getenv("NFOPP_TCS_DBG")) a.dbg = atoi(e);
     NFOPP_REQUIRE(a.packed, "onf(tensor): packed operand copy missing");
     NFOPP_REQUIRE(!a.adam_w || (a.sp && a.packed_out), "onf(tensor): fused Adam needs step parameters and the packed copy");
+    NFOPP_REQUIRE(!a.adam_w || (a.gscratch && x.gscratch_slots > 0), "onf(tensor, streamed): fused Adam needs the gradient hand-over buffers");
     if (a.n == 0 || P == 0) return NFOPP_OK;
-    onf_tcs_kernel<<<P, TS_THREADS, a.t.smem_bytes, stream>>>(a);
+    const int grid = onf_tcs_grid(P, a.adam_w ? x.gscratch_slots : 0);
+    onf_tcs_kernel<<<grid, TS_THREADS, a.t.smem_bytes, stream>>>(a);
     NFOPP_CHECK_CUDA(cudaGetLastError());
     return NFOPP_OK;
 }

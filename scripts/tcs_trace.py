@@ -2,7 +2,7 @@
 """Phase trace of the streamed fused ONF kernel (onf_tcs.cu built with -DNFOPP_TC_TRACE: `make -C .../csrc trace`).
 Runs the corridor workload for a few steps and prints, for the first and last CTA of the three ONF launches of a step
 (candidates forward, train, path), the clock64 stamps of worker thread 0, the MMA-issue warp and the weight-stream warp
-relative to the CTA's start.  Diagnostic only - the product library is libnfopp.so.   python scripts/tcs_trace.py"""
+relative to the CTA's start (the CTAs are persistent: the stamps are those of the CTA's LAST problem).  Diagnostic only - the product library is libnfopp.so.   python scripts/tcs_trace.py"""
 import argparse
 import ctypes as C
 import os
@@ -19,14 +19,15 @@ from nfopp_b200 import _lib as L  # noqa: E402
 L.LIB_PATH = os.path.join(os.path.dirname(L.LIB_PATH), "libnfopp_trace.so")
 import bench as B  # noqa: E402
 
-WORKER = {0: "start", 1: "setup done", 2: "inputs staged", 3: "encode done", 4: "fwd1 done", 5: "ep1 signalled", 6: "fwd2 done",
-          7: "logit partials", 8: "dL/dz", 9: "gH2 signalled", 10: "wgrad2+dgrad2 done", 11: "ep3 signalled",
+WORKER = {0: "start", 1: "setup done (last problem)", 2: "inputs staged", 3: "encode done", 4: "fwd1 done", 5: "ep1 signalled",
+          6: "fwd2 done", 7: "logit partials", 8: "dL/dz", 9: "gH2 signalled", 10: "wgrad2+dgrad2 done", 11: "ep3 signalled",
           12: "dgrad1(0) done", 13: "ep4(0) signalled", 14: "dgrad1(1) done", 15: "ep4(1) signalled", 16: "wgrad1 done",
-          20: "CTA sync", 21: "TMEM drained", 22: "Adam done", 23: "repack done"}
+          20: "tiles done", 21: "gradient handed over", 23: "CTA done"}
 ISSUER = {0: "start", 1: "fwd1 issued", 2: "ep1 ready", 3: "fwd2 issued", 4: "gH2 ready", 5: "W2 slot full", 6: "bwdA issued",
           7: "gH1 ready", 8: "W1 slot full", 9: "ep4(0) ready", 10: "wgrad1(0)+dgrad1(1) issued", 11: "ep4(1) ready",
           12: "wgrad1(1) issued"}
 PRODUCER = {1: "fwd ring streamed", 2: "fwd ring drained", 3: "bwd blocks issued"}
+OPTIMISER = {1: "gradient ready (last problem)", 2: "Adam + operand copy done"}
 
 
 def main():
@@ -43,7 +44,7 @@ def main():
     lib = L.lib()
     lib.nfopp_debug_tcs_trace.restype = C.c_int
     lib.nfopp_debug_tcs_trace.argtypes = [C.c_void_p]
-    buf = np.zeros((3, 2, 3, 64), dtype=np.int64)
+    buf = np.zeros((3, 2, 4, 64), dtype=np.int64)
     rc = lib.nfopp_debug_tcs_trace(buf.ctypes.data_as(C.c_void_p))
     assert rc == 0, rc
     for kind, kname in enumerate(["candidates fwd", "train", "path fwd+dgrad"]):
@@ -51,7 +52,7 @@ def main():
             t = buf[kind, ci]
             t0 = t[0, 0]
             print(f"== {kname} / {cname}")
-            for role, names in enumerate([WORKER, ISSUER, PRODUCER]):
+            for role, names in enumerate([WORKER, ISSUER, PRODUCER, OPTIMISER]):
                 prev, parts = t0, []
                 for k in sorted(names):
                     v = t[role, k]
@@ -59,7 +60,9 @@ def main():
                         continue
                     parts.append(f"{names[k]} @{v - t0} (+{v - prev})")
                     prev = v
-                print(f"  {['worker', 'issuer', 'producer'][role]:8s}: " + " | ".join(parts))
+                print(f"  {['worker', 'issuer', 'producer', 'optimiser'][role]:9s}: " + " | ".join(parts))
+            if t[3, 3] or t[3, 4]:
+                print(f"  optimiser, last problem (cycles): waiting for chunks {t[3, 3]}, arithmetic + stores {t[3, 4]}")
 
 
 if __name__ == "__main__":
