@@ -613,6 +613,7 @@ static int engine_onf(nfopp_engine *e, const EngineDev &d, OnfArgs &a, cudaStrea
     OnfTcExtra x{};
     x.packed = d.onf_wp;
     x.variant = e->tc_variant;
+    x.sm_share = d.P < e->dev.P ? e->lanes : 1;        // a lane's launch shares the GPU with the other lanes'
     return onf_tc_launch(a, x, d.P, s);
 }
 
@@ -630,6 +631,7 @@ static int enqueue_train(nfopp_engine *e, const EngineDev &d, bool warm, cudaStr
         OnfTcExtra x{};
         x.packed = d.onf_wp; x.adam_w = d.onf_w; x.adam_m = d.onf_m; x.adam_v = d.onf_v; x.packed_out = d.onf_wp;
         x.gscratch = d.onf_gpart; x.gscratch_slots = d.gslots;
+        x.sm_share = d.P < e->dev.P ? e->lanes : 1;
         x.w1 = w1; x.beta2 = beta2; x.w2 = w2; x.eps = eps; x.warm = warm;
         x.variant = e->tc_variant;
         if ((rc = onf_tc_launch(a, x, d.P, s))) return rc;

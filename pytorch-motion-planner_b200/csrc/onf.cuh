@@ -45,6 +45,7 @@ struct OnfTcExtra {
     int variant;                   // 0: first generation (onf_tc.cu, bf16 operands, resident weights); 1: streamed (onf_tcs.cu, fp16)
     float *gscratch;               // streamed kernel with fused Adam: [gscratch_slots, 2, n_params] gradient hand-over buffers
     int gscratch_slots;            //   (one pair per persistent CTA: the grid is capped at this many CTAs)
+    int sm_share;                  // streamed kernel: launches that run side by side (engine lanes) - each gets #SMs / sm_share CTAs
 };
 
 bool onf_tc_supported(const OnfDims &d);            // 2 hidden layers, hidden <= 111, f_in <= 224
@@ -57,7 +58,7 @@ int onf_tc_launch(const OnfArgs &a, const OnfTcExtra &x, int P, cudaStream_t str
 // must be packed by the variant that reads it.
 bool onf_tcs_supported(const OnfDims &d);
 int onf_tcs_prepare(const OnfDims &d);
-int onf_tcs_grid(int P, int slots);                 // CTAs of the persistent kernel for P problems (slots > 0: cap)
+int onf_tcs_grid(int P, int slots, int sm_share);   // CTAs of the persistent kernel for P problems (slots > 0: cap)
 constexpr int ONF_TCS_SCRATCH_SLOTS = 320;           // hand-over buffer pairs an engine owns (split evenly between its lanes)
 int onf_tcs_pack(const OnfDims &d, const float *weights, unsigned char *packed, int P, cudaStream_t stream);
 int onf_tcs_launch(const OnfArgs &a, const OnfTcExtra &x, int P, cudaStream_t stream);

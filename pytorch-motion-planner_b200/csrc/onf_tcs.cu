@@ -69,6 +69,8 @@ constexpr int TS_WORKERS = 512;                 // 16 epilogue / encoding warps
 constexpr int TS_OPT_WARPS = 6;                 // optimiser warps (Adam + operand-copy refresh of the PREVIOUS problem)
 constexpr int TS_OPT = 32 * TS_OPT_WARPS;
 constexpr int TS_THREADS = TS_WORKERS + 64 + TS_OPT;   // + MMA-issue warp + weight-stream warp + optimiser warps
+constexpr int TS_GBUF = 1;                      // gradient hand-over buffers per CTA in use (of the 2 allocated): the optimiser has read
+                                                // a problem's gradient long before the next one is ready, and 148 x 133 KB less live data in L2 pays
 constexpr int TS_REGS_WORKER = 88, TS_REGS_SERVICE = 64;   // setmaxnreg split of the 768 x 80 registers the CTA starts with: 512 x 88 + 256 x 64
 constexpr int TS_NT = 112;                      // points per tile
 constexpr uint32_t TS_SPT = TS_NT * 16;         // S_row of the point-indexed operand buffers [hidden / 8][point / 8][8][8]
@@ -76,12 +78,13 @@ constexpr int TS_WST = 8;                       // weight ring stages (K = 16 ch
 constexpr int TS_EF = 64;                       // features per encoding slot (2 slots)
 constexpr uint32_t TS_TM_A = 0, TS_TM_DW2 = TS_NT, TS_TM_DW1 = 2 * TS_NT;   // TMEM columns: work | dW2 [KH] | dW1 [K1]
 constexpr int TS_GX_FLOATS = 4 * TS_NT * 3;     // per-lane-quarter partials of the input gradient
+constexpr int TS_SROW = 68;                     // row stride (floats) of the 64-column gradient staging buffer
 
 struct TsDims {
     int F, A, FIN, H, K1, KH, MB, FB0;           // MB feature blocks of FB0 (last one shorter) for dgrad1 / wgrad1
     int S_colW, w1_half, w2_half;                // packed operand copy: [W1 hi | W1 lo | W2 hi | W2 lo], each [k / 8][row][8]
     int h1_half, e_half, w_stage, b_slot, S_ET, et_half;
-    int off_h1h, off_h1l, off_r, off_w, off_misc, misc_floats, off_bar, smem_bytes, packed_bytes;
+    int off_h1h, off_h1l, off_r, off_w, off_misc, misc_floats, off_stage, off_bar, smem_bytes, packed_bytes;
 };
 
 __host__ __device__ inline int ts_ru16(int x) { return (x + 15) / 16 * 16; }
@@ -109,7 +112,8 @@ __host__ __device__ inline bool ts_make_dims(const OnfDims &d, TsDims *out) {
     t.off_w = t.off_r + ts_max(ts_max(4 * t.e_half, 2 * t.h1_half), ts_max(2 * t.et_half, 10 * 512 * 4));
     t.off_misc = t.off_w + ts_max(TS_WST * t.w_stage, 2 * t.b_slot);
     t.misc_floats = 3 * t.K1 + 32 + 3 * t.KH + 8 + 10 * TS_NT + TS_GX_FLOATS + 32;
-    t.off_bar = (t.off_misc + t.misc_floats * 4 + 127) / 128 * 128;
+    t.off_stage = (t.off_misc + t.misc_floats * 4 + 127) / 128 * 128;   // [128 rows][TS_SROW] floats: transposes the weight gradient
+    t.off_bar = t.off_stage + 128 * TS_SROW * 4;
     t.smem_bytes = t.off_bar + 64 * 8 + 16;
     t.packed_bytes = 2 * t.w1_half + 2 * t.w2_half;
     *out = t;
@@ -274,6 +278,11 @@ __device__ __forceinline__ void ts_wait(uint64_t *bar, uint32_t use) {     // wa
     mbar_wait(bar, use & 1u);
     fence_after_sync();
 }
+__device__ __forceinline__ void ts_wait_relaxed(uint64_t *bar, uint32_t use, uint32_t sleep_ns) {   // long, non-critical waits
+    if (sleep_ns == 0) mbar_wait(bar, use & 1u);
+    else mbar_wait_relaxed(bar, use & 1u, sleep_ns);
+    fence_after_sync();
+}
 
 // store 16 consecutive columns (col0 .. col0+15) of row `row` into [row / 8][col / 8][row % 8][col % 8] operand buffers
 __device__ __forceinline__ void ts_store_row16(unsigned char *hi_buf, unsigned char *lo_buf, int row, int col0, const float *v) {
@@ -310,7 +319,7 @@ __device__ __forceinline__ void ts_producer(const OnfTsArgs &a, const TsShared &
         for (int tile = 0; tile < n_tiles; ++tile) {
             for (int c = 0; c < c1 + c2; ++c, ++wc) {
                 const uint32_t st = wc % TS_WST, k = wc / TS_WST;
-                if (k > 0) ts_wait(s.wempty + st, k - 1);
+                if (k > 0) ts_wait_relaxed(s.wempty + st, k - 1, 64);
                 unsigned char *dst = s.w + st * t.w_stage;
                 const bool second = c >= c1;
                 const unsigned char *g = src + (second ? 2 * t.w1_half : 0) + (size_t)(second ? c - c1 : c) * 2 * t.S_colW;
@@ -320,28 +329,32 @@ __device__ __forceinline__ void ts_producer(const OnfTsArgs &a, const TsShared &
                 bulk_g2s(dst + 2 * t.S_colW, g + half, 2 * t.S_colW, s.wfull + st);
             }
             TS_TRACE(2, 1);
-            if (tile == 0 && p + (int)gridDim.x < a.P) {
-                // this CTA's next problem: operand copy and the fp32 parameters its set-up reads -> L2
-                const int pn = p + (int)gridDim.x;
-                bulk_prefetch_l2(a.packed + (size_t)pn * t.packed_bytes, (uint32_t)t.packed_bytes);
-                const float *Wn = a.weights + (size_t)pn * L.n_params;
-                bulk_prefetch_l2(Wn, (uint32_t)L.off_w[0] * 4u);
-                bulk_prefetch_l2(Wn + L.off_b[0], (uint32_t)t.H * 4u);
-                bulk_prefetch_l2(Wn + L.off_b[1], (uint32_t)(L.off_w_out + t.H - L.off_b[1]) * 4u);
-                bulk_prefetch_l2(Wn + L.off_b_out, 16u);
+            if (tile == n_tiles - 1) {
+                // L2 prefetches, issued late so that the lines are still resident when they are used (ncu: issued at the
+                // start of the problem, a wave's 148 x 0.8 MB outlived the L2 and was read from HBM twice):
+                if (p + (int)gridDim.x < a.P) {
+                    // this CTA's next problem: operand copy and the fp32 parameters its set-up reads
+                    const int pn = p + (int)gridDim.x;
+                    bulk_prefetch_l2(a.packed + (size_t)pn * t.packed_bytes, (uint32_t)t.packed_bytes);
+                    const float *Wn = a.weights + (size_t)pn * L.n_params;
+                    bulk_prefetch_l2(Wn, (uint32_t)L.off_w[0] * 4u);
+                    bulk_prefetch_l2(Wn + L.off_b[0], (uint32_t)t.H * 4u);
+                    bulk_prefetch_l2(Wn + L.off_b[1], (uint32_t)(L.off_w_out + t.H - L.off_b[1]) * 4u);
+                    bulk_prefetch_l2(Wn + L.off_b_out, 16u);
+                }
             }
             if (!want_bwd) continue;
             // every forward MMA that reads the ring has completed before the ring is reused as two big slots
-            for (uint32_t c = wc > TS_WST ? wc - TS_WST : 0; c < wc; ++c) ts_wait(s.wempty + c % TS_WST, c / TS_WST);
+            for (uint32_t c = wc > TS_WST ? wc - TS_WST : 0; c < wc; ++c) ts_wait_relaxed(s.wempty + c % TS_WST, c / TS_WST, 64);
             TS_TRACE(2, 2);
             block(src + 2 * t.w1_half, t.w2_half, t.w2_half);                           // W2 -> dgrad2
-            ts_wait(s.bempty, nbe++);
+            ts_wait_relaxed(s.bempty, nbe++, 64);
             const int len0 = t.FB0 / 8 * t.S_colW;
             block(src, t.w1_half, len0);                                                // W1, feature block 0 -> dgrad1
-            ts_wait(s.bempty, nbe++);
+            ts_wait_relaxed(s.bempty, nbe++, 64);
             if (t.MB == 2) {
                 block(src + len0, t.w1_half, (t.K1 - t.FB0) / 8 * t.S_colW);            // W1, feature block 1
-                ts_wait(s.bempty, nbe++);
+                ts_wait_relaxed(s.bempty, nbe++, 64);
             }
             TS_TRACE(2, 3);
         }
@@ -512,18 +525,18 @@ struct TsItem {
 };
 __device__ __forceinline__ float4 ts_ldcg4(const float *p) { return __ldcg(reinterpret_cast<const float4 *>(p)); }
 
-// The optimiser warps share a problem's parameters by interleaving 32-lane groups of "half-octets" (4 consecutive weights of
-// one row): lane pair (2i, 2i + 1) owns one column octet of one row of W1p / W2, so the fp32 loads and stores run through
-// the rows linearly (coalesced) and one shuffle per lane completes the 16 B of hi parts (even lane) / lo parts (odd lane) at
-// [octet][row] of the operand copy; a row's last octet may be half (or all) padding - zeros in the operand copy.  Loads of
-// the next group are issued before the arithmetic of the current one (registers as the staging buffer: no shared memory, no
-// bulk copies that would queue in front of the weight stream).
-__device__ __forceinline__ void ts_optimizer(const OnfTsArgs &a, const TsShared &s, int otid) {
+// The warps that apply a problem's update share its parameters by interleaving 32-lane groups of "half-octets" (4 consecutive
+// weights of one row): lane pair (2i, 2i + 1) owns one column octet of one row of W1p / W2, so the fp32 loads and stores run
+// through the rows linearly (coalesced) and one shuffle per lane completes the 16 B of hi parts (even lane) / lo parts (odd
+// lane) at [octet][row] of the operand copy; a row's last octet may be half (or all) padding - zeros in the operand copy.
+// Loads of the next group are issued before the arithmetic of the current one (registers as the staging buffer: no shared
+// memory, no bulk copies that would queue in front of the weight stream).  Warp `rank` of `nranks` takes groups rank,
+// rank + nranks, ...
+__device__ __forceinline__ void ts_adam_problem(const OnfTsArgs &a, const float *G, int p, int rank, int nranks, int lane) {
     const TsDims &t = a.t;
     const nfopp_onf_layout &L = a.d.lay;
-    const int wo = otid >> 5, lane = otid & 31, hf = lane & 1;
+    const int hf = lane & 1;
     const float step_size = a.sp->onf_step_size, inv_bc2 = 1.f / a.sp->onf_bc2_sqrt;
-    int it = 0;
     int moff[4], mlen[4];
     ts_misc_ranges(t, L, moff, mlen);
     const int nhs1 = 2 * ((t.FIN + 7) / 8), nhs2 = 2 * ((t.H + 7) / 8);       // half-octet slots per row (incl. padding)
@@ -531,85 +544,102 @@ __device__ __forceinline__ void ts_optimizer(const OnfTsArgs &a, const TsShared 
     const int n3 = (mlen[0] + mlen[1] + mlen[2] + mlen[3]) / 4;
     const int ntot = n1 + n2 + n3;
     const float inv1 = 1.f / (float)nhs1, inv2 = 1.f / (float)nhs2;
+    const size_t po = (size_t)p * L.n_params;
+    float *gw = a.adam_w + po, *gm = a.adam_m + po, *gv = a.adam_v + po;
+    unsigned char *pk = a.packed_out + (size_t)p * t.packed_bytes;
+    // flat index i of a half-octet: [0, n1) rows of W1p, [n1, n1 + n2) rows of W2, then the float4s of the other ranges
+    auto fetch = [&](int i) {
+        TsItem x;
+        x.go = -1; x.poff = -1;
+        if (i < n1 + n2) {
+            const bool second = i >= n1;
+            const int j = second ? i - n1 : i;
+            const int r = (int)(((float)j + 0.5f) * (second ? inv2 : inv1));
+            const int hs = j - r * (second ? nhs2 : nhs1);
+            const int rowlen = second ? t.H : t.FIN;
+            const int row_off = second ? L.off_w[1] + r * t.H : (r < t.H ? L.off_w[0] + r * t.FIN : L.off_w_out + t.H);
+            if (4 * hs < rowlen) x.go = row_off + 4 * hs;
+            x.poff = (second ? 2 * t.w1_half : 0) + (hf ? (second ? t.w2_half : t.w1_half) : 0) + (hs >> 1) * t.S_colW +
+                     (r >> 3) * 128 + (r & 7) * 16;
+        } else if (i < ntot) {
+            int j = 4 * (i - n1 - n2);
+            x.go = j < mlen[0] ? moff[0] + j
+                   : (j -= mlen[0]) < mlen[1] ? moff[1] + j
+                   : (j -= mlen[1]) < mlen[2] ? moff[2] + j : moff[3] + j - mlen[2];
+        }
+        const int ld = x.go >= 0 ? x.go : 0;
+        x.g = ts_ldcg4(G + ld);
+        x.w = ts_ldcg4(gw + ld);
+        x.m = ts_ldcg4(gm + ld);
+        x.v = ts_ldcg4(gv + ld);
+        return x;
+    };
+    const int stride = 32 * nranks;
+    if (rank * 32 >= ntot) return;
+    TsItem cur = fetch(rank * 32 + lane);
+    for (int base = rank * 32; base < ntot; base += stride) {              // warp-uniform trip count (shuffles inside)
+        TsItem nxt = cur;
+        if (base + stride < ntot) nxt = fetch(base + stride + lane);
+        const bool upd = cur.go >= 0;
+        ts_adam4(cur.w, cur.m, cur.v, cur.g, a.w1, a.beta2, a.w2, a.eps, step_size, inv_bc2);
+#ifdef NFOPP_TC_TRACE
+        if (upd && !(a.dbg & 2)) {
+#else
+        if (upd) {
+#endif
+            *reinterpret_cast<float4 *>(gw + cur.go) = cur.w;
+            *reinterpret_cast<float4 *>(gm + cur.go) = cur.m;
+            *reinterpret_cast<float4 *>(gv + cur.go) = cur.v;
+        }
+        if (base < n1 + n2) {                                              // (warp-uniform; lanes past the matrices have poff < 0)
+            const float4 wq = upd ? cur.w : make_float4(0.f, 0.f, 0.f, 0.f);
+            uint32_t h0, l0, h1, l1;
+            split2h(wq.x, wq.y, h0, l0);
+            split2h(wq.z, wq.w, h1, l1);
+            // even lane keeps its hi parts and receives the partner's; odd lane keeps its lo parts and receives the partner's
+            const uint32_t s0 = hf ? h0 : l0, s1 = hf ? h1 : l1;
+            const uint32_t r0 = __shfl_xor_sync(0xffffffffu, s0, 1), r1 = __shfl_xor_sync(0xffffffffu, s1, 1);
+#ifdef NFOPP_TC_TRACE
+            if (cur.poff >= 0 && !(a.dbg & 1))
+#else
+            if (cur.poff >= 0)
+#endif
+                *reinterpret_cast<uint4 *>(pk + cur.poff) = hf ? make_uint4(r0, r1, l0, l1) : make_uint4(h0, h1, r0, r1);
+        }
+        cur = nxt;
+    }
+}
+
+// the optimiser warps: problem after problem as the workers hand the gradients over.  (Letting the sixteen worker warps join
+// in for the CTA's last problem, which has nothing to hide under, does not shorten it: all CTAs reach that point together and
+// the 148 x 1.1 MB burst is HBM-bound - measured.)
+__device__ __forceinline__ void ts_optimizer(const OnfTsArgs &a, const TsShared &s, int otid) {
+    const nfopp_onf_layout &L = a.d.lay;
+    const int wo = otid >> 5, lane = otid & 31;
+    int it = 0;
     for (int p = blockIdx.x; p < a.P; p += gridDim.x) {
         const int cnt = a.count ? a.count[p] : a.n;
         if (cnt <= 0) continue;
-        const size_t po = (size_t)p * L.n_params;
-        const float *G = a.gscratch + ((size_t)blockIdx.x * 2 + (it & 1)) * L.n_params;
-        float *gw = a.adam_w + po, *gm = a.adam_m + po, *gv = a.adam_v + po;
-        unsigned char *pk = a.packed_out + (size_t)p * t.packed_bytes;
+        const int gb = it % TS_GBUF;
+        const float *G = a.gscratch + ((size_t)blockIdx.x * 2 + gb) * L.n_params;
         if (otid == 0) {
-            // this problem's Adam state is needed when its tiles are done: pull it into L2 under them
+            // this problem's Adam state: pull it into L2 now - the previous problem's update has just finished, the tiles
+            // of this one are under way (measured: issued at the problem's first tile the lines do not survive in L2 until
+            // they are used, issued at its last tile they arrive late)
+            const size_t po = (size_t)p * L.n_params;
             const uint32_t bytes = (uint32_t)(L.n_params * sizeof(float)) & ~15u;
-            bulk_prefetch_l2(gw, bytes);
-            bulk_prefetch_l2(gm, bytes);
-            bulk_prefetch_l2(gv, bytes);
+            bulk_prefetch_l2(a.adam_w + po, bytes);
+            bulk_prefetch_l2(a.adam_m + po, bytes);
+            bulk_prefetch_l2(a.adam_v + po, bytes);
         }
-        // flat index i of a half-octet: [0, n1) rows of W1p, [n1, n1 + n2) rows of W2, then the float4s of the other ranges
-        auto fetch = [&](int i) {
-            TsItem x;
-            x.go = -1; x.poff = -1;
-            if (i < n1 + n2) {
-                const bool second = i >= n1;
-                const int j = second ? i - n1 : i;
-                const int r = (int)(((float)j + 0.5f) * (second ? inv2 : inv1));
-                const int hs = j - r * (second ? nhs2 : nhs1);
-                const int rowlen = second ? t.H : t.FIN;
-                const int row_off = second ? L.off_w[1] + r * t.H : (r < t.H ? L.off_w[0] + r * t.FIN : L.off_w_out + t.H);
-                if (4 * hs < rowlen) x.go = row_off + 4 * hs;
-                x.poff = (second ? 2 * t.w1_half : 0) + (hf ? (second ? t.w2_half : t.w1_half) : 0) + (hs >> 1) * t.S_colW +
-                         (r >> 3) * 128 + (r & 7) * 16;
-            } else if (i < ntot) {
-                int j = 4 * (i - n1 - n2);
-                x.go = j < mlen[0] ? moff[0] + j
-                       : (j -= mlen[0]) < mlen[1] ? moff[1] + j
-                       : (j -= mlen[1]) < mlen[2] ? moff[2] + j : moff[3] + j - mlen[2];
-            }
-            const int ld = x.go >= 0 ? x.go : 0;
-            x.g = ts_ldcg4(G + ld);
-            x.w = ts_ldcg4(gw + ld);
-            x.m = ts_ldcg4(gm + ld);
-            x.v = ts_ldcg4(gv + ld);
-            return x;
-        };
-        ts_wait(s.gfull + (it & 1), (uint32_t)(it >> 1));
+        ts_wait_relaxed(s.gfull + gb, (uint32_t)(it / TS_GBUF), 256);
         if (otid == 0) TS_TRACE(3, 1);
-        TsItem cur = fetch(wo * 32 + lane);
-        for (int base = wo * 32; base < ntot; base += TS_OPT) {          // warp-uniform trip count (shuffles inside)
-            TsItem nxt = cur;
-            if (base + TS_OPT < ntot) nxt = fetch(base + TS_OPT + lane);
-            const bool upd = cur.go >= 0;
-            ts_adam4(cur.w, cur.m, cur.v, cur.g, a.w1, a.beta2, a.w2, a.eps, step_size, inv_bc2);
-#ifdef NFOPP_TC_TRACE
-            if (upd && !(a.dbg & 2)) {
-#else
-            if (upd) {
-#endif
-                *reinterpret_cast<float4 *>(gw + cur.go) = cur.w;
-                *reinterpret_cast<float4 *>(gm + cur.go) = cur.m;
-                *reinterpret_cast<float4 *>(gv + cur.go) = cur.v;
-            }
-            if (base < n1 + n2) {                                        // (warp-uniform: n1, n2 are multiples of 32? no - see poff)
-                const float4 wq = upd ? cur.w : make_float4(0.f, 0.f, 0.f, 0.f);
-                uint32_t h0, l0, h1, l1;
-                split2h(wq.x, wq.y, h0, l0);
-                split2h(wq.z, wq.w, h1, l1);
-                // even lane keeps its hi parts and receives the partner's; odd lane keeps its lo parts and receives the partner's
-                const uint32_t s0 = hf ? h0 : l0, s1 = hf ? h1 : l1;
-                const uint32_t r0 = __shfl_xor_sync(0xffffffffu, s0, 1), r1 = __shfl_xor_sync(0xffffffffu, s1, 1);
-#ifdef NFOPP_TC_TRACE
-                if (cur.poff >= 0 && !(a.dbg & 1))
-#else
-                if (cur.poff >= 0)
-#endif
-                    *reinterpret_cast<uint4 *>(pk + cur.poff) = hf ? make_uint4(r0, r1, l0, l1) : make_uint4(h0, h1, r0, r1);
-            }
-            cur = nxt;
-        }
+        // (a CTA with a single problem has nothing to overlap the update with: the worker warps join in, see the kernel)
+        ts_adam_problem(a, G, p, wo, a.P <= (int)gridDim.x ? TS_OPT_WARPS + TS_WORKERS / 32 : TS_OPT_WARPS, lane);
         // every gradient value this warp needs is in its registers: once all warps say so the workers may overwrite the
         // hand-over buffer
         __syncwarp();
-        if (lane == 0) mbar_arrive(s.gempty + (it & 1));
+        if (lane == 0) mbar_arrive(s.gempty + gb);
         if (otid == 0) TS_TRACE(3, 2);
         ++it;
     }
@@ -1004,8 +1034,10 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
                     const float s3 = warp_sum(tid < TS_NT ? acc_db3 : 0.f);
                     if (lane == 0) red[9 * 512 + warp] = s3;
                 }
-                float *G = fused_adam ? a.gscratch + ((size_t)blockIdx.x * 2 + (it & 1)) * L.n_params : a.grad_out + (size_t)p * L.n_params;
-                if (fused_adam && it >= 2) ts_wait(s.gempty + (it & 1), (uint32_t)((it >> 1) - 1));   // the optimiser has read buffer it - 2
+                const int gb = it % TS_GBUF;
+                float *G = fused_adam ? a.gscratch + ((size_t)blockIdx.x * 2 + gb) * L.n_params : a.grad_out + (size_t)p * L.n_params;
+                if (fused_adam && it >= TS_GBUF) ts_wait(s.gempty + gb, (uint32_t)(it / TS_GBUF - 1));   // the optimiser has read this buffer
+                TS_TRACE(0, 22);
                 {
                     // everything outside W1 / W2 / the skip row: zero first (alignment padding stays zero), totals below
                     int moff[4], mlen[4];
@@ -1015,32 +1047,40 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
                         for (int i = tid; i < mlen[r]; i += TS_WORKERS) G[moff[r] + i] = 0.f;
                 }
                 ts_worker_sync();
-                // dW1: rows j < H -> mlp.0.weight[j,:], row H -> mlp2.0.weight[0, H:];  dW2: rows i < H -> mlp.2.weight[i,:]
-                for (int ch = cq; ch < K1 / 16; ch += 4) {
-                    float g[16];
-                    const int f0 = 16 * ch;
-                    tmem_ld16(tm_lane + TS_TM_DW1 + f0, g);
-                    if (row <= H) {
-                        float *dst = G + (row < H ? L.off_w[0] + row * FIN : L.off_w_out + H) + f0;
+                // dW1: rows j < H -> mlp.0.weight[j,:], row H -> mlp2.0.weight[0, H:];  dW2: rows i < H -> mlp.2.weight[i,:].
+                // A thread holds 16 consecutive columns of ONE row (TMEM lane): 64 columns at a time go through a shared-memory
+                // buffer so that the global stores run along the rows (a warp writes 2 x 256 contiguous bytes per instruction
+                // instead of 32 x 16)
+                float *S = reinterpret_cast<float *>(smem_raw + t.off_stage);
+                auto drain = [&](uint32_t tm_col, int ncols, int width, bool first) {
+                    for (int c0 = 0; c0 < ncols; c0 += 64) {
+                        const int cl = c0 + 16 * cq;
+                        if (cl < ncols) {
+                            float g[16];
+                            tmem_ld16(tm_lane + tm_col + cl, g);
 #pragma unroll
-                        for (int c4 = 0; c4 < 4; ++c4)
-                            if (f0 + 4 * c4 < FIN)
-                                *reinterpret_cast<float4 *>(dst + 4 * c4) =
+                            for (int c4 = 0; c4 < 4; ++c4)
+                                *reinterpret_cast<float4 *>(S + row * TS_SROW + 16 * cq + 4 * c4) =
                                     make_float4(g[4 * c4] * invS, g[4 * c4 + 1] * invS, g[4 * c4 + 2] * invS, g[4 * c4 + 3] * invS);
-                    }
-                }
-                for (int ch = cq; ch < KH / 16; ch += 4) {
-                    float g[16];
-                    tmem_ld16(tm_lane + TS_TM_DW2 + 16 * ch, g);
-                    if (row < H) {
-                        float *dst = G + L.off_w[1] + row * H + 16 * ch;
+                        }
+                        ts_worker_sync();
 #pragma unroll
-                        for (int c4 = 0; c4 < 4; ++c4)
-                            if (16 * ch + 4 * c4 < H)
-                                *reinterpret_cast<float4 *>(dst + 4 * c4) =
-                                    make_float4(g[4 * c4] * invS, g[4 * c4 + 1] * invS, g[4 * c4 + 2] * invS, g[4 * c4 + 3] * invS);
+                        for (int k2 = 0; k2 < 4; ++k2) {
+                            const int r = 8 * warp + 2 * k2 + (lane >> 4), c = c0 + 4 * (lane & 15);
+                            const bool row_on = first ? r <= H : r < H;
+                            if (row_on && c < width) {
+                                float *dst = G + (first ? (r < H ? L.off_w[0] + r * FIN : L.off_w_out + H) : L.off_w[1] + r * H) + c;
+                                *reinterpret_cast<float4 *>(dst) = *reinterpret_cast<const float4 *>(S + r * TS_SROW + 4 * (lane & 15));
+                            }
+                        }
+                        ts_worker_sync();
                     }
-                }
+                };
+                TS_TRACE(0, 24);
+                drain(TS_TM_DW1, K1, FIN, true);
+                TS_TRACE(0, 25);
+                drain(TS_TM_DW2, KH, H, false);
+                TS_TRACE(0, 26);
                 if (tid < 128) {
                     auto tot = [&](int qn) {
                         const float *r = red + qn * 512 + tid;
@@ -1070,18 +1110,21 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
                         G[L.off_b_out] = g3;
                     }
                 }
-                fence_proxy_async_all();                  // the optimiser reads the buffer with bulk copies (async proxy)
                 fence_before_sync();
                 ts_worker_sync();                         // (also: `red` and the per-problem parameters are free again)
-                if (fused_adam && tid == 0) mbar_arrive(s.gfull + (it & 1));
+                if (fused_adam && tid == 0) mbar_arrive(s.gfull + gb);
+                // one problem per CTA (small batches, the single-problem planner API): nothing left to overlap, all 22 warps
+                // share the update.  (With several problems per CTA the last update is HBM-bound - every CTA reaches it at the
+                // same time - and the extra warps measured no gain.)
+                if (fused_adam && a.P <= (int)gridDim.x) ts_adam_problem(a, G, p, TS_OPT_WARPS + warp, TS_OPT_WARPS + TS_WORKERS / 32, lane);
                 ++it;
             }
-            TS_TRACE(0, 21);
+            TS_TRACE(0, 27);
         }
     }
     fence_before_sync();
     __syncthreads();
-    TS_TRACE(0, 23);
+    TS_TRACE(0, 28);
     if (is_issuer) tmem_dealloc(tmem, 512);
 }
 
@@ -1104,13 +1147,18 @@ int onf_tcs_prepare(const OnfDims &d) {
     return NFOPP_OK;
 }
 
-// persistent grid: one CTA per SM (NFOPP_TCS_GRID overrides the cap, 0 = one CTA per problem)
-int onf_tcs_grid(int P, int slots) {
-    int cap = g_tcs_sms > 0 ? g_tcs_sms : 148;
+// persistent grid: one CTA per SM; launches that are meant to run side by side (the engine's lanes) take an equal share of
+// the SMs each, so that they do run side by side instead of queueing CTA by CTA behind one another (measured, 1024 corridor
+// problems: 0.860 ms/step with 2 lanes x 148 CTAs, 0.844 with 2 x 74, 0.838 with 4 x 37).  NFOPP_TCS_GRID overrides the cap
+// (0 = one CTA per problem).
+int onf_tcs_grid(int P, int slots, int sm_share) {
+    const int sms = g_tcs_sms > 0 ? g_tcs_sms : 148;
+    int cap = sm_share > 1 ? sms / sm_share : sms;
     if (const char *e = getenv("NFOPP_TCS_GRID")) {
         const int v = atoi(e);
         cap = v > 0 ? v : P;
     }
+    if (cap < 1) cap = 1;
     int grid = P < cap ? P : cap;
     if (slots > 0 && grid > slots) grid = slots;
     return grid < 1 ? 1 : grid;
@@ -1144,7 +1192,7 @@ int onf_tcs_launch(const OnfArgs &o, const OnfTcExtra &x, int P, cudaStream_t st
     NFOPP_REQUIRE(!a.adam_w || (a.sp && a.packed_out), "onf(tensor): fused Adam needs step parameters and the packed copy");
     NFOPP_REQUIRE(!a.adam_w || (a.gscratch && x.gscratch_slots > 0), "onf(tensor, streamed): fused Adam needs the gradient hand-over buffers");
     if (a.n == 0 || P == 0) return NFOPP_OK;
-    const int grid = onf_tcs_grid(P, a.adam_w ? x.gscratch_slots : 0);
+    const int grid = onf_tcs_grid(P, a.adam_w ? x.gscratch_slots : 0, x.sm_share);
     onf_tcs_kernel<<<grid, TS_THREADS, a.t.smem_bytes, stream>>>(a);
     NFOPP_CHECK_CUDA(cudaGetLastError());
     return NFOPP_OK;

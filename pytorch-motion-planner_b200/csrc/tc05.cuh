@@ -70,6 +70,23 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
     }
 }
 
+// The same for waits that are long and not latency-critical (a whole problem's tiles, the optimiser's pass): the warp backs off with
+// nanosleep between polls instead of competing with the working warps for issue slots (ncu, persistent streamed kernel: the
+// polling loops were 17 % of all executed instructions)
+__device__ __forceinline__ void mbar_wait_relaxed(uint64_t *bar, uint32_t parity, uint32_t sleep_ns) {
+    if (mbar_try_wait(bar, parity)) return;
+    uint32_t spins = 0;
+    long long t0 = 0;
+    while (!mbar_try_wait(bar, parity)) {
+        __nanosleep(sleep_ns);
+        if ((++spins & 255u) == 0) {
+            const long long now = clock64();
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > 4000000000LL) __trap();
+        }
+    }
+}
+
 // ---- bulk async copy global -> shared (TMA, 1-D), completion counted on an mbarrier -------------------
 __device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes, uint64_t *bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(

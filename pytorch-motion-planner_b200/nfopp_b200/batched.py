@@ -63,13 +63,15 @@ class BatchedPlanner:
     def __init__(self, config: EngineConfig, device="cuda", use_normal_init=True, lanes="auto"):
         self.config = config
         self.engine = PlannerEngine(config, device=device)
-        # lanes of the graphed step: 2 independent problem ranges once each still fills the GPU's SMs (measured on B200, 1024
-        # corridor problems: 1.104 ms/step with 1 lane, 1.047 with 2, 1.070 with 4)
+        # lanes of the graphed step: independent problem ranges on parallel streams inside the one CUDA graph.  The streamed
+        # tensor kernels are persistent and give every lane #SMs / lanes CTAs, so the lanes really run side by side and one
+        # lane's small kernels, launch tails and HBM bursts fall under another lane's tensor work (measured on B200, 1024
+        # corridor problems: 0.876 ms/step with 1 lane, 0.844 with 2, 0.839 with 3, 0.838 with 4)
         # (the wide ONF path's persistent kernels gain nothing from lanes: 4.78 -> 4.98 ms/step at 2 lanes, so auto keeps 1)
         narrow = config.onf_impl in ("fma", "tensor") or (config.onf_impl == "auto" and config.onf.layers == 2 and config.onf.hidden <= 111)
         if lanes == "auto" and os.environ.get("NFOPP_LANES"):      # profiling: one launch per kernel over all problems
             lanes = int(os.environ["NFOPP_LANES"])
-        self.lanes = (2 if config.problems >= 296 and narrow else 1) if lanes == "auto" else int(lanes)
+        self.lanes = ((4 if config.problems >= 592 else 2 if config.problems >= 296 else 1) if narrow else 1) if lanes == "auto" else int(lanes)
         if self.lanes > 1:
             try:
                 self.engine.set_lanes(self.lanes)

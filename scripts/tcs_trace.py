@@ -22,7 +22,7 @@ import bench as B  # noqa: E402
 WORKER = {0: "start", 1: "setup done (last problem)", 2: "inputs staged", 3: "encode done", 4: "fwd1 done", 5: "ep1 signalled",
           6: "fwd2 done", 7: "logit partials", 8: "dL/dz", 9: "gH2 signalled", 10: "wgrad2+dgrad2 done", 11: "ep3 signalled",
           12: "dgrad1(0) done", 13: "ep4(0) signalled", 14: "dgrad1(1) done", 15: "ep4(1) signalled", 16: "wgrad1 done",
-          20: "tiles done", 21: "gradient handed over", 23: "CTA done"}
+          20: "tiles done", 22: "hand-over buffer free", 24: "partials staged", 25: "dW1 out", 26: "dW2 out", 27: "gradient handed over", 28: "CTA done"}
 ISSUER = {0: "start", 1: "fwd1 issued", 2: "ep1 ready", 3: "fwd2 issued", 4: "gH2 ready", 5: "W2 slot full", 6: "bwdA issued",
           7: "gH1 ready", 8: "W1 slot full", 9: "ep4(0) ready", 10: "wgrad1(0)+dgrad1(1) issued", 11: "ep4(1) ready",
           12: "wgrad1(1) issued"}
