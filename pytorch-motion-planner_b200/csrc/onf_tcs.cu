@@ -78,13 +78,16 @@ constexpr int TS_WST = 8;                       // weight ring stages (K = 16 ch
 constexpr int TS_EF = 64;                       // features per encoding slot (2 slots)
 constexpr uint32_t TS_TM_A = 0, TS_TM_DW2 = TS_NT, TS_TM_DW1 = 2 * TS_NT;   // TMEM columns: work | dW2 [KH] | dW1 [K1]
 constexpr int TS_GX_FLOATS = 4 * TS_NT * 3;     // per-lane-quarter partials of the input gradient
+constexpr int TS_AST = 3;                       // cp.async stages of an updating warp
+constexpr int TS_ASTAGE = 4 * 32 * 16 + 32 * 8; // one stage: 32 lanes x ([g | w | m | v] x 16 B + the lane's two offsets)
+constexpr int TS_ARING = TS_AST * TS_ASTAGE;    // bytes of one warp's ring
 constexpr int TS_SROW = 68;                     // row stride (floats) of the 64-column gradient staging buffer
 
 struct TsDims {
     int F, A, FIN, H, K1, KH, MB, FB0;           // MB feature blocks of FB0 (last one shorter) for dgrad1 / wgrad1
     int S_colW, w1_half, w2_half;                // packed operand copy: [W1 hi | W1 lo | W2 hi | W2 lo], each [k / 8][row][8]
     int h1_half, e_half, w_stage, b_slot, S_ET, et_half;
-    int off_h1h, off_h1l, off_r, off_w, off_misc, misc_floats, off_stage, off_bar, smem_bytes, packed_bytes;
+    int off_h1h, off_h1l, off_r, off_w, off_misc, misc_floats, off_stage, off_red, off_aring, off_praw, praw_floats, off_bar, smem_bytes, packed_bytes;
 };
 
 __host__ __device__ inline int ts_ru16(int x) { return (x + 15) / 16 * 16; }
@@ -112,13 +115,20 @@ __host__ __device__ inline bool ts_make_dims(const OnfDims &d, TsDims *out) {
     t.off_w = t.off_r + ts_max(ts_max(4 * t.e_half, 2 * t.h1_half), ts_max(2 * t.et_half, 10 * 512 * 4));
     t.off_misc = t.off_w + ts_max(TS_WST * t.w_stage, 2 * t.b_slot);
     t.misc_floats = 3 * t.K1 + 32 + 3 * t.KH + 8 + 10 * TS_NT + TS_GX_FLOATS + 32;
-    t.off_stage = (t.off_misc + t.misc_floats * 4 + 127) / 128 * 128;   // [128 rows][TS_SROW] floats: transposes the weight gradient
-    t.off_bar = t.off_stage + 128 * TS_SROW * 4;
+    t.off_stage = t.off_h1h;                     // [128 rows][TS_SROW] floats: transposes the weight gradient when the problem's
+                                                 // MMAs are done (H1 / gH1 are dead until the next problem's first epilogue)
+    t.off_red = ts_max(t.off_r, t.off_stage + 128 * TS_SROW * 4);   // per-unit partial sums [10][4][128] floats, behind it
+    t.off_aring = (t.off_misc + t.misc_floats * 4 + 127) / 128 * 128;   // cp.async rings of the optimiser warps
+    // raw fp32 parameters outside W1 / W2 / the skip row (encoder | b1 | b2, w_out[:H] | b_out) of the problem being set up and
+    // of the next one: bulk-copied by the weight-stream warp while the previous problem computes
+    t.praw_floats = d.lay.off_w[0] + t.H + (d.lay.off_w_out + t.H - d.lay.off_b[1]) + 4;
+    t.off_praw = t.off_aring + TS_OPT_WARPS * TS_ARING;
+    t.off_bar = t.off_praw + 2 * t.praw_floats * 4;
     t.smem_bytes = t.off_bar + 64 * 8 + 16;
     t.packed_bytes = 2 * t.w1_half + 2 * t.w2_half;
     *out = t;
     return d.L == 2 && t.KH <= TS_NT && t.K1 <= 256 && t.H >= 8 && t.H % 4 == 0 && t.FIN % 4 == 0 &&
-           (int)TS_TM_DW1 + t.K1 <= 512 && t.smem_bytes <= 227 * 1024;
+           (int)TS_TM_DW1 + t.K1 <= 512 && t.off_red + 10 * 512 * 4 <= t.off_w && t.smem_bytes <= 227 * 1024;
 }
 
 struct OnfTsArgs {
@@ -214,11 +224,11 @@ __device__ __forceinline__ float ts_pow2_scale(float m) {
 }
 
 struct TsShared {
-    unsigned char *h1h, *h1l, *r, *w;
+    unsigned char *h1h, *h1l, *r, *w, *aring;
     // per input feature f < K1: arg = x1 * pb + u0 * pa + pc  (x1 = u1 for Fourier features, theta for heading features;
     // pc carries the bias and +pi/2 for cosine features, so every feature is sin(arg) with derivative cos(arg))
-    float *pa, *pb, *pc, *ang_b, *b1, *b2, *w3h, *scal, *in0, *aux, *skip, *gbar, *zp, *gxp, *red;
-    uint64_t *wfull, *wempty, *efull, *eempty, *bfull, *bempty, *ready, *done, *gfull, *gempty;
+    float *pa, *pb, *pc, *ang_b, *b1, *b2, *w3h, *scal, *in0, *aux, *skip, *gbar, *zp, *gxp, *red, *praw;
+    uint64_t *wfull, *wempty, *efull, *eempty, *bfull, *bempty, *ready, *done, *gfull, *gempty, *pfull;
     uint32_t *tmem_slot;
     __device__ TsShared(unsigned char *base, const TsDims &t) {
         h1h = base + t.off_h1h; h1l = base + t.off_h1l; r = base + t.off_r; w = base + t.off_w;
@@ -238,6 +248,8 @@ struct TsShared {
         zp = f; f += 4 * TS_NT;
         gxp = f; f += TS_GX_FLOATS;
         red = f; f += 32;
+        praw = reinterpret_cast<float *>(base + t.off_praw);
+        aring = base + t.off_aring;
         uint64_t *b = reinterpret_cast<uint64_t *>(base + t.off_bar);
         wfull = b; b += TS_WST;
         wempty = b; b += TS_WST;
@@ -248,6 +260,7 @@ struct TsShared {
         ready = b++; done = b++;
         gfull = b; b += 2;
         gempty = b; b += 2;
+        pfull = b; b += 2;
         tmem_slot = reinterpret_cast<uint32_t *>(b);
     }
 };
@@ -311,11 +324,34 @@ __device__ __forceinline__ void ts_producer(const OnfTsArgs &a, const TsShared &
         mbar_expect_tx(s.bfull + 1, (uint32_t)bytes);
         bulk_g2s(s.w + t.b_slot, hi + half, bytes, s.bfull + 1);
     };
+    // raw fp32 parameters of problem q -> buffer (use % 2) of s.praw (set-up of the worker warps)
+    auto stage_params = [&](int q, uint32_t use) {
+        const float *Wq = a.weights + (size_t)q * L.n_params;
+        float *dst = s.praw + (size_t)(use & 1u) * t.praw_floats;
+        uint64_t *bar = s.pfull + (use & 1u);
+        const int l0 = L.off_w[0], l1 = t.H, l2 = L.off_w_out + t.H - L.off_b[1];
+        mbar_expect_tx(bar, (uint32_t)(l0 + l1 + l2 + 4) * 4u);
+        bulk_g2s(dst, Wq, (uint32_t)l0 * 4u, bar);
+        bulk_g2s(dst + l0, Wq + L.off_b[0], (uint32_t)l1 * 4u, bar);
+        bulk_g2s(dst + l0 + l1, Wq + L.off_b[1], (uint32_t)l2 * 4u, bar);
+        bulk_g2s(dst + l0 + l1 + l2, Wq + L.off_b_out, 16u, bar);
+    };
+    auto next_problem = [&](int q) {                    // the next problem of this CTA with points (or >= a.P)
+        for (q += (int)gridDim.x; q < a.P; q += (int)gridDim.x)
+            if ((a.count ? a.count[q] : a.n) > 0) break;
+        return q;
+    };
+    uint32_t np = 0;
+    {
+        const int p0 = next_problem((int)blockIdx.x - (int)gridDim.x);
+        if (p0 < a.P) stage_params(p0, 0);
+    }
     for (int p = blockIdx.x; p < a.P; p += gridDim.x) {
         const int cnt = a.count ? a.count[p] : a.n;
         if (cnt <= 0) continue;
         const int n_tiles = (cnt + TS_NT - 1) / TS_NT;
         const unsigned char *src = a.packed + (size_t)p * t.packed_bytes;
+        ++np;
         for (int tile = 0; tile < n_tiles; ++tile) {
             for (int c = 0; c < c1 + c2; ++c, ++wc) {
                 const uint32_t st = wc % TS_WST, k = wc / TS_WST;
@@ -332,15 +368,12 @@ __device__ __forceinline__ void ts_producer(const OnfTsArgs &a, const TsShared &
             if (tile == n_tiles - 1) {
                 // L2 prefetches, issued late so that the lines are still resident when they are used (ncu: issued at the
                 // start of the problem, a wave's 148 x 0.8 MB outlived the L2 and was read from HBM twice):
-                if (p + (int)gridDim.x < a.P) {
-                    // this CTA's next problem: operand copy and the fp32 parameters its set-up reads
-                    const int pn = p + (int)gridDim.x;
+                const int pn = next_problem(p);
+                if (pn < a.P) {
+                    // this CTA's next problem: operand copy -> L2, the fp32 parameters its set-up reads -> shared memory (the
+                    // buffer was last read by the set-up of the previous problem)
                     bulk_prefetch_l2(a.packed + (size_t)pn * t.packed_bytes, (uint32_t)t.packed_bytes);
-                    const float *Wn = a.weights + (size_t)pn * L.n_params;
-                    bulk_prefetch_l2(Wn, (uint32_t)L.off_w[0] * 4u);
-                    bulk_prefetch_l2(Wn + L.off_b[0], (uint32_t)t.H * 4u);
-                    bulk_prefetch_l2(Wn + L.off_b[1], (uint32_t)(L.off_w_out + t.H - L.off_b[1]) * 4u);
-                    bulk_prefetch_l2(Wn + L.off_b_out, 16u);
+                    stage_params(pn, np);
                 }
             }
             if (!want_bwd) continue;
@@ -517,22 +550,38 @@ __device__ __forceinline__ void ts_misc_ranges(const TsDims &t, const nfopp_onf_
     off[3] = L.off_b_out; len[3] = L.n_params - L.off_b_out;
 }
 
-// one float4 of the blob in flight: gradient (hand-over buffer, L2), w / m / v (HBM or L2), where they go back
-struct TsItem {
-    float4 g, w, m, v;
-    int go;          // float offset in the blob (-1: nothing to update)
-    int poff;        // byte offset of the lane pair's 16 B in the operand copy (-1: none)
-};
-__device__ __forceinline__ float4 ts_ldcg4(const float *p) { return __ldcg(reinterpret_cast<const float4 *>(p)); }
+__device__ __forceinline__ void cp_async16(void *dst_smem, const void *src_gmem) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst_smem)), "l"(src_gmem) : "memory");
+}
+// L2 eviction-priority hints: the Adam state streams through L2 exactly once per step - marked evict_first it stops pushing
+// the operand copies (read four times per problem by the weight stream) out of L2
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ void cp_async16_hint(void *dst_smem, const void *src_gmem, uint64_t pol) {
+    asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void st_global_hint4(float *dst, const float4 v, uint64_t pol) {
+    asm volatile("st.global.L2::cache_hint.v4.f32 [%0], {%1, %2, %3, %4}, %5;" ::"l"(dst), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w), "l"(pol)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
 
 // The warps that apply a problem's update share its parameters by interleaving 32-lane groups of "half-octets" (4 consecutive
 // weights of one row): lane pair (2i, 2i + 1) owns one column octet of one row of W1p / W2, so the fp32 loads and stores run
 // through the rows linearly (coalesced) and one shuffle per lane completes the 16 B of hi parts (even lane) / lo parts (odd
 // lane) at [octet][row] of the operand copy; a row's last octet may be half (or all) padding - zeros in the operand copy.
-// Loads of the next group are issued before the arithmetic of the current one (registers as the staging buffer: no shared
-// memory, no bulk copies that would queue in front of the weight stream).  Warp `rank` of `nranks` takes groups rank,
-// rank + nranks, ...
-__device__ __forceinline__ void ts_adam_problem(const OnfTsArgs &a, const float *G, int p, int rank, int nranks, int lane) {
+// Gradient (hand-over buffer, L2), w / m / v (HBM / L2) travel through a per-warp cp.async ring in shared memory, TS_AST - 1
+// groups ahead of the arithmetic (a lane reads back only what it copied itself: no barrier; measured with loads into
+// registers one group ahead the sweep was latency-bound at ~1.3 k cycles per group).  Warp `rank` of `nranks` takes groups
+// rank, rank + nranks, ...
+__device__ __forceinline__ void ts_adam_problem(const OnfTsArgs &a, const float *G, int p, int rank, int nranks, int lane,
+                                                unsigned char *ring) {
     const TsDims &t = a.t;
     const nfopp_onf_layout &L = a.d.lay;
     const int hf = lane & 1;
@@ -548,9 +597,9 @@ __device__ __forceinline__ void ts_adam_problem(const OnfTsArgs &a, const float 
     float *gw = a.adam_w + po, *gm = a.adam_m + po, *gv = a.adam_v + po;
     unsigned char *pk = a.packed_out + (size_t)p * t.packed_bytes;
     // flat index i of a half-octet: [0, n1) rows of W1p, [n1, n1 + n2) rows of W2, then the float4s of the other ranges
-    auto fetch = [&](int i) {
-        TsItem x;
-        x.go = -1; x.poff = -1;
+    // -> go: float offset in the blob (-1: nothing to update), poff: byte offset of the lane pair's 16 B in the operand copy (-1: none)
+    auto locate = [&](int i, int &go, int &poff) {
+        go = -1; poff = -1;
         if (i < n1 + n2) {
             const bool second = i >= n1;
             const int j = second ? i - n1 : i;
@@ -558,56 +607,76 @@ __device__ __forceinline__ void ts_adam_problem(const OnfTsArgs &a, const float 
             const int hs = j - r * (second ? nhs2 : nhs1);
             const int rowlen = second ? t.H : t.FIN;
             const int row_off = second ? L.off_w[1] + r * t.H : (r < t.H ? L.off_w[0] + r * t.FIN : L.off_w_out + t.H);
-            if (4 * hs < rowlen) x.go = row_off + 4 * hs;
-            x.poff = (second ? 2 * t.w1_half : 0) + (hf ? (second ? t.w2_half : t.w1_half) : 0) + (hs >> 1) * t.S_colW +
-                     (r >> 3) * 128 + (r & 7) * 16;
+            if (4 * hs < rowlen) go = row_off + 4 * hs;
+            poff = (second ? 2 * t.w1_half : 0) + (hf ? (second ? t.w2_half : t.w1_half) : 0) + (hs >> 1) * t.S_colW +
+                   (r >> 3) * 128 + (r & 7) * 16;
         } else if (i < ntot) {
             int j = 4 * (i - n1 - n2);
-            x.go = j < mlen[0] ? moff[0] + j
-                   : (j -= mlen[0]) < mlen[1] ? moff[1] + j
-                   : (j -= mlen[1]) < mlen[2] ? moff[2] + j : moff[3] + j - mlen[2];
+            go = j < mlen[0] ? moff[0] + j
+                 : (j -= mlen[0]) < mlen[1] ? moff[1] + j
+                 : (j -= mlen[1]) < mlen[2] ? moff[2] + j : moff[3] + j - mlen[2];
         }
-        const int ld = x.go >= 0 ? x.go : 0;
-        x.g = ts_ldcg4(G + ld);
-        x.w = ts_ldcg4(gw + ld);
-        x.m = ts_ldcg4(gm + ld);
-        x.v = ts_ldcg4(gv + ld);
-        return x;
     };
     const int stride = 32 * nranks;
     if (rank * 32 >= ntot) return;
-    TsItem cur = fetch(rank * 32 + lane);
-    for (int base = rank * 32; base < ntot; base += stride) {              // warp-uniform trip count (shuffles inside)
-        TsItem nxt = cur;
-        if (base + stride < ntot) nxt = fetch(base + stride + lane);
-        const bool upd = cur.go >= 0;
-        ts_adam4(cur.w, cur.m, cur.v, cur.g, a.w1, a.beta2, a.w2, a.eps, step_size, inv_bc2);
-#ifdef NFOPP_TC_TRACE
-        if (upd && !(a.dbg & 2)) {
-#else
+    const uint64_t pol = l2_policy_evict_first();
+    unsigned char *mine = ring + lane * 16;                                  // stage s, array k at mine + s * TS_ASTAGE + k * 512
+    int2 *mine_off = reinterpret_cast<int2 *>(ring + 2048) + lane;          // (go, poff) of stage s at byte s * TS_ASTAGE
+    auto issue = [&](int base, int sl) {                                     // group `base` -> ring stage sl (one commit group)
+        int go = -1, poff = -1;
+        if (base < ntot) locate(base + lane, go, poff);
+        *reinterpret_cast<int2 *>(reinterpret_cast<unsigned char *>(mine_off) + sl * TS_ASTAGE) = make_int2(go, poff);
+        if (go >= 0) {
+            unsigned char *dst = mine + sl * TS_ASTAGE;
+            cp_async16(dst, G + go);
+            cp_async16_hint(dst + 512, gw + go, pol);
+            cp_async16_hint(dst + 1024, gm + go, pol);
+            cp_async16_hint(dst + 1536, gv + go, pol);
+        }
+        cp_async_commit();
+    };
+#pragma unroll
+    for (int j = 0; j < TS_AST - 1; ++j) issue(rank * 32 + j * stride, j);
+    int sl = 0;
+    for (int base = rank * 32; base < ntot; base += stride) {                // warp-uniform trip count (shuffles inside)
+        issue(base + (TS_AST - 1) * stride, sl == 0 ? TS_AST - 1 : sl - 1);
+        cp_async_wait<TS_AST - 1>();
+        const int2 gp = *reinterpret_cast<const int2 *>(reinterpret_cast<const unsigned char *>(mine_off) + sl * TS_ASTAGE);
+        const int go = gp.x, poff = gp.y;
+        const bool upd = go >= 0;
+        float4 w4 = make_float4(0.f, 0.f, 0.f, 0.f);
         if (upd) {
+            const unsigned char *srcp = mine + sl * TS_ASTAGE;
+            const float4 g4 = *reinterpret_cast<const float4 *>(srcp);
+            float4 m4 = *reinterpret_cast<const float4 *>(srcp + 1024), v4 = *reinterpret_cast<const float4 *>(srcp + 1536);
+            w4 = *reinterpret_cast<const float4 *>(srcp + 512);
+            ts_adam4(w4, m4, v4, g4, a.w1, a.beta2, a.w2, a.eps, step_size, inv_bc2);
+#ifdef NFOPP_TC_TRACE
+            if (!(a.dbg & 2))
 #endif
-            *reinterpret_cast<float4 *>(gw + cur.go) = cur.w;
-            *reinterpret_cast<float4 *>(gm + cur.go) = cur.m;
-            *reinterpret_cast<float4 *>(gv + cur.go) = cur.v;
+            {
+                st_global_hint4(gw + go, w4, pol);
+                st_global_hint4(gm + go, m4, pol);
+                st_global_hint4(gv + go, v4, pol);
+            }
         }
         if (base < n1 + n2) {                                              // (warp-uniform; lanes past the matrices have poff < 0)
-            const float4 wq = upd ? cur.w : make_float4(0.f, 0.f, 0.f, 0.f);
             uint32_t h0, l0, h1, l1;
-            split2h(wq.x, wq.y, h0, l0);
-            split2h(wq.z, wq.w, h1, l1);
+            split2h(w4.x, w4.y, h0, l0);
+            split2h(w4.z, w4.w, h1, l1);
             // even lane keeps its hi parts and receives the partner's; odd lane keeps its lo parts and receives the partner's
             const uint32_t s0 = hf ? h0 : l0, s1 = hf ? h1 : l1;
             const uint32_t r0 = __shfl_xor_sync(0xffffffffu, s0, 1), r1 = __shfl_xor_sync(0xffffffffu, s1, 1);
 #ifdef NFOPP_TC_TRACE
-            if (cur.poff >= 0 && !(a.dbg & 1))
+            if (poff >= 0 && !(a.dbg & 1))
 #else
-            if (cur.poff >= 0)
+            if (poff >= 0)
 #endif
-                *reinterpret_cast<uint4 *>(pk + cur.poff) = hf ? make_uint4(r0, r1, l0, l1) : make_uint4(h0, h1, r0, r1);
+                *reinterpret_cast<uint4 *>(pk + poff) = hf ? make_uint4(r0, r1, l0, l1) : make_uint4(h0, h1, r0, r1);
         }
-        cur = nxt;
+        sl = sl + 1 == TS_AST ? 0 : sl + 1;
     }
+    cp_async_wait<0>();
 }
 
 // the optimiser warps: problem after problem as the workers hand the gradients over.  (Letting the sixteen worker warps join
@@ -635,7 +704,10 @@ __device__ __forceinline__ void ts_optimizer(const OnfTsArgs &a, const TsShared 
         ts_wait_relaxed(s.gfull + gb, (uint32_t)(it / TS_GBUF), 256);
         if (otid == 0) TS_TRACE(3, 1);
         // (a CTA with a single problem has nothing to overlap the update with: the worker warps join in, see the kernel)
-        ts_adam_problem(a, G, p, wo, a.P <= (int)gridDim.x ? TS_OPT_WARPS + TS_WORKERS / 32 : TS_OPT_WARPS, lane);
+#ifdef NFOPP_TC_TRACE
+        if (!(a.dbg & 4))
+#endif
+        ts_adam_problem(a, G, p, wo, a.P <= (int)gridDim.x ? TS_OPT_WARPS + TS_WORKERS / 32 : TS_OPT_WARPS, lane, s.aring + wo * TS_ARING);
         // every gradient value this warp needs is in its registers: once all warps say so the workers may overwrite the
         // hand-over buffer
         __syncwarp();
@@ -674,7 +746,7 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
         mbar_init(s.bempty, 1);
         mbar_init(s.ready, TS_WORKERS / 32);
         mbar_init(s.done, 1);
-        for (int i = 0; i < 2; ++i) { mbar_init(s.gfull + i, 1); mbar_init(s.gempty + i, TS_OPT_WARPS); }
+        for (int i = 0; i < 2; ++i) { mbar_init(s.gfull + i, 1); mbar_init(s.gempty + i, TS_OPT_WARPS); mbar_init(s.pfull + i, 1); }
         fence_mbar_init();
     }
     if (is_issuer) tmem_alloc(s.tmem_slot, 512);
@@ -707,41 +779,77 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
         int it = 0;
         float *u0s = s.in0, *u1s = s.in0 + TS_NT, *ths = s.in0 + 2 * TS_NT;
         const int n_slots = (K1 + TS_EF - 1) / TS_EF;
-        for (int p = blockIdx.x; p < a.P; p += gridDim.x) {
-            const int cnt = a.count ? a.count[p] : a.n;
-            if (cnt <= 0) continue;
-            const int n_tiles = (cnt + TS_NT - 1) / TS_NT;
-            const float *W = a.weights + (size_t)p * L.n_params;
-            // ---- per-problem setup: per-feature / per-unit fp32 parameters, gradient operand scale ----
-            for (int f = tid; f < K1; f += TS_WORKERS) {
-                float pa = 0.f, pb = 0.f, pc = 0.f;
-                if (f < F) {
-                    pa = W[L.off_enc_w + 2 * f];
-                    pb = W[L.off_enc_w + 2 * f + 1];
-                    pc = W[L.off_enc_b + f] + ((d.use_cos && f >= 100) ? 1.57079632679489662f : 0.f);
-                } else if (f < FIN) {
-                    const int k = f - F;
-                    const float b = W[L.off_ang_b + k], fr = W[L.off_ang_f + k];
-                    s.ang_b[k] = b;
-                    pb = fr;
-                    pc = fmaf(b, fr, k >= t.A / 2 ? 1.57079632679489662f : 0.f);
+        auto next_problem = [&](int q, int &c) {             // the next problem of this CTA with points (or >= a.P)
+            c = 0;
+            for (q += (int)gridDim.x; q < a.P; q += (int)gridDim.x)
+                if ((c = (a.count ? a.count[q] : a.n)) > 0) break;
+            return q;
+        };
+        // inputs (and label / upstream gradient) of point i of problem q, for thread tid < TS_NT; fetched one tile ahead
+        float cx0 = 0.f, cx1 = 0.f, cx2 = 0.f, cax = 0.f;
+        auto fetch_inputs = [&](int q, int i, int c) {
+            cx0 = 0.f; cx1 = 0.f; cx2 = 0.f; cax = 0.f;
+            if (tid < TS_NT && i < c) {
+                const size_t gi = (size_t)q * a.n + i;
+                const float *xp = a.x + gi * a.x_stride;
+                cx0 = xp[0]; cx1 = xp[1];
+                if (L.in_dim == 3) cx2 = xp[2];
+                if (want_bwd) {
+                    if (a.gbar_mode == 0) cax = a.gz[gi];
+                    else if (a.gbar_mode != 2) cax = a.aux[gi];
                 }
-                s.pa[f] = pa; s.pb[f] = pb; s.pc[f] = pc;
             }
-            for (int i = tid; i < KH; i += TS_WORKERS) {
-                s.b1[i] = i < H ? W[L.off_b[0] + i] : 0.f;
-                s.b2[i] = i < H ? W[L.off_b[1] + i] : 0.f;
-                s.w3h[i] = i < H ? W[L.off_w_out + i] : 0.f;
+        };
+        int cnt = 0;
+        int p = next_problem((int)blockIdx.x - (int)gridDim.x, cnt);
+        if (p < a.P) fetch_inputs(p, tid, cnt);
+        uint32_t np = 0;
+        while (p < a.P) {
+            int cnt_next;
+            const int p_next = next_problem(p, cnt_next);
+            if (np == 1) TS_TRACE(0, 29);
+            TS_TRACE(0, 30);
+            const int n_tiles = (cnt + TS_NT - 1) / TS_NT;
+            // ---- per-problem setup: per-feature / per-unit fp32 parameters (raw values staged by the weight-stream warp),
+            // gradient operand scale ----
+            {
+                ts_wait(s.pfull + (np & 1u), np >> 1);
+                const float *R = s.praw + (size_t)(np & 1u) * t.praw_floats;      // [encoder | b1 | b2, w_out[:H] | b_out]
+                const float *Rb1 = R + L.off_w[0], *Rb2 = Rb1 + H, *Rw3 = Rb2 + (L.off_w_out - L.off_b[1]), *Rb3 = Rw3 + H;
+                for (int f = tid; f < K1; f += TS_WORKERS) {
+                    float pa = 0.f, pb = 0.f, pc = 0.f;
+                    if (f < F) {
+                        pa = R[L.off_enc_w + 2 * f];
+                        pb = R[L.off_enc_w + 2 * f + 1];
+                        pc = R[L.off_enc_b + f] + ((d.use_cos && f >= 100) ? 1.57079632679489662f : 0.f);
+                    } else if (f < FIN) {
+                        const int k = f - F;
+                        const float b = R[L.off_ang_b + k], fr = R[L.off_ang_f + k];
+                        s.ang_b[k] = b;
+                        pb = fr;
+                        pc = fmaf(b, fr, k >= t.A / 2 ? 1.57079632679489662f : 0.f);
+                    }
+                    s.pa[f] = pa; s.pb[f] = pb; s.pc[f] = pc;
+                }
+                for (int i = tid; i < KH; i += TS_WORKERS) {
+                    s.b1[i] = i < H ? Rb1[i] : 0.f;
+                    s.b2[i] = i < H ? Rb2[i] : 0.f;
+                    s.w3h[i] = i < H ? Rw3[i] : 0.f;
+                }
+                if (tid == 0) s.scal[0] = Rb3[0];
+                ++np;
             }
-            if (tid == 0) s.scal[0] = W[L.off_b_out];
             {
                 // bound of |dL/dz| over the problem -> power-of-two scale of the fp16 gradient operands (one scale for all
-                // tiles: the weight-gradient accumulators are shared): external gz / multipliers are scanned, BCE is bounded
-                // by 1 / N
+                // tiles: the weight-gradient accumulators are shared): external gz / multipliers are scanned (a single tile's
+                // values are already in the registers), BCE is bounded by 1 / N
                 float m = 0.f;
                 if (want_bwd && (a.gbar_mode == 0 || a.gbar_mode == 3)) {
-                    const float *src = (a.gbar_mode == 0 ? a.gz : a.aux) + (size_t)p * a.n;
-                    for (int i = tid; i < cnt; i += TS_WORKERS) m = fmaxf(m, fabsf(src[i]));
+                    if (n_tiles == 1) m = fabsf(cax);
+                    else {
+                        const float *src = (a.gbar_mode == 0 ? a.gz : a.aux) + (size_t)p * a.n;
+                        for (int i = tid; i < cnt; i += TS_WORKERS) m = fmaxf(m, fabsf(src[i]));
+                    }
                 }
 #pragma unroll
                 for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
@@ -769,24 +877,16 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
                 const int nv = min(TS_NT, cnt - n0);
                 const int Nt = ts_ru16(nv);
                 const int nch = Nt / 16;
-                // ---- P0: inputs of the tile (onf_model.py:37-38), labels / upstream gradients ----
+                // ---- P0: inputs of the tile (onf_model.py:37-38), labels / upstream gradients: fetched during the previous
+                // tile; the loads of the next tile (of this or of the next problem) are issued right away ----
                 if (tid < TS_NT) {
-                    float x0 = 0.f, x1 = 0.f, x2 = 0.f, ax = 0.f;
-                    if (tid < nv) {
-                        const size_t gi = (size_t)p * a.n + n0 + tid;
-                        const float *xp = a.x + gi * a.x_stride;
-                        x0 = xp[0]; x1 = xp[1];
-                        if (L.in_dim == 3) x2 = xp[2];
-                        if (want_bwd) {
-                            if (a.gbar_mode == 0) ax = a.gz[gi];
-                            else if (a.gbar_mode != 2) ax = a.aux[gi];
-                        }
-                    }
-                    u0s[tid] = (x0 - d.mean) / d.sigma;
-                    u1s[tid] = (x1 - d.mean) / d.sigma;
-                    ths[tid] = x2;
-                    s.aux[tid] = ax;
+                    u0s[tid] = (cx0 - d.mean) / d.sigma;
+                    u1s[tid] = (cx1 - d.mean) / d.sigma;
+                    ths[tid] = cx2;
+                    s.aux[tid] = cax;
                 }
+                if (tile + 1 < n_tiles) fetch_inputs(p, n0 + TS_NT + tid, cnt);
+                else if (p_next < a.P) fetch_inputs(p_next, tid, cnt_next);
                 ts_worker_sync();
                 TS_TRACE(0, 2);
                 // ---- P1: encoding (CUDA cores) feeding fwd1 in slots of 64 features: thread = (point, feature octets g, g+4) ----
@@ -1020,12 +1120,12 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
                 ts_worker_sync();                             // zp, gx, skip, gbar, inputs are rewritten by the next tile
             }
             TS_TRACE(0, 20);
-            if (!want_wgrad) continue;
+            if (!want_wgrad) { p = p_next; cnt = cnt_next; continue; }
             // ---- weight gradients: TMEM accumulators -> global hand-over buffer (blob order) -> optimiser warps / caller ----
             // every MMA of the problem has completed (the wait after the last wgrad1): the encoding ring is dead until the next
             // problem's encoding and holds the per-unit partial sums [10][4][128]
             {
-                float *red = reinterpret_cast<float *>(s.r);
+                float *red = reinterpret_cast<float *>(smem_raw + t.off_red);
                 float *r0 = red + cq * 128 + row;
                 r0[0 * 512] = acc_db1; r0[1 * 512] = acc_db2; r0[2 * 512] = acc_dw3;
                 r0[3 * 512] = fa0; r0[4 * 512] = fb0; r0[5 * 512] = fc0;
@@ -1116,10 +1216,13 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
                 // one problem per CTA (small batches, the single-problem planner API): nothing left to overlap, all 22 warps
                 // share the update.  (With several problems per CTA the last update is HBM-bound - every CTA reaches it at the
                 // same time - and the extra warps measured no gain.)
-                if (fused_adam && a.P <= (int)gridDim.x) ts_adam_problem(a, G, p, TS_OPT_WARPS + warp, TS_OPT_WARPS + TS_WORKERS / 32, lane);
+                // (their cp.async rings sit in the encoding-ring / weight-ring regions: no further problem, nothing streams)
+                if (fused_adam && a.P <= (int)gridDim.x)
+                    ts_adam_problem(a, G, p, TS_OPT_WARPS + warp, TS_OPT_WARPS + TS_WORKERS / 32, lane, s.r + warp * TS_ARING);
                 ++it;
             }
             TS_TRACE(0, 27);
+            p = p_next; cnt = cnt_next;
         }
     }
     fence_before_sync();
