@@ -132,10 +132,11 @@ def init_blob(cfg: OnfConfig, use_normal_init: bool, generator: torch.Generator)
     return pack(named, cfg)
 
 
-def onf_forward(blob: torch.Tensor, cfg: OnfConfig, x: torch.Tensor):
-    """x [N, 2|3] float32 -> (logit [N], cache).  onf_model.py:33-50, angle_encoder.py:15-18."""
-    p = unpack(blob, cfg)
-    x = x.to(torch.float32)
+def onf_forward(blob: torch.Tensor, cfg: OnfConfig, x: torch.Tensor, dtype=torch.float32):
+    """x [N, 2|3] float32 -> (logit [N], cache).  onf_model.py:33-50, angle_encoder.py:15-18.  dtype=float64 gives the
+    exact-arithmetic reference the full-width GPU tests compare with (the reference itself computes in float32)."""
+    p = unpack(blob.to(dtype), cfg)
+    x = x.to(dtype)
     u = (x[:, :2] - cfg.mean) / cfg.sigma                                   # onf_model.py:38
     pre = u @ p["enc_w"].t() + p["enc_b"]                                   # onf_model.py:39
     if cfg.use_cos:                                                          # onf_model.py:40-43
@@ -152,22 +153,24 @@ def onf_forward(blob: torch.Tensor, cfg: OnfConfig, x: torch.Tensor):
         cache.update(dpsi=dpsi, theta=x[:, 2:3])
     else:
         e = phi
-    hs = [e]
+    hs, pre_act = [e], []
     for l in range(cfg.layers):                                              # onf_model.py:47
-        hs.append(torch.relu(hs[-1] @ p[f"W{l}"].t() + p[f"b{l}"]))
+        pre_act.append(hs[-1] @ p[f"W{l}"].t() + p[f"b{l}"])
+        hs.append(torch.relu(pre_act[-1]))
     z = torch.cat([hs[-1], e], 1) @ p["w_out"] + p["b_out"]                  # onf_model.py:48-49
     cache["hs"] = hs
+    cache["pre_act"] = pre_act                                               # (tests: points whose ReLU masks are rounding-sensitive)
     return z, cache
 
 
 def onf_backward(blob: torch.Tensor, cfg: OnfConfig, cache: dict, gz: torch.Tensor):
     """Given dL/dz [N] return (dL/dblob, dL/dx [N, 2|3]).  Analytic restatement of what autograd does
     for onf_model.py:33-50."""
-    p = unpack(blob, cfg)
-    g = {k: torch.zeros_like(v) for k, v in p.items()}
     hs, H = cache["hs"], cfg.hidden
     e = hs[0]
-    gz = gz.to(torch.float32)
+    p = unpack(blob.to(e.dtype), cfg)
+    g = {k: torch.zeros_like(v) for k, v in p.items()}
+    gz = gz.to(e.dtype)
     g["w_out"] = torch.cat([hs[-1], e], 1).t() @ gz
     g["b_out"] = gz.sum()[None]
     gh = gz[:, None] * p["w_out"][None, :H]

@@ -2,7 +2,8 @@
 """BASELINE config 5: ONF fwd+bwd microbench sweep (run on a B200).
 
 For hidden in {64,128,256,512} x layers in {2,4} x points per weight set in {256,4096,65536} x total points
-2^16..2^22: one "point" = forward + weight-gradient + input-gradient (nfopp_onf_backward, BCE upstream gradient,
+2^16..2^24 (totals beyond 2^20 points run as consecutive launches over 2^20-point groups of weight sets, so the activation
+workspace stays at its 2^20-point size; the timed region covers all of them): one "point" = forward + weight-gradient + input-gradient (nfopp_onf_backward, BCE upstream gradient,
 per-problem weights), timed with CUDA events over `reps` calls after warm-up.  Reports Mpts/s, algorithmic TFLOP/s
 (6 x MAC x points) and the fraction of the measured bf16 tensor peak (MEASURED_PEAKS.json).
     python scripts/onf_sweep.py [--quick] [--json out.json] [--impl 3]
@@ -46,8 +47,9 @@ def init_weights(cc, P, gen):
     return w, lay
 
 
-def bench_case(H, layers, n, total, impl, reps, gen):
+def bench_case(H, layers, n, total, impl, reps, gen, chunk_points=1 << 20):
     P = max(1, total // n)
+    Pc = max(1, min(P, chunk_points // n))                 # weight sets per launch
     cc = OnfSpec(0.0, 1.0, True, True, H, layers).to_c()
     w8, lay = init_weights(cc, min(P, 8), gen)
     w = w8.repeat((P + 7) // 8, 1)[:P].contiguous().cuda()
@@ -57,14 +59,16 @@ def bench_case(H, layers, n, total, impl, reps, gen):
     x = x.cuda()
     y = (torch.rand(P, n, generator=gen) < 0.3).float().cuda()
     lib, s = L.lib(), L.stream_ptr()
-    scratch = L.onf_scratch(cc, P, impl, "cuda", n, True)
+    scratch = L.onf_scratch(cc, Pc, impl, "cuda", n, True)
     z = torch.zeros(P, n, device="cuda")
     gx = torch.zeros(P, n, 3, device="cuda")
     gw = torch.zeros(P, lay.n_params, device="cuda")
 
     def call():
-        L.check(lib.nfopp_onf_backward(C.byref(cc), L.ptr(w), L.ptr(x), None, P, n, 1, None, L.ptr(y), 0.0, 1.0, L.ptr(z),
-                                       L.ptr(gx), L.ptr(gw), impl, L.ptr(scratch), s))
+        for p0 in range(0, P, Pc):
+            pc = min(Pc, P - p0)
+            L.check(lib.nfopp_onf_backward(C.byref(cc), L.ptr(w[p0:]), L.ptr(x[p0:]), None, pc, n, 1, None, L.ptr(y[p0:]), 0.0, 1.0,
+                                           L.ptr(z[p0:]), L.ptr(gx[p0:]), L.ptr(gw[p0:]), impl, L.ptr(scratch), s))
     for _ in range(3):
         call()
     torch.cuda.synchronize()
@@ -79,7 +83,7 @@ def bench_case(H, layers, n, total, impl, reps, gen):
     flops = 6.0 * mac_per_point(lay.f_pos, lay.f_in, H, layers) * pts
     finite = bool(torch.isfinite(gw).all() and torch.isfinite(gx).all())
     del scratch
-    return {"hidden": H, "layers": layers, "points_per_problem": n, "problems": P, "points": pts, "ms": ms,
+    return {"hidden": H, "layers": layers, "points_per_problem": n, "problems": P, "launch_groups": (P + Pc - 1) // Pc, "points": pts, "ms": ms,
             "mpts_per_s": pts / ms / 1e3, "tflops": flops / ms / 1e9, "finite": finite,
             "scratch_gb": int(torch.cuda.max_memory_allocated()) / 1e9}
 
@@ -100,11 +104,12 @@ def main():
     cases = []
     if a.quick:
         grid = [(256, 4, 4096, 1 << 18), (256, 4, 256, 1 << 18), (512, 4, 4096, 1 << 18), (128, 2, 4096, 1 << 18),
-                (64, 2, 65536, 1 << 18), (256, 4, 65536, 1 << 20)]
+                (64, 2, 65536, 1 << 18), (256, 4, 65536, 1 << 20), (256, 4, 65536, 1 << 24)]
     else:
         grid = [(H, Ly, n, tot) for H in (64, 128, 256, 512) for Ly in (2, 4) for n in (256, 4096, 65536)
                 for tot in (1 << 16, 1 << 18, 1 << 20) if tot >= n]
         grid += [(256, 4, 65536, 1 << 22), (128, 4, 65536, 1 << 22)]
+        grid += [(H, Ly, 65536, 1 << 24) for H in (64, 128, 256, 512) for Ly in (2, 4)]      # BASELINE configs[4]'s upper end
     for H, Ly, n, tot in grid:
         torch.cuda.reset_peak_memory_stats()
         r = bench_case(H, Ly, n, tot, a.impl, a.reps, gen)
