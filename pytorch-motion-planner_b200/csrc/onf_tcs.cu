@@ -65,6 +65,20 @@ __device__ long long g_ts_trace[3][2][4][64];   // [launch kind: fwd | train | p
 #define TS_CLOCK() 0LL
 #endif
 
+// device-side bounds asserts (make -C csrc debug; compute-sanitizer is closed on the GPU pool): a violated extent traps with
+// the line number instead of corrupting a neighbouring buffer
+#ifdef NFOPP_DEBUG
+#define TS_ASSERT(cond)                                                                                                   \
+    do {                                                                                                                \
+        if (!(cond)) {                                                                                                  \
+            printf("onf_tcs.cu:%d: assertion failed: %s (block %d thread %d)\n", __LINE__, #cond, (int)blockIdx.x, (int)threadIdx.x); \
+            __trap();                                                                                                   \
+        }                                                                                                               \
+    } while (0)
+#else
+#define TS_ASSERT(cond) do { } while (0)
+#endif
+
 constexpr int TS_WORKERS = 512;                 // 16 epilogue / encoding warps
 constexpr int TS_OPT_WARPS = 6;                 // optimiser warps (Adam + operand-copy refresh of the PREVIOUS problem)
 constexpr int TS_OPT = 32 * TS_OPT_WARPS;
@@ -319,6 +333,8 @@ __device__ __forceinline__ void ts_producer(const OnfTsArgs &a, const TsShared &
     const int c1 = t.K1 / 16, c2 = t.KH / 16;
     uint32_t wc = 0, nbe = 0;
     auto block = [&](const unsigned char *hi, int half, int bytes) {      // one weight block, hi and lo parts
+        TS_ASSERT(bytes > 0 && bytes <= t.b_slot && t.off_w + 2 * t.b_slot <= t.off_misc && (bytes & 15) == 0);
+        TS_ASSERT(hi + half + bytes <= a.packed + (size_t)a.P * t.packed_bytes);
         mbar_expect_tx(s.bfull + 0, (uint32_t)bytes);
         bulk_g2s(s.w, hi, bytes, s.bfull + 0);
         mbar_expect_tx(s.bfull + 1, (uint32_t)bytes);
@@ -357,6 +373,7 @@ __device__ __forceinline__ void ts_producer(const OnfTsArgs &a, const TsShared &
                 const uint32_t st = wc % TS_WST, k = wc / TS_WST;
                 if (k > 0) ts_wait_relaxed(s.wempty + st, k - 1, 64);
                 unsigned char *dst = s.w + st * t.w_stage;
+                TS_ASSERT(st < (uint32_t)TS_WST && t.off_w + (int)(st + 1) * t.w_stage <= t.off_misc);
                 const bool second = c >= c1;
                 const unsigned char *g = src + (second ? 2 * t.w1_half : 0) + (size_t)(second ? c - c1 : c) * 2 * t.S_colW;
                 const int half = second ? t.w2_half : t.w1_half;
@@ -411,6 +428,8 @@ __device__ __forceinline__ void ts_issuer(const OnfTsArgs &a, const TsShared &s,
     const int n_tiles = (cnt + TS_NT - 1) / TS_NT;
     for (int tile = 0; tile < n_tiles; ++tile) {
         const int Nt = ts_ru16(min(TS_NT, cnt - tile * TS_NT));
+        TS_ASSERT(Nt >= 16 && Nt <= TS_NT && (int)TS_TM_DW1 + t.K1 <= 512 && (int)TS_TM_DW2 + t.KH <= (int)TS_TM_DW1);
+        TS_ASSERT(t.off_r + 2 * t.et_half <= t.off_w && t.off_r + 4 * t.e_half <= t.off_w && 2 * t.h1_half <= t.off_r);
         const bool acc = tile > 0;                                   // weight-gradient accumulators persist across tiles
         // fwd1: D1[j,n] (+)= W1p[j,k] E[n,k]: one encoding slot (64 features) = up to 4 ring stages of K = 16
         for (int sl = 0; sl < n_slots; ++sl, ++ec) {
@@ -625,6 +644,8 @@ __device__ __forceinline__ void ts_adam_problem(const OnfTsArgs &a, const float 
     auto issue = [&](int base, int sl) {                                     // group `base` -> ring stage sl (one commit group)
         int go = -1, poff = -1;
         if (base < ntot) locate(base + lane, go, poff);
+        TS_ASSERT(sl >= 0 && sl < TS_AST && go + 4 <= L.n_params && (go < 0 || (go & 3) == 0));
+        TS_ASSERT(poff < 0 || (poff + 16 <= t.packed_bytes && (poff & 15) == 0));
         *reinterpret_cast<int2 *>(reinterpret_cast<unsigned char *>(mine_off) + sl * TS_ASTAGE) = make_int2(go, poff);
         if (go >= 0) {
             unsigned char *dst = mine + sl * TS_ASTAGE;
@@ -1155,6 +1176,7 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
                 auto drain = [&](uint32_t tm_col, int ncols, int width, bool first) {
                     for (int c0 = 0; c0 < ncols; c0 += 64) {
                         const int cl = c0 + 16 * cq;
+                        TS_ASSERT(t.off_stage + (row * TS_SROW + 16 * cq + 16) * 4 <= t.off_red && t.off_red + 10 * 512 * 4 <= t.off_w);
                         if (cl < ncols) {
                             float g[16];
                             tmem_ld16(tm_lane + tm_col + cl, g);

@@ -853,6 +853,18 @@ __global__ void __launch_bounds__(256) wide_asm_kernel(const WideAsmArgs a) {
 constexpr int WC_PARTS = 4;              // epilogue warps per TMEM lane quarter (each takes 1/WC_PARTS of the columns)
 constexpr int WC_EPI = 128 * WC_PARTS;
 constexpr int WC_THREADS = 64 + WC_EPI;  // warp 0 producer, warp 1 MMA issue + TMEM, then the epilogue warps
+// device-side bounds asserts of the ring / operand-tile extents (make -C csrc debug)
+#ifdef NFOPP_DEBUG
+#define WIDE_ASSERT(cond)                                                                                                 \
+    do {                                                                                                                \
+        if (!(cond)) {                                                                                                  \
+            printf("onf_wide.cu:%d: assertion failed: %s (block %d thread %d)\n", __LINE__, #cond, (int)blockIdx.x, (int)threadIdx.x); \
+            __trap();                                                                                                   \
+        }                                                                                                               \
+    } while (0)
+#else
+#define WIDE_ASSERT(cond) do { } while (0)
+#endif
 constexpr int WC_STAGES = 5;
 constexpr int WC_STAGE = 16 * WG_NT * 4;             // K = 16 x N <= 256 x (hi + lo)
 constexpr int WC_ACT = 128 * 256 * 4;                // 128 points x K <= 256 x (hi + lo)
@@ -965,6 +977,7 @@ __global__ void __launch_bounds__(WC_THREADS, 1) wide_chain_kernel(const WideCha
                 const unsigned char *Wl = Wp + (dg ? w.wd_off[l] : w.wf_off[l]);
                 for (int st = 0; st < K / 16; ++st, ++it) {
                     const int s = it % WC_STAGES;
+                    WIDE_ASSERT(N * 32 <= WC_STAGE / 2 && N % 16 == 0 && K % 16 == 0 && (size_t)(dg ? w.wd_off[l] : w.wf_off[l]) + (size_t)2 * K * N * 2 <= a.w_stride);
                     mbar_wait(empty + s, ((it / WC_STAGES) & 1) ^ 1);
                     if (lane == 0) mbar_expect_tx(full + s, (uint32_t)(N * 64));
                     __syncwarp();
@@ -1418,6 +1431,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wide_wgrad2_kernel(const WideWg
             const int CB = w.kin[l];
             for (int t = t0; t < t1; ++t, ++it) {
                 const int s = it % W2_STAGES;
+                WIDE_ASSERT(w.Hp * 64 <= W2_HALF && CB * 64 <= W2_HALF);
                 mbar_wait(empty + s, ((it / W2_STAGES) & 1) ^ 1);
                 unsigned char *st = smem + s * W2_STAGE;
                 const size_t tile = (size_t)p * a.T32 + t;

@@ -252,8 +252,19 @@ __global__ void __launch_bounds__(TRAJ_THREADS) traj_post_kernel(const EngineDev
     // ---- grad <- inv_hessian @ grad (nerf_opt_planner.py:151), Adam (:154) --------------------------
     for (int i = tid; i < T; i += TRAJ_THREADS) {
         float acc[3] = {0.f, 0.f, 0.f};
-        for (int j = 0; j < T; ++j) {
-            const float h = __ldg(e.inv_hessian_t + (size_t)j * T + i);      // = inv_hessian[i][j], coalesced
+        // (the matrix is L2-resident: ten rows' loads in flight at a time - one after the other the kernel was bound by 100
+        // dependent L2 latencies per thread; the accumulation order is unchanged)
+        int j = 0;
+        for (; j + 10 <= T; j += 10) {
+            float h[10];
+#pragma unroll
+            for (int u = 0; u < 10; ++u) h[u] = __ldg(e.inv_hessian_t + (size_t)(j + u) * T + i);   // = inv_hessian[i][j + u], coalesced
+#pragma unroll
+            for (int u = 0; u < 10; ++u)
+                for (int d = 0; d < D; ++d) acc[d] = fmaf(h[u], s.g[(j + u) * D + d], acc[d]);
+        }
+        for (; j < T; ++j) {
+            const float h = __ldg(e.inv_hessian_t + (size_t)j * T + i);
             for (int d = 0; d < D; ++d) acc[d] = fmaf(h, s.g[j * D + d], acc[d]);
         }
         for (int d = 0; d < D; ++d) {

@@ -5,6 +5,8 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libnfopp.so")
+if os.environ.get("NFOPP_LIB"):          # diagnostics: libnfopp_debug.so (device-side bounds asserts) / libnfopp_trace.so (phase trace)
+    LIB_PATH = os.path.join(_HERE, os.environ["NFOPP_LIB"])
 MAX_LAYERS = 8
 
 
