@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define NFOPP_ABI_VERSION 4
+#define NFOPP_ABI_VERSION 5
 #define NFOPP_MAX_LAYERS 8
 
 typedef enum {
@@ -221,11 +221,14 @@ int nfopp_engine_evaluate_paths(nfopp_engine *e, int samples_per_segment, uint8_
  * (+ start, goal) is re-parametrised to the T trajectory points by utils/math.py:57-65 (quadratic interpolating
  * spline).  Writes x, y of the stored trajectories; headings are left as they are.  start_cells_dev / goal_cells_dev
  * [P, 2] int32 (row = y cell, column = x cell; computed by the caller with the reference's float32 floor division),
- * workspace_dev from nfopp_engine_astar_workspace_bytes, path_cells_dev [P] int32 (cells on each A* path) or NULL. */
+ * workspace_dev from nfopp_engine_astar_workspace_bytes, path_cells_dev [P] int32 (cells on each A* path) or NULL.
+ * origin_xy (host, 2 doubles: x_min, y_min of collision_checker.get_boundaries(), astar_trajectory_initializer.py:29-34) places
+ * the cell grid; NULL = the labelling boundaries of the engine's checker.  The two differ for a checker that reports
+ * boundaries but does not OR them into its labels (the notebook's MapCollisionChecker). */
 int nfopp_engine_astar_workspace_bytes(nfopp_engine *e, int x_cells, int y_cells, size_t *bytes);
-int nfopp_engine_init_astar(nfopp_engine *e, int x_cells, int y_cells, double resolution, const int32_t *start_cells_dev,
-                            const int32_t *goal_cells_dev, void *workspace_dev, size_t workspace_bytes,
-                            int32_t *path_cells_dev, void *stream);
+int nfopp_engine_init_astar(nfopp_engine *e, int x_cells, int y_cells, double resolution, const double *origin_xy,
+                            const int32_t *start_cells_dev, const int32_t *goal_cells_dev, void *workspace_dev,
+                            size_t workspace_bytes, int32_t *path_cells_dev, void *stream);
 /* Path-quality statistics of every problem's current path, the numbers BenchmarkAdapter::evaluate
  * (benchmark/bench_mr_binding/BenchmarkAdapter.cpp:68-103) files per plan: stats_dev [P, 8] float32 =
  * {path length (x,y), max curvature, normalised curvature (sum of curvature x arc length), angle over length,

@@ -51,7 +51,7 @@ __host__ __device__ inline AstarLayout astar_layout(int X, int Y) {
 struct AstarArgs {
     EngineDev e;
     AstarLayout l;
-    double resolution;
+    double resolution, ox, oy;               // cell size, origin (x_min, y_min) of the cell grid
     const int32_t *start_cell, *goal_cell;   // [P, 2] (row = y cell, col = x cell)
     unsigned char *ws;
     int32_t *path_len;                       // [P] cells on the A* path (or null)
@@ -69,8 +69,8 @@ __global__ void __launch_bounds__(256) astar_label_kernel(const AstarArgs a) {
     const double half = __ddiv_rn(a.resolution, 2.0), th = __ddiv_rn(__dmul_rn(3.0, 3.141592653589793), 4.0);
     for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < a.l.cells; c += gridDim.x * blockDim.x) {
         const int iy = c / a.l.X, ix = c - iy * a.l.X;
-        const double x = __dadd_rn(__dadd_rn(__dmul_rn((double)ix, a.resolution), half), e.checker.bounds[0]);
-        const double y = __dadd_rn(__dadd_rn(__dmul_rn((double)iy, a.resolution), half), e.checker.bounds[2]);
+        const double x = __dadd_rn(__dadd_rn(__dmul_rn((double)ix, a.resolution), half), a.ox);
+        const double y = __dadd_rn(__dadd_rn(__dmul_rn((double)iy, a.resolution), half), a.oy);
         matrix[c] = label_pose(e.checker, obs, m, grid, x, y, th) ? 1 : 0;
     }
 }
@@ -185,8 +185,8 @@ __global__ void __launch_bounds__(32) astar_spline_kernel(const AstarArgs a) {
     pts[0] = e.start[(size_t)p * D]; pts[1] = e.start[(size_t)p * D + 1];
     for (int i = 0; i < n_cells; ++i) {
         const int r = path[i] / l.X, c = path[i] - r * l.X;
-        pts[2 * (i + 1)] = (float)__dadd_rn(__dadd_rn(__dmul_rn((double)c, a.resolution), half), e.checker.bounds[0]);
-        pts[2 * (i + 1) + 1] = (float)__dadd_rn(__dadd_rn(__dmul_rn((double)r, a.resolution), half), e.checker.bounds[2]);
+        pts[2 * (i + 1)] = (float)__dadd_rn(__dadd_rn(__dmul_rn((double)c, a.resolution), half), a.ox);
+        pts[2 * (i + 1) + 1] = (float)__dadd_rn(__dadd_rn(__dmul_rn((double)r, a.resolution), half), a.oy);
     }
     pts[2 * (n - 1)] = e.goal[(size_t)p * D]; pts[2 * (n - 1) + 1] = e.goal[(size_t)p * D + 1];
     // float32 chord lengths + 1e-6, float32 running sum, normalised in float64 (utils/math.py:58-61)
@@ -220,13 +220,15 @@ __global__ void __launch_bounds__(32) astar_spline_kernel(const AstarArgs a) {
 // ---- host side ---------------------------------------------------------------------------------------------------
 size_t astar_workspace_bytes(int P, int X, int Y) { return (size_t)P * astar_layout(X, Y).per_problem; }
 
-int launch_astar_init(const EngineDev &e, int X, int Y, double resolution, const int32_t *start_cell, const int32_t *goal_cell,
-                      unsigned char *ws, size_t ws_bytes, int32_t *path_len, cudaStream_t s) {
+int launch_astar_init(const EngineDev &e, int X, int Y, double resolution, const double *origin_xy, const int32_t *start_cell,
+                      const int32_t *goal_cell, unsigned char *ws, size_t ws_bytes, int32_t *path_len, cudaStream_t s) {
     NFOPP_REQUIRE(X >= 1 && Y >= 1 && (long long)X * Y <= (1 << 24), "astar: grid %d x %d cells", X, Y);
-    NFOPP_REQUIRE(resolution > 0 && e.checker.has_bounds, "astar: needs a positive resolution and checker boundaries");
+    NFOPP_REQUIRE(resolution > 0 && (origin_xy || e.checker.has_bounds), "astar: needs a positive resolution and an origin (checker boundaries)");
     NFOPP_REQUIRE(start_cell && goal_cell && ws && ws_bytes >= astar_workspace_bytes(e.P, X, Y), "astar: workspace too small");
     AstarArgs a{};
     a.e = e; a.l = astar_layout(X, Y); a.resolution = resolution;
+    a.ox = origin_xy ? origin_xy[0] : e.checker.bounds[0];
+    a.oy = origin_xy ? origin_xy[1] : e.checker.bounds[2];
     a.start_cell = start_cell; a.goal_cell = goal_cell; a.ws = ws; a.path_len = path_len;
     dim3 grid((a.l.cells + 255) / 256 < 64 ? (a.l.cells + 255) / 256 : 64, e.P);
     astar_label_kernel<<<grid, 256, 0, s>>>(a);

@@ -64,8 +64,8 @@ int launch_reparam(const EngineDev &e, cudaStream_t s);
 int launch_evaluate_paths(const EngineDev &e, int k, uint8_t *collides, float *length, int32_t *n_hit, cudaStream_t s);
 int launch_path_statistics(const EngineDev &e, double cusp_threshold, int window, float *out, cudaStream_t s);
 size_t astar_workspace_bytes(int P, int X, int Y);
-int launch_astar_init(const EngineDev &e, int X, int Y, double resolution, const int32_t *start_cell, const int32_t *goal_cell,
-                      unsigned char *ws, size_t ws_bytes, int32_t *path_len, cudaStream_t s);
+int launch_astar_init(const EngineDev &e, int X, int Y, double resolution, const double *origin_xy, const int32_t *start_cell,
+                      const int32_t *goal_cell, unsigned char *ws, size_t ws_bytes, int32_t *path_len, cudaStream_t s);
 
 // impl 0 = auto: the tensor path whenever the network shape fits it
 static int resolve_impl(const OnfDims &d, int impl, int *out) {
@@ -892,13 +892,13 @@ extern "C" int nfopp_engine_astar_workspace_bytes(nfopp_engine *e, int x_cells, 
     return NFOPP_OK;
 }
 
-extern "C" int nfopp_engine_init_astar(nfopp_engine *e, int x_cells, int y_cells, double resolution, const int32_t *start_cells,
-                                       const int32_t *goal_cells, void *workspace, size_t workspace_bytes, int32_t *path_cells,
-                                       void *stream) {
+extern "C" int nfopp_engine_init_astar(nfopp_engine *e, int x_cells, int y_cells, double resolution, const double *origin_xy,
+                                       const int32_t *start_cells, const int32_t *goal_cells, void *workspace, size_t workspace_bytes,
+                                       int32_t *path_cells, void *stream) {
     NFOPP_REQUIRE(e, "init_astar: engine missing");
     e->launches += 3;
-    return launch_astar_init(e->dev, x_cells, y_cells, resolution, start_cells, goal_cells, static_cast<unsigned char *>(workspace),
-                             workspace_bytes, path_cells, (cudaStream_t)stream);
+    return launch_astar_init(e->dev, x_cells, y_cells, resolution, origin_xy, start_cells, goal_cells,
+                             static_cast<unsigned char *>(workspace), workspace_bytes, path_cells, (cudaStream_t)stream);
 }
 
 extern "C" int nfopp_engine_path_statistics(nfopp_engine *e, double cusp_angle_threshold, int clearing_window_cells, float *stats,

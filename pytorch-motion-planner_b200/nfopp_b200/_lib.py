@@ -80,7 +80,7 @@ SIGNATURES = {
     "nfopp_engine_reparametrize": (_I, [_P, _P]),
     "nfopp_engine_evaluate_paths": (_I, [_P, _I, _P, _P, _P, _P]),
     "nfopp_engine_astar_workspace_bytes": (_I, [_P, _I, _I, C.POINTER(C.c_size_t)]),
-    "nfopp_engine_init_astar": (_I, [_P, _I, _I, C.c_double, _P, _P, _P, C.c_size_t, _P, _P]),
+    "nfopp_engine_init_astar": (_I, [_P, _I, _I, C.c_double, _P, _P, _P, _P, C.c_size_t, _P, _P]),
     "nfopp_engine_path_statistics": (_I, [_P, C.c_double, _I, _P, _P]),
     "nfopp_postprocess_workspace_bytes": (_I, [_I, _I, _P]),
     "nfopp_postprocess_paths": (_I, [_P, _I, _I, C.c_double, C.c_double, _I, _P, C.c_size_t, _P, _P, _P]),
@@ -107,7 +107,7 @@ def lib():
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(handle, name)
             fn.restype, fn.argtypes = res, args
-        if handle.nfopp_abi_version() != 4:
+        if handle.nfopp_abi_version() != 5:
             raise NfoppError("libnfopp.so ABI version mismatch")
         _lib = handle
     return _lib

@@ -13,4 +13,13 @@ class AstarTrajectoryInitializer(TrajectoryInitializer):
     def initialize_engine(self, engine):
         """x, y from A* over the checker-labelled grid; headings as TrajectoryInitializer.initialize_angle (:21-29)."""
         engine.init_trajectories()
-        return engine.init_astar(self._resolution)
+        # the cell grid spans collision_checker.get_boundaries() (:29-34) - also for a checker whose labels do not include
+        # its boundaries (GridCollisionChecker)
+        extent = None
+        checker = getattr(self, "_collision_checker", None)
+        if checker is not None and hasattr(checker, "get_boundaries"):
+            try:
+                extent = checker.get_boundaries()
+            except Exception:
+                extent = None
+        return engine.init_astar(self._resolution, extent=extent)

@@ -259,13 +259,17 @@ class PlannerEngine:
             goal_angle = wrap_angle(goal[:, 2] - start[:, 2]) + start[:, 2]
             traj[:, :, 2] = batched_linspace(start[:, 2], goal_angle, n)[:, 1:-1]
 
-    def init_astar(self, resolution):
+    def init_astar(self, resolution, extent=None):
         """AstarTrajectoryInitializer.initialize_trajectory (astar/astar_trajectory_initializer.py:15-46) for every problem,
         on the device: checker-labelled cell grid -> A* (astar/jps.py, jps=False) -> quadratic re-parametrisation into the
-        x, y of the trajectories (call after init_trajectories, which sets the headings).  -> int32 [P] cells per A* path."""
-        if self.config.checker_bounds is None:
+        x, y of the trajectories (call after init_trajectories, which sets the headings).  -> int32 [P] cells per A* path.
+        extent = collision_checker.get_boundaries() (x_min, x_max, y_min, y_max) of the cell grid; default: the checker's
+        labelling boundaries (the two differ for a checker that reports boundaries without OR-ing them into its labels)."""
+        if extent is None:
+            extent = self.config.checker_bounds
+        if extent is None:
             raise ValueError("A* initialisation needs collision-checker boundaries (get_boundaries)")
-        b = tuple(float(v) for v in self.config.checker_bounds)
+        b = tuple(float(v) for v in extent)
         res = float(resolution)
         # grid shape and start / goal cells exactly as the reference computes them (:29-34: python floor division on the
         # boundaries, float32 floor division on the float32 end points)
@@ -284,7 +288,8 @@ class PlannerEngine:
         ws = torch.empty(int(nbytes.value), dtype=torch.uint8, device=self.device)
         path_cells = torch.empty(self.config.problems, dtype=torch.int32, device=self.device)
         with torch.cuda.device(self.device):
-            L.check(self._lib.nfopp_engine_init_astar(self._h, x_cells, y_cells, res, L.ptr(cells[0]), L.ptr(cells[1]), L.ptr(ws),
+            origin = (C.c_double * 2)(b[0], b[2])
+            L.check(self._lib.nfopp_engine_init_astar(self._h, x_cells, y_cells, res, origin, L.ptr(cells[0]), L.ptr(cells[1]), L.ptr(ws),
                                                       C.c_size_t(ws.numel()), L.ptr(path_cells), L.stream_ptr()))
             torch.cuda.current_stream().synchronize()          # the workspace is freed on return
         return path_cells

@@ -725,6 +725,22 @@ def test_astar_initialiser_through_the_factory_and_on_a_grid():
     path = planner.get_path()
     assert path.shape == (102, 3)
     assert np.abs(path[1:-1, :2] - fx["disc_coarse/trajectory"][:, :2]).max() <= 2e-6
+    # a checker that reports boundaries but does not OR them into its labels (the notebook's MapCollisionChecker): the A*
+    # cell grid spans get_boundaries() (astar_trajectory_initializer.py:29-34), the labels stay the checker's own
+    from nfopp_b200.collision_checker import GridCollisionChecker, MapImage
+    rs = np.random.RandomState(5)
+    occ = (rs.rand(60, 60) < 0.08).astype(np.uint8)
+    occ[:6, :6] = 0
+    occ[-8:, -8:] = 0
+    bounds = (0.0, 3.0, 0.0, 3.0)
+    gc = GridCollisionChecker(MapImage(60, 60, 0.0, 0.0, 0.05, occ), bounds)
+    gplanner = PlannerFactory.make_constrained_onf_planner(gc, params)
+    start, goal = np.array([0.12, 0.12, 0.0]), np.array([2.8, 2.8, 0.0])
+    gplanner.init(start, goal, bounds)
+    gpath = gplanner.get_path()
+    label = lambda q: OC.grid_labels(q, occ, 0.0, 0.0, 0.05)            # noqa: E731  (no boundary OR)
+    xy, _, _ = A.initial_trajectory_xy(start.astype(np.float32), goal.astype(np.float32), bounds, 0.25, label, 100)
+    assert np.abs(gpath[1:-1, :2] - xy).max() <= 2e-6
 
 
 # ---------------------------------------------------------------------------------------- BASELINE's full sizes

@@ -22,7 +22,7 @@ def test_library_loads_and_exports_every_declared_symbol():
     for name in declared:
         assert hasattr(handle, name), f"{name} declared in include/nfopp.h but not exported"
     assert declared == set(L.SIGNATURES), declared ^ set(L.SIGNATURES)
-    assert handle.nfopp_abi_version() == 4
+    assert handle.nfopp_abi_version() == 5
 
 
 @pytest.mark.parametrize("name", list(U.ONF_CFGS))
