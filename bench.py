@@ -41,8 +41,9 @@ PROBLEMS_PER_GPU = 1024
 
 
 WORKLOADS = ("corridor", "forest", "gridmap-wide")
-TENSOR_IMPL = ("tensor (fused tcgen05 kernel, 112-point tiles, streamed fp16 hi/lo weights, every product 3 MMA passes "
-               "(hi.hi + lo.hi + hi.lo), static power-of-two gradient scale, fp32 TMEM accumulators, fused Adam)")
+TENSOR_IMPL = ("tensor (persistent fused tcgen05 kernel: one CTA per SM walks its problems, 112-point tiles, streamed fp16 hi/lo "
+               "weights, every product 3 MMA passes (hi.hi + lo.hi + hi.lo), static power-of-two gradient scale, fp32 TMEM "
+               "accumulators, Adam + operand-copy refresh of the previous problem on six optimiser warps under the next one's tiles)")
 FOREST_TOTAL = 16384            # BASELINE configs[2]: problems of the whole job, sharded over the GPUs
 
 
@@ -70,7 +71,8 @@ def workload_config(problems, onf_impl="auto", workload="corridor"):
     cfg.update({"problems_per_gpu": problems, "trajectory_length": 100, "samples_per_step": 209,
                 "rng": "on-device Philox4x32-10", "onf_impl": impl if tensor else "fma (CUDA-core fp32)",
                 "launch": "one CUDA graph per step" + ("" if workload == "gridmap-wide" else
-                                                       ", two lanes (independent problem ranges on parallel streams inside the graph)"),
+                                                       ", up to four lanes (independent problem ranges on parallel streams inside the graph, "
+                                                       "each lane's persistent kernels on #SMs / lanes CTAs; BatchedPlanner picks the count)"),
                 "l2": f"per-step working set ({ws}) exceeds the 126 MB L2",
                 "e2e": "per step: inputs pinned host -> device staging (copy stream) -> engine buffers, planner.step, paths -> "
                        "pinned host (copy stream); the copies of neighbouring steps run under the step's kernels"})
@@ -342,7 +344,7 @@ def measure_planner(D, workload, count, lo, total, steps, warmup, onf_impl="auto
     launches = eng.launches - launches0
     out = {"planner": planner, "cfg": cfg, "init_kw": init_kw, "starts": starts, "goals": goals, "ms": ms,
            "ms_per_step": ms / steps, "value": total * steps / (ms * 1e-3), "launches": int(launches),
-           "clocks": clock_summary, "steps": steps}
+           "clocks": clock_summary, "steps": steps, "lanes": int(planner.lanes)}
     # ---- end-to-end through the host-facing API with HOST buffers: inputs pinned host -> staging (copy-in stream) ->
     # engine buffers, planner.step, paths -> pinned host (copy-out stream), alternating buffer sets.  Every step's inputs
     # leave pinned host memory and every step's paths reach it inside the timed region.
@@ -604,7 +606,7 @@ def run_ours(args):
         "metric": METRIC, "value": m["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": m["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32 (tensor path: fp16 hi/lo split products, 3 MMA passes each, fp32 accumulate)" if impl != "fma" else "f32",
-        "data": "synthetic", "config": workload_config(P, impl, args.workload),
+        "data": "synthetic", "config": dict(workload_config(P, impl, args.workload), lanes=m["lanes"]),
         "clocks": m["clocks"], "e2e": m["e2e"], "gpu_launches": m["launches"],
         "roofline": roof, "kernel_ms": m["prof"], "streams": streams,
         "paths_finite": finite, "paths_gathered": list(all_paths.shape),
