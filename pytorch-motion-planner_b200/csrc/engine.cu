@@ -470,7 +470,7 @@ static void fill_dev_config(nfopp_engine *e) {
     CheckerParams &k = d.checker;
     k.kind = c.checker_kind; k.has_bounds = c.has_bounds;
     for (int i = 0; i < 4; ++i) { k.bounds[i] = c.bounds[i]; k.box[i] = c.box[i]; }
-    k.radius = c.robot_radius; k.rows = c.grid_rows; k.cols = c.grid_cols;
+    k.radius = c.robot_radius; k.radius_sq = circle_threshold(c.robot_radius); k.rows = c.grid_rows; k.cols = c.grid_cols;
     k.ox = c.grid_origin_x; k.oy = c.grid_origin_y; k.cell = c.grid_cell;
     d.env_shared = c.env_shared; d.m_max = c.max_obstacles > 0 ? c.max_obstacles : 1;
 }

@@ -121,6 +121,7 @@ extern "C" int nfopp_label_circle(const double *poses, int P, int n, int pose_di
     CheckerParams c{};
     c.kind = 1;
     c.radius = radius;
+    c.radius_sq = circle_threshold(radius);
     fill_bounds(c, bounds);
     NFOPP_REQUIRE(obstacles || m_max == 0, "label_circle: obstacles missing");
     return launch_label(c, poses, P, n, pose_dim, m_max ? obstacles : nullptr, count, P_env, m_max, nullptr, labels,

@@ -1,6 +1,8 @@
 // label.cuh - ground-truth collision labels for one pose, float64, in numpy's operation order with FMA
 // contraction made impossible by explicit round-to-nearest intrinsics.
 #pragma once
+#include <math.h>
+
 #include "common.cuh"
 
 namespace nfopp {
@@ -10,10 +12,23 @@ struct CheckerParams {
     int has_bounds;
     double bounds[4];  // x0,x1,y0,y1
     double radius;
+    double radius_sq;  // smallest float64 s with sqrt(s) >= radius (circle_threshold): sqrt(s) < radius  <=>  s < radius_sq
     double box[4];
     int rows, cols;
     double ox, oy, cell;
 };
+
+// smallest float64 s >= 0 with sqrt(s) >= r (IEEE correctly rounded sqrt on the host = __dsqrt_rn on the device); 0 for r <= 0
+// (sqrt(s) < r is then never true), NaN for a NaN radius
+inline double circle_threshold(double r) {
+    if (!(r == r)) return r;
+    if (r <= 0.0) return 0.0;
+    double s = r * r;
+    if (!(s < 1.0e308)) return s;                       // r so large that r * r overflows: every finite distance is inside
+    while (s > 0.0 && sqrt(s) >= r) s = nextafter(s, -1.0);
+    while (sqrt(s) < r) s = nextafter(s, 1.0e308 * 10.0);
+    return s;
+}
 
 // collision_checker/collision_checker.py:12-19 (strict inequalities)
 __device__ __forceinline__ bool label_boundary(const CheckerParams &c, double x, double y) {
@@ -21,13 +36,16 @@ __device__ __forceinline__ bool label_boundary(const CheckerParams &c, double x,
     return (x > c.bounds[1]) | (x < c.bounds[0]) | (y > c.bounds[3]) | (y < c.bounds[2]);
 }
 
-// circle_collision_checker.py:11-14: any_m sqrt(dx*dx + dy*dy) < r
-__device__ __forceinline__ bool label_circle(const double *__restrict__ obs, int m, double r, double x, double y) {
+// circle_collision_checker.py:11-14: any_m sqrt(dx*dx + dy*dy) < r.  The correctly rounded square root is monotone, so
+// sqrt(s) < r is the same predicate as s < thr with thr = the smallest float64 whose square root rounds to >= r (found on
+// the host, circle_threshold): no square root per pose-obstacle pair, the same labels bit for bit (NaN / inf included:
+// both comparisons are false).
+__device__ __forceinline__ bool label_circle(const double *__restrict__ obs, int m, double thr, double x, double y) {
     bool hit = false;
     for (int i = 0; i < m; ++i) {
         double dx = __dsub_rn(x, obs[2 * i]), dy = __dsub_rn(y, obs[2 * i + 1]);
-        double d = __dsqrt_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
-        hit |= d < r;
+        double s = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
+        hit |= s < thr;
     }
     return hit;
 }
@@ -65,7 +83,7 @@ __device__ __forceinline__ bool label_grid(const uint8_t *__restrict__ grid, con
 __device__ __forceinline__ bool label_pose(const CheckerParams &c, const double *__restrict__ obs, int m,
                                            const uint8_t *__restrict__ grid, double x, double y, double th) {
     bool hit = false;
-    if (c.kind == 1) hit = label_circle(obs, m, c.radius, x, y);
+    if (c.kind == 1) hit = label_circle(obs, m, c.radius_sq, x, y);
     else if (c.kind == 2) hit = label_rectangle(obs, m, c.box, x, y, th);
     else if (c.kind == 3) hit = label_grid(grid, c, x, y);
     return hit | label_boundary(c, x, y);
