@@ -85,8 +85,9 @@ constexpr int TS_OPT = 32 * TS_OPT_WARPS;
 constexpr int TS_THREADS = TS_WORKERS + 64 + TS_OPT;   // + MMA-issue warp + weight-stream warp + optimiser warps
 constexpr int TS_GBUF = 1;                      // gradient hand-over buffers per CTA in use (of the 2 allocated): the optimiser has read
                                                 // a problem's gradient long before the next one is ready, and 148 x 133 KB less live data in L2 pays
-constexpr int TS_REGS_WORKER = 88, TS_REGS_SERVICE = 64;   // setmaxnreg split of the 768 x 80 registers the CTA starts with: 512 x 88 + 256 x 64
+constexpr int TS_REGS_WORKER = 96, TS_REGS_SERVICE = 48;   // setmaxnreg split of the 768 x 80 registers the CTA starts with: 512 x 88 + 256 x 64
 constexpr int TS_NT = 112;                      // points per tile
+constexpr int TS_HALF = 64;                     // ... handled as two halves (0..63 | 64..111) from the first epilogue on
 constexpr uint32_t TS_SPT = TS_NT * 16;         // S_row of the point-indexed operand buffers [hidden / 8][point / 8][8][8]
 constexpr int TS_WST = 8;                       // weight ring stages (K = 16 chunk of W, hi + lo)
 constexpr int TS_EF = 64;                       // features per encoding slot (2 slots)
@@ -271,7 +272,8 @@ struct TsShared {
         eempty = b; b += 2;
         bfull = b; b += 2;
         bempty = b++;
-        ready = b++; done = b++;
+        ready = b; b += 2;                          // per half tile (points 0..63 | 64..111)
+        done = b; b += 2;
         gfull = b; b += 2;
         gempty = b; b += 2;
         pfull = b; b += 2;
@@ -302,7 +304,11 @@ __device__ __forceinline__ void ts_signal(uint64_t *bar) {
     if ((threadIdx.x & 31) == 0) mbar_arrive(bar);
 }
 __device__ __forceinline__ void ts_wait(uint64_t *bar, uint32_t use) {     // wait for completion number `use` (0-based)
+#ifdef NFOPP_TS_SPIN
+    mbar_wait_spin(bar, use & 1u);
+#else
     mbar_wait(bar, use & 1u);
+#endif
     fence_after_sync();
 }
 __device__ __forceinline__ void ts_wait_relaxed(uint64_t *bar, uint32_t use, uint32_t sleep_ns) {   // long, non-critical waits
@@ -324,7 +330,7 @@ __device__ __forceinline__ void ts_store_row16(unsigned char *hi_buf, unsigned c
 }
 
 // ---- the weight-stream warp (one elected lane): per problem and tile the forward ring, then the backward blocks (hi ->
-// slot 0, lo -> slot 1).  The CTA is persistent: the ring runs on into the next problem's weights as soon as the last
+// slot 0, lo -> slot 1; the slots overlay the ring).  The CTA is persistent: the ring runs on into the next problem's weights as soon as the last
 // backward block of this one has been consumed, and the operand copy + the small fp32 parameters of the problem after
 // that are pulled into L2 while this one computes.
 __device__ __forceinline__ void ts_producer(const OnfTsArgs &a, const TsShared &s, bool want_bwd) {
@@ -369,7 +375,7 @@ __device__ __forceinline__ void ts_producer(const OnfTsArgs &a, const TsShared &
         const unsigned char *src = a.packed + (size_t)p * t.packed_bytes;
         ++np;
         for (int tile = 0; tile < n_tiles; ++tile) {
-            for (int c = 0; c < c1 + c2; ++c, ++wc) {
+            for (int c = 0; c < c1 + c2; ++c, ++wc) {                 // fwd1, fwd2: K = 16 chunks of W1p, then of W2p (hi + lo)
                 const uint32_t st = wc % TS_WST, k = wc / TS_WST;
                 if (k > 0) ts_wait_relaxed(s.wempty + st, k - 1, 64);
                 unsigned char *dst = s.w + st * t.w_stage;
@@ -397,7 +403,7 @@ __device__ __forceinline__ void ts_producer(const OnfTsArgs &a, const TsShared &
             // every forward MMA that reads the ring has completed before the ring is reused as two big slots
             for (uint32_t c = wc > TS_WST ? wc - TS_WST : 0; c < wc; ++c) ts_wait_relaxed(s.wempty + c % TS_WST, c / TS_WST, 64);
             TS_TRACE(2, 2);
-            block(src + 2 * t.w1_half, t.w2_half, t.w2_half);                           // W2 -> dgrad2
+            block(src + 2 * t.w1_half, t.w2_half, t.w2_half);                           // W2p -> dgrad2
             ts_wait_relaxed(s.bempty, nbe++, 64);
             const int len0 = t.FB0 / 8 * t.S_colW;
             block(src, t.w1_half, len0);                                                // W1, feature block 0 -> dgrad1
@@ -421,7 +427,8 @@ __device__ __forceinline__ void ts_issuer(const OnfTsArgs &a, const TsShared &s,
     const uint32_t tmA = tmem + TS_TM_A, tmDW2 = tmem + TS_TM_DW2, tmDW1 = tmem + TS_TM_DW1;
     const int c2 = t.KH / 16;
     const int n_slots = (t.K1 + TS_EF - 1) / TS_EF;
-    uint32_t wc = 0, ec = 0, nready = 0, nbf = 0;
+    uint32_t wc = 0, ec = 0, nbf = 0;
+    uint32_t nready0 = 0, nready1 = 0;
     for (int p = blockIdx.x; p < a.P; p += gridDim.x) {
     const int cnt = a.count ? a.count[p] : a.n;
     if (cnt <= 0) continue;
@@ -431,6 +438,10 @@ __device__ __forceinline__ void ts_issuer(const OnfTsArgs &a, const TsShared &s,
         TS_ASSERT(Nt >= 16 && Nt <= TS_NT && (int)TS_TM_DW1 + t.K1 <= 512 && (int)TS_TM_DW2 + t.KH <= (int)TS_TM_DW1);
         TS_ASSERT(t.off_r + 2 * t.et_half <= t.off_w && t.off_r + 4 * t.e_half <= t.off_w && 2 * t.h1_half <= t.off_r);
         const bool acc = tile > 0;                                   // weight-gradient accumulators persist across tiles
+        // From the first epilogue on the tile is handled as two HALVES (points 0..63 | 64..Nt-1) with their own ready / done
+        // barriers: the epilogue of one half runs under the MMAs of the other (same operand buffers and the same work
+        // accumulator - the halves are disjoint point columns of both).
+        const int nh = (want_bwd && Nt > TS_HALF) ? 2 : 1;           // (forward-only launches have nothing to overlap: one half)
         // fwd1: D1[j,n] (+)= W1p[j,k] E[n,k]: one encoding slot (64 features) = up to 4 ring stages of K = 16
         for (int sl = 0; sl < n_slots; ++sl, ++ec) {
             const uint32_t es = ec & 1u;
@@ -450,10 +461,10 @@ __device__ __forceinline__ void ts_issuer(const OnfTsArgs &a, const TsShared &s,
             }
             mma_commit(s.eempty + es, lead);
         }
-        mma_commit(s.done, lead);
+        for (int h = 0; h < nh; ++h) mma_commit(s.done + h, lead);
         TS_TRACE(1, 1);
-        // fwd2: D2[i,n] = W2p[i,j] H1[j,n]
-        ts_wait(s.ready, nready++);
+        // fwd2: D2[i,n] = W2p[i,j] H1[j,n]      (both halves at once: its weights stream through the ring behind fwd1's)
+        for (int h = 0; h < nh; ++h) ts_wait(s.ready + h, (h ? nready1++ : nready0++));
         TS_TRACE(1, 2);
         for (int ks = 0; ks < c2; ++ks, ++wc) {
             const uint32_t st = wc % TS_WST;
@@ -464,52 +475,71 @@ __device__ __forceinline__ void ts_issuer(const OnfTsArgs &a, const TsShared &s,
                       instr_desc_f16(128, Nt, 0, 1), ks > 0, lead);
             mma_commit(s.wempty + st, lead);
         }
-        mma_commit(s.done, lead);
+        for (int h = 0; h < nh; ++h) mma_commit(s.done + h, lead);
         TS_TRACE(1, 3);
         if (!want_bwd) continue;
         // wgrad2: dW2[i,j] += gH2[i,n] H1[j,n];   dgrad2: gD1[j,n] = W2p[i,j] gH2[i,n]     (gH2 hi, lo in the old encoding ring)
-        ts_wait(s.ready, nready++);
-        TS_TRACE(1, 4);
-        if (want_wgrad)
-            ts_kloop3(tmDW2, desc_kmajor(rr, TS_SPT, 128), desc_kmajor(rr + t.h1_half, TS_SPT, 128), desc_kmajor(h1h, TS_SPT, 128),
-                      desc_kmajor(h1l, TS_SPT, 128), 256, 256, Nt / 16, instr_desc_f16(128, t.KH, 0, 0), acc, lead);
-        ts_wait(s.bfull + 0, nbf);
-        ts_wait(s.bfull + 1, nbf);
-        ++nbf;
-        TS_TRACE(1, 5);
-        ts_kloop3(tmA, desc_mnmajor(s0, 128, t.S_colW), desc_mnmajor(s1, 128, t.S_colW), desc_mnmajor(rr, TS_SPT, 128),
-                  desc_mnmajor(rr + t.h1_half, TS_SPT, 128), 256, 2 * TS_SPT, c2, instr_desc_f16(128, Nt, 1, 1), false, lead);
-        mma_commit(s.bempty, lead);
-        mma_commit(s.done, lead);
-        TS_TRACE(1, 6);
-        // dgrad1, feature block 0: gE[k,n] = W1p[j,k] gH1[j,n]      (gH1 hi, lo in place over H1 hi, lo)
-        ts_wait(s.ready, nready++);
-        TS_TRACE(1, 7);
-        ts_wait(s.bfull + 0, nbf);
-        ts_wait(s.bfull + 1, nbf);
-        ++nbf;
-        TS_TRACE(1, 8);
-        ts_kloop3(tmA, desc_mnmajor(s0, 128, t.S_colW), desc_mnmajor(s1, 128, t.S_colW), desc_mnmajor(h1h, TS_SPT, 128),
-                  desc_mnmajor(h1l, TS_SPT, 128), 256, 2 * TS_SPT, c2, instr_desc_f16(128, Nt, 1, 1), false, lead);
-        mma_commit(s.bempty, lead);
-        mma_commit(s.done, lead);
-        for (int mb = 0; mb < t.MB; ++mb) {
-            ts_wait(s.ready, nready++);                 // block mb of gE consumed, E^T of block mb written (hi, lo)
-            TS_TRACE(1, 9 + 2 * mb);
-            if (want_wgrad)                             // wgrad1: dW1[j, block mb] += gH1[j,n] E[n, block mb]
-                ts_kloop3(tmDW1 + mb * t.FB0, desc_kmajor(h1h, TS_SPT, 128), desc_kmajor(h1l, TS_SPT, 128), desc_kmajor(rr, 128, t.S_ET),
-                          desc_kmajor(rr + t.et_half, 128, t.S_ET), 256, 2 * t.S_ET, Nt / 16,
-                          instr_desc_f16(128, min(t.FB0, t.K1 - mb * t.FB0), 0, 0), acc, lead);
-            if (mb + 1 < t.MB) {
+        for (int h = 0; h < nh; ++h) {
+            const int Nh = nh == 1 ? Nt : (h == 0 ? TS_HALF : Nt - TS_HALF);
+            const uint32_t po = (uint32_t)h * (TS_HALF / 8) * 128u;
+            ts_wait(s.ready + h, (h ? nready1++ : nready0++));
+            TS_TRACE(1, 4);
+            if (want_wgrad)
+                ts_kloop3(tmDW2, desc_kmajor(rr + po, TS_SPT, 128), desc_kmajor(rr + t.h1_half + po, TS_SPT, 128),
+                          desc_kmajor(h1h + po, TS_SPT, 128), desc_kmajor(h1l + po, TS_SPT, 128), 256, 256, Nh / 16,
+                          instr_desc_f16(128, t.KH, 0, 0), acc || h > 0, lead);
+            if (h == 0) {
                 ts_wait(s.bfull + 0, nbf);
                 ts_wait(s.bfull + 1, nbf);
                 ++nbf;
-                ts_kloop3(tmA, desc_mnmajor(s0, 128, t.S_colW), desc_mnmajor(s1, 128, t.S_colW), desc_mnmajor(h1h, TS_SPT, 128),
-                          desc_mnmajor(h1l, TS_SPT, 128), 256, 2 * TS_SPT, c2, instr_desc_f16(128, Nt, 1, 1), false, lead);
-                mma_commit(s.bempty, lead);
             }
-            if (want_wgrad || mb + 1 < t.MB) mma_commit(s.done, lead);
-            TS_TRACE(1, 10 + 2 * mb);
+            ts_kloop3(tmA + h * TS_HALF, desc_mnmajor(s0, 128, t.S_colW), desc_mnmajor(s1, 128, t.S_colW), desc_mnmajor(rr + po, TS_SPT, 128),
+                      desc_mnmajor(rr + t.h1_half + po, TS_SPT, 128), 256, 2 * TS_SPT, c2, instr_desc_f16(128, Nh, 1, 1), false, lead);
+            if (h == nh - 1) mma_commit(s.bempty, lead);
+            mma_commit(s.done + h, lead);
+        }
+        TS_TRACE(1, 6);
+        // dgrad1, feature block 0: gE[k,n] = W1p[j,k] gH1[j,n]      (gH1 hi, lo in place over H1 hi, lo)
+        for (int h = 0; h < nh; ++h) {
+            const int Nh = nh == 1 ? Nt : (h == 0 ? TS_HALF : Nt - TS_HALF);
+            const uint32_t po = (uint32_t)h * (TS_HALF / 8) * 128u;
+            ts_wait(s.ready + h, (h ? nready1++ : nready0++));
+            TS_TRACE(1, 7);
+            if (h == 0) {
+                ts_wait(s.bfull + 0, nbf);
+                ts_wait(s.bfull + 1, nbf);
+                ++nbf;
+            }
+            ts_kloop3(tmA + h * TS_HALF, desc_mnmajor(s0, 128, t.S_colW), desc_mnmajor(s1, 128, t.S_colW), desc_mnmajor(h1h + po, TS_SPT, 128),
+                      desc_mnmajor(h1l + po, TS_SPT, 128), 256, 2 * TS_SPT, c2, instr_desc_f16(128, Nh, 1, 1), false, lead);
+            if (h == nh - 1) mma_commit(s.bempty, lead);
+            mma_commit(s.done + h, lead);
+        }
+        for (int mb = 0; mb < t.MB; ++mb) {
+            for (int h = 0; h < nh; ++h) {
+                const int Nh = nh == 1 ? Nt : (h == 0 ? TS_HALF : Nt - TS_HALF);
+                const uint32_t po = (uint32_t)h * (TS_HALF / 8) * 128u;
+                ts_wait(s.ready + h, (h ? nready1++ : nready0++));          // block mb of gE consumed, E^T of block mb written (hi, lo)
+                TS_TRACE(1, 9 + 2 * mb);
+                if (want_wgrad)                             // wgrad1: dW1[j, block mb] += gH1[j,n] E[n, block mb]
+                    ts_kloop3(tmDW1 + mb * t.FB0, desc_kmajor(h1h + po, TS_SPT, 128), desc_kmajor(h1l + po, TS_SPT, 128),
+                              desc_kmajor(rr + h * (TS_HALF / 8) * t.S_ET, 128, t.S_ET),
+                              desc_kmajor(rr + t.et_half + h * (TS_HALF / 8) * t.S_ET, 128, t.S_ET), 256, 2 * t.S_ET, Nh / 16,
+                              instr_desc_f16(128, min(t.FB0, t.K1 - mb * t.FB0), 0, 0), acc || h > 0, lead);
+                if (mb + 1 < t.MB) {
+                    if (h == 0) {
+                        ts_wait(s.bfull + 0, nbf);
+                        ts_wait(s.bfull + 1, nbf);
+                        ++nbf;
+                    }
+                    ts_kloop3(tmA + h * TS_HALF, desc_mnmajor(s0, 128, t.S_colW), desc_mnmajor(s1, 128, t.S_colW),
+                              desc_mnmajor(h1h + po, TS_SPT, 128), desc_mnmajor(h1l + po, TS_SPT, 128), 256, 2 * TS_SPT, c2,
+                              instr_desc_f16(128, Nh, 1, 1), false, lead);
+                    if (h == nh - 1) mma_commit(s.bempty, lead);
+                }
+                if (want_wgrad || mb + 1 < t.MB) mma_commit(s.done + h, lead);
+                TS_TRACE(1, 10 + 2 * mb);
+            }
         }
     }
     }
@@ -765,8 +795,7 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
         for (int i = 0; i < TS_WST; ++i) { mbar_init(s.wfull + i, 1); mbar_init(s.wempty + i, 1); }
         for (int i = 0; i < 2; ++i) { mbar_init(s.efull + i, TS_WORKERS / 32); mbar_init(s.eempty + i, 1); mbar_init(s.bfull + i, 1); }
         mbar_init(s.bempty, 1);
-        mbar_init(s.ready, TS_WORKERS / 32);
-        mbar_init(s.done, 1);
+        for (int i = 0; i < 2; ++i) { mbar_init(s.ready + i, TS_WORKERS / 32); mbar_init(s.done + i, 1); }
         for (int i = 0; i < 2; ++i) { mbar_init(s.gfull + i, 1); mbar_init(s.gempty + i, TS_OPT_WARPS); mbar_init(s.pfull + i, 1); }
         fence_mbar_init();
     }
@@ -796,7 +825,7 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
     } else {
         asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(TS_REGS_WORKER));
         const uint32_t tA = tm_lane + TS_TM_A;
-        uint32_t ndone = 0, ec = 0;
+        uint32_t ndone0 = 0, ndone1 = 0, ec = 0;
         int it = 0;
         float *u0s = s.in0, *u1s = s.in0 + TS_NT, *ths = s.in0 + 2 * TS_NT;
         const int n_slots = (K1 + TS_EF - 1) / TS_EF;
@@ -937,124 +966,140 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
                     }
                 }
                 TS_TRACE(0, 3);
+                // From here on the tile is two halves (points 0..63 | 64..Nt-1) with their own done / ready barriers: a warp owns
+                // ONE 16-point chunk per half (chunk 4 h + cq), and the epilogue of one half runs under the MMAs of the other.
+                const int nh = (want_bwd && Nt > TS_HALF) ? 2 : 1;
+                // chunks of half h for this warp: 4 h + cq (two halves) or cq, cq + 4 (one)
+    #define TS_HALF_CHUNKS(ch) for (int ch = 4 * h + cq, ch##_end = (nh == 2 && h == 0) ? 4 : nch; ch < ch##_end; ch += 4)
                 // ---- P2: epilogue 1: bias + ReLU -> H1 operand (hi, lo); row H = skip term of the logit ----
-                ts_wait(s.done, ndone++);
-                TS_TRACE(0, 4);
-                for (int ch = cq; ch < nch; ch += 4) {
-                    const int c0 = 16 * ch;
-                    float v[16];
-                    tmem_ld16(tA + c0, v);
-                    if (row < H) {
+    #pragma unroll 1
+                for (int h = 0; h < nh; ++h) {
+                    ts_wait(s.done + h, (h ? ndone1++ : ndone0++));
+                    TS_TRACE(0, 4);
+                    TS_HALF_CHUNKS(ch) {
+                        const int c0 = 16 * ch;
+                        float v[16];
+                        tmem_ld16(tA + c0, v);
+                        if (row < H) {
     #pragma unroll
-                        for (int i = 0; i < 16; ++i) v[i] = fminf(fmaxf(v[i] + my_b1, 0.f), 60000.f);
-                    } else {
-                        if (row == H) {
+                            for (int i = 0; i < 16; ++i) v[i] = fminf(fmaxf(v[i] + my_b1, 0.f), 60000.f);
+                        } else {
+                            if (row == H) {
     #pragma unroll
-                            for (int i = 0; i < 16; ++i) s.skip[c0 + i] = v[i];
+                                for (int i = 0; i < 16; ++i) s.skip[c0 + i] = v[i];
+                            }
+    #pragma unroll
+                            for (int i = 0; i < 16; ++i) v[i] = 0.f;
                         }
-    #pragma unroll
-                        for (int i = 0; i < 16; ++i) v[i] = 0.f;
+                        if (row < KH) ts_store_row16(s.h1h, s.h1l, row, c0, v);
                     }
-                    if (row < KH) ts_store_row16(s.h1h, s.h1l, row, c0, v);
+                    ts_signal(s.ready + h);                   // -> fwd2 of this half
                 }
-                ts_signal(s.ready);                           // -> fwd2
                 TS_TRACE(0, 5);
-                // ---- P3: epilogue 2, first pass: logit partial sums over the hidden units of each lane quarter ----
-                ts_wait(s.done, ndone++);
-                TS_TRACE(0, 6);
-                for (int ch = cq; ch < nch; ch += 4) {
-                    const int c0 = 16 * ch;
-                    float pz[16];
-                    tmem_ld16(tA + c0, pz);
+                // ---- P3 / P4: epilogue 2: logit partial sums over the hidden units of each lane quarter, z and dL/dz per
+                // point, then gH2 = dL/dz * w3 * 1[h2 > 0] (scaled, fp16 hi + lo) -> old encoding ring ----
+    #pragma unroll 1
+                for (int h = 0; h < nh; ++h) {
+                    ts_wait(s.done + h, (h ? ndone1++ : ndone0++));
+                    TS_TRACE(0, 6);
+                    TS_HALF_CHUNKS(ch) {
+                        const int c0 = 16 * ch;
+                        float pz[16];
+                        tmem_ld16(tA + c0, pz);
     #pragma unroll
-                    for (int i = 0; i < 16; ++i) pz[i] = row < H ? my_w3 * fmaxf(pz[i] + my_b2, 0.f) : 0.f;
-                    const float zs = ts_colsum16(pz, lane);
-                    if ((lane & 1) == 0) s.zp[q * TS_NT + c0 + (lane >> 1)] = zs;
-                }
-                ts_worker_sync();
-                TS_TRACE(0, 7);
-                if (tid < TS_NT) {
-                    const int n = tid;
-                    float gb = 0.f;
-                    if (n < nv) {
-                        const float z = s.zp[n] + s.zp[TS_NT + n] + s.zp[2 * TS_NT + n] + s.zp[3 * TS_NT + n] + s.skip[n] + s.scal[0];
-                        const size_t gi = (size_t)p * a.n + n0 + n;
-                        if (a.z_out) a.z_out[gi] = z;
-                        if (want_bwd) {                                 // dL/dz
-                            const float ax = s.aux[n];
-                            if (a.gbar_mode == 0) gb = ax;
-                            else if (a.gbar_mode == 1) gb = (sigmoid_f(z) - ax) / (float)cnt;
-                            else {
-                                const float zb = z * a.beta;
-                                const float ez = expf(zb);
-                                gb = a.wc * (zb > 20.f ? 1.f : ez / (ez + 1.f));
-                                if (a.gbar_mode == 3) {
-                                    const float tz = tanhf(z);
-                                    gb += ax * (1.f - tz * tz);
+                        for (int i = 0; i < 16; ++i) pz[i] = row < H ? my_w3 * fmaxf(pz[i] + my_b2, 0.f) : 0.f;
+                        const float zs = ts_colsum16(pz, lane);
+                        if ((lane & 1) == 0) s.zp[q * TS_NT + c0 + (lane >> 1)] = zs;
+                    }
+                    ts_worker_sync();
+                    TS_TRACE(0, 7);
+                    if (tid >= h * TS_HALF && tid < ((nh == 2 && h == 0) ? TS_HALF : Nt)) {
+                        const int n = tid;
+                        float gb = 0.f;
+                        if (n < nv) {
+                            const float z = s.zp[n] + s.zp[TS_NT + n] + s.zp[2 * TS_NT + n] + s.zp[3 * TS_NT + n] + s.skip[n] + s.scal[0];
+                            const size_t gi = (size_t)p * a.n + n0 + n;
+                            if (a.z_out) a.z_out[gi] = z;
+                            if (want_bwd) {                                 // dL/dz
+                                const float ax = s.aux[n];
+                                if (a.gbar_mode == 0) gb = ax;
+                                else if (a.gbar_mode == 1) gb = (sigmoid_f(z) - ax) / (float)cnt;
+                                else {
+                                    const float zb = z * a.beta;
+                                    const float ez = expf(zb);
+                                    gb = a.wc * (zb > 20.f ? 1.f : ez / (ez + 1.f));
+                                    if (a.gbar_mode == 3) {
+                                        const float tz = tanhf(z);
+                                        gb += ax * (1.f - tz * tz);
+                                    }
                                 }
                             }
                         }
+                        s.gbar[n] = gb;
+                        acc_db3 += gb;
                     }
-                    s.gbar[n] = gb;
-                    acc_db3 += gb;
-                }
-                ts_worker_sync();
-                TS_TRACE(0, 8);
-                if (!want_bwd) continue;
-                // ---- P4: epilogue 2, second pass: gH2 = dL/dz * w3 * 1[h2 > 0] (scaled, fp16 hi + lo) -> old encoding ring ----
-                for (int ch = cq; ch < nch; ch += 4) {
-                    const int c0 = 16 * ch;
-                    float r2[16], v[16];
-                    tmem_ld16(tA + c0, r2);
-    #pragma unroll
-                    for (int i = 0; i < 16; ++i) {
-                        const float h2 = row < H ? fmaxf(r2[i] + my_b2, 0.f) : 0.f;
-                        const float gb = s.gbar[c0 + i];
-                        acc_dw3 = fmaf(gb, h2, acc_dw3);
-                        const float gg = h2 > 0.f ? gb * my_w3 : 0.f;
-                        acc_db2 += gg;
-                        v[i] = gg * S;
-                    }
-                    if (row < KH) ts_store_row16(s.r, s.r + t.h1_half, row, c0, v);
-                }
-                ts_signal(s.ready);                           // -> wgrad2 + dgrad2
-                TS_TRACE(0, 9);
-                // ---- P5: epilogue 3: ReLU mask of layer 1 -> gH1 operand (in place over H1 hi, lo); row H := dL/dz ----
-                ts_wait(s.done, ndone++);
-                TS_TRACE(0, 10);
-                for (int ch = cq; ch < nch; ch += 4) {
-                    const int c0 = 16 * ch;
-                    float v[16];
-                    tmem_ld16(tA + c0, v);
-                    if (row < H) {
-                        const int off = (row >> 3) * TS_SPT + (c0 >> 3) * 128 + (row & 7) * 16;
-                        const uint4 m0 = *reinterpret_cast<const uint4 *>(s.h1h + off);
-                        const uint4 m1 = *reinterpret_cast<const uint4 *>(s.h1h + off + 128);
-                        const uint32_t mw[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
-                        float sum = 0.f;
+                    if (!want_bwd) continue;
+                    ts_worker_sync();
+                    TS_TRACE(0, 8);
+                    TS_HALF_CHUNKS(ch) {
+                        const int c0 = 16 * ch;
+                        float r2[16], v[16];
+                        tmem_ld16(tA + c0, r2);
     #pragma unroll
                         for (int i = 0; i < 16; ++i) {
-                            const uint32_t bits = (mw[i >> 1] >> ((i & 1) * 16)) & 0x7FFFu;
-                            v[i] = bits != 0 ? fminf(fmaxf(v[i], -60000.f), 60000.f) : 0.f;
-                            sum += v[i];
+                            const float h2 = row < H ? fmaxf(r2[i] + my_b2, 0.f) : 0.f;
+                            const float gb = s.gbar[c0 + i];
+                            acc_dw3 = fmaf(gb, h2, acc_dw3);
+                            const float gg = h2 > 0.f ? gb * my_w3 : 0.f;
+                            acc_db2 += gg;
+                            v[i] = gg * S;
                         }
-                        acc_db1 = fmaf(sum, invS, acc_db1);
-                    } else if (row == H) {
-    #pragma unroll
-                        for (int i = 0; i < 16; ++i) v[i] = s.gbar[c0 + i] * S;
-                    } else {
-    #pragma unroll
-                        for (int i = 0; i < 16; ++i) v[i] = 0.f;
+                        if (row < KH) ts_store_row16(s.r, s.r + t.h1_half, row, c0, v);
                     }
-                    if (row < KH) ts_store_row16(s.h1h, s.h1l, row, c0, v);
+                    ts_signal(s.ready + h);                   // -> wgrad2 + dgrad2 of this half
                 }
-                ts_signal(s.ready);                           // -> dgrad1 (block 0)
+                if (!want_bwd) {
+                    ts_worker_sync();                         // zp / skip / inputs are rewritten by the next tile
+                    continue;
+                }
+                TS_TRACE(0, 9);
+                // ---- P5: epilogue 3: ReLU mask of layer 1 -> gH1 operand (in place over H1 hi, lo); row H := dL/dz ----
+    #pragma unroll 1
+                for (int h = 0; h < nh; ++h) {
+                    ts_wait(s.done + h, (h ? ndone1++ : ndone0++));
+                    TS_TRACE(0, 10);
+                    TS_HALF_CHUNKS(ch) {
+                        const int c0 = 16 * ch;
+                        float v[16];
+                        tmem_ld16(tA + c0, v);
+                        if (row < H) {
+                            const int off = (row >> 3) * TS_SPT + (c0 >> 3) * 128 + (row & 7) * 16;
+                            const uint4 m0 = *reinterpret_cast<const uint4 *>(s.h1h + off);
+                            const uint4 m1 = *reinterpret_cast<const uint4 *>(s.h1h + off + 128);
+                            const uint32_t mw[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+                            float sum = 0.f;
+    #pragma unroll
+                            for (int i = 0; i < 16; ++i) {
+                                const uint32_t bits = (mw[i >> 1] >> ((i & 1) * 16)) & 0x7FFFu;
+                                v[i] = bits != 0 ? fminf(fmaxf(v[i], -60000.f), 60000.f) : 0.f;
+                                sum += v[i];
+                            }
+                            acc_db1 = fmaf(sum, invS, acc_db1);
+                        } else if (row == H) {
+    #pragma unroll
+                            for (int i = 0; i < 16; ++i) v[i] = s.gbar[c0 + i] * S;
+                        } else {
+    #pragma unroll
+                            for (int i = 0; i < 16; ++i) v[i] = 0.f;
+                        }
+                        if (row < KH) ts_store_row16(s.h1h, s.h1l, row, c0, v);
+                    }
+                    ts_signal(s.ready + h);                   // -> dgrad1 (block 0) of this half
+                }
                 TS_TRACE(0, 11);
                 // ---- P6: epilogue 4 per feature block: encoding backward (+ input gradient), E^T operand (hi, lo), wgrad1 ----
     #pragma unroll 1
                 for (int mb = 0; mb < t.MB; ++mb) {
-                    ts_wait(s.done, ndone++);                 // gE of block mb (and wgrad1 of block mb - 1: E^T is free again)
-                    TS_TRACE(0, 12 + 2 * mb);
                     const int fb = mb * t.FB0;
                     const int pf = min(t.FB0, K1 - fb);       // features of this block that are MMA rows
                     const int f = fb + row;
@@ -1065,48 +1110,54 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
                                 eaf = (f_on && !fourier && f < FIN) ? ppb : 0.f;
                     const float *x1src = fourier ? u1s : ths;
                     float ta = 0.f, tb = 0.f, tc = 0.f;      // sum gp*u0, sum gp*x1, sum gp  (all still scaled by S)
-                    for (int ch = cq; ch < nch; ch += 4) {
-                        const int c0 = 16 * ch;
-                        float v[16], ev[16], xu[16], x1[16];
-                        tmem_ld16(tA + c0, v);
+    #pragma unroll 1
+                    for (int h = 0; h < nh; ++h) {
+                        ts_wait(s.done + h, (h ? ndone1++ : ndone0++));      // gE of block mb (and wgrad1 of block mb - 1: E^T is free again)
+                        TS_TRACE(0, 12 + 2 * mb);
+                        TS_HALF_CHUNKS(ch) {
+                            const int c0 = 16 * ch;
+                            float v[16], ev[16], xu[16], x1[16];
+                            tmem_ld16(tA + c0, v);
     #pragma unroll
-                        for (int i4 = 0; i4 < 4; ++i4) {
-                            *reinterpret_cast<float4 *>(xu + 4 * i4) = *reinterpret_cast<const float4 *>(u0s + c0 + 4 * i4);
-                            *reinterpret_cast<float4 *>(x1 + 4 * i4) = *reinterpret_cast<const float4 *>(x1src + c0 + 4 * i4);
-                        }
+                            for (int i4 = 0; i4 < 4; ++i4) {
+                                *reinterpret_cast<float4 *>(xu + 4 * i4) = *reinterpret_cast<const float4 *>(u0s + c0 + 4 * i4);
+                                *reinterpret_cast<float4 *>(x1 + 4 * i4) = *reinterpret_cast<const float4 *>(x1src + c0 + 4 * i4);
+                            }
     #pragma unroll
-                        for (int i = 0; i < 16; ++i) {
-                            const float arg = fmaf(x1[i], ppb, fmaf(xu[i], ppa, ppc));
-                            const float gp = (f_on ? v[i] : 0.f) * __cosf(arg);      // rows beyond the block hold garbage
-                            ev[i] = __sinf(arg);                                       // (= 0 there: pa = pb = pc = 0)
-                            v[i] = gp;
-                            ta = fmaf(gp, xu[i], ta);
-                            tb = fmaf(gp, x1[i], tb);
-                            tc += gp;
-                        }
-                        if (want_gx) {
-                            // gx[n] = (sum_f gp[f,n] * We[f,c]) / sigma ; g_theta[n] = sum_k gp[k,n] * f_k   (reduce over lanes)
-                            float cv[16];
-                            float *dst = s.gxp + ((size_t)q * TS_NT + c0 + (lane >> 1)) * 3;
+                            for (int i = 0; i < 16; ++i) {
+                                const float arg = fmaf(x1[i], ppb, fmaf(xu[i], ppa, ppc));
+                                const float gp = (f_on ? v[i] : 0.f) * __cosf(arg);      // rows beyond the block hold garbage
+                                ev[i] = __sinf(arg);                                       // (= 0 there: pa = pb = pc = 0)
+                                v[i] = gp;
+                                ta = fmaf(gp, xu[i], ta);
+                                tb = fmaf(gp, x1[i], tb);
+                                tc += gp;
+                            }
+                            if (want_gx) {
+                                // gx[n] = (sum_f gp[f,n] * We[f,c]) / sigma ; g_theta[n] = sum_k gp[k,n] * f_k   (reduce over lanes)
+                                float cv[16];
+                                float *dst = s.gxp + ((size_t)q * TS_NT + c0 + (lane >> 1)) * 3;
     #pragma unroll
-                            for (int c = 0; c < 3; ++c) {
-                                const float wgt = c == 0 ? ew0 : c == 1 ? ew1 : eaf;
+                                for (int c = 0; c < 3; ++c) {
+                                    const float wgt = c == 0 ? ew0 : c == 1 ? ew1 : eaf;
     #pragma unroll
-                                for (int i = 0; i < 16; ++i) cv[i] = v[i] * wgt;
-                                const float sum = ts_colsum16(cv, lane);
-                                if ((lane & 1) == 0) dst[c] = mb == 0 ? sum : dst[c] + sum;
+                                    for (int i = 0; i < 16; ++i) cv[i] = v[i] * wgt;
+                                    const float sum = ts_colsum16(cv, lane);
+                                    if ((lane & 1) == 0) dst[c] = mb == 0 ? sum : dst[c] + sum;
+                                }
+                            }
+                            if (want_wgrad && row < t.FB0) {     // E^T operand [point / 8][feature][8 points], hi and lo
+    #pragma unroll
+                                for (int o = 0; o < 2; ++o) {
+                                    const int off = ((c0 >> 3) + o) * t.S_ET + (row >> 3) * 128 + (row & 7) * 16;
+                                    uint4 eh, el;
+                                    split8h(ev + 8 * o, eh, el);
+                                    *reinterpret_cast<uint4 *>(s.r + off) = eh;
+                                    *reinterpret_cast<uint4 *>(s.r + t.et_half + off) = el;
+                                }
                             }
                         }
-                        if (want_wgrad && row < t.FB0) {     // E^T operand [point / 8][feature][8 points], hi and lo
-    #pragma unroll
-                            for (int o = 0; o < 2; ++o) {
-                                const int off = ((c0 >> 3) + o) * t.S_ET + (row >> 3) * 128 + (row & 7) * 16;
-                                uint4 eh, el;
-                                split8h(ev + 8 * o, eh, el);
-                                *reinterpret_cast<uint4 *>(s.r + off) = eh;
-                                *reinterpret_cast<uint4 *>(s.r + t.et_half + off) = el;
-                            }
-                        }
+                        ts_signal(s.ready + h);               // -> wgrad1(mb), dgrad1(mb + 1) of this half
                     }
                     ta *= invS; tb *= invS; tc *= invS;
                     if (f_on && !fourier) {                   // heading features: d ang_b = f_k * sum gp,
@@ -1116,7 +1167,6 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
                     }
                     if (mb == 0) { fa0 += ta; fb0 += tb; fc0 += tc; }
                     else { fa1 += ta; fb1 += tb; fc1 += tc; }
-                    ts_signal(s.ready);                       // -> wgrad1(mb), dgrad1(mb + 1)
                     TS_TRACE(0, 13 + 2 * mb);
                 }
                 if (want_gx) {
@@ -1136,7 +1186,8 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
                         for (int c = L.in_dim; c < a.x_stride; ++c) out[c] = 0.f;   // pose columns the ONF does not read
                     }
                 }
-                if (want_wgrad) ts_wait(s.done, ndone++);     // the last wgrad1: E^T (= the encoding ring) and gH1 are free again
+                if (want_wgrad)                               // the last wgrad1: E^T (= the encoding ring) and gH1 are free again
+                    for (int h = 0; h < nh; ++h) ts_wait(s.done + h, (h ? ndone1++ : ndone0++));
                 TS_TRACE(0, 16);
                 ts_worker_sync();                             // zp, gx, skip, gbar, inputs are rewritten by the next tile
             }

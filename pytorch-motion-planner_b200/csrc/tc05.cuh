@@ -70,6 +70,20 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
     }
 }
 
+// Pure polling (no suspend hint): for the latency-critical handshakes between the MMA-issue warp and the epilogue warps -
+// the waiter is back one poll after the phase completes
+__device__ __forceinline__ void mbar_wait_spin(uint64_t *bar, uint32_t parity) {
+    uint32_t spins = 0;
+    long long t0 = 0;
+    while (!mbar_try_wait(bar, parity)) {
+        if ((++spins & 4095u) == 0) {
+            const long long now = clock64();
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > 4000000000LL) __trap();
+        }
+    }
+}
+
 // The same for waits that are long and not latency-critical (a whole problem's tiles, the optimiser's pass): the warp backs off with
 // nanosleep between polls instead of competing with the working warps for issue slots (ncu, persistent streamed kernel: the
 // polling loops were 17 % of all executed instructions)
