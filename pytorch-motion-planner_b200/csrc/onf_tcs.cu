@@ -60,9 +60,11 @@ __device__ long long g_ts_trace[3][2][4][64];   // [launch kind: fwd | train | p
             g_ts_trace[!a.want_bwd ? 0 : ((a.grad_out || a.adam_w) ? 1 : 2)][blockIdx.x == 0 ? 0 : 1][(role)][(slot)] = (val); \
     } while (0)
 #define TS_CLOCK() clock64()
+#define TS_TWAIT(acc, stmt) do { const long long _t0 = clock64(); stmt; (acc) += clock64() - _t0; } while (0)
 #else
 #define TS_TRACE_VAL(role, slot, val) do { } while (0)
 #define TS_CLOCK() 0LL
+#define TS_TWAIT(acc, stmt) do { stmt; } while (0)
 #endif
 
 // device-side bounds asserts (make -C csrc debug; compute-sanitizer is closed on the GPU pool): a violated extent traps with
@@ -282,7 +284,9 @@ struct TsShared {
 };
 
 // K loop of a three-pass split product, descriptors advanced by constant strides:
-// D (+)= sum_k Ahi*Bhi + Alo*Bhi + Ahi*Blo
+// D (+)= sum_k Ahi*Bhi + Alo*Bhi + Ahi*Blo.  (Unrolling it with descriptors formed as base + ks * stride was measured: no
+// gain in the issue warp's ~65 cycles per tcgen05.mma - uniform-datapath latency, not instruction count - and the larger
+// code cost 3 %.)
 __device__ __forceinline__ void ts_kloop3(uint32_t tmem_d, uint64_t ah, uint64_t al, uint64_t bh, uint64_t bl, uint32_t a_step,
                                           uint32_t b_step, int ksteps, uint32_t idesc, bool accumulate, uint32_t issue) {
     const uint64_t da = a_step >> 4, db = b_step >> 4;
@@ -429,6 +433,7 @@ __device__ __forceinline__ void ts_issuer(const OnfTsArgs &a, const TsShared &s,
     const int n_slots = (t.K1 + TS_EF - 1) / TS_EF;
     uint32_t wc = 0, ec = 0, nbf = 0;
     uint32_t nready0 = 0, nready1 = 0;
+    long long t_ef = 0, t_wf = 0, t_bf = 0, t_rd = 0, t_tile0 = 0;
     for (int p = blockIdx.x; p < a.P; p += gridDim.x) {
     const int cnt = a.count ? a.count[p] : a.n;
     if (cnt <= 0) continue;
@@ -438,6 +443,8 @@ __device__ __forceinline__ void ts_issuer(const OnfTsArgs &a, const TsShared &s,
         TS_ASSERT(Nt >= 16 && Nt <= TS_NT && (int)TS_TM_DW1 + t.K1 <= 512 && (int)TS_TM_DW2 + t.KH <= (int)TS_TM_DW1);
         TS_ASSERT(t.off_r + 2 * t.et_half <= t.off_w && t.off_r + 4 * t.e_half <= t.off_w && 2 * t.h1_half <= t.off_r);
         const bool acc = tile > 0;                                   // weight-gradient accumulators persist across tiles
+        t_ef = t_wf = t_bf = t_rd = 0;
+        t_tile0 = TS_CLOCK();
         // From the first epilogue on the tile is handled as two HALVES (points 0..63 | 64..Nt-1) with their own ready / done
         // barriers: the epilogue of one half runs under the MMAs of the other (same operand buffers and the same work
         // accumulator - the halves are disjoint point columns of both).
@@ -445,12 +452,12 @@ __device__ __forceinline__ void ts_issuer(const OnfTsArgs &a, const TsShared &s,
         // fwd1: D1[j,n] (+)= W1p[j,k] E[n,k]: one encoding slot (64 features) = up to 4 ring stages of K = 16
         for (int sl = 0; sl < n_slots; ++sl, ++ec) {
             const uint32_t es = ec & 1u;
-            ts_wait(s.efull + es, ec >> 1);
+            TS_TWAIT(t_ef, ts_wait(s.efull + es, ec >> 1));
             const uint32_t eb = rr + es * 2 * t.e_half;
             const int ksl = min(TS_EF, t.K1 - sl * TS_EF) / 16;
             for (int ks = 0; ks < ksl; ++ks, ++wc) {
                 const uint32_t st = wc % TS_WST;
-                ts_wait(s.wfull + st, wc / TS_WST);
+                TS_TWAIT(t_wf, ts_wait(s.wfull + st, wc / TS_WST));
                 const uint32_t wb = ww + st * t.w_stage;
                 const uint32_t idesc = instr_desc_f16(128, Nt, 0, 0);
                 const bool first = sl == 0 && ks == 0;
@@ -464,11 +471,11 @@ __device__ __forceinline__ void ts_issuer(const OnfTsArgs &a, const TsShared &s,
         for (int h = 0; h < nh; ++h) mma_commit(s.done + h, lead);
         TS_TRACE(1, 1);
         // fwd2: D2[i,n] = W2p[i,j] H1[j,n]      (both halves at once: its weights stream through the ring behind fwd1's)
-        for (int h = 0; h < nh; ++h) ts_wait(s.ready + h, (h ? nready1++ : nready0++));
+        for (int h = 0; h < nh; ++h) TS_TWAIT(t_rd, ts_wait(s.ready + h, (h ? nready1++ : nready0++)));
         TS_TRACE(1, 2);
         for (int ks = 0; ks < c2; ++ks, ++wc) {
             const uint32_t st = wc % TS_WST;
-            ts_wait(s.wfull + st, wc / TS_WST);
+            TS_TWAIT(t_wf, ts_wait(s.wfull + st, wc / TS_WST));
             const uint32_t wb = ww + st * t.w_stage;
             ts_kloop3(tmA, desc_kmajor(wb, 128, t.S_colW), desc_kmajor(wb + 2 * t.S_colW, 128, t.S_colW),
                       desc_mnmajor(h1h + ks * 2 * TS_SPT, TS_SPT, 128), desc_mnmajor(h1l + ks * 2 * TS_SPT, TS_SPT, 128), 0, 0, 1,
@@ -482,15 +489,15 @@ __device__ __forceinline__ void ts_issuer(const OnfTsArgs &a, const TsShared &s,
         for (int h = 0; h < nh; ++h) {
             const int Nh = nh == 1 ? Nt : (h == 0 ? TS_HALF : Nt - TS_HALF);
             const uint32_t po = (uint32_t)h * (TS_HALF / 8) * 128u;
-            ts_wait(s.ready + h, (h ? nready1++ : nready0++));
+            TS_TWAIT(t_rd, ts_wait(s.ready + h, (h ? nready1++ : nready0++)));
             TS_TRACE(1, 4);
             if (want_wgrad)
                 ts_kloop3(tmDW2, desc_kmajor(rr + po, TS_SPT, 128), desc_kmajor(rr + t.h1_half + po, TS_SPT, 128),
                           desc_kmajor(h1h + po, TS_SPT, 128), desc_kmajor(h1l + po, TS_SPT, 128), 256, 256, Nh / 16,
                           instr_desc_f16(128, t.KH, 0, 0), acc || h > 0, lead);
             if (h == 0) {
-                ts_wait(s.bfull + 0, nbf);
-                ts_wait(s.bfull + 1, nbf);
+                TS_TWAIT(t_bf, ts_wait(s.bfull + 0, nbf));
+                TS_TWAIT(t_bf, ts_wait(s.bfull + 1, nbf));
                 ++nbf;
             }
             ts_kloop3(tmA + h * TS_HALF, desc_mnmajor(s0, 128, t.S_colW), desc_mnmajor(s1, 128, t.S_colW), desc_mnmajor(rr + po, TS_SPT, 128),
@@ -503,11 +510,11 @@ __device__ __forceinline__ void ts_issuer(const OnfTsArgs &a, const TsShared &s,
         for (int h = 0; h < nh; ++h) {
             const int Nh = nh == 1 ? Nt : (h == 0 ? TS_HALF : Nt - TS_HALF);
             const uint32_t po = (uint32_t)h * (TS_HALF / 8) * 128u;
-            ts_wait(s.ready + h, (h ? nready1++ : nready0++));
+            TS_TWAIT(t_rd, ts_wait(s.ready + h, (h ? nready1++ : nready0++)));
             TS_TRACE(1, 7);
             if (h == 0) {
-                ts_wait(s.bfull + 0, nbf);
-                ts_wait(s.bfull + 1, nbf);
+                TS_TWAIT(t_bf, ts_wait(s.bfull + 0, nbf));
+                TS_TWAIT(t_bf, ts_wait(s.bfull + 1, nbf));
                 ++nbf;
             }
             ts_kloop3(tmA + h * TS_HALF, desc_mnmajor(s0, 128, t.S_colW), desc_mnmajor(s1, 128, t.S_colW), desc_mnmajor(h1h + po, TS_SPT, 128),
@@ -519,7 +526,7 @@ __device__ __forceinline__ void ts_issuer(const OnfTsArgs &a, const TsShared &s,
             for (int h = 0; h < nh; ++h) {
                 const int Nh = nh == 1 ? Nt : (h == 0 ? TS_HALF : Nt - TS_HALF);
                 const uint32_t po = (uint32_t)h * (TS_HALF / 8) * 128u;
-                ts_wait(s.ready + h, (h ? nready1++ : nready0++));          // block mb of gE consumed, E^T of block mb written (hi, lo)
+                TS_TWAIT(t_rd, ts_wait(s.ready + h, (h ? nready1++ : nready0++)));          // block mb of gE consumed, E^T of block mb written (hi, lo)
                 TS_TRACE(1, 9 + 2 * mb);
                 if (want_wgrad)                             // wgrad1: dW1[j, block mb] += gH1[j,n] E[n, block mb]
                     ts_kloop3(tmDW1 + mb * t.FB0, desc_kmajor(h1h + po, TS_SPT, 128), desc_kmajor(h1l + po, TS_SPT, 128),
@@ -528,8 +535,8 @@ __device__ __forceinline__ void ts_issuer(const OnfTsArgs &a, const TsShared &s,
                               instr_desc_f16(128, min(t.FB0, t.K1 - mb * t.FB0), 0, 0), acc || h > 0, lead);
                 if (mb + 1 < t.MB) {
                     if (h == 0) {
-                        ts_wait(s.bfull + 0, nbf);
-                        ts_wait(s.bfull + 1, nbf);
+                        TS_TWAIT(t_bf, ts_wait(s.bfull + 0, nbf));
+                        TS_TWAIT(t_bf, ts_wait(s.bfull + 1, nbf));
                         ++nbf;
                     }
                     ts_kloop3(tmA + h * TS_HALF, desc_mnmajor(s0, 128, t.S_colW), desc_mnmajor(s1, 128, t.S_colW),
@@ -541,6 +548,8 @@ __device__ __forceinline__ void ts_issuer(const OnfTsArgs &a, const TsShared &s,
                 TS_TRACE(1, 10 + 2 * mb);
             }
         }
+        TS_TRACE_VAL(1, 40, t_ef); TS_TRACE_VAL(1, 41, t_wf); TS_TRACE_VAL(1, 42, t_bf); TS_TRACE_VAL(1, 43, t_rd);
+        TS_TRACE_VAL(1, 44, TS_CLOCK() - t_tile0);
     }
     }
 }

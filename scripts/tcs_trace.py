@@ -61,6 +61,9 @@ def main():
                     parts.append(f"{names[k]} @{v - t0} (+{v - prev})")
                     prev = v
                 print(f"  {['worker', 'issuer', 'producer', 'optimiser'][role]:9s}: " + " | ".join(parts))
+            if t[1, 44]:
+                print(f"  issuer, last tile (cycles): {t[1, 44]} of which waiting for the encoding {t[1, 40]}, the weight ring {t[1, 41]}, "
+                      f"weight blocks {t[1, 42]}, the epilogue warps {t[1, 43]}")
             if t[3, 3] or t[3, 4]:
                 print(f"  optimiser, last problem (cycles): waiting for chunks {t[3, 3]}, arithmetic + stores {t[3, 4]}")
 
