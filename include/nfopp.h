@@ -101,6 +101,21 @@ int nfopp_onf_forward(const nfopp_onf_config *cfg, const float *weights_dev, con
                       const int32_t *count_dev, int P, int n, float *z_dev, int impl, void *scratch_dev,
                       void *stream);
 
+/* nfopp_onf_forward on the streamed tensor path WITHOUT scratch_dev and without any allocation.  NO COUNTERPART IN THE
+ * REFERENCE: added for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it).  The fp16 hi/lo operand copy of the hidden-layer weights lives
+ * in one static device array of NFOPP_STATIC_SCRATCH_BYTES inside the library (every GPU that loads the library holds it
+ * until exit); the entry point calls no cudaMalloc / cudaFree / allocating routine.  Limits and rules:
+ *   - network shapes of the streamed tensor path only (2 hidden layers, hidden <= 111, f_in <= 256), forward only;
+ *   - P * (operand copy per weight set) <= NFOPP_STATIC_SCRATCH_BYTES, else NFOPP_ERR_INVALID with a message naming the limit
+ *     (reference network, 150 528 bytes per weight set: P <= 27); n is unlimited;
+ *   - every call shares the array, which keeps the last call's contents; each call rewrites every byte it reads, so nothing
+ *     is cleared; calls that overlap on the GPU (other streams / threads) RACE on it - serialise them on one stream;
+ *   - works on the current device; results are bit-identical to nfopp_onf_forward(impl = 2). */
+#define NFOPP_STATIC_SCRATCH_BYTES (4 * 1024 * 1024)
+int nfopp_onf_forward_static(const nfopp_onf_config *cfg, const float *weights_dev, const float *x_dev,
+                             const int32_t *count_dev, int P, int n, float *z_dev, void *stream);
+
 /* gbar_mode selects dL/dz:
  *   0 external : gz_dev [P,n] given (what autograd hands ONF.backward)
  *   1 bce      : (sigmoid(z) - y)/count, y = aux_dev [P,n]           nerf_opt_planner.py:25,85-89

@@ -55,6 +55,7 @@ SIGNATURES = {
     "nfopp_onf_scratch_bytes": (_I, [C.POINTER(OnfConfig), _I, _I, C.POINTER(C.c_size_t)]),
     "nfopp_onf_scratch_bytes_n": (_I, [C.POINTER(OnfConfig), _I, _I, _I, _I, C.POINTER(C.c_size_t)]),
     "nfopp_onf_forward": (_I, [C.POINTER(OnfConfig), _P, _P, _P, _I, _I, _P, _I, _P, _P]),
+    "nfopp_onf_forward_static": (_I, [C.POINTER(OnfConfig), _P, _P, _P, _I, _I, _P, _P]),
     "nfopp_onf_tiles": (_I, [C.POINTER(OnfConfig), _I, _I]),
     "nfopp_onf_backward": (_I, [C.POINTER(OnfConfig), _P, _P, _P, _I, _I, _I, _P, _P, C.c_float, C.c_float, _P, _P,
                                 _P, _I, _P, _P]),
