@@ -260,6 +260,12 @@ struct nfopp_engine {
     int launches_per_step, launches_per_step_1;     // with the current lane count / with one lane
     cudaGraph_t graph;
     cudaGraphExec_t graph_exec;
+    // wide path with optimize_collision_model_freq > 1: its ONF launches cannot be switched off by a device-side flag (dozens of
+    // kernels), so steps that do not train replay a second graph captured WITHOUT the candidates-forward and train launches;
+    // the host mirrors the step counter (host_sp) and picks the graph
+    cudaGraph_t graph_skip;
+    cudaGraphExec_t graph_exec_skip;
+    int launches_per_step_skip;
     int warm_iterations_done;
     // lanes: the problems of a graphed step split into contiguous ranges, each enqueued on its own stream inside the one
     // CUDA graph (fork / join): independent problems have no cross-lane dependency, so the latency-bound small kernels and
@@ -269,6 +275,13 @@ struct nfopp_engine {
     std::vector<cudaEvent_t> lane_events;     // [0] fork, [l] join of lane l
     size_t lane_ws_stride;                    // wide path: bytes between the lanes' activation workspaces
 };
+
+static void drop_graphs(nfopp_engine *e) {
+    if (e->graph_exec) { cudaGraphExecDestroy(e->graph_exec); e->graph_exec = nullptr; }
+    if (e->graph) { cudaGraphDestroy(e->graph); e->graph = nullptr; }
+    if (e->graph_exec_skip) { cudaGraphExecDestroy(e->graph_exec_skip); e->graph_exec_skip = nullptr; }
+    if (e->graph_skip) { cudaGraphDestroy(e->graph_skip); e->graph_skip = nullptr; }
+}
 
 static void host_step_params(nfopp_engine *e) {
     StepParams &sp = e->host_sp;
@@ -296,8 +309,10 @@ static void add_buffer(nfopp_engine *e, const char *name, T **slot, char dtype, 
 }
 
 // kernel launches of one step over P problems (incl. the counter tick)
-static int step_launches(const nfopp_engine *e, int P) {
+static int step_launches(const nfopp_engine *e, int P, bool train = true) {
     if (e->impl != 3) return e->impl == 2 ? 8 : 9;
+    if (!train)                                                 // wide path, step that does not train: path launches only
+        return 5 + onf_wide_launch_count(e->onf, P, e->dev.T - 1, true, false);
     // 5 planner kernels + candidates forward + train (backward, Adam + re-pack) + path forward/input-gradient
     const EngineDev &d = e->dev;
     return 5 + onf_wide_launch_count(e->onf, P, d.NC, false, false) + onf_wide_launch_count(e->onf, P, d.NTR, true, true) + 1 +
@@ -345,8 +360,6 @@ static int validate(const nfopp_planner_config *c, OnfDims *onf, int *impl) {
     NFOPP_REQUIRE(c->checker_kind != 3 || (c->grid_rows > 1 && c->grid_cols > 1 && c->grid_cell > 0), "grid shape missing");
     NFOPP_REQUIRE(c->rng_mode == 0 || c->rng_mode == 1, "rng_mode=%d", c->rng_mode);
     if ((rc = resolve_impl(*onf, c->onf_impl, impl))) return rc;
-    NFOPP_REQUIRE(*impl != 3 || c->optimize_collision_model_freq == 1,
-                  "onf(wide) in the planner engine needs optimize_collision_model_freq == 1");
     return NFOPP_OK;
 }
 
@@ -528,6 +541,7 @@ extern "C" int nfopp_engine_create(const nfopp_planner_config *cfg, void *worksp
     e->pack_dirty = true;
     e->launches_per_step = step_launches(e, e->dev.P);
     e->launches_per_step_1 = e->launches_per_step;
+    e->launches_per_step_skip = step_launches(e, e->dev.P, false);
     e->lanes = 1;
     *out = e;
     return NFOPP_OK;
@@ -535,8 +549,7 @@ extern "C" int nfopp_engine_create(const nfopp_planner_config *cfg, void *worksp
 
 extern "C" int nfopp_engine_destroy(nfopp_engine *e) {
     if (!e) return NFOPP_OK;
-    if (e->graph_exec) cudaGraphExecDestroy(e->graph_exec);
-    if (e->graph) cudaGraphDestroy(e->graph);
+    drop_graphs(e);
     for (cudaStream_t st : e->lane_streams) cudaStreamDestroy(st);
     for (cudaEvent_t ev : e->lane_events) cudaEventDestroy(ev);
     delete e;
@@ -676,8 +689,12 @@ static const char *const kStepKernelNames[9] = {"sample_pre", "onf_forward_candi
                                                 "onf_train_fwd_bwd", "onf_reduce_adam", "traj_pre",
                                                 "onf_path_fwd_dgrad", "traj_post", "tick"};
 
-static int enqueue_step(nfopp_engine *e, const EngineDev &d, cudaStream_t s, cudaEvent_t *ev = nullptr, bool tick = true) {
+// train_host: the host's copy of StepParams::do_train for this step.  Only the wide path looks at it (its ONF launches for
+// the candidates and the training update are left out of a step that does not train); the other paths skip on the device.
+static int enqueue_step(nfopp_engine *e, const EngineDev &d, cudaStream_t s, cudaEvent_t *ev = nullptr, bool tick = true,
+                        bool train_host = true) {
     int rc;
+    const bool skip_onf_train = e->impl == 3 && !train_host;
     int evi = 0;
 #define NFOPP_MARK() do { if (ev) NFOPP_CHECK_CUDA(cudaEventRecord(ev[evi++], s)); } while (0)
     NFOPP_MARK();
@@ -685,7 +702,7 @@ static int enqueue_step(nfopp_engine *e, const EngineDev &d, cudaStream_t s, cud
     if ((rc = launch_sample_pre(d, s))) return rc;
     NFOPP_MARK();
     // (2) ONF forward on the candidates (resampling weights)  :123-125   [skipped on device when !do_train]
-    {
+    if (!skip_onf_train) {
         OnfArgs a{};
         a.d = e->onf; a.weights = d.onf_w; a.x = d.cand_x; a.count = d.cand_n; a.n = d.NC; a.x_stride = d.D;
         a.z_out = d.cand_z; a.sp = d.sp;
@@ -696,7 +713,12 @@ static int enqueue_step(nfopp_engine *e, const EngineDev &d, cudaStream_t s, cud
     if ((rc = launch_resample_label(d, 1, s))) return rc;
     NFOPP_MARK();
     // (4,5) BCE training step of the ONF: fwd+bwd per tile, then reduce + Adam   :83-90
-    if ((rc = enqueue_train(e, d, false, s, ev ? &ev[evi] : nullptr))) return rc;
+    if (!skip_onf_train) {
+        if ((rc = enqueue_train(e, d, false, s, ev ? &ev[evi] : nullptr))) return rc;
+    } else if (ev) {
+        NFOPP_CHECK_CUDA(cudaEventRecord(ev[evi], s));
+        NFOPP_CHECK_CUDA(cudaEventRecord(ev[evi + 1], s));
+    }
     if (ev) evi += 2;
     // (6) collision sample points on the path                 :113-117 / constrained:78-83
     if ((rc = launch_traj_pre(d, s))) return rc;
@@ -723,9 +745,9 @@ static int enqueue_step(nfopp_engine *e, const EngineDev &d, cudaStream_t s, cud
 
 // one step of all problems inside a stream capture: lanes > 1 fork the problem ranges onto the lane streams and join them
 // before the (single) counter tick
-static int enqueue_step_lanes(nfopp_engine *e, cudaStream_t s) {
+static int enqueue_step_lanes(nfopp_engine *e, cudaStream_t s, bool train_host = true) {
     const int L = e->lanes, P = e->dev.P;
-    if (L <= 1) return enqueue_step(e, e->dev, s);
+    if (L <= 1) return enqueue_step(e, e->dev, s, nullptr, true, train_host);
     int rc = NFOPP_OK;
     NFOPP_CHECK_CUDA(cudaEventRecord(e->lane_events[0], s));
     for (int l = 0; l < L && !rc; ++l) {
@@ -733,7 +755,7 @@ static int enqueue_step_lanes(nfopp_engine *e, cudaStream_t s) {
         const EngineDev d = slice_problems(e, p0, p1 - p0, l);
         cudaStream_t ls = l == 0 ? s : e->lane_streams[l];
         if (l > 0) NFOPP_CHECK_CUDA(cudaStreamWaitEvent(ls, e->lane_events[0], 0));
-        rc = enqueue_step(e, d, ls, nullptr, false);
+        rc = enqueue_step(e, d, ls, nullptr, false, train_host);
         if (l > 0 && !rc) NFOPP_CHECK_CUDA(cudaEventRecord(e->lane_events[l], ls));
     }
     for (int l = 1; l < L; ++l) NFOPP_CHECK_CUDA(cudaStreamWaitEvent(s, e->lane_events[l], 0));   // (joins even after an error)
@@ -758,8 +780,7 @@ extern "C" int nfopp_engine_set_lanes(nfopp_engine *e, int lanes) {
                       stride * lanes, have);
         e->lane_ws_stride = stride;
     }
-    if (e->graph_exec) { cudaGraphExecDestroy(e->graph_exec); e->graph_exec = nullptr; }
-    if (e->graph) { cudaGraphDestroy(e->graph); e->graph = nullptr; }
+    drop_graphs(e);
     while ((int)e->lane_streams.size() < lanes) {
         cudaStream_t st = nullptr;
         cudaEvent_t ev = nullptr;
@@ -770,9 +791,11 @@ extern "C" int nfopp_engine_set_lanes(nfopp_engine *e, int lanes) {
     }
     e->lanes = lanes;
     e->launches_per_step = 1;                                  // the tick; everything else runs once per lane
+    e->launches_per_step_skip = 1;
     for (int l = 0; l < lanes; ++l) {
         const int P = e->dev.P, p0 = (int)((long long)P * l / lanes), p1 = (int)((long long)P * (l + 1) / lanes);
         e->launches_per_step += step_launches(e, p1 - p0) - 1;
+        e->launches_per_step_skip += step_launches(e, p1 - p0, false) - 1;
     }
     return NFOPP_OK;
 }
@@ -789,8 +812,7 @@ extern "C" int nfopp_engine_set_bounds(nfopp_engine *e, const double *sample_bor
     }
     fill_dev_config(e);
     // kernel arguments are captured by value: the next graphed step re-captures
-    if (e->graph_exec) { cudaGraphExecDestroy(e->graph_exec); e->graph_exec = nullptr; }
-    if (e->graph) { cudaGraphDestroy(e->graph); e->graph = nullptr; }
+    drop_graphs(e);
     return NFOPP_OK;
 }
 
@@ -819,19 +841,25 @@ extern "C" int nfopp_engine_step(nfopp_engine *e, int n_steps, int use_graph, vo
     int rc;
     if (e->sp_dirty && (rc = upload_step_params(e, s))) return rc;
     if ((rc = ensure_packed(e, s))) return rc;
-    if (use_graph && !e->graph_exec) {
+    const bool two_graphs = e->impl == 3 && e->cfg.optimize_collision_model_freq > 1;
+    auto capture = [&](bool train_host, cudaGraph_t *g, cudaGraphExec_t *ge) -> int {
         NFOPP_REQUIRE(s != nullptr, "step: CUDA-graph capture needs a non-default stream");
         NFOPP_CHECK_CUDA(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
-        rc = enqueue_step_lanes(e, s);
-        cudaError_t ce = cudaStreamEndCapture(s, &e->graph);
-        if (rc) return rc;
+        const int rc2 = enqueue_step_lanes(e, s, train_host);
+        cudaError_t ce = cudaStreamEndCapture(s, g);
+        if (rc2) return rc2;
         NFOPP_CHECK_CUDA(ce);
-        NFOPP_CHECK_CUDA(cudaGraphInstantiate(&e->graph_exec, e->graph, 0));
-    }
+        NFOPP_CHECK_CUDA(cudaGraphInstantiate(ge, *g, 0));
+        return NFOPP_OK;
+    };
+    if (use_graph && !e->graph_exec && (rc = capture(true, &e->graph, &e->graph_exec))) return rc;
+    if (use_graph && two_graphs && !e->graph_exec_skip && (rc = capture(false, &e->graph_skip, &e->graph_exec_skip))) return rc;
     for (int it = 0; it < n_steps; ++it) {
+        const bool train_host = e->host_sp.do_train != 0;
+        const bool skip = two_graphs && !train_host;
         if (use_graph) {
-            NFOPP_CHECK_CUDA(cudaGraphLaunch(e->graph_exec, s));
-        } else if ((rc = enqueue_step(e, e->dev, s))) {
+            NFOPP_CHECK_CUDA(cudaGraphLaunch(skip ? e->graph_exec_skip : e->graph_exec, s));
+        } else if ((rc = enqueue_step(e, e->dev, s, nullptr, true, train_host))) {
             return rc;
         }
         StepParams &sp = e->host_sp;
@@ -839,7 +867,7 @@ extern "C" int nfopp_engine_step(nfopp_engine *e, int n_steps, int use_graph, vo
         sp.traj_step += 1;
         sp.step_count += 1;
         host_step_params(e);
-        e->launches += e->launches_per_step;
+        e->launches += skip ? e->launches_per_step_skip : e->launches_per_step;
     }
     return NFOPP_OK;
 }
@@ -852,7 +880,8 @@ extern "C" int nfopp_engine_profile_step(nfopp_engine *e, float *ms_out, int n_o
     if ((rc = ensure_packed(e, s))) return rc;
     cudaEvent_t ev[10];
     for (auto &x : ev) NFOPP_CHECK_CUDA(cudaEventCreate(&x));
-    rc = enqueue_step(e, e->dev, s, ev);
+    const bool prof_train = e->host_sp.do_train != 0;
+    rc = enqueue_step(e, e->dev, s, ev, true, prof_train);
     if (!rc) {
         cudaError_t ce = cudaStreamSynchronize(s);
         if (ce != cudaSuccess) { set_error("profile_step: %s", cudaGetErrorString(ce)); rc = NFOPP_ERR_CUDA; }

@@ -526,6 +526,44 @@ def test_wide_engine_graph_replay_and_batch_independence():
     assert not torch.equal(outs[0][0], outs[0][1])
 
 
+def test_wide_engine_with_training_every_other_step():
+    """nerf_opt_planner.py:62 on the wide path: optimize_collision_model_freq = 2 (and reparametrize_trajectory_freq = 3).  The
+    wide ONF's launches cannot be switched off by a device-side flag, so steps that do not train replay a second CUDA graph
+    without them: weights, Adam counter and replay buffer stay bit-identical over such a step while the trajectory moves;
+    graph replay == plain launches; and the run stays next to the FMA path's (same RNG streams, ONF outputs to ~1e-6)."""
+    from nfopp_b200.batched import BatchedPlanner, gridmap_wide_config
+    from nfopp_b200.test_environment_builder import TestEnvironmentBuilder as B
+    grid, _, cell = B.make_blob_grid(200, 200, 0.1, 0.015, blob_cells=12, seed=2)
+    P = 5
+    starts, goals = B.free_endpoints(grid, cell, P, seed=4, margin_cells=10)
+    outs = {}
+    for impl, graph in (("wide", False), ("wide", True), ("fma", True)):
+        cfg = gridmap_wide_config(P, rows=200, cols=200, cell=cell, seed=9, hidden=64, layers=2, onf_impl=impl,
+                                  optimize_collision_model_freq=2, reparametrize_trajectory_freq=3)
+        bp = BatchedPlanner(cfg, lanes=1)
+        bp.init(starts, goals, grids=grid)
+        eng = bp.engine
+        bp.step(1, graph=graph)                                   # step_count 0: trains
+        torch.cuda.synchronize()
+        assert eng.counter("onf_step") == 1
+        w1, buf1, traj1 = eng["onf_w"].clone(), eng["buf_pos"].clone(), eng["traj"].clone()
+        bp.step(1, graph=graph)                                   # step_count 1: no training
+        torch.cuda.synchronize()
+        assert eng.counter("onf_step") == 1 and eng.counter("step_count") == 2
+        assert torch.equal(eng["onf_w"], w1) and torch.equal(eng["buf_pos"], buf1)
+        assert not torch.equal(eng["traj"], traj1)
+        bp.step(3, graph=graph)                                   # step_count 2, 3, 4: trains, skips, trains
+        torch.cuda.synchronize()
+        assert eng.counter("onf_step") == 3 and eng.counter("step_count") == 5
+        assert not torch.equal(eng["onf_w"], w1)
+        assert int(np.abs(bp.status()).max()) == 0
+        outs[(impl, graph)] = (bp.paths().clone(), eng["onf_w"].clone())
+    assert torch.equal(outs[("wide", False)][0], outs[("wide", True)][0])
+    assert torch.equal(outs[("wide", False)][1], outs[("wide", True)][1])
+    dpath = (outs[("wide", True)][0] - outs[("fma", True)][0]).abs().max().item()
+    assert dpath < 1e-2, dpath
+
+
 # ---------------------------------------------------------------------------------------- path evaluation (SURVEY 8f-1)
 @pytest.mark.parametrize("name,k", [("car", 4), ("corridor", 7), ("holonomic", 1)])
 def test_evaluate_paths_matches_oracle(name, k):
