@@ -277,11 +277,11 @@ __global__ void __launch_bounds__(SAMPLE_THREADS) warm_sample_kernel(const Engin
     if (threadIdx.x == 0) e.train_n[p] = e.NW;
 }
 
-constexpr int RESAMPLE_THREADS = 256;
+constexpr int RESAMPLE_THREADS = 128;
 
 // nerf_opt_planner.py:122-133 (resample the replay buffer) + :86,93-96 (ground-truth labels of the train set)
 // resample == 0: labelling only (warm-up iterations)
-__global__ void __launch_bounds__(RESAMPLE_THREADS, 4) resample_label_kernel(const EngineDev e, int resample) {
+__global__ void __launch_bounds__(RESAMPLE_THREADS, 8) resample_label_kernel(const EngineDev e, int resample) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const StepParams sp = *e.sp;
     if (resample && !sp.do_train) return;

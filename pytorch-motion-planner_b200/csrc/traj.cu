@@ -51,7 +51,7 @@ __device__ __forceinline__ float relu_f(float v) { return v > 0.f ? v : 0.f; }
 struct TrajSmem {
     float *full;     // [(T+2)*D]
     float *hi, *lo;  // per segment: gradient contribution to node j+1 / node j, [(T+1)*D] each
-    float *g;        // raw gradient per trajectory point [T*D]
+    float *g;        // raw gradient per trajectory point [T][4] (x, y, theta | 0, pad): one 16-byte read per point in the mat-vec
     float *gm;       // g_mu [T]
     float *cseg;     // non-holonomic residual per segment [T+1]
     float *wd;       // wrapped dtheta per segment / segment length / cdf [T+2]
@@ -65,7 +65,8 @@ __device__ TrajSmem carve_traj(float *base, int T, int D) {
     s.full = p; p += (T + 2) * D;
     s.hi = p; p += (T + 1) * D;
     s.lo = p; p += (T + 1) * D;
-    s.g = p; p += T * D;
+    p += (4 - ((p - base) & 3)) & 3;             // 16-byte aligned (base is)
+    s.g = p; p += T * 4;
     s.gm = p; p += T;
     s.cseg = p; p += T + 1;
     s.wd = p; p += T + 2;
@@ -75,7 +76,7 @@ __device__ TrajSmem carve_traj(float *base, int T, int D) {
 }
 
 static size_t traj_smem_bytes(int T, int D) {
-    return (size_t)((T + 2) * D + 2 * (T + 1) * D + T * D + T + (T + 1) + 2 * (T + 2) + 4) * sizeof(float);
+    return (size_t)((T + 2) * D + 2 * (T + 1) * D + 3 + T * 4 + T + (T + 1) + 2 * (T + 2) + 4) * sizeof(float);
 }
 
 // Writes the updated path / multipliers held in shared memory (s.full, s.gm = mu, s.cseg = lambda) back to
@@ -245,7 +246,7 @@ __global__ void __launch_bounds__(TRAJ_THREADS) traj_post_kernel(const EngineDev
             for (int d = 0; d < D; ++d) g[d] += omt * gq[(i - 1) * D + d];
             gmu += omt * tanhf(pz[i - 1]);
         }
-        for (int d = 0; d < D; ++d) s.g[i * D + d] = g[d];
+        *reinterpret_cast<float4 *>(s.g + 4 * i) = make_float4(g[0], g[1], D == 3 ? g[2] : 0.f, 0.f);
         s.gm[i] = gmu;
     }
     __syncthreads();
@@ -260,12 +261,15 @@ __global__ void __launch_bounds__(TRAJ_THREADS) traj_post_kernel(const EngineDev
 #pragma unroll
             for (int u = 0; u < 10; ++u) h[u] = __ldg(e.inv_hessian_t + (size_t)(j + u) * T + i);   // = inv_hessian[i][j + u], coalesced
 #pragma unroll
-            for (int u = 0; u < 10; ++u)
-                for (int d = 0; d < D; ++d) acc[d] = fmaf(h[u], s.g[(j + u) * D + d], acc[d]);
+            for (int u = 0; u < 10; ++u) {
+                const float4 g4 = *reinterpret_cast<const float4 *>(s.g + 4 * (j + u));
+                acc[0] = fmaf(h[u], g4.x, acc[0]); acc[1] = fmaf(h[u], g4.y, acc[1]); acc[2] = fmaf(h[u], g4.z, acc[2]);
+            }
         }
         for (; j < T; ++j) {
             const float h = __ldg(e.inv_hessian_t + (size_t)j * T + i);
-            for (int d = 0; d < D; ++d) acc[d] = fmaf(h, s.g[j * D + d], acc[d]);
+            const float4 g4 = *reinterpret_cast<const float4 *>(s.g + 4 * j);
+            acc[0] = fmaf(h, g4.x, acc[0]); acc[1] = fmaf(h, g4.y, acc[1]); acc[2] = fmaf(h, g4.z, acc[2]);
         }
         for (int d = 0; d < D; ++d) {
             const size_t o = (size_t)p * T * D + i * D + d;
