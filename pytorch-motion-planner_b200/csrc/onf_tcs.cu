@@ -739,6 +739,15 @@ __device__ __forceinline__ void ts_adam_problem(const OnfTsArgs &a, const float 
     cp_async_wait<0>();
 }
 
+// The CTA's last problem has no further tiles to hide its update under: the sixteen worker warps join the optimiser warps for
+// it (ranks TS_OPT_WARPS ..).  With every SM in the same launch that burst is HBM-bound and the extra warps gain nothing
+// (measured), but the engine's lanes run 2-4 launches side by side on a share of the SMs each, whose tails fall at different
+// times.  NFOPP_TCS_DBG bit 7 (128) switches it off for launches with several problems per CTA.
+__device__ __forceinline__ bool ts_join_last(const OnfTsArgs &a, int p) {
+    if (a.P <= (int)gridDim.x) return true;
+    return !(a.dbg & 128) && p + (int)gridDim.x >= a.P;
+}
+
 // the optimiser warps: problem after problem as the workers hand the gradients over.  (Letting the sixteen worker warps join
 // in for the CTA's last problem, which has nothing to hide under, does not shorten it: all CTAs reach that point together and
 // the 148 x 1.1 MB burst is HBM-bound - measured.)
@@ -767,7 +776,7 @@ __device__ __forceinline__ void ts_optimizer(const OnfTsArgs &a, const TsShared 
 #ifdef NFOPP_TC_TRACE
         if (!(a.dbg & 4))
 #endif
-        ts_adam_problem(a, G, p, wo, a.P <= (int)gridDim.x ? TS_OPT_WARPS + TS_WORKERS / 32 : TS_OPT_WARPS, lane, s.aring + wo * TS_ARING);
+        ts_adam_problem(a, G, p, wo, ts_join_last(a, p) ? TS_OPT_WARPS + TS_WORKERS / 32 : TS_OPT_WARPS, lane, s.aring + wo * TS_ARING);
         // every gradient value this warp needs is in its registers: once all warps say so the workers may overwrite the
         // hand-over buffer
         __syncwarp();
@@ -1299,7 +1308,7 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
                 // share the update.  (With several problems per CTA the last update is HBM-bound - every CTA reaches it at the
                 // same time - and the extra warps measured no gain.)
                 // (their cp.async rings sit in the encoding-ring / weight-ring regions: no further problem, nothing streams)
-                if (fused_adam && a.P <= (int)gridDim.x)
+                if (fused_adam && ts_join_last(a, p))
                     ts_adam_problem(a, G, p, TS_OPT_WARPS + warp, TS_OPT_WARPS + TS_WORKERS / 32, lane, s.r + warp * TS_ARING);
                 ++it;
             }
