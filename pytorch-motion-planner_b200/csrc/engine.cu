@@ -436,6 +436,7 @@ static int build_layout(nfopp_engine *e) {
     add_buffer(e, "choice_idx", &d.choice_idx, 'i', P, C);
     add_buffer(e, "choice_used", &d.choice_used, 'i', P);
     add_buffer(e, "status", &d.status, 'i', P);
+    add_buffer(e, "frozen", &d.frozen, 'i', P);
     add_buffer(e, "inv_hessian_t", &d.inv_hessian_t, 'f', T, T);
     add_buffer(e, "lin_s", &d.lin_s, 'f', T);
     if (c.checker_kind == 1 || c.checker_kind == 2) {
@@ -668,7 +669,7 @@ static int enqueue_train(nfopp_engine *e, const EngineDev &d, bool warm, cudaStr
     if (ev) NFOPP_CHECK_CUDA(cudaEventRecord(ev[0], s));
     if (e->impl == 3) {
         // Adam + operand-copy refresh in one pass over w/m/v/grad
-        if ((rc = onf_wide_adam_pack(e->onf, d.onf_w, d.onf_m, d.onf_v, d.onf_gpart, d.onf_wp, d.sp, warm, w1, beta2, w2, eps, d.P, s)))
+        if ((rc = onf_wide_adam_pack(e->onf, d.onf_w, d.onf_m, d.onf_v, d.onf_gpart, d.onf_wp, d.sp, warm, w1, beta2, w2, eps, d.P, s, d.train_n)))
             return rc;
         if (ev) NFOPP_CHECK_CUDA(cudaEventRecord(ev[1], s));
         return NFOPP_OK;

@@ -59,6 +59,7 @@ struct EngineDev {
     float *path_q, *path_mu, *path_z, *path_gq, *path_t;
     int32_t *path_n;
     int32_t *choice_idx, *choice_used, *status;
+    int32_t *frozen;                        // [P] != 0: the problem is finished - no kernel of a step touches its state any more
     // constants
     float *inv_hessian_t, *lin_s;
     double *obstacles;

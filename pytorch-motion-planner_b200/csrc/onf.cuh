@@ -80,7 +80,8 @@ int onf_wide_pack(const OnfDims &d, const float *weights, unsigned char *packed,
 int onf_wide_launch(const OnfArgs &a, const OnfWideExtra &x, int P, cudaStream_t stream);
 int onf_wide_launch_count(const OnfDims &d, int P, int n, bool want_bwd, bool want_wgrad);
 int onf_wide_adam_pack(const OnfDims &d, float *weights, float *m, float *v, const float *grad, unsigned char *packed,
-                       const StepParams *sp, int warm, float w1, float beta2, float w2, float eps, int P, cudaStream_t stream);
+                       const StepParams *sp, int warm, float w1, float beta2, float w2, float eps, int P, cudaStream_t stream,
+                       const int32_t *count = nullptr);
 
 int onf_fma_tile_points(const OnfDims &d);          // 32, 16 or 0 (does not fit)
 int onf_fma_prepare(const OnfDims &d);               // one-time kernel attributes (outside graph capture)

@@ -400,6 +400,7 @@ __global__ void __launch_bounds__(256) onf_adam_kernel(const AdamArgs a) {
         bc2_sqrt = a.sp->onf_bc2_sqrt;
     }
     const int cnt = a.count ? a.count[p] : a.n;
+    if (a.sp && !a.grad_out && cnt <= 0) return;     // engine: a finished (frozen) problem has an empty training set - no update
     const int tiles = min(a.tiles, (cnt + a.tp - 1) / a.tp);
     const float *gp = a.gpart + (size_t)p * a.tiles * a.n_params + 4 * i4;
     float4 g = make_float4(0, 0, 0, 0);

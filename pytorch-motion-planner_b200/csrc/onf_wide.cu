@@ -122,12 +122,14 @@ struct WidePackArgs {
     float *adam_w, *adam_m, *adam_v;
     const float *grad;
     const StepParams *sp;
+    const int32_t *count;        // fused Adam: problems with count <= 0 (finished / frozen) are left untouched
     int warm;
     float w1, beta2, w2, eps;
 };
 
 __global__ void __launch_bounds__(256) wide_pack_kernel(const WidePackArgs a) {
     const int p = blockIdx.y;
+    if (a.adam_m && a.count && a.count[p] <= 0) return;
     const WideDims &w = a.w;
     const float *W = a.weights + (size_t)p * a.d.lay.n_params;
     unsigned char *out = a.packed + (size_t)p * ((w.packed_bytes + 255) / 256 * 256);
@@ -1671,12 +1673,14 @@ static int chain_max_clusters(int CL) {
 
 // engine: Adam on the whole blob fused with the refresh of the operand copies (one pass over w/m/v/grad)
 int onf_wide_adam_pack(const OnfDims &d, float *weights, float *m, float *v, const float *grad, unsigned char *packed,
-                       const StepParams *sp, int warm, float w1, float beta2, float w2, float eps, int P, cudaStream_t stream) {
+                       const StepParams *sp, int warm, float w1, float beta2, float w2, float eps, int P, cudaStream_t stream,
+                       const int32_t *count) {
     WidePackArgs a{};
     a.d = d;
     NFOPP_REQUIRE(make_wide_dims(d, &a.w), "onf(wide): unsupported network shape");
     NFOPP_REQUIRE(weights && m && v && grad && packed && sp, "onf_wide_adam_pack: bad arguments");
     a.weights = weights; a.packed = packed; a.adam_w = weights; a.adam_m = m; a.adam_v = v; a.grad = grad; a.sp = sp; a.warm = warm;
+    a.count = count;
     a.w1 = w1; a.beta2 = beta2; a.w2 = w2; a.eps = eps;
     int max_tiles = 0;
     for (int l = 0; l < a.w.L; ++l) max_tiles = max(max_tiles, ((a.w.Hp + 31) / 32) * ((a.w.kin[l] / 8 + 7) / 8));

@@ -170,6 +170,10 @@ __global__ void __launch_bounds__(SAMPLE_THREADS) sample_pre_kernel(const Engine
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float *s_prev = reinterpret_cast<float *>(smem_raw);      // [T*D]
     const StepParams sp = *e.sp;
+    if (e.frozen[blockIdx.x]) {                      // finished problem: no candidates -> the ONF launches skip it
+        if (threadIdx.x == 0) e.cand_n[blockIdx.x] = 0;
+        return;
+    }
     if (!sp.do_train) return;
     const int p = blockIdx.x, tid = threadIdx.x, T = e.T, D = e.D, n = T - 1;
     const bool inj = e.rng_mode == 1;
@@ -284,6 +288,10 @@ constexpr int RESAMPLE_THREADS = 128;
 __global__ void __launch_bounds__(RESAMPLE_THREADS, 8) resample_label_kernel(const EngineDev e, int resample) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const StepParams sp = *e.sp;
+    if (resample && e.frozen[blockIdx.x]) {          // finished problem: empty training set -> no ONF update
+        if (threadIdx.x == 0) e.train_n[blockIdx.x] = 0;
+        return;
+    }
     if (resample && !sp.do_train) return;
     const int p = blockIdx.x, tid = threadIdx.x, D = e.D, n = e.T - 1, C = e.C;
     ChoiceScratch sc = carve_choice(smem_raw, e.NC, C);

@@ -17,6 +17,10 @@ constexpr int TRAJ_THREADS = 128;
 __global__ void __launch_bounds__(TRAJ_THREADS) traj_pre_kernel(const EngineDev e) {
     const StepParams sp = *e.sp;
     const int p = blockIdx.x, T = e.T, D = e.D, n = T - 1;
+    if (e.frozen[p]) {                               // finished problem: no path samples -> the ONF launch skips it
+        if (threadIdx.x == 0) e.path_n[p] = 0;
+        return;
+    }
     const float *X = e.traj + (size_t)p * T * D;
     for (int i = threadIdx.x; i < n; i += TRAJ_THREADS) {
         float t;
@@ -157,6 +161,7 @@ __global__ void __launch_bounds__(TRAJ_THREADS) traj_post_kernel(const EngineDev
     extern __shared__ __align__(16) float smem_f[];
     const StepParams sp = *e.sp;
     const int p = blockIdx.x, tid = threadIdx.x, T = e.T, D = e.D, n = T - 1;
+    if (e.frozen[p]) return;                         // finished problem: trajectory, moments and multipliers stay as they are
     TrajSmem s = carve_traj(smem_f, T, D);
     float *X = e.traj + (size_t)p * T * D;
     const float *gq = e.path_gq + (size_t)p * n * D;

@@ -156,18 +156,24 @@ class BatchedPlanner:
         from .path_postprocessor import PathPostprocessor
         return PathPostprocessor(minimal_distance, distance_step, self.device).process_batch(self.engine.paths(), max_points)
 
-    def solve(self, max_iterations=1000, min_iterations=200, check_every=50, samples_per_segment=4, graph=True):
+    def solve(self, max_iterations=1000, min_iterations=200, check_every=50, samples_per_segment=4, graph=True,
+              freeze_finished=True):
         """scripts/run_bench_mr.py:109-131 for all problems at once: step, and every `check_every` iterations past
         `min_iterations` evaluate every path on the device; a problem keeps its shortest collision-free path and is
         DONE once a later collision-free path is no shorter (the reference's `break`).  Problems are independent, so
-        the batch keeps stepping until all are done or `max_iterations` is reached; finished problems simply stop
-        being recorded.  Returns dict(paths [P,T+2,D], solved bool [P], length [P], iterations int [P])."""
+        the batch keeps stepping until all are done or `max_iterations` is reached.  A finished problem is FROZEN
+        (engine buffer `frozen`): as in the reference, where every problem is its own run that stops at the `break`, no
+        kernel touches it any more and the ONF launches skip it, so the remaining steps get cheaper as problems finish
+        (freeze_finished=False keeps stepping them; the results are identical, problems being independent).
+        Returns dict(paths [P,T+2,D], solved bool [P], length [P], iterations int [P])."""
         P, dev = self.config.problems, self.device
         best_len = torch.full((P,), float("inf"), device=dev)
         best_path = self.engine.paths().clone()
         stop_path, stop_len = best_path.clone(), torch.zeros(P, device=dev)
         done = torch.zeros(P, dtype=torch.bool, device=dev)
         iters = torch.full((P,), max_iterations, dtype=torch.int32, device=dev)
+        frozen = self.engine["frozen"]
+        frozen.zero_()
         i = 0
         while i < max_iterations:
             # the reference checks after step i (0-based) when i > min_iterations and i % check_every == 0
@@ -190,6 +196,8 @@ class BatchedPlanner:
                 stop_len = torch.where(stop, length, stop_len)
             iters = torch.where(stop, torch.full_like(iters, i), iters)
             done |= stop
+            if freeze_finished:
+                frozen.copy_(done.to(frozen.dtype))
             if bool(done.all()):
                 break
         collides, length, _ = self.engine.evaluate_paths(samples_per_segment)
@@ -199,6 +207,7 @@ class BatchedPlanner:
         paths[use_best] = best_path[use_best]
         length = torch.where(done, stop_len, torch.where(use_best, best_len, length))
         solved = done | ~collides | use_best
+        frozen.zero_()                                      # later step() calls move every problem again
         return dict(paths=paths, solved=solved, length=length, iterations=iters, steps_run=i)
 
     def gather_paths(self) -> torch.Tensor:

@@ -611,6 +611,54 @@ def test_batched_solve_loop_matches_reference_bookkeeping():
     assert ((its == 600) | ((its - 1) % 50 == 0)).all() and (its[its < 600] > 200).all()
 
 
+def test_finished_problems_are_frozen_without_disturbing_the_others():
+    """In the reference every problem is its own run that stops at the `break` of run_bench_mr.py:109-131.  The batched
+    engine freezes a finished problem (buffer `frozen`): no kernel touches its state any more, the ONF launches skip it,
+    and - problems being independent - every other problem continues bit for bit as if nothing had been frozen.  Checked
+    on all three ONF paths, then end to end: solve() with and without freezing returns identical results."""
+    from nfopp_b200.batched import BatchedPlanner, corridor_config
+    from nfopp_b200.test_environment_builder import TestEnvironmentBuilder as B
+    P = 12
+    starts, goals, _, obstacles = B.make_corridor_batch(P, seed=1)
+    names = ["traj", "traj_m", "traj_v", "lam", "mu", "onf_w", "onf_m", "onf_v", "buf_pos", "buf_age"]
+    for impl, hidden in (("tensor", 100), ("fma", 100), ("wide", 64)):
+        runs = []
+        for freeze in (False, True):
+            from dataclasses import replace
+            cfg = corridor_config(P, seed=5, onf_impl=impl)
+            cfg = replace(cfg, onf=replace(cfg.onf, hidden=hidden))
+            bp = BatchedPlanner(cfg, lanes=2 if impl == "tensor" else 1)
+            bp.init(starts, goals, obstacles=obstacles)
+            bp.step(3)
+            eng = bp.engine
+            before = {k: eng[k].clone() for k in names}
+            if freeze:
+                eng["frozen"][::3] = 1
+            bp.step(4)
+            torch.cuda.synchronize()
+            runs.append((before, {k: eng[k].clone() for k in names}))
+            assert int(np.abs(bp.status()).max()) == 0
+        (b0, a0), (b1, a1) = runs
+        for k in names:
+            assert torch.equal(b0[k], b1[k]), (impl, k)
+            assert torch.equal(a1[k][::3], b1[k][::3]), (impl, k, "a frozen problem moved")
+            keep = torch.ones(P, dtype=torch.bool)
+            keep[::3] = False
+            assert torch.equal(a1[k][keep], a0[k][keep]), (impl, k, "freezing disturbed another problem")
+            assert not torch.equal(a0[k][::3], b0[k][::3]) or k in ("buf_pos", "buf_age"), (impl, k)
+    P = 48
+    starts, goals, _, obstacles = B.make_corridor_batch(P, seed=0)
+    outs = []
+    for freeze in (False, True):
+        bp = BatchedPlanner(corridor_config(P, seed=3))
+        bp.init(starts, goals, obstacles=obstacles)
+        outs.append(bp.solve(max_iterations=500, min_iterations=200, check_every=50, freeze_finished=freeze))
+        assert int(bp.engine["frozen"].abs().max()) == 0
+    assert int(outs[0]["solved"].sum()) > 0 and int((outs[0]["iterations"] < 500).sum()) > 0
+    for k in ("paths", "solved", "length", "iterations"):
+        assert torch.equal(outs[0][k], outs[1][k]), k
+
+
 # ---------------------------------------------------------------------------------------- path statistics (SURVEY 8f-4)
 @pytest.mark.parametrize("name", ["car", "corridor", "holonomic"])
 def test_path_statistics_match_oracle(name):
