@@ -393,6 +393,7 @@ __device__ __forceinline__ void ts_producer(const OnfTsArgs &a, const TsShared &
             }
             TS_TRACE(2, 1);
             if (tile == n_tiles - 1) {
+                // (prefetching the CTA's FIRST problem here for the step's next ONF launch was measured: no effect)
                 // L2 prefetches, issued late so that the lines are still resident when they are used (ncu: issued at the
                 // start of the problem, a wave's 148 x 0.8 MB outlived the L2 and was read from HBM twice):
                 const int pn = next_problem(p);
@@ -940,6 +941,7 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
             float acc_db1 = 0.f, acc_db2 = 0.f, acc_dw3 = 0.f, acc_db3 = 0.f;
             float fa0 = 0.f, fb0 = 0.f, fc0 = 0.f, fa1 = 0.f, fb1 = 0.f, fc1 = 0.f;
             TS_TRACE(0, 1);
+            if (np == 1) TS_TRACE(0, 31);
             for (int tile = 0; tile < n_tiles; ++tile) {
                 const int n0 = tile * TS_NT;
                 const int nv = min(TS_NT, cnt - n0);
@@ -957,6 +959,7 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
                 else if (p_next < a.P) fetch_inputs(p_next, tid, cnt_next);
                 ts_worker_sync();
                 TS_TRACE(0, 2);
+                if (np == 1 && tile == 0) TS_TRACE(0, 32);
                 // ---- P1: encoding (CUDA cores) feeding fwd1 in slots of 64 features: thread = (point, feature octets g, g+4) ----
                 {
                     const int g = tid / Nt, n = tid - g * Nt;
@@ -984,6 +987,7 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
                     }
                 }
                 TS_TRACE(0, 3);
+                if (np == 1 && tile == 0) TS_TRACE(0, 33);
                 // From here on the tile is two halves (points 0..63 | 64..Nt-1) with their own done / ready barriers: a warp owns
                 // ONE 16-point chunk per half (chunk 4 h + cq), and the epilogue of one half runs under the MMAs of the other.
                 const int nh = (want_bwd && Nt > TS_HALF) ? 2 : 1;
@@ -994,6 +998,7 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
                 for (int h = 0; h < nh; ++h) {
                     ts_wait(s.done + h, (h ? ndone1++ : ndone0++));
                     TS_TRACE(0, 4);
+                    if (np == 1 && tile == 0 && h == 0) TS_TRACE(0, 34);
                     TS_HALF_CHUNKS(ch) {
                         const int c0 = 16 * ch;
                         float v[16];
@@ -1014,6 +1019,7 @@ __global__ void __launch_bounds__(TS_THREADS, 1) onf_tcs_kernel(const OnfTsArgs 
                     ts_signal(s.ready + h);                   // -> fwd2 of this half
                 }
                 TS_TRACE(0, 5);
+                if (np == 1 && tile == 0) TS_TRACE(0, 35);
                 // ---- P3 / P4: epilogue 2: logit partial sums over the hidden units of each lane quarter, z and dL/dz per
                 // point, then gH2 = dL/dz * w3 * 1[h2 > 0] (scaled, fp16 hi + lo) -> old encoding ring ----
     #pragma unroll 1

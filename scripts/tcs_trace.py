@@ -19,7 +19,7 @@ from nfopp_b200 import _lib as L  # noqa: E402
 L.LIB_PATH = os.path.join(os.path.dirname(L.LIB_PATH), "libnfopp_trace.so")
 import bench as B  # noqa: E402
 
-WORKER = {0: "start", 29: "first problem done", 30: "last problem begins", 1: "setup done (last problem)", 2: "inputs staged", 3: "encode done", 4: "fwd1 done", 5: "ep1 signalled",
+WORKER = {0: "start", 31: "P0 setup done", 32: "P0 inputs staged", 33: "P0 encode done", 34: "P0 fwd1 done", 35: "P0 ep1 signalled", 29: "first problem done", 30: "last problem begins", 1: "setup done (last problem)", 2: "inputs staged", 3: "encode done", 4: "fwd1 done", 5: "ep1 signalled",
           6: "fwd2 done", 7: "logit partials", 8: "dL/dz", 9: "gH2 signalled", 10: "wgrad2+dgrad2 done", 11: "ep3 signalled",
           12: "dgrad1(0) done", 13: "ep4(0) signalled", 14: "dgrad1(1) done", 15: "ep4(1) signalled", 16: "wgrad1 done",
           20: "tiles done", 22: "hand-over buffer free", 24: "partials staged", 25: "dW1 out", 26: "dW2 out", 27: "gradient handed over", 28: "CTA done"}
@@ -54,7 +54,7 @@ def main():
             print(f"== {kname} / {cname}")
             for role, names in enumerate([WORKER, ISSUER, PRODUCER, OPTIMISER]):
                 prev, parts = t0, []
-                for k in (sorted(names) if role else [0, 29, 30] + [k for k in sorted(names) if k not in (0, 29, 30)]):
+                for k in (sorted(names) if role else [0, 31, 32, 33, 34, 35, 29, 30] + [k for k in sorted(names) if k not in (0, 29, 30, 31, 32, 33, 34, 35)]):
                     v = t[role, k]
                     if v == 0 or v < t0:
                         continue
